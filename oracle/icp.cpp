@@ -1,0 +1,270 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see oracle.h).
+//
+// Restatement of PointMatcher<float>::ICP — libpointmatcher/pointmatcher/ICP.cpp:813-1349 (compute,
+// initReference, computeWithTransformedReference, degeneracyAwareness = kNone) and of the transformation
+// checkers — TransformationCheckersImpl.cpp:46-151, TransformationChecker.cpp:109-121.
+#include "oracle.h"
+#include "la_small.hpp"
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <vector>
+
+namespace {
+
+typedef float M4[16];  // column-major
+
+void eye4(float* T) {
+  for (int i = 0; i < 16; ++i) T[i] = 0.f;
+  T[0] = T[5] = T[10] = T[15] = 1.f;
+}
+void mul4(const float* A, const float* B, float* C) {  // C = A * B, depth-sequential accumulation
+  float R[16];
+  for (int j = 0; j < 4; ++j)
+    for (int i = 0; i < 4; ++i) {
+      float acc = A[i] * B[4 * j];
+      acc = acc + A[i + 4] * B[1 + 4 * j];
+      acc = acc + A[i + 8] * B[2 + 4 * j];
+      acc = acc + A[i + 12] * B[3 + 4 * j];
+      R[i + 4 * j] = acc;
+    }
+  std::memcpy(C, R, sizeof(R));
+}
+bool inv4(const float* A, float* Ainv) {  // Gauss-Jordan with partial pivoting (plays PartialPivLU::inverse)
+  float a[4][8];
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j) { a[i][j] = A[i + 4 * j]; a[i][4 + j] = (i == j) ? 1.f : 0.f; }
+  for (int c = 0; c < 4; ++c) {
+    int piv = c;
+    for (int r = c + 1; r < 4; ++r)
+      if (std::fabs(a[r][c]) > std::fabs(a[piv][c])) piv = r;
+    if (a[piv][c] == 0.f) return false;
+    if (piv != c)
+      for (int j = 0; j < 8; ++j) std::swap(a[piv][j], a[c][j]);
+    const float d = a[c][c];
+    for (int j = 0; j < 8; ++j) a[c][j] /= d;
+    for (int r = 0; r < 4; ++r)
+      if (r != c) {
+        const float f = a[r][c];
+        if (f != 0.f)
+          for (int j = 0; j < 8; ++j) a[r][j] -= f * a[c][j];
+      }
+  }
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j) Ainv[i + 4 * j] = a[i][4 + j];
+  return true;
+}
+
+struct Quat { float w, x, y, z; };
+
+// Eigen::Quaternion(Matrix3) — Shoemake's algorithm as in Eigen/src/Geometry/Quaternion.h
+Quat quatFromT(const float* T) {
+  auto m = [&](int i, int j) { return T[i + 4 * j]; };
+  Quat q;
+  float t = m(0, 0) + m(1, 1) + m(2, 2);
+  if (t > 0.f) {
+    t = std::sqrt(t + 1.f);
+    q.w = 0.5f * t;
+    t = 0.5f / t;
+    q.x = (m(2, 1) - m(1, 2)) * t;
+    q.y = (m(0, 2) - m(2, 0)) * t;
+    q.z = (m(1, 0) - m(0, 1)) * t;
+  } else {
+    int i = 0;
+    if (m(1, 1) > m(0, 0)) i = 1;
+    if (m(2, 2) > m(i, i)) i = 2;
+    const int j = (i + 1) % 3, k = (j + 1) % 3;
+    t = std::sqrt(m(i, i) - m(j, j) - m(k, k) + 1.f);
+    float v[3];
+    v[i] = 0.5f * t;
+    t = 0.5f / t;
+    q.w = (m(k, j) - m(j, k)) * t;
+    v[j] = (m(j, i) + m(i, j)) * t;
+    v[k] = (m(k, i) + m(i, k)) * t;
+    q.x = v[0]; q.y = v[1]; q.z = v[2];
+  }
+  return q;
+}
+// Quaternion::angularDistance (Eigen >= 3.3): d = a * conj(b); 2 * atan2(|d.vec|, |d.w|)
+float angularDistance(const Quat& a, const Quat& b0) {
+  const Quat b{b0.w, -b0.x, -b0.y, -b0.z};
+  const float w = a.w * b.w - a.x * b.x - a.y * b.y - a.z * b.z;
+  const float x = a.w * b.x + a.x * b.w + a.y * b.z - a.z * b.y;
+  const float y = a.w * b.y + a.y * b.w + a.z * b.x - a.x * b.z;
+  const float z = a.w * b.z + a.z * b.w + a.x * b.y - a.y * b.x;
+  const float vn = std::sqrt(x * x + y * y + z * z);
+  return 2.f * std::atan2(vn, std::fabs(w));
+}
+
+struct Checkers {
+  const orc_icp_params* p;
+  float counter = 0.f;
+  std::vector<Quat> rot;
+  std::vector<float> tr;  // 3 per entry
+  void init(const float* T) {
+    counter = 0.f;
+    rot.clear(); tr.clear();
+    rot.push_back(quatFromT(T));
+    tr.push_back(T[12]); tr.push_back(T[13]); tr.push_back(T[14]);
+  }
+  // returns status; sets iterate / maxReached
+  int check(const float* T, bool& iterate, bool& maxReached) {
+    bool counterHit = false;
+    if (p->max_iterations > 0) {
+      counter += 1.f;
+      if (counter >= (float)p->max_iterations) counterHit = true;  // throws MaxNumIterationsReached
+    }
+    if (p->use_differential) {
+      rot.push_back(quatFromT(T));
+      tr.push_back(T[12]); tr.push_back(T[13]); tr.push_back(T[14]);
+      float cv0 = 0.f, cv1 = 0.f;
+      const size_t L = (size_t)p->smooth_length;
+      if (rot.size() > L) {
+        for (size_t i = rot.size() - 1; i >= rot.size() - L; --i) {
+          cv0 += std::fabs(angularDistance(rot[i], rot[i - 1]));
+          const float dx = tr[3 * i] - tr[3 * (i - 1)], dy = tr[3 * i + 1] - tr[3 * (i - 1) + 1],
+                      dz = tr[3 * i + 2] - tr[3 * (i - 1) + 2];
+          cv1 += std::fabs(std::sqrt(dx * dx + dy * dy + dz * dz));
+        }
+        cv0 /= (float)L;
+        cv1 /= (float)L;
+        if (cv0 < p->min_diff_rot && cv1 < p->min_diff_trans) iterate = false;
+      }
+      if (cv0 != cv0 || cv1 != cv1) return ORC_E_NAN;  // ConvergenceError, TransformationCheckersImpl.cpp:147-150
+    }
+    if (counterHit) { iterate = false; maxReached = true; }
+    return ORC_OK;
+  }
+};
+
+void meanOf(const float* feat, int N, int mode, float* mean3) {
+  if (mode == 0) {
+    float s[3] = {0, 0, 0};
+    for (int i = 0; i < N; ++i)
+      for (int d = 0; d < 3; ++d) s[d] += feat[4 * (size_t)i + d];
+    for (int d = 0; d < 3; ++d) mean3[d] = s[d] / (float)N;
+  } else {
+    double s[3] = {0, 0, 0};
+    for (int i = 0; i < N; ++i)
+      for (int d = 0; d < 3; ++d) s[d] += (double)feat[4 * (size_t)i + d];
+    for (int d = 0; d < 3; ++d) mean3[d] = (float)(s[d] / (double)N);
+  }
+}
+
+}  // namespace
+
+extern "C" int orc_icp(const orc_icp_params* prm, const float* ref4xM, const float* refn3xM, int M,
+                       const float* read4xN, const float* readn3xN, int N, const float* Tinit, orc_icp_result* res,
+                       int max_log, float* logH, float* logb, float* logx, float* logT, int* logP,
+                       int32_t* last_ids, float* last_dists, float* last_w) {
+  if (M <= 0 || N <= 0) return ORC_E_BAD_PARAM;
+  const int k = prm->knn;
+  // ---- initReference, ICP.cpp:847-898
+  std::vector<float> ref(ref4xM, ref4xM + 4 * (size_t)M);
+  float meanRef[3];
+  meanOf(ref.data(), M, prm->mean_mode, meanRef);
+  float T_refIn_refMean[16];
+  eye4(T_refIn_refMean);
+  for (int d = 0; d < 3; ++d) T_refIn_refMean[12 + d] = meanRef[d];
+  for (int i = 0; i < M; ++i)
+    for (int d = 0; d < 3; ++d) ref[4 * (size_t)i + d] -= meanRef[d];
+  void* tree = orc_kdtree_build(ref.data(), M);
+
+  // ---- computeWithTransformedReference, ICP.cpp:902-1000
+  std::vector<float> reading(read4xN, read4xN + 4 * (size_t)N);
+  std::vector<float> readingN;
+  if (readn3xN) readingN.assign(readn3xN, readn3xN + 3 * (size_t)N);
+  float meanRead[3];
+  meanOf(reading.data(), N, prm->mean_mode, meanRead);
+  float T_readIn_readMean[16];
+  eye4(T_readIn_readMean);
+  for (int d = 0; d < 3; ++d) T_readIn_readMean[12 + d] = meanRead[d];
+  for (int i = 0; i < N; ++i)
+    for (int d = 0; d < 3; ++d) reading[4 * (size_t)i + d] -= meanRead[d];
+  float invRef[16], T_refMean_readMean[16], tmp[16];
+  inv4(T_refIn_refMean, invRef);
+  mul4(invRef, Tinit, tmp);
+  mul4(tmp, T_readIn_readMean, T_refMean_readMean);       // ICP.cpp:983
+  orc_rigid_apply(T_refMean_readMean, reading.data(), readingN.empty() ? nullptr : readingN.data(), N);  // :984
+
+  float T_iter[16];
+  eye4(T_iter);
+  bool iterate = true, maxReached = false;
+  Checkers chk;
+  chk.p = prm;
+  chk.init(T_iter);                                        // :997
+
+  std::vector<float> step(4 * (size_t)N), stepN;
+  std::vector<int32_t> ids((size_t)k * N);
+  std::vector<float> dists((size_t)k * N), w((size_t)k * N), w2((size_t)k * N);
+  std::vector<float> readP(4 * (size_t)k * N), refP(4 * (size_t)k * N), refnP(3 * (size_t)k * N), wP((size_t)k * N);
+  int iterationCount = 0, status = ORC_OK, P = 0;
+  long touched = 0;
+  float wpur = 0.f;
+  while (iterate) {                                        // :1027
+    step = reading;                                        // :1034
+    if (!readingN.empty()) stepN = readingN;
+    orc_rigid_apply(T_iter, step.data(), stepN.empty() ? nullptr : stepN.data(), N);  // :1047
+    touched += orc_kdtree_knn(tree, step.data(), N, k, prm->maxDist, prm->knn_threads, ids.data(), dists.data());
+    // outlier filter chain: element-wise product, OutlierFilter.cpp:84-99
+    const long n = (long)k * N;
+    bool first = true;
+    auto chain = [&](int st) {
+      if (st) { status = st; return; }
+      if (first) { w = w2; first = false; }
+      else for (long i = 0; i < n; ++i) w[i] = w[i] * w2[i];
+    };
+    if (prm->use_trimmed) chain(orc_outlier_trimmed(dists.data(), n, prm->trimmed_ratio, w2.data()));
+    if (!status && prm->use_maxdist_filter) chain(orc_outlier_maxdist(dists.data(), n, prm->maxdist_filter, w2.data()));
+    if (!status && prm->use_surface_normal_filter)
+      chain(orc_outlier_surface_normal(stepN.empty() ? nullptr : stepN.data(), refn3xM, ids.data(), k, N,
+                                       prm->surface_normal_max_angle, w2.data()));
+    if (!status && first) orc_outlier_null(dists.data(), n, w.data());
+    if (status) break;
+    float pur;
+    status = orc_error_elements(step.data(), ref.data(), refn3xM, w.data(), ids.data(), dists.data(), k, N,
+                                readP.data(), refP.data(), refn3xM ? refnP.data() : nullptr, wP.data(), nullptr,
+                                nullptr, &P, &pur, &wpur);  // :1061
+    if (status) break;
+    float H[36] = {0}, b[6] = {0}, x[6] = {0}, real[16];
+    if (prm->minimizer == 0) {
+      if (!refn3xM) { status = ORC_E_BAD_PARAM; break; }   // InvalidField "normals", ICP.cpp:1519
+      orc_p2plane_hb(readP.data(), refP.data(), refnP.data(), wP.data(), P, prm->accum, H, b);  // :1071
+      int info;
+      orc_solve6(H, b, x, &info);                          // :1205 -> PointToPlane.cpp:299
+      orc_p2plane_T(x, real);
+    } else {
+      orc_p2point_T(readP.data(), refP.data(), wP.data(), P, real);
+    }
+    mul4(real, T_iter, T_iter);                            // :1213
+    if (iterationCount < max_log) {
+      if (logH) std::memcpy(logH + 36 * (size_t)iterationCount, H, sizeof(H));
+      if (logb) std::memcpy(logb + 6 * (size_t)iterationCount, b, sizeof(b));
+      if (logx) std::memcpy(logx + 6 * (size_t)iterationCount, x, sizeof(x));
+      if (logT) std::memcpy(logT + 16 * (size_t)iterationCount, T_iter, sizeof(T_iter));
+      if (logP) logP[iterationCount] = P;
+    }
+    status = chk.check(T_iter, iterate, maxReached);       // :1292-1298
+    ++iterationCount;
+    if (status) break;
+  }
+  orc_kdtree_free(tree);
+  // ---- result, ICP.cpp:1345
+  float invRead[16], r1[16], r2[16];
+  inv4(T_readIn_readMean, invRead);
+  mul4(T_refIn_refMean, T_iter, r1);
+  mul4(r1, T_refMean_readMean, r2);
+  mul4(r2, invRead, res->T);
+  res->iterations = iterationCount;
+  res->max_iterations_reached = maxReached ? 1 : 0;
+  res->n_matches_last = P;
+  res->weighted_point_used_ratio = wpur;
+  res->points_touched = touched;
+  std::memcpy(res->T_iter, T_iter, sizeof(T_iter));
+  std::memcpy(res->T_refIn_refMean, T_refIn_refMean, sizeof(T_refIn_refMean));
+  std::memcpy(res->T_refMean_readMean, T_refMean_readMean, sizeof(T_refMean_readMean));
+  if (last_ids) std::memcpy(last_ids, ids.data(), ids.size() * sizeof(int32_t));
+  if (last_dists) std::memcpy(last_dists, dists.data(), dists.size() * sizeof(float));
+  if (last_w) std::memcpy(last_w, w.data(), w.size() * sizeof(float));
+  return status;
+}

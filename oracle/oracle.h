@@ -1,0 +1,129 @@
+/* ORACLE — TEST INFRASTRUCTURE ONLY.
+ *
+ * CPU restatement of the reference's registration hot path (libpointmatcher fork inside
+ * leggedrobotics/open3d_slam_private). It is the checker for the CUDA path, never the product: only tests/,
+ * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load it.
+ *
+ * Pinning status:
+ *   - whole-ICP results are pinned against the reference's own goldens: validT3d (utest.cpp:351-360),
+ *     icpSingular / icpIdentity known answers (utest.cpp:163-221) and the icp_data ref_trans files.
+ *   - kNN ids/dists, normals, weights, H, b, iteration counts: the reference has no test that pins them and
+ *     libnabo / Eigen are not in /root/reference => "parity unpinned" for those quantities; the oracle fixes
+ *     them by the published algorithm (exact kNN at epsilon = 0, ties -> smallest index).
+ *
+ * All matrices are column-major exactly like the reference's Eigen matrices:
+ *   features 4 x N  (x,y,z,1 per point),  normals 3 x N,  dists/ids/weights k x N.
+ */
+#ifndef ORACLE_H_
+#define ORACLE_H_
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORC_OK 0
+#define ORC_E_NO_MATCHES 1   /* PointMatcher::ConvergenceError */
+#define ORC_E_BAD_PARAM 2
+#define ORC_E_NAN 3
+
+/* ---- kNN (stands in for libnabo NNS::knn as called at MatchersImpl.cpp:98) ---- */
+int orc_knn_brute(const float* ref4xM, int M, const float* query4xN, int N, int k, float maxDist,
+                  int32_t* ids_kxN, float* dists_kxN);
+void* orc_kdtree_build(const float* ref4xM, int M);
+void orc_kdtree_free(void* tree);
+/* returns number of points touched (libnabo's visit statistic, our tree's own count) */
+long orc_kdtree_knn(const void* tree, const float* query4xN, int N, int k, float maxDist, int nthreads,
+                    int32_t* ids_kxN, float* dists_kxN);
+
+/* ---- Matches::getDistsQuantile (Matches.cpp:60-87) ---- */
+int orc_dists_quantile(const float* dists, long n, float quantile, float* out);
+
+/* ---- outlier filters (OutlierFiltersImpl.cpp:75-81, 95-101, 117-125, 140-147, 236-288) ---- */
+int orc_outlier_maxdist(const float* dists, long n, float maxDist, float* w);
+int orc_outlier_mindist(const float* dists, long n, float minDist, float* w);
+int orc_outlier_median(const float* dists, long n, float factor, float* w);
+int orc_outlier_trimmed(const float* dists, long n, float ratio, float* w);
+int orc_outlier_surface_normal(const float* nread3xN, const float* nref3xM, const int32_t* ids_kxN, int k, int N,
+                               float maxAngle, float* w);
+/* OutlierFilters::compute with an empty chain (OutlierFilter.cpp:66-83) */
+int orc_outlier_null(const float* dists, long n, float* w);
+
+/* ---- ErrorElements ctor (ErrorMinimizer.cpp:59-193): order-preserving compaction.
+ * outputs sized for k*N pairs; returns P through *P_out. */
+int orc_error_elements(const float* read4xN, const float* ref4xM, const float* refn3xM /*nullable*/,
+                       const float* w_kxN, const int32_t* ids_kxN, const float* dists_kxN, int k, int N,
+                       float* read4xP, float* ref4xP, float* refn3xP, float* w_P, int32_t* ids_P, float* dists_P,
+                       int* P_out, float* pointUsedRatio, float* weightedPointUsedRatio);
+
+/* ---- ICP::calculateOptimizationHessian (ICP.cpp:1513-1566). accum: 0 = float sequential (reference-like
+ * float GEMM, order is an Eigen artefact), 1 = float products accumulated in double ("truth"). */
+int orc_p2plane_hb(const float* read4xP, const float* ref4xP, const float* refn3xP, const float* w_P, int P,
+                   int accum, float* H36, float* b6);
+
+/* ---- solvePossiblyUnderdeterminedLinearSystem (PointToPlane.cpp:113-265, unconstrained branch).
+ * info: 0 = full-rank double-SVD path, 1 = rank-deficient minimal-norm path, 2 = SVD fallback */
+int orc_solve6(const float* A36, const float* b6, float* x6, int* info);
+/* x -> 4x4 (PointToPlane.cpp:337-381) */
+int orc_p2plane_T(const float* x6, float* T16);
+
+/* ---- PointToPointErrorMinimizer::compute_in_place (PointToPoint.cpp:62-103) ---- */
+int orc_p2point_T(const float* read4xP, const float* ref4xP, const float* w_P, int P, float* T16);
+
+/* ---- RigidTransformation::inPlaceCompute (TransformationsImpl.cpp:61-102) incl. check/correct ---- */
+int orc_rigid_apply(const float* T16, float* feat4xN, float* normals3xN /*nullable*/, int N);
+
+/* ---- SurfaceNormalDataPointsFilter::inPlaceFilter (SurfaceNormal.cpp:82-290).
+ * Any output may be NULL. eigVectors row-major serialised (utils.h:89-103). */
+int orc_surface_normals(const float* feat4xN, int N, int knn, float maxDist, int sortEigen, int smoothNormals,
+                        float* normals3xN, float* densities1xN, float* eigValues3xN, float* eigVectors9xN,
+                        float* matchedIds_kxN, float* meanDists1xN, int32_t* ids_kxN, float* dists_kxN);
+
+/* ---- SamplingSurfaceNormalDataPointsFilter (SamplingSurfaceNormal.cpp:76-344); reference pre-filter of the
+ * golden configs. Returns number of output points; feat/normals are written compacted (capacity N).
+ * samplingMethod 0 keeps every point whose rand()/RAND_MAX < ratio (std::rand, unseeded like the reference). */
+int orc_sampling_surface_normal(const float* feat4xN, int N, int knn, float ratio, int samplingMethod,
+                                float maxBoxDim, float* featOut4xN, float* normalsOut3xN);
+
+/* ---- whole ICP (ICP.cpp:813-1349) ---- */
+typedef struct {
+  int knn;              /* KDTreeMatcher knn */
+  float maxDist;        /* KDTreeMatcher maxDist (inf allowed) */
+  int use_trimmed;      /* TrimmedDistOutlierFilter */
+  float trimmed_ratio;
+  int use_maxdist_filter; /* MaxDistOutlierFilter */
+  float maxdist_filter;
+  int use_surface_normal_filter; /* SurfaceNormalOutlierFilter */
+  float surface_normal_max_angle;
+  int minimizer;        /* 0 = PointToPlane, 1 = PointToPoint */
+  int max_iterations;   /* CounterTransformationChecker; <=0: absent */
+  int use_differential; /* DifferentialTransformationChecker */
+  float min_diff_rot, min_diff_trans;
+  int smooth_length;
+  int counter_first;    /* 1: Counter is checked before Differential (setDefault order), 0: after (icp.yaml) */
+  int accum;            /* see orc_p2plane_hb */
+  int mean_mode;        /* 0 = reference-literal sequential float mean, 1 = double sum rounded to float */
+  int knn_threads;      /* kd-tree query threads (1 = like the single-threaded reference) */
+} orc_icp_params;
+
+typedef struct {
+  int iterations;
+  int max_iterations_reached;
+  int n_matches_last;   /* P of the last iteration */
+  float T[16];          /* result, column-major 4x4 */
+  float T_iter[16];
+  float T_refIn_refMean[16];
+  float T_refMean_readMean[16];
+  float weighted_point_used_ratio;
+  long points_touched;
+} orc_icp_result;
+
+/* log_* (nullable): per-iteration dumps, capacity max_log iterations: H 36, b 6, x 6, T_iter 16 floats, P int */
+int orc_icp(const orc_icp_params* prm, const float* ref4xM, const float* refn3xM, int M, const float* read4xN,
+            const float* readn3xN /*nullable*/, int N, const float* Tinit16, orc_icp_result* res, int max_log,
+            float* logH, float* logb, float* logx, float* logT, int* logP, int32_t* last_ids, float* last_dists,
+            float* last_w);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,276 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY. ctypes binding of oracle/liboracle.so (see oracle/oracle.h).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this module.
+The product package (open3d_slam_private_b200) never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+ORC_OK, ORC_E_NO_MATCHES, ORC_E_BAD_PARAM, ORC_E_NAN = 0, 1, 2, 3
+
+_f32p = C.POINTER(C.c_float)
+_i32p = C.POINTER(C.c_int32)
+
+
+class IcpParams(C.Structure):
+    _fields_ = [
+        ("knn", C.c_int), ("maxDist", C.c_float),
+        ("use_trimmed", C.c_int), ("trimmed_ratio", C.c_float),
+        ("use_maxdist_filter", C.c_int), ("maxdist_filter", C.c_float),
+        ("use_surface_normal_filter", C.c_int), ("surface_normal_max_angle", C.c_float),
+        ("minimizer", C.c_int), ("max_iterations", C.c_int),
+        ("use_differential", C.c_int), ("min_diff_rot", C.c_float), ("min_diff_trans", C.c_float),
+        ("smooth_length", C.c_int), ("counter_first", C.c_int), ("accum", C.c_int), ("mean_mode", C.c_int),
+        ("knn_threads", C.c_int),
+    ]
+
+
+class IcpResult(C.Structure):
+    _fields_ = [
+        ("iterations", C.c_int), ("max_iterations_reached", C.c_int), ("n_matches_last", C.c_int),
+        ("T", C.c_float * 16), ("T_iter", C.c_float * 16), ("T_refIn_refMean", C.c_float * 16),
+        ("T_refMean_readMean", C.c_float * 16), ("weighted_point_used_ratio", C.c_float),
+        ("points_touched", C.c_long),
+    ]
+
+
+def build(force=False):
+    so = os.path.join(_HERE, "liboracle.so")
+    srcs = [os.path.join(_HERE, f) for f in ("knn.cpp", "modules.cpp", "normals.cpp", "icp.cpp", "oracle.h",
+                                             "la_small.hpp")]
+    if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
+        subprocess.check_call(["make", "-C", _HERE, "-s"])
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        _LIB = C.CDLL(build())
+        _LIB.orc_kdtree_build.restype = C.c_void_p
+        _LIB.orc_kdtree_knn.restype = C.c_long
+    return _LIB
+
+
+def _fp(a):
+    return None if a is None else a.ctypes.data_as(_f32p)
+
+
+def _ip(a):
+    return None if a is None else a.ctypes.data_as(_i32p)
+
+
+def feat4(xyz):
+    """(N,3) -> reference `features` memory image: N x {x,y,z,1} float32 (4 x N column-major)."""
+    xyz = np.asarray(xyz, dtype=np.float32)
+    out = np.ones((xyz.shape[0], 4), dtype=np.float32)
+    out[:, :3] = xyz
+    return np.ascontiguousarray(out)
+
+
+def f32(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.float32)
+
+
+def knn_brute(ref4, q4, k, max_dist=np.inf):
+    ref4, q4 = f32(ref4), f32(q4)
+    n = q4.shape[0]
+    ids = np.empty((n, k), np.int32)
+    d = np.empty((n, k), np.float32)
+    st = lib().orc_knn_brute(_fp(ref4), ref4.shape[0], _fp(q4), n, k, C.c_float(max_dist), _ip(ids), _fp(d))
+    assert st == 0
+    return ids, d
+
+
+class KdTree:
+    def __init__(self, ref4):
+        self.ref4 = f32(ref4)
+        self.h = C.c_void_p(lib().orc_kdtree_build(_fp(self.ref4), self.ref4.shape[0]))
+
+    def knn(self, q4, k, max_dist=np.inf, threads=1):
+        q4 = f32(q4)
+        n = q4.shape[0]
+        ids = np.empty((n, k), np.int32)
+        d = np.empty((n, k), np.float32)
+        self.touched = lib().orc_kdtree_knn(self.h, _fp(q4), n, k, C.c_float(max_dist), threads, _ip(ids), _fp(d))
+        return ids, d
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_kdtree_free(self.h)
+            self.h = None
+
+
+def dists_quantile(dists, q):
+    dists = f32(dists).ravel()
+    out = C.c_float()
+    st = lib().orc_dists_quantile(_fp(dists), C.c_long(dists.size), C.c_float(q), C.byref(out))
+    return st, out.value
+
+
+def _outlier(fn, dists, param):
+    dists = f32(dists)
+    w = np.empty_like(dists)
+    st = fn(_fp(dists), C.c_long(dists.size), C.c_float(param), _fp(w))
+    return st, w
+
+
+def outlier_trimmed(dists, ratio):
+    return _outlier(lib().orc_outlier_trimmed, dists, ratio)
+
+
+def outlier_maxdist(dists, max_dist):
+    return _outlier(lib().orc_outlier_maxdist, dists, max_dist)
+
+
+def outlier_mindist(dists, min_dist):
+    return _outlier(lib().orc_outlier_mindist, dists, min_dist)
+
+
+def outlier_median(dists, factor):
+    return _outlier(lib().orc_outlier_median, dists, factor)
+
+
+def outlier_null(dists):
+    dists = f32(dists)
+    w = np.empty_like(dists)
+    lib().orc_outlier_null(_fp(dists), C.c_long(dists.size), _fp(w))
+    return 0, w
+
+
+def outlier_surface_normal(nread, nref, ids, max_angle):
+    nread, nref = f32(nread), f32(nref)
+    ids = np.ascontiguousarray(ids, np.int32)
+    n, k = ids.shape
+    w = np.empty((n, k), np.float32)
+    st = lib().orc_outlier_surface_normal(_fp(nread), _fp(nref), _ip(ids), k, n, C.c_float(max_angle), _fp(w))
+    return st, w
+
+
+def error_elements(read4, ref4, refn, w, ids, dists):
+    read4, ref4, refn, w, dists = f32(read4), f32(ref4), f32(refn), f32(w), f32(dists)
+    ids = np.ascontiguousarray(ids, np.int32)
+    n, k = ids.shape
+    cap = n * k
+    readP = np.empty((cap, 4), np.float32)
+    refP = np.empty((cap, 4), np.float32)
+    refnP = np.empty((cap, 3), np.float32) if refn is not None else None
+    wP = np.empty(cap, np.float32)
+    idsP = np.empty(cap, np.int32)
+    dP = np.empty(cap, np.float32)
+    P = C.c_int()
+    pur, wpur = C.c_float(), C.c_float()
+    st = lib().orc_error_elements(_fp(read4), _fp(ref4), _fp(refn), _fp(w), _ip(ids), _fp(dists), k, n, _fp(readP),
+                                  _fp(refP), _fp(refnP), _fp(wP), _ip(idsP), _fp(dP), C.byref(P), C.byref(pur),
+                                  C.byref(wpur))
+    p = P.value
+    return st, dict(reading=readP[:p], reference=refP[:p], ref_normals=None if refnP is None else refnP[:p],
+                    weights=wP[:p], ids=idsP[:p], dists=dP[:p], point_used_ratio=pur.value,
+                    weighted_point_used_ratio=wpur.value)
+
+
+def p2plane_hb(readP, refP, refnP, wP, accum=1):
+    readP, refP, refnP, wP = f32(readP), f32(refP), f32(refnP), f32(wP)
+    H = np.empty(36, np.float32)
+    b = np.empty(6, np.float32)
+    lib().orc_p2plane_hb(_fp(readP), _fp(refP), _fp(refnP), _fp(wP), readP.shape[0], accum, _fp(H), _fp(b))
+    return H.reshape(6, 6).T.copy(), b  # H returned as a normal (row, col) numpy matrix
+
+
+def solve6(H, b):
+    A = np.ascontiguousarray(np.asarray(H, np.float32).T).ravel()  # column-major
+    b = f32(b)
+    x = np.empty(6, np.float32)
+    info = C.c_int()
+    lib().orc_solve6(_fp(A), _fp(b), _fp(x), C.byref(info))
+    return x, info.value
+
+
+def p2plane_T(x):
+    x = f32(x)
+    T = np.empty(16, np.float32)
+    lib().orc_p2plane_T(_fp(x), _fp(T))
+    return T.reshape(4, 4).T.copy()
+
+
+def p2point_T(readP, refP, wP):
+    readP, refP, wP = f32(readP), f32(refP), f32(wP)
+    T = np.empty(16, np.float32)
+    lib().orc_p2point_T(_fp(readP), _fp(refP), _fp(wP), readP.shape[0], _fp(T))
+    return T.reshape(4, 4).T.copy()
+
+
+def rigid_apply(T, feat4_, normals=None):
+    Tc = np.ascontiguousarray(np.asarray(T, np.float32).T).ravel()
+    f = f32(feat4_).copy()
+    n = None if normals is None else f32(normals).copy()
+    lib().orc_rigid_apply(_fp(Tc), _fp(f), _fp(n), f.shape[0])
+    return f, n
+
+
+def surface_normals(feat4_, knn, max_dist=np.inf, sort_eigen=0, smooth=0):
+    f = f32(feat4_)
+    n = f.shape[0]
+    out = dict(normals=np.empty((n, 3), np.float32), densities=np.empty(n, np.float32),
+               eigValues=np.empty((n, 3), np.float32), eigVectors=np.empty((n, 9), np.float32),
+               matchedIds=np.empty((n, knn), np.float32), meanDists=np.empty(n, np.float32),
+               ids=np.empty((n, knn), np.int32), dists=np.empty((n, knn), np.float32))
+    st = lib().orc_surface_normals(_fp(f), n, knn, C.c_float(max_dist), sort_eigen, smooth, _fp(out["normals"]),
+                                   _fp(out["densities"]), _fp(out["eigValues"]), _fp(out["eigVectors"]),
+                                   _fp(out["matchedIds"]), _fp(out["meanDists"]), _ip(out["ids"]), _fp(out["dists"]))
+    return st, out
+
+
+def sampling_surface_normal(feat4_, knn=7, ratio=0.5, sampling_method=0, max_box_dim=np.inf):
+    f = f32(feat4_)
+    n = f.shape[0]
+    fo = np.empty((n, 4), np.float32)
+    no = np.empty((n, 3), np.float32)
+    m = lib().orc_sampling_surface_normal(_fp(f), n, knn, C.c_float(ratio), sampling_method, C.c_float(max_box_dim),
+                                          _fp(fo), _fp(no))
+    return fo[:m].copy(), no[:m].copy()
+
+
+def default_params(**kw):
+    """PointMatcher ICPChainBase::setDefault (ICP.cpp:100-113) + module defaults."""
+    p = IcpParams(knn=1, maxDist=np.inf, use_trimmed=1, trimmed_ratio=0.85, use_maxdist_filter=0, maxdist_filter=1.0,
+                  use_surface_normal_filter=0, surface_normal_max_angle=1.57, minimizer=0, max_iterations=40,
+                  use_differential=1, min_diff_rot=0.001, min_diff_trans=0.001, smooth_length=3, counter_first=1,
+                  accum=1, mean_mode=1, knn_threads=1)
+    for k_, v in kw.items():
+        assert hasattr(p, k_), k_
+        setattr(p, k_, v)
+    return p
+
+
+def icp(params, ref4, refn, read4, readn=None, T_init=None, max_log=64):
+    ref4, refn, read4, readn = f32(ref4), f32(refn), f32(read4), f32(readn)
+    M, N, k = ref4.shape[0], read4.shape[0], params.knn
+    Ti = np.eye(4, dtype=np.float32) if T_init is None else np.asarray(T_init, np.float32)
+    Tc = np.ascontiguousarray(Ti.T).ravel()
+    res = IcpResult()
+    logH = np.zeros((max_log, 36), np.float32)
+    logb = np.zeros((max_log, 6), np.float32)
+    logx = np.zeros((max_log, 6), np.float32)
+    logT = np.zeros((max_log, 16), np.float32)
+    logP = np.zeros(max_log, np.int32)
+    ids = np.empty((N, k), np.int32)
+    dists = np.empty((N, k), np.float32)
+    w = np.empty((N, k), np.float32)
+    st = lib().orc_icp(C.byref(params), _fp(ref4), _fp(refn), M, _fp(read4), _fp(readn), N, _fp(Tc), C.byref(res),
+                       max_log, _fp(logH), _fp(logb), _fp(logx), _fp(logT), _ip(logP), _ip(ids), _fp(dists), _fp(w))
+    it = min(res.iterations, max_log)
+    m = lambda a: np.array(a, np.float32).reshape(4, 4).T.copy()
+    return dict(status=st, iterations=res.iterations, max_iterations_reached=bool(res.max_iterations_reached),
+                n_matches_last=res.n_matches_last, T=m(res.T), T_iter=m(res.T_iter),
+                T_refIn_refMean=m(res.T_refIn_refMean), T_refMean_readMean=m(res.T_refMean_readMean),
+                weighted_point_used_ratio=res.weighted_point_used_ratio, points_touched=res.points_touched,
+                H=logH[:it].reshape(it, 6, 6).transpose(0, 2, 1).copy(), b=logb[:it], x=logx[:it],
+                T_iters=logT[:it].reshape(it, 4, 4).transpose(0, 2, 1).copy(), P=logP[:it], ids=ids, dists=dists,
+                weights=w)
