@@ -1,0 +1,191 @@
+/* b200reg.h — C ABI of the B200-native point-cloud registration core.
+ *
+ * Drop-in boundary for ONE hot path of leggedrobotics/open3d_slam_private: the modules that run inside each ICP
+ * iteration of libpointmatcher's PointMatcher<float>::ICP. Every entry point names the reference interface it
+ * replaces (paths relative to the reference root). Plain pointers and sizes only; no C++/torch types.
+ *
+ * Conventions (identical to the reference's Eigen memory images, so shims pass `.data()` straight through):
+ *   features   4 x N float, column-major  => N x {x,y,z,1}           (PointMatcher.h:222-403, DataPoints::features)
+ *   normals    3 x N float, column-major  => N x {nx,ny,nz}          (descriptor block "normals")
+ *   dists/ids/weights  k x N, column-major => per query k contiguous  (PointMatcher.h:416-442, Matches/OutlierWeights)
+ *   ids are int32, invalid = -1; dists are SQUARED L2 in float, invalid = +inf (MatchersImpl.cpp:96-97)
+ *   4x4 transforms are column-major float[16] (Eigen default)
+ * All host arrays are caller-owned and caller-sized; the library never frees caller memory. Device memory is owned
+ * by the handles. Handles are single-owner (not internally locked); calls on different handles are re-entrant.
+ * Every function returns a b200_status; b200_last_error() gives the message for the calling thread.
+ * There is NO CPU fallback: without a CUDA device every compute entry point returns B200_E_CUDA.
+ */
+#ifndef B200REG_H_
+#define B200REG_H_
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  B200_OK = 0,
+  B200_E_NO_MATCHES = 1,   /* PointMatcher::ConvergenceError ("no point to minimize", Matches.cpp:75, ErrorMinimizer.cpp:76) */
+  B200_E_BAD_PARAM = 2,    /* PointMatcherSupport::InvalidParameter / InvalidField */
+  B200_E_NAN = 3,          /* ConvergenceError("abs rotation norm not a number"), TransformationCheckersImpl.cpp:147 */
+  B200_E_CUDA = 4,         /* CUDA runtime failure or no device */
+  B200_E_UNSUPPORTED = 5,  /* accepted by the reference, not by this core (e.g. knn > 64, force2D) */
+  B200_E_NOT_INITIALIZED = 6 /* std::runtime_error("You must setup a matcher before running ICP") analogue */
+} b200_status;
+
+const char* b200_last_error(void);
+int b200_version(void);
+/* number of visible CUDA devices (0 when none / driver missing) */
+int b200_device_count(void);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Matcher — replaces MatchersImpl<float>::KDTreeMatcher (MatchersImpl.h:70-101, MatchersImpl.cpp:60-102) and
+ * KDTreeVarDistMatcher (MatchersImpl.cpp:108-150). The libnabo kd-tree becomes a device-resident uniform-grid index.
+ * ---------------------------------------------------------------------------------------------------------- */
+typedef struct b200_index b200_index;
+
+typedef struct {
+  float cell_size;       /* <= 0: choose automatically from the point density */
+  float target_per_cell; /* <= 0: default (points per occupied cell aimed at by the automatic choice) */
+  uint64_t max_cells;    /* 0: default cap on the dense cell table */
+} b200_index_opts;
+
+/* KDTreeMatcher::init(filteredReference) — MatchersImpl.cpp:78-83. normals3xM may be NULL. opts may be NULL. */
+int b200_index_create(b200_index** out, int device, const float* ref4xM, const float* normals3xM, int M,
+                      const b200_index_opts* opts);
+void b200_index_destroy(b200_index* idx);
+/* KDTreeMatcher::findClosests(filteredReading) — MatchersImpl.cpp:85-102. epsilon is accepted for interface
+ * compatibility; the search is always exact (the exact answer satisfies every epsilon). maxDistPerPoint (1 x N,
+ * nullable) reproduces KDTreeVarDistMatcher (MatchersImpl.cpp:133-150). visit_count (nullable) receives the number
+ * of candidate points examined (Matcher::visitCounter). */
+int b200_index_knn(b200_index* idx, const float* query4xN, int N, int knn, float epsilon, float maxDist,
+                   const float* maxDistPerPoint, int32_t* ids_kxN, float* dists_kxN, uint64_t* visit_count);
+/* build statistics: cell size, grid dims, occupied cells, build time (ms, device) */
+int b200_index_info(const b200_index* idx, float* cell_size, int32_t dims[3], int64_t* occupied_cells,
+                    float* build_ms);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * DataPointsFilter — replaces SurfaceNormalDataPointsFilter::inPlaceFilter (SurfaceNormal.cpp:82-290).
+ * Any output pointer may be NULL (the corresponding keep* flag of the reference is false).
+ * ---------------------------------------------------------------------------------------------------------- */
+typedef struct {
+  int knn;            /* default 5 (SurfaceNormal.h:70) */
+  float maxDist;      /* default inf */
+  float epsilon;      /* accepted, search is exact */
+  int sortEigen;      /* 0/1 */
+  int smoothNormals;  /* 0/1 */
+} b200_surface_normal_params;
+
+int b200_surface_normals(int device, const float* feat4xN, int N, const b200_surface_normal_params* prm,
+                         float* normals3xN, float* densities1xN, float* eigValues3xN, float* eigVectors9xN,
+                         float* matchedIds_kxN, float* meanDists1xN);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * OutlierFilter — replaces OutlierFiltersImpl<float>::{MaxDist,MinDist,MedianDist,TrimmedDist,SurfaceNormal}
+ * OutlierFilter::compute (OutlierFiltersImpl.cpp:75-81, 95-101, 117-125, 140-147, 236-288) and the empty chain of
+ * OutlierFilters::compute (OutlierFilter.cpp:66-83). n = k*N entries.
+ * ---------------------------------------------------------------------------------------------------------- */
+typedef enum {
+  B200_OUTLIER_NULL = 0,
+  B200_OUTLIER_MAXDIST = 1,
+  B200_OUTLIER_MINDIST = 2,
+  B200_OUTLIER_MEDIANDIST = 3,
+  B200_OUTLIER_TRIMMEDDIST = 4
+} b200_outlier_kind;
+int b200_outlier_dist(int device, int kind, float param, const float* dists, int64_t n, float* weights);
+/* Matches::getDistsQuantile (Matches.cpp:60-87) */
+int b200_dists_quantile(int device, const float* dists, int64_t n, float quantile, float* out);
+/* SurfaceNormalOutlierFilter::compute; either normals pointer NULL => all ones (OutlierFiltersImpl.cpp:273-283) */
+int b200_outlier_surface_normal(int device, const float* nread3xN, const float* nref3xM, int M,
+                                const int32_t* ids_kxN, int knn, int N, float maxAngle, float* weights);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * ErrorMinimizer — replaces ErrorMinimizer::ErrorElements (ErrorMinimizer.cpp:59-193),
+ * ICP::calculateOptimizationHessian (ICP.cpp:1513-1566), PointToPlaneErrorMinimizer::compute_in_place with
+ * degeneracyAwareness = kNone (PointToPlane.cpp:113-265, 275-400) and PointToPointErrorMinimizer::compute_in_place
+ * (PointToPoint.cpp:62-103).
+ * ---------------------------------------------------------------------------------------------------------- */
+/* order-preserving compaction; outputs have capacity k*N columns; any output may be NULL */
+int b200_error_elements(int device, const float* read4xN, const float* ref4xM, const float* refn3xM, int M,
+                        const float* w_kxN, const int32_t* ids_kxN, const float* dists_kxN, int knn, int N,
+                        float* read4xP, float* ref4xP, float* refn3xP, float* w_P, int32_t* ids_P, float* dists_P,
+                        int* P, float* pointUsedRatio, float* weightedPointUsedRatio);
+/* H (6x6 column-major) and b from already matched pairs */
+int b200_p2plane_hessian(int device, const float* read4xP, const float* ref4xP, const float* refn3xP,
+                         const float* w_P, int P, float* H36, float* b6);
+/* 6x6 solve + SE(3) construction on device. info: 0 full rank, 1 rank-deficient minimal norm, 2 SVD fallback */
+int b200_p2plane_solve(int device, const float* H36, const float* b6, float* x6, float* T16, int* info);
+int b200_p2point(int device, const float* read4xP, const float* ref4xP, const float* w_P, int P, float* T16);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Transformation — replaces TransformationsImpl<float>::RigidTransformation::inPlaceCompute incl.
+ * checkParameters / correctParameters (TransformationsImpl.cpp:61-170). In place; normals may be NULL.
+ * ---------------------------------------------------------------------------------------------------------- */
+int b200_rigid_apply(int device, const float* T16, float* feat4xN, float* normals3xN, int N);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * ICP chain — replaces PointMatcher<float>::ICP::{initReference, compute, operator()} (ICP.cpp:793-1349) for the
+ * chain {RigidTransformation, KDTreeMatcher, [TrimmedDist][MaxDist][SurfaceNormal]OutlierFilter,
+ * PointToPlane|PointToPoint ErrorMinimizer, [Counter][Differential]TransformationChecker}, degeneracyAwareness
+ * None. All iterations run in ONE persistent cooperative kernel; the host reads back one result struct.
+ * ---------------------------------------------------------------------------------------------------------- */
+typedef struct b200_icp b200_icp;
+
+typedef struct {
+  int knn;                       /* KDTreeMatcher.knn (1..64) */
+  float epsilon;                 /* KDTreeMatcher.epsilon (accepted; exact search) */
+  float maxDist;                 /* KDTreeMatcher.maxDist (inf allowed) */
+  int use_trimmed;               /* TrimmedDistOutlierFilter */
+  float trimmed_ratio;
+  int use_maxdist_filter;        /* MaxDistOutlierFilter */
+  float maxdist_filter;
+  int use_surface_normal_filter; /* SurfaceNormalOutlierFilter */
+  float surface_normal_max_angle;
+  int minimizer;                 /* 0 PointToPlaneErrorMinimizer, 1 PointToPointErrorMinimizer */
+  int max_iterations;            /* CounterTransformationChecker.maxIterationCount; <= 0: absent */
+  int use_differential;          /* DifferentialTransformationChecker */
+  float min_diff_rot, min_diff_trans;
+  int smooth_length;
+  float cell_size;               /* index option, <= 0 automatic */
+} b200_icp_params;
+
+typedef struct {
+  int status;                    /* b200_status decided on device */
+  int iterations;                /* Inspector stat "IterationsCount" */
+  int max_iterations_reached;    /* ICP::maxNumIterationsReached */
+  int n_matches_last;            /* ErrorElements size of the last iteration */
+  float T[16];                   /* T_refIn_readIn result (ICP.cpp:1345) */
+  float T_iter[16];
+  float T_refIn_refMean[16];
+  float T_refMean_readMean[16];
+  float weighted_point_used_ratio; /* "OverlapRatio" */
+  float point_used_ratio;
+  uint64_t points_touched;       /* "PointCountTouched" */
+  float device_ms;               /* CUDA-event time of the registration kernel */
+  float h2d_ms, total_ms;        /* upload time and whole call (events) */
+} b200_icp_result;
+
+void b200_icp_default_params(b200_icp_params* prm); /* ICPChainBase::setDefault, ICP.cpp:100-113 */
+int b200_icp_create(b200_icp** out, int device, const b200_icp_params* prm);
+void b200_icp_destroy(b200_icp* icp);
+/* ICP::initReference(referenceIn) — ICP.cpp:847-898: mean-centre, build the index. refn3xM may be NULL for
+ * PointToPoint. */
+int b200_icp_init_reference(b200_icp* icp, const float* ref4xM, const float* refn3xM, int M);
+/* ICP::compute(readingIn, <unused>, T_refIn_readIn, initializeMatcherWithInputReference=false) — ICP.cpp:813-844,
+ * the call Mapper.cpp:372-373 makes. readn3xN may be NULL. Tinit16 NULL = identity (ICP::operator(), ICP.cpp:793). */
+int b200_icp_compute(b200_icp* icp, const float* read4xN, const float* readn3xN, int N, const float* Tinit16,
+                     b200_icp_result* res);
+/* Same registration with the reading already resident on the device (for kernel-only timing):
+ * upload once, then run any number of times. */
+int b200_icp_upload_reading(b200_icp* icp, const float* read4xN, const float* readn3xN, int N);
+int b200_icp_run_resident(b200_icp* icp, const float* Tinit16, b200_icp_result* res);
+/* ICP::matches / ICP::outlierWeights of the last iteration (PointMatcher.h ICPChainBase members) */
+int b200_icp_get_matches(b200_icp* icp, int32_t* ids_kxN, float* dists_kxN, float* weights_kxN);
+/* per-iteration trace (first max_log iterations): H 36, b 6, x 6, T_iter 16 floats, P int. Returns count in *n. */
+int b200_icp_get_log(b200_icp* icp, int max_log, float* H, float* b, float* x, float* T_iter, int32_t* P, int* n);
+/* evict L2 (writes a buffer larger than L2) on the handle's stream; for benchmarking hygiene */
+int b200_icp_flush_l2(b200_icp* icp);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200REG_H_ */

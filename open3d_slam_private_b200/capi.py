@@ -1,0 +1,363 @@
+"""ctypes binding of the C ABI (include/b200reg.h). Thin: numpy arrays in the reference's memory layout go straight
+through as pointers. No CPU fallback — a missing library or a missing device raises.
+
+Layouts (identical to the reference's Eigen images): features (N,4) float32 C-contiguous == 4xN column-major;
+normals (N,3); ids/dists/weights (N,k) == k x N column-major; 4x4 matrices are passed column-major and returned as
+ordinary (row, col) numpy matrices.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIBPATH = os.path.join(_HERE, "lib", "libb200reg.so")
+_lib = None
+
+B200_OK, B200_E_NO_MATCHES, B200_E_BAD_PARAM, B200_E_NAN, B200_E_CUDA, B200_E_UNSUPPORTED, B200_E_NOT_INITIALIZED = range(7)
+OUTLIER_NULL, OUTLIER_MAXDIST, OUTLIER_MINDIST, OUTLIER_MEDIANDIST, OUTLIER_TRIMMEDDIST = range(5)
+
+_f32p = C.POINTER(C.c_float)
+_i32p = C.POINTER(C.c_int32)
+
+
+class B200Error(RuntimeError):
+    def __init__(self, status, msg):
+        super().__init__("b200 status %d: %s" % (status, msg))
+        self.status = status
+
+
+class ConvergenceError(B200Error):
+    """PointMatcher::ConvergenceError analogue (status NO_MATCHES / NAN)."""
+
+
+class IndexOpts(C.Structure):
+    _fields_ = [("cell_size", C.c_float), ("target_per_cell", C.c_float), ("max_cells", C.c_uint64)]
+
+
+class SurfaceNormalParams(C.Structure):
+    _fields_ = [("knn", C.c_int), ("maxDist", C.c_float), ("epsilon", C.c_float), ("sortEigen", C.c_int),
+                ("smoothNormals", C.c_int)]
+
+
+class IcpParams(C.Structure):
+    _fields_ = [
+        ("knn", C.c_int), ("epsilon", C.c_float), ("maxDist", C.c_float),
+        ("use_trimmed", C.c_int), ("trimmed_ratio", C.c_float),
+        ("use_maxdist_filter", C.c_int), ("maxdist_filter", C.c_float),
+        ("use_surface_normal_filter", C.c_int), ("surface_normal_max_angle", C.c_float),
+        ("minimizer", C.c_int), ("max_iterations", C.c_int),
+        ("use_differential", C.c_int), ("min_diff_rot", C.c_float), ("min_diff_trans", C.c_float),
+        ("smooth_length", C.c_int), ("cell_size", C.c_float),
+    ]
+
+
+class IcpResult(C.Structure):
+    _fields_ = [
+        ("status", C.c_int), ("iterations", C.c_int), ("max_iterations_reached", C.c_int), ("n_matches_last", C.c_int),
+        ("T", C.c_float * 16), ("T_iter", C.c_float * 16), ("T_refIn_refMean", C.c_float * 16),
+        ("T_refMean_readMean", C.c_float * 16), ("weighted_point_used_ratio", C.c_float),
+        ("point_used_ratio", C.c_float), ("points_touched", C.c_uint64), ("device_ms", C.c_float),
+        ("h2d_ms", C.c_float), ("total_ms", C.c_float),
+    ]
+
+
+def lib_path():
+    return _LIBPATH
+
+
+def load():
+    """Load the CUDA library; build it in-tree if sources are newer. Raises if it cannot be had."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_LIBPATH):
+        from . import build as _b
+        _b.build()
+    lib = C.CDLL(_LIBPATH)
+    lib.b200_last_error.restype = C.c_char_p
+    _lib = lib
+    return lib
+
+
+def device_count():
+    return load().b200_device_count()
+
+
+def require_device():
+    n = device_count()
+    if n < 1:
+        raise B200Error(B200_E_CUDA, "no CUDA device visible; the B200 registration core has no CPU fallback")
+    return n
+
+
+def _check(st):
+    if st == B200_OK:
+        return
+    msg = load().b200_last_error().decode("utf-8", "replace")
+    if st in (B200_E_NO_MATCHES, B200_E_NAN):
+        raise ConvergenceError(st, msg)
+    raise B200Error(st, msg)
+
+
+def _fp(a):
+    return None if a is None else a.ctypes.data_as(_f32p)
+
+
+def _ip(a):
+    return None if a is None else a.ctypes.data_as(_i32p)
+
+
+def f32(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.float32)
+
+
+def feat4(xyz):
+    xyz = np.asarray(xyz, dtype=np.float32)
+    out = np.ones((xyz.shape[0], 4), dtype=np.float32)
+    out[:, :3] = xyz[:, :3]
+    return out
+
+
+def _colmajor(T):
+    return np.ascontiguousarray(np.asarray(T, np.float32).T).ravel()
+
+
+def _mat(a):
+    return np.array(a, np.float32).reshape(4, 4).T.copy()
+
+
+class Index:
+    """KDTreeMatcher replacement: init() at construction, find_closests() == findClosests()."""
+
+    def __init__(self, ref4, normals=None, device=0, cell_size=0.0, target_per_cell=0.0, max_cells=0):
+        require_device()
+        self.ref4 = f32(ref4)
+        self.normals = f32(normals)
+        self.h = C.c_void_p()
+        opts = IndexOpts(cell_size, target_per_cell, max_cells)
+        _check(load().b200_index_create(C.byref(self.h), device, _fp(self.ref4), _fp(self.normals),
+                                        self.ref4.shape[0], C.byref(opts)))
+        self.visit_counter = 0
+
+    def find_closests(self, q4, knn=1, epsilon=0.0, max_dist=np.inf, max_dist_per_point=None):
+        q4 = f32(q4)
+        n = q4.shape[0]
+        ids = np.empty((n, knn), np.int32)
+        d = np.empty((n, knn), np.float32)
+        mdpp = f32(max_dist_per_point)
+        vis = C.c_uint64()
+        _check(load().b200_index_knn(self.h, _fp(q4), n, knn, C.c_float(epsilon), C.c_float(max_dist), _fp(mdpp),
+                                     _ip(ids), _fp(d), C.byref(vis)))
+        self.visit_counter += vis.value
+        return ids, d
+
+    def info(self):
+        cell = C.c_float()
+        dims = (C.c_int32 * 3)()
+        occ = C.c_int64()
+        ms = C.c_float()
+        _check(load().b200_index_info(self.h, C.byref(cell), dims, C.byref(occ), C.byref(ms)))
+        return dict(cell_size=cell.value, dims=tuple(dims), occupied_cells=occ.value, build_ms=ms.value)
+
+    def close(self):
+        if getattr(self, "h", None) and self.h.value:
+            load().b200_index_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def surface_normals(feat4_, knn=5, max_dist=np.inf, sort_eigen=0, smooth=0, device=0, keep=("normals",)):
+    require_device()
+    f = f32(feat4_)
+    n = f.shape[0]
+    shapes = dict(normals=(n, 3), densities=(n,), eigValues=(n, 3), eigVectors=(n, 9), matchedIds=(n, knn),
+                  meanDists=(n,))
+    out = {k_: (np.empty(shapes[k_], np.float32) if k_ in keep else None) for k_ in shapes}
+    prm = SurfaceNormalParams(knn, max_dist, 0.0, sort_eigen, smooth)
+    _check(load().b200_surface_normals(device, _fp(f), n, C.byref(prm), _fp(out["normals"]), _fp(out["densities"]),
+                                       _fp(out["eigValues"]), _fp(out["eigVectors"]), _fp(out["matchedIds"]),
+                                       _fp(out["meanDists"])))
+    return {k_: v for k_, v in out.items() if v is not None}
+
+
+def dists_quantile(dists, q, device=0):
+    require_device()
+    d = f32(dists).ravel()
+    out = C.c_float()
+    _check(load().b200_dists_quantile(device, _fp(d), C.c_int64(d.size), C.c_float(q), C.byref(out)))
+    return out.value
+
+
+def outlier_dist(kind, param, dists, device=0):
+    require_device()
+    d = f32(dists)
+    w = np.empty_like(d)
+    _check(load().b200_outlier_dist(device, kind, C.c_float(param), _fp(d), C.c_int64(d.size), _fp(w)))
+    return w
+
+
+def outlier_surface_normal(nread, nref, ids, max_angle, device=0):
+    require_device()
+    nread, nref = f32(nread), f32(nref)
+    ids = np.ascontiguousarray(ids, np.int32)
+    n, k = ids.shape
+    w = np.empty((n, k), np.float32)
+    m = 0 if nref is None else nref.shape[0]
+    _check(load().b200_outlier_surface_normal(device, _fp(nread), _fp(nref), m, _ip(ids), k, n, C.c_float(max_angle),
+                                              _fp(w)))
+    return w
+
+
+def error_elements(read4, ref4, refn, w, ids, dists, device=0):
+    require_device()
+    read4, ref4, refn, w, dists = f32(read4), f32(ref4), f32(refn), f32(w), f32(dists)
+    ids = np.ascontiguousarray(ids, np.int32)
+    n, k = ids.shape
+    cap = n * k
+    readP = np.empty((cap, 4), np.float32)
+    refP = np.empty((cap, 4), np.float32)
+    refnP = np.empty((cap, 3), np.float32) if refn is not None else None
+    wP = np.empty(cap, np.float32)
+    idsP = np.empty(cap, np.int32)
+    dP = np.empty(cap, np.float32)
+    P = C.c_int()
+    pur, wpur = C.c_float(), C.c_float()
+    _check(load().b200_error_elements(device, _fp(read4), _fp(ref4), _fp(refn), ref4.shape[0], _fp(w), _ip(ids),
+                                      _fp(dists), k, n, _fp(readP), _fp(refP), _fp(refnP), _fp(wP), _ip(idsP), _fp(dP),
+                                      C.byref(P), C.byref(pur), C.byref(wpur)))
+    p = P.value
+    return dict(reading=readP[:p], reference=refP[:p], ref_normals=None if refnP is None else refnP[:p],
+                weights=wP[:p], ids=idsP[:p], dists=dP[:p], point_used_ratio=pur.value,
+                weighted_point_used_ratio=wpur.value)
+
+
+def p2plane_hessian(readP, refP, refnP, wP, device=0):
+    require_device()
+    readP, refP, refnP, wP = f32(readP), f32(refP), f32(refnP), f32(wP)
+    H = np.empty(36, np.float32)
+    b = np.empty(6, np.float32)
+    _check(load().b200_p2plane_hessian(device, _fp(readP), _fp(refP), _fp(refnP), _fp(wP), readP.shape[0], _fp(H),
+                                       _fp(b)))
+    return H.reshape(6, 6).T.copy(), b
+
+
+def p2plane_solve(H, b, device=0):
+    require_device()
+    A = np.ascontiguousarray(np.asarray(H, np.float32).T).ravel()
+    b = f32(b)
+    x = np.empty(6, np.float32)
+    T = np.empty(16, np.float32)
+    info = C.c_int()
+    _check(load().b200_p2plane_solve(device, _fp(A), _fp(b), _fp(x), _fp(T), C.byref(info)))
+    return x, T.reshape(4, 4).T.copy(), info.value
+
+
+def p2point(readP, refP, wP, device=0):
+    require_device()
+    readP, refP, wP = f32(readP), f32(refP), f32(wP)
+    T = np.empty(16, np.float32)
+    _check(load().b200_p2point(device, _fp(readP), _fp(refP), _fp(wP), readP.shape[0], _fp(T)))
+    return T.reshape(4, 4).T.copy()
+
+
+def rigid_apply(T, feat4_, normals=None, device=0):
+    require_device()
+    f = f32(feat4_).copy()
+    n = None if normals is None else f32(normals).copy()
+    Tc = _colmajor(T)
+    _check(load().b200_rigid_apply(device, _fp(Tc), _fp(f), _fp(n), f.shape[0]))
+    return f, n
+
+
+def default_icp_params(**kw):
+    p = IcpParams()
+    load().b200_icp_default_params(C.byref(p))
+    for k_, v in kw.items():
+        assert hasattr(p, k_), k_
+        setattr(p, k_, v)
+    return p
+
+
+class ICP:
+    """PointMatcher<float>::ICP replacement for the supported chain (see include/b200reg.h)."""
+
+    def __init__(self, params=None, device=0):
+        require_device()
+        self.params = params if params is not None else default_icp_params()
+        self.h = C.c_void_p()
+        _check(load().b200_icp_create(C.byref(self.h), device, C.byref(self.params)))
+        self._n = 0
+
+    def init_reference(self, ref4, normals=None):
+        self._ref4, self._refn = f32(ref4), f32(normals)
+        _check(load().b200_icp_init_reference(self.h, _fp(self._ref4), _fp(self._refn), self._ref4.shape[0]))
+
+    def _result(self, res, st, raise_on_error):
+        out = dict(status=st, iterations=res.iterations, max_iterations_reached=bool(res.max_iterations_reached),
+                   n_matches_last=res.n_matches_last, T=_mat(res.T), T_iter=_mat(res.T_iter),
+                   T_refIn_refMean=_mat(res.T_refIn_refMean), T_refMean_readMean=_mat(res.T_refMean_readMean),
+                   weighted_point_used_ratio=res.weighted_point_used_ratio, point_used_ratio=res.point_used_ratio,
+                   points_touched=res.points_touched, device_ms=res.device_ms, h2d_ms=res.h2d_ms,
+                   total_ms=res.total_ms)
+        if raise_on_error:
+            _check(st)
+        return out
+
+    def compute(self, read4, normals=None, T_init=None, raise_on_error=True):
+        read4, normals = f32(read4), f32(normals)
+        self._n = read4.shape[0]
+        Tc = None if T_init is None else _colmajor(T_init)
+        res = IcpResult()
+        st = load().b200_icp_compute(self.h, _fp(read4), _fp(normals), self._n, _fp(Tc), C.byref(res))
+        return self._result(res, st, raise_on_error)
+
+    def upload_reading(self, read4, normals=None):
+        read4, normals = f32(read4), f32(normals)
+        self._n = read4.shape[0]
+        _check(load().b200_icp_upload_reading(self.h, _fp(read4), _fp(normals), self._n))
+
+    def run_resident(self, T_init=None, raise_on_error=True):
+        Tc = None if T_init is None else _colmajor(T_init)
+        res = IcpResult()
+        st = load().b200_icp_run_resident(self.h, _fp(Tc), C.byref(res))
+        return self._result(res, st, raise_on_error)
+
+    def matches(self):
+        k = self.params.knn
+        ids = np.empty((self._n, k), np.int32)
+        d = np.empty((self._n, k), np.float32)
+        w = np.empty((self._n, k), np.float32)
+        _check(load().b200_icp_get_matches(self.h, _ip(ids), _fp(d), _fp(w)))
+        return ids, d, w
+
+    def log(self, max_log=64):
+        H = np.zeros((max_log, 36), np.float32)
+        b = np.zeros((max_log, 6), np.float32)
+        x = np.zeros((max_log, 6), np.float32)
+        T = np.zeros((max_log, 16), np.float32)
+        P = np.zeros(max_log, np.int32)
+        n = C.c_int()
+        _check(load().b200_icp_get_log(self.h, max_log, _fp(H), _fp(b), _fp(x), _fp(T), _ip(P), C.byref(n)))
+        it = n.value
+        return dict(H=H[:it].reshape(it, 6, 6).transpose(0, 2, 1).copy(), b=b[:it], x=x[:it],
+                    T_iters=T[:it].reshape(it, 4, 4).transpose(0, 2, 1).copy(), P=P[:it])
+
+    def flush_l2(self):
+        _check(load().b200_icp_flush_l2(self.h))
+
+    def close(self):
+        if getattr(self, "h", None) and self.h.value:
+            load().b200_icp_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,462 @@
+// Whole multi-iteration ICP registration as ONE persistent cooperative kernel (no host round trips).
+//
+// Replaces the hot loop of PointMatcher<float>::ICP::computeWithTransformedReference
+// (libpointmatcher/pointmatcher/ICP.cpp:1027-1311) for degeneracyAwareness = None:
+//   transformations.apply      (:1047)  -> apply_T on the fly, never materialised
+//   matcher->findClosests      (:1051)  -> knn_query over the grid index
+//   outlierFilters.compute     (:1055)  -> radix select (TrimmedDist) + per-pair predicates
+//   ErrorElements              (:1061)  -> implicit (pairs with valid dist and non-zero weight)
+//   calculateOptimizationHessian (:1071) -> 27-term accumulation, warp shuffles + one CTA partial
+//   errorMinimizer->compute    (:1205)  -> 6x6 solve + SE(3) in-kernel
+//   T_iter = real * T_iter     (:1213), transformationCheckers.check (:1292)
+// Every CTA redundantly reduces the CTA partials in a fixed order and solves, so all CTAs hold bit-identical
+// state and only grid-wide barriers (no broadcasts) separate the phases.
+#include "icp_kernel.cuh"
+#include "knn.cuh"
+#include "solve.cuh"
+#include <cooperative_groups.h>
+#include <algorithm>
+
+namespace cg = cooperative_groups;
+
+namespace b200 {
+namespace {
+
+struct BlockState {
+  float T_iter[16];
+  float Tc[16];
+  float R9[9];
+  int iterate, status, iteration, maxReached;
+  float counter;
+  int nrot;
+  Quat rot[kMaxHist];
+  float tr[kMaxHist][3];
+  unsigned sel_bin, sel_rank, sel_total;
+  int P, solve_info;
+  float wsum;
+  float H[36], b[6], x[6];
+};
+
+constexpr int kWarps = kIcpThreads / 32;
+
+__device__ __forceinline__ unsigned block_excl_scan(unsigned v, unsigned* s, unsigned& total) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  unsigned inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) s[wid] = inc;
+  __syncthreads();
+  if (wid == 0) {
+    const unsigned w = lane < kWarps ? s[lane] : 0u;
+    unsigned winc = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned t = __shfl_up_sync(0xffffffffu, winc, o);
+      if (lane >= o) winc += t;
+    }
+    s[lane] = winc - w;
+    if (lane == 31) s[32] = winc;
+  }
+  __syncthreads();
+  const unsigned res = s[wid] + inc - v;
+  total = s[32];
+  __syncthreads();
+  return res;
+}
+
+// every CTA finds the bin that holds element `rank` of the global histogram (kHistBins bins). With `first` the rank
+// is derived from the histogram total exactly like Matches::getDistsQuantile (Matches.cpp:82-86):
+// index = (size_t)(float(n_valid) * ratio), the maximum when ratio == 1.
+__device__ __forceinline__ void select_bin(const unsigned* __restrict__ ghist, unsigned rank, bool first, float ratio,
+                                           unsigned* s_scan, BlockState& S) {
+  constexpr int per = kHistBins / kIcpThreads;
+  unsigned c[per], sum = 0;
+#pragma unroll
+  for (int j = 0; j < per; ++j) {
+    c[j] = __ldcg(&ghist[threadIdx.x * per + j]);
+    sum += c[j];
+  }
+  unsigned total;
+  unsigned ex = block_excl_scan(sum, s_scan, total);
+  if (threadIdx.x == 0) S.sel_total = total;
+  if (first && total > 0u) {
+    if (ratio == 1.0f) rank = total - 1u;
+    else {
+      rank = (unsigned)__fmul_rn((float)total, ratio);
+      if (rank > total - 1u) rank = total - 1u;
+    }
+  }
+  if (total > 0u && rank >= ex && rank < ex + sum) {
+#pragma unroll
+    for (int j = 0; j < per; ++j) {
+      if (rank >= ex && rank < ex + c[j]) { S.sel_bin = threadIdx.x * per + j; S.sel_rank = rank - ex; }
+      ex += c[j];
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ void flush_hist(unsigned* s_hist, unsigned* __restrict__ ghist) {
+  __syncthreads();
+  for (int b = threadIdx.x; b < kHistBins; b += kIcpThreads) {
+    const unsigned v = s_hist[b];
+    if (v) atomicAdd(&ghist[b], v);
+  }
+}
+__device__ __forceinline__ void zero_hist(unsigned* s_hist) {
+  for (int b = threadIdx.x; b < kHistBins; b += kIcpThreads) s_hist[b] = 0u;
+  __syncthreads();
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+template <int K>
+__global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __grid_constant__ IcpKernelParams p) {
+  cg::grid_group grid = cg::this_grid();
+  __shared__ BlockState S;
+  __shared__ unsigned s_hist[kHistBins];
+  __shared__ double s_red[kWarps][kAccum];
+  __shared__ unsigned s_scan[40];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int nthreads = gridDim.x * kIcpThreads;
+  const int gtid = blockIdx.x * kIcpThreads + tid;
+  const int k = p.k;
+
+  if (tid == 0) {
+    eye4(S.T_iter);
+    S.iterate = 1; S.status = B200_OK; S.iteration = 0; S.maxReached = 0;
+    S.counter = 0.f;
+    S.nrot = 1;
+    S.rot[0] = quat_from_T(S.T_iter);   // transformationCheckers.init, ICP.cpp:997
+    S.tr[0][0] = S.tr[0][1] = S.tr[0][2] = 0.f;
+    S.P = 0; S.wsum = 0.f; S.solve_info = 0;
+  }
+  __syncthreads();
+  unsigned long long visited_total = 0ull;
+
+  while (true) {
+    if (tid == 0) rigid_prepare(S.T_iter, S.Tc, S.R9);
+    zero_hist(s_hist);  // includes __syncthreads
+    const int par = S.iteration & 1;
+    unsigned* gh = p.hist + (size_t)par * 3 * kHistBins;
+
+    // ---------------- phase 1: transform + match ----------------
+    for (int i = gtid; i < p.N; i += nthreads) {
+      const float4 q = apply_T(S.Tc, __ldg(&p.reading[i]));
+      KList<K> L;
+      unsigned vis = 0;
+      knn_query<K>(p.g, q.x, q.y, q.z, p.md2, k, L, vis);
+      visited_total += vis;
+#pragma unroll
+      for (int j = 0; j < K; ++j)
+        if (j < k) {
+          const size_t e = (size_t)i * k + j;
+          p.ids[e] = L.id[j]; p.dists[e] = L.d[j]; p.spos[e] = L.sp[j];
+          if (p.use_trimmed && L.d[j] != INFINITY) atomicAdd(&s_hist[(__float_as_uint(L.d[j]) >> 20) & 0x7ffu], 1u);
+        }
+    }
+
+    // ---------------- phase 2: TrimmedDist quantile by 3-pass radix select ----------------
+    float limit = INFINITY;
+    if (p.use_trimmed) {
+      flush_hist(s_hist, gh);
+      grid.sync();
+      // Matches::getDistsQuantile, Matches.cpp:60-87: index = (size_t)(float(n_valid) * ratio), max if ratio == 1
+      select_bin(gh, 0u, true, p.trimmed_ratio, s_scan, S);
+      if (S.sel_total == 0u) {  // ConvergenceError("No matches available..."), Matches.cpp:75-76
+        __syncthreads();
+        if (tid == 0) { S.status = B200_E_NO_MATCHES; S.iterate = 0; }
+        __syncthreads();
+        break;
+      }
+      const unsigned bin0 = S.sel_bin, rank0 = S.sel_rank;
+      zero_hist(s_hist);
+      for (int i = gtid; i < p.N; i += nthreads)
+        for (int j = 0; j < k; ++j) {
+          const float d = p.dists[(size_t)i * k + j];
+          const unsigned bits = __float_as_uint(d);
+          if (d != INFINITY && ((bits >> 20) & 0x7ffu) == bin0) atomicAdd(&s_hist[(bits >> 9) & 0x7ffu], 1u);
+        }
+      flush_hist(s_hist, gh + kHistBins);
+      grid.sync();
+      select_bin(gh + kHistBins, rank0, false, 0.f, s_scan, S);
+      const unsigned bin1 = S.sel_bin, rank1 = S.sel_rank;
+      const unsigned pre = (bin0 << 11) | bin1;
+      zero_hist(s_hist);
+      for (int i = gtid; i < p.N; i += nthreads)
+        for (int j = 0; j < k; ++j) {
+          const float d = p.dists[(size_t)i * k + j];
+          const unsigned bits = __float_as_uint(d);
+          if (d != INFINITY && ((bits >> 9) & 0x3fffffu) == pre) atomicAdd(&s_hist[bits & 0x1ffu], 1u);
+        }
+      flush_hist(s_hist, gh + 2 * kHistBins);
+      grid.sync();
+      select_bin(gh + 2 * kHistBins, rank1, false, 0.f, s_scan, S);
+      limit = __uint_as_float((pre << 9) | S.sel_bin);
+    }
+    // zero the other parity's histograms for the next iteration (their last readers finished an iteration ago)
+    {
+      unsigned* gz = p.hist + (size_t)(par ^ 1) * 3 * kHistBins;
+      for (int b = gtid; b < 3 * kHistBins; b += nthreads) gz[b] = 0u;
+    }
+
+    // ---------------- phase 3: weights + linearisation, reduced to one partial per CTA ----------------
+    for (int t = tid; t < kWarps * kAccum; t += kIcpThreads) (&s_red[0][0])[t] = 0.0;
+    __syncthreads();
+    for (int base = blockIdx.x * kIcpThreads + wid * 32; base < p.N; base += nthreads) {
+      const int i = base + lane;
+      const bool in = i < p.N;
+      float4 q = make_float4(0.f, 0.f, 0.f, 1.f);
+      float3 nq = make_float3(0.f, 0.f, 0.f);
+      if (in) {
+        q = apply_T(S.Tc, __ldg(&p.reading[i]));
+        if (p.use_sn && p.reading_n) {
+          const float4 n4 = __ldg(&p.reading_n[i]);
+          const float3 r = apply_R(S.R9, make_float3(n4.x, n4.y, n4.z));
+          float v[3] = {r.x, r.y, r.z}, o[3];
+          normalized3_dev(v, o);
+          nq = make_float3(o[0], o[1], o[2]);
+        }
+      }
+      for (int j = 0; j < k; ++j) {
+        float v[29];
+#pragma unroll
+        for (int t = 0; t < 29; ++t) v[t] = 0.f;
+        double mom[16];
+        bool kept = false;
+        float w = 0.f;
+        float4 r4 = make_float4(0.f, 0.f, 0.f, 0.f), n4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (in) {
+          const size_t e = (size_t)i * k + j;
+          const float d = p.dists[e];
+          const int sp = p.spos[e];
+          // outlier filter chain = product of the filters' weights (OutlierFilter.cpp:84-99); empty chain:
+          // weight = (dist != inf) (:66-83)
+          const bool any = p.use_trimmed || p.use_maxdist || p.use_sn;
+          w = any ? 1.f : (d == INFINITY ? 0.f : 1.f);
+          if (p.use_trimmed) w *= (d <= limit) ? 1.f : 0.f;
+          if (p.use_maxdist) w *= (d <= p.maxdist_lim2) ? 1.f : 0.f;
+          if (sp >= 0) {
+            r4 = __ldg(&p.g.pts[sp]);
+            if (p.g.nrm) n4 = __ldg(&p.g.nrm[sp]);
+          }
+          if (p.use_sn) {
+            if (p.reading_n && p.g.nrm) {
+              if (sp < 0) w = 0.f;
+              else {
+                float nv[3] = {n4.x, n4.y, n4.z}, no[3];
+                normalized3_dev(nv, no);
+                float dotn = __fmul_rn(nq.x, no[0]);
+                dotn = __fadd_rn(dotn, __fmul_rn(nq.y, no[1]));
+                dotn = __fadd_rn(dotn, __fmul_rn(nq.z, no[2]));
+                w *= (dotn < p.sn_cos) ? 0.f : 1.f;
+              }
+            }
+          }
+          p.weights[e] = w;
+          kept = (d != INFINITY) && (w != 0.f);  // ErrorElements, ErrorMinimizer.cpp:103-107
+        }
+        if (kept) {
+          if (p.minimizer == 0) {
+            // crossProduct (ErrorMinimizer.cpp:376-378) and calculateOptimizationHessian (ICP.cpp:1527-1565)
+            float F[6], wF[6];
+            F[0] = __fsub_rn(__fmul_rn(q.y, n4.z), __fmul_rn(q.z, n4.y));
+            F[1] = __fsub_rn(__fmul_rn(q.z, n4.x), __fmul_rn(q.x, n4.z));
+            F[2] = __fsub_rn(__fmul_rn(q.x, n4.y), __fmul_rn(q.y, n4.x));
+            F[3] = n4.x; F[4] = n4.y; F[5] = n4.z;
+#pragma unroll
+            for (int a = 0; a < 6; ++a) wF[a] = __fmul_rn(w, F[a]);
+            float dot = __fmul_rn(__fsub_rn(q.x, r4.x), n4.x);
+            dot = __fadd_rn(dot, __fmul_rn(__fsub_rn(q.y, r4.y), n4.y));
+            dot = __fadd_rn(dot, __fmul_rn(__fsub_rn(q.z, r4.z), n4.z));
+            int t = 0;
+#pragma unroll
+            for (int c = 0; c < 6; ++c)
+#pragma unroll
+              for (int a = 0; a <= c; ++a) v[t++] = __fmul_rn(wF[a], F[c]);
+#pragma unroll
+            for (int a = 0; a < 6; ++a) v[21 + a] = __fmul_rn(wF[a], dot);
+          }
+          v[27] = 1.f;
+          v[28] = w;
+        }
+        if (p.minimizer == 0) {
+#pragma unroll
+          for (int t = 0; t < 29; ++t) {
+            const double s = warp_sum((double)v[t]);
+            if (lane == 0) s_red[wid][t] += s;
+          }
+        } else {
+#pragma unroll
+          for (int t = 0; t < 16; ++t) mom[t] = 0.0;
+          if (kept) {
+            const double wd = (double)w;
+            const double rr[3] = {(double)q.x, (double)q.y, (double)q.z};
+            const double ff[3] = {(double)r4.x, (double)r4.y, (double)r4.z};
+            mom[0] = wd;
+            for (int d = 0; d < 3; ++d) { mom[1 + d] = wd * rr[d]; mom[4 + d] = wd * ff[d]; }
+            for (int c = 0; c < 3; ++c)
+              for (int a = 0; a < 3; ++a) mom[7 + a + 3 * c] = wd * ff[a] * rr[c];
+          }
+#pragma unroll
+          for (int t = 0; t < 16; ++t) {
+            const double s = warp_sum(mom[t]);
+            if (lane == 0) s_red[wid][t] += s;
+          }
+          const double s27 = warp_sum((double)v[27]), s28 = warp_sum((double)v[28]);
+          if (lane == 0) { s_red[wid][27] += s27; s_red[wid][28] += s28; }
+        }
+      }
+    }
+    __syncthreads();
+    if (tid < kAccum) {
+      double s = 0.0;
+      for (int w2 = 0; w2 < kWarps; ++w2) s += s_red[w2][tid];
+      __stcg(&p.partials[(size_t)blockIdx.x * kAccum + tid], s);
+    }
+    grid.sync();
+
+    // ---------------- phase 4: every CTA reduces all partials in block order, solves, updates, checks ----------------
+    if (tid < kAccum) {
+      double s = 0.0;
+      for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(&p.partials[(size_t)b * kAccum + tid]);
+      s_red[0][tid] = s;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      const double* a = s_red[0];
+      const int P = (int)(a[27] + 0.5);
+      S.P = P;
+      S.wsum = (float)a[28];
+      float real[16];
+      eye4(real);
+      for (int t = 0; t < 36; ++t) S.H[t] = 0.f;
+      for (int t = 0; t < 6; ++t) { S.b[t] = 0.f; S.x[t] = 0.f; }
+      if (P == 0) {
+        S.status = B200_E_NO_MATCHES;  // ErrorElements: "no point to minimize", ErrorMinimizer.cpp:75-77
+        S.iterate = 0;
+      } else {
+        if (p.minimizer == 0) {
+          int t = 0;
+          for (int c = 0; c < 6; ++c)
+            for (int r = 0; r <= c; ++r) {
+              const float h = (float)a[t++];
+              S.H[r + 6 * c] = h; S.H[c + 6 * r] = h;
+            }
+          for (int r = 0; r < 6; ++r) S.b[r] = -(float)a[21 + r];
+          solve6_dev(S.H, S.b, S.x, &S.solve_info);
+          p2plane_T_dev(S.x, real);
+        } else {
+          p2point_from_moments(a, real);
+        }
+        mul4_dev(real, S.T_iter, S.T_iter);  // ICP.cpp:1213
+        // transformationCheckers.check, ICP.cpp:1292-1298
+        bool counterHit = false;
+        if (p.max_iterations > 0) {
+          S.counter += 1.f;
+          if (S.counter >= (float)p.max_iterations) counterHit = true;
+        }
+        if (p.use_differential) {
+          const int n = S.nrot;
+          S.rot[n % kMaxHist] = quat_from_T(S.T_iter);
+          S.tr[n % kMaxHist][0] = S.T_iter[12]; S.tr[n % kMaxHist][1] = S.T_iter[13]; S.tr[n % kMaxHist][2] = S.T_iter[14];
+          S.nrot = n + 1;
+          float cv0 = 0.f, cv1 = 0.f;
+          const int Ls = p.smooth;
+          if (S.nrot > Ls) {
+            for (int i = S.nrot - 1; i >= S.nrot - Ls; --i) {
+              const int c = i % kMaxHist, pr = (i - 1) % kMaxHist;
+              cv0 += fabsf(angular_distance(S.rot[c], S.rot[pr]));
+              const float dx = S.tr[c][0] - S.tr[pr][0], dy = S.tr[c][1] - S.tr[pr][1], dz = S.tr[c][2] - S.tr[pr][2];
+              cv1 += fabsf(sqrtf(dx * dx + dy * dy + dz * dz));
+            }
+            cv0 /= (float)Ls;
+            cv1 /= (float)Ls;
+            if (cv0 < p.min_rot && cv1 < p.min_trans) S.iterate = 0;
+          }
+          if (cv0 != cv0 || cv1 != cv1) { S.status = B200_E_NAN; S.iterate = 0; }
+        }
+        if (counterHit) { S.iterate = 0; S.maxReached = 1; }
+      }
+      if (blockIdx.x == 0 && S.iteration < kMaxLog && p.log) {
+        IcpLogEntry& e = p.log[S.iteration];
+        for (int t = 0; t < 36; ++t) e.H[t] = S.H[t];
+        for (int t = 0; t < 6; ++t) { e.b[t] = S.b[t]; e.x[t] = S.x[t]; }
+        for (int t = 0; t < 16; ++t) e.T_iter[t] = S.T_iter[t];
+        e.P = P; e.solve_info = S.solve_info;
+      }
+      S.iteration += 1;
+    }
+    __syncthreads();
+    if (!S.iterate) break;
+  }
+
+  // points touched: one atomic per warp
+  {
+    unsigned long long v = visited_total;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0 && v) atomicAdd(&p.out->points_touched, v);
+  }
+  if (blockIdx.x == 0 && tid == 0) {
+    IcpDeviceResult* o = p.out;
+    o->status = S.status;
+    o->iterations = S.iteration;
+    o->max_iterations_reached = S.maxReached;
+    o->n_matches_last = S.P;
+    for (int t = 0; t < 16; ++t) o->T_iter[t] = S.T_iter[t];
+    // move the result back to the callers' frames, ICP.cpp:1345
+    float invRead[16], r1[16], r2[16], fr[48];
+    for (int t = 0; t < 48; ++t) fr[t] = p.frames[t];
+    inv4_dev(fr + 32, invRead);
+    mul4_dev(fr, S.T_iter, r1);
+    mul4_dev(r1, fr + 16, r2);
+    mul4_dev(r2, invRead, r1);
+    for (int t = 0; t < 16; ++t) o->T[t] = r1[t];
+    const float denom = (float)((long long)p.k * (long long)p.N);
+    o->weighted_point_used_ratio = S.wsum / denom;   // ErrorMinimizer.cpp:139-140
+    o->point_used_ratio = (float)S.P / denom;
+  }
+}
+
+template <int K>
+int launch_k(const IcpKernelParams& p, int device, cudaStream_t s, int* grid_out) {
+  int per_sm = 0, sms = 0;
+  B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, icp_persistent_kernel<K>, kIcpThreads, 0));
+  B200_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+  if (per_sm < 1) { set_error("persistent ICP kernel does not fit on an SM"); return B200_E_CUDA; }
+  int grid = per_sm * sms;
+  // do not launch more CTAs than there is work for (fewer CTAs = cheaper grid barriers)
+  const int need = std::max(1, (p.N + kIcpThreads - 1) / kIcpThreads);
+  grid = std::min(grid, need);
+  IcpKernelParams pc = p;
+  void* args[] = {(void*)&pc};
+  B200_CUDA(cudaLaunchCooperativeKernel((void*)icp_persistent_kernel<K>, dim3(grid), dim3(kIcpThreads), args, 0, s));
+  if (grid_out) *grid_out = grid;
+  return B200_OK;
+}
+
+}  // namespace
+
+size_t icp_partials_capacity(int device) {
+  int sms = 148;
+  if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) { cudaGetLastError(); sms = 148; }
+  return (size_t)sms * 8 * kAccum;  // up to 8 CTAs per SM
+}
+
+int launch_icp_kernel(const IcpKernelParams& p, int device, cudaStream_t s, int* grid_out) {
+  if (p.k <= 1) return launch_k<1>(p, device, s, grid_out);
+  if (p.k <= 4) return launch_k<4>(p, device, s, grid_out);
+  if (p.k <= 16) return launch_k<16>(p, device, s, grid_out);
+  set_error("ICP chain supports knn <= 16 (use b200_index_knn for larger k)");
+  return B200_E_UNSUPPORTED;
+}
+
+}  // namespace b200

@@ -1,0 +1,449 @@
+// C ABI of the whole-registration chain (b200_icp_*): replaces PointMatcher<float>::ICP::{initReference, compute}
+// (libpointmatcher/pointmatcher/ICP.cpp:813-1349). One call = 1 H2D of the reading + 4 kernels
+// (centroid sums -> frames -> reading preparation -> persistent ICP kernel) + 1 D2H of the result struct, with no
+// intermediate host synchronisation.
+#include "common.cuh"
+#include "grid_index.cuh"
+#include "icp_kernel.cuh"
+#include "solve.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <new>
+
+using namespace b200;
+
+namespace {
+
+constexpr int kMeanBlocks = 256;
+constexpr int kMeanThreads = 256;
+
+// per-block partial sums of xyz in double (fixed order => deterministic)
+__global__ void __launch_bounds__(kMeanThreads) read_sum_kernel(const float4* __restrict__ p, int N,
+                                                                double* __restrict__ partials) {
+  double s[3] = {0.0, 0.0, 0.0};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+    const float4 v = __ldg(&p[i]);
+    s[0] += (double)v.x; s[1] += (double)v.y; s[2] += (double)v.z;
+  }
+  __shared__ double sm[3][kMeanThreads / 32];
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    for (int o = 16; o > 0; o >>= 1) s[d] += __shfl_xor_sync(0xffffffffu, s[d], o);
+    if ((threadIdx.x & 31) == 0) sm[d][threadIdx.x >> 5] = s[d];
+  }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    double t = 0.0;
+    for (int w = 0; w < kMeanThreads / 32; ++w) t += sm[threadIdx.x][w];
+    partials[3 * (size_t)blockIdx.x + threadIdx.x] = t;
+  }
+}
+
+// frames[0..15] = T_refIn_refMean (set at initReference); this kernel fills
+// frames[16..31] = T_refMean_readMean = T_refIn_refMean^-1 * T_init * T_readIn_readMean (ICP.cpp:983)
+// frames[32..47] = T_readIn_readMean (ICP.cpp:968-970), frames[48..50] = reading centroid
+__global__ void frames_kernel(const double* __restrict__ partials, int nblocks, int N, const float* __restrict__ Tinit,
+                              float* __restrict__ frames) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  double s[3] = {0.0, 0.0, 0.0};
+  for (int b = 0; b < nblocks; ++b)
+    for (int d = 0; d < 3; ++d) s[d] += partials[3 * (size_t)b + d];
+  float mean[3];
+  for (int d = 0; d < 3; ++d) mean[d] = (float)(s[d] / (double)N);
+  float Tread[16], invRef[16], tmp[16], Tpre[16], Tref[16], Ti[16];
+  eye4(Tread);
+  for (int d = 0; d < 3; ++d) Tread[12 + d] = mean[d];
+  for (int t = 0; t < 16; ++t) { Tref[t] = frames[t]; Ti[t] = Tinit[t]; }
+  inv4_dev(Tref, invRef);
+  mul4_dev(invRef, Ti, tmp);
+  mul4_dev(tmp, Tread, Tpre);
+  for (int t = 0; t < 16; ++t) { frames[16 + t] = Tpre[t]; frames[32 + t] = Tread[t]; }
+  for (int d = 0; d < 3; ++d) frames[48 + d] = mean[d];
+}
+
+// reading.features.topRows(3).colwise() -= mean (ICP.cpp:973), then transformations.apply(reading,
+// T_refMean_readMean) (ICP.cpp:984) incl. the rotation of the "normals" descriptor
+__global__ void prepare_reading_kernel(const float4* __restrict__ raw, const float4* __restrict__ raw_n, int N,
+                                       const float* __restrict__ frames, float4* __restrict__ out,
+                                       float4* __restrict__ out_n) {
+  __shared__ float Tc[16], R9[9], mean[3];
+  if (threadIdx.x == 0) {
+    rigid_prepare(frames + 16, Tc, R9);
+    mean[0] = frames[48]; mean[1] = frames[49]; mean[2] = frames[50];
+  }
+  __syncthreads();
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+    float4 v = __ldg(&raw[i]);
+    v.x = __fsub_rn(v.x, mean[0]); v.y = __fsub_rn(v.y, mean[1]); v.z = __fsub_rn(v.z, mean[2]);
+    out[i] = apply_T(Tc, v);
+    if (raw_n) {
+      const float4 n = __ldg(&raw_n[i]);
+      const float3 r = apply_R(R9, make_float3(n.x, n.y, n.z));
+      out_n[i] = make_float4(r.x, r.y, r.z, 0.f);
+    }
+  }
+}
+
+__global__ void flush_kernel(float4* __restrict__ buf, size_t n, float v) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    buf[i] = make_float4(v, v, v, v);
+}
+
+}  // namespace
+
+struct b200_icp {
+  int device = 0;
+  b200_icp_params prm;
+  cudaStream_t stream = nullptr;
+  MapIndex map;
+  bool ref_ready = false, ref_has_normals = false;
+  // reading
+  float4 *d_raw = nullptr, *d_raw_n = nullptr, *d_read = nullptr, *d_read_n = nullptr;
+  float* d_stage3 = nullptr;
+  size_t cap_read = 0;
+  int N = 0;
+  bool has_read_n = false;
+  // work
+  int *d_ids = nullptr, *d_spos = nullptr;
+  float *d_dists = nullptr, *d_w = nullptr;
+  size_t cap_work = 0;
+  unsigned* d_hist = nullptr;
+  double *d_partials = nullptr, *d_meanpart = nullptr;
+  IcpDeviceResult* d_out = nullptr;
+  IcpLogEntry* d_log = nullptr;
+  float *d_frames = nullptr, *d_Tinit = nullptr;
+  // pinned host mirrors
+  IcpDeviceResult* h_out = nullptr;
+  float* h_frames = nullptr;  // 64 floats
+  float* h_Tinit = nullptr;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  float4* d_flush = nullptr;
+  size_t flush_elems = 0;
+  int last_grid = 0;
+};
+
+namespace {
+
+int icp_alloc_fixed(b200_icp* h) {
+  B200_CUDA(cudaMalloc(&h->d_hist, (size_t)2 * 3 * kHistBins * sizeof(unsigned)));
+  B200_CUDA(cudaMalloc(&h->d_partials, icp_partials_capacity(h->device) * sizeof(double)));
+  B200_CUDA(cudaMalloc(&h->d_meanpart, (size_t)3 * 1024 * sizeof(double)));
+  B200_CUDA(cudaMalloc(&h->d_out, sizeof(IcpDeviceResult)));
+  B200_CUDA(cudaMalloc(&h->d_log, (size_t)kMaxLog * sizeof(IcpLogEntry)));
+  B200_CUDA(cudaMalloc(&h->d_frames, 64 * sizeof(float)));
+  B200_CUDA(cudaMalloc(&h->d_Tinit, 16 * sizeof(float)));
+  B200_CUDA(cudaMallocHost(&h->h_out, sizeof(IcpDeviceResult)));
+  B200_CUDA(cudaMallocHost(&h->h_frames, 64 * sizeof(float)));
+  B200_CUDA(cudaMallocHost(&h->h_Tinit, 16 * sizeof(float)));
+  for (int i = 0; i < 4; ++i) B200_CUDA(cudaEventCreate(&h->ev[i]));
+  B200_CUDA(cudaMemset(h->d_log, 0, (size_t)kMaxLog * sizeof(IcpLogEntry)));
+  return B200_OK;
+}
+
+int icp_ensure_reading(b200_icp* h, int N, bool normals) {
+  if ((size_t)N > h->cap_read) {
+    cudaFree(h->d_raw); cudaFree(h->d_raw_n); cudaFree(h->d_read); cudaFree(h->d_read_n); cudaFree(h->d_stage3);
+    h->d_raw = h->d_raw_n = h->d_read = h->d_read_n = nullptr;
+    h->d_stage3 = nullptr;
+    h->cap_read = 0;
+    const size_t b = (size_t)N * sizeof(float4);
+    B200_CUDA(cudaMalloc(&h->d_raw, b));
+    B200_CUDA(cudaMalloc(&h->d_raw_n, b));
+    B200_CUDA(cudaMalloc(&h->d_read, b));
+    B200_CUDA(cudaMalloc(&h->d_read_n, b));
+    B200_CUDA(cudaMalloc(&h->d_stage3, (size_t)N * 3 * sizeof(float)));
+    h->cap_read = (size_t)N;
+  }
+  const size_t need = (size_t)N * (size_t)h->prm.knn;
+  if (need > h->cap_work) {
+    cudaFree(h->d_ids); cudaFree(h->d_spos); cudaFree(h->d_dists); cudaFree(h->d_w);
+    h->d_ids = h->d_spos = nullptr;
+    h->d_dists = h->d_w = nullptr;
+    h->cap_work = 0;
+    B200_CUDA(cudaMalloc(&h->d_ids, need * sizeof(int)));
+    B200_CUDA(cudaMalloc(&h->d_spos, need * sizeof(int)));
+    B200_CUDA(cudaMalloc(&h->d_dists, need * sizeof(float)));
+    B200_CUDA(cudaMalloc(&h->d_w, need * sizeof(float)));
+    h->cap_work = need;
+  }
+  (void)normals;
+  return B200_OK;
+}
+
+int check_params(const b200_icp_params* p) {
+  if (p->knn < 1) { set_error("KDTreeMatcher: knn must be >= 1"); return B200_E_BAD_PARAM; }
+  if (p->knn > 16) { set_error("ICP chain supports knn <= 16"); return B200_E_UNSUPPORTED; }
+  if (!(p->maxDist >= 0.f)) { set_error("KDTreeMatcher: maxDist must be >= 0"); return B200_E_BAD_PARAM; }
+  if (p->use_trimmed && !(p->trimmed_ratio > 0.f && p->trimmed_ratio <= 1.f)) {
+    set_error("TrimmedDistOutlierFilter: ratio must lie in (0, 1]");
+    return B200_E_BAD_PARAM;
+  }
+  if (p->minimizer != 0 && p->minimizer != 1) { set_error("unknown error minimizer"); return B200_E_BAD_PARAM; }
+  if (p->max_iterations <= 0 && !p->use_differential) {
+    set_error("ICP chain needs at least one transformation checker");
+    return B200_E_BAD_PARAM;
+  }
+  if (p->use_differential && (p->smooth_length < 0 || p->smooth_length > kMaxHist - 2)) {
+    set_error("DifferentialTransformationChecker: smoothLength must lie in [0, 62]");
+    return B200_E_UNSUPPORTED;
+  }
+  return B200_OK;
+}
+
+int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool timed_upload) {
+  cudaStream_t s = h->stream;
+  const int N = h->N;
+  if (Tinit16) std::memcpy(h->h_Tinit, Tinit16, 16 * sizeof(float));
+  else eye4(h->h_Tinit);
+  B200_CUDA(cudaMemcpyAsync(h->d_Tinit, h->h_Tinit, 16 * sizeof(float), cudaMemcpyHostToDevice, s));
+  B200_CUDA(cudaEventRecord(h->ev[1], s));
+  const int mb = std::min(kMeanBlocks, std::max(1, (N + kMeanThreads - 1) / kMeanThreads));
+  read_sum_kernel<<<mb, kMeanThreads, 0, s>>>(h->d_raw, N, h->d_meanpart);
+  frames_kernel<<<1, 32, 0, s>>>(h->d_meanpart, mb, N, h->d_Tinit, h->d_frames);
+  const int pb = std::max(1, std::min(148 * 8, (N + 255) / 256));
+  prepare_reading_kernel<<<pb, 256, 0, s>>>(h->d_raw, h->has_read_n ? h->d_raw_n : nullptr, N, h->d_frames, h->d_read,
+                                            h->d_read_n);
+  B200_CUDA(cudaGetLastError());
+  B200_CUDA(cudaMemsetAsync(h->d_hist, 0, (size_t)2 * 3 * kHistBins * sizeof(unsigned), s));
+  B200_CUDA(cudaMemsetAsync(h->d_out, 0, sizeof(IcpDeviceResult), s));
+  IcpKernelParams p;
+  std::memset(&p, 0, sizeof(p));
+  p.g = h->map.view();
+  p.reading = h->d_read;
+  p.reading_n = h->has_read_n ? h->d_read_n : nullptr;
+  p.N = N; p.k = h->prm.knn;
+  p.md2 = std::isinf(h->prm.maxDist) ? INFINITY : h->prm.maxDist * h->prm.maxDist;
+  p.use_trimmed = h->prm.use_trimmed; p.trimmed_ratio = h->prm.trimmed_ratio;
+  p.use_maxdist = h->prm.use_maxdist_filter; p.maxdist_lim2 = (float)std::pow(h->prm.maxdist_filter, 2);
+  p.use_sn = h->prm.use_surface_normal_filter; p.sn_cos = std::cos(h->prm.surface_normal_max_angle);
+  p.minimizer = h->prm.minimizer;
+  p.max_iterations = h->prm.max_iterations; p.use_differential = h->prm.use_differential;
+  p.min_rot = h->prm.min_diff_rot; p.min_trans = h->prm.min_diff_trans; p.smooth = h->prm.smooth_length;
+  p.ids = h->d_ids; p.dists = h->d_dists; p.spos = h->d_spos; p.weights = h->d_w;
+  p.hist = h->d_hist; p.partials = h->d_partials; p.out = h->d_out; p.log = h->d_log; p.frames = h->d_frames;
+  B200_CUDA(cudaEventRecord(h->ev[2], s));
+  B200_TRY(launch_icp_kernel(p, h->device, s, &h->last_grid));
+  B200_CUDA(cudaEventRecord(h->ev[3], s));
+  B200_CUDA(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(IcpDeviceResult), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaMemcpyAsync(h->h_frames, h->d_frames, 64 * sizeof(float), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  if (res) {
+    std::memset(res, 0, sizeof(*res));
+    const IcpDeviceResult& o = *h->h_out;
+    res->status = o.status; res->iterations = o.iterations;
+    res->max_iterations_reached = o.max_iterations_reached; res->n_matches_last = o.n_matches_last;
+    std::memcpy(res->T, o.T, sizeof(o.T));
+    std::memcpy(res->T_iter, o.T_iter, sizeof(o.T_iter));
+    std::memcpy(res->T_refIn_refMean, h->h_frames, 16 * sizeof(float));
+    std::memcpy(res->T_refMean_readMean, h->h_frames + 16, 16 * sizeof(float));
+    res->weighted_point_used_ratio = o.weighted_point_used_ratio;
+    res->point_used_ratio = o.point_used_ratio;
+    res->points_touched = o.points_touched;
+    B200_CUDA(cudaEventElapsedTime(&res->device_ms, h->ev[2], h->ev[3]));
+    float pre = 0.f;
+    B200_CUDA(cudaEventElapsedTime(&pre, h->ev[1], h->ev[3]));
+    if (timed_upload) {
+      B200_CUDA(cudaEventElapsedTime(&res->h2d_ms, h->ev[0], h->ev[1]));
+      B200_CUDA(cudaEventElapsedTime(&res->total_ms, h->ev[0], h->ev[3]));
+    } else {
+      res->h2d_ms = 0.f;
+      res->total_ms = pre;
+    }
+  }
+  const int st = h->h_out->status;
+  if (st == B200_E_NO_MATCHES) set_error("ConvergenceError: no point to minimize / no matches");
+  else if (st == B200_E_NAN) set_error("ConvergenceError: abs rotation norm not a number");
+  return st;
+}
+
+int icp_upload(b200_icp* h, const float* read4xN, const float* readn3xN, int N) {
+  B200_TRY(icp_ensure_reading(h, N, readn3xN != nullptr));
+  B200_CUDA(cudaEventRecord(h->ev[0], h->stream));
+  B200_TRY(upload_features(h->d_raw, read4xN, N, h->stream));
+  if (readn3xN) B200_TRY(upload_normals(h->d_raw_n, readn3xN, N, h->d_stage3, h->stream));
+  h->N = N;
+  h->has_read_n = readn3xN != nullptr;
+  return B200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+void b200_icp_default_params(b200_icp_params* p) {
+  if (!p) return;
+  std::memset(p, 0, sizeof(*p));
+  p->knn = 1; p->epsilon = 0.f; p->maxDist = INFINITY;            // MatchersImpl.h:83-86
+  p->use_trimmed = 1; p->trimmed_ratio = 0.85f;                    // OutlierFiltersImpl.h:137
+  p->use_maxdist_filter = 0; p->maxdist_filter = 1.f;
+  p->use_surface_normal_filter = 0; p->surface_normal_max_angle = 1.57f;
+  p->minimizer = 0;
+  p->max_iterations = 40;                                          // TransformationCheckersImpl.h:70
+  p->use_differential = 1; p->min_diff_rot = 0.001f; p->min_diff_trans = 0.001f; p->smooth_length = 3;  // :90-92
+  p->cell_size = 0.f;
+}
+
+int b200_icp_create(b200_icp** out, int device, const b200_icp_params* prm) {
+  if (!out || !prm) { set_error("b200_icp_create: bad arguments"); return B200_E_BAD_PARAM; }
+  *out = nullptr;
+  B200_TRY(check_params(prm));
+  DeviceGuard dg(device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  int coop = 0;
+  if (cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device) != cudaSuccess || !coop) {
+    cudaGetLastError();
+    set_error("device does not support cooperative launch");
+    return B200_E_CUDA;
+  }
+  b200_icp* h = new (std::nothrow) b200_icp();
+  if (!h) { set_error("out of host memory"); return B200_E_CUDA; }
+  h->device = device;
+  h->prm = *prm;
+  h->map.device = device;
+  int st = B200_OK;
+  if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess)
+    st = cuda_fail(cudaGetLastError(), "cudaStreamCreate", __FILE__, __LINE__);
+  h->map.stream = h->stream;
+  if (!st) st = icp_alloc_fixed(h);
+  if (st) { b200_icp_destroy(h); return st; }
+  *out = h;
+  return B200_OK;
+}
+
+void b200_icp_destroy(b200_icp* h) {
+  if (!h) return;
+  {
+    DeviceGuard dg(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    cudaFree(h->d_raw); cudaFree(h->d_raw_n); cudaFree(h->d_read); cudaFree(h->d_read_n); cudaFree(h->d_stage3);
+    cudaFree(h->d_ids); cudaFree(h->d_spos); cudaFree(h->d_dists); cudaFree(h->d_w);
+    cudaFree(h->d_hist); cudaFree(h->d_partials); cudaFree(h->d_meanpart); cudaFree(h->d_out); cudaFree(h->d_log);
+    cudaFree(h->d_frames); cudaFree(h->d_Tinit); cudaFree(h->d_flush);
+    cudaFreeHost(h->h_out); cudaFreeHost(h->h_frames); cudaFreeHost(h->h_Tinit);
+    for (int i = 0; i < 4; ++i)
+      if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    h->map.release();
+    if (h->stream) cudaStreamDestroy(h->stream);
+  }
+  delete h;
+}
+
+int b200_icp_init_reference(b200_icp* h, const float* ref4xM, const float* refn3xM, int M) {
+  if (!h || M < 0 || (M > 0 && !ref4xM)) { set_error("b200_icp_init_reference: bad arguments"); return B200_E_BAD_PARAM; }
+  h->ref_ready = false;
+  if (M == 0) {  // "The reference point cloud is empty" — initReference returns false, ICP.cpp:850-855
+    set_error("The reference point cloud is empty");
+    return B200_E_NOT_INITIALIZED;
+  }
+  if (h->prm.minimizer == 0 && !refn3xM) {  // InvalidField at getDescriptorViewByName("normals"), ICP.cpp:1519
+    set_error("PointToPlaneErrorMinimizer needs the 'normals' descriptor on the reference");
+    return B200_E_BAD_PARAM;
+  }
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  cudaStream_t s = h->stream;
+  B200_TRY(index_alloc_points(h->map, M, refn3xM != nullptr));
+  B200_TRY(upload_features(h->map.d_ref, ref4xM, M, s));
+  if (refn3xM) {
+    float* stage = nullptr;
+    B200_CUDA(cudaMallocAsync(&stage, (size_t)M * 3 * sizeof(float), s));
+    const int st = upload_normals(h->map.d_nrm_orig, refn3xM, M, stage, s);
+    cudaFreeAsync(stage, s);
+    if (st) return st;
+  }
+  h->ref_has_normals = refn3xM != nullptr;
+  // centroid in double, rounded to float; reference expressed in <refMean> (ICP.cpp:883-890)
+  double mean[3];
+  B200_TRY(device_mean3(h->map.d_ref, M, h->d_meanpart, mean, s));
+  const float mf[3] = {(float)mean[0], (float)mean[1], (float)mean[2]};
+  B200_TRY(device_subtract3(h->map.d_ref, M, mf[0], mf[1], mf[2], s));
+  b200_index_opts opts;
+  std::memset(&opts, 0, sizeof(opts));
+  opts.cell_size = h->prm.cell_size;
+  B200_TRY(index_build(h->map, &opts));
+  float frames[64];
+  std::memset(frames, 0, sizeof(frames));
+  eye4(frames);
+  frames[12] = mf[0]; frames[13] = mf[1]; frames[14] = mf[2];
+  std::memcpy(h->h_frames, frames, sizeof(frames));
+  B200_CUDA(cudaMemcpyAsync(h->d_frames, h->h_frames, sizeof(frames), cudaMemcpyHostToDevice, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  h->ref_ready = true;
+  return B200_OK;
+}
+
+int b200_icp_compute(b200_icp* h, const float* read4xN, const float* readn3xN, int N, const float* Tinit16,
+                     b200_icp_result* res) {
+  if (!h || N < 0 || (N > 0 && !read4xN)) { set_error("b200_icp_compute: bad arguments"); return B200_E_BAD_PARAM; }
+  if (!h->ref_ready) { set_error("You must setup a matcher before running ICP (no reference)"); return B200_E_NOT_INITIALIZED; }
+  if (N == 0) { set_error("The reading point cloud is empty."); return B200_E_BAD_PARAM; }  // ICP.cpp:958-960
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  B200_TRY(icp_upload(h, read4xN, readn3xN, N));
+  return icp_launch(h, Tinit16, res, true);
+}
+
+int b200_icp_upload_reading(b200_icp* h, const float* read4xN, const float* readn3xN, int N) {
+  if (!h || N <= 0 || !read4xN) { set_error("b200_icp_upload_reading: bad arguments"); return B200_E_BAD_PARAM; }
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  B200_TRY(icp_upload(h, read4xN, readn3xN, N));
+  B200_CUDA(cudaStreamSynchronize(h->stream));
+  return B200_OK;
+}
+
+int b200_icp_run_resident(b200_icp* h, const float* Tinit16, b200_icp_result* res) {
+  if (!h) { set_error("null handle"); return B200_E_BAD_PARAM; }
+  if (!h->ref_ready || h->N <= 0) { set_error("reference or reading not resident"); return B200_E_NOT_INITIALIZED; }
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  return icp_launch(h, Tinit16, res, false);
+}
+
+int b200_icp_get_matches(b200_icp* h, int32_t* ids, float* dists, float* weights) {
+  if (!h || h->N <= 0) { set_error("no registration has run"); return B200_E_NOT_INITIALIZED; }
+  DeviceGuard dg(h->device);
+  const size_t n = (size_t)h->N * h->prm.knn;
+  if (ids) B200_CUDA(cudaMemcpyAsync(ids, h->d_ids, n * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+  if (dists) B200_CUDA(cudaMemcpyAsync(dists, h->d_dists, n * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+  if (weights) B200_CUDA(cudaMemcpyAsync(weights, h->d_w, n * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+  B200_CUDA(cudaStreamSynchronize(h->stream));
+  return B200_OK;
+}
+
+int b200_icp_get_log(b200_icp* h, int max_log, float* H, float* b, float* x, float* T_iter, int32_t* P, int* n) {
+  if (!h || !n) { set_error("b200_icp_get_log: bad arguments"); return B200_E_BAD_PARAM; }
+  DeviceGuard dg(h->device);
+  IcpLogEntry* tmp = new (std::nothrow) IcpLogEntry[kMaxLog];
+  if (!tmp) { set_error("out of host memory"); return B200_E_CUDA; }
+  if (cudaMemcpy(tmp, h->d_log, (size_t)kMaxLog * sizeof(IcpLogEntry), cudaMemcpyDeviceToHost) != cudaSuccess) {
+    delete[] tmp;
+    return cuda_fail(cudaGetLastError(), "cudaMemcpy(log)", __FILE__, __LINE__);
+  }
+  const int cnt = std::min(std::min(max_log, kMaxLog), h->h_out ? h->h_out->iterations : 0);
+  for (int i = 0; i < cnt; ++i) {
+    if (H) std::memcpy(H + 36 * (size_t)i, tmp[i].H, sizeof(tmp[i].H));
+    if (b) std::memcpy(b + 6 * (size_t)i, tmp[i].b, sizeof(tmp[i].b));
+    if (x) std::memcpy(x + 6 * (size_t)i, tmp[i].x, sizeof(tmp[i].x));
+    if (T_iter) std::memcpy(T_iter + 16 * (size_t)i, tmp[i].T_iter, sizeof(tmp[i].T_iter));
+    if (P) P[i] = tmp[i].P;
+  }
+  *n = cnt;
+  delete[] tmp;
+  return B200_OK;
+}
+
+int b200_icp_flush_l2(b200_icp* h) {
+  if (!h) { set_error("null handle"); return B200_E_BAD_PARAM; }
+  DeviceGuard dg(h->device);
+  if (!h->d_flush) {
+    h->flush_elems = ((size_t)256 << 20) / sizeof(float4);  // 256 MiB > 126 MB L2
+    B200_CUDA(cudaMalloc(&h->d_flush, h->flush_elems * sizeof(float4)));
+  }
+  flush_kernel<<<148 * 8, 256, 0, h->stream>>>(h->d_flush, h->flush_elems, 1.0f);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+}  // extern "C"

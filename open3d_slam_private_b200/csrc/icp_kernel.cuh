@@ -1,0 +1,61 @@
+// Parameter block and result layout of the persistent whole-registration kernel (icp_fused.cu).
+#pragma once
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int kIcpThreads = 512;       // threads per CTA of the persistent kernel
+constexpr int kHistBins = 2048;        // radix-select bins per pass (11 + 11 + 9 bits of a non-negative float)
+constexpr int kAccum = 32;             // doubles per CTA partial (29 used)
+constexpr int kMaxHist = 64;           // ring of past poses kept for DifferentialTransformationChecker
+constexpr int kMaxLog = 64;            // per-iteration trace capacity
+
+struct IcpLogEntry {
+  float H[36];
+  float b[6];
+  float x[6];
+  float T_iter[16];
+  int P;
+  int solve_info;
+  int pad[2];
+};
+
+struct IcpDeviceResult {
+  int status;
+  int iterations;
+  int max_iterations_reached;
+  int n_matches_last;
+  float T_iter[16];
+  float T[16];                 // T_refIn_refMean * T_iter * T_refMean_readMean * T_readIn_readMean^-1 (ICP.cpp:1345)
+  float weighted_point_used_ratio;
+  float point_used_ratio;
+  unsigned long long points_touched;
+};
+
+struct IcpKernelParams {
+  GridView g;
+  const float4* reading;    // N points already expressed in the refMean frame (ICP.cpp:984)
+  const float4* reading_n;  // N normals rotated alike, or null
+  int N, k;
+  float md2;                // KDTreeMatcher maxDist^2 (inf allowed)
+  int use_trimmed; float trimmed_ratio;
+  int use_maxdist; float maxdist_lim2;
+  int use_sn; float sn_cos;
+  int minimizer;            // 0 point-to-plane, 1 point-to-point
+  int max_iterations; int use_differential; float min_rot, min_trans; int smooth;
+  // work buffers (k x N)
+  int* ids; float* dists; int* spos; float* weights;
+  unsigned* hist;           // [2][3][kHistBins]
+  double* partials;         // [gridDim.x][kAccum]
+  IcpDeviceResult* out;
+  IcpLogEntry* log;         // kMaxLog entries
+  const float* frames;      // 3 x 16 floats: T_refIn_refMean, T_refMean_readMean, T_readIn_readMean
+};
+
+// launches the persistent kernel for capacity K in {1, 4, 16} (K >= p.k); cooperative launch, grid chosen from
+// the occupancy calculator. Returns the grid size used through *grid_out.
+int launch_icp_kernel(const IcpKernelParams& p, int device, cudaStream_t s, int* grid_out);
+// how many doubles of `partials` the launch needs
+size_t icp_partials_capacity(int device);
+
+}  // namespace b200

@@ -1,0 +1,182 @@
+"""Synthetic LiDAR-shaped workloads (BASELINE configs C2-C5): an analytic street-canyon scene
+(ground, two facing walls, axis-aligned boxes, vertical cylinders), a jittered-lattice map with analytic normals and
+ray-cast 64-beam scans. Pure numpy, seeded, generated at run time (nothing of this size is committed).
+"""
+import numpy as np
+
+SEED = 20261104
+
+
+class Scene:
+    def __init__(self, seed=SEED, length=200.0, width=30.0, wall_h=12.0, n_boxes=200, n_cyl=100):
+        rng = np.random.default_rng(seed)
+        self.length, self.width, self.wall_h = float(length), float(width), float(wall_h)
+        hx, hy = self.length / 2, self.width / 2
+        # boxes: centre (x,y), half sizes, height; sit on the ground
+        e = rng.uniform(0.5, 6.0, size=(n_boxes, 3))
+        cx = rng.uniform(-hx + 4, hx - 4, n_boxes)
+        cy = rng.uniform(-hy + 1, hy - 1, n_boxes)
+        self.box_min = np.stack([cx - e[:, 0] / 2, cy - e[:, 1] / 2, np.zeros(n_boxes)], 1)
+        self.box_max = np.stack([cx + e[:, 0] / 2, cy + e[:, 1] / 2, e[:, 2]], 1)
+        self.cyl_c = np.stack([rng.uniform(-hx + 2, hx - 2, n_cyl), rng.uniform(-hy + 1, hy - 1, n_cyl)], 1)
+        self.cyl_r = rng.uniform(0.15, 0.5, n_cyl)
+        self.cyl_h = rng.uniform(2.0, 8.0, n_cyl)
+
+    # ---- surfaces as parametric patches ----
+    def _rects(self):
+        """list of (origin, u, v, normal) rectangles"""
+        hx, hy, H = self.length / 2, self.width / 2, self.wall_h
+        R = [(np.array([-hx, -hy, 0.0]), np.array([2 * hx, 0, 0.0]), np.array([0, 2 * hy, 0.0]), np.array([0, 0, 1.0])),
+             (np.array([-hx, -hy, 0.0]), np.array([2 * hx, 0, 0.0]), np.array([0, 0, H]), np.array([0, 1.0, 0])),
+             (np.array([-hx, hy, 0.0]), np.array([2 * hx, 0, 0.0]), np.array([0, 0, H]), np.array([0, -1.0, 0]))]
+        for mn, mx in zip(self.box_min, self.box_max):
+            d = mx - mn
+            R.append((np.array([mn[0], mn[1], mx[2]]), np.array([d[0], 0, 0]), np.array([0, d[1], 0]), np.array([0, 0, 1.0])))
+            R.append((mn.copy(), np.array([d[0], 0, 0]), np.array([0, 0, d[2]]), np.array([0, -1.0, 0])))
+            R.append((np.array([mn[0], mx[1], mn[2]]), np.array([d[0], 0, 0]), np.array([0, 0, d[2]]), np.array([0, 1.0, 0])))
+            R.append((mn.copy(), np.array([0, d[1], 0]), np.array([0, 0, d[2]]), np.array([-1.0, 0, 0])))
+            R.append((np.array([mx[0], mn[1], mn[2]]), np.array([0, d[1], 0]), np.array([0, 0, d[2]]), np.array([1.0, 0, 0])))
+        return R
+
+    def area(self):
+        a = sum(np.linalg.norm(u) * np.linalg.norm(v) for _, u, v, _ in self._rects())
+        a += float(np.sum(2 * np.pi * self.cyl_r * self.cyl_h))
+        return a
+
+    def sample_map(self, M, seed=SEED + 1, jitter=0.01):
+        """exactly M points on the surfaces (jittered lattice), float32 xyz + analytic normals, shuffled."""
+        rng = np.random.default_rng(seed)
+        s = np.sqrt(self.area() / (M * 1.02))
+        pts, nrm = [], []
+        for o, u, v, n in self._rects():
+            lu, lv = np.linalg.norm(u), np.linalg.norm(v)
+            nu, nv = max(1, int(np.ceil(lu / s))), max(1, int(np.ceil(lv / s)))
+            a = (np.arange(nu) + 0.5) / nu
+            b = (np.arange(nv) + 0.5) / nv
+            A, B = np.meshgrid(a, b, indexing="ij")
+            p = o[None, :] + A.reshape(-1, 1) * u[None, :] + B.reshape(-1, 1) * v[None, :]
+            pts.append(p)
+            nrm.append(np.broadcast_to(n, p.shape))
+        for c, r, h in zip(self.cyl_c, self.cyl_r, self.cyl_h):
+            na, nh = max(3, int(np.ceil(2 * np.pi * r / s))), max(1, int(np.ceil(h / s)))
+            ang = (np.arange(na) + 0.5) / na * 2 * np.pi
+            zz = (np.arange(nh) + 0.5) / nh * h
+            A, Z = np.meshgrid(ang, zz, indexing="ij")
+            d = np.stack([np.cos(A.ravel()), np.sin(A.ravel()), np.zeros(A.size)], 1)
+            p = np.stack([c[0] + r * d[:, 0], c[1] + r * d[:, 1], Z.ravel()], 1)
+            pts.append(p)
+            nrm.append(d)
+        P = np.concatenate(pts)
+        Nn = np.concatenate(nrm)
+        if P.shape[0] < M:  # top up with random duplicates of the lattice (never happens with the 2 % margin)
+            extra = rng.integers(0, P.shape[0], M - P.shape[0])
+            P = np.concatenate([P, P[extra]])
+            Nn = np.concatenate([Nn, Nn[extra]])
+        perm = rng.permutation(P.shape[0])[:M]
+        P = P[perm] + rng.uniform(-jitter, jitter, size=(M, 3))
+        return P.astype(np.float32), np.ascontiguousarray(Nn[perm]).astype(np.float32)
+
+    # ---- ray casting ----
+    def raycast(self, origin, dirs, max_range=100.0):
+        """distance along each ray to the first surface (inf when none within max_range)"""
+        n = dirs.shape[0]
+        t = np.full(n, np.inf)
+        hx, hy, H = self.length / 2, self.width / 2, self.wall_h
+        with np.errstate(divide="ignore", invalid="ignore"):
+            tg = -origin[2] / dirs[:, 2]
+            pg = origin[None, :2] + tg[:, None] * dirs[:, :2]
+            ok = (tg > 0) & (np.abs(pg[:, 0]) <= hx) & (np.abs(pg[:, 1]) <= hy)
+            t = np.where(ok & (tg < t), tg, t)
+            for ywall in (-hy, hy):
+                tw = (ywall - origin[1]) / dirs[:, 1]
+                pw_x = origin[0] + tw * dirs[:, 0]
+                pw_z = origin[2] + tw * dirs[:, 2]
+                ok = (tw > 0) & (np.abs(pw_x) <= hx) & (pw_z >= 0) & (pw_z <= H)
+                t = np.where(ok & (tw < t), tw, t)
+            # boxes: slab test, chunked over rays
+            inv = 1.0 / dirs
+            for lo in range(0, n, 16384):
+                sl = slice(lo, min(n, lo + 16384))
+                t1 = (self.box_min[None, :, :] - origin[None, None, :]) * inv[sl, None, :]
+                t2 = (self.box_max[None, :, :] - origin[None, None, :]) * inv[sl, None, :]
+                tn = np.nanmax(np.minimum(t1, t2), axis=2)
+                tf = np.nanmin(np.maximum(t1, t2), axis=2)
+                hit = (tf >= np.maximum(tn, 0)) & (tn > 0)
+                tb = np.where(hit, tn, np.inf).min(axis=1)
+                t[sl] = np.minimum(t[sl], tb)
+                # cylinders
+                dxy = dirs[sl, :2]
+                a = np.sum(dxy * dxy, axis=1)[:, None]
+                oc = origin[None, None, :2] - self.cyl_c[None, :, :]
+                b = 2 * np.sum(oc * dxy[:, None, :], axis=2)
+                c = np.sum(oc * oc, axis=2) - self.cyl_r[None, :] ** 2
+                disc = b * b - 4 * a * c
+                tc = (-b - np.sqrt(np.where(disc >= 0, disc, np.nan))) / (2 * a)
+                z = origin[2] + tc * dirs[sl, 2][:, None]
+                hitc = (disc >= 0) & (tc > 0) & (z >= 0) & (z <= self.cyl_h[None, :])
+                tcm = np.where(hitc, tc, np.inf).min(axis=1)
+                t[sl] = np.minimum(t[sl], tcm)
+        t[t > max_range] = np.inf
+        return t
+
+    def scan(self, pose_xyyaw, n_points=131072, rings=64, seed=0, noise=0.02, height=1.8, max_range=100.0):
+        """64-beam scan from a sensor pose; returns (points in the SENSOR frame (n,3) float32, T_map_sensor 4x4)."""
+        rng = np.random.default_rng(SEED + 1000 + seed)
+        x, y, yaw = pose_xyyaw
+        az_n = int(np.ceil(n_points / rings * 1.25))
+        elev = np.deg2rad(np.linspace(-24.8, 2.0, rings))
+        az = (np.arange(az_n) + rng.uniform(0, 1)) / az_n * 2 * np.pi
+        E, A = np.meshgrid(elev, az, indexing="ij")
+        d_s = np.stack([np.cos(E) * np.cos(A), np.cos(E) * np.sin(A), np.sin(E)], -1).reshape(-1, 3)
+        c, s = np.cos(yaw), np.sin(yaw)
+        Rm = np.array([[c, -s, 0], [s, c, 0], [0, 0, 1.0]])
+        origin = np.array([x, y, height])
+        t = self.raycast(origin, d_s @ Rm.T, max_range)
+        hit = np.isfinite(t)
+        idx = np.flatnonzero(hit)
+        if idx.size < n_points:
+            raise RuntimeError("scene too open for this pose: %d hits < %d" % (idx.size, n_points))
+        # keep an even subset of the hits (preserves the ring structure)
+        idx = idx[np.linspace(0, idx.size - 1, n_points).astype(np.int64)]
+        r = t[idx] + rng.normal(0, noise, n_points)
+        pts_s = d_s[idx] * r[:, None]
+        T = np.eye(4)
+        T[:3, :3] = Rm
+        T[:3, 3] = origin
+        return pts_s.astype(np.float32), T
+
+
+def perturbation(seed, trans=0.25, rot_deg=2.0):
+    """initial-guess error: translation U(-trans, trans) per axis, rotation rot_deg about a random axis"""
+    rng = np.random.default_rng(SEED + 5000 + seed)
+    tr = rng.uniform(-trans, trans, 3)
+    ax = rng.normal(size=3)
+    ax /= np.linalg.norm(ax)
+    th = np.deg2rad(rot_deg)
+    K = np.array([[0, -ax[2], ax[1]], [ax[2], 0, -ax[0]], [-ax[1], ax[0], 0]])
+    R = np.eye(3) + np.sin(th) * K + (1 - np.cos(th)) * K @ K
+    T = np.eye(4)
+    T[:3, :3] = R
+    T[:3, 3] = tr
+    return T
+
+
+def feat4(xyz):
+    out = np.ones((xyz.shape[0], 4), np.float32)
+    out[:, :3] = xyz
+    return out
+
+
+def make_c2(M=5_000_000, N=131072, n_poses=32, seed=SEED, scene_kw=None):
+    """BASELINE config C2: map (M points + normals), n_poses scans of N points with truth and initial guesses."""
+    sc = Scene(seed=seed, **(scene_kw or {}))
+    map_xyz, map_n = sc.sample_map(M)
+    rng = np.random.default_rng(seed + 77)
+    scans = []
+    for i in range(n_poses):
+        pose = (rng.uniform(-sc.length / 2 + 20, sc.length / 2 - 20), rng.uniform(-sc.width / 2 + 4, sc.width / 2 - 4),
+                rng.uniform(-np.pi, np.pi))
+        pts, T_true = sc.scan(pose, n_points=N, seed=i)
+        T_init = T_true @ perturbation(i)
+        scans.append(dict(xyz=pts, T_true=T_true, T_init=T_init.astype(np.float32)))
+    return dict(scene=sc, map_xyz=map_xyz, map_normals=map_n, scans=scans)

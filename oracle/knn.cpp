@@ -28,7 +28,7 @@ struct KBest {
     for (int j = 0; j < k; ++j) { ids[j] = -1; dists[j] = std::numeric_limits<float>::infinity(); }
   }
   inline bool better(float d, int32_t id, int slot) const {
-    return d < dists[slot] || (d == dists[slot] && (ids[slot] < 0 || id < ids[slot]));
+    return d < dists[slot] || (d == dists[slot] && id < ids[slot]);
   }
   inline void offer(float d, int32_t id) {
     if (!better(d, id, k - 1)) return;

@@ -60,7 +60,7 @@ struct FullPivQR {
       }
       rowTransp[k] = rb;
       colTransp[k] = cb;
-      if (k != rb) { for (int j = 0; j < N; ++j) std::swap(at(k, j), at(rb, j)); ++numTransp; }
+      if (k != rb) { for (int j = k; j < N; ++j) std::swap(at(k, j), at(rb, j)); ++numTransp; }  // tail only, as Eigen
       if (k != cb) { for (int i = 0; i < N; ++i) std::swap(at(i, k), at(i, cb)); ++numTransp; }
       // makeHouseholderInPlace on column k, rows k..N-1
       T tailSq = T(0);

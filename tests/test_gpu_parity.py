@@ -1,0 +1,368 @@
+"""GPU parity tests: the CUDA path (through the C ABI, ctypes) against the CPU oracle on the same inputs.
+
+Bars (north_star): kNN ids / dists and outlier masks BIT-EXACT; H, b, poses within float tolerance
+(rotation < 1e-5 rad, translation < 1e-5 m after convergence) with identical iteration counts.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle_py as O
+from open3d_slam_private_b200 import capi as B
+
+pytestmark = pytest.mark.gpu
+
+ROT_TOL = 1e-5   # rad
+TRANS_TOL = 1e-5  # m
+
+
+def bits(a):
+    return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
+def rot_angle(Ra, Rb):
+    R = Ra.astype(np.float64).T @ Rb.astype(np.float64)
+    return float(np.arccos(np.clip((np.trace(R) - 1) / 2, -1, 1)))
+
+
+@pytest.fixture(scope="module")
+def gold(golden_dir):
+    g = json.load(open(os.path.join(golden_dir, "reference_goldens.json")))
+    g["c400"] = np.load(os.path.join(golden_dir, "car_cloud400.npz"))
+    g["c401"] = np.load(os.path.join(golden_dir, "car_cloud401.npz"))
+    g["cloud0"] = np.load(os.path.join(golden_dir, "cloud.00000.npz"))["xyz"]
+    g["cloud1"] = np.load(os.path.join(golden_dir, "cloud.00001.npz"))["xyz"]
+    return g
+
+
+def to_b(p):
+    """oracle IcpParams -> C-ABI IcpParams"""
+    return B.default_icp_params(knn=p.knn, maxDist=p.maxDist, use_trimmed=p.use_trimmed, trimmed_ratio=p.trimmed_ratio,
+                                use_maxdist_filter=p.use_maxdist_filter, maxdist_filter=p.maxdist_filter,
+                                use_surface_normal_filter=p.use_surface_normal_filter,
+                                surface_normal_max_angle=p.surface_normal_max_angle, minimizer=p.minimizer,
+                                max_iterations=p.max_iterations, use_differential=p.use_differential,
+                                min_diff_rot=p.min_diff_rot, min_diff_trans=p.min_diff_trans,
+                                smooth_length=p.smooth_length)
+
+
+# ----------------------------------------------------------------------------------------------------- kNN
+@pytest.mark.parametrize("k,md", [(1, np.inf), (1, 0.5), (1, 0.05), (2, np.inf), (3, 0.5), (5, np.inf), (10, 0.3),
+                                  (20, np.inf), (33, 1.0)])
+def test_knn_bit_exact_car_clouds(gold, k, md):
+    """ui/Matcher.cpp:40-64 sweeps knn x epsilon x maxDist on these clouds; here ids/dists are pinned bit-exact."""
+    ref4 = O.feat4(gold["c400"]["xyz"])
+    q4 = O.feat4(gold["c401"]["xyz"])
+    idx = B.Index(ref4)
+    ids, d = idx.find_closests(q4, knn=k, max_dist=md)
+    oi, od = O.KdTree(ref4).knn(q4, k, md, threads=4)
+    assert (ids == oi).all()
+    assert (bits(d) == bits(od)).all()
+    assert idx.visit_counter > 0
+
+
+@pytest.mark.parametrize("cell", [0.0, 0.02, 0.3, 5.0])
+def test_knn_independent_of_cell_size(gold, cell):
+    ref4 = O.feat4(gold["c400"]["xyz"][::3])
+    q4 = O.feat4(gold["c401"]["xyz"][::5])
+    ids, d = B.Index(ref4, cell_size=cell).find_closests(q4, knn=4, max_dist=np.inf)
+    oi, od = O.KdTree(ref4).knn(q4, 4, np.inf)
+    assert (ids == oi).all() and (bits(d) == bits(od)).all()
+
+
+def test_knn_ties_duplicates_and_outside_queries():
+    rng = np.random.default_rng(11)
+    base = rng.integers(-20, 20, size=(3000, 3)).astype(np.float32) * 0.25  # lattice => many exact ties
+    ref = np.concatenate([base, base[:500], base[:100]])                    # duplicate points
+    ref4 = O.feat4(ref)
+    q = np.concatenate([rng.integers(-24, 24, size=(2000, 3)).astype(np.float32) * 0.25,
+                        rng.uniform(-200, 200, size=(200, 3)).astype(np.float32),       # far outside the grid
+                        np.array([[1e6, 0, 0], [0, -1e6, 1e6]], np.float32)])
+    q4 = O.feat4(q)
+    idx = B.Index(ref4)
+    for k, md in ((1, np.inf), (4, np.inf), (7, 1.0), (1, 0.1)):
+        ids, d = idx.find_closests(q4, knn=k, max_dist=md)
+        oi, od = O.knn_brute(ref4, q4, k, md)
+        assert (ids == oi).all(), (k, md)
+        assert (bits(d) == bits(od)).all()
+
+
+def test_knn_edge_cases():
+    ref4 = O.feat4(np.array([[0, 0, 0], [1, 1, 1]], np.float32))
+    idx = B.Index(ref4)
+    ids, d = idx.find_closests(O.feat4(np.array([[0.1, 0, 0]], np.float32)), knn=5)   # k > M
+    assert ids[0].tolist() == [0, 1, -1, -1, -1] and np.isinf(d[0, 2:]).all()
+    ids, d = idx.find_closests(np.zeros((0, 4), np.float32), knn=1)                    # empty query
+    assert ids.shape == (0, 1)
+    ids, d = idx.find_closests(O.feat4(np.array([[np.nan, 0, 0]], np.float32)), knn=1)  # NaN query: no match
+    assert ids[0, 0] == -1
+    one = B.Index(O.feat4(np.array([[2, 3, 4]], np.float32)))                          # single point, degenerate bbox
+    ids, d = one.find_closests(O.feat4(np.array([[2, 3, 5]], np.float32)), knn=1)
+    assert ids[0, 0] == 0 and d[0, 0] == 1.0
+    with pytest.raises(B.B200Error):
+        idx.find_closests(ref4, knn=65)
+
+
+def test_knn_var_dist(gold):
+    """KDTreeVarDistMatcher (MatchersImpl.cpp:133-150): per-point radius."""
+    ref4 = O.feat4(gold["c400"]["xyz"])
+    q4 = O.feat4(gold["c401"]["xyz"][:4000])
+    rng = np.random.default_rng(2)
+    radii = rng.uniform(0.01, 0.3, q4.shape[0]).astype(np.float32)
+    ids, d = B.Index(ref4).find_closests(q4, knn=2, max_dist_per_point=radii)
+    kd = O.KdTree(ref4)
+    for i in range(0, 4000, 97):
+        oi, od = kd.knn(q4[i:i + 1], 2, float(radii[i]))
+        assert (ids[i] == oi[0]).all() and (bits(d[i]) == bits(od[0])).all()
+
+
+# ----------------------------------------------------------------------------------------------------- outlier filters
+def test_outlier_filters_bit_exact(gold):
+    ref4 = O.feat4(gold["c400"]["xyz"])
+    q4 = O.feat4(gold["c401"]["xyz"])
+    ids, d = O.KdTree(ref4).knn(q4, 3, 0.08, threads=4)   # contains invalid (inf) entries
+    assert np.isinf(d).any()
+    for q in (0.0, 0.1, 0.5, 0.85, 0.9, 0.999999, 1.0):
+        st, v = O.dists_quantile(d, q)
+        assert st == 0 and B.dists_quantile(d, q) == v
+        st, w = O.outlier_trimmed(d, q)
+        assert (B.outlier_dist(B.OUTLIER_TRIMMEDDIST, q, d) == w).all()
+    assert (B.outlier_dist(B.OUTLIER_MAXDIST, 0.05, d) == O.outlier_maxdist(d, 0.05)[1]).all()
+    assert (B.outlier_dist(B.OUTLIER_MINDIST, 0.02, d) == O.outlier_mindist(d, 0.02)[1]).all()
+    assert (B.outlier_dist(B.OUTLIER_MEDIANDIST, 3.0, d) == O.outlier_median(d, 3.0)[1]).all()
+    assert (B.outlier_dist(B.OUTLIER_NULL, 0.0, d) == O.outlier_null(d)[1]).all()
+    # all invalid -> ConvergenceError (Matches.cpp:75-76)
+    with pytest.raises(B.ConvergenceError):
+        B.outlier_dist(B.OUTLIER_TRIMMEDDIST, 0.9, np.full((10, 1), np.inf, np.float32))
+    # many equal values around the quantile
+    dd = np.repeat(np.array([0.5, 0.25, 0.25, 1.0], np.float32), 1000)
+    for q in (0.3, 0.5, 0.74, 0.76):
+        assert B.dists_quantile(dd, q) == O.dists_quantile(dd, q)[1]
+
+
+def test_outlier_surface_normal_bit_exact(gold):
+    ref4, refn = O.feat4(gold["c400"]["xyz"]), gold["c400"]["normals"]
+    q4 = O.feat4(gold["c401"]["xyz"])
+    ids, d = O.KdTree(ref4).knn(q4, 2, 0.1, threads=4)
+    rng = np.random.default_rng(4)
+    nread = rng.normal(size=(q4.shape[0], 3)).astype(np.float32)
+    for ang in (0.3, 1.0, 1.57):
+        st, w = O.outlier_surface_normal(nread, refn, ids, ang)
+        assert (B.outlier_surface_normal(nread, refn, ids, ang) == w).all()
+    assert (B.outlier_surface_normal(None, None, ids, 1.0) == 1).all()
+
+
+# ----------------------------------------------------------------------------------------------------- error minimizer
+@pytest.fixture(scope="module")
+def matched(gold):
+    ref4, refn = O.feat4(gold["c400"]["xyz"]), gold["c400"]["normals"]
+    q4 = O.feat4(gold["c401"]["xyz"])
+    ids, d = O.KdTree(ref4).knn(q4, 2, 0.15, threads=4)
+    st, w = O.outlier_trimmed(d, 0.8)
+    return ref4, refn, q4, ids, d, w
+
+
+def test_error_elements_bit_exact(matched):
+    ref4, refn, q4, ids, d, w = matched
+    st, o = O.error_elements(q4, ref4, refn, w, ids, d)
+    g = B.error_elements(q4, ref4, refn, w, ids, d)
+    assert g["reading"].shape == o["reading"].shape
+    for key in ("reading", "reference", "ref_normals", "weights", "dists"):
+        assert (bits(g[key]) == bits(o[key])).all(), key
+    assert (g["ids"] == o["ids"]).all()
+    assert g["point_used_ratio"] == o["point_used_ratio"]
+    assert g["weighted_point_used_ratio"] == o["weighted_point_used_ratio"]
+    with pytest.raises(B.ConvergenceError):
+        B.error_elements(q4, ref4, refn, np.zeros_like(w), ids, d)
+
+
+def test_hessian_solve_and_p2point(matched):
+    ref4, refn, q4, ids, d, w = matched
+    st, o = O.error_elements(q4, ref4, refn, w, ids, d)
+    H, b = O.p2plane_hb(o["reading"], o["reference"], o["ref_normals"], o["weights"], accum=1)
+    Hg, bg = B.p2plane_hessian(o["reading"], o["reference"], o["ref_normals"], o["weights"])
+    assert np.abs(Hg - H).max() <= 2e-6 * np.abs(H).max()
+    assert np.abs(bg - b).max() <= 2e-6 * max(np.abs(b).max(), 1e-3)
+    x, info = O.solve6(H, b)
+    xg, Tg, infog = B.p2plane_solve(H, b)
+    assert info == infog == 0
+    assert np.allclose(xg, x, rtol=1e-5, atol=1e-7)
+    T = O.p2plane_T(x)
+    assert np.abs(Tg - T).max() < 1e-6
+    # rank-deficient (icpSingular-like) system takes the same branch
+    H2 = H.copy()
+    H2[[2, 3, 4], :] = 0
+    H2[:, [2, 3, 4]] = 0
+    b2 = b.copy()
+    b2[[2, 3, 4]] = 0
+    x2, i2 = O.solve6(H2, b2)
+    xg2, _, ig2 = B.p2plane_solve(H2, b2)
+    assert i2 == ig2 == 1 and np.allclose(xg2, x2, rtol=1e-4, atol=1e-6)
+    # zero system -> identity (NaN guard, PointToPlane.cpp:374-380)
+    xz, Tz, _ = B.p2plane_solve(np.zeros((6, 6), np.float32), np.zeros(6, np.float32))
+    assert (Tz == np.eye(4)).all()
+    Tp = O.p2point_T(o["reading"], o["reference"], o["weights"])
+    Tpg = B.p2point(o["reading"], o["reference"], o["weights"])
+    assert np.abs(Tpg - Tp).max() < 2e-6
+
+
+def test_rigid_apply_bit_exact(gold):
+    rng = np.random.default_rng(9)
+    f = O.feat4(gold["cloud0"])
+    n = rng.normal(size=(f.shape[0], 3)).astype(np.float32)
+    T = O.p2plane_T(np.array([0.02, -0.01, 0.03, 0.5, -0.2, 0.1], np.float32))
+    for Tm in (T, np.diag([1.1, 1, 1, 1]).astype(np.float32) @ T):   # second one triggers correctParameters
+        fo, no = O.rigid_apply(Tm, f, n)
+        fg, ng = B.rigid_apply(Tm, f, n)
+        assert (bits(fg) == bits(fo)).all() and (bits(ng) == bits(no)).all()
+
+
+# ----------------------------------------------------------------------------------------------------- surface normals
+@pytest.mark.parametrize("knn,md,sort", [(5, np.inf, 0), (10, np.inf, 1), (20, 1.0, 0)])
+def test_surface_normals(gold, knn, md, sort):
+    f = O.feat4(gold["cloud0"])
+    st, o = O.surface_normals(f, knn, md, sort_eigen=sort)
+    g = B.surface_normals(f, knn, md, sort_eigen=sort,
+                          keep=("normals", "densities", "eigValues", "eigVectors", "matchedIds", "meanDists"))
+    assert (g["matchedIds"] == o["matchedIds"]).all()          # self-kNN ids bit-exact
+    assert (bits(g["densities"]) == bits(o["densities"])).all()
+    assert (bits(g["meanDists"]) == bits(o["meanDists"])).all()
+    assert np.allclose(g["eigValues"], o["eigValues"], rtol=1e-5, atol=1e-9)
+    # normals modulo sign (eigenvector sign is an artefact of the eigen solver)
+    dots = np.abs(np.sum(g["normals"] * o["normals"], axis=1))
+    nz = np.linalg.norm(o["normals"], axis=1) > 0
+    assert (dots[nz] > 1 - 1e-5).mean() > 0.999   # near-degenerate eigenvalue pairs may rotate within the eigenspace
+    assert (np.linalg.norm(g["normals"][~nz], axis=1) == 0).all()
+
+
+# ----------------------------------------------------------------------------------------------------- whole ICP
+def run_both(p, ref4, refn, read4, readn=None, T_init=None):
+    o = O.icp(p, ref4, refn, read4, readn, T_init)
+    icp = B.ICP(to_b(p))
+    icp.init_reference(ref4, refn)
+    g = icp.compute(read4, readn, T_init, raise_on_error=False)
+    return o, g, icp
+
+
+def assert_icp_parity(o, g, icp, check_matches=True):
+    assert g["status"] == o["status"]
+    assert g["iterations"] == o["iterations"], (g["iterations"], o["iterations"])
+    assert g["max_iterations_reached"] == o["max_iterations_reached"]
+    assert np.abs(g["T"][:3, 3] - o["T"][:3, 3]).max() < TRANS_TOL
+    assert rot_angle(g["T"][:3, :3], o["T"][:3, :3]) < ROT_TOL
+    assert g["n_matches_last"] == o["n_matches_last"]
+    if check_matches:
+        ids, d, w = icp.matches()
+        assert (ids == o["ids"]).all()
+        assert (bits(d) == bits(o["dists"])).all()
+        assert (w == o["weights"]).all()
+    lg = icp.log()
+    n = min(len(lg["P"]), len(o["P"]))
+    assert (lg["P"][:n] == o["P"][:n]).all()
+    if n and np.abs(o["H"][0]).max() > 0:
+        assert np.abs(lg["H"][0] - o["H"][0]).max() <= 5e-6 * np.abs(o["H"][0]).max()
+
+
+def test_icp_validT3d_and_parity(gold):
+    ref4, refn = O.feat4(gold["c400"]["xyz"]), gold["c400"]["normals"]
+    read4 = O.feat4(gold["c401"]["xyz"])
+    o, g, icp = run_both(O.default_params(), ref4, refn, read4)
+    assert_icp_parity(o, g, icp)
+    V = np.array(gold["validT3d"])
+    assert abs(np.linalg.norm(V[:3, 3]) - np.linalg.norm(g["T"][:3, 3])) < 0.1   # utest.h:83-84
+    assert rot_angle(V[:3, :3], g["T"][:3, :3]) < 0.1
+
+
+@pytest.mark.parametrize("kw", [
+    dict(maxDist=0.5, trimmed_ratio=0.9, max_iterations=30, min_diff_trans=0.008),           # param/icp.yaml (eps 0)
+    dict(use_trimmed=0, use_maxdist_filter=1, maxdist_filter=0.3),
+    dict(use_trimmed=0),                                                                      # empty filter chain
+    dict(knn=3, trimmed_ratio=0.7),
+    dict(minimizer=1, trimmed_ratio=0.8),                                                     # point-to-point
+    dict(use_differential=0, max_iterations=7),
+    dict(trimmed_ratio=1.0, maxDist=0.2),
+])
+def test_icp_chain_variants(gold, kw):
+    ref4, refn = O.feat4(gold["c400"]["xyz"]), gold["c400"]["normals"]
+    read4 = O.feat4(gold["c401"]["xyz"])
+    o, g, icp = run_both(O.default_params(**kw), ref4, refn, read4)
+    assert_icp_parity(o, g, icp)
+
+
+def test_icp_surface_normal_filter(gold):
+    ref4, refn = O.feat4(gold["c400"]["xyz"]), gold["c400"]["normals"]
+    read4 = O.feat4(gold["c401"]["xyz"])
+    st, sn = O.surface_normals(read4, 10)
+    p = O.default_params(maxDist=0.5, trimmed_ratio=0.9, use_surface_normal_filter=1, surface_normal_max_angle=1.0)
+    o, g, icp = run_both(p, ref4, refn, read4, sn["normals"])
+    assert_icp_parity(o, g, icp)
+
+
+def test_icp_singular_and_identity(gold):
+    pid = O.default_params(trimmed_ratio=1.0, max_iterations=40, min_diff_rot=0.001, min_diff_trans=0.01, smooth_length=4)
+    nX, d = 10, np.float32(0.1)
+    pts = np.array([[d * x - (nX * d / 2), d * y - (nX * d / 2), 0] for x in range(nX) for y in range(nX)], np.float32)
+    pts0 = O.feat4(pts)
+    pts1 = pts0.copy()
+    pts1[:, 2] = 1
+    rf, rn = O.sampling_surface_normal(pts1, knn=10, ratio=1.0, sampling_method=0)
+    o, g, icp = run_both(pid, rf, rn, pts0)
+    assert_icp_parity(o, g, icp)
+    E = np.array(gold["icpSingular_expected"], np.float32)
+    assert np.linalg.norm(E - g["T"]) <= 1e-5 * np.linalg.norm(E)          # utest.cpp:195-198
+    c0 = O.feat4(gold["cloud0"])
+    rf, rn = O.sampling_surface_normal(c0, knn=10, ratio=1.0, sampling_method=0)
+    o, g, icp = run_both(pid, rf, rn, c0)
+    assert_icp_parity(o, g, icp)
+    assert np.linalg.norm(g["T"] - np.eye(4)) <= 1e-4 * 2                   # utest.cpp:219
+
+
+def test_icp_ref_trans_golden(gold):
+    rf, rn = O.sampling_surface_normal(O.feat4(gold["cloud0"]), knn=10, ratio=0.666666, sampling_method=1)
+    p = O.default_params(trimmed_ratio=0.75, max_iterations=40, min_diff_rot=0.001, min_diff_trans=0.01, smooth_length=4)
+    data = O.feat4(gold["cloud1"])
+    o, g, icp = run_both(p, rf, rn, data)
+    assert_icp_parity(o, g, icp)
+    refT = np.array(gold["defaultIdentityDataPointsFilter.ref_trans"])
+    D = data.T.astype(np.float64)
+    cur = g["T"].astype(np.float64) @ D
+    assert np.median(np.abs(cur - refT @ D)) / np.median(np.abs(cur)) < 0.05   # utest.cpp:147-159
+
+
+def test_icp_errors(gold):
+    ref4, refn = O.feat4(gold["c400"]["xyz"]), gold["c400"]["normals"]
+    read4 = O.feat4(gold["c401"]["xyz"])
+    icp = B.ICP(B.default_icp_params())
+    with pytest.raises(B.B200Error):     # no reference yet
+        icp.compute(read4)
+    with pytest.raises(B.B200Error):     # point-to-plane without normals (InvalidField, ICP.cpp:1519)
+        icp.init_reference(ref4, None)
+    icp.init_reference(ref4, refn)
+    far = read4.copy()
+    far[:, :3] += 1000
+    icp2 = B.ICP(B.default_icp_params(maxDist=0.1))
+    icp2.init_reference(ref4, refn)
+    with pytest.raises(B.ConvergenceError):   # no matches at all
+        icp2.compute(far)
+    with pytest.raises(B.B200Error):
+        B.ICP(B.default_icp_params(max_iterations=0, use_differential=0))
+
+
+def test_icp_with_initial_guess_and_reuse(gold):
+    """Mapper.cpp:343,373 pattern: one initReference, many compute() calls with a prior."""
+    ref4, refn = O.feat4(gold["c400"]["xyz"]), gold["c400"]["normals"]
+    read4 = O.feat4(gold["c401"]["xyz"])
+    p = O.default_params(maxDist=0.5, trimmed_ratio=0.9, max_iterations=30, min_diff_trans=0.008)
+    icp = B.ICP(to_b(p))
+    icp.init_reference(ref4, refn)
+    for seed in range(3):
+        rng = np.random.default_rng(seed)
+        Ti = O.p2plane_T(np.r_[rng.normal(0, 0.02, 3), rng.normal(0, 0.05, 3)].astype(np.float32))
+        o = O.icp(p, ref4, refn, read4, None, Ti)
+        g = icp.compute(read4, None, Ti, raise_on_error=False)
+        assert_icp_parity(o, g, icp)
+        icp.upload_reading(read4)
+        g2 = icp.run_resident(Ti)
+        assert (g2["T"] == g["T"]).all() and g2["iterations"] == g["iterations"]   # deterministic
