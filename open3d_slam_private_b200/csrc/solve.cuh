@@ -238,75 +238,89 @@ __device__ inline float angular_distance(const Quat& a, const Quat& b0) {
   return 2.f * atan2f(sqrtf(x * x + y * y + z * z), fabsf(w));
 }
 
-// one-sided Jacobi SVD of a 3x3 in double: A = sum_j S[j] * U(:,j) V(:,j)^T (unsorted)
-__device__ inline void svd3(const double* A, double* U, double* S, double* V) {
-  double W[9];
-  for (int i = 0; i < 9; ++i) { W[i] = A[i]; V[i] = 0.0; }
-  V[0] = V[4] = V[8] = 1.0;
+// one-sided Jacobi SVD of a 3x3 in FLOAT with singular values sorted descending (stable): plays
+// Eigen::JacobiSVD<Matrix3f> of PointToPoint.cpp:86 in the reference's own precision. A = U diag(S) V^T.
+__device__ inline void svd3f(const float* A, float* U, float* S, float* V) {
+  float W[9], Vw[9];
+  for (int i = 0; i < 9; ++i) { W[i] = A[i]; Vw[i] = 0.f; }
+  Vw[0] = Vw[4] = Vw[8] = 1.f;
   for (int sweep = 0; sweep < 60; ++sweep) {
     bool rot = false;
     for (int p = 0; p < 2; ++p)
       for (int q = p + 1; q < 3; ++q) {
-        double al = 0, be = 0, ga = 0;
+        float al = 0.f, be = 0.f, ga = 0.f;
         for (int i = 0; i < 3; ++i) {
           al += W[i + 3 * p] * W[i + 3 * p]; be += W[i + 3 * q] * W[i + 3 * q]; ga += W[i + 3 * p] * W[i + 3 * q];
         }
-        if (ga == 0.0 || fabs(ga) <= DBL_EPSILON * sqrt(al * be)) continue;
+        if (ga == 0.f || fabsf(ga) <= FLT_EPSILON * sqrtf(al * be)) continue;
         rot = true;
-        const double zeta = (be - al) / (2.0 * ga);
-        const double t = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
-        const double c = 1.0 / sqrt(1.0 + t * t), s = c * t;
+        const float zeta = (be - al) / (2.f * ga);
+        const float t = (zeta >= 0.f ? 1.f : -1.f) / (fabsf(zeta) + sqrtf(1.f + zeta * zeta));
+        const float c = 1.f / sqrtf(1.f + t * t), sn = c * t;
         for (int i = 0; i < 3; ++i) {
-          const double wp = W[i + 3 * p], wq = W[i + 3 * q];
-          W[i + 3 * p] = c * wp - s * wq; W[i + 3 * q] = s * wp + c * wq;
-          const double vp = V[i + 3 * p], vq = V[i + 3 * q];
-          V[i + 3 * p] = c * vp - s * vq; V[i + 3 * q] = s * vp + c * vq;
+          const float wp = W[i + 3 * p], wq = W[i + 3 * q];
+          W[i + 3 * p] = c * wp - sn * wq; W[i + 3 * q] = sn * wp + c * wq;
+          const float vp = Vw[i + 3 * p], vq = Vw[i + 3 * q];
+          Vw[i + 3 * p] = c * vp - sn * vq; Vw[i + 3 * q] = sn * vp + c * vq;
         }
       }
     if (!rot) break;
   }
+  float sv[3];
+  int order[3] = {0, 1, 2};
   for (int j = 0; j < 3; ++j) {
-    double n2 = 0;
+    float n2 = 0.f;
     for (int i = 0; i < 3; ++i) n2 += W[i + 3 * j] * W[i + 3 * j];
-    S[j] = sqrt(n2);
-    for (int i = 0; i < 3; ++i) U[i + 3 * j] = S[j] > 0.0 ? W[i + 3 * j] / S[j] : 0.0;
+    sv[j] = sqrtf(n2);
+  }
+  // stable insertion sort, descending
+  for (int a = 1; a < 3; ++a)
+    for (int b = a; b > 0 && sv[order[b]] > sv[order[b - 1]]; --b) { const int t = order[b]; order[b] = order[b - 1]; order[b - 1] = t; }
+  for (int jj = 0; jj < 3; ++jj) {
+    const int j = order[jj];
+    S[jj] = sv[j];
+    for (int i = 0; i < 3; ++i) {
+      U[i + 3 * jj] = sv[j] > 0.f ? W[i + 3 * j] / sv[j] : 0.f;
+      V[i + 3 * jj] = Vw[i + 3 * j];
+    }
   }
 }
 
-// PointToPointErrorMinimizer::compute_in_place (PointToPoint.cpp:62-103) from raw weighted moments:
-// m[0] = sum w, m[1..3] = sum w*r, m[4..6] = sum w*f, m[7..15] = sum w * f_i * r_j (column-major i + 3j)
+// PointToPointErrorMinimizer::compute_in_place (PointToPoint.cpp:62-103) from raw weighted moments summed in double:
+// m[0] = sum w, m[1..3] = sum w*r, m[4..6] = sum w*f, m[7..15] = sum w * f_i * r_j (column-major i + 3j).
+// Centroids and the centred cross-covariance are rounded to float, and SVD / R = U V^T / reflection fix / t are done
+// in float exactly like the reference (Matrix3f JacobiSVD).
 __device__ inline void p2point_from_moments(const double* m, float* T) {
   const double winv = 1.0 / m[0];
-  double mr[3], mf[3], C[9];
-  for (int d = 0; d < 3; ++d) { mr[d] = m[1 + d] * winv; mf[d] = m[4 + d] * winv; }
+  double mrd[3], mfd[3];
+  float mr[3], mf[3], C[9];
+  for (int d = 0; d < 3; ++d) { mrd[d] = m[1 + d] * winv; mfd[d] = m[4 + d] * winv; mr[d] = (float)mrd[d]; mf[d] = (float)mfd[d]; }
   for (int j = 0; j < 3; ++j)
-    for (int i = 0; i < 3; ++i) C[i + 3 * j] = m[7 + i + 3 * j] - m[0] * mf[i] * mr[j];
-  double U[9], S[3], V[9], R[9];
-  svd3(C, U, S, V);
-  auto compose = [&](const double* sg) {
+    for (int i = 0; i < 3; ++i) C[i + 3 * j] = (float)(m[7 + i + 3 * j] - m[0] * mfd[i] * mrd[j]);
+  float U[9], S[3], V[9], Vt[9], R[9];
+  svd3f(C, U, S, V);
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) Vt[i + 3 * j] = V[j + 3 * i];
+  auto compose = [&]() {
     for (int j = 0; j < 3; ++j)
       for (int i = 0; i < 3; ++i) {
-        double a = 0;
-        for (int k = 0; k < 3; ++k) a += sg[k] * U[i + 3 * k] * V[j + 3 * k];
+        float a = 0.f;
+        for (int k = 0; k < 3; ++k) a += U[i + 3 * k] * Vt[k + 3 * j];
         R[i + 3 * j] = a;
       }
   };
-  double sg[3] = {1.0, 1.0, 1.0};
-  compose(sg);
-  if (la::det3(R) < 0.0) {
-    int mn = 0;
-    if (S[1] < S[mn]) mn = 1;
-    if (S[2] < S[mn]) mn = 2;
-    sg[mn] = -1.0;
-    compose(sg);
+  compose();
+  if (la::det3(R) < 0.f) {  // PointToPoint.cpp:92-97: negate the last row of V^T
+    for (int j = 0; j < 3; ++j) Vt[2 + 3 * j] = -Vt[2 + 3 * j];
+    compose();
   }
   eye4(T);
   for (int j = 0; j < 3; ++j)
-    for (int i = 0; i < 3; ++i) T[i + 4 * j] = (float)R[i + 3 * j];
+    for (int i = 0; i < 3; ++i) T[i + 4 * j] = R[i + 3 * j];
   for (int i = 0; i < 3; ++i) {
-    double a = 0;
+    float a = 0.f;
     for (int j = 0; j < 3; ++j) a += R[i + 3 * j] * mr[j];
-    T[12 + i] = (float)(mf[i] - a);
+    T[12 + i] = mf[i] - a;
   }
 }
 

@@ -157,6 +157,18 @@ extern "C" int orc_icp(const orc_icp_params* prm, const float* ref4xM, const flo
                        const float* read4xN, const float* readn3xN, int N, const float* Tinit, orc_icp_result* res,
                        int max_log, float* logH, float* logb, float* logx, float* logT, int* logP,
                        int32_t* last_ids, float* last_dists, float* last_w) {
+  return orc_icp_forced(prm, ref4xM, refn3xM, M, read4xN, readn3xN, N, Tinit, res, max_log, logH, logb, logx, logT,
+                        logP, last_ids, last_dists, last_w, nullptr, 0);
+}
+
+// One-step ("teacher-forced") variant used by the parity tests: with forcedT (n_forced column-major 4x4), iteration
+// i logs the oracle's own T_iter computed from the current state and then CONTINUES from forcedT[i] (the pose another
+// implementation reached after its iteration i). Runs exactly n_forced iterations; the checkers see the forced poses.
+extern "C" int orc_icp_forced(const orc_icp_params* prm, const float* ref4xM, const float* refn3xM, int M,
+                              const float* read4xN, const float* readn3xN, int N, const float* Tinit,
+                              orc_icp_result* res, int max_log, float* logH, float* logb, float* logx, float* logT,
+                              int* logP, int32_t* last_ids, float* last_dists, float* last_w, const float* forcedT,
+                              int n_forced) {
   if (M <= 0 || N <= 0) return ORC_E_BAD_PARAM;
   const int k = prm->knn;
   // ---- initReference, ICP.cpp:847-898
@@ -234,7 +246,7 @@ extern "C" int orc_icp(const orc_icp_params* prm, const float* ref4xM, const flo
       orc_solve6(H, b, x, &info);                          // :1205 -> PointToPlane.cpp:299
       orc_p2plane_T(x, real);
     } else {
-      orc_p2point_T(readP.data(), refP.data(), wP.data(), P, real);
+      orc_p2point_T2(readP.data(), refP.data(), wP.data(), P, prm->accum, real);
     }
     mul4(real, T_iter, T_iter);                            // :1213
     if (iterationCount < max_log) {
@@ -244,9 +256,11 @@ extern "C" int orc_icp(const orc_icp_params* prm, const float* ref4xM, const flo
       if (logT) std::memcpy(logT + 16 * (size_t)iterationCount, T_iter, sizeof(T_iter));
       if (logP) logP[iterationCount] = P;
     }
+    if (forcedT) std::memcpy(T_iter, forcedT + 16 * (size_t)iterationCount, sizeof(T_iter));
     status = chk.check(T_iter, iterate, maxReached);       // :1292-1298
     ++iterationCount;
     if (status) break;
+    if (forcedT) iterate = iterationCount < n_forced;
   }
   orc_kdtree_free(tree);
   // ---- result, ICP.cpp:1345

@@ -316,22 +316,46 @@ int orc_p2plane_T(const float* x, float* T) {
 
 // PointToPointErrorMinimizer::compute_in_place — PointToPoint.cpp:62-103
 int orc_p2point_T(const float* read, const float* ref, const float* w, int P, float* T) {
-  float wsum = 0.f;
-  for (int p = 0; p < P; ++p) wsum += w[p];
-  const float winv = 1.f / wsum;
+  return orc_p2point_T2(read, ref, w, P, 0, T);
+}
+
+// accum 0: reference-literal float sums in index order (the order is an Eigen artefact); accum 1: the same float
+// inputs summed in double ("truth"), rounded to float before the SVD — what the device path is compared with.
+int orc_p2point_T2(const float* read, const float* ref, const float* w, int P, int accum, float* T) {
   float mr[3] = {0, 0, 0}, mf[3] = {0, 0, 0};
-  for (int p = 0; p < P; ++p)
-    for (int d = 0; d < 3; ++d) {
-      mr[d] += read[4 * (size_t)p + d] * w[p];
-      mf[d] += ref[4 * (size_t)p + d] * w[p];
-    }
-  for (int d = 0; d < 3; ++d) { mr[d] *= winv; mf[d] *= winv; }
   float m[9] = {0};  // m = ref_c * diag(w) * read_c^T, column-major m(i,j)
-  for (int p = 0; p < P; ++p) {
-    float rc[3], fc[3];
-    for (int d = 0; d < 3; ++d) { rc[d] = read[4 * (size_t)p + d] - mr[d]; fc[d] = ref[4 * (size_t)p + d] - mf[d]; }
-    for (int j = 0; j < 3; ++j)
-      for (int i = 0; i < 3; ++i) m[i + 3 * j] += (fc[i] * w[p]) * rc[j];
+  if (!accum) {
+    float wsum = 0.f;
+    for (int p = 0; p < P; ++p) wsum += w[p];
+    const float winv = 1.f / wsum;
+    for (int p = 0; p < P; ++p)
+      for (int d = 0; d < 3; ++d) {
+        mr[d] += read[4 * (size_t)p + d] * w[p];
+        mf[d] += ref[4 * (size_t)p + d] * w[p];
+      }
+    for (int d = 0; d < 3; ++d) { mr[d] *= winv; mf[d] *= winv; }
+    for (int p = 0; p < P; ++p) {
+      float rc[3], fc[3];
+      for (int d = 0; d < 3; ++d) { rc[d] = read[4 * (size_t)p + d] - mr[d]; fc[d] = ref[4 * (size_t)p + d] - mf[d]; }
+      for (int j = 0; j < 3; ++j)
+        for (int i = 0; i < 3; ++i) m[i + 3 * j] += (fc[i] * w[p]) * rc[j];
+    }
+  } else {
+    double wsum = 0.0, dr[3] = {0, 0, 0}, df[3] = {0, 0, 0}, dm[9] = {0};
+    for (int p = 0; p < P; ++p) {
+      const double wd = (double)w[p];
+      wsum += wd;
+      for (int d = 0; d < 3; ++d) { dr[d] += wd * (double)read[4 * (size_t)p + d]; df[d] += wd * (double)ref[4 * (size_t)p + d]; }
+    }
+    for (int d = 0; d < 3; ++d) { dr[d] /= wsum; df[d] /= wsum; }
+    for (int p = 0; p < P; ++p) {
+      const double wd = (double)w[p];
+      for (int j = 0; j < 3; ++j)
+        for (int i = 0; i < 3; ++i)
+          dm[i + 3 * j] += ((double)ref[4 * (size_t)p + i] - df[i]) * wd * ((double)read[4 * (size_t)p + j] - dr[j]);
+    }
+    for (int d = 0; d < 3; ++d) { mr[d] = (float)dr[d]; mf[d] = (float)df[d]; }
+    for (int i = 0; i < 9; ++i) m[i] = (float)dm[i];
   }
   float U[9], S[3], V[9];
   orc::jacobiSVD<float, 3>(m, U, S, V);

@@ -68,6 +68,8 @@ int orc_p2plane_T(const float* x6, float* T16);
 
 /* ---- PointToPointErrorMinimizer::compute_in_place (PointToPoint.cpp:62-103) ---- */
 int orc_p2point_T(const float* read4xP, const float* ref4xP, const float* w_P, int P, float* T16);
+/* accum as in orc_p2plane_hb: 0 = float sums in index order, 1 = float inputs summed in double */
+int orc_p2point_T2(const float* read4xP, const float* ref4xP, const float* w_P, int P, int accum, float* T16);
 
 /* ---- RigidTransformation::inPlaceCompute (TransformationsImpl.cpp:61-102) incl. check/correct ---- */
 int orc_rigid_apply(const float* T16, float* feat4xN, float* normals3xN /*nullable*/, int N);
@@ -122,6 +124,12 @@ int orc_icp(const orc_icp_params* prm, const float* ref4xM, const float* refn3xM
             const float* readn3xN /*nullable*/, int N, const float* Tinit16, orc_icp_result* res, int max_log,
             float* logH, float* logb, float* logx, float* logT, int* logP, int32_t* last_ids, float* last_dists,
             float* last_w);
+/* teacher-forced variant (see icp.cpp): after logging its own result of iteration i the oracle continues from
+ * forcedT[i]; runs exactly n_forced iterations */
+int orc_icp_forced(const orc_icp_params* prm, const float* ref4xM, const float* refn3xM, int M, const float* read4xN,
+                   const float* readn3xN, int N, const float* Tinit16, orc_icp_result* res, int max_log, float* logH,
+                   float* logb, float* logx, float* logT, int* logP, int32_t* last_ids, float* last_dists,
+                   float* last_w, const float* forcedT, int n_forced);
 
 #ifdef __cplusplus
 }

@@ -199,10 +199,10 @@ def p2plane_T(x):
     return T.reshape(4, 4).T.copy()
 
 
-def p2point_T(readP, refP, wP):
+def p2point_T(readP, refP, wP, accum=0):
     readP, refP, wP = f32(readP), f32(refP), f32(wP)
     T = np.empty(16, np.float32)
-    lib().orc_p2point_T(_fp(readP), _fp(refP), _fp(wP), readP.shape[0], _fp(T))
+    lib().orc_p2point_T2(_fp(readP), _fp(refP), _fp(wP), readP.shape[0], accum, _fp(T))
     return T.reshape(4, 4).T.copy()
 
 
@@ -249,7 +249,9 @@ def default_params(**kw):
     return p
 
 
-def icp(params, ref4, refn, read4, readn=None, T_init=None, max_log=64):
+def icp(params, ref4, refn, read4, readn=None, T_init=None, max_log=64, forced_T_iters=None):
+    """forced_T_iters (n,4,4): one-step mode, see orc_icp_forced — T_iters[i] of the result is the oracle's own
+    update computed from forced_T_iters[i-1]; ids/dists/weights are those of the last iteration."""
     ref4, refn, read4, readn = f32(ref4), f32(refn), f32(read4), f32(readn)
     M, N, k = ref4.shape[0], read4.shape[0], params.knn
     Ti = np.eye(4, dtype=np.float32) if T_init is None else np.asarray(T_init, np.float32)
@@ -263,8 +265,14 @@ def icp(params, ref4, refn, read4, readn=None, T_init=None, max_log=64):
     ids = np.empty((N, k), np.int32)
     dists = np.empty((N, k), np.float32)
     w = np.empty((N, k), np.float32)
-    st = lib().orc_icp(C.byref(params), _fp(ref4), _fp(refn), M, _fp(read4), _fp(readn), N, _fp(Tc), C.byref(res),
-                       max_log, _fp(logH), _fp(logb), _fp(logx), _fp(logT), _ip(logP), _ip(ids), _fp(dists), _fp(w))
+    if forced_T_iters is None:
+        fT, nf = None, 0
+    else:
+        fT = np.ascontiguousarray(np.asarray(forced_T_iters, np.float32).transpose(0, 2, 1)).reshape(-1)
+        nf = len(forced_T_iters)
+    st = lib().orc_icp_forced(C.byref(params), _fp(ref4), _fp(refn), M, _fp(read4), _fp(readn), N, _fp(Tc),
+                              C.byref(res), max_log, _fp(logH), _fp(logb), _fp(logx), _fp(logT), _ip(logP), _ip(ids),
+                              _fp(dists), _fp(w), _fp(fT), nf)
     it = min(res.iterations, max_log)
     m = lambda a: np.array(a, np.float32).reshape(4, 4).T.copy()
     return dict(status=st, iterations=res.iterations, max_iterations_reached=bool(res.max_iterations_reached),
