@@ -161,7 +161,10 @@ typedef struct {
   float point_used_ratio;
   uint64_t points_touched;       /* "PointCountTouched" */
   float device_ms;               /* CUDA-event time of the registration kernel */
-  float h2d_ms, total_ms;        /* upload time and whole call (events) */
+  float h2d_ms, total_ms;        /* upload time; first event .. end of the registration kernel */
+  float e2e_ms;                  /* first event .. after the device->host copy of this result (0 for run_resident) */
+  int kernel_launches;           /* kernels this call launched on the device (uploads/memsets not counted) */
+  int grid_ctas;                 /* CTAs of the persistent registration kernel */
 } b200_icp_result;
 
 void b200_icp_default_params(b200_icp_params* prm); /* ICPChainBase::setDefault, ICP.cpp:100-113 */

@@ -58,7 +58,8 @@ class IcpResult(C.Structure):
         ("T", C.c_float * 16), ("T_iter", C.c_float * 16), ("T_refIn_refMean", C.c_float * 16),
         ("T_refMean_readMean", C.c_float * 16), ("weighted_point_used_ratio", C.c_float),
         ("point_used_ratio", C.c_float), ("points_touched", C.c_uint64), ("device_ms", C.c_float),
-        ("h2d_ms", C.c_float), ("total_ms", C.c_float),
+        ("h2d_ms", C.c_float), ("total_ms", C.c_float), ("e2e_ms", C.c_float), ("kernel_launches", C.c_int),
+        ("grid_ctas", C.c_int),
     ]
 
 
@@ -304,7 +305,8 @@ class ICP:
                    T_refIn_refMean=_mat(res.T_refIn_refMean), T_refMean_readMean=_mat(res.T_refMean_readMean),
                    weighted_point_used_ratio=res.weighted_point_used_ratio, point_used_ratio=res.point_used_ratio,
                    points_touched=res.points_touched, device_ms=res.device_ms, h2d_ms=res.h2d_ms,
-                   total_ms=res.total_ms)
+                   total_ms=res.total_ms, e2e_ms=res.e2e_ms, kernel_launches=res.kernel_launches,
+                   grid_ctas=res.grid_ctas)
         if raise_on_error:
             _check(st)
         return out

@@ -117,7 +117,8 @@ struct b200_icp {
   IcpDeviceResult* h_out = nullptr;
   float* h_frames = nullptr;  // 64 floats
   float* h_Tinit = nullptr;
-  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  int upload_launches = 0;
   float4* d_flush = nullptr;
   size_t flush_elems = 0;
   int last_grid = 0;
@@ -136,7 +137,7 @@ int icp_alloc_fixed(b200_icp* h) {
   B200_CUDA(cudaMallocHost(&h->h_out, sizeof(IcpDeviceResult)));
   B200_CUDA(cudaMallocHost(&h->h_frames, 64 * sizeof(float)));
   B200_CUDA(cudaMallocHost(&h->h_Tinit, 16 * sizeof(float)));
-  for (int i = 0; i < 4; ++i) B200_CUDA(cudaEventCreate(&h->ev[i]));
+  for (int i = 0; i < 5; ++i) B200_CUDA(cudaEventCreate(&h->ev[i]));
   B200_CUDA(cudaMemset(h->d_log, 0, (size_t)kMaxLog * sizeof(IcpLogEntry)));
   return B200_OK;
 }
@@ -227,6 +228,7 @@ int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool tim
   B200_CUDA(cudaEventRecord(h->ev[3], s));
   B200_CUDA(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(IcpDeviceResult), cudaMemcpyDeviceToHost, s));
   B200_CUDA(cudaMemcpyAsync(h->h_frames, h->d_frames, 64 * sizeof(float), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaEventRecord(h->ev[4], s));
   B200_CUDA(cudaStreamSynchronize(s));
   if (res) {
     std::memset(res, 0, sizeof(*res));
@@ -240,13 +242,17 @@ int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool tim
     res->weighted_point_used_ratio = o.weighted_point_used_ratio;
     res->point_used_ratio = o.point_used_ratio;
     res->points_touched = o.points_touched;
+    res->grid_ctas = h->last_grid;
     B200_CUDA(cudaEventElapsedTime(&res->device_ms, h->ev[2], h->ev[3]));
     float pre = 0.f;
     B200_CUDA(cudaEventElapsedTime(&pre, h->ev[1], h->ev[3]));
     if (timed_upload) {
       B200_CUDA(cudaEventElapsedTime(&res->h2d_ms, h->ev[0], h->ev[1]));
       B200_CUDA(cudaEventElapsedTime(&res->total_ms, h->ev[0], h->ev[3]));
+      B200_CUDA(cudaEventElapsedTime(&res->e2e_ms, h->ev[0], h->ev[4]));
+      res->kernel_launches = 4 + h->upload_launches;  // centroid sums, frames, reading preparation, registration
     } else {
+      res->kernel_launches = 4;
       res->h2d_ms = 0.f;
       res->total_ms = pre;
     }
@@ -262,6 +268,7 @@ int icp_upload(b200_icp* h, const float* read4xN, const float* readn3xN, int N) 
   B200_CUDA(cudaEventRecord(h->ev[0], h->stream));
   B200_TRY(upload_features(h->d_raw, read4xN, N, h->stream));
   if (readn3xN) B200_TRY(upload_normals(h->d_raw_n, readn3xN, N, h->d_stage3, h->stream));
+  h->upload_launches = readn3xN ? 1 : 0;  // normals repack kernel
   h->N = N;
   h->has_read_n = readn3xN != nullptr;
   return B200_OK;
@@ -321,7 +328,7 @@ void b200_icp_destroy(b200_icp* h) {
     cudaFree(h->d_hist); cudaFree(h->d_partials); cudaFree(h->d_meanpart); cudaFree(h->d_out); cudaFree(h->d_log);
     cudaFree(h->d_frames); cudaFree(h->d_Tinit); cudaFree(h->d_flush);
     cudaFreeHost(h->h_out); cudaFreeHost(h->h_frames); cudaFreeHost(h->h_Tinit);
-    for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < 5; ++i)
       if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     h->map.release();
     if (h->stream) cudaStreamDestroy(h->stream);

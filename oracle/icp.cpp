@@ -164,23 +164,65 @@ extern "C" int orc_icp(const orc_icp_params* prm, const float* ref4xM, const flo
 // One-step ("teacher-forced") variant used by the parity tests: with forcedT (n_forced column-major 4x4), iteration
 // i logs the oracle's own T_iter computed from the current state and then CONTINUES from forcedT[i] (the pose another
 // implementation reached after its iteration i). Runs exactly n_forced iterations; the checkers see the forced poses.
+// ---- initReference, ICP.cpp:847-898: mean-centre the reference and build the matcher's tree. Kept as a handle so
+// that one reference serves many compute() calls (Mapper.cpp:343 vs :373) and the baseline can time them apart.
+struct OrcRef {
+  std::vector<float> ref;
+  std::vector<float> refn;
+  bool has_n = false;
+  int M = 0;
+  float T_refIn_refMean[16];
+  void* tree = nullptr;
+};
+
+extern "C" void* orc_icp_ref_create(const float* ref4xM, const float* refn3xM, int M, int mean_mode) {
+  if (M <= 0) return nullptr;
+  OrcRef* r = new OrcRef();
+  r->M = M;
+  r->ref.assign(ref4xM, ref4xM + 4 * (size_t)M);
+  if (refn3xM) { r->refn.assign(refn3xM, refn3xM + 3 * (size_t)M); r->has_n = true; }
+  float meanRef[3];
+  meanOf(r->ref.data(), M, mean_mode, meanRef);
+  eye4(r->T_refIn_refMean);
+  for (int d = 0; d < 3; ++d) r->T_refIn_refMean[12 + d] = meanRef[d];
+  for (int i = 0; i < M; ++i)
+    for (int d = 0; d < 3; ++d) r->ref[4 * (size_t)i + d] -= meanRef[d];
+  r->tree = orc_kdtree_build(r->ref.data(), M);
+  return r;
+}
+
+extern "C" void orc_icp_ref_free(void* h) {
+  OrcRef* r = (OrcRef*)h;
+  if (!r) return;
+  orc_kdtree_free(r->tree);
+  delete r;
+}
+
 extern "C" int orc_icp_forced(const orc_icp_params* prm, const float* ref4xM, const float* refn3xM, int M,
                               const float* read4xN, const float* readn3xN, int N, const float* Tinit,
                               orc_icp_result* res, int max_log, float* logH, float* logb, float* logx, float* logT,
                               int* logP, int32_t* last_ids, float* last_dists, float* last_w, const float* forcedT,
                               int n_forced) {
   if (M <= 0 || N <= 0) return ORC_E_BAD_PARAM;
+  void* h = orc_icp_ref_create(ref4xM, refn3xM, M, prm->mean_mode);
+  const int st = orc_icp_compute(h, prm, read4xN, readn3xN, N, Tinit, res, max_log, logH, logb, logx, logT, logP,
+                                 last_ids, last_dists, last_w, forcedT, n_forced);
+  orc_icp_ref_free(h);
+  return st;
+}
+
+// ICP::compute on a prepared reference (ICP.cpp:813-844 with initializeMatcherWithInputReference = false)
+extern "C" int orc_icp_compute(void* href, const orc_icp_params* prm, const float* read4xN, const float* readn3xN,
+                               int N, const float* Tinit, orc_icp_result* res, int max_log, float* logH, float* logb,
+                               float* logx, float* logT, int* logP, int32_t* last_ids, float* last_dists,
+                               float* last_w, const float* forcedT, int n_forced) {
+  OrcRef* R = (OrcRef*)href;
+  if (!R || N <= 0) return ORC_E_BAD_PARAM;
   const int k = prm->knn;
-  // ---- initReference, ICP.cpp:847-898
-  std::vector<float> ref(ref4xM, ref4xM + 4 * (size_t)M);
-  float meanRef[3];
-  meanOf(ref.data(), M, prm->mean_mode, meanRef);
-  float T_refIn_refMean[16];
-  eye4(T_refIn_refMean);
-  for (int d = 0; d < 3; ++d) T_refIn_refMean[12 + d] = meanRef[d];
-  for (int i = 0; i < M; ++i)
-    for (int d = 0; d < 3; ++d) ref[4 * (size_t)i + d] -= meanRef[d];
-  void* tree = orc_kdtree_build(ref.data(), M);
+  const std::vector<float>& ref = R->ref;
+  const float* refn3xM = R->has_n ? R->refn.data() : nullptr;
+  const float* T_refIn_refMean = R->T_refIn_refMean;
+  void* tree = R->tree;
 
   // ---- computeWithTransformedReference, ICP.cpp:902-1000
   std::vector<float> reading(read4xN, read4xN + 4 * (size_t)N);
@@ -262,7 +304,6 @@ extern "C" int orc_icp_forced(const orc_icp_params* prm, const float* ref4xM, co
     if (status) break;
     if (forcedT) iterate = iterationCount < n_forced;
   }
-  orc_kdtree_free(tree);
   // ---- result, ICP.cpp:1345
   float invRead[16], r1[16], r2[16];
   inv4(T_readIn_readMean, invRead);
@@ -275,7 +316,7 @@ extern "C" int orc_icp_forced(const orc_icp_params* prm, const float* ref4xM, co
   res->weighted_point_used_ratio = wpur;
   res->points_touched = touched;
   std::memcpy(res->T_iter, T_iter, sizeof(T_iter));
-  std::memcpy(res->T_refIn_refMean, T_refIn_refMean, sizeof(T_refIn_refMean));
+  std::memcpy(res->T_refIn_refMean, T_refIn_refMean, 16 * sizeof(float));
   std::memcpy(res->T_refMean_readMean, T_refMean_readMean, sizeof(T_refMean_readMean));
   if (last_ids) std::memcpy(last_ids, ids.data(), ids.size() * sizeof(int32_t));
   if (last_dists) std::memcpy(last_dists, dists.data(), dists.size() * sizeof(float));

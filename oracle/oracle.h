@@ -131,6 +131,14 @@ int orc_icp_forced(const orc_icp_params* prm, const float* ref4xM, const float* 
                    float* logb, float* logx, float* logT, int* logP, int32_t* last_ids, float* last_dists,
                    float* last_w, const float* forcedT, int n_forced);
 
+/* the same split as the reference's initReference / compute (one reference, many readings) */
+void* orc_icp_ref_create(const float* ref4xM, const float* refn3xM, int M, int mean_mode);
+void orc_icp_ref_free(void* h);
+int orc_icp_compute(void* href, const orc_icp_params* prm, const float* read4xN, const float* readn3xN, int N,
+                    const float* Tinit16, orc_icp_result* res, int max_log, float* logH, float* logb, float* logx,
+                    float* logT, int* logP, int32_t* last_ids, float* last_dists, float* last_w, const float* forcedT,
+                    int n_forced);
+
 #ifdef __cplusplus
 }
 #endif

@@ -282,3 +282,32 @@ def icp(params, ref4, refn, read4, readn=None, T_init=None, max_log=64, forced_T
                 H=logH[:it].reshape(it, 6, 6).transpose(0, 2, 1).copy(), b=logb[:it], x=logx[:it],
                 T_iters=logT[:it].reshape(it, 4, 4).transpose(0, 2, 1).copy(), P=logP[:it], ids=ids, dists=dists,
                 weights=w)
+
+
+class IcpSession:
+    """initReference once, compute many (Mapper.cpp:343,373 pattern); lets the CPU baseline time compute() apart
+    from the kd-tree build."""
+
+    def __init__(self, ref4, refn, mean_mode=1):
+        self.ref4, self.refn = f32(ref4), f32(refn)
+        lib().orc_icp_ref_create.restype = C.c_void_p
+        self.h = C.c_void_p(lib().orc_icp_ref_create(_fp(self.ref4), _fp(self.refn), self.ref4.shape[0], mean_mode))
+
+    def compute(self, params, read4, readn=None, T_init=None):
+        read4, readn = f32(read4), f32(readn)
+        Ti = np.eye(4, dtype=np.float32) if T_init is None else np.asarray(T_init, np.float32)
+        Tc = np.ascontiguousarray(Ti.T).ravel()
+        res = IcpResult()
+        st = lib().orc_icp_compute(self.h, C.byref(params), _fp(read4), _fp(readn), read4.shape[0], _fp(Tc),
+                                   C.byref(res), 0, None, None, None, None, None, None, None, None, None, 0)
+        m = lambda a: np.array(a, np.float32).reshape(4, 4).T.copy()
+        return dict(status=st, iterations=res.iterations, max_iterations_reached=bool(res.max_iterations_reached),
+                    n_matches_last=res.n_matches_last, T=m(res.T), points_touched=res.points_touched)
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().orc_icp_ref_free(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
