@@ -185,6 +185,14 @@ int b200_icp_run_resident(b200_icp* icp, const float* Tinit16, b200_icp_result* 
 int b200_icp_get_matches(b200_icp* icp, int32_t* ids_kxN, float* dists_kxN, float* weights_kxN);
 /* per-iteration trace (first max_log iterations): H 36, b 6, x 6, T_iter 16 floats, P int. Returns count in *n. */
 int b200_icp_get_log(b200_icp* icp, int max_log, float* H, float* b, float* x, float* T_iter, int32_t* P, int* n);
+/* profiling aid: per-iteration phase durations in microseconds as seen by CTA 0 of the registration kernel
+ * (%globaltimer): us[6*i + {0 match, 1 trimmed select, 2 linearise, 3 wait for all partials, 4 reduce+solve+checks,
+ * 5 whole iteration}] */
+int b200_icp_get_phase_times(b200_icp* icp, int max_log, float* us, int* n);
+/* profiling aid, filled only when the handle was created with env B200_ICP_DEBUG=1 (adds global atomics to the
+ * kernel): st[4*i + {0 cell rows resolved, 1 candidates examined, 2 slowest CTA's matching phase (us), 3 mean CTA
+ * matching phase (us)}] */
+int b200_icp_get_debug_stats(b200_icp* icp, int max_log, double* st, int* n);
 /* evict L2 (writes a buffer larger than L2) on the handle's stream; for benchmarking hygiene */
 int b200_icp_flush_l2(b200_icp* icp);
 

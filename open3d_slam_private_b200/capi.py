@@ -350,6 +350,20 @@ class ICP:
         return dict(H=H[:it].reshape(it, 6, 6).transpose(0, 2, 1).copy(), b=b[:it], x=x[:it],
                     T_iters=T[:it].reshape(it, 4, 4).transpose(0, 2, 1).copy(), P=P[:it])
 
+    def phase_times(self, max_log=64):
+        """(iterations, 6) microseconds: match, trimmed select, linearise, wait, reduce+solve, whole iteration"""
+        us = np.zeros((max_log, 6), np.float32)
+        n = C.c_int()
+        _check(load().b200_icp_get_phase_times(self.h, max_log, _fp(us), C.byref(n)))
+        return us[:n.value]
+
+    def debug_stats(self, max_log=64):
+        """(iterations, 4): rows, candidates, slowest CTA match us, mean CTA match us (needs B200_ICP_DEBUG=1)"""
+        st = np.zeros((max_log, 4), np.float64)
+        n = C.c_int()
+        _check(load().b200_icp_get_debug_stats(self.h, max_log, st.ctypes.data_as(C.POINTER(C.c_double)), C.byref(n)))
+        return st[:n.value]
+
     def flush_l2(self):
         _check(load().b200_icp_flush_l2(self.h))
 

@@ -111,6 +111,12 @@ __device__ __forceinline__ void zero_hist(unsigned* s_hist) {
   __syncthreads();
 }
 
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -141,29 +147,61 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
   __syncthreads();
   unsigned long long visited_total = 0ull;
 
+  const bool stamp = (blockIdx.x == 0 && tid == 0 && p.log != nullptr);
+  unsigned long long ts[6] = {0ull, 0ull, 0ull, 0ull, 0ull, 0ull};
   while (true) {
+    if (stamp) ts[0] = gtimer();
     if (tid == 0) rigid_prepare(S.T_iter, S.Tc, S.R9);
     zero_hist(s_hist);  // includes __syncthreads
     const int par = S.iteration & 1;
     unsigned* gh = p.hist + (size_t)par * 3 * kHistBins;
 
     // ---------------- phase 1: transform + match ----------------
-    for (int i = gtid; i < p.N; i += nthreads) {
-      const float4 q = apply_T(S.Tc, __ldg(&p.reading[i]));
-      KList<K> L;
+    unsigned dbg_rows = 0, dbg_cands = 0;
+    const unsigned long long dbg_t0 = p.debug_stats ? gtimer() : 0ull;
+    for (int base = gtid - lane; base < p.N; base += nthreads) {  // warp-uniform: the k = 1 search is a warp collective
+      const int i = base + lane;
+      const bool in = i < p.N;
+      const float4 q = in ? apply_T(S.Tc, __ldg(&p.reading[i])) : make_float4(0.f, 0.f, 0.f, 1.f);
       unsigned vis = 0;
-      knn_query<K>(p.g, q.x, q.y, q.z, p.md2, k, L, vis);
-      visited_total += vis;
-#pragma unroll
-      for (int j = 0; j < K; ++j)
-        if (j < k) {
-          const size_t e = (size_t)i * k + j;
-          p.ids[e] = L.id[j]; p.dists[e] = L.d[j]; p.spos[e] = L.sp[j];
-          if (p.use_trimmed && L.d[j] != INFINITY) atomicAdd(&s_hist[(__float_as_uint(L.d[j]) >> 20) & 0x7ffu], 1u);
+      if (K == 1) {
+        float bd; int bid, bsp;
+        knn_query_warp1(p.g, in, q.x, q.y, q.z, p.md2, bd, bid, bsp, vis, p.debug_stats ? &dbg_rows : nullptr);
+        if (in) {
+          p.ids[i] = bid; p.dists[i] = bd; p.spos[i] = bsp;
+          if (p.use_trimmed && bd != INFINITY) atomicAdd(&s_hist[(__float_as_uint(bd) >> 20) & 0x7ffu], 1u);
         }
+      } else if (in) {
+        KList<K> L;
+        knn_query<K>(p.g, q.x, q.y, q.z, p.md2, k, L, vis);
+#pragma unroll
+        for (int j = 0; j < K; ++j)
+          if (j < k) {
+            const size_t e = (size_t)i * k + j;
+            p.ids[e] = L.id[j]; p.dists[e] = L.d[j]; p.spos[e] = L.sp[j];
+            if (p.use_trimmed && L.d[j] != INFINITY) atomicAdd(&s_hist[(__float_as_uint(L.d[j]) >> 20) & 0x7ffu], 1u);
+          }
+      }
+      visited_total += vis;
+      dbg_cands += vis;
+    }
+    if (p.debug_stats && p.log && S.iteration < kMaxLog) {
+      IcpLogEntry& e = p.log[S.iteration];
+      for (int o = 16; o > 0; o >>= 1) {
+        dbg_rows += __shfl_xor_sync(0xffffffffu, dbg_rows, o);
+        dbg_cands += __shfl_xor_sync(0xffffffffu, dbg_cands, o);
+      }
+      if (lane == 0) { atomicAdd(&e.dbg_rows, (unsigned long long)dbg_rows); atomicAdd(&e.dbg_cands, (unsigned long long)dbg_cands); }
+      __syncthreads();
+      if (tid == 0) {
+        const unsigned long long dt = gtimer() - dbg_t0;
+        atomicMax(&e.dbg_match_ns_max, dt);
+        atomicAdd(&e.dbg_match_ns_sum, dt);
+      }
     }
 
     // ---------------- phase 2: TrimmedDist quantile by 3-pass radix select ----------------
+    if (stamp) ts[1] = gtimer();
     float limit = INFINITY;
     if (p.use_trimmed) {
       flush_hist(s_hist, gh);
@@ -201,6 +239,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
       select_bin(gh + 2 * kHistBins, rank1, false, 0.f, s_scan, S);
       limit = __uint_as_float((pre << 9) | S.sel_bin);
     }
+    if (stamp) ts[2] = gtimer();
     // zero the other parity's histograms for the next iteration (their last readers finished an iteration ago)
     {
       unsigned* gz = p.hist + (size_t)(par ^ 1) * 3 * kHistBins;
@@ -321,13 +360,23 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
       for (int w2 = 0; w2 < kWarps; ++w2) s += s_red[w2][tid];
       __stcg(&p.partials[(size_t)blockIdx.x * kAccum + tid], s);
     }
+    if (stamp) ts[3] = gtimer();
     grid.sync();
+    if (stamp) ts[4] = gtimer();
 
     // ---------------- phase 4: every CTA reduces all partials in block order, solves, updates, checks ----------------
-    if (tid < kAccum) {
+    {  // fixed order (slice-major, then slices in order) => every CTA gets bit-identical sums
+      const int c = tid & (kAccum - 1), slice = tid / kAccum;
+      constexpr int kSlices = kIcpThreads / kAccum;
       double s = 0.0;
-      for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(&p.partials[(size_t)b * kAccum + tid]);
-      s_red[0][tid] = s;
+      for (unsigned b = slice; b < gridDim.x; b += kSlices) s += __ldcg(&p.partials[(size_t)b * kAccum + c]);
+      s_red[slice][c] = s;
+      __syncthreads();
+      if (tid < kAccum) {
+        double t = 0.0;
+        for (int sl = 0; sl < kSlices; ++sl) t += s_red[sl][tid];
+        s_red[0][tid] = t;
+      }
     }
     __syncthreads();
     if (tid == 0) {
@@ -391,6 +440,8 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
         for (int t = 0; t < 6; ++t) { e.b[t] = S.b[t]; e.x[t] = S.x[t]; }
         for (int t = 0; t < 16; ++t) e.T_iter[t] = S.T_iter[t];
         e.P = P; e.solve_info = S.solve_info;
+        ts[5] = gtimer();
+        for (int t = 0; t < 6; ++t) e.ts[t] = ts[t];
       }
       S.iteration += 1;
     }

@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <cstdlib>
 #include <new>
 
 using namespace b200;
@@ -122,6 +123,7 @@ struct b200_icp {
   float4* d_flush = nullptr;
   size_t flush_elems = 0;
   int last_grid = 0;
+  int debug_stats = 0;  // env B200_ICP_DEBUG=1
 };
 
 namespace {
@@ -222,6 +224,8 @@ int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool tim
   p.max_iterations = h->prm.max_iterations; p.use_differential = h->prm.use_differential;
   p.min_rot = h->prm.min_diff_rot; p.min_trans = h->prm.min_diff_trans; p.smooth = h->prm.smooth_length;
   p.ids = h->d_ids; p.dists = h->d_dists; p.spos = h->d_spos; p.weights = h->d_w;
+  p.debug_stats = h->debug_stats;
+  if (h->debug_stats) B200_CUDA(cudaMemsetAsync(h->d_log, 0, (size_t)kMaxLog * sizeof(IcpLogEntry), s));
   p.hist = h->d_hist; p.partials = h->d_partials; p.out = h->d_out; p.log = h->d_log; p.frames = h->d_frames;
   B200_CUDA(cudaEventRecord(h->ev[2], s));
   B200_TRY(launch_icp_kernel(p, h->device, s, &h->last_grid));
@@ -307,6 +311,7 @@ int b200_icp_create(b200_icp** out, int device, const b200_icp_params* prm) {
   if (!h) { set_error("out of host memory"); return B200_E_CUDA; }
   h->device = device;
   h->prm = *prm;
+  { const char* e = getenv("B200_ICP_DEBUG"); h->debug_stats = (e && e[0] == '1') ? 1 : 0; }
   h->map.device = device;
   int st = B200_OK;
   if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess)
@@ -435,6 +440,47 @@ int b200_icp_get_log(b200_icp* h, int max_log, float* H, float* b, float* x, flo
     if (x) std::memcpy(x + 6 * (size_t)i, tmp[i].x, sizeof(tmp[i].x));
     if (T_iter) std::memcpy(T_iter + 16 * (size_t)i, tmp[i].T_iter, sizeof(tmp[i].T_iter));
     if (P) P[i] = tmp[i].P;
+  }
+  *n = cnt;
+  delete[] tmp;
+  return B200_OK;
+}
+
+int b200_icp_get_phase_times(b200_icp* h, int max_log, float* us, int* n) {
+  if (!h || !n || !us) { set_error("b200_icp_get_phase_times: bad arguments"); return B200_E_BAD_PARAM; }
+  DeviceGuard dg(h->device);
+  IcpLogEntry* tmp = new (std::nothrow) IcpLogEntry[kMaxLog];
+  if (!tmp) { set_error("out of host memory"); return B200_E_CUDA; }
+  if (cudaMemcpy(tmp, h->d_log, (size_t)kMaxLog * sizeof(IcpLogEntry), cudaMemcpyDeviceToHost) != cudaSuccess) {
+    delete[] tmp;
+    return cuda_fail(cudaGetLastError(), "cudaMemcpy(log)", __FILE__, __LINE__);
+  }
+  const int cnt = std::min(std::min(max_log, kMaxLog), h->h_out ? h->h_out->iterations : 0);
+  for (int i = 0; i < cnt; ++i) {
+    for (int t = 0; t < 5; ++t) us[6 * (size_t)i + t] = (float)((double)(tmp[i].ts[t + 1] - tmp[i].ts[t]) * 1e-3);
+    us[6 * (size_t)i + 5] = (i + 1 < cnt) ? (float)((double)(tmp[i + 1].ts[0] - tmp[i].ts[0]) * 1e-3)
+                                          : (float)((double)(tmp[i].ts[5] - tmp[i].ts[0]) * 1e-3);
+  }
+  *n = cnt;
+  delete[] tmp;
+  return B200_OK;
+}
+
+int b200_icp_get_debug_stats(b200_icp* h, int max_log, double* st, int* n) {
+  if (!h || !n || !st) { set_error("b200_icp_get_debug_stats: bad arguments"); return B200_E_BAD_PARAM; }
+  DeviceGuard dg(h->device);
+  IcpLogEntry* tmp = new (std::nothrow) IcpLogEntry[kMaxLog];
+  if (!tmp) { set_error("out of host memory"); return B200_E_CUDA; }
+  if (cudaMemcpy(tmp, h->d_log, (size_t)kMaxLog * sizeof(IcpLogEntry), cudaMemcpyDeviceToHost) != cudaSuccess) {
+    delete[] tmp;
+    return cuda_fail(cudaGetLastError(), "cudaMemcpy(log)", __FILE__, __LINE__);
+  }
+  const int cnt = std::min(std::min(max_log, kMaxLog), h->h_out ? h->h_out->iterations : 0);
+  for (int i = 0; i < cnt; ++i) {
+    st[4 * (size_t)i + 0] = (double)tmp[i].dbg_rows;
+    st[4 * (size_t)i + 1] = (double)tmp[i].dbg_cands;
+    st[4 * (size_t)i + 2] = (double)tmp[i].dbg_match_ns_max * 1e-3;
+    st[4 * (size_t)i + 3] = (double)tmp[i].dbg_match_ns_sum * 1e-3 / std::max(1, h->last_grid);
   }
   *n = cnt;
   delete[] tmp;

@@ -18,6 +18,12 @@ struct IcpLogEntry {
   int P;
   int solve_info;
   int pad[2];
+  // %globaltimer (ns) seen by thread 0 of CTA 0: iteration start, own matching done, trimmed limit known,
+  // own linearisation done, all partials visible, solve + checks done
+  unsigned long long ts[6];
+  // debug statistics (only with IcpKernelParams::debug_stats): cell rows resolved, candidates examined, and the
+  // slowest / summed per-CTA duration of the matching phase (ns)
+  unsigned long long dbg_rows, dbg_cands, dbg_match_ns_max, dbg_match_ns_sum;
 };
 
 struct IcpDeviceResult {
@@ -49,6 +55,7 @@ struct IcpKernelParams {
   double* partials;         // [gridDim.x][kAccum]
   IcpDeviceResult* out;
   IcpLogEntry* log;         // kMaxLog entries
+  int debug_stats;          // collect IcpLogEntry::dbg_* (adds global atomics; profiling aid only)
   const float* frames;      // 3 x 16 floats: T_refIn_refMean, T_refMean_readMean, T_readIn_readMean
 };
 

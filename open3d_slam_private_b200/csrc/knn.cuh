@@ -6,9 +6,21 @@
 // accepted iff dist2 <= maxDist^2, result ascending by (dist2, original index), ties -> smallest index, unfilled
 // slots id = -1 / dist = +inf.
 //
-// Search: cells are visited in growing cubic blocks around the query; a block of half-width s guarantees that every
-// unvisited point is farther than a conservative radius r(s). The query stops as soon as its k-th best is within
-// r(s) or r(s) exceeds maxDist, so the answer is exact for ANY cell size and ANY maxDist (including inf).
+// Search. Everything is done in "cell units" u = (x - origin) * inv_cell, computed with the SAME float expression
+// the index build uses, so the point -> cell map is monotone. A query scans the cells of a box
+// [floor(u - h), floor(u + h)]^3, which contains every map point whose cell coordinates are within h of the query's
+// on every axis, hence every point within distance (h - slack) * cell. After a box is scanned the radius still
+// needed is r = min(sqrt(k-th best), maxDist); the query is finished as soon as h covers r, otherwise the box grows
+// to r (or doubles while no bound exists) and only the new shell is scanned. Rows (runs of cells along x, ONE
+// contiguous candidate range in the cell-sorted point array) farther than r from the query in (y, z) are skipped and
+// the x-extent of a row is clipped to the ball. The answer is exact for ANY cell size and ANY maxDist (incl. inf).
+//
+// Two drivers share the row scanner:
+//   knn_query<K>      one thread per query (k > 1; register-resident k-best list)
+//   knn_query_warp1   k = 1, warp-cooperative: the (query, row) work items of the 32 queries of a warp are
+//                     flattened and dealt round-robin to the 32 lanes, so a query with a far neighbour (or none
+//                     within maxDist) no longer stalls the other 31 lanes — the tail that dominated the first version
+//                     (ncu: 80 % of warp samples waiting at barriers).
 #pragma once
 #include "common.cuh"
 
@@ -56,79 +68,312 @@ __device__ __forceinline__ int cell_of(float u, int n) {
   return c < 0 ? 0 : (c >= n ? n - 1 : c);
 }
 
-template <int K>
-__device__ __forceinline__ void scan_range(const GridView& g, uint32_t a, uint32_t b, float qx, float qy, float qz,
-                                           float md2, KList<K>& L, unsigned& visited) {
-  for (uint32_t j = a; j < b; ++j) {
-    const float4 p = __ldg(&g.pts[j]);
-    const float d = dist2_rn(qx, qy, qz, p.x, p.y, p.z);
-    if (d <= md2) L.offer(d, __float_as_int(p.w), (int)j);
-  }
-  visited += (b - a);
+// inclusive cell box, clamped to the grid; empty when lo > hi on any axis
+struct CellBox {
+  int x0, x1, y0, y1, z0, z1;
+  __device__ __forceinline__ bool empty() const { return x0 > x1 || y0 > y1 || z0 > z1; }
+  __device__ __forceinline__ int ny() const { return y1 - y0 + 1; }
+  __device__ __forceinline__ int rows() const { return empty() ? 0 : (y1 - y0 + 1) * (z1 - z0 + 1); }
+};
+
+__device__ __forceinline__ void axis_range(float u, float h, int n, int& lo, int& hi) {
+  // floor(u -+ h) clamped in float first (u, h may be huge), then to the grid
+  const float a = fminf(fmaxf(floorf(u - h), -1.0f), (float)n);
+  const float b = fminf(fmaxf(floorf(u + h), -1.0f), (float)n);
+  lo = max((int)a, 0);
+  hi = min((int)b, n - 1);
 }
 
+__device__ __forceinline__ CellBox ball_box(const GridView& g, float ux, float uy, float uz, float h) {
+  CellBox b;
+  axis_range(ux, h, g.nx, b.x0, b.x1);
+  axis_range(uy, h, g.ny, b.y0, b.y1);
+  axis_range(uz, h, g.nz, b.z0, b.z1);
+  return b;
+}
+
+__device__ __forceinline__ bool covers_grid(const GridView& g, const CellBox& b) {
+  return b.x0 <= 0 && b.y0 <= 0 && b.z0 <= 0 && b.x1 >= g.nx - 1 && b.y1 >= g.ny - 1 && b.z1 >= g.nz - 1;
+}
+
+// per-query constants of the search
+struct QueryGeom {
+  float qx, qy, qz;   // query position
+  float ux, uy, uz;   // in cell units
+  float slack;        // bound (cell units) on the rounding of any cell-unit difference involving this query
+  float md2;          // maxDist^2 (inf allowed)
+  float rmd;          // maxDist in cell units incl. slack (inf allowed)
+};
+
+__device__ __forceinline__ bool make_geom(const GridView& g, float qx, float qy, float qz, float md2, QueryGeom& q) {
+  q.qx = qx; q.qy = qy; q.qz = qz; q.md2 = md2;
+  q.ux = cell_coord(qx, g.ox, g.inv_cell);
+  q.uy = cell_coord(qy, g.oy, g.inv_cell);
+  q.uz = cell_coord(qz, g.oz, g.inv_cell);
+  const float nmax = (float)max(g.nx, max(g.ny, g.nz));
+  q.slack = fmaxf(fmaxf(fabsf(q.ux), fabsf(q.uy)), fmaxf(fabsf(q.uz), nmax)) * 4.8e-7f;  // ~2^-21 relative
+  q.rmd = (md2 == INFINITY) ? INFINITY : sqrtf(md2) * g.inv_cell * 1.00001f + q.slack;
+  return q.ux == q.ux && q.uy == q.uy && q.uz == q.uz;  // false for a NaN query: it has no matches
+}
+
+// radius (cell units, conservative) that still has to be covered given the current k-th best distance
+__device__ __forceinline__ float need_radius(const GridView& g, const QueryGeom& q, float kth) {
+  const float rk = (kth == INFINITY) ? INFINITY : sqrtf(kth) * g.inv_cell * 1.00001f + q.slack;
+  return fminf(rk, q.rmd);
+}
+
+// first box half-width: the 2x2x2 block around the query (h = 0.5), smaller when maxDist is smaller; when the
+// query lies outside the grid, far enough to reach it
+__device__ __forceinline__ float first_halfwidth(const GridView& g, const QueryGeom& q) {
+  float h = 0.5f;
+  const float ox = fmaxf(fmaxf(-q.ux, q.ux - (float)g.nx), 0.f);
+  const float oy = fmaxf(fmaxf(-q.uy, q.uy - (float)g.ny), 0.f);
+  const float oz = fmaxf(fmaxf(-q.uz, q.uz - (float)g.nz), 0.f);
+  const float out = fmaxf(ox, fmaxf(oy, oz));
+  if (out > 0.f) h = out + 1.0f + q.slack;
+  return fminf(h, q.rmd);
+}
+
+// ---- candidate range / row scanners ------------------------------------------------------------------------------
+// visit(d, original index, sorted position) is called for every candidate with d <= maxDist^2
+template <class Visit>
+__device__ __forceinline__ void scan_range(const GridView& g, const QueryGeom& q, uint32_t a, uint32_t b,
+                                           unsigned& visited, Visit&& visit) {
+  visited += (b - a);
+  uint32_t j = a;
+  for (; j + 4u <= b; j += 4u) {  // four independent 16-byte loads in flight
+    const float4 p0 = __ldg(&g.pts[j]), p1 = __ldg(&g.pts[j + 1]), p2 = __ldg(&g.pts[j + 2]), p3 = __ldg(&g.pts[j + 3]);
+    const float d0 = dist2_rn(q.qx, q.qy, q.qz, p0.x, p0.y, p0.z);
+    const float d1 = dist2_rn(q.qx, q.qy, q.qz, p1.x, p1.y, p1.z);
+    const float d2 = dist2_rn(q.qx, q.qy, q.qz, p2.x, p2.y, p2.z);
+    const float d3 = dist2_rn(q.qx, q.qy, q.qz, p3.x, p3.y, p3.z);
+    if (d0 <= q.md2) visit(d0, __float_as_int(p0.w), (int)j);
+    if (d1 <= q.md2) visit(d1, __float_as_int(p1.w), (int)j + 1);
+    if (d2 <= q.md2) visit(d2, __float_as_int(p2.w), (int)j + 2);
+    if (d3 <= q.md2) visit(d3, __float_as_int(p3.w), (int)j + 3);
+  }
+  for (; j < b; ++j) {
+    const float4 p = __ldg(&g.pts[j]);
+    const float d = dist2_rn(q.qx, q.qy, q.qz, p.x, p.y, p.z);
+    if (d <= q.md2) visit(d, __float_as_int(p.w), (int)j);
+  }
+}
+
+// one row (iy, iz) of box B; cells of the previously scanned box P are skipped; rc = radius (cell units) beyond
+// which nothing is needed any more (inf: no pruning)
+template <class Visit>
+__device__ __forceinline__ void scan_row(const GridView& g, const QueryGeom& q, int bx0, int bx1, int px0, int px1,
+                                         int py0, int py1, int pz0, int pz1, float rc, int iy, int iz,
+                                         unsigned& visited, Visit&& visit) {
+  int xa = bx0, xb = bx1;
+  if (rc != INFINITY) {
+    const float dy = fmaxf(fmaxf((float)iy - q.uy, q.uy - (float)(iy + 1)) - q.slack, 0.f);
+    const float dz = fmaxf(fmaxf((float)iz - q.uz, q.uz - (float)(iz + 1)) - q.slack, 0.f);
+    const float rem = rc * rc - dy * dy - dz * dz;
+    if (rem < 0.f) return;
+    const float xh = sqrtf(rem) * 1.00001f + q.slack;
+    int lo, hi;
+    axis_range(q.ux, xh, g.nx, lo, hi);
+    xa = max(xa, lo); xb = min(xb, hi);
+    if (xa > xb) return;
+  }
+  const uint32_t* row = g.G + ((size_t)g.nx * ((size_t)iy + (size_t)g.ny * (size_t)iz));
+  if (px0 <= px1 && iy >= py0 && iy <= py1 && iz >= pz0 && iz <= pz1) {
+    const int e1 = min(xb, px0 - 1), s2 = max(xa, px1 + 1);
+    const bool left = xa <= e1, right = s2 <= xb;
+    uint32_t a0 = 0, b0 = 0, a1 = 0, b1 = 0;
+    if (left) { a0 = __ldg(row + xa); b0 = __ldg(row + e1 + 1); }
+    if (right) { a1 = __ldg(row + s2); b1 = __ldg(row + xb + 1); }
+    if (left) scan_range(g, q, a0, b0, visited, visit);
+    if (right) scan_range(g, q, a1, b1, visited, visit);
+  } else {
+    const uint32_t a = __ldg(row + xa), b = __ldg(row + xb + 1);
+    scan_range(g, q, a, b, visited, visit);
+  }
+}
+
+// ---- one thread per query, k-best list in registers --------------------------------------------------------------
 // kq = number of neighbours actually requested (<= K)
 template <int K>
 __device__ void knn_query(const GridView& g, float qx, float qy, float qz, float md2, int kq, KList<K>& L,
                           unsigned& visited) {
   L.init();
-  const float ux = cell_coord(qx, g.ox, g.inv_cell);
-  const float uy = cell_coord(qy, g.oy, g.inv_cell);
-  const float uz = cell_coord(qz, g.oz, g.inv_cell);
-  if (!(ux == ux && uy == uy && uz == uz)) return;  // NaN query: no matches
-  const float lim = 1.0e9f;
-  if (fabsf(ux) > lim || fabsf(uy) > lim || fabsf(uz) > lim) {
-    // absurdly far query: every map point is a candidate only if maxDist allows it; scan everything (exact)
-    scan_range<K>(g, 0u, (uint32_t)g.M, qx, qy, qz, md2, L, visited);
+  QueryGeom q;
+  if (!make_geom(g, qx, qy, qz, md2, q)) return;  // NaN query: no matches
+  auto visit = [&](float d, int id, int sp) { L.offer(d, id, sp); };
+  if (fabsf(q.ux) > 1.0e9f || fabsf(q.uy) > 1.0e9f || fabsf(q.uz) > 1.0e9f) {
+    // absurdly far query (cell arithmetic no longer resolves cells): scan everything, still exact
+    scan_range(g, q, 0u, (uint32_t)g.M, visited, visit);
     return;
   }
-  const float nmax = (float)max(g.nx, max(g.ny, g.nz));
-  const float slack = fmaxf(fmaxf(fabsf(ux), fabsf(uy)), fmaxf(fabsf(uz), nmax)) * 4.8e-7f;  // ~2^-21 relative
-  const int bx = (int)floorf(ux - 0.5f), by = (int)floorf(uy - 0.5f), bz = (int)floorf(uz - 0.5f);
-  // first stage whose block touches the grid on every axis
-  int s = 0;
-  s = max(s, bx - (g.nx - 1)); s = max(s, -(bx + 1));
-  s = max(s, by - (g.ny - 1)); s = max(s, -(by + 1));
-  s = max(s, bz - (g.nz - 1)); s = max(s, -(bz + 1));
-  // previously scanned block (clamped, inclusive); empty at start
-  int px0 = 1, px1 = 0, py0 = 1, py1 = 0, pz0 = 1, pz1 = 0;
-  while (true) {
-    const int lx = bx - s, hx = bx + 1 + s, ly = by - s, hy = by + 1 + s, lz = bz - s, hz = bz + 1 + s;
-    const int cx0 = max(lx, 0), cx1 = min(hx, g.nx - 1);
-    const int cy0 = max(ly, 0), cy1 = min(hy, g.ny - 1);
-    const int cz0 = max(lz, 0), cz1 = min(hz, g.nz - 1);
-    for (int iz = cz0; iz <= cz1; ++iz) {
-      const bool zin = (iz >= pz0 && iz <= pz1);
-      for (int iy = cy0; iy <= cy1; ++iy) {
-        const uint32_t* row = g.G + ((size_t)g.nx * ((size_t)iy + (size_t)g.ny * (size_t)iz));
-        if (zin && iy >= py0 && iy <= py1) {
-          // row crosses the already scanned block: only the two new end segments
-          if (cx0 < px0) scan_range<K>(g, __ldg(row + cx0), __ldg(row + px0), qx, qy, qz, md2, L, visited);
-          if (cx1 > px1) scan_range<K>(g, __ldg(row + px1 + 1), __ldg(row + cx1 + 1), qx, qy, qz, md2, L, visited);
-        } else {
-          scan_range<K>(g, __ldg(row + cx0), __ldg(row + cx1 + 1), qx, qy, qz, md2, L, visited);
-        }
-      }
-    }
-    px0 = cx0; px1 = cx1; py0 = cy0; py1 = cy1; pz0 = cz0; pz1 = cz1;
-    // conservative distance (in cells) from the query to the nearest face beyond which unvisited points may lie
-    float gmin = INFINITY;
-    if (lx > 0) gmin = fminf(gmin, ux - (float)lx);
-    if (hx < g.nx - 1) gmin = fminf(gmin, (float)(hx + 1) - ux);
-    if (ly > 0) gmin = fminf(gmin, uy - (float)ly);
-    if (hy < g.ny - 1) gmin = fminf(gmin, (float)(hy + 1) - uy);
-    if (lz > 0) gmin = fminf(gmin, uz - (float)lz);
-    if (hz < g.nz - 1) gmin = fminf(gmin, (float)(hz + 1) - uz);
-    if (gmin == INFINITY) break;  // the block covers the whole grid
-    const float gc = (gmin - slack) * g.cell * 0.999998f;
-    const float r2 = gc > 0.f ? gc * gc : 0.f;
+  auto kth_of = [&]() {
     float kth = L.d[K - 1];
 #pragma unroll
     for (int j = 0; j < K - 1; ++j)
       if (j == kq - 1) kth = L.d[j];  // register-resident select (no dynamic indexing)
-    if (kth <= r2) break;  // k-th best is closer than anything unvisited
-    if (r2 > md2) break;           // nothing unvisited can be accepted
-    s += 1 + (s >> 1);
+    return kth;
+  };
+  float h = first_halfwidth(g, q);
+  CellBox P;
+  P.x0 = P.y0 = P.z0 = 1; P.x1 = P.y1 = P.z1 = 0;
+  while (true) {
+    const CellBox B = ball_box(g, q.ux, q.uy, q.uz, h + q.slack);
+    if (!B.empty()) {
+      for (int iz = B.z0; iz <= B.z1; ++iz)
+        for (int iy = B.y0; iy <= B.y1; ++iy) {
+          const float rc = need_radius(g, q, kth_of());  // shrinks while the scan finds closer points
+          scan_row(g, q, B.x0, B.x1, P.x0, P.x1, P.y0, P.y1, P.z0, P.z1, rc, iy, iz, visited, visit);
+        }
+      P = B;
+    }
+    const float need = need_radius(g, q, kth_of());
+    if (h >= need || covers_grid(g, B)) break;
+    h = (need <= fmaxf(4.f * h, 3.f)) ? need : fmaxf(2.f * h, 1.f);
+  }
+}
+
+// ---- k = 1, warp-cooperative -------------------------------------------------------------------------------------
+// Must be called by all 32 lanes of a converged warp; lanes with active == false only help. Each pass, every lane
+// that still needs cells owns nrows(lane) rows of its current box; the rows of all lanes are numbered consecutively
+// (warp prefix sum) and dealt 32 x kItems at a time. Phase A resolves kItems rows per lane to candidate ranges (all
+// cell-table loads of a round are in flight together); phase B scans them. A lane scanning a row for another lane's
+// query keeps a local best; a segmented warp minimum (items of one owner are contiguous) folds the 32 local
+// results, and every owner picks up the minimum of its segment. (d, id) ordering with ties -> smallest id keeps the
+// result independent of which lane scanned what. Cells already scanned by an earlier pass are scanned again
+// (harmless for k = 1: the same (d, id) never replaces itself), which keeps an item one contiguous range.
+__device__ __forceinline__ bool better1(float d, int id, float bd, int bid) {
+  return d < bd || (d == bd && id < bid);
+}
+
+// next half-width once a box of half-width h did not settle the query: straight to the needed radius when that is
+// known and not much larger; doubling otherwise (unknown radius, or a radius so large that a nearer shell probably
+// already holds the neighbour)
+__device__ __forceinline__ float next_halfwidth(float h, float need) {
+  return (need <= fmaxf(4.f * h, 3.f)) ? need : fmaxf(2.f * h, 1.f);
+}
+
+constexpr int kItems = 4;
+
+__device__ inline void knn_query_warp1(const GridView& g, bool active, float qx, float qy, float qz, float md2,
+                                       float& best_d, int& best_id, int& best_sp, unsigned& visited,
+                                       unsigned* rows_out = nullptr) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  best_d = INFINITY; best_id = -1; best_sp = -1;
+  QueryGeom q;
+  bool need = make_geom(g, qx, qy, qz, md2, q) && active;
+  if (need && (fabsf(q.ux) > 1.0e9f || fabsf(q.uy) > 1.0e9f || fabsf(q.uz) > 1.0e9f)) {
+    // absurdly far query: scan everything (exact); rare enough not to be shared
+    auto visit = [&](float d, int id, int sp) { if (better1(d, id, best_d, best_id)) { best_d = d; best_id = id; best_sp = sp; } };
+    scan_range(g, q, 0u, (uint32_t)g.M, visited, visit);
+    need = false;
+  }
+  float h = need ? first_halfwidth(g, q) : 0.f;
+  while (__any_sync(FULL, need)) {
+    CellBox B;
+    B.x0 = B.y0 = B.z0 = 1; B.x1 = B.y1 = B.z1 = 0;
+    float rc = INFINITY;
+    if (need) {
+      B = ball_box(g, q.ux, q.uy, q.uz, h + q.slack);
+      rc = need_radius(g, q, best_d);
+    }
+    const int nrows = need ? B.rows() : 0;
+    int incl = nrows;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(FULL, incl, o);
+      if (lane >= o) incl += t;
+    }
+    const int excl = incl - nrows;
+    const int total = __shfl_sync(FULL, incl, 31);
+    const int bny = B.ny();
+    for (int base = 0; base < total; base += 32 * kItems) {
+      // ---- phase A: item -> owner -> row -> candidate range
+      uint32_t ra[kItems], rb[kItems];
+      int own[kItems];
+#pragma unroll
+      for (int s = 0; s < kItems; ++s) {
+        const int t = base + s * 32 + lane;
+        int o = 0;  // owner of item t: the first lane whose inclusive prefix exceeds t
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1) {
+          const int v = __shfl_sync(FULL, incl, (o + step - 1) & 31);
+          if (v <= t) o += step;
+        }
+        const bool work = t < total;
+        o &= 31;
+        const float oux = __shfl_sync(FULL, q.ux, o), ouy = __shfl_sync(FULL, q.uy, o), ouz = __shfl_sync(FULL, q.uz, o);
+        const float oslack = __shfl_sync(FULL, q.slack, o);
+        const float orc = __shfl_sync(FULL, rc, o);
+        const int obx0 = __shfl_sync(FULL, B.x0, o), obx1 = __shfl_sync(FULL, B.x1, o);
+        const int oby0 = __shfl_sync(FULL, B.y0, o), obz0 = __shfl_sync(FULL, B.z0, o);
+        const int ony = __shfl_sync(FULL, bny, o);
+        const int oexcl = __shfl_sync(FULL, excl, o);
+        ra[s] = 0u; rb[s] = 0u;
+        own[s] = work ? o : -1;
+        if (work && rows_out) ++*rows_out;
+        if (work) {
+          const int r = t - oexcl;
+          const int iz = obz0 + r / ony, iy = oby0 + r % ony;
+          int xa = obx0, xb = obx1;
+          bool skip = false;
+          if (orc != INFINITY) {  // clip the row to the ball of the radius still needed
+            const float dy = fmaxf(fmaxf((float)iy - ouy, ouy - (float)(iy + 1)) - oslack, 0.f);
+            const float dz = fmaxf(fmaxf((float)iz - ouz, ouz - (float)(iz + 1)) - oslack, 0.f);
+            const float rem = orc * orc - dy * dy - dz * dz;
+            if (rem < 0.f) skip = true;
+            else {
+              const float xh = sqrtf(rem) * 1.00001f + oslack;
+              int lo, hi;
+              axis_range(oux, xh, g.nx, lo, hi);
+              xa = max(xa, lo); xb = min(xb, hi);
+              skip = xa > xb;
+            }
+          }
+          if (!skip) {
+            const uint32_t* row = g.G + ((size_t)g.nx * ((size_t)iy + (size_t)g.ny * (size_t)iz));
+            ra[s] = __ldg(row + xa); rb[s] = __ldg(row + xb + 1);
+          }
+        }
+      }
+      // ---- phase B: scan, fold, hand back
+#pragma unroll
+      for (int s = 0; s < kItems; ++s) {
+        if (base + s * 32 >= total) break;  // warp-uniform
+        const int o = own[s] & 31;
+        QueryGeom oq;
+        oq.qx = __shfl_sync(FULL, q.qx, o); oq.qy = __shfl_sync(FULL, q.qy, o); oq.qz = __shfl_sync(FULL, q.qz, o);
+        oq.md2 = __shfl_sync(FULL, q.md2, o);
+        float ld = INFINITY;
+        int lid = -1, lsp = -1;
+        if (own[s] >= 0 && rb[s] > ra[s]) {
+          auto visit = [&](float d, int id, int sp) { if (better1(d, id, ld, lid)) { ld = d; lid = id; lsp = sp; } };
+          scan_range(g, oq, ra[s], rb[s], visited, visit);
+        }
+        const int seg = own[s] >= 0 ? own[s] : -1 - lane;  // idle lanes form singleton segments
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {  // segmented minimum towards the first lane of every segment
+          const float d2 = __shfl_down_sync(FULL, ld, off);
+          const int id2 = __shfl_down_sync(FULL, lid, off);
+          const int sp2 = __shfl_down_sync(FULL, lsp, off);
+          const int sg2 = __shfl_down_sync(FULL, seg, off);
+          if (lane + off < 32 && sg2 == seg && better1(d2, id2, ld, lid)) { ld = d2; lid = id2; lsp = sp2; }
+        }
+        const int b0 = base + s * 32;
+        const int lo = max(excl, b0), hi = min(incl, b0 + 32);
+        const bool has = need && lo < hi;
+        const int src = has ? (lo - b0) : lane;
+        const float rd = __shfl_sync(FULL, ld, src);
+        const int rid = __shfl_sync(FULL, lid, src);
+        const int rsp = __shfl_sync(FULL, lsp, src);
+        if (has && better1(rd, rid, best_d, best_id)) { best_d = rd; best_id = rid; best_sp = rsp; }
+      }
+    }
+    if (need) {
+      const float nd = need_radius(g, q, best_d);
+      if (h >= nd || covers_grid(g, B)) need = false;
+      else h = next_halfwidth(h, nd);
+    }
   }
 }
 

@@ -28,23 +28,33 @@ __global__ void __launch_bounds__(kThreads) knn_kernel(const __grid_constant__ G
                                                        float* __restrict__ dists,
                                                        unsigned long long* __restrict__ visited) {
   unsigned long long vis_total = 0ull;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
-    const float4 q = __ldg(&query[i]);
+  // warp-uniform trip count: the k = 1 search is a warp collective
+  const int lane = threadIdx.x & 31;
+  for (int base = (blockIdx.x * blockDim.x + threadIdx.x) - lane; base < N; base += gridDim.x * blockDim.x) {
+    const int i = base + lane;
+    const bool in = i < N;
+    const float4 q = in ? __ldg(&query[i]) : make_float4(0.f, 0.f, 0.f, 1.f);
     float m2 = md2;
-    if (mdpp) {  // KDTreeVarDistMatcher: per-point radius
+    if (mdpp && in) {  // KDTreeVarDistMatcher: per-point radius
       const float r = __ldg(&mdpp[i]);
       m2 = isinf(r) ? INFINITY : __fmul_rn(r, r);
     }
-    KList<K> L;
     unsigned vis = 0;
-    knn_query<K>(g, q.x, q.y, q.z, m2, kq, L, vis);
-    vis_total += vis;
+    if (K == 1) {
+      float bd; int bid, bsp;
+      knn_query_warp1(g, in, q.x, q.y, q.z, m2, bd, bid, bsp, vis);
+      if (in) { ids[i] = bid; dists[i] = bd; }
+    } else if (in) {
+      KList<K> L;
+      knn_query<K>(g, q.x, q.y, q.z, m2, kq, L, vis);
 #pragma unroll
-    for (int j = 0; j < K; ++j)
-      if (j < kq) {
-        ids[(size_t)i * kq + j] = L.id[j];
-        dists[(size_t)i * kq + j] = L.d[j];
-      }
+      for (int j = 0; j < K; ++j)
+        if (j < kq) {
+          ids[(size_t)i * kq + j] = L.id[j];
+          dists[(size_t)i * kq + j] = L.d[j];
+        }
+    }
+    vis_total += vis;
   }
   for (int o = 16; o > 0; o >>= 1) vis_total += __shfl_xor_sync(0xffffffffu, vis_total, o);
   if (visited && (threadIdx.x & 31) == 0 && vis_total) atomicAdd(visited, vis_total);

@@ -119,31 +119,124 @@ struct PivQR {
   }
 };
 
+// Rank decision of PivQR<T, N> (compute() + rank()) with every loop unrolled and every pivot swap written as a
+// predicated swap over compile-time indices, so the N x N working matrix lives in registers (PivQR's dynamic
+// row/column indices push it to local memory, ~10x slower for one thread). Same operations in the same order =>
+// bit-identical pivots and the same rank as PivQR.
+template <typename T, int N>
+__device__ __forceinline__ int pivqr_rank(const T* A) {
+  T q[N * N];
+#pragma unroll
+  for (int i = 0; i < N * N; ++i) q[i] = A[i];
+  const T prec = Eps<T>::eps() * T(N);
+  int nonzero = N;
+  bool stopped = false;
+  T maxpivot = T(0), biggest = T(0);
+  T diag[N];
+#pragma unroll
+  for (int k = 0; k < N; ++k) {
+    diag[k] = T(0);
+    if (!stopped) {
+      int rb = k, cb = k;
+      T big = T(-1);
+#pragma unroll
+      for (int j = k; j < N; ++j)
+#pragma unroll
+        for (int i = k; i < N; ++i) {
+          const T v = fabs(q[i + j * N]);
+          if (v > big) { big = v; rb = i; cb = j; }
+        }
+      if (k == 0) biggest = big;
+      if (fabs(big) <= fabs(biggest) * prec) {
+        nonzero = k;
+        stopped = true;
+      } else {
+#pragma unroll
+        for (int r = k + 1; r < N; ++r)
+          if (r == rb) {
+#pragma unroll
+            for (int j = k; j < N; ++j) { const T t = q[k + j * N]; q[k + j * N] = q[r + j * N]; q[r + j * N] = t; }
+          }
+#pragma unroll
+        for (int c = k + 1; c < N; ++c)
+          if (c == cb) {
+#pragma unroll
+            for (int i = 0; i < N; ++i) { const T t = q[i + k * N]; q[i + k * N] = q[i + c * N]; q[i + c * N] = t; }
+          }
+        T tail = T(0);
+#pragma unroll
+        for (int i = k + 1; i < N; ++i) tail += q[i + k * N] * q[i + k * N];
+        const T c0 = q[k + k * N];
+        T beta, tk;
+        if (tail <= Eps<T>::tiny()) {
+          tk = T(0); beta = c0;
+#pragma unroll
+          for (int i = k + 1; i < N; ++i) q[i + k * N] = T(0);
+        } else {
+          beta = sqrt(c0 * c0 + tail);
+          if (c0 >= T(0)) beta = -beta;
+#pragma unroll
+          for (int i = k + 1; i < N; ++i) q[i + k * N] = q[i + k * N] / (c0 - beta);
+          tk = (beta - c0) / beta;
+        }
+        q[k + k * N] = beta;
+        diag[k] = beta;
+        if (fabs(beta) > maxpivot) maxpivot = fabs(beta);
+        if (N - k > 1 && tk != T(0)) {
+#pragma unroll
+          for (int j = k + 1; j < N; ++j) {
+            T tmp = T(0);
+#pragma unroll
+            for (int i = k + 1; i < N; ++i) tmp += q[i + k * N] * q[i + j * N];
+            tmp += q[k + j * N];
+            q[k + j * N] -= tk * tmp;
+#pragma unroll
+            for (int i = k + 1; i < N; ++i) q[i + j * N] -= tk * q[i + k * N] * tmp;
+          }
+        }
+      }
+    }
+  }
+  const T pre = fabs(maxpivot) * (Eps<T>::eps() * T(N));
+  int r = 0;
+#pragma unroll
+  for (int i = 0; i < N; ++i) r += (i < nonzero && fabs(diag[i]) > pre) ? 1 : 0;
+  return r;
+}
+
 // Cholesky solve of a symmetric positive definite system in double. Returns false on a non-positive pivot.
 template <int N>
 __host__ __device__ bool cholSolve(const double* A, const double* b, double* x) {
   double L[N * N];
+#pragma unroll
   for (int j = 0; j < N; ++j) {
     double d = A[j + j * N];
+#pragma unroll
     for (int k = 0; k < j; ++k) d -= L[j + k * N] * L[j + k * N];
     if (!(d > 0.0)) return false;
     d = sqrt(d);
     L[j + j * N] = d;
     const double inv = 1.0 / d;
+#pragma unroll
     for (int i = j + 1; i < N; ++i) {
       double s = A[i + j * N];
+#pragma unroll
       for (int k = 0; k < j; ++k) s -= L[i + k * N] * L[j + k * N];
       L[i + j * N] = s * inv;
     }
   }
   double y[N];
+#pragma unroll
   for (int i = 0; i < N; ++i) {
     double s = b[i];
+#pragma unroll
     for (int k = 0; k < i; ++k) s -= L[i + k * N] * y[k];
     y[i] = s / L[i + i * N];
   }
+#pragma unroll
   for (int i = N - 1; i >= 0; --i) {
     double s = y[i];
+#pragma unroll
     for (int k = i + 1; k < N; ++k) s -= L[k + i * N] * x[k];
     x[i] = s / L[i + i * N];
   }

@@ -75,9 +75,7 @@ __device__ __forceinline__ float3 apply_R(const float* R9, float3 n) {
 // solvePossiblyUnderdeterminedLinearSystem(A, b, x, false) — PointToPlane.cpp:199-256.
 // info: 0 full rank, 1 rank-deficient minimal-norm, 2 double-SVD fallback.
 __device__ inline void solve6_dev(const float* A, const float* b, float* x, int* info) {
-  la::PivQR<float, 6> qr;
-  qr.compute(A);
-  const int rank = qr.rank();
+  const int rank = la::pivqr_rank<float, 6>(A);  // register-resident; the full factorisation only when needed
   double Ad[36], bd[6], xd[6];
   for (int i = 0; i < 36; ++i) Ad[i] = (double)A[i];
   for (int i = 0; i < 6; ++i) bd[i] = (double)b[i];
@@ -97,6 +95,8 @@ __device__ inline void solve6_dev(const float* A, const float* b, float* x, int*
     return;
   }
   *info = 1;
+  la::PivQR<float, 6> qr;
+  qr.compute(A);
   if (rank == 0) {
     for (int i = 0; i < 6; ++i) x[i] = 0.f;
   } else {
