@@ -34,6 +34,9 @@ typedef enum {
 
 const char* b200_last_error(void);
 int b200_version(void);
+/* sizeof of the ABI structs as compiled (0 b200_icp_params, 1 b200_icp_result, 2 b200_index_opts,
+ * 3 b200_surface_normal_params), so a binding can verify its mirror */
+int b200_struct_size(int which);
 /* number of visible CUDA devices (0 when none / driver missing) */
 int b200_device_count(void);
 

@@ -91,7 +91,16 @@ struct b200_index {
 extern "C" {
 
 const char* b200_last_error(void) { return g_err.c_str(); }
-int b200_version(void) { return 100; }
+int b200_version(void) { return 101; }
+int b200_struct_size(int which) {
+  switch (which) {
+    case 0: return (int)sizeof(b200_icp_params);
+    case 1: return (int)sizeof(b200_icp_result);
+    case 2: return (int)sizeof(b200_index_opts);
+    case 3: return (int)sizeof(b200_surface_normal_params);
+    default: return -1;
+  }
+}
 
 int b200_device_count(void) {
   int n = 0;

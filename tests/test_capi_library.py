@@ -41,9 +41,11 @@ def test_version_and_default_params():
 
 def test_struct_sizes_match_header():
     # the ctypes mirrors must have the C layout of include/b200reg.h
-    assert ctypes.sizeof(B.IcpParams) == 16 * 4
-    assert ctypes.sizeof(B.IcpResult) == 4 * 4 + 4 * 16 * 4 + 2 * 4 + 8 + 3 * 4 + 4  # incl. tail padding
-    assert ctypes.sizeof(B.IndexOpts) == 16
+    lib = B.load()
+    assert ctypes.sizeof(B.IcpParams) == lib.b200_struct_size(0) == 16 * 4
+    assert ctypes.sizeof(B.IcpResult) == lib.b200_struct_size(1)
+    assert ctypes.sizeof(B.IndexOpts) == lib.b200_struct_size(2) == 16
+    assert ctypes.sizeof(B.SurfaceNormalParams) == lib.b200_struct_size(3)
 
 
 def test_no_cpu_fallback_without_device():
