@@ -196,6 +196,8 @@ int b200_icp_get_phase_times(b200_icp* icp, int max_log, float* us, int* n);
  * kernel): st[4*i + {0 cell rows resolved, 1 candidates examined, 2 slowest CTA's matching phase (us), 3 mean CTA
  * matching phase (us)}] */
 int b200_icp_get_debug_stats(b200_icp* icp, int max_log, double* st, int* n);
+/* profiling aid (B200_ICP_DEBUG=1): per warp slot of the first iteration {rows, candidates, passes, ns} */
+int b200_icp_get_debug_warps(b200_icp* icp, uint32_t* out4xS, int max_slots, int* n);
 /* evict L2 (writes a buffer larger than L2) on the handle's stream; for benchmarking hygiene */
 int b200_icp_flush_l2(b200_icp* icp);
 

@@ -364,6 +364,13 @@ class ICP:
         _check(load().b200_icp_get_debug_stats(self.h, max_log, st.ctypes.data_as(C.POINTER(C.c_double)), C.byref(n)))
         return st[:n.value]
 
+    def debug_warps(self):
+        slots = (self._n + 31) // 32
+        out = np.zeros((slots, 4), np.uint32)
+        n = C.c_int()
+        _check(load().b200_icp_get_debug_warps(self.h, out.ctypes.data_as(C.POINTER(C.c_uint32)), slots, C.byref(n)))
+        return out[:n.value]
+
     def flush_l2(self):
         _check(load().b200_icp_flush_l2(self.h))
 

@@ -159,14 +159,34 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     // ---------------- phase 1: transform + match ----------------
     unsigned dbg_rows = 0, dbg_cands = 0;
     const unsigned long long dbg_t0 = p.debug_stats ? gtimer() : 0ull;
-    for (int base = gtid - lane; base < p.N; base += nthreads) {  // warp-uniform: the k = 1 search is a warp collective
-      const int i = base + lane;
+    // Query -> thread map: lane l of warp slot w takes query l * nslots + w. Consecutive scan points (spatially
+    // coherent, so equally cheap or equally expensive) are spread over different warps; a warp holding 32 expensive
+    // queries was the tail every other warp waited for at the grid barrier. Warp-uniform trip count: the k = 1 search
+    // is a warp collective.
+    const int nslots = (p.N + 31) >> 5;
+    for (int slot = gtid >> 5; slot < nslots; slot += nthreads >> 5) {
+      const int i = lane * nslots + (int)(((unsigned)slot + (unsigned)lane * 97u) % (unsigned)nslots);
       const bool in = i < p.N;
       const float4 q = in ? apply_T(S.Tc, __ldg(&p.reading[i])) : make_float4(0.f, 0.f, 0.f, 1.f);
       unsigned vis = 0;
       if (K == 1) {
         float bd; int bid, bsp;
-        knn_query_warp1(p.g, in, q.x, q.y, q.z, p.md2, bd, bid, bsp, vis, p.debug_stats ? &dbg_rows : nullptr);
+        unsigned w_rows = 0, w_pass = 0;
+        const unsigned long long w_t0 = p.debug_stats ? gtimer() : 0ull;
+        knn_query_warp1(p.g, in, q.x, q.y, q.z, p.md2, bd, bid, bsp, vis, p.debug_stats ? &w_rows : nullptr,
+                        p.debug_stats ? &w_pass : nullptr);
+        if (p.debug_stats) {
+          dbg_rows += w_rows;
+          if (p.dbg_warp && S.iteration == 0) {
+            const unsigned long long w_dt = gtimer() - w_t0;
+            unsigned r = w_rows, c = vis;
+            for (int o = 16; o > 0; o >>= 1) { r += __shfl_xor_sync(0xffffffffu, r, o); c += __shfl_xor_sync(0xffffffffu, c, o); }
+            if (lane == 0) {
+              p.dbg_warp[4 * slot + 0] = r; p.dbg_warp[4 * slot + 1] = c; p.dbg_warp[4 * slot + 2] = w_pass;
+              p.dbg_warp[4 * slot + 3] = (unsigned)w_dt;
+            }
+          }
+        }
         if (in) {
           p.ids[i] = bid; p.dists[i] = bd; p.spos[i] = bsp;
           if (p.use_trimmed && bd != INFINITY) atomicAdd(&s_hist[(__float_as_uint(bd) >> 20) & 0x7ffu], 1u);
@@ -249,8 +269,8 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     // ---------------- phase 3: weights + linearisation, reduced to one partial per CTA ----------------
     for (int t = tid; t < kWarps * kAccum; t += kIcpThreads) (&s_red[0][0])[t] = 0.0;
     __syncthreads();
-    for (int base = blockIdx.x * kIcpThreads + wid * 32; base < p.N; base += nthreads) {
-      const int i = base + lane;
+    for (int slot = gtid >> 5; slot < nslots; slot += nthreads >> 5) {  // same map as phase 1 (no barrier needed in between)
+      const int i = lane * nslots + (int)(((unsigned)slot + (unsigned)lane * 97u) % (unsigned)nslots);
       const bool in = i < p.N;
       float4 q = make_float4(0.f, 0.f, 0.f, 1.f);
       float3 nq = make_float3(0.f, 0.f, 0.f);

@@ -124,6 +124,8 @@ struct b200_icp {
   size_t flush_elems = 0;
   int last_grid = 0;
   int debug_stats = 0;  // env B200_ICP_DEBUG=1
+  unsigned* d_dbg_warp = nullptr;
+  size_t cap_dbg_warp = 0;
 };
 
 namespace {
@@ -225,6 +227,17 @@ int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool tim
   p.min_rot = h->prm.min_diff_rot; p.min_trans = h->prm.min_diff_trans; p.smooth = h->prm.smooth_length;
   p.ids = h->d_ids; p.dists = h->d_dists; p.spos = h->d_spos; p.weights = h->d_w;
   p.debug_stats = h->debug_stats;
+  p.dbg_warp = nullptr;
+  if (h->debug_stats) {
+    const size_t need = (size_t)((N + 31) / 32) * 4;
+    if (need > h->cap_dbg_warp) {
+      cudaFree(h->d_dbg_warp);
+      h->d_dbg_warp = nullptr;
+      B200_CUDA(cudaMalloc(&h->d_dbg_warp, need * sizeof(unsigned)));
+      h->cap_dbg_warp = need;
+    }
+    p.dbg_warp = h->d_dbg_warp;
+  }
   if (h->debug_stats) B200_CUDA(cudaMemsetAsync(h->d_log, 0, (size_t)kMaxLog * sizeof(IcpLogEntry), s));
   p.hist = h->d_hist; p.partials = h->d_partials; p.out = h->d_out; p.log = h->d_log; p.frames = h->d_frames;
   B200_CUDA(cudaEventRecord(h->ev[2], s));
@@ -331,7 +344,7 @@ void b200_icp_destroy(b200_icp* h) {
     cudaFree(h->d_raw); cudaFree(h->d_raw_n); cudaFree(h->d_read); cudaFree(h->d_read_n); cudaFree(h->d_stage3);
     cudaFree(h->d_ids); cudaFree(h->d_spos); cudaFree(h->d_dists); cudaFree(h->d_w);
     cudaFree(h->d_hist); cudaFree(h->d_partials); cudaFree(h->d_meanpart); cudaFree(h->d_out); cudaFree(h->d_log);
-    cudaFree(h->d_frames); cudaFree(h->d_Tinit); cudaFree(h->d_flush);
+    cudaFree(h->d_frames); cudaFree(h->d_Tinit); cudaFree(h->d_flush); cudaFree(h->d_dbg_warp);
     cudaFreeHost(h->h_out); cudaFreeHost(h->h_frames); cudaFreeHost(h->h_Tinit);
     for (int i = 0; i < 5; ++i)
       if (h->ev[i]) cudaEventDestroy(h->ev[i]);
@@ -484,6 +497,17 @@ int b200_icp_get_debug_stats(b200_icp* h, int max_log, double* st, int* n) {
   }
   *n = cnt;
   delete[] tmp;
+  return B200_OK;
+}
+
+int b200_icp_get_debug_warps(b200_icp* h, uint32_t* out, int max_slots, int* n) {
+  if (!h || !out || !n) { set_error("b200_icp_get_debug_warps: bad arguments"); return B200_E_BAD_PARAM; }
+  DeviceGuard dg(h->device);
+  const int slots = std::min(max_slots, (h->N + 31) / 32);
+  *n = 0;
+  if (!h->d_dbg_warp || slots <= 0) return B200_OK;
+  B200_CUDA(cudaMemcpy(out, h->d_dbg_warp, (size_t)slots * 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  *n = slots;
   return B200_OK;
 }
 

@@ -55,6 +55,7 @@ struct IcpKernelParams {
   double* partials;         // [gridDim.x][kAccum]
   IcpDeviceResult* out;
   IcpLogEntry* log;         // kMaxLog entries
+  unsigned* dbg_warp;       // debug: per warp slot of iteration 0: {rows, candidates, passes, ns} (nullable)
   int debug_stats;          // collect IcpLogEntry::dbg_* (adds global atomics; profiling aid only)
   const float* frames;      // 3 x 16 floats: T_refIn_refMean, T_refMean_readMean, T_readIn_readMean
 };

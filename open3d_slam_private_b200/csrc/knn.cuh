@@ -152,10 +152,15 @@ __device__ __forceinline__ void scan_range(const GridView& g, const QueryGeom& q
     if (d2 <= q.md2) visit(d2, __float_as_int(p2.w), (int)j + 2);
     if (d3 <= q.md2) visit(d3, __float_as_int(p3.w), (int)j + 3);
   }
-  for (; j < b; ++j) {
-    const float4 p = __ldg(&g.pts[j]);
-    const float d = dist2_rn(q.qx, q.qy, q.qz, p.x, p.y, p.z);
-    if (d <= q.md2) visit(d, __float_as_int(p.w), (int)j);
+  if (j < b) {  // 1..3 left: one batch of clamped loads (a serial loop would pay the memory latency per candidate)
+    const uint32_t j1 = min(j + 1u, b - 1u), j2 = min(j + 2u, b - 1u);
+    const float4 p0 = __ldg(&g.pts[j]), p1 = __ldg(&g.pts[j1]), p2 = __ldg(&g.pts[j2]);
+    const float d0 = dist2_rn(q.qx, q.qy, q.qz, p0.x, p0.y, p0.z);
+    const float d1 = dist2_rn(q.qx, q.qy, q.qz, p1.x, p1.y, p1.z);
+    const float d2 = dist2_rn(q.qx, q.qy, q.qz, p2.x, p2.y, p2.z);
+    if (d0 <= q.md2) visit(d0, __float_as_int(p0.w), (int)j);
+    if (j + 1u < b && d1 <= q.md2) visit(d1, __float_as_int(p1.w), (int)j1);
+    if (j + 2u < b && d2 <= q.md2) visit(d2, __float_as_int(p2.w), (int)j2);
   }
 }
 
@@ -256,7 +261,7 @@ constexpr int kItems = 4;
 
 __device__ inline void knn_query_warp1(const GridView& g, bool active, float qx, float qy, float qz, float md2,
                                        float& best_d, int& best_id, int& best_sp, unsigned& visited,
-                                       unsigned* rows_out = nullptr) {
+                                       unsigned* rows_out = nullptr, unsigned* passes_out = nullptr) {
   constexpr unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   best_d = INFINITY; best_id = -1; best_sp = -1;
@@ -269,7 +274,34 @@ __device__ inline void knn_query_warp1(const GridView& g, bool active, float qx,
     need = false;
   }
   float h = need ? first_halfwidth(g, q) : 0.f;
+  // ---- pass 1, per lane: the 2x2x2 block around the query. Every lane has the same <= 4 rows of work, so there is
+  // nothing to balance and no shuffle traffic; near convergence this pass settles every query. All cell-table
+  // loads are issued before the first candidate is touched.
+  if (need && h <= 0.5f) {
+    const CellBox B = ball_box(g, q.ux, q.uy, q.uz, h + q.slack);
+    if (B.y1 - B.y0 <= 1 && B.z1 - B.z0 <= 1) {
+      uint32_t ra[4], rb[4];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int iy = B.y0 + (r & 1), iz = B.z0 + (r >> 1);
+        ra[r] = 0u; rb[r] = 0u;
+        if (iy <= B.y1 && iz <= B.z1 && B.x0 <= B.x1) {
+          const uint32_t* row = g.G + ((size_t)g.nx * ((size_t)iy + (size_t)g.ny * (size_t)iz));
+          ra[r] = __ldg(row + B.x0); rb[r] = __ldg(row + B.x1 + 1);
+          if (rows_out) ++*rows_out;
+        }
+      }
+      auto visit = [&](float d, int id, int sp) { if (better1(d, id, best_d, best_id)) { best_d = d; best_id = id; best_sp = sp; } };
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+        if (rb[r] > ra[r]) scan_range(g, q, ra[r], rb[r], visited, visit);
+      const float nd = need_radius(g, q, best_d);
+      if (h >= nd || covers_grid(g, B)) need = false;
+      else h = next_halfwidth(h, nd);
+    }
+  }
   while (__any_sync(FULL, need)) {
+    if (passes_out) ++*passes_out;
     CellBox B;
     B.x0 = B.y0 = B.z0 = 1; B.x1 = B.y1 = B.z1 = 0;
     float rc = INFINITY;
@@ -314,7 +346,8 @@ __device__ inline void knn_query_warp1(const GridView& g, bool active, float qx,
         if (work && rows_out) ++*rows_out;
         if (work) {
           const int r = t - oexcl;
-          const int iz = obz0 + r / ony, iy = oby0 + r % ony;
+          const int rz = (int)(((float)r + 0.5f) * __frcp_rn((float)ony));  // exact: r, ony < 2^20
+          const int iz = obz0 + rz, iy = oby0 + (r - rz * ony);
           int xa = obx0, xb = obx1;
           bool skip = false;
           if (orc != INFINITY) {  // clip the row to the ball of the radius still needed

@@ -24,5 +24,14 @@ for rep in range(2):
             print("  " + " ".join("%7.1f" % v for v in row))
         print("  sum " + " ".join("%7.1f" % v for v in pt.sum(0)))
         if os.environ.get("B200_ICP_DEBUG") == "1":
+            w = icp.debug_warps().astype(np.float64)
+            if len(w):
+                o = np.argsort(w[:, 3])
+                print("   per-warp it0: ns pct 50/90/99/max %s | rows 50/99/max %s | cands 50/99/max %s" % (
+                    np.percentile(w[:, 3], [50, 90, 99, 100]).astype(int), np.percentile(w[:, 0], [50, 99, 100]).astype(int),
+                    np.percentile(w[:, 1], [50, 99, 100]).astype(int)))
+                print("   corr(ns, rows) %.2f corr(ns, cands) %.2f ; slowest 5 warps (rows, cands, passes, ns): %s" % (
+                    np.corrcoef(w[:, 3], w[:, 0])[0, 1], np.corrcoef(w[:, 3], w[:, 1])[0, 1], w[o[-5:]].astype(int).tolist()))
+                print("   fastest 3: %s" % w[o[:3]].astype(int).tolist())
             for row in icp.debug_stats():
                 print("   rows/q %.1f cands/q %.1f match max %.1f us mean %.1f us" % (row[0] / N, row[1] / N, row[2], row[3]))
