@@ -399,20 +399,15 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
       }
     }
     __syncthreads();
-    if (tid == 0) {
-      const double* a = s_red[0];
-      const int P = (int)(a[27] + 0.5);
-      S.P = P;
-      S.wsum = (float)a[28];
-      float real[16];
-      eye4(real);
-      for (int t = 0; t < 36; ++t) S.H[t] = 0.f;
-      for (int t = 0; t < 6; ++t) { S.b[t] = 0.f; S.x[t] = 0.f; }
-      if (P == 0) {
-        S.status = B200_E_NO_MATCHES;  // ErrorElements: "no point to minimize", ErrorMinimizer.cpp:75-77
-        S.iterate = 0;
-      } else {
-        if (p.minimizer == 0) {
+    if (wid == 0) {
+      // lane 0 forms H and b; the whole warp solves (solve6_warp); lane 0 updates the pose and runs the checkers
+      if (lane == 0) {
+        const double* a = s_red[0];
+        S.P = (int)(a[27] + 0.5);
+        S.wsum = (float)a[28];
+        for (int t = 0; t < 36; ++t) S.H[t] = 0.f;
+        for (int t = 0; t < 6; ++t) { S.b[t] = 0.f; S.x[t] = 0.f; }
+        if (S.P != 0 && p.minimizer == 0) {
           int t = 0;
           for (int c = 0; c < 6; ++c)
             for (int r = 0; r <= c; ++r) {
@@ -420,12 +415,33 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
               S.H[r + 6 * c] = h; S.H[c + 6 * r] = h;
             }
           for (int r = 0; r < 6; ++r) S.b[r] = -(float)a[21 + r];
-          solve6_dev(S.H, S.b, S.x, &S.solve_info);
+        }
+      }
+      __syncwarp();
+      unsigned long long tsub[5] = {0ull, 0ull, 0ull, 0ull, 0ull};
+      if (stamp) tsub[0] = gtimer();
+      bool fast = false;
+      if (S.P != 0 && p.minimizer == 0) fast = solve6_warp(S.H, S.b, S.x, &s_red[1][0]);
+      __syncwarp();
+     if (lane == 0) {
+      const double* a = s_red[0];
+      const int P = S.P;
+      float real[16];
+      eye4(real);
+      if (P == 0) {
+        S.status = B200_E_NO_MATCHES;  // ErrorElements: "no point to minimize", ErrorMinimizer.cpp:75-77
+        S.iterate = 0;
+      } else {
+        if (p.minimizer == 0) {
+          if (fast) S.solve_info = 0;
+          else solve6_dev(S.H, S.b, S.x, &S.solve_info);  // rank-deficient / borderline systems: serial reference path
+          if (stamp) tsub[1] = gtimer();
           p2plane_T_dev(S.x, real);
         } else {
           p2point_from_moments(a, real);
         }
         mul4_dev(real, S.T_iter, S.T_iter);  // ICP.cpp:1213
+        if (stamp) tsub[2] = gtimer();
         // transformationCheckers.check, ICP.cpp:1292-1298
         bool counterHit = false;
         if (p.max_iterations > 0) {
@@ -453,6 +469,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
           if (cv0 != cv0 || cv1 != cv1) { S.status = B200_E_NAN; S.iterate = 0; }
         }
         if (counterHit) { S.iterate = 0; S.maxReached = 1; }
+        if (stamp) tsub[3] = gtimer();
       }
       if (blockIdx.x == 0 && S.iteration < kMaxLog && p.log) {
         IcpLogEntry& e = p.log[S.iteration];
@@ -462,8 +479,13 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
         e.P = P; e.solve_info = S.solve_info;
         ts[5] = gtimer();
         for (int t = 0; t < 6; ++t) e.ts[t] = ts[t];
+        e.sub_ns[0] = (unsigned)(tsub[0] - ts[4]);
+        e.sub_ns[1] = (unsigned)(tsub[1] - tsub[0]);
+        e.sub_ns[2] = (unsigned)(tsub[2] - tsub[1]);
+        e.sub_ns[3] = (unsigned)(tsub[3] - tsub[2]);
       }
       S.iteration += 1;
+     }
     }
     __syncthreads();
     if (!S.iterate) break;

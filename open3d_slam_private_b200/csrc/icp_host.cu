@@ -490,10 +490,11 @@ int b200_icp_get_debug_stats(b200_icp* h, int max_log, double* st, int* n) {
   }
   const int cnt = std::min(std::min(max_log, kMaxLog), h->h_out ? h->h_out->iterations : 0);
   for (int i = 0; i < cnt; ++i) {
-    st[4 * (size_t)i + 0] = (double)tmp[i].dbg_rows;
-    st[4 * (size_t)i + 1] = (double)tmp[i].dbg_cands;
-    st[4 * (size_t)i + 2] = (double)tmp[i].dbg_match_ns_max * 1e-3;
-    st[4 * (size_t)i + 3] = (double)tmp[i].dbg_match_ns_sum * 1e-3 / std::max(1, h->last_grid);
+    st[8 * (size_t)i + 0] = (double)tmp[i].dbg_rows;
+    st[8 * (size_t)i + 1] = (double)tmp[i].dbg_cands;
+    st[8 * (size_t)i + 2] = (double)tmp[i].dbg_match_ns_max * 1e-3;
+    st[8 * (size_t)i + 3] = (double)tmp[i].dbg_match_ns_sum * 1e-3 / std::max(1, h->last_grid);
+    for (int t = 0; t < 4; ++t) st[8 * (size_t)i + 4 + t] = (double)tmp[i].sub_ns[t] * 1e-3;
   }
   *n = cnt;
   delete[] tmp;

@@ -24,6 +24,7 @@ struct IcpLogEntry {
   // debug statistics (only with IcpKernelParams::debug_stats): cell rows resolved, candidates examined, and the
   // slowest / summed per-CTA duration of the matching phase (ns)
   unsigned long long dbg_rows, dbg_cands, dbg_match_ns_max, dbg_match_ns_sum;
+  unsigned sub_ns[4];  // CTA 0 inside "reduce+solve": reduction of partials, 6x6 solve, pose update, checkers
 };
 
 struct IcpDeviceResult {

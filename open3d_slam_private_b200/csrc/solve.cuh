@@ -74,7 +74,7 @@ __device__ __forceinline__ float3 apply_R(const float* R9, float3 n) {
 
 // solvePossiblyUnderdeterminedLinearSystem(A, b, x, false) — PointToPlane.cpp:199-256.
 // info: 0 full rank, 1 rank-deficient minimal-norm, 2 double-SVD fallback.
-__device__ inline void solve6_dev(const float* A, const float* b, float* x, int* info) {
+static __device__ __noinline__ void solve6_dev(const float* A, const float* b, float* x, int* info) {
   const int rank = la::pivqr_rank<float, 6>(A);  // register-resident; the full factorisation only when needed
   double Ad[36], bd[6], xd[6];
   for (int i = 0; i < 36; ++i) Ad[i] = (double)A[i];
@@ -160,6 +160,141 @@ __device__ inline void solve6_dev(const float* A, const float* b, float* x, int*
     for (int i = 0; i < 6; ++i) x[i] = (float)xd[i];
     *info = 2;
   }
+}
+
+// Rank decision of la::pivqr_rank<float, 6> replayed by one warp on a shared-memory work matrix (36 floats): lane j
+// owns column j, rolled loops, same operations per element in the same order => the same pivots and the same rank as
+// Eigen's FullPivHouseholderQR restatement, in compact code. Returns true iff the rank is 6.
+__device__ inline bool pivqr_full_rank6_warp(const float* A, float* Q) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  if (lane < 6)
+    for (int i = 0; i < 6; ++i) Q[i + 6 * lane] = A[i + 6 * lane];
+  __syncwarp();
+  const float prec = FLT_EPSILON * 6.f;
+  float maxpivot = 0.f, minpivot = INFINITY, biggest = 0.f;
+  for (int k = 0; k < 6; ++k) {
+    float big = -1.f;
+    int rb = k, cb = lane;
+    if (lane >= k && lane < 6)
+      for (int i = k; i < 6; ++i) {
+        const float v = fabsf(Q[i + 6 * lane]);
+        if (v > big) { big = v; rb = i; }
+      }
+    for (int o = 4; o > 0; o >>= 1) {
+      const float ob = __shfl_xor_sync(FULL, big, o);
+      const int orb = __shfl_xor_sync(FULL, rb, o), ocb = __shfl_xor_sync(FULL, cb, o);
+      if (ob > big || (ob == big && ocb < cb)) { big = ob; rb = orb; cb = ocb; }
+    }
+    big = __shfl_sync(FULL, big, 0); rb = __shfl_sync(FULL, rb, 0); cb = __shfl_sync(FULL, cb, 0);
+    if (k == 0) biggest = big;
+    if (fabsf(big) <= fabsf(biggest) * prec) return false;
+    if (lane >= k && lane < 6 && rb != k) { const float t = Q[k + 6 * lane]; Q[k + 6 * lane] = Q[rb + 6 * lane]; Q[rb + 6 * lane] = t; }
+    __syncwarp();
+    if (cb != k && lane < 6) { const float t = Q[lane + 6 * k]; Q[lane + 6 * k] = Q[lane + 6 * cb]; Q[lane + 6 * cb] = t; }
+    __syncwarp();
+    float tail = 0.f;
+    for (int i = k + 1; i < 6; ++i) tail += Q[i + 6 * k] * Q[i + 6 * k];
+    const float c0 = Q[k + 6 * k];
+    float beta, tk;
+    const bool tiny = tail <= FLT_MIN;
+    if (tiny) { tk = 0.f; beta = c0; }
+    else {
+      beta = sqrtf(c0 * c0 + tail);
+      if (c0 >= 0.f) beta = -beta;
+      tk = (beta - c0) / beta;
+    }
+    __syncwarp();
+    if (lane > k && lane < 6) Q[lane + 6 * k] = tiny ? 0.f : Q[lane + 6 * k] / (c0 - beta);  // essential part, one entry per lane
+    if (lane == k) Q[k + 6 * k] = beta;
+    __syncwarp();
+    maxpivot = fmaxf(maxpivot, fabsf(beta));
+    minpivot = fminf(minpivot, fabsf(beta));
+    if (k < 5 && tk != 0.f && lane > k && lane < 6) {
+      float tmp = 0.f;
+      for (int i = k + 1; i < 6; ++i) tmp += Q[i + 6 * k] * Q[i + 6 * lane];
+      tmp += Q[k + 6 * lane];
+      Q[k + 6 * lane] -= tk * tmp;
+      for (int i = k + 1; i < 6; ++i) Q[i + 6 * lane] -= tk * Q[i + 6 * k] * tmp;
+    }
+    __syncwarp();
+  }
+  return minpivot > fabsf(maxpivot) * prec;
+}
+
+// Warp-parallel fast path of solve6_dev for the common case (numerically full rank, symmetric positive definite).
+// Deliberately COMPACT code: rolled loops over a shared-memory work matrix. One warp executes this once per
+// iteration, so its cost is dominated by instruction fetch of straight-line code, not by arithmetic: the fully
+// unrolled register version (and the serial reference path) took 7-9 us per iteration, this one well under 2 us.
+//
+// Lanes 0..5 factor A = L D L^T in double (column j on lane j); lanes 8..13 run the SAME instructions on A - s I,
+// s = 8 * (6 eps_f) * trace(A), which is the rank certificate: every diagonal entry of any QR factor satisfies
+// |R_kk| >= sigma_min(A), and the reference's rank threshold is 6 eps_f * max|R_kk| <= 6 eps_f * trace(A) for a
+// symmetric positive semidefinite A; if A - s I is still positive definite then lambda_min(A) > s and
+// FullPivHouseholderQR (PointToPlane.cpp:202-203) finds full rank with an 8x margin. 1/d_k comes from a float seed
+// and three Newton steps in double (IEEE double division/sqrt are long dependent sequences here); against
+// cond(A) ~ 1e4..1e5 the ~1 ulp quotient error is ~1e-11 relative in x, invisible after the cast to float.
+// Returns false (x untouched) when the serial reference routine has to decide: certificate failed, asymmetric input.
+// W: 98 doubles of shared memory. Must be called by all 32 lanes of one warp.
+__device__ inline bool solve6_warp(const float* A, const float* b, float* x, double* W) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int blk = (lane >> 3) & 1, j = lane & 7;   // block 0: A, block 1: A - s I
+  const bool mine = lane < 16 && j < 6;
+  double* M = W + 36 * blk;                          // column-major 6x6, lower triangle used
+  // shift s = 2.8 * (6 eps_f) * cmax, cmax = largest column norm >= max|R_kk| (Householder reflections preserve
+  // column norms): 1x is the reference's threshold, the rest covers the ~eps_f * |A| rounding of a float QR
+  float cn = 0.f;
+  for (int i = 0; i < 6; ++i) { const float t = A[i + 6 * (j < 6 ? j : 0)]; cn += t * t; }
+  for (int o = 4; o > 0; o >>= 1) cn = fmaxf(cn, __shfl_xor_sync(FULL, cn, o));
+  const float cmax = sqrtf(__shfl_sync(FULL, cn, 0));
+  const double sft = (double)(2.8f * 6.f * FLT_EPSILON * cmax);
+  bool good = cmax > 0.f;
+  if (mine) {
+    for (int i = 0; i < 6; ++i) {
+      const double u = (double)A[i + 6 * j], w = (double)A[j + 6 * i];
+      if (fabs(u - w) > 1e-6 * (fabs((double)A[i + 6 * i]) + fabs((double)A[j + 6 * j]))) good = false;
+      M[i + 6 * j] = 0.5 * (u + w) - ((blk == 1 && i == j) ? sft : 0.0);
+    }
+  }
+  __syncwarp();
+  double* rinv = W + 72;  // 6 reciprocals of block 0
+  for (int k = 0; k < 6; ++k) {
+    const double d = M[k + 6 * k];
+    if (!(d > 0.0)) good = false;
+    double rk = (double)(1.0f / (float)d);
+    rk = rk * (2.0 - d * rk);
+    rk = rk * (2.0 - d * rk);
+    rk = rk * (2.0 - d * rk);
+    if (mine && j > k) {  // a(i, j) -= L(i, k) * d_k * L(j, k), i >= j, with column k still holding L * d
+      const double cjk = M[j + 6 * k];
+      for (int i = j; i < 6; ++i) M[i + 6 * j] -= (M[i + 6 * k] * rk) * cjk;
+    }
+    __syncwarp();
+    if (mine && j > k) M[j + 6 * k] *= rk;  // column k becomes L(:, k); one entry per lane
+    if (lane == 0) rinv[k] = rk;
+    __syncwarp();
+  }
+  // block 0 must have factored; block 1 is only the certificate
+  const bool good0 = __all_sync(FULL, good || blk == 1);
+  if (!good0) return false;
+  if (!__all_sync(FULL, good)) {
+    // certificate failed: replay the reference's rank decision exactly (work matrix after the two double blocks)
+    if (!pivqr_full_rank6_warp(A, reinterpret_cast<float*>(W + 80))) return false;
+  }
+  // substitutions on block 0: lane i owns component i
+  double v = (lane < 6) ? (double)b[lane] : 0.0;
+  for (int k = 0; k < 6; ++k) {  // forward, unit L
+    const double yk = __shfl_sync(FULL, v, k);
+    if (lane < 6 && lane > k) v -= W[lane + 6 * k] * yk;
+  }
+  if (lane < 6) v *= rinv[lane];
+  for (int k = 5; k >= 0; --k) {  // backward, L^T
+    const double xk = __shfl_sync(FULL, v, k);
+    if (lane < k) v -= W[k + 6 * lane] * xk;
+  }
+  if (lane < 6) x[lane] = (float)v;
+  return true;
 }
 
 // x -> 4x4 — PointToPlane.cpp:337-381 (6-DOF branch)

@@ -34,4 +34,6 @@ for rep in range(2):
                     np.corrcoef(w[:, 3], w[:, 0])[0, 1], np.corrcoef(w[:, 3], w[:, 1])[0, 1], w[o[-5:]].astype(int).tolist()))
                 print("   fastest 3: %s" % w[o[:3]].astype(int).tolist())
             for row in icp.debug_stats():
-                print("   rows/q %.1f cands/q %.1f match max %.1f us mean %.1f us" % (row[0] / N, row[1] / N, row[2], row[3]))
+                print("   rows/q %.1f cands/q %.1f match max %.1f us mean %.1f us | reduce %.1f solve %.1f update %.1f check %.1f us" % (
+                    row[0] / N, row[1] / N, row[2], row[3], row[4], row[5], row[6], row[7]))
+np.save(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out", "H_log.npy"), icp.log()["H"])
