@@ -1,0 +1,134 @@
+// b200_cloud_registration.hpp — boundary B: a registration backend for open3d_slam's CloudRegistration interface
+// (open3d_slam/include/open3d_slam/CloudRegistration.hpp:19-28; factory src/CloudRegistration.cpp:105-121) backed by
+// the B200 registration core.
+//
+// Header-only and templated so that it compiles without Open3D: in the reference tree
+//   Cloud  = open3d::geometry::PointCloud   (points_, normals_ : std::vector<Eigen::Vector3d>)
+//   Result = open3d::pipelines::registration::RegistrationResult (transformation_, correspondence_set_, fitness_,
+//            inlier_rmse_)
+//   Mat4   = Eigen::Matrix4d (Transform::matrix())
+// and the class below is wrapped by a 10-line subclass of o3d_slam::CloudRegistration. Clouds are
+// converted double -> float exactly like open3dToPointmatcher (open3d_conversions.cpp:57-118).
+//
+// Semantics: the chain run on the device is the libpointmatcher one (1-NN within maxCorrespondenceDistance_, no
+// outlier filter, point-to-plane or point-to-point minimiser, Counter{maxNumIter_} + Differential checkers) — the
+// same linear system Open3D's TransformationEstimationPointToPlane builds (JtJ = sum F F^T, Jtr = sum F r). Open3D's
+// own Euler-angle pose update and relative fitness/RMSE stopping rule (Open3D v0.15.1, not in the reference tree) are
+// a "next" item in DESIGN.md; fitness_ and inlier_rmse_ are computed from the final correspondences as Open3D
+// defines them (#correspondences / #source points, sqrt(mean squared distance)).
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/b200reg.h"
+
+namespace b200o3d {
+
+enum class Kind { PointToPlane, PointToPoint };
+
+template <class Cloud, class Mat4, class Result>
+class RegistrationIcpB200 {
+ public:
+  double maxCorrespondenceDistance_ = 1.0;   // IcpParameters::maxCorrespondenceDistance_ (Parameters.hpp:66-72)
+  int maxNumIter_ = 50;                      // IcpParameters::maxNumIter_
+  int knnNormalEstimation_ = 10;             // IcpParameters::knn_
+  double maxRadiusNormalEstimation_ = 2.0;   // IcpParameters::maxDistanceKnn_
+  Kind kind_ = Kind::PointToPlane;
+  int device_ = 0;
+
+  RegistrationIcpB200() = default;
+  ~RegistrationIcpB200() { b200_icp_destroy(icp_); }
+  RegistrationIcpB200(const RegistrationIcpB200&) = delete;
+  RegistrationIcpB200& operator=(const RegistrationIcpB200&) = delete;
+
+  // CloudRegistration::registerClouds(source, target, init)
+  Result registerClouds(const Cloud& source, const Cloud& target, const Mat4& init) {
+    ensure();
+    std::vector<float> tgt4, tgtn, src4;
+    to_feat4(target.points_, tgt4);
+    const bool hasN = target.normals_.size() == target.points_.size() && !target.normals_.empty();
+    if (kind_ == Kind::PointToPlane && !hasN) throw std::runtime_error("RegistrationIcpB200: target cloud has no normals");
+    if (hasN) to_xyz3(target.normals_, tgtn);
+    to_feat4(source.points_, src4);
+    check(b200_icp_init_reference(icp_, tgt4.data(), hasN ? tgtn.data() : nullptr, (int)target.points_.size()));
+    float Ti[16];
+    for (int j = 0; j < 4; ++j)
+      for (int i = 0; i < 4; ++i) Ti[i + 4 * j] = (float)init(i, j);
+    b200_icp_result r;
+    const int n = (int)source.points_.size();
+    check(b200_icp_compute(icp_, src4.data(), nullptr, n, Ti, &r));
+    Result out;
+    for (int j = 0; j < 4; ++j)
+      for (int i = 0; i < 4; ++i) out.transformation_(i, j) = (double)r.T[i + 4 * j];
+    std::vector<int32_t> ids(n);
+    std::vector<float> d(n), w(n);
+    check(b200_icp_get_matches(icp_, ids.data(), d.data(), w.data()));
+    double s2 = 0.0;
+    out.correspondence_set_.clear();
+    for (int i = 0; i < n; ++i)
+      if (ids[i] >= 0 && w[i] != 0.f) {
+        out.correspondence_set_.emplace_back(i, ids[i]);
+        s2 += (double)d[i];
+      }
+    const size_t c = out.correspondence_set_.size();
+    out.fitness_ = n > 0 ? (double)c / (double)n : 0.0;
+    out.inlier_rmse_ = c > 0 ? std::sqrt(s2 / (double)c) : 0.0;
+    return out;
+  }
+
+  // CloudRegistration::estimateNormalsOrCovariancesIfNeeded (CloudRegistration.cpp:27-46, 67-79): skip when the
+  // cloud has normals; else k-NN normals (hybrid radius = maxRadiusNormalEstimation_), normalised, flipped towards
+  // the origin (OrientNormalsTowardsCameraLocation with the default camera location).
+  void estimateNormalsOrCovariancesIfNeeded(Cloud* cloud) const {
+    if (!cloud || (cloud->normals_.size() == cloud->points_.size() && !cloud->points_.empty())) return;
+    std::vector<float> f4;
+    to_feat4(cloud->points_, f4);
+    const int n = (int)cloud->points_.size();
+    std::vector<float> nrm(3 * (size_t)n);
+    b200_surface_normal_params prm;
+    prm.knn = knnNormalEstimation_; prm.maxDist = (float)maxRadiusNormalEstimation_; prm.epsilon = 0.f;
+    prm.sortEigen = 0; prm.smoothNormals = 0;
+    check(b200_surface_normals(device_, f4.data(), n, &prm, nrm.data(), nullptr, nullptr, nullptr, nullptr, nullptr));
+    cloud->normals_.resize(n);
+    for (int i = 0; i < n; ++i) {
+      double v[3] = {nrm[3 * i], nrm[3 * i + 1], nrm[3 * i + 2]};
+      const double nn = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+      if (nn > 0) { v[0] /= nn; v[1] /= nn; v[2] /= nn; }
+      const auto& p = cloud->points_[i];
+      if (v[0] * (-p[0]) + v[1] * (-p[1]) + v[2] * (-p[2]) < 0) { v[0] = -v[0]; v[1] = -v[1]; v[2] = -v[2]; }
+      cloud->normals_[i][0] = v[0]; cloud->normals_[i][1] = v[1]; cloud->normals_[i][2] = v[2];
+    }
+  }
+
+ private:
+  static void check(int st) {
+    if (st != B200_OK) throw std::runtime_error(std::string("b200: ") + b200_last_error());
+  }
+  template <class V>
+  static void to_feat4(const V& pts, std::vector<float>& out) {
+    out.resize(4 * pts.size());
+    for (size_t i = 0; i < pts.size(); ++i) {
+      out[4 * i] = (float)pts[i][0]; out[4 * i + 1] = (float)pts[i][1]; out[4 * i + 2] = (float)pts[i][2]; out[4 * i + 3] = 1.f;
+    }
+  }
+  template <class V>
+  static void to_xyz3(const V& v, std::vector<float>& out) {
+    out.resize(3 * v.size());
+    for (size_t i = 0; i < v.size(); ++i) { out[3 * i] = (float)v[i][0]; out[3 * i + 1] = (float)v[i][1]; out[3 * i + 2] = (float)v[i][2]; }
+  }
+  void ensure() {
+    if (icp_) return;
+    b200_icp_params p;
+    b200_icp_default_params(&p);
+    p.knn = 1; p.maxDist = (float)maxCorrespondenceDistance_; p.use_trimmed = 0;
+    p.minimizer = kind_ == Kind::PointToPlane ? 0 : 1;
+    p.max_iterations = maxNumIter_;
+    check(b200_icp_create(&icp_, device_, &p));
+  }
+  b200_icp* icp_ = nullptr;
+};
+
+}  // namespace b200o3d

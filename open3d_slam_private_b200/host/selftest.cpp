@@ -1,0 +1,137 @@
+// Self-test of the host-side C++ shims against pm_mirror.h. Without a CUDA device it checks that every module
+// fails loudly with the mapped exception (no CPU fallback); with a device it runs the modules on a small synthetic
+// cloud and checks them against a brute-force computation done right here.
+#include <array>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <random>
+#include <utility>
+
+#include "b200_cloud_registration.hpp"
+#include "b200_pm_modules.hpp"
+#include "pm_mirror.h"
+
+using PM = pmmirror::PM;
+
+static int fails = 0;
+#define EXPECT(c) do { if (!(c)) { std::printf("FAIL %s:%d %s\n", __FILE__, __LINE__, #c); ++fails; } } while (0)
+
+static PM::DataPoints plane_cloud(int n, unsigned seed, float dz, bool normals) {
+  std::mt19937 rng(seed);
+  std::uniform_real_distribution<float> U(-5.f, 5.f), J(-0.01f, 0.01f);
+  PM::DataPoints c;
+  c.features.resize(4, n);
+  for (int i = 0; i < n; ++i) {
+    const float x = U(rng), y = U(rng);
+    c.features(0, i) = x; c.features(1, i) = y;
+    c.features(2, i) = 0.05f * std::sin(x) + 0.03f * y * y * 0.1f + dz + J(rng);
+    c.features(3, i) = 1.f;
+  }
+  if (normals) {
+    PM::Matrix nn(3, n);
+    for (int i = 0; i < n; ++i) {
+      const float x = c.features(0, i), y = c.features(1, i);
+      float v[3] = {-0.05f * std::cos(x), -0.006f * y, 1.f};
+      const float s = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+      for (int d = 0; d < 3; ++d) nn(d, i) = v[d] / s;
+    }
+    c.addDescriptor("normals", nn);
+  }
+  return c;
+}
+
+struct V3 { double v[3]; double& operator[](int i) { return v[i]; } const double& operator[](int i) const { return v[i]; } };
+struct Cloud { std::vector<V3> points_, normals_; };
+struct M4 { double m[16]; double& operator()(int i, int j) { return m[i + 4 * j]; } const double& operator()(int i, int j) const { return m[i + 4 * j]; } };
+struct Result { M4 transformation_; std::vector<std::pair<int, int>> correspondence_set_; double fitness_ = 0, inlier_rmse_ = 0; };
+
+int main() {
+  const int ndev = b200_device_count();
+  std::printf("devices: %d\n", ndev);
+  PM::DataPoints ref = plane_cloud(4000, 1, 0.f, true), read = plane_cloud(1500, 2, 0.08f, false);
+  if (ndev < 1) {
+    // no CPU fallback: every module must throw
+    bool threw = false;
+    try { b200pm::B200KDTreeMatcher<PM> m; m.init(ref); } catch (const std::runtime_error&) { threw = true; }
+    EXPECT(threw);
+    threw = false;
+    try { b200pm::B200ICP<PM> icp; icp.initReference(ref); } catch (const std::runtime_error&) { threw = true; }
+    EXPECT(threw);
+    threw = false;
+    try { b200pm::B200KDTreeMatcher<PM> m({{"knn", "0"}}); } catch (const PM::InvalidParameter&) { threw = true; }
+    EXPECT(threw);
+    std::printf(fails ? "selftest FAILED\n" : "selftest ok (no device: loud failure verified)\n");
+    return fails ? 1 : 0;
+  }
+  // ---- matcher vs brute force (bit-exact: same float arithmetic, ties -> smallest index)
+  b200pm::B200KDTreeMatcher<PM> matcher({{"knn", "3"}, {"maxDist", "0.5"}});
+  matcher.init(ref);
+  PM::Matches m = matcher.findClosests(read);
+  EXPECT(m.ids.rows() == 3 && m.ids.cols() == 1500 && matcher.visitCounter > 0);
+  int bad = 0;
+  for (int i = 0; i < 1500; i += 7) {
+    float bd[3] = {INFINITY, INFINITY, INFINITY};
+    int bi[3] = {-1, -1, -1};
+    for (int j = 0; j < 4000; ++j) {
+      const float dx = read.features(0, i) - ref.features(0, j), dy = read.features(1, i) - ref.features(1, j),
+                  dz = read.features(2, i) - ref.features(2, j);
+      volatile float a = dx * dx, b = dy * dy, c = dz * dz;  // volatile: no FMA contraction
+      volatile float s1 = a + b;
+      const float d = s1 + c;
+      if (d > 0.25f) continue;
+      for (int k = 0; k < 3; ++k)
+        if (d < bd[k] || (d == bd[k] && j < bi[k])) {
+          for (int t = 2; t > k; --t) { bd[t] = bd[t - 1]; bi[t] = bi[t - 1]; }
+          bd[k] = d; bi[k] = j;
+          break;
+        }
+    }
+    for (int k = 0; k < 3; ++k) bad += (m.ids(k, i) != bi[k]) || (m.dists(k, i) != bd[k]);
+  }
+  EXPECT(bad == 0);
+  // ---- outlier filters
+  b200pm::B200TrimmedDistOutlierFilter<PM> trimmed({{"ratio", "0.8"}});
+  PM::OutlierWeights w = trimmed.compute(read, ref, m);
+  long kept = 0, valid = 0;
+  for (int i = 0; i < 1500; ++i)
+    for (int k = 0; k < 3; ++k) { kept += w(k, i) != 0.f; valid += std::isfinite(m.dists(k, i)); }
+  EXPECT(kept > 0 && kept <= valid && kept >= (long)(0.78 * valid));
+  b200pm::B200MaxDistOutlierFilter<PM> maxd({{"maxDist", "0.2"}});
+  PM::OutlierWeights w2 = maxd.compute(read, ref, m);
+  for (int i = 0; i < 1500; i += 11) EXPECT((w2(0, i) != 0.f) == (m.dists(0, i) <= 0.04f));
+  // ---- surface normals
+  b200pm::B200SurfaceNormalDataPointsFilter<PM> sn({{"knn", "10"}, {"keepDensities", "1"}});
+  PM::DataPoints withN = sn.filter(read);
+  EXPECT(withN.descriptorExists("normals") && withN.descriptorExists("densities") && withN.descriptors.rows() == 4);
+  int upright = 0;
+  for (int i = 0; i < 1500; ++i) upright += std::fabs(withN.descriptors(2, i)) > 0.9f;
+  EXPECT(upright > 1400);
+  // ---- whole chain: recovers the 0.08 m offset along z
+  b200pm::B200ICP<PM> icp;
+  icp.prm.maxDist = 0.5f; icp.prm.trimmed_ratio = 0.9f;
+  PM::TransformationParameters T = icp(read, ref);
+  EXPECT(std::fabs(T(2, 3) + 0.08f) < 0.01f && icp.last.iterations > 1);
+  PM::OutlierWeights wl;
+  PM::Matches ml = icp.matches(&wl);
+  EXPECT(ml.ids.cols() == 1500 && wl.cols() == 1500);
+  // ---- boundary B
+  Cloud src, tgt;
+  for (int i = 0; i < 1500; ++i) src.points_.push_back(V3{{read.features(0, i), read.features(1, i), read.features(2, i)}});
+  for (int i = 0; i < 4000; ++i) {
+    tgt.points_.push_back(V3{{ref.features(0, i), ref.features(1, i), ref.features(2, i)}});
+    tgt.normals_.push_back(V3{{ref.descriptors(0, i), ref.descriptors(1, i), ref.descriptors(2, i)}});
+  }
+  b200o3d::RegistrationIcpB200<Cloud, M4, Result> reg;
+  reg.maxCorrespondenceDistance_ = 0.5;
+  M4 I{};
+  for (int i = 0; i < 4; ++i) I(i, i) = 1.0;
+  Result rr = reg.registerClouds(src, tgt, I);
+  EXPECT(std::fabs(rr.transformation_(2, 3) + 0.08) < 0.01 && rr.fitness_ > 0.9 && rr.inlier_rmse_ < 0.1);
+  Cloud bare;
+  bare.points_ = tgt.points_;
+  reg.estimateNormalsOrCovariancesIfNeeded(&bare);
+  EXPECT(bare.normals_.size() == bare.points_.size());
+  std::printf(fails ? "selftest FAILED\n" : "selftest ok (device path)\n");
+  return fails ? 1 : 0;
+}
