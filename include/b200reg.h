@@ -193,8 +193,9 @@ int b200_icp_get_log(b200_icp* icp, int max_log, float* H, float* b, float* x, f
  * 5 whole iteration}] */
 int b200_icp_get_phase_times(b200_icp* icp, int max_log, float* us, int* n);
 /* profiling aid, filled only when the handle was created with env B200_ICP_DEBUG=1 (adds global atomics to the
- * kernel): st[8*i + {0 cell rows resolved, 1 candidates examined, 2 slowest CTA's matching phase (us), 3 mean CTA
- * matching phase (us), 4 reduction of partials, 5 6x6 solve, 6 pose update, 7 checkers (us, CTA 0)}] */
+ * kernel): st[12*i + {0 cell rows resolved, 1 candidates examined, 2 slowest CTA's matching phase (us), 3 mean CTA
+ * matching phase (us), 4 reduction of partials, 5 6x6 solve, 6 pose update, 7 checkers (us, CTA 0), 8 iteration shape (1 single-barrier, 0 general, 2 single-barrier attempt fell back),
+ * 9 bracket candidates, 10 TrimmedDist limit, 11 bracket half-width used by the previous attempt}]. Columns 4-9 are filled without the env switch as well. */
 int b200_icp_get_debug_stats(b200_icp* icp, int max_log, double* st, int* n);
 /* profiling aid (B200_ICP_DEBUG=1): per warp slot of the first iteration {rows, candidates, passes, ns} */
 int b200_icp_get_debug_warps(b200_icp* icp, uint32_t* out4xS, int max_slots, int* n);

@@ -359,7 +359,7 @@ class ICP:
 
     def debug_stats(self, max_log=64):
         """(iterations, 4): rows, candidates, slowest CTA match us, mean CTA match us (needs B200_ICP_DEBUG=1)"""
-        st = np.zeros((max_log, 8), np.float64)
+        st = np.zeros((max_log, 12), np.float64)
         n = C.c_int()
         _check(load().b200_icp_get_debug_stats(self.h, max_log, st.ctypes.data_as(C.POINTER(C.c_double)), C.byref(n)))
         return st[:n.value]

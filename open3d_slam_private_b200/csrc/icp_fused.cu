@@ -11,6 +11,16 @@
 //   T_iter = real * T_iter     (:1213), transformationCheckers.check (:1292)
 // Every CTA redundantly reduces the CTA partials in a fixed order and solves, so all CTAs hold bit-identical
 // state and only grid-wide barriers (no broadcasts) separate the phases.
+//
+// Two iteration shapes. GENERAL: match | barrier | 3-pass radix select of the TrimmedDist quantile (2 more
+// barriers) | weights + H/b partials | barrier | reduce + solve: 4 grid barriers. SINGLE-BARRIER (k = 1,
+// point-to-plane): the quantile moves little between iterations, so the limit is bracketed by
+// [lim_prev (1 - delta), lim_prev (1 + delta)]; during matching every pair is classified as certainly inside (d <= lo,
+// accumulated at once), certainly outside (d > hi) or a candidate (few hundred; d and the pair's linearisation are
+// parked in a per-CTA segment). After ONE barrier every CTA sums the partials and the class counts, checks that the
+// exact rank of Matches::getDistsQuantile falls among the candidates, selects it by counting in shared memory, adds
+// the accepted candidates in a fixed order and solves. If the bracket missed (or no bracket exists yet) the
+// iteration falls through to the general shape, so the result is exact either way.
 #include "icp_kernel.cuh"
 #include "knn.cuh"
 #include "solve.cuh"
@@ -20,6 +30,8 @@
 namespace cg = cooperative_groups;
 
 namespace b200 {
+int icp_cand_segment(int N, int grid);
+size_t icp_cand_capacity(int N);
 namespace {
 
 struct BlockState {
@@ -34,6 +46,10 @@ struct BlockState {
   unsigned sel_bin, sel_rank, sel_total;
   int P, solve_info;
   float wsum;
+  // TrimmedDist bracket predicted from the previous iteration's limit (single-barrier path)
+  int have_bracket, try_fast, path;
+  float lim_prev, delta, lo, hi, dens, step_prev;
+  unsigned limit_bits;
   float H[36], b[6], x[6];
 };
 
@@ -123,6 +139,17 @@ __device__ __forceinline__ double warp_sum(double v) {
   return v;
 }
 
+// Staging tile s_v[value][thread] (kFastVals x kIcpThreads floats). Thread (value = tid / 16, segment = tid % 16)
+// sums its value over the 32 threads of its segment in double, in a fixed (rotated, bank-conflict-free) order.
+__device__ __forceinline__ double role_sum(const float* s_v, int tid) {
+  const int vi = tid >> 4, seg = tid & 15;
+  const float* base = s_v + vi * kIcpThreads + seg * 32;
+  double a = 0.0;
+#pragma unroll 8
+  for (int j = 0; j < 32; ++j) a += (double)base[(j + seg) & 31];
+  return a;
+}
+
 template <int K>
 __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __grid_constant__ IcpKernelParams p) {
   cg::grid_group grid = cg::this_grid();
@@ -130,6 +157,8 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
   __shared__ unsigned s_hist[kHistBins];
   __shared__ double s_red[kWarps][kAccum];
   __shared__ unsigned s_scan[40];
+  __shared__ double s_tot[kAccum];   // grid totals of the 27 H/b terms, pair count, weight sum (+ class counts)
+  extern __shared__ __align__(16) float s_dyn[];   // kFastVals x kIcpThreads staging tile / candidate staging
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int nthreads = gridDim.x * kIcpThreads;
   const int gtid = blockIdx.x * kIcpThreads + tid;
@@ -143,6 +172,8 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     S.rot[0] = quat_from_T(S.T_iter);   // transformationCheckers.init, ICP.cpp:997
     S.tr[0][0] = S.tr[0][1] = S.tr[0][2] = 0.f;
     S.P = 0; S.wsum = 0.f; S.solve_info = 0;
+    S.have_bracket = 0; S.try_fast = 0; S.path = 0; S.lim_prev = 0.f; S.delta = 0.25f; S.lo = 0.f; S.hi = 0.f; S.dens = 0.f; S.step_prev = 0.f;
+    S.limit_bits = 0u;
   }
   __syncthreads();
   unsigned long long visited_total = 0ull;
@@ -155,6 +186,12 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     zero_hist(s_hist);  // includes __syncthreads
     const int par = S.iteration & 1;
     unsigned* gh = p.hist + (size_t)par * 3 * kHistBins;
+    // zero the other parity's histograms for the next iteration: their last readers finished before the barrier
+    // that ended the previous iteration, their next writers start after this iteration's barrier
+    if (p.use_trimmed) {
+      unsigned* gz = p.hist + (size_t)(par ^ 1) * 3 * kHistBins;
+      for (int b = gtid; b < 3 * kHistBins; b += nthreads) gz[b] = 0u;
+    }
 
     // ---------------- phase 1: transform + match ----------------
     unsigned dbg_rows = 0, dbg_cands = 0;
@@ -164,8 +201,15 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     // queries was the tail every other warp waited for at the grid barrier. Warp-uniform trip count: the k = 1 search
     // is a warp collective.
     const int nslots = (p.N + 31) >> 5;
-    for (int slot = gtid >> 5; slot < nslots; slot += nthreads >> 5) {
-      const int i = lane * nslots + (int)(((unsigned)slot + (unsigned)lane * 97u) % (unsigned)nslots);
+    const int rounds = (nslots + (nthreads >> 5) - 1) / (nthreads >> 5);  // grid-uniform trip count
+    // single-barrier shape for this iteration? (needs the previous limit when TrimmedDist is in the chain)
+    const bool fast = (K == 1) && p.fast_path && p.minimizer == 0 && (!p.use_trimmed || (S.have_bracket && S.try_fast));
+    const float br_lo = p.use_trimmed ? S.lo : INFINITY, br_hi = p.use_trimmed ? S.hi : INFINITY;
+    double role_acc = 0.0;    // thread (value v = tid / 16, segment = tid % 16) sums value v over 32 threads
+    unsigned cand_base = 0u;  // candidates this CTA has parked so far
+    for (int round = 0; round < rounds; ++round) {
+      const int slot = (gtid >> 5) + round * (nthreads >> 5);
+      const int i = slot < nslots ? lane * nslots + (int)(((unsigned)slot + (unsigned)lane * 97u) % (unsigned)nslots) : p.N;
       const bool in = i < p.N;
       const float4 q = in ? apply_T(S.Tc, __ldg(&p.reading[i])) : make_float4(0.f, 0.f, 0.f, 1.f);
       unsigned vis = 0;
@@ -190,6 +234,90 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
         if (in) {
           p.ids[i] = bid; p.dists[i] = bd; p.spos[i] = bsp;
           if (p.use_trimmed && bd != INFINITY) atomicAdd(&s_hist[(__float_as_uint(bd) >> 20) & 0x7ffu], 1u);
+        }
+        if (fast) {
+          // weight factors that do not depend on the quantile, pair linearisation, class w.r.t. the bracket
+          float F[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, dot = 0.f, w_other = 0.f, w = 0.f;
+          unsigned is_cand = 0u;
+          float c_valid = 0.f, c_below = 0.f;
+          if (in) {
+            const bool valid = bd != INFINITY;
+            const bool any = p.use_trimmed || p.use_maxdist || p.use_sn;
+            w_other = any ? 1.f : (valid ? 1.f : 0.f);           // OutlierFilter.cpp:66-99
+            if (p.use_maxdist) w_other *= (bd <= p.maxdist_lim2) ? 1.f : 0.f;
+            float4 r4 = make_float4(0.f, 0.f, 0.f, 0.f), n4 = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (bsp >= 0) {
+              r4 = __ldg(&p.g.pts[bsp]);
+              if (p.g.nrm) n4 = __ldg(&p.g.nrm[bsp]);
+            }
+            if (p.use_sn && p.reading_n && p.g.nrm) {
+              if (bsp < 0) w_other = 0.f;
+              else {
+                const float4 rn = __ldg(&p.reading_n[i]);
+                const float3 rr = apply_R(S.R9, make_float3(rn.x, rn.y, rn.z));
+                float a3[3] = {rr.x, rr.y, rr.z}, qn[3], nv[3] = {n4.x, n4.y, n4.z}, no[3];
+                normalized3_dev(a3, qn);
+                normalized3_dev(nv, no);
+                float dotn = __fmul_rn(qn[0], no[0]);
+                dotn = __fadd_rn(dotn, __fmul_rn(qn[1], no[1]));
+                dotn = __fadd_rn(dotn, __fmul_rn(qn[2], no[2]));
+                w_other *= (dotn < p.sn_cos) ? 0.f : 1.f;
+              }
+            }
+            // crossProduct (ErrorMinimizer.cpp:376-378) and calculateOptimizationHessian (ICP.cpp:1527-1565)
+            F[0] = __fsub_rn(__fmul_rn(q.y, n4.z), __fmul_rn(q.z, n4.y));
+            F[1] = __fsub_rn(__fmul_rn(q.z, n4.x), __fmul_rn(q.x, n4.z));
+            F[2] = __fsub_rn(__fmul_rn(q.x, n4.y), __fmul_rn(q.y, n4.x));
+            F[3] = n4.x; F[4] = n4.y; F[5] = n4.z;
+            dot = __fmul_rn(__fsub_rn(q.x, r4.x), n4.x);
+            dot = __fadd_rn(dot, __fmul_rn(__fsub_rn(q.y, r4.y), n4.y));
+            dot = __fadd_rn(dot, __fmul_rn(__fsub_rn(q.z, r4.z), n4.z));
+            float trim = 1.f;
+            if (p.use_trimmed) {
+              if (!valid) trim = 0.f;
+              else {
+                c_valid = 1.f;
+                if (bd <= br_lo) c_below = 1.f;
+                else if (bd <= br_hi) { is_cand = 1u; trim = 0.f; }   // decided after the barrier
+                else trim = 0.f;
+              }
+            }
+            w = w_other * trim;
+            if (!is_cand) p.weights[i] = w;
+            if (!valid) w = 0.f;   // ErrorElements keeps pairs with a valid dist and a non-zero weight
+          }
+          // park the candidates of this round in the CTA's segment, in thread order (deterministic)
+          if (p.use_trimmed) {
+            unsigned tot;
+            const unsigned pos = block_excl_scan(is_cand, s_scan, tot);
+            if (is_cand) {
+              const size_t ci = (size_t)blockIdx.x * p.cand_seg + cand_base + pos;
+              p.cand_d[ci] = bd; p.cand_q[ci] = i;
+              p.cand_rec[2 * ci] = make_float4(F[0], F[1], F[2], F[3]);
+              p.cand_rec[2 * ci + 1] = make_float4(F[4], F[5], dot, w_other);
+            }
+            cand_base += tot;
+          }
+          // stage the 32 values of this thread, then sum them per role in double (fixed order)
+          {
+            float* col = s_dyn + tid;
+            const bool kept = w != 0.f;
+            int t = 0;
+#pragma unroll
+            for (int c = 0; c < 6; ++c)
+#pragma unroll
+              for (int a = 0; a <= c; ++a) { col[t * kIcpThreads] = kept ? __fmul_rn(__fmul_rn(w, F[a]), F[c]) : 0.f; ++t; }
+#pragma unroll
+            for (int a = 0; a < 6; ++a) col[(21 + a) * kIcpThreads] = kept ? __fmul_rn(__fmul_rn(w, F[a]), dot) : 0.f;
+            col[27 * kIcpThreads] = kept ? 1.f : 0.f;
+            col[28 * kIcpThreads] = kept ? w : 0.f;
+            col[29 * kIcpThreads] = is_cand ? 1.f : 0.f;
+            col[30 * kIcpThreads] = c_valid;
+            col[31 * kIcpThreads] = c_below;
+          }
+          __syncthreads();
+          role_acc += role_sum(s_dyn, tid);
+          __syncthreads();
         }
       } else if (in) {
         KList<K> L;
@@ -220,9 +348,158 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
       }
     }
 
-    // ---------------- phase 2: TrimmedDist quantile by 3-pass radix select ----------------
-    if (stamp) ts[1] = gtimer();
     float limit = INFINITY;
+    bool have_totals = false;
+    int n_cand_seen = 0;
+    // ---------------- single-barrier shape: partials + class counts -> barrier -> resolve the bracket ----------------
+    if (fast) {
+      double* red = &s_red[0][0];  // kFastVals x 16 segment sums, index = value * 16 + segment = tid
+      red[tid] = role_acc;
+      __syncthreads();
+      if (tid < kFastVals) {
+        double t = 0.0;
+        for (int sg = 0; sg < 16; ++sg) t += red[tid * 16 + sg];
+        __stcg(&p.partials[(size_t)blockIdx.x * kAccum + tid], t);
+      }
+      if (stamp) ts[1] = gtimer();
+      grid.sync();
+      if (stamp) ts[2] = gtimer();
+      {  // fixed-order sum of the CTA partials (same order in every CTA)
+        const int c = tid & (kAccum - 1), slice = tid / kAccum;
+        constexpr int kSlices = kIcpThreads / kAccum;
+        double sacc = 0.0;
+        for (unsigned b = slice; b < gridDim.x; b += kSlices) sacc += __ldcg(&p.partials[(size_t)b * kAccum + c]);
+        red[slice * kAccum + c] = sacc;
+        __syncthreads();
+        if (tid < kAccum) {
+          double t = 0.0;
+          for (int sl = 0; sl < kSlices; ++sl) t += red[sl * kAccum + tid];
+          s_tot[tid] = t;
+        }
+        __syncthreads();
+      }
+      bool ok = true;
+      unsigned r_in = 0u;
+      const unsigned n_cand = (unsigned)(s_tot[29] + 0.5), n_valid = (unsigned)(s_tot[30] + 0.5),
+                     n_below = (unsigned)(s_tot[31] + 0.5);
+      n_cand_seen = (int)n_cand;
+      if (p.use_trimmed) {
+        if (n_valid == 0u) {  // ConvergenceError("No matches available..."), Matches.cpp:75-76
+          if (tid == 0) { S.status = B200_E_NO_MATCHES; S.iterate = 0; }
+          __syncthreads();
+          break;
+        }
+        // Matches::getDistsQuantile, Matches.cpp:82-86: index = (size_t)(float(n_valid) * ratio), max if ratio == 1
+        unsigned rank = n_valid - 1u;
+        if (p.trimmed_ratio != 1.0f) {
+          rank = (unsigned)__fmul_rn((float)n_valid, p.trimmed_ratio);
+          if (rank > n_valid - 1u) rank = n_valid - 1u;
+        }
+        ok = rank >= n_below && (rank - n_below) < n_cand && n_cand <= (unsigned)kCandCap;
+        r_in = rank - n_below;
+      }
+      if (ok) {
+        if (p.use_trimmed) {
+          float* s_cd = s_dyn + kFastVals * kIcpThreads;              // candidate distances (kCandCap)
+          int* s_ci = reinterpret_cast<int*>(s_cd + kCandCap);         // their positions in the global segments
+          // compact numbering of the parked candidates: offsets of the CTA segments by a block scan, then every thread
+          // resolves its candidates' segment by bisection (all loads of a round are independent)
+          unsigned* s_off = reinterpret_cast<unsigned*>(s_hist);   // the level-0 histogram is not needed any more
+          const unsigned nb = tid < (int)gridDim.x ? (unsigned)(__ldcg(&p.partials[(size_t)tid * kAccum + 29]) + 0.5) : 0u;
+          unsigned tot;
+          const unsigned off = block_excl_scan(nb, s_scan, tot);
+          s_off[tid] = off;
+          if (tid == 0) s_off[kIcpThreads] = tot;
+          __syncthreads();
+          for (unsigned c = tid; c < n_cand; c += kIcpThreads) {
+            int lo_b = 0, hi_b = (int)gridDim.x - 1;   // last segment whose offset is <= c
+            while (lo_b < hi_b) {
+              const int mid = (lo_b + hi_b + 1) >> 1;
+              if (s_off[mid] <= c) lo_b = mid; else hi_b = mid - 1;
+            }
+            const int ci = lo_b * p.cand_seg + (int)(c - s_off[lo_b]);
+            s_cd[c] = __ldcg(&p.cand_d[ci]);
+            s_ci[c] = ci;
+          }
+          __syncthreads();
+          // the r_in-th smallest candidate: radix select, 9 bits per pass, on key = bits(d) - bits(lo) (monotone for
+          // positive floats; the bracket is narrow, so 2-3 passes)
+          {
+            unsigned* bins = reinterpret_cast<unsigned*>(red);  // 512 counters, one per thread
+            const unsigned base_bits = __float_as_uint(br_lo);
+            const unsigned range = __float_as_uint(br_hi) - base_bits;
+            const int nbits = 32 - __clz((int)(range | 1u));
+            unsigned prefix = 0u, mask = 0u, rank = r_in;
+            int shift = nbits > 9 ? nbits - 9 : 0;
+            while (true) {
+              bins[tid] = 0u;
+              __syncthreads();
+              for (unsigned c = tid; c < n_cand; c += kIcpThreads) {
+                const unsigned key = __float_as_uint(s_cd[c]) - base_bits;
+                if ((key & mask) == prefix) atomicAdd(&bins[(key >> shift) & 511u], 1u);
+              }
+              __syncthreads();
+              const unsigned cnt = bins[tid];
+              unsigned tot2;
+              const unsigned ex = block_excl_scan(cnt, s_scan, tot2);
+              if (rank >= ex && rank < ex + cnt) { S.sel_bin = (unsigned)tid; S.sel_rank = rank - ex; }
+              __syncthreads();
+              prefix |= S.sel_bin << shift;
+              mask |= 511u << shift;
+              rank = S.sel_rank;
+              if (shift == 0) break;
+              shift = shift > 9 ? shift - 9 : 0;
+            }
+            if (tid == 0) S.limit_bits = base_bits + prefix;
+            __syncthreads();
+          }
+          limit = __uint_as_float(S.limit_bits);
+          // add the accepted candidates (fixed order: candidate c is staged by thread c mod 512)
+          double acc2 = 0.0;
+          for (unsigned c0 = 0; c0 < n_cand; c0 += kIcpThreads) {
+            const unsigned c = c0 + tid;
+            float F[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, dot = 0.f, w = 0.f;
+            if (c < n_cand) {
+              const int ci = s_ci[c];
+              const float4 ra = __ldcg(&p.cand_rec[2 * (size_t)ci]), rb = __ldcg(&p.cand_rec[2 * (size_t)ci + 1]);
+              F[0] = ra.x; F[1] = ra.y; F[2] = ra.z; F[3] = ra.w; F[4] = rb.x; F[5] = rb.y; dot = rb.z;
+              w = (s_cd[c] <= limit) ? rb.w : 0.f;
+              if (blockIdx.x == 0) p.weights[__ldcg(&p.cand_q[ci])] = w;
+            }
+            float* col = s_dyn + tid;
+            const bool kept = w != 0.f;
+            int t = 0;
+#pragma unroll
+            for (int cc = 0; cc < 6; ++cc)
+#pragma unroll
+              for (int a = 0; a <= cc; ++a) { col[t * kIcpThreads] = kept ? __fmul_rn(__fmul_rn(w, F[a]), F[cc]) : 0.f; ++t; }
+#pragma unroll
+            for (int a = 0; a < 6; ++a) col[(21 + a) * kIcpThreads] = kept ? __fmul_rn(__fmul_rn(w, F[a]), dot) : 0.f;
+            col[27 * kIcpThreads] = kept ? 1.f : 0.f;
+            col[28 * kIcpThreads] = kept ? w : 0.f;
+            col[29 * kIcpThreads] = 0.f; col[30 * kIcpThreads] = 0.f; col[31 * kIcpThreads] = 0.f;
+            __syncthreads();
+            acc2 += role_sum(s_dyn, tid);
+            __syncthreads();
+          }
+          red[tid] = acc2;
+          __syncthreads();
+          if (tid < 29) {
+            double t = 0.0;
+            for (int sg = 0; sg < 16; ++sg) t += red[tid * 16 + sg];
+            s_tot[tid] += t;
+          }
+          __syncthreads();
+        }
+        have_totals = true;
+        if (stamp) { ts[3] = gtimer(); ts[4] = ts[3]; }
+      }
+      if (tid == 0) S.path = ok ? 1 : 2;
+    } else if (tid == 0) S.path = 0;
+
+    if (!have_totals) {
+    // ---------------- phase 2: TrimmedDist quantile by 3-pass radix select ----------------
+    if (stamp && !fast) ts[1] = gtimer();
     if (p.use_trimmed) {
       flush_hist(s_hist, gh);
       grid.sync();
@@ -260,11 +537,6 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
       limit = __uint_as_float((pre << 9) | S.sel_bin);
     }
     if (stamp) ts[2] = gtimer();
-    // zero the other parity's histograms for the next iteration (their last readers finished an iteration ago)
-    {
-      unsigned* gz = p.hist + (size_t)(par ^ 1) * 3 * kHistBins;
-      for (int b = gtid; b < 3 * kHistBins; b += nthreads) gz[b] = 0u;
-    }
 
     // ---------------- phase 3: weights + linearisation, reduced to one partial per CTA ----------------
     for (int t = tid; t < kWarps * kAccum; t += kIcpThreads) (&s_red[0][0])[t] = 0.0;
@@ -395,14 +667,15 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
       if (tid < kAccum) {
         double t = 0.0;
         for (int sl = 0; sl < kSlices; ++sl) t += s_red[sl][tid];
-        s_red[0][tid] = t;
+        s_tot[tid] = t;
       }
     }
+    }  // !have_totals
     __syncthreads();
     if (wid == 0) {
       // lane 0 forms H and b; the whole warp solves (solve6_warp); lane 0 updates the pose and runs the checkers
       if (lane == 0) {
-        const double* a = s_red[0];
+        const double* a = s_tot;
         S.P = (int)(a[27] + 0.5);
         S.wsum = (float)a[28];
         for (int t = 0; t < 36; ++t) S.H[t] = 0.f;
@@ -424,7 +697,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
       if (S.P != 0 && p.minimizer == 0) fast = solve6_warp(S.H, S.b, S.x, &s_red[1][0]);
       __syncwarp();
      if (lane == 0) {
-      const double* a = s_red[0];
+      const double* a = s_tot;
       const int P = S.P;
       float real[16];
       eye4(real);
@@ -476,13 +749,33 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
         for (int t = 0; t < 36; ++t) e.H[t] = S.H[t];
         for (int t = 0; t < 6; ++t) { e.b[t] = S.b[t]; e.x[t] = S.x[t]; }
         for (int t = 0; t < 16; ++t) e.T_iter[t] = S.T_iter[t];
-        e.P = P; e.solve_info = S.solve_info;
+        e.P = P; e.solve_info = S.solve_info; e.path = S.path; e.n_cand = n_cand_seen; e.limit = limit; e.delta = S.delta;
         ts[5] = gtimer();
         for (int t = 0; t < 6; ++t) e.ts[t] = ts[t];
         e.sub_ns[0] = (unsigned)(tsub[0] - ts[4]);
         e.sub_ns[1] = (unsigned)(tsub[1] - tsub[0]);
         e.sub_ns[2] = (unsigned)(tsub[2] - tsub[1]);
         e.sub_ns[3] = (unsigned)(tsub[3] - tsub[2]);
+      }
+      if (p.use_trimmed) {
+        // bracket for the next iteration: wide enough for the movement just seen (4x), narrow enough to keep the
+        // candidate set at a few hundred; if both cannot be had the next iteration takes the general shape at once
+        const float rel = S.have_bracket ? fabsf(limit - S.lim_prev) / S.lim_prev : 1.f;
+        if (S.path != 0 && n_cand_seen > 0) S.dens = (float)n_cand_seen / S.delta;   // candidates per unit of delta
+        else if (S.dens == 0.f) S.dens = 0.5f * (float)p.N * (float)p.k;
+        const float dmax = fminf(1200.f / S.dens, 0.25f);
+        // predicted movement of the limit: what was just seen, scaled by how fast the pose updates are shrinking
+        float step = 0.f;
+        for (int t = 0; t < 6; ++t) step += S.x[t] * S.x[t];
+        step = sqrtf(step);
+        const float shrink = (S.step_prev > 0.f) ? fminf(step / S.step_prev, 1.f) : 1.f;
+        S.step_prev = step;
+        S.try_fast = (2.f * rel * shrink <= dmax) ? 1 : 0;
+        S.delta = dmax;
+        S.lim_prev = limit;
+        S.have_bracket = (limit > 0.f && limit < INFINITY) ? 1 : 0;
+        S.lo = limit * (1.f - dmax);
+        S.hi = limit * (1.f + dmax);
       }
       S.iteration += 1;
      }
@@ -522,7 +815,8 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
 template <int K>
 int launch_k(const IcpKernelParams& p, int device, cudaStream_t s, int* grid_out) {
   int per_sm = 0, sms = 0;
-  B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, icp_persistent_kernel<K>, kIcpThreads, 0));
+  B200_CUDA(cudaFuncSetAttribute(icp_persistent_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kIcpDynSmem));
+  B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, icp_persistent_kernel<K>, kIcpThreads, kIcpDynSmem));
   B200_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
   if (per_sm < 1) { set_error("persistent ICP kernel does not fit on an SM"); return B200_E_CUDA; }
   int grid = per_sm * sms;
@@ -530,13 +824,24 @@ int launch_k(const IcpKernelParams& p, int device, cudaStream_t s, int* grid_out
   const int need = std::max(1, (p.N + kIcpThreads - 1) / kIcpThreads);
   grid = std::min(grid, need);
   IcpKernelParams pc = p;
+  pc.cand_seg = icp_cand_segment(p.N, grid);
+  if (grid > kIcpThreads || (size_t)grid * (size_t)pc.cand_seg > icp_cand_capacity(p.N)) pc.fast_path = 0;
   void* args[] = {(void*)&pc};
-  B200_CUDA(cudaLaunchCooperativeKernel((void*)icp_persistent_kernel<K>, dim3(grid), dim3(kIcpThreads), args, 0, s));
+  B200_CUDA(cudaLaunchCooperativeKernel((void*)icp_persistent_kernel<K>, dim3(grid), dim3(kIcpThreads), args,
+                                        kIcpDynSmem, s));
   if (grid_out) *grid_out = grid;
   return B200_OK;
 }
 
 }  // namespace
+
+// candidates one CTA can park: every query it owns (rounds x threads)
+int icp_cand_segment(int N, int grid) {
+  const int nslots = (N + 31) / 32, warps = grid * (kIcpThreads / 32);
+  const int rounds = (nslots + warps - 1) / warps;
+  return rounds * kIcpThreads;
+}
+size_t icp_cand_capacity(int N) { return (size_t)N + (size_t)kIcpThreads * 1024; }
 
 size_t icp_partials_capacity(int device) {
   int sms = 148;

@@ -109,6 +109,9 @@ struct b200_icp {
   int *d_ids = nullptr, *d_spos = nullptr;
   float *d_dists = nullptr, *d_w = nullptr;
   size_t cap_work = 0;
+  float* d_cand_d = nullptr; int* d_cand_q = nullptr; float4* d_cand_rec = nullptr;
+  size_t cap_cand = 0;
+  int fast_path = 1;  // env B200_ICP_FAST=0 forces the general iteration
   unsigned* d_hist = nullptr;
   double *d_partials = nullptr, *d_meanpart = nullptr;
   IcpDeviceResult* d_out = nullptr;
@@ -172,6 +175,16 @@ int icp_ensure_reading(b200_icp* h, int N, bool normals) {
     B200_CUDA(cudaMalloc(&h->d_w, need * sizeof(float)));
     h->cap_work = need;
   }
+  const size_t cneed = icp_cand_capacity(N);
+  if (cneed > h->cap_cand) {
+    cudaFree(h->d_cand_d); cudaFree(h->d_cand_q); cudaFree(h->d_cand_rec);
+    h->d_cand_d = nullptr; h->d_cand_q = nullptr; h->d_cand_rec = nullptr;
+    h->cap_cand = 0;
+    B200_CUDA(cudaMalloc(&h->d_cand_d, cneed * sizeof(float)));
+    B200_CUDA(cudaMalloc(&h->d_cand_q, cneed * sizeof(int)));
+    B200_CUDA(cudaMalloc(&h->d_cand_rec, cneed * 2 * sizeof(float4)));
+    h->cap_cand = cneed;
+  }
   (void)normals;
   return B200_OK;
 }
@@ -226,6 +239,8 @@ int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool tim
   p.max_iterations = h->prm.max_iterations; p.use_differential = h->prm.use_differential;
   p.min_rot = h->prm.min_diff_rot; p.min_trans = h->prm.min_diff_trans; p.smooth = h->prm.smooth_length;
   p.ids = h->d_ids; p.dists = h->d_dists; p.spos = h->d_spos; p.weights = h->d_w;
+  p.cand_d = h->d_cand_d; p.cand_q = h->d_cand_q; p.cand_rec = h->d_cand_rec; p.cand_seg = 0;
+  p.fast_path = (h->fast_path && h->prm.knn == 1) ? 1 : 0;
   p.debug_stats = h->debug_stats;
   p.dbg_warp = nullptr;
   if (h->debug_stats) {
@@ -325,6 +340,7 @@ int b200_icp_create(b200_icp** out, int device, const b200_icp_params* prm) {
   h->device = device;
   h->prm = *prm;
   { const char* e = getenv("B200_ICP_DEBUG"); h->debug_stats = (e && e[0] == '1') ? 1 : 0; }
+  { const char* e = getenv("B200_ICP_FAST"); h->fast_path = (e && e[0] == '0') ? 0 : 1; }
   h->map.device = device;
   int st = B200_OK;
   if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess)
@@ -343,6 +359,7 @@ void b200_icp_destroy(b200_icp* h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     cudaFree(h->d_raw); cudaFree(h->d_raw_n); cudaFree(h->d_read); cudaFree(h->d_read_n); cudaFree(h->d_stage3);
     cudaFree(h->d_ids); cudaFree(h->d_spos); cudaFree(h->d_dists); cudaFree(h->d_w);
+    cudaFree(h->d_cand_d); cudaFree(h->d_cand_q); cudaFree(h->d_cand_rec);
     cudaFree(h->d_hist); cudaFree(h->d_partials); cudaFree(h->d_meanpart); cudaFree(h->d_out); cudaFree(h->d_log);
     cudaFree(h->d_frames); cudaFree(h->d_Tinit); cudaFree(h->d_flush); cudaFree(h->d_dbg_warp);
     cudaFreeHost(h->h_out); cudaFreeHost(h->h_frames); cudaFreeHost(h->h_Tinit);
@@ -490,11 +507,15 @@ int b200_icp_get_debug_stats(b200_icp* h, int max_log, double* st, int* n) {
   }
   const int cnt = std::min(std::min(max_log, kMaxLog), h->h_out ? h->h_out->iterations : 0);
   for (int i = 0; i < cnt; ++i) {
-    st[8 * (size_t)i + 0] = (double)tmp[i].dbg_rows;
-    st[8 * (size_t)i + 1] = (double)tmp[i].dbg_cands;
-    st[8 * (size_t)i + 2] = (double)tmp[i].dbg_match_ns_max * 1e-3;
-    st[8 * (size_t)i + 3] = (double)tmp[i].dbg_match_ns_sum * 1e-3 / std::max(1, h->last_grid);
-    for (int t = 0; t < 4; ++t) st[8 * (size_t)i + 4 + t] = (double)tmp[i].sub_ns[t] * 1e-3;
+    st[12 * (size_t)i + 0] = (double)tmp[i].dbg_rows;
+    st[12 * (size_t)i + 1] = (double)tmp[i].dbg_cands;
+    st[12 * (size_t)i + 2] = (double)tmp[i].dbg_match_ns_max * 1e-3;
+    st[12 * (size_t)i + 3] = (double)tmp[i].dbg_match_ns_sum * 1e-3 / std::max(1, h->last_grid);
+    for (int t = 0; t < 4; ++t) st[12 * (size_t)i + 4 + t] = (double)tmp[i].sub_ns[t] * 1e-3;
+    st[12 * (size_t)i + 8] = (double)tmp[i].path;
+    st[12 * (size_t)i + 9] = (double)tmp[i].n_cand;
+    st[12 * (size_t)i + 10] = (double)tmp[i].limit;
+    st[12 * (size_t)i + 11] = (double)tmp[i].delta;
   }
   *n = cnt;
   delete[] tmp;

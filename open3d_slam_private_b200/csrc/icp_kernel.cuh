@@ -9,6 +9,10 @@ constexpr int kHistBins = 2048;        // radix-select bins per pass (11 + 11 + 
 constexpr int kAccum = 32;             // doubles per CTA partial (29 used)
 constexpr int kMaxHist = 64;           // ring of past poses kept for DifferentialTransformationChecker
 constexpr int kMaxLog = 64;            // per-iteration trace capacity
+constexpr int kFastVals = 32;          // values reduced per pair on the single-barrier path (27 H/b + 5 counters)
+constexpr int kCandCap = 2048;         // bracket candidates the single-barrier path resolves in shared memory
+// 64 KiB staging tile + candidate distances and positions
+constexpr size_t kIcpDynSmem = (size_t)kFastVals * kIcpThreads * sizeof(float) + (size_t)kCandCap * 8;
 
 struct IcpLogEntry {
   float H[36];
@@ -17,13 +21,15 @@ struct IcpLogEntry {
   float T_iter[16];
   int P;
   int solve_info;
-  int pad[2];
+  int path;        // 1: single-barrier iteration, 0: general iteration, 2: single-barrier attempt fell back
+  int n_cand;      // bracket candidates of the attempt
   // %globaltimer (ns) seen by thread 0 of CTA 0: iteration start, own matching done, trimmed limit known,
   // own linearisation done, all partials visible, solve + checks done
   unsigned long long ts[6];
   // debug statistics (only with IcpKernelParams::debug_stats): cell rows resolved, candidates examined, and the
   // slowest / summed per-CTA duration of the matching phase (ns)
   unsigned long long dbg_rows, dbg_cands, dbg_match_ns_max, dbg_match_ns_sum;
+  float limit, delta;  // TrimmedDist limit of this iteration, bracket half-width prepared for the next
   unsigned sub_ns[4];  // CTA 0 inside "reduce+solve": reduction of partials, 6x6 solve, pose update, checkers
 };
 
@@ -56,6 +62,10 @@ struct IcpKernelParams {
   double* partials;         // [gridDim.x][kAccum]
   IcpDeviceResult* out;
   IcpLogEntry* log;         // kMaxLog entries
+  // single-barrier iteration (see icp_fused.cu): per-CTA segments of TrimmedDist bracket candidates
+  float* cand_d; int* cand_q; float4* cand_rec;   // capacity gridDim * cand_seg (cand_rec: 2 float4 per candidate)
+  int cand_seg;             // entries per CTA segment (set by the launcher)
+  int fast_path;            // 0: always run the general 4-barrier iteration
   unsigned* dbg_warp;       // debug: per warp slot of iteration 0: {rows, candidates, passes, ns} (nullable)
   int debug_stats;          // collect IcpLogEntry::dbg_* (adds global atomics; profiling aid only)
   const float* frames;      // 3 x 16 floats: T_refIn_refMean, T_refMean_readMean, T_readIn_readMean
@@ -64,6 +74,8 @@ struct IcpKernelParams {
 // launches the persistent kernel for capacity K in {1, 4, 16} (K >= p.k); cooperative launch, grid chosen from
 // the occupancy calculator. Returns the grid size used through *grid_out.
 int launch_icp_kernel(const IcpKernelParams& p, int device, cudaStream_t s, int* grid_out);
+// entries of the cand_* arrays the launch may use for N queries (upper bound over all grids)
+size_t icp_cand_capacity(int N);
 // how many doubles of `partials` the launch needs
 size_t icp_partials_capacity(int device);
 

@@ -23,6 +23,9 @@ for rep in range(2):
         for row in pt:
             print("  " + " ".join("%7.1f" % v for v in row))
         print("  sum " + " ".join("%7.1f" % v for v in pt.sum(0)))
+        ds = icp.debug_stats()
+        print("  shape/cands: " + " ".join("%d/%d" % (r[8], r[9]) for r in ds))
+        print("  limit: " + " ".join("%.5f" % r[10] for r in ds) + " | delta: " + " ".join("%.4f" % r[11] for r in ds))
         if os.environ.get("B200_ICP_DEBUG") == "1":
             w = icp.debug_warps().astype(np.float64)
             if len(w):
