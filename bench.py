@@ -37,7 +37,7 @@ METRIC = "icp_registrations_per_s_128k_scan_vs_5M_map"
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--steps", type=int, default=1000)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--map-points", type=int, default=5_000_000)
@@ -82,9 +82,13 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
 
-    def stop(self):
+    def mark(self):
+        return time.time()
+
+    def stop(self, t0=None, t1=None):
+        """summary over the samples taken in [t0, t1] (the timed region); all samples when none fall inside"""
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -94,7 +98,11 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, pw, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        inside = [r for (t, r) in self.rows if t0 is not None and t0 - 0.05 <= t <= t1 + 0.15]
+        window = "timed region"
+        if not inside:
+            inside, window = [r for (_, r) in self.rows], "whole run (timed region shorter than the sampling period)"
+        for r in inside:
             if len(r) < 8:
                 continue
             try:
@@ -105,7 +113,8 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(n)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "window": window,
+                "reasons": sorted(reasons)}
 
 
 def dist_env():
@@ -221,12 +230,13 @@ def run_b200(args):
     mine = lambda i: host_scans[(rank + i * world) % len(host_scans)]
     flush = (lambda: None) if args.no_flush else icp.flush_l2
 
+    clk = ClockSampler(local) if rank == 0 else None   # started early: nvidia-smi needs a moment to come up
     for i in range(args.warmup):
         a, Ti, _ = mine(i)
         icp.compute(a, None, Ti)
     # ---- value: everything resident, CUDA events around all device work of one registration
     barrier()
-    clk = ClockSampler(local) if rank == 0 else None
+    t_mark0 = time.time()
     t_wall0 = time.perf_counter()
     tot_ms = kern_ms = 0.0
     iters, launches, touched, perr, grid = [], 0, 0, 0.0, 0
@@ -249,7 +259,7 @@ def run_b200(args):
         e2e_ms += r["e2e_ms"]
     barrier()
     wall_s = time.perf_counter() - t_wall0
-    clocks = clk.stop() if clk else None
+    clocks = clk.stop(t_mark0, time.time()) if clk else None
     if dist is not None:
         t = torch.tensor([tot_ms, e2e_ms, kern_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

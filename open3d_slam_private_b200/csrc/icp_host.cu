@@ -46,10 +46,15 @@ __global__ void __launch_bounds__(kMeanThreads) read_sum_kernel(const float4* __
 // frames[32..47] = T_readIn_readMean (ICP.cpp:968-970), frames[48..50] = reading centroid
 __global__ void frames_kernel(const double* __restrict__ partials, int nblocks, int N, const float* __restrict__ Tinit,
                               float* __restrict__ frames) {
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  // one warp: lane l sums blocks l, l + 32, ... (fixed order), then a fixed shuffle tree
+  const int lane = threadIdx.x & 31;
+  if (blockIdx.x != 0 || threadIdx.x >= 32) return;
   double s[3] = {0.0, 0.0, 0.0};
-  for (int b = 0; b < nblocks; ++b)
+  for (int b = lane; b < nblocks; b += 32)
     for (int d = 0; d < 3; ++d) s[d] += partials[3 * (size_t)b + d];
+  for (int d = 0; d < 3; ++d)
+    for (int o = 16; o > 0; o >>= 1) s[d] += __shfl_xor_sync(0xffffffffu, s[d], o);
+  if (lane != 0) return;
   float mean[3];
   for (int d = 0; d < 3; ++d) mean[d] = (float)(s[d] / (double)N);
   float Tread[16], invRef[16], tmp[16], Tpre[16], Tref[16], Ti[16];
