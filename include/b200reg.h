@@ -202,6 +202,44 @@ int b200_icp_get_debug_warps(b200_icp* icp, uint32_t* out4xS, int max_slots, int
 /* evict L2 (writes a buffer larger than L2) on the handle's stream; for benchmarking hygiene */
 int b200_icp_flush_l2(b200_icp* icp);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Boundary B — replaces the Open3D v0.15.1 pipeline behind o3d_slam::CloudRegistration::registerClouds
+ * (open3d_slam/src/CloudRegistration.cpp:17-23 RegistrationGeneralizedICP, :62-66 and :89-94 RegistrationICP;
+ * constraint_builders.cpp:65-68): 1-NN within max_correspondence_distance, point-to-plane or generalized-ICP
+ * linearisation (covariances C = R diag(eps,1,1) R^T derived from the normals, as Open3D does when the clouds carry
+ * normals), x = -(JtJ)^-1 Jtr, T(x) = Rz Ry Rx, stop on |d fitness| and |d inlier_rmse| below the criteria or after
+ * max_iteration updates. Transformations are column-major DOUBLE 4x4 (Eigen::Matrix4d).
+ * ---------------------------------------------------------------------------------------------------------- */
+typedef struct b200_o3d b200_o3d;
+typedef struct {
+  int kind;                          /* 0 TransformationEstimationPointToPlane, 1 ...PointToPoint, 2 ...ForGeneralizedICP */
+  float max_correspondence_distance; /* IcpParameters::maxCorrespondenceDistance_ (Parameters.hpp:66-72) */
+  int max_iteration;                 /* ICPConvergenceCriteria::max_iteration_ <- IcpParameters::maxNumIter_ */
+  double relative_fitness, relative_rmse; /* ICPConvergenceCriteria, Open3D defaults 1e-6 */
+  double gicp_epsilon;               /* TransformationEstimationForGeneralizedICP::epsilon_, 1e-3 */
+  float cell_size;                   /* index option, <= 0 automatic */
+} b200_o3d_params;
+typedef struct {
+  double T[16];            /* RegistrationResult::transformation_ */
+  double fitness;          /* #correspondences / #source points */
+  double inlier_rmse;      /* sqrt(mean squared correspondence distance) */
+  int iterations;          /* transformation updates applied */
+  int n_correspondences;   /* RegistrationResult::correspondence_set_.size() */
+  int kernel_launches;
+  float device_ms, total_ms;
+} b200_o3d_result;
+void b200_o3d_default_params(b200_o3d_params* prm);
+int b200_o3d_create(b200_o3d** out, int device, const b200_o3d_params* prm);
+void b200_o3d_destroy(b200_o3d* h);
+/* target cloud with normals (estimateNormalsOrCovariancesIfNeeded has run on it, CloudRegistration.cpp:27-46);
+ * normals may be NULL for kind 1 */
+int b200_o3d_set_target(b200_o3d* h, const float* tgt4xM, const float* tgtn3xM, int M);
+/* registerClouds(source, target, init); srcn3xN is required for kind 2 only */
+int b200_o3d_register(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16,
+                      b200_o3d_result* res);
+/* correspondence_set_: matched target index per source point (-1: none) and squared distances; either may be NULL */
+int b200_o3d_get_correspondences(b200_o3d* h, int32_t* ids_N, float* dists_N);
+
 #ifdef __cplusplus
 }
 #endif

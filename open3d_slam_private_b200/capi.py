@@ -63,6 +63,18 @@ class IcpResult(C.Structure):
     ]
 
 
+class O3dParams(C.Structure):
+    _fields_ = [("kind", C.c_int), ("max_correspondence_distance", C.c_float), ("max_iteration", C.c_int),
+                ("relative_fitness", C.c_double), ("relative_rmse", C.c_double), ("gicp_epsilon", C.c_double),
+                ("cell_size", C.c_float)]
+
+
+class O3dResult(C.Structure):
+    _fields_ = [("T", C.c_double * 16), ("fitness", C.c_double), ("inlier_rmse", C.c_double), ("iterations", C.c_int),
+                ("n_correspondences", C.c_int), ("kernel_launches", C.c_int), ("device_ms", C.c_float),
+                ("total_ms", C.c_float)]
+
+
 def lib_path():
     return _LIBPATH
 
@@ -378,6 +390,58 @@ class ICP:
         if getattr(self, "h", None) and self.h.value:
             load().b200_icp_destroy(self.h)
             self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+O3D_POINT_TO_PLANE, O3D_GENERALIZED = 0, 2
+
+
+class O3dICP:
+    """Boundary B: Open3D-semantics RegistrationICP / RegistrationGeneralizedICP on the device (b200_o3d_*)."""
+
+    def __init__(self, kind=O3D_POINT_TO_PLANE, max_correspondence_distance=1.0, max_iteration=30,
+                 relative_fitness=1e-6, relative_rmse=1e-6, gicp_epsilon=1e-3, cell_size=0.0, device=0):
+        require_device()
+        p = O3dParams()
+        load().b200_o3d_default_params(C.byref(p))
+        p.kind, p.max_correspondence_distance, p.max_iteration = kind, max_correspondence_distance, max_iteration
+        p.relative_fitness, p.relative_rmse, p.gicp_epsilon, p.cell_size = relative_fitness, relative_rmse, gicp_epsilon, cell_size
+        self.params = p
+        self._h = C.c_void_p()
+        self._n = 0
+        _check(load().b200_o3d_create(C.byref(self._h), device, C.byref(p)))
+
+    def set_target(self, tgt4, normals):
+        tgt4, normals = f32(tgt4), f32(normals)
+        _check(load().b200_o3d_set_target(self._h, _fp(tgt4), _fp(normals), tgt4.shape[0]))
+
+    def register(self, src4, normals=None, init=None):
+        src4, normals = f32(src4), f32(normals)
+        Ti = np.eye(4) if init is None else np.asarray(init, np.float64)
+        Tc = np.ascontiguousarray(Ti.T).ravel()
+        r = O3dResult()
+        self._n = src4.shape[0]
+        _check(load().b200_o3d_register(self._h, _fp(src4), _fp(normals), self._n,
+                                        Tc.ctypes.data_as(C.POINTER(C.c_double)), C.byref(r)))
+        return dict(T=np.array(r.T, np.float64).reshape(4, 4).T.copy(), fitness=r.fitness, inlier_rmse=r.inlier_rmse,
+                    iterations=r.iterations, n_correspondences=r.n_correspondences, device_ms=r.device_ms,
+                    total_ms=r.total_ms, kernel_launches=r.kernel_launches)
+
+    def correspondences(self):
+        ids = np.empty(self._n, np.int32)
+        d = np.empty(self._n, np.float32)
+        _check(load().b200_o3d_get_correspondences(self._h, _ip(ids), _fp(d)))
+        return ids, d
+
+    def close(self):
+        if self._h:
+            load().b200_o3d_destroy(self._h)
+            self._h = C.c_void_p()
 
     def __del__(self):
         try:

@@ -91,13 +91,15 @@ struct b200_index {
 extern "C" {
 
 const char* b200_last_error(void) { return g_err.c_str(); }
-int b200_version(void) { return 101; }
+int b200_version(void) { return 102; }
 int b200_struct_size(int which) {
   switch (which) {
     case 0: return (int)sizeof(b200_icp_params);
     case 1: return (int)sizeof(b200_icp_result);
     case 2: return (int)sizeof(b200_index_opts);
     case 3: return (int)sizeof(b200_surface_normal_params);
+    case 4: return (int)sizeof(b200_o3d_params);
+    case 5: return (int)sizeof(b200_o3d_result);
     default: return -1;
   }
 }

@@ -1,0 +1,514 @@
+// Boundary B: the registration loop behind open3d_slam's CloudRegistration::registerClouds
+// (open3d_slam/src/CloudRegistration.cpp:17-23 RegistrationGeneralizedICP, :62-66 / :89-94 RegistrationICP), i.e.
+// Open3D v0.15.1's RegistrationICP with TransformationEstimationPointToPlane or ...ForGeneralizedICP. Open3D is not in
+// the reference tree; the algorithm is recalled from upstream (parity unpinned).
+//
+//   result = match(T src); repeat { x = -(JtJ)^-1 Jtr; T = T(x) T; result' = match(T src);
+//                                   stop when |d fitness| < rel_fitness and |d rmse| < rel_rmse }  (<= max_iteration updates)
+//
+// Device shape: every iteration is two kernels on one stream, enqueued max_iteration + 1 times without any host
+// synchronisation; a device-side `done` flag turns the remaining launches into no-ops, and ONE result struct is read
+// back at the end.
+//   o3d_match_lin_kernel  transform (double T, float result like the cloud Open3D hands to its kd-tree after our
+//                         double->float conversion) -> exact 1-NN within max_correspondence_distance (warp-cooperative
+//                         search of knn.cuh) -> residual rows and Jacobians in double -> 21 + 6 + 2 sums per CTA
+//   o3d_solve_kernel      fixed-order reduction of the CTA partials, fitness / inlier RMSE, convergence test against
+//                         the previous match, LDL^T solve of the 6x6 system, T(x) = Rz Ry Rx, T <- T(x) T
+// GICP covariances are Open3D's "from normals" form C = R diag(eps, 1, 1) R^T = I - (1 - eps) n n^T (with its quirk:
+// normals within ~8 degrees of -e1 are treated as e1), so M = C_t + C_s has the closed-form eigen-decomposition used
+// below for W = M^-1/2 (eigenvectors (a + b), (a - b), a x b): no per-pair iterative eigen-solver.
+#include "common.cuh"
+#include "grid_index.cuh"
+#include "knn.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <new>
+
+using namespace b200;
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kVals = 32;  // 21 JtJ (upper, column-major packed) + 6 Jtr + count + sum d^2 (+ 3 spare)
+
+struct O3dState {
+  double T[16];          // current transformation (column-major)
+  double fitness, rmse;  // of the last match
+  double prev_fitness, prev_rmse;
+  int updates;           // transformation updates applied so far (Open3D's loop counter)
+  int matches_done;      // match kernels executed
+  int done;
+  int n_corr;
+  int status;
+};
+
+struct O3dParams {
+  GridView g;
+  const float4* src;     // N source points
+  const float4* src_n;   // N source normals (GICP) or null
+  int N, kind;           // kind 0 point-to-plane, 1 point-to-point, 2 generalized
+  float md2;
+  int max_iteration;
+  double rel_fitness, rel_rmse, eps;
+  int* ids; float* dists;
+  double* partials;      // gridDim x kVals
+  O3dState* st;
+};
+
+__device__ __forceinline__ double3 gicp_axis(float4 n) {
+  // unit length restored in double (the reference's normals are unit doubles; the float boundary rounds them).
+  // Open3D GetRotationFromE1ToX: c = e1 . x < -0.99 -> identity rotation, i.e. the covariance of the e1 normal;
+  // a zero normal gives the identity rotation too.
+  const double x = (double)n.x, y = (double)n.y, z = (double)n.z;
+  const double nn = sqrt(x * x + y * y + z * z);
+  if (!(nn > 0.0)) return make_double3(1.0, 0.0, 0.0);
+  const double c = x / nn;
+  if (c < -0.99) return make_double3(1.0, 0.0, 0.0);
+  return make_double3(c, y / nn, z / nn);
+}
+
+__global__ void __launch_bounds__(kThreads) o3d_match_lin_kernel(const __grid_constant__ O3dParams p) {
+  __shared__ double s_part[kThreads / 32][kVals];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  if (p.st->done) return;
+  double T[12];
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int i = 0; i < 3; ++i) T[i + 3 * j] = p.st->T[i + 4 * j];
+  double acc[kVals];
+#pragma unroll
+  for (int t = 0; t < kVals; ++t) acc[t] = 0.0;
+  const int nthreads = gridDim.x * kThreads;
+  for (int base = blockIdx.x * kThreads + wid * 32; base < p.N; base += nthreads) {
+    const int i = base + lane;
+    const bool in = i < p.N;
+    float4 q = make_float4(0.f, 0.f, 0.f, 1.f);
+    if (in) {
+      const float4 s = __ldg(&p.src[i]);
+      q.x = (float)(T[0] * s.x + T[3] * s.y + T[6] * s.z + T[9]);
+      q.y = (float)(T[1] * s.x + T[4] * s.y + T[7] * s.z + T[10]);
+      q.z = (float)(T[2] * s.x + T[5] * s.y + T[8] * s.z + T[11]);
+    }
+    float bd; int bid, bsp;
+    unsigned vis = 0;
+    knn_query_warp1(p.g, in, q.x, q.y, q.z, p.md2, bd, bid, bsp, vis);
+    if (!in) continue;
+    p.ids[i] = bid; p.dists[i] = bd;
+    if (bid < 0) continue;
+    const float4 t4 = __ldg(&p.g.pts[bsp]);
+    const float4 n4 = p.kind == 1 ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldg(&p.g.nrm[bsp]);
+    const double s[3] = {(double)q.x, (double)q.y, (double)q.z};
+    const double d[3] = {s[0] - (double)t4.x, s[1] - (double)t4.y, s[2] - (double)t4.z};
+    acc[27] += 1.0;
+    acc[28] += (double)bd;
+    if (p.kind == 1) {
+      // Umeyama moments: sum s (0..2), sum t (3..5), sum t s^T (6..14, column-major)
+      const double t[3] = {(double)t4.x, (double)t4.y, (double)t4.z};
+#pragma unroll
+      for (int a = 0; a < 3; ++a) { acc[a] += s[a]; acc[3 + a] += t[a]; }
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+#pragma unroll
+        for (int r = 0; r < 3; ++r) acc[6 + r + 3 * c] += t[r] * s[c];
+    } else if (p.kind == 0) {
+      const double n[3] = {(double)n4.x, (double)n4.y, (double)n4.z};
+      const double r = d[0] * n[0] + d[1] * n[1] + d[2] * n[2];
+      const double J[6] = {s[1] * n[2] - s[2] * n[1], s[2] * n[0] - s[0] * n[2], s[0] * n[1] - s[1] * n[0], n[0], n[1], n[2]};
+      int t = 0;
+#pragma unroll
+      for (int c = 0; c < 6; ++c)
+#pragma unroll
+        for (int a = 0; a <= c; ++a) acc[t++] += J[a] * J[c];
+#pragma unroll
+      for (int a = 0; a < 6; ++a) acc[21 + a] += J[a] * r;
+    } else {
+      // M = C_t + R C_s R^T = 2 I - (1 - eps) (a a^T + b b^T), a = target axis, b = rotated source axis
+      const double3 a = gicp_axis(n4);
+      const double3 b0 = gicp_axis(__ldg(&p.src_n[i]));
+      const double3 b = make_double3(T[0] * b0.x + T[3] * b0.y + T[6] * b0.z, T[1] * b0.x + T[4] * b0.y + T[7] * b0.z,
+                                     T[2] * b0.x + T[5] * b0.y + T[8] * b0.z);
+      const double k1 = 1.0 - p.eps;
+      const double ab = a.x * b.x + a.y * b.y + a.z * b.z;
+      // eigenpairs in span{a, b}: u+ ~ a + b (lambda 2 - k1 (1 + ab)), u- ~ a - b (lambda 2 - k1 (1 - ab)); rest: 2
+      double up[3] = {a.x + b.x, a.y + b.y, a.z + b.z}, um[3] = {a.x - b.x, a.y - b.y, a.z - b.z};
+      const double np2 = up[0] * up[0] + up[1] * up[1] + up[2] * up[2], nm2 = um[0] * um[0] + um[1] * um[1] + um[2] * um[2];
+      const double w0 = 0.70710678118654752440;  // 2^-1/2
+      const double wp = np2 > 1e-24 ? 1.0 / sqrt(2.0 - k1 * (1.0 + ab)) - w0 : 0.0;
+      const double wm = nm2 > 1e-24 ? 1.0 / sqrt(2.0 - k1 * (1.0 - ab)) - w0 : 0.0;
+      const double ip = np2 > 1e-24 ? wp / np2 : 0.0, im = nm2 > 1e-24 ? wm / nm2 : 0.0;
+      double W[9];  // symmetric: W = w0 I + wp u+ u+^T + wm u- u-^T
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+#pragma unroll
+        for (int r = 0; r < 3; ++r) W[r + 3 * c] = (r == c ? w0 : 0.0) + ip * up[r] * up[c] + im * um[r] * um[c];
+      // J = W [ -[s]x  I ], r = W d; three rows
+#pragma unroll
+      for (int row = 0; row < 3; ++row) {
+        const double wr[3] = {W[row], W[row + 3], W[row + 6]};
+        // -[s]x has columns (0, -s2, s1), (s2, 0, -s0), (-s1, s0, 0)
+        const double J[6] = {wr[2] * s[1] - wr[1] * s[2], wr[0] * s[2] - wr[2] * s[0], wr[1] * s[0] - wr[0] * s[1],
+                             wr[0], wr[1], wr[2]};
+        const double r = wr[0] * d[0] + wr[1] * d[1] + wr[2] * d[2];
+        int t = 0;
+#pragma unroll
+        for (int c = 0; c < 6; ++c)
+#pragma unroll
+          for (int a2 = 0; a2 <= c; ++a2) acc[t++] += J[a2] * J[c];
+#pragma unroll
+        for (int a2 = 0; a2 < 6; ++a2) acc[21 + a2] += J[a2] * r;
+      }
+    }
+  }
+  // CTA partial: warp shuffle tree, then warps in order (deterministic)
+#pragma unroll
+  for (int t = 0; t < 29; ++t) {
+    double v = acc[t];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) s_part[wid][t] = v;
+  }
+  __syncthreads();
+  if (tid < 29) {
+    double v = 0.0;
+    for (int w = 0; w < kThreads / 32; ++w) v += s_part[w][tid];
+    p.partials[(size_t)blockIdx.x * kVals + tid] = v;
+  }
+}
+
+// R = U diag(1, 1, det(U) det(V)) V^T for the SVD S = U diag(sigma) V^T, by one-sided Jacobi on the columns of S
+// (sigma sorted descending; the third left vector is rebuilt as u1 x u2, which also covers rank-2 S).
+__device__ void kabsch3(const double* S, double* R) {
+  double A[9], V[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+  for (int i = 0; i < 9; ++i) A[i] = S[i];
+  for (int sweep = 0; sweep < 40; ++sweep) {
+    bool rotated = false;
+    for (int pc = 0; pc < 2; ++pc)
+      for (int qc = pc + 1; qc < 3; ++qc) {
+        double al = 0, be = 0, ga = 0;
+        for (int k = 0; k < 3; ++k) { al += A[k + 3 * pc] * A[k + 3 * pc]; be += A[k + 3 * qc] * A[k + 3 * qc]; ga += A[k + 3 * pc] * A[k + 3 * qc]; }
+        if (ga == 0.0 || fabs(ga) <= 1e-16 * sqrt(al * be)) continue;
+        rotated = true;
+        const double zeta = (be - al) / (2.0 * ga);
+        const double t = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+        const double c = 1.0 / sqrt(1.0 + t * t), sn = c * t;
+        for (int k = 0; k < 3; ++k) {
+          const double ap = A[k + 3 * pc], aq = A[k + 3 * qc];
+          A[k + 3 * pc] = c * ap - sn * aq; A[k + 3 * qc] = sn * ap + c * aq;
+          const double vp = V[k + 3 * pc], vq = V[k + 3 * qc];
+          V[k + 3 * pc] = c * vp - sn * vq; V[k + 3 * qc] = sn * vp + c * vq;
+        }
+      }
+    if (!rotated) break;
+  }
+  double sg[3];
+  int o[3] = {0, 1, 2};
+  for (int j = 0; j < 3; ++j) sg[j] = sqrt(A[3 * j] * A[3 * j] + A[1 + 3 * j] * A[1 + 3 * j] + A[2 + 3 * j] * A[2 + 3 * j]);
+  for (int a = 0; a < 2; ++a)
+    for (int b = a + 1; b < 3; ++b)
+      if (sg[o[b]] > sg[o[a]]) { const int t = o[a]; o[a] = o[b]; o[b] = t; }
+  double u1[3], u2[3], u3[3], v1[3], v2[3], v3[3];
+  for (int k = 0; k < 3; ++k) {
+    u1[k] = sg[o[0]] > 0 ? A[k + 3 * o[0]] / sg[o[0]] : (k == 0);
+    v1[k] = V[k + 3 * o[0]]; v2[k] = V[k + 3 * o[1]]; v3[k] = V[k + 3 * o[2]];
+  }
+  if (sg[o[1]] > 1e-300) {
+    for (int k = 0; k < 3; ++k) u2[k] = A[k + 3 * o[1]] / sg[o[1]];
+  } else {  // rank <= 1: any unit vector orthogonal to u1
+    const int m = fabs(u1[0]) <= fabs(u1[1]) ? (fabs(u1[0]) <= fabs(u1[2]) ? 0 : 2) : (fabs(u1[1]) <= fabs(u1[2]) ? 1 : 2);
+    double e[3] = {0, 0, 0};
+    e[m] = 1.0;
+    const double d = u1[m];
+    double n2 = 0;
+    for (int k = 0; k < 3; ++k) { u2[k] = e[k] - d * u1[k]; n2 += u2[k] * u2[k]; }
+    for (int k = 0; k < 3; ++k) u2[k] /= sqrt(n2);
+  }
+  u3[0] = u1[1] * u2[2] - u1[2] * u2[1]; u3[1] = u1[2] * u2[0] - u1[0] * u2[2]; u3[2] = u1[0] * u2[1] - u1[1] * u2[0];
+  const double detV = v1[0] * (v2[1] * v3[2] - v2[2] * v3[1]) - v2[0] * (v1[1] * v3[2] - v1[2] * v3[1]) + v3[0] * (v1[1] * v2[2] - v1[2] * v2[1]);
+  const double sgn = detV < 0 ? -1.0 : 1.0;
+  for (int c = 0; c < 3; ++c)
+    for (int r = 0; r < 3; ++r) R[r + 3 * c] = u1[r] * v1[c] + u2[r] * v2[c] + sgn * u3[r] * v3[c];
+}
+
+// one CTA: reduce, test convergence, solve, update
+__global__ void __launch_bounds__(kThreads) o3d_solve_kernel(const __grid_constant__ O3dParams p, int nblocks) {
+  __shared__ double s_sum[kThreads / kVals][kVals];
+  __shared__ double s_tot[kVals];
+  O3dState* st = p.st;
+  if (st->done) return;
+  const int tid = threadIdx.x;
+  {  // fixed order: slice-major over CTAs, then slices in order
+    const int c = tid & (kVals - 1), slice = tid / kVals;
+    constexpr int kSlices = kThreads / kVals;
+    double s = 0.0;
+    for (int b = slice; b < nblocks; b += kSlices) s += p.partials[(size_t)b * kVals + c];
+    s_sum[slice][c] = s;
+    __syncthreads();
+    if (tid < kVals) {
+      double t = 0.0;
+      for (int sl = 0; sl < kSlices; ++sl) t += s_sum[sl][tid];
+      s_tot[tid] = t;
+    }
+    __syncthreads();
+  }
+  if (tid != 0) return;
+  const double cnt = s_tot[27];
+  const double fit = cnt / (double)p.N;
+  const double err = cnt > 0.0 ? sqrt(s_tot[28] / cnt) : 0.0;
+  const int j = st->matches_done;  // this is match number j (0 = the match before the first update)
+  st->matches_done = j + 1;
+  st->prev_fitness = st->fitness; st->prev_rmse = st->rmse;
+  st->fitness = fit; st->rmse = err;
+  st->n_corr = (int)(cnt + 0.5);
+  bool stop = false;
+  if (j >= 1 && fabs(st->prev_fitness - fit) < p.rel_fitness && fabs(st->prev_rmse - err) < p.rel_rmse) stop = true;
+  if (st->updates >= p.max_iteration) stop = true;
+  if (cnt == 0.0) stop = true;   // nothing to estimate from (Open3D would apply identity updates until it "converges")
+  if (!stop && p.kind == 1) {
+    // TransformationEstimationPointToPoint: Eigen::umeyama(source, target, with_scaling = false)
+    double ms[3], mt[3], S[9], U[16];
+    for (int a = 0; a < 3; ++a) { ms[a] = s_tot[a] / cnt; mt[a] = s_tot[3 + a] / cnt; }
+    for (int c = 0; c < 3; ++c)
+      for (int r = 0; r < 3; ++r) S[r + 3 * c] = s_tot[6 + r + 3 * c] / cnt - mt[r] * ms[c];
+    double R3[9];
+    kabsch3(S, R3);
+    for (int c = 0; c < 3; ++c)
+      for (int r = 0; r < 3; ++r) U[r + 4 * c] = R3[r + 3 * c];
+    for (int r = 0; r < 3; ++r) U[r + 12] = mt[r] - (R3[r] * ms[0] + R3[r + 3] * ms[1] + R3[r + 6] * ms[2]);
+    U[3] = 0.0; U[7] = 0.0; U[11] = 0.0; U[15] = 1.0;
+    double R[16];
+    for (int c = 0; c < 4; ++c)
+      for (int r = 0; r < 4; ++r) {
+        double a = 0.0;
+        for (int k = 0; k < 4; ++k) a += U[r + 4 * k] * st->T[k + 4 * c];
+        R[r + 4 * c] = a;
+      }
+    for (int i = 0; i < 16; ++i) st->T[i] = R[i];
+    st->updates += 1;
+  } else if (!stop) {
+    // x = -(JtJ)^-1 Jtr by LDL^T (Eigen ldlt(), no pivoting needed for these positive definite systems)
+    double A[36], L[36], D[6], y[6], x[6];
+    int t = 0;
+    for (int c = 0; c < 6; ++c)
+      for (int r = 0; r <= c; ++r) { A[r + 6 * c] = s_tot[t]; A[c + 6 * r] = s_tot[t]; ++t; }
+    bool ok = true;
+    for (int i = 0; i < 36; ++i) L[i] = 0.0;
+    for (int c = 0; c < 6 && ok; ++c) {
+      double d = A[c + 6 * c];
+      for (int k = 0; k < c; ++k) d -= L[c + 6 * k] * L[c + 6 * k] * D[k];
+      if (!(fabs(d) > 0.0)) { ok = false; break; }
+      D[c] = d;
+      L[c + 6 * c] = 1.0;
+      for (int i = c + 1; i < 6; ++i) {
+        double s = A[i + 6 * c];
+        for (int k = 0; k < c; ++k) s -= L[i + 6 * k] * L[c + 6 * k] * D[k];
+        L[i + 6 * c] = s / d;
+      }
+    }
+    if (!ok) stop = true;
+    else {
+      for (int i = 0; i < 6; ++i) {
+        double s = -s_tot[21 + i];
+        for (int k = 0; k < i; ++k) s -= L[i + 6 * k] * y[k];
+        y[i] = s;
+      }
+      for (int i = 0; i < 6; ++i) y[i] /= D[i];
+      for (int i = 5; i >= 0; --i) {
+        double s = y[i];
+        for (int k = i + 1; k < 6; ++k) s -= L[k + 6 * i] * x[k];
+        x[i] = s;
+      }
+      // TransformVector6dToMatrix4d: R = Rz(x2) Ry(x1) Rx(x0), t = x3..5; T <- U T
+      const double cx = cos(x[0]), sx = sin(x[0]), cy = cos(x[1]), sy = sin(x[1]), cz = cos(x[2]), sz = sin(x[2]);
+      double U[16];
+      U[0] = cz * cy; U[4] = cz * sy * sx - sz * cx; U[8] = cz * sy * cx + sz * sx; U[12] = x[3];
+      U[1] = sz * cy; U[5] = sz * sy * sx + cz * cx; U[9] = sz * sy * cx - cz * sx; U[13] = x[4];
+      U[2] = -sy;     U[6] = cy * sx;                U[10] = cy * cx;               U[14] = x[5];
+      U[3] = 0.0; U[7] = 0.0; U[11] = 0.0; U[15] = 1.0;
+      double R[16];
+      for (int c = 0; c < 4; ++c)
+        for (int r = 0; r < 4; ++r) {
+          double a = 0.0;
+          for (int k = 0; k < 4; ++k) a += U[r + 4 * k] * st->T[k + 4 * c];
+          R[r + 4 * c] = a;
+        }
+      for (int i = 0; i < 16; ++i) st->T[i] = R[i];
+      st->updates += 1;
+    }
+  }
+  if (stop) st->done = 1;
+}
+
+}  // namespace
+
+struct b200_o3d {
+  int device = 0;
+  b200_o3d_params prm;
+  cudaStream_t stream = nullptr;
+  MapIndex map;
+  bool target_ready = false;
+  float4 *d_src = nullptr, *d_src_n = nullptr;
+  float* d_stage3 = nullptr;
+  int* d_ids = nullptr;
+  float* d_dists = nullptr;
+  size_t cap_src = 0;
+  int N = 0;
+  double* d_partials = nullptr;
+  int max_blocks = 0;
+  O3dState* d_state = nullptr;
+  O3dState* h_state = nullptr;  // pinned
+  cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+};
+
+extern "C" {
+
+void b200_o3d_default_params(b200_o3d_params* p) {
+  if (!p) return;
+  std::memset(p, 0, sizeof(*p));
+  p->kind = 0;
+  p->max_correspondence_distance = 1.0f;   // RegistrationIcp*::maxCorrespondenceDistance_ (CloudRegistration.hpp:38)
+  p->max_iteration = 30;                   // open3d ICPConvergenceCriteria defaults: 1e-6, 1e-6, 30
+  p->relative_fitness = 1e-6;
+  p->relative_rmse = 1e-6;
+  p->gicp_epsilon = 1e-3;                  // TransformationEstimationForGeneralizedICP::epsilon_
+  p->cell_size = 0.f;
+}
+
+int b200_o3d_create(b200_o3d** out, int device, const b200_o3d_params* prm) {
+  if (!out || !prm) { set_error("b200_o3d_create: bad arguments"); return B200_E_BAD_PARAM; }
+  *out = nullptr;
+  if (prm->kind < 0 || prm->kind > 2) { set_error("b200_o3d: kind must be 0 (point-to-plane), 1 (point-to-point) or 2 (generalized)"); return B200_E_BAD_PARAM; }
+  if (!(prm->max_correspondence_distance > 0.f) || prm->max_iteration < 0) { set_error("b200_o3d: bad parameters"); return B200_E_BAD_PARAM; }
+  DeviceGuard dg(device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  b200_o3d* h = new (std::nothrow) b200_o3d();
+  if (!h) { set_error("out of host memory"); return B200_E_CUDA; }
+  h->device = device;
+  h->prm = *prm;
+  h->map.device = device;
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  h->max_blocks = sms * 8;
+  auto fail = [&](cudaError_t e, const char* what) { const int st = cuda_fail(e, what, __FILE__, __LINE__); b200_o3d_destroy(h); return st; };
+  cudaError_t e;
+  if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail(e, "cudaStreamCreate");
+  h->map.stream = h->stream;
+  if ((e = cudaMalloc(&h->d_partials, (size_t)h->max_blocks * kVals * sizeof(double))) != cudaSuccess) return fail(e, "cudaMalloc");
+  if ((e = cudaMalloc(&h->d_state, sizeof(O3dState))) != cudaSuccess) return fail(e, "cudaMalloc");
+  if ((e = cudaMallocHost(&h->h_state, sizeof(O3dState))) != cudaSuccess) return fail(e, "cudaMallocHost");
+  for (int i = 0; i < 3; ++i)
+    if ((e = cudaEventCreate(&h->ev[i])) != cudaSuccess) return fail(e, "cudaEventCreate");
+  *out = h;
+  return B200_OK;
+}
+
+void b200_o3d_destroy(b200_o3d* h) {
+  if (!h) return;
+  {
+    DeviceGuard dg(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    cudaFree(h->d_src); cudaFree(h->d_src_n); cudaFree(h->d_stage3); cudaFree(h->d_ids); cudaFree(h->d_dists);
+    cudaFree(h->d_partials); cudaFree(h->d_state);
+    cudaFreeHost(h->h_state);
+    for (int i = 0; i < 3; ++i)
+      if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    h->map.release();
+    if (h->stream) cudaStreamDestroy(h->stream);
+  }
+  delete h;
+}
+
+int b200_o3d_set_target(b200_o3d* h, const float* tgt4xM, const float* tgtn3xM, int M) {
+  if (!h || M <= 0 || !tgt4xM) { set_error("b200_o3d_set_target: bad arguments"); return B200_E_BAD_PARAM; }
+  if (!tgtn3xM && h->prm.kind != 1) { set_error("b200_o3d: the target cloud needs normals (point-to-plane residuals / GICP covariances)"); return B200_E_BAD_PARAM; }
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  h->target_ready = false;
+  cudaStream_t s = h->stream;
+  B200_TRY(index_alloc_points(h->map, M, tgtn3xM != nullptr));
+  B200_TRY(upload_features(h->map.d_ref, tgt4xM, M, s));
+  if (tgtn3xM) {
+    float* stage = nullptr;
+    B200_CUDA(cudaMallocAsync(&stage, (size_t)M * 3 * sizeof(float), s));
+    const int st = upload_normals(h->map.d_nrm_orig, tgtn3xM, M, stage, s);
+    cudaFreeAsync(stage, s);
+    if (st) return st;
+  }
+  b200_index_opts opts;
+  std::memset(&opts, 0, sizeof(opts));
+  opts.cell_size = h->prm.cell_size;
+  B200_TRY(index_build(h->map, &opts));   // no mean-centring: Open3D registers in the callers' frame
+  h->target_ready = true;
+  return B200_OK;
+}
+
+int b200_o3d_register(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16,
+                      b200_o3d_result* res) {
+  if (!h || N <= 0 || !src4xN || !res) { set_error("b200_o3d_register: bad arguments"); return B200_E_BAD_PARAM; }
+  if (!h->target_ready) { set_error("b200_o3d_register: no target set"); return B200_E_NOT_INITIALIZED; }
+  if (h->prm.kind == 2 && !srcn3xN) { set_error("b200_o3d: generalized ICP needs source normals (covariances are derived from them)"); return B200_E_BAD_PARAM; }
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  cudaStream_t s = h->stream;
+  if ((size_t)N > h->cap_src) {
+    cudaFree(h->d_src); cudaFree(h->d_src_n); cudaFree(h->d_stage3); cudaFree(h->d_ids); cudaFree(h->d_dists);
+    h->d_src = h->d_src_n = nullptr; h->d_stage3 = nullptr; h->d_ids = nullptr; h->d_dists = nullptr;
+    h->cap_src = 0;
+    B200_CUDA(cudaMalloc(&h->d_src, (size_t)N * sizeof(float4)));
+    B200_CUDA(cudaMalloc(&h->d_src_n, (size_t)N * sizeof(float4)));
+    B200_CUDA(cudaMalloc(&h->d_stage3, (size_t)N * 3 * sizeof(float)));
+    B200_CUDA(cudaMalloc(&h->d_ids, (size_t)N * sizeof(int)));
+    B200_CUDA(cudaMalloc(&h->d_dists, (size_t)N * sizeof(float)));
+    h->cap_src = (size_t)N;
+  }
+  h->N = N;
+  B200_CUDA(cudaEventRecord(h->ev[0], s));
+  B200_TRY(upload_features(h->d_src, src4xN, N, s));
+  if (srcn3xN) B200_TRY(upload_normals(h->d_src_n, srcn3xN, N, h->d_stage3, s));
+  std::memset(h->h_state, 0, sizeof(O3dState));
+  for (int i = 0; i < 16; ++i) h->h_state->T[i] = init16 ? init16[i] : ((i % 5 == 0) ? 1.0 : 0.0);
+  B200_CUDA(cudaMemcpyAsync(h->d_state, h->h_state, sizeof(O3dState), cudaMemcpyHostToDevice, s));
+  O3dParams p;
+  std::memset(&p, 0, sizeof(p));
+  p.g = h->map.view();
+  p.src = h->d_src;
+  p.src_n = srcn3xN ? h->d_src_n : nullptr;
+  p.N = N; p.kind = h->prm.kind;
+  p.md2 = h->prm.max_correspondence_distance * h->prm.max_correspondence_distance;
+  p.max_iteration = h->prm.max_iteration;
+  p.rel_fitness = h->prm.relative_fitness; p.rel_rmse = h->prm.relative_rmse; p.eps = h->prm.gicp_epsilon;
+  p.ids = h->d_ids; p.dists = h->d_dists; p.partials = h->d_partials; p.st = h->d_state;
+  const int blocks = std::max(1, std::min(h->max_blocks, (N + kThreads - 1) / kThreads));
+  B200_CUDA(cudaEventRecord(h->ev[1], s));
+  // max_iteration updates need max_iteration + 1 matches; launches after `done` return at once
+  for (int it = 0; it <= h->prm.max_iteration; ++it) {
+    o3d_match_lin_kernel<<<blocks, kThreads, 0, s>>>(p);
+    o3d_solve_kernel<<<1, kThreads, 0, s>>>(p, blocks);
+  }
+  B200_CUDA(cudaGetLastError());
+  B200_CUDA(cudaEventRecord(h->ev[2], s));
+  B200_CUDA(cudaMemcpyAsync(h->h_state, h->d_state, sizeof(O3dState), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  std::memset(res, 0, sizeof(*res));
+  for (int i = 0; i < 16; ++i) res->T[i] = h->h_state->T[i];
+  res->fitness = h->h_state->fitness;
+  res->inlier_rmse = h->h_state->rmse;
+  res->iterations = h->h_state->updates;
+  res->n_correspondences = h->h_state->n_corr;
+  res->kernel_launches = 2 * (h->prm.max_iteration + 1) + (srcn3xN ? 1 : 0);
+  B200_CUDA(cudaEventElapsedTime(&res->device_ms, h->ev[1], h->ev[2]));
+  B200_CUDA(cudaEventElapsedTime(&res->total_ms, h->ev[0], h->ev[2]));
+  return B200_OK;
+}
+
+int b200_o3d_get_correspondences(b200_o3d* h, int32_t* ids_N, float* dists_N) {
+  if (!h || h->N <= 0) { set_error("no registration has run"); return B200_E_NOT_INITIALIZED; }
+  DeviceGuard dg(h->device);
+  if (ids_N) B200_CUDA(cudaMemcpyAsync(ids_N, h->d_ids, (size_t)h->N * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+  if (dists_N) B200_CUDA(cudaMemcpyAsync(dists_N, h->d_dists, (size_t)h->N * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+  B200_CUDA(cudaStreamSynchronize(h->stream));
+  return B200_OK;
+}
+
+}  // extern "C"

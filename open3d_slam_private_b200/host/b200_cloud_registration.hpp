@@ -10,12 +10,10 @@
 // and the class below is wrapped by a 10-line subclass of o3d_slam::CloudRegistration. Clouds are
 // converted double -> float exactly like open3dToPointmatcher (open3d_conversions.cpp:57-118).
 //
-// Semantics: the chain run on the device is the libpointmatcher one (1-NN within maxCorrespondenceDistance_, no
-// outlier filter, point-to-plane or point-to-point minimiser, Counter{maxNumIter_} + Differential checkers) — the
-// same linear system Open3D's TransformationEstimationPointToPlane builds (JtJ = sum F F^T, Jtr = sum F r). Open3D's
-// own Euler-angle pose update and relative fitness/RMSE stopping rule (Open3D v0.15.1, not in the reference tree) are
-// a "next" item in DESIGN.md; fitness_ and inlier_rmse_ are computed from the final correspondences as Open3D
-// defines them (#correspondences / #source points, sqrt(mean squared distance)).
+// Semantics: Open3D's own loop (b200_o3d_* in include/b200reg.h): 1-NN within maxCorrespondenceDistance_, the
+// TransformationEstimation{PointToPlane, PointToPoint, ForGeneralizedICP} update, T <- update * T in double, and the
+// ICPConvergenceCriteria stopping rule (relative fitness / relative RMSE / max_iteration). fitness_, inlier_rmse_ and
+// correspondence_set_ are those of the last match, as in RegistrationResult.
 #pragma once
 #include <cmath>
 #include <cstdint>
@@ -27,57 +25,59 @@
 
 namespace b200o3d {
 
-enum class Kind { PointToPlane, PointToPoint };
+enum class Kind { PointToPlane = 0, PointToPoint = 1, Generalized = 2 };
 
 template <class Cloud, class Mat4, class Result>
 class RegistrationIcpB200 {
  public:
   double maxCorrespondenceDistance_ = 1.0;   // IcpParameters::maxCorrespondenceDistance_ (Parameters.hpp:66-72)
-  int maxNumIter_ = 50;                      // IcpParameters::maxNumIter_
+  int maxNumIter_ = 50;                      // IcpParameters::maxNumIter_ -> ICPConvergenceCriteria::max_iteration_
+  double relativeFitness_ = 1e-6;            // ICPConvergenceCriteria::relative_fitness_ (Open3D default)
+  double relativeRmse_ = 1e-6;               // ICPConvergenceCriteria::relative_rmse_ (Open3D default)
+  double gicpEpsilon_ = 1e-3;                // TransformationEstimationForGeneralizedICP::epsilon_
   int knnNormalEstimation_ = 10;             // IcpParameters::knn_
   double maxRadiusNormalEstimation_ = 2.0;   // IcpParameters::maxDistanceKnn_
   Kind kind_ = Kind::PointToPlane;
   int device_ = 0;
 
   RegistrationIcpB200() = default;
-  ~RegistrationIcpB200() { b200_icp_destroy(icp_); }
+  ~RegistrationIcpB200() { b200_o3d_destroy(h_); }
   RegistrationIcpB200(const RegistrationIcpB200&) = delete;
   RegistrationIcpB200& operator=(const RegistrationIcpB200&) = delete;
 
   // CloudRegistration::registerClouds(source, target, init)
   Result registerClouds(const Cloud& source, const Cloud& target, const Mat4& init) {
     ensure();
-    std::vector<float> tgt4, tgtn, src4;
+    std::vector<float> tgt4, tgtn, src4, srcn;
     to_feat4(target.points_, tgt4);
-    const bool hasN = target.normals_.size() == target.points_.size() && !target.normals_.empty();
-    if (kind_ == Kind::PointToPlane && !hasN) throw std::runtime_error("RegistrationIcpB200: target cloud has no normals");
-    if (hasN) to_xyz3(target.normals_, tgtn);
+    const bool tgtHasN = target.normals_.size() == target.points_.size() && !target.normals_.empty();
+    const bool srcHasN = source.normals_.size() == source.points_.size() && !source.normals_.empty();
+    if (kind_ != Kind::PointToPoint && !tgtHasN) throw std::runtime_error("RegistrationIcpB200: target cloud has no normals");
+    if (kind_ == Kind::Generalized && !srcHasN) throw std::runtime_error("RegistrationIcpB200: source cloud has no normals");
+    if (tgtHasN) to_xyz3(target.normals_, tgtn);
+    if (srcHasN && kind_ == Kind::Generalized) to_xyz3(source.normals_, srcn);
     to_feat4(source.points_, src4);
-    check(b200_icp_init_reference(icp_, tgt4.data(), hasN ? tgtn.data() : nullptr, (int)target.points_.size()));
-    float Ti[16];
+    check(b200_o3d_set_target(h_, tgt4.data(), tgtHasN ? tgtn.data() : nullptr, (int)target.points_.size()));
+    double Ti[16];
     for (int j = 0; j < 4; ++j)
-      for (int i = 0; i < 4; ++i) Ti[i + 4 * j] = (float)init(i, j);
-    b200_icp_result r;
+      for (int i = 0; i < 4; ++i) Ti[i + 4 * j] = (double)init(i, j);
+    b200_o3d_result r;
     const int n = (int)source.points_.size();
-    check(b200_icp_compute(icp_, src4.data(), nullptr, n, Ti, &r));
+    check(b200_o3d_register(h_, src4.data(), srcn.empty() ? nullptr : srcn.data(), n, Ti, &r));
     Result out;
     for (int j = 0; j < 4; ++j)
-      for (int i = 0; i < 4; ++i) out.transformation_(i, j) = (double)r.T[i + 4 * j];
+      for (int i = 0; i < 4; ++i) out.transformation_(i, j) = r.T[i + 4 * j];
     std::vector<int32_t> ids(n);
-    std::vector<float> d(n), w(n);
-    check(b200_icp_get_matches(icp_, ids.data(), d.data(), w.data()));
-    double s2 = 0.0;
+    check(b200_o3d_get_correspondences(h_, ids.data(), nullptr));
     out.correspondence_set_.clear();
     for (int i = 0; i < n; ++i)
-      if (ids[i] >= 0 && w[i] != 0.f) {
-        out.correspondence_set_.emplace_back(i, ids[i]);
-        s2 += (double)d[i];
-      }
-    const size_t c = out.correspondence_set_.size();
-    out.fitness_ = n > 0 ? (double)c / (double)n : 0.0;
-    out.inlier_rmse_ = c > 0 ? std::sqrt(s2 / (double)c) : 0.0;
+      if (ids[i] >= 0) out.correspondence_set_.emplace_back(i, ids[i]);
+    out.fitness_ = r.fitness;
+    out.inlier_rmse_ = r.inlier_rmse;
+    lastIterations_ = r.iterations;
     return out;
   }
+  int lastIterations_ = 0;
 
   // CloudRegistration::estimateNormalsOrCovariancesIfNeeded (CloudRegistration.cpp:27-46, 67-79): skip when the
   // cloud has normals; else k-NN normals (hybrid radius = maxRadiusNormalEstimation_), normalised, flipped towards
@@ -120,15 +120,16 @@ class RegistrationIcpB200 {
     for (size_t i = 0; i < v.size(); ++i) { out[3 * i] = (float)v[i][0]; out[3 * i + 1] = (float)v[i][1]; out[3 * i + 2] = (float)v[i][2]; }
   }
   void ensure() {
-    if (icp_) return;
-    b200_icp_params p;
-    b200_icp_default_params(&p);
-    p.knn = 1; p.maxDist = (float)maxCorrespondenceDistance_; p.use_trimmed = 0;
-    p.minimizer = kind_ == Kind::PointToPlane ? 0 : 1;
-    p.max_iterations = maxNumIter_;
-    check(b200_icp_create(&icp_, device_, &p));
+    if (h_) return;
+    b200_o3d_params p;
+    b200_o3d_default_params(&p);
+    p.kind = (int)kind_;
+    p.max_correspondence_distance = (float)maxCorrespondenceDistance_;
+    p.max_iteration = maxNumIter_;
+    p.relative_fitness = relativeFitness_; p.relative_rmse = relativeRmse_; p.gicp_epsilon = gicpEpsilon_;
+    check(b200_o3d_create(&h_, device_, &p));
   }
-  b200_icp* icp_ = nullptr;
+  b200_o3d* h_ = nullptr;
 };
 
 }  // namespace b200o3d

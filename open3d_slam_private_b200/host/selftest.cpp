@@ -134,6 +134,17 @@ int main() {
   bare.points_ = tgt.points_;
   reg.estimateNormalsOrCovariancesIfNeeded(&bare);
   EXPECT(bare.normals_.size() == bare.points_.size());
+  // generalized and point-to-point estimators through the same class
+  Cloud srcN = src;
+  reg.estimateNormalsOrCovariancesIfNeeded(&srcN);
+  for (b200o3d::Kind k : {b200o3d::Kind::Generalized, b200o3d::Kind::PointToPoint}) {
+    b200o3d::RegistrationIcpB200<Cloud, M4, Result> rk;
+    rk.kind_ = k;
+    rk.maxCorrespondenceDistance_ = 0.5;
+    Result r2 = rk.registerClouds(srcN, tgt, I);
+    std::printf("boundary B kind %d: tz %.5f fitness %.4f iterations %d\n", (int)k, r2.transformation_(2, 3), r2.fitness_, rk.lastIterations_);
+    EXPECT(std::fabs(r2.transformation_(2, 3) + 0.08) < 0.02 && r2.fitness_ > 0.9);
+  }
   std::printf(fails ? "selftest FAILED\n" : "selftest ok (device path)\n");
   return fails ? 1 : 0;
 }

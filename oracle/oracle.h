@@ -131,6 +131,15 @@ int orc_icp_forced(const orc_icp_params* prm, const float* ref4xM, const float* 
                    float* logb, float* logx, float* logT, int* logP, int32_t* last_ids, float* last_dists,
                    float* last_w, const float* forcedT, int n_forced);
 
+/* ---- boundary B: Open3D v0.15.1 RegistrationICP / RegistrationGeneralizedICP as called by
+ * open3d_slam/src/CloudRegistration.cpp:17-23, 62-66 (recalled from upstream, see o3d.cpp). kind 0 point-to-plane,
+ * 2 generalized. Matrices column-major double. corr_ids (nullable): matched target index per source point or -1. */
+void orc_o3d_covariances_from_normals(const float* n3xN, int N, double eps, double* cov9xN);
+int orc_o3d_icp(int kind, const float* src4xN, int N, const float* tgt4xM, int M, const float* tgtn3xM,
+                const double* srccov9xN, const double* tgtcov9xM, float max_dist, const double* init16,
+                int max_iteration, double rel_fitness, double rel_rmse, int knn_threads, double* T16, double* fitness,
+                double* rmse, int* iterations, int32_t* corr_ids);
+
 /* the same split as the reference's initReference / compute (one reference, many readings) */
 void* orc_icp_ref_create(const float* ref4xM, const float* refn3xM, int M, int mean_mode);
 void orc_icp_ref_free(void* h);

@@ -42,7 +42,7 @@ class IcpResult(C.Structure):
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("knn.cpp", "modules.cpp", "normals.cpp", "icp.cpp", "oracle.h",
+    srcs = [os.path.join(_HERE, f) for f in ("knn.cpp", "modules.cpp", "normals.cpp", "icp.cpp", "o3d.cpp", "oracle.h",
                                              "la_small.hpp")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s"])
@@ -311,3 +311,34 @@ class IcpSession:
 
     def __del__(self):
         self.close()
+
+
+def o3d_covariances_from_normals(normals, eps=1e-3):
+    n = f32(normals)
+    cov = np.empty((n.shape[0], 9), np.float64)
+    lib().orc_o3d_covariances_from_normals(_fp(n), n.shape[0], C.c_double(eps), cov.ctypes.data_as(C.POINTER(C.c_double)))
+    return cov
+
+
+def o3d_icp(kind, src4, tgt4, tgt_normals=None, src_normals=None, max_dist=1.0, init=None, max_iteration=30,
+            rel_fitness=1e-6, rel_rmse=1e-6, eps=1e-3, threads=4):
+    """Open3D RegistrationICP (kind 0 point-to-plane) / RegistrationGeneralizedICP (kind 2, covariances from normals)."""
+    src4, tgt4, tn, sn = f32(src4), f32(tgt4), f32(tgt_normals), f32(src_normals)
+    n = src4.shape[0]
+    dp = C.POINTER(C.c_double)
+    Ti = np.eye(4) if init is None else np.asarray(init, np.float64)
+    Tc = np.ascontiguousarray(Ti.T).ravel()
+    sc = tc = None
+    if kind == 2:
+        sc = o3d_covariances_from_normals(sn, eps)
+        tc = o3d_covariances_from_normals(tn, eps)
+    T = np.empty(16, np.float64)
+    fit, rmse, it = C.c_double(), C.c_double(), C.c_int()
+    ids = np.empty(n, np.int32)
+    st = lib().orc_o3d_icp(kind, _fp(src4), n, _fp(tgt4), tgt4.shape[0], _fp(tn),
+                           None if sc is None else sc.ctypes.data_as(dp), None if tc is None else tc.ctypes.data_as(dp),
+                           C.c_float(max_dist), Tc.ctypes.data_as(dp), max_iteration, C.c_double(rel_fitness),
+                           C.c_double(rel_rmse), threads, T.ctypes.data_as(dp), C.byref(fit), C.byref(rmse),
+                           C.byref(it), _ip(ids))
+    return dict(status=st, T=T.reshape(4, 4).T.copy(), fitness=fit.value, inlier_rmse=rmse.value,
+                iterations=it.value, ids=ids)

@@ -46,6 +46,8 @@ def test_struct_sizes_match_header():
     assert ctypes.sizeof(B.IcpResult) == lib.b200_struct_size(1)
     assert ctypes.sizeof(B.IndexOpts) == lib.b200_struct_size(2) == 16
     assert ctypes.sizeof(B.SurfaceNormalParams) == lib.b200_struct_size(3)
+    assert ctypes.sizeof(B.O3dParams) == lib.b200_struct_size(4)
+    assert ctypes.sizeof(B.O3dResult) == lib.b200_struct_size(5)
 
 
 def test_no_cpu_fallback_without_device():
