@@ -237,7 +237,22 @@ int b200_o3d_set_target(b200_o3d* h, const float* tgt4xM, const float* tgtn3xM, 
 /* registerClouds(source, target, init); srcn3xN is required for kind 2 only */
 int b200_o3d_register(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16,
                       b200_o3d_result* res);
-/* correspondence_set_: matched target index per source point (-1: none) and squared distances; either may be NULL */
+/* Spatially partitioned map: each device holds one slab of the map (padded by a halo of
+ * max_correspondence_distance) as its target and answers only for the source points whose transformed coordinate along
+ * `axis` lies in [lo, hi) -- exactly one owner per point, so the union of the slabs' correspondences is the
+ * single-device result. gid_M (nullable) maps slab-local target indices to indices in the whole map. The host drives
+ * the loop and sums the 32 doubles of every slab between the two steps (NCCL allreduce on `stream`):
+ *   begin; repeat max_iteration + 1 times { step_linearize(sums); allreduce(sums); step_update(sums) }; finish.
+ * sums layout: 21 JtJ upper (column-major packed) + 6 Jtr (kind 1: Umeyama moments in 0..14), [27] correspondence
+ * count, [28] sum of squared distances, [29..31] zero. Steps after convergence write zeros / do nothing. */
+int b200_o3d_set_partition(b200_o3d* h, int axis, float lo, float hi, const int32_t* gid_M);
+int b200_o3d_begin(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16,
+                   void* cuda_stream /* cudaStream_t; NULL: the handle's own; cudaStreamLegacy (0x1) names the default stream */);
+int b200_o3d_step_linearize(b200_o3d* h, double* d_sums32 /* DEVICE pointer */);
+int b200_o3d_step_update(b200_o3d* h, const double* d_sums32 /* DEVICE pointer, totals over all slabs */);
+int b200_o3d_poll(b200_o3d* h, int* done, int* updates); /* synchronises the stream */
+int b200_o3d_finish(b200_o3d* h, b200_o3d_result* res);
+/* correspondence_set_: matched target index per source point (-2: owned by another slab) (-1: none) and squared distances; either may be NULL */
 int b200_o3d_get_correspondences(b200_o3d* h, int32_t* ids_N, float* dists_N);
 
 #ifdef __cplusplus

@@ -432,6 +432,37 @@ class O3dICP:
                     iterations=r.iterations, n_correspondences=r.n_correspondences, device_ms=r.device_ms,
                     total_ms=r.total_ms, kernel_launches=r.kernel_launches)
 
+    # ---- partitioned map: stepwise run, the caller sums the 32 doubles over the slabs between the two steps
+    def set_partition(self, axis, lo, hi, gid=None):
+        g = None if gid is None else np.ascontiguousarray(gid, np.int32)
+        _check(load().b200_o3d_set_partition(self._h, int(axis), C.c_float(lo), C.c_float(hi), _ip(g)))
+
+    def begin(self, src4, normals=None, init=None, stream=None):
+        src4, normals = f32(src4), f32(normals)
+        Ti = np.eye(4) if init is None else np.asarray(init, np.float64)
+        Tc = np.ascontiguousarray(Ti.T).ravel()
+        self._n = src4.shape[0]
+        _check(load().b200_o3d_begin(self._h, _fp(src4), _fp(normals), self._n, Tc.ctypes.data_as(C.POINTER(C.c_double)),
+                                     C.c_void_p(stream or 0)))
+
+    def step_linearize(self, sums_ptr):
+        _check(load().b200_o3d_step_linearize(self._h, C.c_void_p(sums_ptr)))
+
+    def step_update(self, sums_ptr):
+        _check(load().b200_o3d_step_update(self._h, C.c_void_p(sums_ptr)))
+
+    def poll(self):
+        done, upd = C.c_int(), C.c_int()
+        _check(load().b200_o3d_poll(self._h, C.byref(done), C.byref(upd)))
+        return bool(done.value), upd.value
+
+    def finish(self):
+        r = O3dResult()
+        _check(load().b200_o3d_finish(self._h, C.byref(r)))
+        return dict(T=np.array(r.T, np.float64).reshape(4, 4).T.copy(), fitness=r.fitness, inlier_rmse=r.inlier_rmse,
+                    iterations=r.iterations, n_correspondences=r.n_correspondences, device_ms=r.device_ms,
+                    total_ms=r.total_ms, kernel_launches=r.kernel_launches)
+
     def correspondences(self):
         ids = np.empty(self._n, np.int32)
         d = np.empty(self._n, np.float32)

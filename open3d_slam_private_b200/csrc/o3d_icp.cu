@@ -54,6 +54,11 @@ struct O3dParams {
   int* ids; float* dists;
   double* partials;      // gridDim x kVals
   O3dState* st;
+  // spatially partitioned target (one slab of a larger map per device): this device answers only for the queries whose
+  // transformed coordinate along own_axis lies in [own_lo, own_hi); gid maps slab-local ids to ids in the whole map
+  int own_axis;          // -1: not partitioned
+  float own_lo, own_hi;
+  const int* gid;
 };
 
 __device__ __forceinline__ double3 gicp_axis(float4 n) {
@@ -91,11 +96,17 @@ __global__ void __launch_bounds__(kThreads) o3d_match_lin_kernel(const __grid_co
       q.y = (float)(T[1] * s.x + T[4] * s.y + T[7] * s.z + T[10]);
       q.z = (float)(T[2] * s.x + T[5] * s.y + T[8] * s.z + T[11]);
     }
+    bool mine = in;
+    if (p.own_axis >= 0) {
+      const float c = p.own_axis == 0 ? q.x : (p.own_axis == 1 ? q.y : q.z);
+      mine = in && c >= p.own_lo && c < p.own_hi;
+    }
     float bd; int bid, bsp;
     unsigned vis = 0;
-    knn_query_warp1(p.g, in, q.x, q.y, q.z, p.md2, bd, bid, bsp, vis);
+    knn_query_warp1(p.g, mine, q.x, q.y, q.z, p.md2, bd, bid, bsp, vis);
     if (!in) continue;
-    p.ids[i] = bid; p.dists[i] = bd;
+    if (!mine) { p.ids[i] = -2; p.dists[i] = __int_as_float(0x7f800000); continue; }   // another slab's query
+    p.ids[i] = (bid >= 0 && p.gid) ? __ldg(&p.gid[bid]) : bid; p.dists[i] = bd;
     if (bid < 0) continue;
     const float4 t4 = __ldg(&p.g.pts[bsp]);
     const float4 n4 = p.kind == 1 ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldg(&p.g.nrm[bsp]);
@@ -170,9 +181,9 @@ __global__ void __launch_bounds__(kThreads) o3d_match_lin_kernel(const __grid_co
     if (lane == 0) s_part[wid][t] = v;
   }
   __syncthreads();
-  if (tid < 29) {
+  if (tid < kVals) {
     double v = 0.0;
-    for (int w = 0; w < kThreads / 32; ++w) v += s_part[w][tid];
+    for (int w = 0; w < kThreads / 32 && tid < 29; ++w) v += s_part[w][tid];
     p.partials[(size_t)blockIdx.x * kVals + tid] = v;
   }
 }
@@ -231,14 +242,39 @@ __device__ void kabsch3(const double* S, double* R) {
     for (int r = 0; r < 3; ++r) R[r + 3 * c] = u1[r] * v1[c] + u2[r] * v2[c] + sgn * u3[r] * v3[c];
 }
 
+// one CTA: this device's partials -> out[kVals] (zeros once the registration is done, so a late allreduce is harmless)
+__global__ void __launch_bounds__(kThreads) o3d_reduce_kernel(const __grid_constant__ O3dParams p, int nblocks,
+                                                              double* __restrict__ out) {
+  __shared__ double s_sum[kThreads / kVals][kVals];
+  const int tid = threadIdx.x;
+  const int c = tid & (kVals - 1), slice = tid / kVals;
+  constexpr int kSlices = kThreads / kVals;
+  double s = 0.0;
+  if (!p.st->done)
+    for (int b = slice; b < nblocks; b += kSlices) s += p.partials[(size_t)b * kVals + c];
+  s_sum[slice][c] = s;
+  __syncthreads();
+  if (tid < kVals) {
+    double t = 0.0;
+    for (int sl = 0; sl < kSlices; ++sl) t += s_sum[sl][tid];
+    out[tid] = t;
+  }
+}
+
 // one CTA: reduce, test convergence, solve, update
-__global__ void __launch_bounds__(kThreads) o3d_solve_kernel(const __grid_constant__ O3dParams p, int nblocks) {
+// sums == nullptr: reduce this device's partials and go on; otherwise `sums` already holds the totals over all slabs
+// (after the allreduce) and the partials are not read
+__global__ void __launch_bounds__(kThreads) o3d_solve_kernel(const __grid_constant__ O3dParams p, int nblocks,
+                                                             const double* __restrict__ sums) {
   __shared__ double s_sum[kThreads / kVals][kVals];
   __shared__ double s_tot[kVals];
   O3dState* st = p.st;
   if (st->done) return;
   const int tid = threadIdx.x;
-  {  // fixed order: slice-major over CTAs, then slices in order
+  if (sums) {
+    if (tid < kVals) s_tot[tid] = sums[tid];
+    __syncthreads();
+  } else {  // fixed order: slice-major over CTAs, then slices in order
     const int c = tid & (kVals - 1), slice = tid / kVals;
     constexpr int kSlices = kThreads / kVals;
     double s = 0.0;
@@ -359,6 +395,16 @@ struct b200_o3d {
   O3dState* d_state = nullptr;
   O3dState* h_state = nullptr;  // pinned
   cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+  // partition (one slab of a larger map)
+  int own_axis = -1;
+  float own_lo = 0.f, own_hi = 0.f;
+  int* d_gid = nullptr;
+  // stepwise run
+  O3dParams p;
+  int blocks = 0;
+  cudaStream_t run_stream = nullptr;
+  bool running = false;
+  int launches = 0;
 };
 
 extern "C" {
@@ -409,7 +455,7 @@ void b200_o3d_destroy(b200_o3d* h) {
     DeviceGuard dg(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     cudaFree(h->d_src); cudaFree(h->d_src_n); cudaFree(h->d_stage3); cudaFree(h->d_ids); cudaFree(h->d_dists);
-    cudaFree(h->d_partials); cudaFree(h->d_state);
+    cudaFree(h->d_partials); cudaFree(h->d_state); cudaFree(h->d_gid);
     cudaFreeHost(h->h_state);
     for (int i = 0; i < 3; ++i)
       if (h->ev[i]) cudaEventDestroy(h->ev[i]);
@@ -439,18 +485,39 @@ int b200_o3d_set_target(b200_o3d* h, const float* tgt4xM, const float* tgtn3xM, 
   std::memset(&opts, 0, sizeof(opts));
   opts.cell_size = h->prm.cell_size;
   B200_TRY(index_build(h->map, &opts));   // no mean-centring: Open3D registers in the callers' frame
+  B200_CUDA(cudaStreamSynchronize(s));
+  cudaFree(h->d_gid);
+  h->d_gid = nullptr;
+  h->own_axis = -1;
   h->target_ready = true;
   return B200_OK;
 }
 
-int b200_o3d_register(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16,
-                      b200_o3d_result* res) {
-  if (!h || N <= 0 || !src4xN || !res) { set_error("b200_o3d_register: bad arguments"); return B200_E_BAD_PARAM; }
-  if (!h->target_ready) { set_error("b200_o3d_register: no target set"); return B200_E_NOT_INITIALIZED; }
+int b200_o3d_set_partition(b200_o3d* h, int axis, float lo, float hi, const int32_t* gid_M) {
+  if (!h || axis < -1 || axis > 2) { set_error("b200_o3d_set_partition: bad arguments"); return B200_E_BAD_PARAM; }
+  if (!h->target_ready) { set_error("b200_o3d_set_partition: set the slab as target first"); return B200_E_NOT_INITIALIZED; }
+  if (axis >= 0 && !(lo < hi)) { set_error("b200_o3d_set_partition: empty ownership interval"); return B200_E_BAD_PARAM; }
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  cudaFree(h->d_gid);
+  h->d_gid = nullptr;
+  h->own_axis = axis; h->own_lo = lo; h->own_hi = hi;
+  if (axis >= 0 && gid_M) {
+    const size_t bytes = (size_t)h->map.M * sizeof(int32_t);
+    B200_CUDA(cudaMalloc(&h->d_gid, bytes));
+    B200_CUDA(cudaMemcpy(h->d_gid, gid_M, bytes, cudaMemcpyHostToDevice));
+  }
+  return B200_OK;
+}
+
+int b200_o3d_begin(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16, void* stream) {
+  if (!h || N <= 0 || !src4xN) { set_error("b200_o3d_begin: bad arguments"); return B200_E_BAD_PARAM; }
+  if (!h->target_ready) { set_error("b200_o3d: no target set"); return B200_E_NOT_INITIALIZED; }
   if (h->prm.kind == 2 && !srcn3xN) { set_error("b200_o3d: generalized ICP needs source normals (covariances are derived from them)"); return B200_E_BAD_PARAM; }
   DeviceGuard dg(h->device);
   if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
-  cudaStream_t s = h->stream;
+  cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+  h->running = false;
   if ((size_t)N > h->cap_src) {
     cudaFree(h->d_src); cudaFree(h->d_src_n); cudaFree(h->d_stage3); cudaFree(h->d_ids); cudaFree(h->d_dists);
     h->d_src = h->d_src_n = nullptr; h->d_stage3 = nullptr; h->d_ids = nullptr; h->d_dists = nullptr;
@@ -469,7 +536,7 @@ int b200_o3d_register(b200_o3d* h, const float* src4xN, const float* srcn3xN, in
   std::memset(h->h_state, 0, sizeof(O3dState));
   for (int i = 0; i < 16; ++i) h->h_state->T[i] = init16 ? init16[i] : ((i % 5 == 0) ? 1.0 : 0.0);
   B200_CUDA(cudaMemcpyAsync(h->d_state, h->h_state, sizeof(O3dState), cudaMemcpyHostToDevice, s));
-  O3dParams p;
+  O3dParams& p = h->p;
   std::memset(&p, 0, sizeof(p));
   p.g = h->map.view();
   p.src = h->d_src;
@@ -479,14 +546,48 @@ int b200_o3d_register(b200_o3d* h, const float* src4xN, const float* srcn3xN, in
   p.max_iteration = h->prm.max_iteration;
   p.rel_fitness = h->prm.relative_fitness; p.rel_rmse = h->prm.relative_rmse; p.eps = h->prm.gicp_epsilon;
   p.ids = h->d_ids; p.dists = h->d_dists; p.partials = h->d_partials; p.st = h->d_state;
-  const int blocks = std::max(1, std::min(h->max_blocks, (N + kThreads - 1) / kThreads));
+  p.own_axis = h->own_axis; p.own_lo = h->own_lo; p.own_hi = h->own_hi; p.gid = h->d_gid;
+  h->blocks = std::max(1, std::min(h->max_blocks, (N + kThreads - 1) / kThreads));
+  h->run_stream = s;
+  h->launches = srcn3xN ? 1 : 0;
   B200_CUDA(cudaEventRecord(h->ev[1], s));
-  // max_iteration updates need max_iteration + 1 matches; launches after `done` return at once
-  for (int it = 0; it <= h->prm.max_iteration; ++it) {
-    o3d_match_lin_kernel<<<blocks, kThreads, 0, s>>>(p);
-    o3d_solve_kernel<<<1, kThreads, 0, s>>>(p, blocks);
-  }
+  h->running = true;
+  return B200_OK;
+}
+
+int b200_o3d_step_linearize(b200_o3d* h, double* d_sums32) {
+  if (!h || !h->running || !d_sums32) { set_error("b200_o3d_step_linearize: no registration begun"); return B200_E_NOT_INITIALIZED; }
+  DeviceGuard dg(h->device);
+  o3d_match_lin_kernel<<<h->blocks, kThreads, 0, h->run_stream>>>(h->p);
+  o3d_reduce_kernel<<<1, kThreads, 0, h->run_stream>>>(h->p, h->blocks, d_sums32);
+  h->launches += 2;
   B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+int b200_o3d_step_update(b200_o3d* h, const double* d_sums32) {
+  if (!h || !h->running || !d_sums32) { set_error("b200_o3d_step_update: no registration begun"); return B200_E_NOT_INITIALIZED; }
+  DeviceGuard dg(h->device);
+  o3d_solve_kernel<<<1, kThreads, 0, h->run_stream>>>(h->p, h->blocks, d_sums32);
+  h->launches += 1;
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+int b200_o3d_poll(b200_o3d* h, int* done, int* updates) {
+  if (!h || !h->running) { set_error("b200_o3d_poll: no registration begun"); return B200_E_NOT_INITIALIZED; }
+  DeviceGuard dg(h->device);
+  B200_CUDA(cudaMemcpyAsync(h->h_state, h->d_state, sizeof(O3dState), cudaMemcpyDeviceToHost, h->run_stream));
+  B200_CUDA(cudaStreamSynchronize(h->run_stream));
+  if (done) *done = h->h_state->done;
+  if (updates) *updates = h->h_state->updates;
+  return B200_OK;
+}
+
+int b200_o3d_finish(b200_o3d* h, b200_o3d_result* res) {
+  if (!h || !h->running || !res) { set_error("b200_o3d_finish: no registration begun"); return B200_E_NOT_INITIALIZED; }
+  DeviceGuard dg(h->device);
+  cudaStream_t s = h->run_stream;
   B200_CUDA(cudaEventRecord(h->ev[2], s));
   B200_CUDA(cudaMemcpyAsync(h->h_state, h->d_state, sizeof(O3dState), cudaMemcpyDeviceToHost, s));
   B200_CUDA(cudaStreamSynchronize(s));
@@ -496,10 +597,26 @@ int b200_o3d_register(b200_o3d* h, const float* src4xN, const float* srcn3xN, in
   res->inlier_rmse = h->h_state->rmse;
   res->iterations = h->h_state->updates;
   res->n_correspondences = h->h_state->n_corr;
-  res->kernel_launches = 2 * (h->prm.max_iteration + 1) + (srcn3xN ? 1 : 0);
+  res->kernel_launches = h->launches;
   B200_CUDA(cudaEventElapsedTime(&res->device_ms, h->ev[1], h->ev[2]));
   B200_CUDA(cudaEventElapsedTime(&res->total_ms, h->ev[0], h->ev[2]));
   return B200_OK;
+}
+
+int b200_o3d_register(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16,
+                      b200_o3d_result* res) {
+  if (!res) { set_error("b200_o3d_register: bad arguments"); return B200_E_BAD_PARAM; }
+  if (h && h->own_axis >= 0) { set_error("b200_o3d_register: the target is one slab of a partitioned map; drive it with begin/step/finish"); return B200_E_BAD_PARAM; }
+  B200_TRY(b200_o3d_begin(h, src4xN, srcn3xN, N, init16, nullptr));
+  DeviceGuard dg(h->device);
+  // max_iteration updates need max_iteration + 1 matches; launches after `done` return at once
+  for (int it = 0; it <= h->prm.max_iteration; ++it) {
+    o3d_match_lin_kernel<<<h->blocks, kThreads, 0, h->run_stream>>>(h->p);
+    o3d_solve_kernel<<<1, kThreads, 0, h->run_stream>>>(h->p, h->blocks, nullptr);
+  }
+  h->launches += 2 * (h->prm.max_iteration + 1);
+  B200_CUDA(cudaGetLastError());
+  return b200_o3d_finish(h, res);
 }
 
 int b200_o3d_get_correspondences(b200_o3d* h, int32_t* ids_N, float* dists_N) {

@@ -1,0 +1,140 @@
+"""Spatially partitioned map registration (BASELINE config C5): the map is cut into one slab per
+rank along its longest horizontal axis, every slab is padded by a halo of the correspondence distance, the scan is
+replicated, and per ICP iteration the ranks exchange ONE allreduce of 32 doubles (JtJ, Jtr, correspondence count,
+sum of squared distances). Every rank then applies the same update redundantly — no broadcast.
+
+Exactness: a source point is answered by exactly one rank (the one whose un-padded interval [lo, hi) holds its
+transformed coordinate), and every map point within the correspondence distance of it lies inside that rank's padded
+slab, so the union of the ranks' correspondences is the single-device result (ids are global, ties go to the smallest
+global index because slabs keep the map order).
+
+The loop semantics are boundary B's (Open3D RegistrationICP: 1-NN within max_correspondence_distance, no global
+quantile); libpointmatcher's TrimmedDist would need two extra histogram allreduces per iteration and is not offered in
+this mode (stated deviation).
+"""
+import numpy as np
+
+from . import capi as B
+
+N_SUMS = 32
+
+
+def plan_slabs(map_xyz, n_slabs, axis=None):
+    """-> (axis, edges): edges has n_slabs + 1 float32 entries, edges[0] = -inf, edges[-1] = +inf; slab g owns
+    coordinates in [edges[g], edges[g + 1]). Cuts at equal point counts along the longest horizontal axis."""
+    xyz = np.asarray(map_xyz, np.float32)[:, :3]
+    if axis is None:
+        ext = xyz[:, :2].max(0) - xyz[:, :2].min(0)
+        axis = int(np.argmax(ext))
+    c = xyz[:, axis]
+    edges = np.empty(n_slabs + 1, np.float32)
+    edges[0], edges[-1] = -np.inf, np.inf
+    if n_slabs > 1:
+        qs = np.arange(1, n_slabs) * (c.size / n_slabs)
+        part = np.partition(c, qs.astype(np.int64))
+        edges[1:-1] = part[qs.astype(np.int64)]
+    if np.any(np.diff(edges) <= 0):
+        raise ValueError("degenerate slabs: too many identical coordinates along axis %d" % axis)
+    return axis, edges
+
+
+def halo_width(max_dist, coord_scale):
+    """halo that is safe against the float32 rounding of the distance test: a neighbour accepted with a computed
+    squared distance <= max_dist^2 is never more than this far along one axis"""
+    return np.float32(max_dist * (1.0 + 1e-5) + 4e-7 * coord_scale)
+
+
+def slab_members(map_xyz, axis, edges, g, max_dist):
+    """global indices (ascending) of the map points in slab g's padded interval"""
+    c = np.asarray(map_xyz, np.float32)[:, axis]
+    h = halo_width(max_dist, float(np.abs(c).max()) if c.size else 0.0)
+    return np.flatnonzero((c >= edges[g] - h) & (c < edges[g + 1] + h)).astype(np.int32)
+
+
+class SlabICP:
+    """One rank's share: the padded slab as target of a device registration handle, plus the loop that alternates the
+    device steps with an allreduce. `allreduce(tensor)` sums a CUDA double tensor of N_SUMS entries over the ranks in
+    place on the current stream (torch.distributed.all_reduce with NCCL); None = single slab."""
+
+    def __init__(self, slab4, slab_normals, gid, axis, lo, hi, kind=B.O3D_POINT_TO_PLANE, max_correspondence_distance=1.0,
+                 max_iteration=30, relative_fitness=1e-6, relative_rmse=1e-6, device=0, allreduce=None, poll_every=4):
+        import torch
+        self.torch = torch
+        self.device = device
+        self.h = B.O3dICP(kind=kind, max_correspondence_distance=max_correspondence_distance,
+                          max_iteration=max_iteration, relative_fitness=relative_fitness, relative_rmse=relative_rmse,
+                          device=device)
+        self.h.set_target(slab4, slab_normals)
+        self.h.set_partition(axis, lo, hi, gid)
+        self.max_iteration = max_iteration
+        self.allreduce = allreduce
+        self.poll_every = max(1, int(poll_every))
+        self.sums = torch.zeros(N_SUMS, dtype=torch.float64, device="cuda:%d" % device)
+        self.collectives = 0
+
+    def register(self, src4, src_normals=None, init=None):
+        torch = self.torch
+        with torch.cuda.device(self.device):
+            # torch's default stream is the legacy NULL stream: name it explicitly (cudaStreamLegacy == 0x1), a NULL
+            # argument would select the handle's own stream and lose the ordering with the allreduce
+            stream = torch.cuda.current_stream().cuda_stream or 1
+            self.h.begin(src4, src_normals, init, stream=stream)
+            ptr = self.sums.data_ptr()
+            self.collectives = 0
+            for it in range(self.max_iteration + 1):
+                self.h.step_linearize(ptr)
+                if self.allreduce is not None:
+                    self.allreduce(self.sums)
+                    self.collectives += 1
+                self.h.step_update(ptr)
+                # every rank sees the same totals, so `done` flips on the same iteration everywhere
+                if (it + 1) % self.poll_every == 0 and self.h.poll()[0]:
+                    break
+            res = self.h.finish()
+        res["collectives"] = self.collectives
+        return res
+
+    def correspondences(self):
+        """(ids, squared dists) of the last match; ids are global map indices, -1 no neighbour, -2 another rank's point"""
+        return self.h.correspondences()
+
+    def close(self):
+        self.h.close()
+
+
+def merge_correspondences(ids_list):
+    """union of the per-slab id arrays (each source point is owned by exactly one slab)"""
+    ids = np.stack(ids_list)
+    owners = (ids != -2).sum(0)
+    if not (owners == 1).all():
+        raise AssertionError("ownership is not a partition: %d points with %s owners" % ((owners != 1).sum(), set(owners[owners != 1])))
+    return ids.max(0)
+
+
+def register_partitioned(map4, map_normals, src4, src_normals=None, init=None, dist=None, device=None, **kw):
+    """Driver for one process per GPU: every rank passes the same map (or at least its own slab's points in map
+    order), builds its slab and runs the loop with an NCCL allreduce. dist = torch.distributed (initialised) or None."""
+    import torch
+    world = dist.get_world_size() if dist is not None else 1
+    rank = dist.get_rank() if dist is not None else 0
+    if device is None:
+        device = rank % max(1, torch.cuda.device_count())
+    axis, edges = plan_slabs(map4, world)
+    md = kw.get("max_correspondence_distance", 1.0)
+    gid = slab_members(map4, axis, edges, rank, md)
+    ar = None
+    if world > 1:
+        def ar(t):
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    slab = SlabICP(np.ascontiguousarray(map4[gid]), None if map_normals is None else np.ascontiguousarray(map_normals[gid]),
+                   gid, axis, float(edges[rank]), float(edges[rank + 1]), device=device, allreduce=ar, **kw)
+    res = slab.register(src4, src_normals, init)
+    ids, _ = slab.correspondences()
+    if world > 1:
+        t = torch.from_numpy(ids).to("cuda:%d" % device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ids = t.cpu().numpy()
+    res["ids"] = ids
+    res["slab_points"] = int(gid.size)
+    slab.close()
+    return res
