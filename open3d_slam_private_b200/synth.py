@@ -180,3 +180,93 @@ def make_c2(M=5_000_000, N=131072, n_poses=32, seed=SEED, scene_kw=None):
         T_init = T_true @ perturbation(i)
         scans.append(dict(xyz=pts, T_true=T_true, T_init=T_init.astype(np.float32)))
     return dict(scene=sc, map_xyz=map_xyz, map_normals=map_n, scans=scans)
+
+
+# ------------------------------------------------------------------------------------------- C4: submap pairs
+def make_c4(n_distinct=8, N=200_000, seed=SEED):
+    """BASELINE config C4 (loop-closure candidates): n_distinct source/target submap pairs of N points each — two
+    dense views of the same street from sensor poses ~1.5 m apart, both in their own sensor frame, with the true
+    relative transform. A batch of 256 cycles through them."""
+    sc = Scene(seed=seed + 3)
+    rng = np.random.default_rng(seed + 91)
+    pairs = []
+    for i in range(n_distinct):
+        x, y = rng.uniform(-sc.length / 2 + 25, sc.length / 2 - 25), rng.uniform(-sc.width / 2 + 5, sc.width / 2 - 5)
+        yaw = rng.uniform(-np.pi, np.pi)
+        a, Ta = sc.scan((x, y, yaw), n_points=N, rings=128, seed=100 + 2 * i)
+        b, Tb = sc.scan((x + rng.uniform(-1.5, 1.5), y + rng.uniform(-1.0, 1.0), yaw + rng.uniform(-0.05, 0.05)),
+                        n_points=N, rings=128, seed=101 + 2 * i)
+        T_true = np.linalg.inv(Ta) @ Tb          # source (b) -> target (a) frame
+        pairs.append(dict(tgt_xyz=a, src_xyz=b, T_true=T_true, T_init=T_true @ perturbation(300 + i, 0.15, 1.0)))
+    return pairs
+
+
+# ------------------------------------------------------------------------------------------- C5: tiled city map
+class TiledStreet:
+    """A street made of `n_tiles` street-canyon scenes of equal length laid end to end along x. Tile g is Scene(seed
+    + 100 + g) shifted to x in [g L - L/2, g L + L/2). Each rank of the partitioned mode materialises only its own tile
+    and the halo strips of its two neighbours."""
+
+    def __init__(self, n_tiles, seed=SEED, **scene_kw):
+        self.n = int(n_tiles)
+        self.tiles = [Scene(seed=seed + 100 + g, **scene_kw) for g in range(self.n)]
+        self.L = self.tiles[0].length
+        self.width = self.tiles[0].width
+
+    def edges(self):
+        e = np.empty(self.n + 1, np.float32)
+        e[0], e[-1] = -np.inf, np.inf
+        for g in range(1, self.n):
+            e[g] = np.float32(g * self.L - self.L / 2)
+        return e
+
+    def tile_points(self, g, m_per_tile):
+        xyz, nrm = self.tiles[g].sample_map(m_per_tile, seed=SEED + 1 + g)
+        xyz[:, 0] += np.float32(g * self.L)
+        return xyz, nrm
+
+    def slab(self, g, m_per_tile, halo):
+        """-> (xyz, normals, gid) of tile g padded by the neighbours' points within `halo` of its borders; gid =
+        tile index * m_per_tile + index inside the tile, ascending"""
+        e = self.edges()
+        parts = []
+        for t in (g - 1, g, g + 1):
+            if t < 0 or t >= self.n:
+                continue
+            xyz, nrm = self.tile_points(t, m_per_tile)
+            gid = np.arange(t * m_per_tile, (t + 1) * m_per_tile, dtype=np.int64)
+            keep = (xyz[:, 0] >= e[g] - halo) & (xyz[:, 0] < e[g + 1] + halo)
+            parts.append((xyz[keep], nrm[keep], gid[keep]))
+        xyz = np.concatenate([p[0] for p in parts])
+        nrm = np.concatenate([p[1] for p in parts])
+        gid = np.concatenate([p[2] for p in parts])
+        if gid.max() >= 2 ** 31:
+            raise ValueError("global ids exceed int32")
+        return np.ascontiguousarray(xyz), np.ascontiguousarray(nrm), gid.astype(np.int32)
+
+    def raycast(self, origin, dirs, max_range=100.0):
+        t = np.full(dirs.shape[0], np.inf)
+        for g, sc in enumerate(self.tiles):
+            if abs(origin[0] - g * self.L) > self.L / 2 + max_range:
+                continue
+            o = origin.copy()
+            o[0] -= g * self.L
+            t = np.minimum(t, sc.raycast(o, dirs, max_range))
+        return t
+
+    def scan(self, pose_xyyaw, **kw):
+        proxy = Scene.__new__(Scene)     # reuse Scene.scan's beam pattern with this street's ray caster
+        proxy.raycast = self.raycast
+        return Scene.scan(proxy, pose_xyyaw, **kw)
+
+
+def make_c5_scans(street, n_poses=4, N=131072):
+    """scans taken astride the border between the two middle tiles (both neighbours own part of every scan)"""
+    rng = np.random.default_rng(SEED + 177)
+    xb = (street.n // 2) * street.L - street.L / 2 if street.n > 1 else 0.0
+    out = []
+    for i in range(n_poses):
+        pose = (xb + rng.uniform(-3, 3), rng.uniform(-street.width / 2 + 4, street.width / 2 - 4), rng.uniform(-np.pi, np.pi))
+        pts, T_true = street.scan(pose, n_points=N, seed=700 + i)
+        out.append(dict(xyz=pts, T_true=T_true, T_init=T_true @ perturbation(700 + i)))
+    return out
