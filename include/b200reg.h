@@ -56,6 +56,9 @@ typedef struct {
 int b200_index_create(b200_index** out, int device, const float* ref4xM, const float* normals3xM, int M,
                       const b200_index_opts* opts);
 void b200_index_destroy(b200_index* idx);
+/* Re-initialise an existing index with a new cloud (KDTreeMatcher::init on the next reference, Mapper.cpp:329-347's
+ * periodic rebuild; also the per-scan cloud whose normals are wanted): device buffers are reused when large enough. */
+int b200_index_update(b200_index* idx, const float* ref4xM, const float* normals3xM, int M, const b200_index_opts* opts);
 /* KDTreeMatcher::findClosests(filteredReading) — MatchersImpl.cpp:85-102. epsilon is accepted for interface
  * compatibility; the search is always exact (the exact answer satisfies every epsilon). maxDistPerPoint (1 x N,
  * nullable) reproduces KDTreeVarDistMatcher (MatchersImpl.cpp:133-150). visit_count (nullable) receives the number
@@ -81,6 +84,10 @@ typedef struct {
 int b200_surface_normals(int device, const float* feat4xN, int N, const b200_surface_normal_params* prm,
                          float* normals3xN, float* densities1xN, float* eigValues3xN, float* eigVectors9xN,
                          float* matchedIds_kxN, float* meanDists1xN);
+/* SurfaceNormalDataPointsFilter::inPlaceFilter (SurfaceNormal.cpp:112-262) of the indexed cloud itself, outputs as
+ * b200_surface_normals above; with a kept index (b200_index_update per scan) nothing is allocated per call. */
+int b200_index_self_normals(b200_index* idx, const b200_surface_normal_params* prm, float* normals, float* densities,
+                            float* eigValues, float* eigVectors, float* matchedIds, float* meanDists);
 
 /* ------------------------------------------------------------------------------------------------------------
  * OutlierFilter — replaces OutlierFiltersImpl<float>::{MaxDist,MinDist,MedianDist,TrimmedDist,SurfaceNormal}

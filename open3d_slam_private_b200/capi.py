@@ -165,6 +165,24 @@ class Index:
         self.visit_counter += vis.value
         return ids, d
 
+    def update(self, ref4, normals=None, cell_size=0.0, target_per_cell=0.0, max_cells=0):
+        """re-initialise with a new cloud, reusing the device buffers"""
+        self.ref4, self.normals = f32(ref4), f32(normals)
+        opts = IndexOpts(cell_size, target_per_cell, max_cells)
+        _check(load().b200_index_update(self.h, _fp(self.ref4), _fp(self.normals), self.ref4.shape[0], C.byref(opts)))
+
+    def self_normals(self, knn=5, max_dist=np.inf, sort_eigen=0, keep=("normals",)):
+        """SurfaceNormalDataPointsFilter over the indexed cloud itself"""
+        n = self.ref4.shape[0]
+        shapes = dict(normals=(n, 3), densities=(n,), eigValues=(n, 3), eigVectors=(n, 9), matchedIds=(n, knn),
+                      meanDists=(n,))
+        out = {k_: (np.empty(shapes[k_], np.float32) if k_ in keep else None) for k_ in shapes}
+        prm = SurfaceNormalParams(knn, max_dist, 0.0, sort_eigen, 0)
+        _check(load().b200_index_self_normals(self.h, C.byref(prm), _fp(out["normals"]), _fp(out["densities"]),
+                                              _fp(out["eigValues"]), _fp(out["eigVectors"]), _fp(out["matchedIds"]),
+                                              _fp(out["meanDists"])))
+        return {k_: v for k_, v in out.items() if v is not None}
+
     def info(self):
         cell = C.c_float()
         dims = (C.c_int32 * 3)()

@@ -86,6 +86,9 @@ struct b200_index {
   float* d_mdpp = nullptr;
   unsigned long long* d_visited = nullptr;
   size_t cap_q = 0, cap_kq = 0;
+  // outputs of b200_index_self_normals (grown on demand, kept between calls)
+  float* d_sn = nullptr;
+  size_t cap_sn = 0;
 };
 
 extern "C" {
@@ -138,12 +141,27 @@ int b200_index_create(b200_index** out, int device, const float* ref4xM, const f
   return B200_OK;
 }
 
+int b200_index_update(b200_index* h, const float* ref4xM, const float* normals3xM, int M, const b200_index_opts* opts) {
+  if (!h || M < 0 || (M > 0 && !ref4xM)) { set_error("b200_index_update: bad arguments"); return B200_E_BAD_PARAM; }
+  DeviceGuard dg(h->map.device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  B200_TRY(index_alloc_points(h->map, M, normals3xM != nullptr));
+  B200_TRY(upload_features(h->map.d_ref, ref4xM, M, h->stream));
+  if (normals3xM && M > 0) {
+    Tmp stage;
+    B200_TRY(stage.alloc((size_t)M * 3 * sizeof(float), h->stream));
+    B200_TRY(upload_normals(h->map.d_nrm_orig, normals3xM, M, stage.as<float>(), h->stream));
+  }
+  return index_build(h->map, opts);
+}
+
 void b200_index_destroy(b200_index* h) {
   if (!h) return;
   {
     DeviceGuard dg(h->map.device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     cudaFree(h->d_q); cudaFree(h->d_ids); cudaFree(h->d_dists); cudaFree(h->d_mdpp); cudaFree(h->d_visited);
+    cudaFree(h->d_sn);
     h->map.release();
     if (h->stream) cudaStreamDestroy(h->stream);
   }
@@ -208,10 +226,8 @@ int b200_index_info(const b200_index* h, float* cell_size, int32_t dims[3], int6
 // =================================================================================================================
 extern "C" {
 
-int b200_surface_normals(int device, const float* feat4xN, int N, const b200_surface_normal_params* prm,
-                         float* normals, float* densities, float* eigValues, float* eigVectors, float* matchedIds,
-                         float* meanDists) {
-  if (!prm || N < 0 || (N > 0 && !feat4xN)) { set_error("b200_surface_normals: bad arguments"); return B200_E_BAD_PARAM; }
+static int check_sn_params(const b200_surface_normal_params* prm) {
+  if (!prm) { set_error("b200_surface_normals: bad arguments"); return B200_E_BAD_PARAM; }
   if (prm->knn < 3) { set_error("SurfaceNormalDataPointsFilter: knn must be >= 3"); return B200_E_BAD_PARAM; }
   if (prm->knn > 64) { set_error("SurfaceNormal knn > 64 is not supported"); return B200_E_UNSUPPORTED; }
   if (prm->smoothNormals) {
@@ -219,33 +235,50 @@ int b200_surface_normals(int device, const float* feat4xN, int N, const b200_sur
     set_error("smoothNormals = 1 is not supported by the B200 filter");
     return B200_E_UNSUPPORTED;
   }
+  return B200_OK;
+}
+
+int b200_index_self_normals(b200_index* h, const b200_surface_normal_params* prm, float* normals, float* densities,
+                            float* eigValues, float* eigVectors, float* matchedIds, float* meanDists) {
+  if (!h) { set_error("b200_index_self_normals: bad arguments"); return B200_E_BAD_PARAM; }
+  B200_TRY(check_sn_params(prm));
+  const int N = h->map.M, k = prm->knn;
+  if (N == 0) return B200_OK;
+  DeviceGuard dg(h->map.device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  cudaStream_t s = h->stream;
+  // one grown-on-demand buffer, carved per requested output
+  const size_t cnt[6] = {normals ? (size_t)3 * N : 0, densities ? (size_t)N : 0, eigValues ? (size_t)3 * N : 0,
+                         eigVectors ? (size_t)9 * N : 0, matchedIds ? (size_t)k * N : 0, meanDists ? (size_t)N : 0};
+  size_t total = 0;
+  for (size_t c : cnt) total += c;
+  if (total > h->cap_sn) {
+    cudaFree(h->d_sn);
+    h->d_sn = nullptr; h->cap_sn = 0;
+    B200_CUDA(cudaMalloc(&h->d_sn, total * sizeof(float)));
+    h->cap_sn = total;
+  }
+  float* dp[6];
+  size_t off = 0;
+  for (int i = 0; i < 6; ++i) { dp[i] = cnt[i] ? h->d_sn + off : nullptr; off += cnt[i]; }
+  B200_TRY(surface_normals_device(h->map.view(), h->map.d_ref, N, k, prm->maxDist, prm->sortEigen, dp[0], dp[1], dp[2],
+                                  dp[3], dp[4], dp[5], s));
+  float* host[6] = {normals, densities, eigValues, eigVectors, matchedIds, meanDists};
+  for (int i = 0; i < 6; ++i)
+    if (host[i]) B200_TRY(d2h(host[i], dp[i], cnt[i] * sizeof(float), s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  return B200_OK;
+}
+
+int b200_surface_normals(int device, const float* feat4xN, int N, const b200_surface_normal_params* prm,
+                         float* normals, float* densities, float* eigValues, float* eigVectors, float* matchedIds,
+                         float* meanDists) {
+  if (N < 0 || (N > 0 && !feat4xN)) { set_error("b200_surface_normals: bad arguments"); return B200_E_BAD_PARAM; }
+  B200_TRY(check_sn_params(prm));
   if (N == 0) return B200_OK;
   b200_index* idx = nullptr;
   B200_TRY(b200_index_create(&idx, device, feat4xN, nullptr, N, nullptr));
-  DeviceGuard dg(device);
-  cudaStream_t s = idx->stream;
-  const int k = prm->knn;
-  int st = B200_OK;
-  {
-    Tmp tn, td, tv, te, tm, tmd;
-    auto need = [&](Tmp& t, float* host, size_t count) { return host ? t.alloc(count * sizeof(float), s) : (int)B200_OK; };
-    if (!st) st = need(tn, normals, (size_t)3 * N);
-    if (!st) st = need(td, densities, (size_t)N);
-    if (!st) st = need(tv, eigValues, (size_t)3 * N);
-    if (!st) st = need(te, eigVectors, (size_t)9 * N);
-    if (!st) st = need(tm, matchedIds, (size_t)k * N);
-    if (!st) st = need(tmd, meanDists, (size_t)N);
-    if (!st)
-      st = surface_normals_device(idx->map.view(), idx->map.d_ref, N, k, prm->maxDist, prm->sortEigen, tn.as<float>(),
-                                  td.as<float>(), tv.as<float>(), te.as<float>(), tm.as<float>(), tmd.as<float>(), s);
-    if (!st && normals) st = d2h(normals, tn.p, (size_t)3 * N * sizeof(float), s);
-    if (!st && densities) st = d2h(densities, td.p, (size_t)N * sizeof(float), s);
-    if (!st && eigValues) st = d2h(eigValues, tv.p, (size_t)3 * N * sizeof(float), s);
-    if (!st && eigVectors) st = d2h(eigVectors, te.p, (size_t)9 * N * sizeof(float), s);
-    if (!st && matchedIds) st = d2h(matchedIds, tm.p, (size_t)k * N * sizeof(float), s);
-    if (!st && meanDists) st = d2h(meanDists, tmd.p, (size_t)N * sizeof(float), s);
-    if (!st && cudaStreamSynchronize(s) != cudaSuccess) st = cuda_fail(cudaGetLastError(), "sync", __FILE__, __LINE__);
-  }
+  const int st = b200_index_self_normals(idx, prm, normals, densities, eigValues, eigVectors, matchedIds, meanDists);
   b200_index_destroy(idx);
   return st;
 }

@@ -334,7 +334,10 @@ int index_build(MapIndex& idx, const b200_index_opts* opts) {
   DeviceGuard dg(idx.device);
   if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
   const float target = (opts && opts->target_per_cell > 0.f) ? opts->target_per_cell : 3.0f;
-  const uint64_t max_cells = (opts && opts->max_cells > 0) ? opts->max_cells : (uint64_t)1 << 29;
+  // default cap on the dense table: 2^29 cells, and no more than 64 cells per point (>= 2^22) — a small cloud in a
+  // large bounding box (a raw scan) must not pay for clearing and scanning a table a thousand times its own size
+  const uint64_t auto_cap = std::min<uint64_t>((uint64_t)1 << 29, std::max<uint64_t>((uint64_t)1 << 22, 64ull * (uint64_t)std::max(idx.M, 1)));
+  const uint64_t max_cells = (opts && opts->max_cells > 0) ? opts->max_cells : auto_cap;
   cudaEvent_t e0, e1;
   B200_CUDA(cudaEventCreate(&e0));
   B200_CUDA(cudaEventCreate(&e1));

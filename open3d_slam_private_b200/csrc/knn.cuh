@@ -410,4 +410,181 @@ __device__ inline void knn_query_warp1(const GridView& g, bool active, float qx,
   }
 }
 
+// ---- 2 <= k <= 32, one warp per query ---------------------------------------------------------------------------
+// The k-best list lives across the warp: lane j holds the j-th best (d, id, sorted position), ascending in (d, id)
+// — the reference's order (ties -> smallest index). Candidates arrive 32 at a time, one per lane: when only a few of
+// them beat the current k-th best they are inserted one by one (ballot + shift), otherwise the batch is sorted with a
+// bitonic network and merged (min(L[i], C[31 - i]) + bitonic merge). Empty slots carry (inf, INT_MAX, -1).
+constexpr int kNoId = 0x7fffffff;
+
+__device__ __forceinline__ bool key_less(float d, int id, float od, int oid) { return d < od || (d == od && id < oid); }
+
+__device__ __forceinline__ void warp_cmpx(float& d, int& id, int& sp, int j, bool keep_min) {
+  const float od = __shfl_xor_sync(0xffffffffu, d, j);
+  const int oid = __shfl_xor_sync(0xffffffffu, id, j);
+  const int osp = __shfl_xor_sync(0xffffffffu, sp, j);
+  const bool oless = key_less(od, oid, d, id);
+  if (keep_min == oless) { d = od; id = oid; sp = osp; }   // equal keys only occur between empty slots
+}
+
+struct WarpKList {
+  float d; int id; int sp;        // this lane's element
+  float kth_d; int kth_id;        // element kq - 1 (warp-uniform)
+  int kq;
+  __device__ __forceinline__ void init(int kq_) { d = INFINITY; id = kNoId; sp = -1; kth_d = INFINITY; kth_id = kNoId; kq = kq_; }
+  __device__ __forceinline__ void refresh() {
+    kth_d = __shfl_sync(0xffffffffu, d, kq - 1);
+    kth_id = __shfl_sync(0xffffffffu, id, kq - 1);
+  }
+  // all 32 lanes call; has = this lane carries a candidate
+  __device__ __forceinline__ void offer(bool has, float cd, int cid, int csp) {
+    const int lane = threadIdx.x & 31;
+    has = has && cd != INFINITY && key_less(cd, cid, kth_d, kth_id);
+    unsigned m = __ballot_sync(0xffffffffu, has);
+    if (m == 0u) return;
+    if (__popc(m) <= 6) {
+      while (m) {
+        const int src = __ffs(m) - 1;
+        m &= m - 1u;
+        const float bd = __shfl_sync(0xffffffffu, cd, src);
+        const int bid = __shfl_sync(0xffffffffu, cid, src);
+        const int bsp = __shfl_sync(0xffffffffu, csp, src);
+        if (!key_less(bd, bid, kth_d, kth_id)) continue;   // the k-th best moved meanwhile (warp-uniform test)
+        const int pos = __popc(__ballot_sync(0xffffffffu, key_less(d, id, bd, bid)));   // list sorted: a prefix
+        const float ud = __shfl_up_sync(0xffffffffu, d, 1);
+        const int uid = __shfl_up_sync(0xffffffffu, id, 1);
+        const int usp = __shfl_up_sync(0xffffffffu, sp, 1);
+        if (lane > pos) { d = ud; id = uid; sp = usp; }
+        else if (lane == pos) { d = bd; id = bid; sp = bsp; }
+        refresh();
+      }
+      return;
+    }
+    if (!has) { cd = INFINITY; cid = kNoId; csp = -1; }
+#pragma unroll
+    for (int k = 2; k <= 32; k <<= 1)
+#pragma unroll
+      for (int j = k >> 1; j > 0; j >>= 1) warp_cmpx(cd, cid, csp, j, ((lane & j) == 0) == ((lane & k) == 0));
+    const float rd = __shfl_sync(0xffffffffu, cd, 31 - lane);
+    const int rid = __shfl_sync(0xffffffffu, cid, 31 - lane);
+    const int rsp = __shfl_sync(0xffffffffu, csp, 31 - lane);
+    if (key_less(rd, rid, d, id)) { d = rd; id = rid; sp = rsp; }
+#pragma unroll
+    for (int j = 16; j > 0; j >>= 1) warp_cmpx(d, id, sp, j, (lane & j) == 0);
+    refresh();
+  }
+};
+
+// candidate ranges of one row (iy, iz) of box B for a query: like scan_row, but only resolves the (at most two)
+// ranges of sorted positions; n0 / n1 = their lengths
+__device__ __forceinline__ void row_ranges(const GridView& g, const QueryGeom& q, const CellBox& B, const CellBox& P,
+                                           float rc, int iy, int iz, uint32_t& a0, uint32_t& n0, uint32_t& a1,
+                                           uint32_t& n1) {
+  a0 = a1 = n0 = n1 = 0u;
+  int xa = B.x0, xb = B.x1;
+  if (rc != INFINITY) {
+    const float dy = fmaxf(fmaxf((float)iy - q.uy, q.uy - (float)(iy + 1)) - q.slack, 0.f);
+    const float dz = fmaxf(fmaxf((float)iz - q.uz, q.uz - (float)(iz + 1)) - q.slack, 0.f);
+    const float rem = rc * rc - dy * dy - dz * dz;
+    if (rem < 0.f) return;
+    const float xh = sqrtf(rem) * 1.00001f + q.slack;
+    int lo, hi;
+    axis_range(q.ux, xh, g.nx, lo, hi);
+    xa = max(xa, lo); xb = min(xb, hi);
+    if (xa > xb) return;
+  }
+  const uint32_t* row = g.G + ((size_t)g.nx * ((size_t)iy + (size_t)g.ny * (size_t)iz));
+  if (P.x0 <= P.x1 && iy >= P.y0 && iy <= P.y1 && iz >= P.z0 && iz <= P.z1) {
+    const int e1 = min(xb, P.x0 - 1), s2 = max(xa, P.x1 + 1);
+    if (xa <= e1) { a0 = __ldg(row + xa); n0 = __ldg(row + e1 + 1) - a0; }
+    if (s2 <= xb) { a1 = __ldg(row + s2); n1 = __ldg(row + xb + 1) - a1; }
+  } else {
+    a0 = __ldg(row + xa);
+    n0 = __ldg(row + xb + 1) - a0;
+  }
+}
+
+// All 32 lanes call with the SAME query. On return lane j holds the j-th nearest neighbour (d = inf, id = -1 when
+// there is none); lanes >= kq hold leftovers that must be ignored.
+__device__ inline void knn_query_warpk(const GridView& g, float qx, float qy, float qz, float md2, int kq,
+                                       float& out_d, int& out_id, int& out_sp, unsigned& visited) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  WarpKList L;
+  L.init(kq);
+  QueryGeom q;
+  const bool valid = make_geom(g, qx, qy, qz, md2, q);
+  if (valid && (fabsf(q.ux) > 1.0e9f || fabsf(q.uy) > 1.0e9f || fabsf(q.uz) > 1.0e9f)) {
+    // absurdly far query (cell arithmetic no longer resolves cells): scan everything, still exact
+    for (uint32_t base = 0; base < (uint32_t)g.M; base += 32u) {
+      const uint32_t j = base + lane;
+      bool has = j < (uint32_t)g.M;
+      float d = INFINITY; int id = kNoId;
+      if (has) {
+        const float4 p = __ldg(&g.pts[j]);
+        d = dist2_rn(qx, qy, qz, p.x, p.y, p.z);
+        id = __float_as_int(p.w);
+        has = d <= md2;
+      }
+      L.offer(has, d, id, (int)j);
+    }
+    if (lane == 0) visited += (unsigned)g.M;
+  } else if (valid) {
+    float h = first_halfwidth(g, q);
+    CellBox P;
+    P.x0 = P.y0 = P.z0 = 1; P.x1 = P.y1 = P.z1 = 0;
+    while (true) {
+      const CellBox B = ball_box(g, q.ux, q.uy, q.uz, h + q.slack);
+      const int nrows = B.rows(), ny = B.ny();
+      for (int rb = 0; rb < nrows; rb += 32) {
+        const float rc = need_radius(g, q, L.kth_d);   // shrinks while the scan finds closer points
+        uint32_t a0 = 0, n0 = 0, a1 = 0, n1 = 0;
+        const int r = rb + lane;
+        if (r < nrows) row_ranges(g, q, B, P, rc, B.y0 + r % ny, B.z0 + r / ny, a0, n0, a1, n1);
+        const uint32_t tot = n0 + n1;
+        uint32_t incl = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t v = __shfl_up_sync(FULL, incl, o);
+          if (lane >= o) incl += v;
+        }
+        const uint32_t total = __shfl_sync(FULL, incl, 31);
+        if (lane == 0) visited += total;
+        for (uint32_t base = 0; base < total; base += 32u) {
+          const uint32_t t = base + lane;
+          // owner row of candidate t: the first lane whose inclusive prefix exceeds t
+          int lo = 0;
+#pragma unroll
+          for (int step = 16; step > 0; step >>= 1) {
+            const uint32_t v = __shfl_sync(FULL, incl, lo + step - 1);
+            if (v <= t) lo += step;
+          }
+          lo = min(lo, 31);
+          const uint32_t o_incl = __shfl_sync(FULL, incl, lo), o_tot = __shfl_sync(FULL, tot, lo);
+          const uint32_t o_a0 = __shfl_sync(FULL, a0, lo), o_n0 = __shfl_sync(FULL, n0, lo), o_a1 = __shfl_sync(FULL, a1, lo);
+          bool has = t < total;
+          float d = INFINITY; int id = kNoId; int sp = -1;
+          if (has) {
+            const uint32_t k = t - (o_incl - o_tot);
+            const uint32_t j = k < o_n0 ? o_a0 + k : o_a1 + (k - o_n0);
+            const float4 p = __ldg(&g.pts[j]);
+            d = dist2_rn(qx, qy, qz, p.x, p.y, p.z);
+            id = __float_as_int(p.w);
+            sp = (int)j;
+            has = d <= md2;
+          }
+          L.offer(has, d, id, sp);
+        }
+      }
+      if (!B.empty()) P = B;
+      const float need = need_radius(g, q, L.kth_d);
+      if (h >= need || covers_grid(g, B)) break;
+      h = next_halfwidth(h, need);
+    }
+  }
+  out_d = L.d;
+  out_id = L.d == INFINITY ? -1 : L.id;
+  out_sp = L.d == INFINITY ? -1 : L.sp;
+}
+
 }  // namespace b200

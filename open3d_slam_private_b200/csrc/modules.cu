@@ -60,6 +60,43 @@ __global__ void __launch_bounds__(kThreads) knn_kernel(const __grid_constant__ G
   if (visited && (threadIdx.x & 31) == 0 && vis_total) atomicAdd(visited, vis_total);
 }
 
+// 2 <= kq <= 32: one warp per query, the k-best list spread over the lanes (knn_query_warpk)
+__global__ void __launch_bounds__(kThreads) knn_warpk_kernel(const __grid_constant__ GridView g,
+                                                             const float4* __restrict__ query, int N, int kq, float md2,
+                                                             const float* __restrict__ mdpp, int32_t* __restrict__ ids,
+                                                             float* __restrict__ dists,
+                                                             unsigned long long* __restrict__ visited) {
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+  unsigned long long vis_total = 0ull;
+  for (int i = warp; i < N; i += nwarps) {
+    const float4 q = __ldg(&query[i]);
+    float m2 = md2;
+    if (mdpp) {  // KDTreeVarDistMatcher: per-point radius
+      const float r = __ldg(&mdpp[i]);
+      m2 = isinf(r) ? INFINITY : __fmul_rn(r, r);
+    }
+    unsigned vis = 0;
+    float d; int id, sp;
+    knn_query_warpk(g, q.x, q.y, q.z, m2, kq, d, id, sp, vis);
+    if (lane < kq) {
+      ids[(size_t)i * kq + lane] = id;
+      dists[(size_t)i * kq + lane] = d;
+    }
+    vis_total += vis;
+  }
+  if (visited && lane == 0 && vis_total) atomicAdd(visited, vis_total);
+}
+
+int launch_knn_warpk(const GridView& g, const float4* q, int N, int kq, float md2, const float* mdpp, int32_t* ids,
+                     float* dists, unsigned long long* visited, cudaStream_t s) {
+  const int warps_per_block = kThreads / 32;
+  const int blocks = (int)std::min<long long>(((long long)N + warps_per_block - 1) / warps_per_block, 148LL * 64);
+  knn_warpk_kernel<<<std::max(1, blocks), kThreads, 0, s>>>(g, q, N, kq, md2, mdpp, ids, dists, visited);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
 template <int K>
 int launch_knn(const GridView& g, const float4* q, int N, int kq, float md2, const float* mdpp, int32_t* ids,
                float* dists, unsigned long long* visited, cudaStream_t s) {
@@ -169,10 +206,7 @@ int knn_device(const GridView& g, const float4* q, int N, int kq, float maxDist,
   if (N <= 0) return B200_OK;
   const float md2 = std::isinf(maxDist) ? INFINITY : maxDist * maxDist;
   if (kq <= 1) return launch_knn<1>(g, q, N, kq, md2, mdpp, ids, dists, visited, s);
-  if (kq <= 4) return launch_knn<4>(g, q, N, kq, md2, mdpp, ids, dists, visited, s);
-  if (kq <= 8) return launch_knn<8>(g, q, N, kq, md2, mdpp, ids, dists, visited, s);
-  if (kq <= 16) return launch_knn<16>(g, q, N, kq, md2, mdpp, ids, dists, visited, s);
-  if (kq <= 32) return launch_knn<32>(g, q, N, kq, md2, mdpp, ids, dists, visited, s);
+  if (kq <= 32) return launch_knn_warpk(g, q, N, kq, md2, mdpp, ids, dists, visited, s);
   if (kq <= 64) return launch_knn<64>(g, q, N, kq, md2, mdpp, ids, dists, visited, s);
   set_error("knn > 64 is not supported by the B200 matcher");
   return B200_E_UNSUPPORTED;
@@ -445,6 +479,67 @@ int rigid_apply_device(const float* T16, float4* feat, float* n3, int N, cudaStr
 // =================================================================================================================
 namespace {
 
+// eigen-analysis of one neighbourhood covariance and the descriptor outputs (one thread per point)
+__device__ __forceinline__ void sn_finish(int i, float4 q, const float* C, int realKnn, float maxSq, float mx, float my,
+                                          float mz, int sortEigen, float* __restrict__ normals,
+                                          float* __restrict__ dens, float* __restrict__ eigva,
+                                          float* __restrict__ eigve, float* __restrict__ meandist) {
+  la::PivQR<float, 3> qr;
+  qr.compute(C);
+  const bool degenerate = !(qr.rank() + 1 >= 3);   // :191
+  float va[3] = {0.f, 0.f, 0.f}, ve[9];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) ve[t] = 0.f;
+  if (!degenerate) {
+    double Cd[9], wd[3], Vd[9];
+    for (int t = 0; t < 9; ++t) Cd[t] = (double)C[t];
+    la::symEigen3(Cd, wd, Vd);
+    float v0[3], e0[9];
+    for (int t = 0; t < 3; ++t) v0[t] = (float)wd[t];
+    for (int t = 0; t < 9; ++t) e0[t] = (float)Vd[t];
+    int idx[3] = {0, 1, 2};
+    if (sortEigen) {  // stable ascending (sortIndexes, :199-210)
+      if (v0[idx[1]] < v0[idx[0]]) { const int t = idx[0]; idx[0] = idx[1]; idx[1] = t; }
+      if (v0[idx[2]] < v0[idx[1]]) { const int t = idx[1]; idx[1] = idx[2]; idx[2] = t; }
+      if (v0[idx[1]] < v0[idx[0]]) { const int t = idx[0]; idx[0] = idx[1]; idx[1] = t; }
+    }
+    for (int c = 0; c < 3; ++c) {
+      va[c] = v0[idx[c]];
+      for (int r = 0; r < 3; ++r) ve[r + 3 * c] = e0[r + 3 * idx[c]];
+    }
+  }
+  if (normals) {
+    int col = 0;
+    if (!sortEigen) {  // computeNormal, utils.h:131-150
+      float best = FLT_MAX;
+      for (int j = 0; j < 3; ++j)
+        if (va[j] < best) { col = j; best = va[j]; }
+    }
+    for (int r = 0; r < 3; ++r) normals[3 * (size_t)i + r] = fminf(1.f, fmaxf(-1.f, ve[r + 3 * col]));
+  }
+  if (dens) {
+    float dv = 0.f;
+    if (!degenerate) {  // computeDensity, utils.h:105-129
+      const float volume = __fmul_rn(__fmul_rn((float)(4. / 3.), (float)M_PI), __fmul_rn(maxSq, sqrtf(maxSq)));
+      dv = volume > 0.f ? (float)realKnn / volume : 0.f;
+    }
+    dens[i] = dv;
+  }
+  if (eigva) for (int r = 0; r < 3; ++r) eigva[3 * (size_t)i + r] = va[r];
+  if (eigve)
+    for (int r = 0; r < 3; ++r)
+      for (int c = 0; c < 3; ++c) eigve[9 * (size_t)i + 3 * r + c] = ve[r + 3 * c];
+  if (meandist) {
+    float md;
+    if (degenerate) md = 18446744073709551615.0f;  // float(numeric_limits<size_t>::max()), :245
+    else {
+      const float dx = __fsub_rn(q.x, mx), dy = __fsub_rn(q.y, my), dz = __fsub_rn(q.z, mz);
+      md = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+    }
+    meandist[i] = md;
+  }
+}
+
 template <int K>
 __global__ void __launch_bounds__(128) surface_normal_kernel(const __grid_constant__ GridView g,
                                                              const float4* __restrict__ feat, int N, int knn,
@@ -486,65 +581,77 @@ __global__ void __launch_bounds__(128) surface_normal_kernel(const __grid_consta
 #pragma unroll
           for (int r = 0; r < 3; ++r) C[r + 3 * c] = __fadd_rn(C[r + 3 * c], __fmul_rn(nn[r], nn[c]));
       }
-    la::PivQR<float, 3> qr;
-    qr.compute(C);
-    const bool degenerate = !(qr.rank() + 1 >= 3);   // :191
-    float va[3] = {0.f, 0.f, 0.f}, ve[9];
-#pragma unroll
-    for (int t = 0; t < 9; ++t) ve[t] = 0.f;
-    if (!degenerate) {
-      double Cd[9], wd[3], Vd[9];
-      for (int t = 0; t < 9; ++t) Cd[t] = (double)C[t];
-      la::symEigen3(Cd, wd, Vd);
-      float v0[3], e0[9];
-      for (int t = 0; t < 3; ++t) v0[t] = (float)wd[t];
-      for (int t = 0; t < 9; ++t) e0[t] = (float)Vd[t];
-      int idx[3] = {0, 1, 2};
-      if (sortEigen) {  // stable ascending (sortIndexes, :199-210)
-        if (v0[idx[1]] < v0[idx[0]]) { const int t = idx[0]; idx[0] = idx[1]; idx[1] = t; }
-        if (v0[idx[2]] < v0[idx[1]]) { const int t = idx[1]; idx[1] = idx[2]; idx[2] = t; }
-        if (v0[idx[1]] < v0[idx[0]]) { const int t = idx[0]; idx[0] = idx[1]; idx[1] = t; }
-      }
-      for (int c = 0; c < 3; ++c) {
-        va[c] = v0[idx[c]];
-        for (int r = 0; r < 3; ++r) ve[r + 3 * c] = e0[r + 3 * idx[c]];
-      }
-    }
-    if (normals) {
-      int col = 0;
-      if (!sortEigen) {  // computeNormal, utils.h:131-150
-        float best = FLT_MAX;
-        for (int j = 0; j < 3; ++j)
-          if (va[j] < best) { col = j; best = va[j]; }
-      }
-      for (int r = 0; r < 3; ++r) normals[3 * (size_t)i + r] = fminf(1.f, fmaxf(-1.f, ve[r + 3 * col]));
-    }
-    if (dens) {
-      float dv = 0.f;
-      if (!degenerate) {  // computeDensity, utils.h:105-129
-        const float volume = __fmul_rn(__fmul_rn((float)(4. / 3.), (float)M_PI), __fmul_rn(maxSq, sqrtf(maxSq)));
-        dv = volume > 0.f ? (float)realKnn / volume : 0.f;
-      }
-      dens[i] = dv;
-    }
-    if (eigva) for (int r = 0; r < 3; ++r) eigva[3 * (size_t)i + r] = va[r];
-    if (eigve)
-      for (int r = 0; r < 3; ++r)
-        for (int c = 0; c < 3; ++c) eigve[9 * (size_t)i + 3 * r + c] = ve[r + 3 * c];
-    if (meandist) {
-      float md;
-      if (degenerate) md = 18446744073709551615.0f;  // float(numeric_limits<size_t>::max()), :245
-      else {
-        const float dx = __fsub_rn(q.x, mx), dy = __fsub_rn(q.y, my), dz = __fsub_rn(q.z, mz);
-        md = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
-      }
-      meandist[i] = md;
-    }
+    sn_finish(i, q, C, realKnn, maxSq, mx, my, mz, sortEigen, normals, dens, eigva, eigve, meandist);
     if (matched) {
 #pragma unroll
       for (int j = 0; j < K; ++j)
         if (j < knn) matched[(size_t)i * knn + j] = (float)L.id[j];
     }
+  }
+}
+
+// knn <= 32: a warp takes 32 consecutive points. Phase 1, one point at a time: warp-cooperative k-NN (list across
+// the lanes), mean and covariance accumulated in LIST ORDER with the same float operations as the per-thread kernel
+// (lanes 0..8 own one covariance entry each); the 9 entries move to the lane that owns the point. Phase 2: every lane
+// finishes its own point (rank test, eigen-decomposition, outputs).
+__global__ void __launch_bounds__(128) surface_normal_warp_kernel(const __grid_constant__ GridView g,
+                                                                  const float4* __restrict__ feat, int N, int knn,
+                                                                  float md2, int sortEigen, float* __restrict__ normals,
+                                                                  float* __restrict__ dens, float* __restrict__ eigva,
+                                                                  float* __restrict__ eigve, float* __restrict__ matched,
+                                                                  float* __restrict__ meandist) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+  const int er = lane % 3, ec = (lane / 3) % 3;   // covariance entry of lanes 0..8 (column-major r + 3 c)
+  for (int base = warp * 32; base < N; base += nwarps * 32) {
+    float Cm[9];
+#pragma unroll
+    for (int t = 0; t < 9; ++t) Cm[t] = 0.f;
+    int m_real = 0;
+    float m_maxSq = 0.f, m_mx = 0.f, m_my = 0.f, m_mz = 0.f;
+    float4 m_q = make_float4(0.f, 0.f, 0.f, 1.f);
+    const int cnt = min(32, N - base);
+    for (int t = 0; t < cnt; ++t) {
+      const int i = base + t;
+      const float4 q = __ldg(&feat[i]);
+      unsigned vis = 0;
+      float d; int id, sp;
+      knn_query_warpk(g, q.x, q.y, q.z, md2, knn, d, id, sp, vis);
+      const bool valid = lane < knn && d != INFINITY;
+      const int realKnn = __popc(__ballot_sync(FULL, valid));   // a prefix of the lanes (the list is sorted)
+      float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (valid) p = __ldg(&g.pts[sp]);
+      float sx = 0.f, sy = 0.f, sz = 0.f;
+      for (int j = 0; j < realKnn; ++j) {   // d.rowwise().sum() in list order (:181)
+        sx = __fadd_rn(sx, __shfl_sync(FULL, p.x, j));
+        sy = __fadd_rn(sy, __shfl_sync(FULL, p.y, j));
+        sz = __fadd_rn(sz, __shfl_sync(FULL, p.z, j));
+      }
+      const float mx = sx / (float)realKnn, my = sy / (float)realKnn, mz = sz / (float)realKnn;
+      const float nx = __fsub_rn(p.x, mx), ny = __fsub_rn(p.y, my), nz = __fsub_rn(p.z, mz);
+      float sq = __fmul_rn(nx, nx);
+      sq = __fadd_rn(sq, __fmul_rn(ny, ny));
+      sq = __fadd_rn(sq, __fmul_rn(nz, nz));
+      float maxSq = valid ? sq : 0.f;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) maxSq = fmaxf(maxSq, __shfl_xor_sync(FULL, maxSq, o));
+      float acc = 0.f;
+      for (int j = 0; j < realKnn; ++j) {
+        const float a = __shfl_sync(FULL, nx, j), b = __shfl_sync(FULL, ny, j), c = __shfl_sync(FULL, nz, j);
+        const float vr = er == 0 ? a : (er == 1 ? b : c), vc = ec == 0 ? a : (ec == 1 ? b : c);
+        acc = __fadd_rn(acc, __fmul_rn(vr, vc));
+      }
+#pragma unroll
+      for (int e = 0; e < 9; ++e) {
+        const float v = __shfl_sync(FULL, acc, e);
+        if (lane == t) Cm[e] = v;
+      }
+      if (lane == t) { m_real = realKnn; m_maxSq = maxSq; m_mx = mx; m_my = my; m_mz = mz; m_q = q; }
+      if (matched && lane < knn) matched[(size_t)i * knn + lane] = (float)id;
+    }
+    if (lane < cnt)
+      sn_finish(base + lane, m_q, Cm, m_real, m_maxSq, m_mx, m_my, m_mz, sortEigen, normals, dens, eigva, eigve, meandist);
   }
 }
 
@@ -564,11 +671,15 @@ int surface_normals_device(const GridView& g, const float4* feat, int N, int knn
                            cudaStream_t s) {
   if (N <= 0) return B200_OK;
   const float md2 = std::isinf(maxDist) ? INFINITY : maxDist * maxDist;
+  if (knn >= 2 && knn <= 32) {
+    const long long chunks = ((long long)N + 31) / 32;   // one warp per 32 points, 4 warps per block
+    const int blocks = (int)std::min<long long>((chunks + 3) / 4, 148LL * 32);
+    surface_normal_warp_kernel<<<std::max(1, blocks), 128, 0, s>>>(g, feat, N, knn, md2, sortEigen, normals, dens, eigva,
+                                                                   eigve, matched, meandist);
+    B200_CUDA(cudaGetLastError());
+    return B200_OK;
+  }
 #define B200_SN(KK) return launch_sn<KK>(g, feat, N, knn, md2, sortEigen, normals, dens, eigva, eigve, matched, meandist, s)
-  if (knn <= 4) B200_SN(4);
-  if (knn <= 8) B200_SN(8);
-  if (knn <= 16) B200_SN(16);
-  if (knn <= 32) B200_SN(32);
   if (knn <= 64) B200_SN(64);
 #undef B200_SN
   set_error("SurfaceNormal knn > 64 is not supported by the B200 filter");

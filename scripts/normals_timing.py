@@ -31,3 +31,15 @@ for name, pts in (("raw scan", scan), ("uniform crop", crop)):
     msn, _ = t(lambda: B.surface_normals(f4, knn=20))
     msn10, _ = t(lambda: B.surface_normals(f4, knn=10))
     print("%-13s surface_normals k20 wall %.2f ms, k10 %.2f ms" % (name, msn, msn10))
+
+    idx = B.Index(f4, target_per_cell=8.0)
+    for k in (10, 20):
+        def again():
+            idx.update(f4, target_per_cell=8.0)
+            return idx.self_normals(knn=k)
+        ms, out = t(again, 5)
+        ms2, _ = t(lambda: idx.self_normals(knn=k), 5)
+        ref = B.surface_normals(f4, knn=k)["normals"]
+        print("%-13s kept index: update + normals k%d wall %.2f ms; normals only %.2f ms; equal to stateless: %s"
+              % (name, k, ms, ms2, bool((out["normals"] == ref).all())))
+    idx.close()
