@@ -241,6 +241,10 @@ void b200_o3d_destroy(b200_o3d* h);
 /* target cloud with normals (estimateNormalsOrCovariancesIfNeeded has run on it, CloudRegistration.cpp:27-46);
  * normals may be NULL for kind 1 */
 int b200_o3d_set_target(b200_o3d* h, const float* tgt4xM, const float* tgtn3xM, int M);
+/* target cloud WITHOUT normals: estimateNormalsOrCovariancesIfNeeded (CloudRegistration.cpp:67-79) runs on the device
+ * against the target's own index -- knn neighbours within maxDist (IcpParameters::knn_, maxDistanceKnn_), normalised,
+ * oriented towards the origin of the cloud's frame -- and the normals never leave the device */
+int b200_o3d_set_target_estimate_normals(b200_o3d* h, const float* tgt4xM, int M, int knn, float maxDist);
 /* registerClouds(source, target, init); srcn3xN is required for kind 2 only */
 int b200_o3d_register(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16,
                       b200_o3d_result* res);

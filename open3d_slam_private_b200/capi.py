@@ -438,6 +438,10 @@ class O3dICP:
         tgt4, normals = f32(tgt4), f32(normals)
         _check(load().b200_o3d_set_target(self._h, _fp(tgt4), _fp(normals), tgt4.shape[0]))
 
+    def set_target_estimate_normals(self, tgt4, knn=10, max_dist=np.inf):
+        tgt4 = f32(tgt4)
+        _check(load().b200_o3d_set_target_estimate_normals(self._h, _fp(tgt4), tgt4.shape[0], int(knn), C.c_float(max_dist)))
+
     def register(self, src4, normals=None, init=None):
         src4, normals = f32(src4), f32(normals)
         Ti = np.eye(4) if init is None else np.asarray(init, np.float64)

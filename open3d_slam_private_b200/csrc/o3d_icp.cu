@@ -20,6 +20,7 @@
 #include "common.cuh"
 #include "grid_index.cuh"
 #include "knn.cuh"
+#include "modules.cuh"
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -376,6 +377,21 @@ __global__ void __launch_bounds__(kThreads) o3d_solve_kernel(const __grid_consta
   if (stop) st->done = 1;
 }
 
+// estimateNormalsOrCovariancesIfNeeded's post-processing (CloudRegistration.cpp:67-79): NormalizeNormals, then
+// OrientNormalsTowardsCameraLocation with the camera at the origin of the cloud's frame; in double like the host
+__global__ void __launch_bounds__(kThreads) o3d_orient_normals_kernel(const float4* __restrict__ pts,
+                                                                      const float* __restrict__ n3, int M,
+                                                                      float4* __restrict__ out) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= M) return;
+  const float4 p = __ldg(&pts[j]);
+  double v[3] = {(double)n3[3 * (size_t)j], (double)n3[3 * (size_t)j + 1], (double)n3[3 * (size_t)j + 2]};
+  const double nn = sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+  if (nn > 0.0) { v[0] /= nn; v[1] /= nn; v[2] /= nn; }
+  if (v[0] * (-(double)p.x) + v[1] * (-(double)p.y) + v[2] * (-(double)p.z) < 0.0) { v[0] = -v[0]; v[1] = -v[1]; v[2] = -v[2]; }
+  out[j] = make_float4((float)v[0], (float)v[1], (float)v[2], 0.f);
+}
+
 }  // namespace
 
 struct b200_o3d {
@@ -399,6 +415,8 @@ struct b200_o3d {
   int own_axis = -1;
   float own_lo = 0.f, own_hi = 0.f;
   int* d_gid = nullptr;
+  float* d_nstage = nullptr;   // 3 x M normals before orientation (set_target_estimate_normals)
+  size_t cap_nstage = 0;
   // stepwise run
   O3dParams p;
   int blocks = 0;
@@ -455,7 +473,7 @@ void b200_o3d_destroy(b200_o3d* h) {
     DeviceGuard dg(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     cudaFree(h->d_src); cudaFree(h->d_src_n); cudaFree(h->d_stage3); cudaFree(h->d_ids); cudaFree(h->d_dists);
-    cudaFree(h->d_partials); cudaFree(h->d_state); cudaFree(h->d_gid);
+    cudaFree(h->d_partials); cudaFree(h->d_state); cudaFree(h->d_gid); cudaFree(h->d_nstage);
     cudaFreeHost(h->h_state);
     for (int i = 0; i < 3; ++i)
       if (h->ev[i]) cudaEventDestroy(h->ev[i]);
@@ -485,6 +503,40 @@ int b200_o3d_set_target(b200_o3d* h, const float* tgt4xM, const float* tgtn3xM, 
   std::memset(&opts, 0, sizeof(opts));
   opts.cell_size = h->prm.cell_size;
   B200_TRY(index_build(h->map, &opts));   // no mean-centring: Open3D registers in the callers' frame
+  B200_CUDA(cudaStreamSynchronize(s));
+  cudaFree(h->d_gid);
+  h->d_gid = nullptr;
+  h->own_axis = -1;
+  h->target_ready = true;
+  return B200_OK;
+}
+
+int b200_o3d_set_target_estimate_normals(b200_o3d* h, const float* tgt4xM, int M, int knn, float maxDist) {
+  if (!h || M <= 0 || !tgt4xM) { set_error("b200_o3d_set_target_estimate_normals: bad arguments"); return B200_E_BAD_PARAM; }
+  if (knn < 3 || knn > 64) { set_error("b200_o3d_set_target_estimate_normals: knn must be in 3..64"); return B200_E_BAD_PARAM; }
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  h->target_ready = false;
+  cudaStream_t s = h->stream;
+  B200_TRY(index_alloc_points(h->map, M, true));
+  B200_TRY(upload_features(h->map.d_ref, tgt4xM, M, s));
+  B200_CUDA(cudaMemsetAsync(h->map.d_nrm_orig, 0, (size_t)M * sizeof(float4), s));
+  b200_index_opts opts;
+  std::memset(&opts, 0, sizeof(opts));
+  opts.cell_size = h->prm.cell_size;
+  B200_TRY(index_build(h->map, &opts));
+  if ((size_t)M > h->cap_nstage) {
+    cudaFree(h->d_nstage);
+    h->d_nstage = nullptr; h->cap_nstage = 0;
+    B200_CUDA(cudaMalloc(&h->d_nstage, (size_t)M * 3 * sizeof(float)));
+    h->cap_nstage = (size_t)M;
+  }
+  // the target's own index answers the neighbour queries; queries in cell-sorted order, so the normals land where
+  // the registration kernels read them (no second index, no host round trip)
+  B200_TRY(surface_normals_device(h->map.view(), h->map.d_pts, M, knn, maxDist, 0, h->d_nstage, nullptr, nullptr, nullptr,
+                                  nullptr, nullptr, s));
+  o3d_orient_normals_kernel<<<(M + kThreads - 1) / kThreads, kThreads, 0, s>>>(h->map.d_pts, h->d_nstage, M, h->map.d_nrm);
+  B200_CUDA(cudaGetLastError());
   B200_CUDA(cudaStreamSynchronize(s));
   cudaFree(h->d_gid);
   h->d_gid = nullptr;

@@ -41,7 +41,7 @@ class RegistrationIcpB200 {
   int device_ = 0;
 
   RegistrationIcpB200() = default;
-  ~RegistrationIcpB200() { b200_o3d_destroy(h_); }
+  ~RegistrationIcpB200() { b200_o3d_destroy(h_); b200_index_destroy(nidx_); }
   RegistrationIcpB200(const RegistrationIcpB200&) = delete;
   RegistrationIcpB200& operator=(const RegistrationIcpB200&) = delete;
 
@@ -82,7 +82,7 @@ class RegistrationIcpB200 {
   // CloudRegistration::estimateNormalsOrCovariancesIfNeeded (CloudRegistration.cpp:27-46, 67-79): skip when the
   // cloud has normals; else k-NN normals (hybrid radius = maxRadiusNormalEstimation_), normalised, flipped towards
   // the origin (OrientNormalsTowardsCameraLocation with the default camera location).
-  void estimateNormalsOrCovariancesIfNeeded(Cloud* cloud) const {
+  void estimateNormalsOrCovariancesIfNeeded(Cloud* cloud) {
     if (!cloud || (cloud->normals_.size() == cloud->points_.size() && !cloud->points_.empty())) return;
     std::vector<float> f4;
     to_feat4(cloud->points_, f4);
@@ -91,7 +91,9 @@ class RegistrationIcpB200 {
     b200_surface_normal_params prm;
     prm.knn = knnNormalEstimation_; prm.maxDist = (float)maxRadiusNormalEstimation_; prm.epsilon = 0.f;
     prm.sortEigen = 0; prm.smoothNormals = 0;
-    check(b200_surface_normals(device_, f4.data(), n, &prm, nrm.data(), nullptr, nullptr, nullptr, nullptr, nullptr));
+    if (!nidx_) check(b200_index_create(&nidx_, device_, f4.data(), nullptr, n, nullptr));
+    else check(b200_index_update(nidx_, f4.data(), nullptr, n, nullptr));   // device buffers kept between scans
+    check(b200_index_self_normals(nidx_, &prm, nrm.data(), nullptr, nullptr, nullptr, nullptr, nullptr));
     cloud->normals_.resize(n);
     for (int i = 0; i < n; ++i) {
       double v[3] = {nrm[3 * i], nrm[3 * i + 1], nrm[3 * i + 2]};
@@ -130,6 +132,7 @@ class RegistrationIcpB200 {
     check(b200_o3d_create(&h_, device_, &p));
   }
   b200_o3d* h_ = nullptr;
+  b200_index* nidx_ = nullptr;
 };
 
 }  // namespace b200o3d

@@ -145,10 +145,13 @@ struct B200SurfaceNormalDataPointsFilter : public PM::DataPointsFilter {
     if (keepMeanDist) meand.resize(1, n);
     b200_surface_normal_params prm;
     prm.knn = knn; prm.maxDist = maxDist; prm.epsilon = epsilon; prm.sortEigen = sortEigen; prm.smoothNormals = smoothNormals;
-    check<PM>(b200_surface_normals(device, cloud.features.data(), n, &prm, keepNormals ? normals.data() : nullptr,
-                                   keepDensities ? dens.data() : nullptr, keepEigenValues ? eigva.data() : nullptr,
-                                   keepEigenVectors ? eigve.data() : nullptr, keepMatchedIds ? matched.data() : nullptr,
-                                   keepMeanDist ? meand.data() : nullptr));
+    // the filter keeps its device index between scans: buffers are reused, nothing is allocated per call
+    if (!idx_) check<PM>(b200_index_create(&idx_, device, cloud.features.data(), nullptr, n, nullptr));
+    else check<PM>(b200_index_update(idx_, cloud.features.data(), nullptr, n, nullptr));
+    check<PM>(b200_index_self_normals(idx_, &prm, keepNormals ? normals.data() : nullptr,
+                                      keepDensities ? dens.data() : nullptr, keepEigenValues ? eigva.data() : nullptr,
+                                      keepEigenVectors ? eigve.data() : nullptr, keepMatchedIds ? matched.data() : nullptr,
+                                      keepMeanDist ? meand.data() : nullptr));
     // same descriptor names as SurfaceNormal.cpp:118-150
     if (keepNormals) cloud.addDescriptor("normals", normals);
     if (keepDensities) cloud.addDescriptor("densities", dens);
@@ -157,6 +160,12 @@ struct B200SurfaceNormalDataPointsFilter : public PM::DataPointsFilter {
     if (keepMatchedIds) cloud.addDescriptor("matchedIds", matched);
     if (keepMeanDist) cloud.addDescriptor("meanDists", meand);
   }
+  ~B200SurfaceNormalDataPointsFilter() override { b200_index_destroy(idx_); }
+  B200SurfaceNormalDataPointsFilter(const B200SurfaceNormalDataPointsFilter&) = delete;
+  B200SurfaceNormalDataPointsFilter& operator=(const B200SurfaceNormalDataPointsFilter&) = delete;
+
+ private:
+  b200_index* idx_ = nullptr;
 };
 
 // ---- OutlierFilters ------------------------------------------------------------------------------------------------

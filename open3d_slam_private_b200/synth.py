@@ -183,19 +183,34 @@ def make_c2(M=5_000_000, N=131072, n_poses=32, seed=SEED, scene_kw=None):
 
 
 # ------------------------------------------------------------------------------------------- C4: submap pairs
-def make_c4(n_distinct=8, N=200_000, seed=SEED):
-    """BASELINE config C4 (loop-closure candidates): n_distinct source/target submap pairs of N points each — two
-    dense views of the same street from sensor poses ~1.5 m apart, both in their own sensor frame, with the true
-    relative transform. A batch of 256 cycles through them."""
+def make_c4(n_distinct=8, N=200_000, seed=SEED, map_points=3_000_000):
+    """BASELINE config C4 (loop-closure candidates): n_distinct source/target submap pairs of N points each. A submap
+    is a voxelised map patch (uniform density, like the reference's submaps): the N map points nearest to a pose,
+    expressed in that pose's frame. Source and target come from two independent samplings of the same street, from
+    poses ~1.5 m apart, with the true relative transform. A batch of 256 cycles through them."""
     sc = Scene(seed=seed + 3)
+    map_a, _ = sc.sample_map(map_points, seed=seed + 11)
+    map_b, _ = sc.sample_map(map_points, seed=seed + 12)
     rng = np.random.default_rng(seed + 91)
+
+    def patch(points, pose):
+        x, y, yaw = pose
+        c, s_ = np.cos(yaw), np.sin(yaw)
+        T = np.eye(4)
+        T[:3, :3] = np.array([[c, -s_, 0], [s_, c, 0], [0, 0, 1.0]])
+        T[:3, 3] = [x, y, 0.0]
+        d2 = (points[:, 0] - x) ** 2 + (points[:, 1] - y) ** 2
+        keep = np.argpartition(d2, N)[:N]
+        keep.sort()
+        local = (points[keep].astype(np.float64) - T[:3, 3]) @ T[:3, :3]
+        return local.astype(np.float32), T
+
     pairs = []
     for i in range(n_distinct):
-        x, y = rng.uniform(-sc.length / 2 + 25, sc.length / 2 - 25), rng.uniform(-sc.width / 2 + 5, sc.width / 2 - 5)
+        x, y = rng.uniform(-sc.length / 2 + 40, sc.length / 2 - 40), rng.uniform(-sc.width / 2 + 5, sc.width / 2 - 5)
         yaw = rng.uniform(-np.pi, np.pi)
-        a, Ta = sc.scan((x, y, yaw), n_points=N, rings=128, seed=100 + 2 * i)
-        b, Tb = sc.scan((x + rng.uniform(-1.5, 1.5), y + rng.uniform(-1.0, 1.0), yaw + rng.uniform(-0.05, 0.05)),
-                        n_points=N, rings=128, seed=101 + 2 * i)
+        a, Ta = patch(map_a, (x, y, yaw))
+        b, Tb = patch(map_b, (x + rng.uniform(-1.5, 1.5), y + rng.uniform(-1.0, 1.0), yaw + rng.uniform(-0.05, 0.05)))
         T_true = np.linalg.inv(Ta) @ Tb          # source (b) -> target (a) frame
         pairs.append(dict(tgt_xyz=a, src_xyz=b, T_true=T_true, T_init=T_true @ perturbation(300 + i, 0.15, 1.0)))
     return pairs

@@ -132,3 +132,26 @@ def test_o3d_no_correspondences_and_errors(cars):
     with pytest.raises(B.B200Error):
         g2.register(src4)                      # generalized ICP needs source normals
     g2.close()
+
+
+def test_o3d_target_normals_estimated_on_device(cars):
+    """set_target_estimate_normals == normals from the surface-normal filter (normalised, oriented to the origin)
+    handed over by the host"""
+    tgt4, _, src4, _ = cars
+    n = B.surface_normals(tgt4, knn=10, max_dist=2.0)["normals"].astype(np.float64)
+    n /= np.maximum(np.linalg.norm(n, axis=1, keepdims=True), 1e-300)
+    flip = (n * (-tgt4[:, :3].astype(np.float64))).sum(1) < 0
+    n[flip] *= -1
+    a = B.O3dICP(kind=0, max_correspondence_distance=0.5, max_iteration=30)
+    a.set_target(tgt4, n.astype(np.float32))
+    ra = a.register(src4)
+    ia, _ = a.correspondences()
+    a.close()
+    b = B.O3dICP(kind=0, max_correspondence_distance=0.5, max_iteration=30)
+    b.set_target_estimate_normals(tgt4, knn=10, max_dist=2.0)
+    rb = b.register(src4)
+    ib, _ = b.correspondences()
+    b.close()
+    assert ra["iterations"] == rb["iterations"] and np.array_equal(ra["T"], rb["T"]) and (ia == ib).all()
+    with pytest.raises(B.B200Error):
+        B.O3dICP(kind=0).set_target_estimate_normals(tgt4, knn=2)
