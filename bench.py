@@ -34,6 +34,10 @@ BYTES_PER_QUERY_ITER = 64  # 16 query + 4 id + 4 dist + 16 mat
 METRIC = "icp_registrations_per_s_128k_scan_vs_5M_map"
 
 
+# dram bytes per launch of icp_persistent_kernel<1> on the default workload, from the committed ncu capture
+NCU_TRAFFIC_BYTES_PER_LAUNCH = 9.13e6
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -296,7 +300,11 @@ def run_b200(args):
                 "h2d_bytes_per_step": N * 16 + 64, "d2h_bytes_per_step": 160 + 256},
         "gpu_launches": launches,
         "roofline": {"kernel": "icp_persistent_kernel<1>", "bound": "hbm", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": NCU_TRAFFIC_BYTES_PER_LAUNCH,
+                     "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum, ncu --set full, "
+                                       "profiles/r01_icp_kernel_final_ncu_summary.txt (default workload only)",
+                     "limiter": "issue/latency (smsp issue active 34 %), not HBM: the touched map cells stay in L2",
+                     "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg_bytes / K, "avg_launch_ms": kern_ms / K,
                      "knn_candidate_GBps": touched * 16 / (kern_ms * 1e-3) / 1e9,
                      "candidates_per_query_iteration": touched / max(1.0, float(sum(iters)) * N)},
