@@ -38,6 +38,14 @@ METRIC = "icp_registrations_per_s_128k_scan_vs_5M_map"
 NCU_TRAFFIC_BYTES_PER_LAUNCH = 9.13e6
 
 
+
+def _iter_summary(iters):
+    """ICP iterations per timed step, summarised (the full list is as long as --steps)."""
+    it = [int(v) for v in iters]
+    if not it:
+        return {}
+    return {"mean": sum(it) / len(it), "min": min(it), "max": max(it), "first_8": it[:8]}
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -191,7 +199,7 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": v, "unit": "registrations/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": config_dict(args, {"iterations_per_step": iters}),
+        "config": config_dict(args, {"iterations_per_step": _iter_summary(iters)}),
         "cpu_baseline": {"value": v, "unit": "registrations/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "registrations/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
@@ -293,7 +301,7 @@ def run_b200(args):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": config_dict(args, {
             "l2": "kept warm" if args.no_flush else "flushed (256 MiB write) before every timed step, outside the events",
-            "iterations_per_step": iters, "max_abs_translation_error_vs_truth_m": perr,
+            "iterations_per_step": _iter_summary(iters), "max_abs_translation_error_vs_truth_m": perr,
             "map_index_build_s_incl_h2d": init_ref_s, "synthetic_generation_s": gen_s, "grid_ctas": grid,
             "timed_region_wall_s": wall_s}),
         "e2e": {"value": e2e_v, "unit": "registrations/s", "ms_per_step": e2e_ms / K,
