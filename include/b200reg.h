@@ -140,6 +140,9 @@ int b200_rigid_apply(int device, const float* T16, float* feat4xN, float* normal
  * ---------------------------------------------------------------------------------------------------------- */
 typedef struct b200_icp b200_icp;
 
+#define B200_DEGENERACY_NONE 0
+#define B200_DEGENERACY_OPTIMIZED_EQUALITY 1
+
 typedef struct {
   int knn;                       /* KDTreeMatcher.knn (1..64) */
   float epsilon;                 /* KDTreeMatcher.epsilon (accepted; exact search) */
@@ -156,6 +159,14 @@ typedef struct {
   float min_diff_rot, min_diff_trans;
   int smooth_length;
   float cell_size;               /* index option, <= 0 automatic */
+  /* degeneracyAwareness (ICP::loadAdditionalYAMLContent, ICP.cpp:575-760): B200_DEGENERACY_NONE or
+   * B200_DEGENERACY_OPTIMIZED_EQUALITY = "OptimizedEqualityConstraints" (X-ICP; ICP.cpp:629-670, the setting of
+   * open3d_slam_ros/param/icp.yaml). Needs knn = 1 and the PointToPlaneErrorMinimizer (ICP.cpp:1114). */
+  int degeneracy;
+  float xicp_enough_information;        /* enoughInformationThreshold */
+  float xicp_insufficient_information;  /* insufficientInformationThreshold */
+  float xicp_min_alignment_angle_deg;   /* point2NormalMinimalAlignmentAngleThreshold (degrees) */
+  float xicp_strong_alignment_angle_deg;/* point2NormalStrongAlignmentAngleThreshold (degrees) */
 } b200_icp_params;
 
 typedef struct {
@@ -175,6 +186,17 @@ typedef struct {
   float e2e_ms;                  /* first event .. after the device->host copy of this result (0 for run_resident) */
   int kernel_launches;           /* kernels this call launched on the device (uploads/memsets not counted) */
   int grid_ctas;                 /* CTAs of the persistent registration kernel */
+  /* X-ICP (degeneracy = B200_DEGENERACY_OPTIMIZED_EQUALITY): localizabilityXyz_/Rpy_ of the first iteration's
+   * detection (1 = kLocalizable, PointMatcher.h:602-607, 638-639) per eigenvector index; translation/rotation
+   * eigenvectors (columns, column-major 3x3, optimisation frame) after the last iteration; whether the prior was
+   * returned (ICP.cpp:1335-1341: T = T_refIn_readIn); the alignment sums over all matched pairs (double):
+   * xicp_sums[2e], [2e+1] = combined/high contribution for translation eigenvector e, [6+2e], [7+2e] for rotation
+   * eigenvector e; xicp_borderline != 0 when a sum lay within 0.5 % of a threshold that decided a flag (the reference's
+   * sequential float sum could round to the other side). */
+  int returned_prior, xicp_borderline;
+  int loc_xyz[3], loc_rpy[3];
+  float eig_t[9], eig_r[9];
+  double xicp_sums[12];
 } b200_icp_result;
 
 void b200_icp_default_params(b200_icp_params* prm); /* ICPChainBase::setDefault, ICP.cpp:100-113 */

@@ -49,6 +49,8 @@ class IcpParams(C.Structure):
         ("minimizer", C.c_int), ("max_iterations", C.c_int),
         ("use_differential", C.c_int), ("min_diff_rot", C.c_float), ("min_diff_trans", C.c_float),
         ("smooth_length", C.c_int), ("cell_size", C.c_float),
+        ("degeneracy", C.c_int), ("xicp_enough_information", C.c_float), ("xicp_insufficient_information", C.c_float),
+        ("xicp_min_alignment_angle_deg", C.c_float), ("xicp_strong_alignment_angle_deg", C.c_float),
     ]
 
 
@@ -60,6 +62,8 @@ class IcpResult(C.Structure):
         ("point_used_ratio", C.c_float), ("points_touched", C.c_uint64), ("device_ms", C.c_float),
         ("h2d_ms", C.c_float), ("total_ms", C.c_float), ("e2e_ms", C.c_float), ("kernel_launches", C.c_int),
         ("grid_ctas", C.c_int),
+        ("returned_prior", C.c_int), ("xicp_borderline", C.c_int), ("loc_xyz", C.c_int * 3), ("loc_rpy", C.c_int * 3),
+        ("eig_t", C.c_float * 9), ("eig_r", C.c_float * 9), ("xicp_sums", C.c_double * 12),
     ]
 
 
@@ -336,7 +340,12 @@ class ICP:
                    weighted_point_used_ratio=res.weighted_point_used_ratio, point_used_ratio=res.point_used_ratio,
                    points_touched=res.points_touched, device_ms=res.device_ms, h2d_ms=res.h2d_ms,
                    total_ms=res.total_ms, e2e_ms=res.e2e_ms, kernel_launches=res.kernel_launches,
-                   grid_ctas=res.grid_ctas)
+                   grid_ctas=res.grid_ctas, returned_prior=bool(res.returned_prior),
+                   xicp_borderline=bool(res.xicp_borderline), loc_xyz=np.array(res.loc_xyz[:], np.int32),
+                   loc_rpy=np.array(res.loc_rpy[:], np.int32),
+                   eig_t=np.array(res.eig_t[:], np.float32).reshape(3, 3).T.copy(),
+                   eig_r=np.array(res.eig_r[:], np.float32).reshape(3, 3).T.copy(),
+                   xicp_sums=np.array(res.xicp_sums[:], np.float64))
         if raise_on_error:
             _check(st)
         return out

@@ -24,6 +24,7 @@
 #include "icp_kernel.cuh"
 #include "knn.cuh"
 #include "solve.cuh"
+#include "xicp.cuh"
 #include <cooperative_groups.h>
 #include <algorithm>
 
@@ -51,6 +52,9 @@ struct BlockState {
   float lim_prev, delta, lo, hi, dens, step_prev;
   unsigned limit_bits;
   float H[36], b[6], x[6];
+  // X-ICP: pose that takes the matched points back to the frame the reading came in (ICP.cpp:2236)
+  float TcInv[16], R9Inv[9];
+  XicpState X;
 };
 
 constexpr int kWarps = kIcpThreads / 32;
@@ -174,8 +178,16 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     S.P = 0; S.wsum = 0.f; S.solve_info = 0;
     S.have_bracket = 0; S.try_fast = 0; S.path = 0; S.lim_prev = 0.f; S.delta = 0.25f; S.lo = 0.f; S.hi = 0.f; S.dens = 0.f; S.step_prev = 0.f;
     S.limit_bits = 0u;
+    xicp_state_init(S.X);
+    if (K == 1 && p.xicp) {
+      rigid_prepare(p.frames + 80, S.TcInv, S.R9Inv);
+      for (int j = 0; j < 3; ++j)
+        for (int i = 0; i < 3; ++i) S.X.R[i + 3 * j] = p.frames[64 + i + 4 * j];
+      if (!inv3_dev(S.X.R, S.X.Rinv)) S.X.return_prior = 1;
+    }
   }
   __syncthreads();
+  const bool xicp = (K == 1) && p.xicp && p.minimizer == 0;
   unsigned long long visited_total = 0ull;
 
   const bool stamp = (blockIdx.x == 0 && tid == 0 && p.log != nullptr);
@@ -203,7 +215,8 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     const int nslots = (p.N + 31) >> 5;
     const int rounds = (nslots + (nthreads >> 5) - 1) / (nthreads >> 5);  // grid-uniform trip count
     // single-barrier shape for this iteration? (needs the previous limit when TrimmedDist is in the chain)
-    const bool fast = (K == 1) && p.fast_path && p.minimizer == 0 && (!p.use_trimmed || (S.have_bracket && S.try_fast));
+    const bool fast = (K == 1) && p.fast_path && p.minimizer == 0 && (!p.use_trimmed || (S.have_bracket && S.try_fast)) &&
+                      !(xicp && S.iteration == 0);
     const float br_lo = p.use_trimmed ? S.lo : INFINITY, br_hi = p.use_trimmed ? S.hi : INFINITY;
     double role_acc = 0.0;    // thread (value v = tid / 16, segment = tid % 16) sums value v over 32 threads
     unsigned cand_base = 0u;  // candidates this CTA has parked so far
@@ -644,6 +657,14 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
           const double s27 = warp_sum((double)v[27]), s28 = warp_sum((double)v[28]);
           if (lane == 0) { s_red[wid][27] += s27; s_red[wid][28] += s28; }
         }
+        if (xicp && S.iteration == 0) {
+          // calculatePointCloudCenter (ICP.cpp:1594-1618) of the matched reading points in the frame the reading came
+          // in: sums in double here, sequential float in the reference
+          float4 pb = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (kept) pb = apply_T(S.TcInv, q);
+          const double cx = warp_sum((double)pb.x), cy = warp_sum((double)pb.y), cz = warp_sum((double)pb.z);
+          if (lane == 0) { s_red[wid][29] += cx; s_red[wid][30] += cy; s_red[wid][31] += cz; }
+        }
       }
     }
     __syncthreads();
@@ -672,6 +693,115 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     }
     }  // !have_totals
     __syncthreads();
+    // ---------------- X-ICP: eigen-analysis, first-iteration detection (one more pass + barrier) ----------------
+    if (xicp) {
+      const int P0 = (int)(s_tot[27] + 0.5);
+      if (tid == 0 && P0 != 0) {
+        XicpState& X = S.X;
+        S.P = P0;
+        int t = 0;
+        for (int c = 0; c < 6; ++c)
+          for (int r = 0; r <= c; ++r) {
+            const float h = (float)s_tot[t++];
+            S.H[r + 6 * c] = h; S.H[c + 6 * r] = h;
+          }
+        bool allZero = true;
+        for (int i = 0; i < 36; ++i) allZero = allZero && (S.H[i] == 0.f);
+        if (allZero) X.return_prior = 1;                                   // ICP.cpp:2197-2201
+        else {
+          if (X.repeat_eigen) xicp_eigen_analysis(S.H, X.Ut, X.Ur);        // :2205-2210
+          bool zt = true, zr = true;
+          for (int i = 0; i < 9; ++i) { zt = zt && (X.Ut[i] == 0.f); zr = zr && (X.Ur[i] == 0.f); }
+          if (zt || zr) X.return_prior = 1;                                // :2212-2219
+        }
+        if (!X.return_prior && S.iteration == 0) {
+          for (int c = 0; c < 3; ++c) {                                    // :2248-2267
+            mul3v_dev(X.Rinv, X.Ur + 3 * c, X.UrB + 3 * c);
+            mul3v_dev(X.Rinv, X.Ut + 3 * c, X.UtB + 3 * c);
+          }
+          for (int d = 0; d < 3; ++d) X.center[d] = (float)(s_tot[29 + d] / (double)P0);
+        }
+      }
+      __syncthreads();
+      if (P0 != 0 && S.X.return_prior) {   // ICP.cpp:1117-1121, 1175-1179: leave the loop before the minimiser
+        if (tid == 0) S.iterate = 0;
+        __syncthreads();
+        break;
+      }
+      if (P0 != 0 && S.iteration == 0) {
+        // alignment of every matched pair with the six eigenvectors (ICP.cpp:2270-2385)
+        for (int t = tid; t < kWarps * kAccum; t += kIcpThreads) (&s_red[0][0])[t] = 0.0;
+        __syncthreads();
+        const float cmin = p.x_cos_min, cstr = p.x_cos_strong;
+        for (int slot = gtid >> 5; slot < nslots; slot += nthreads >> 5) {
+          const int i = lane * nslots + (int)(((unsigned)slot + (unsigned)lane * 97u) % (unsigned)nslots);
+          double acc[12];
+#pragma unroll
+          for (int t = 0; t < 12; ++t) acc[t] = 0.0;
+          if (i < p.N) {
+            const float d = p.dists[i], w = p.weights[i];
+            const int sp = p.spos[i];
+            if (d != INFINITY && w != 0.f && sp >= 0) {
+              const float4 q = apply_T(S.Tc, __ldg(&p.reading[i]));
+              const float4 n4 = __ldg(&p.g.nrm[sp]);
+              const float4 pb = apply_T(S.TcInv, q);
+              const float3 nb = apply_R(S.R9Inv, make_float3(n4.x, n4.y, n4.z));
+              const float ax = pb.x - S.X.center[0], ay = pb.y - S.X.center[1], az = pb.z - S.X.center[2];
+              float c0 = ay * nb.z - az * nb.y, c1 = az * nb.x - ax * nb.z, c2 = ax * nb.y - ay * nb.x;
+              const float nn = sqrtf(c0 * c0 + c1 * c1 + c2 * c2);
+              if (!(nn < 1.0f)) { c0 /= nn; c1 /= nn; c2 /= nn; }          // :2283-2291
+#pragma unroll
+              for (int e = 0; e < 3; ++e) {
+                const float* vt = S.X.UtB + 3 * e;
+                const float* vr = S.X.UrB + 3 * e;
+                const float at = fabsf(nb.x * vt[0] + nb.y * vt[1] + nb.z * vt[2]);
+                const float ar = fabsf(c0 * vr[0] + c1 * vr[1] + c2 * vr[2]);
+                if (at > cmin) acc[2 * e] = (double)at;
+                if (at > cstr) acc[2 * e + 1] = (double)at;
+                if (ar > cmin) acc[6 + 2 * e] = (double)ar;
+                if (ar > cstr) acc[7 + 2 * e] = (double)ar;
+              }
+            }
+          }
+#pragma unroll
+          for (int t = 0; t < 12; ++t) {
+            const double sv = warp_sum(acc[t]);
+            if (lane == 0) s_red[wid][t] += sv;
+          }
+        }
+        __syncthreads();
+        if (tid < 16) {
+          double sv = 0.0;
+          for (int w2 = 0; w2 < kWarps; ++w2) sv += s_red[w2][tid];
+          __stcg(&p.partials2[(size_t)blockIdx.x * 16 + tid], sv);
+        }
+        grid.sync();
+        if (tid < 12) {
+          double sv = 0.0;
+          for (unsigned b = 0; b < gridDim.x; ++b) sv += __ldcg(&p.partials2[(size_t)b * 16 + tid]);
+          S.X.sums[tid] = sv;
+        }
+        __syncthreads();
+        if (tid == 0) {
+          XicpState& X = S.X;
+          for (int e = 0; e < 3; ++e) {
+            X.loc_xyz[e] = xicp_decide(X.sums[2 * e], X.sums[2 * e + 1], p.x_enough, p.x_insufficient, &X.borderline);
+            X.cT[e] = X.loc_xyz[e] ? 1.f : 0.f;
+            X.loc_rpy[e] = xicp_decide(X.sums[6 + 2 * e], X.sums[7 + 2 * e], p.x_enough, p.x_insufficient, &X.borderline);
+            X.cR[e] = X.loc_rpy[e] ? 1.f : 0.f;
+          }
+          for (int c = 0; c < 3; ++c) {                                    // :2389-2411 back to the optimisation frame
+            mul3v_dev(X.R, X.UrB + 3 * c, X.Ur + 3 * c);
+            mul3v_dev(X.R, X.UtB + 3 * c, X.Ut + 3 * c);
+          }
+          X.repeat_eigen = 0;                                              // :2415-2429
+          for (int i = 0; i < 3; ++i)
+            if (X.loc_xyz[i] == 0 || X.loc_rpy[i] == 0) X.repeat_eigen = 1;
+        }
+        __syncthreads();
+      }
+    }
+    const int n_constr = xicp ? xicp_num_constraints(S.X) : 0;
     if (wid == 0) {
       // lane 0 forms H and b; the whole warp solves (solve6_warp); lane 0 updates the pose and runs the checkers
       if (lane == 0) {
@@ -694,7 +824,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
       unsigned long long tsub[5] = {0ull, 0ull, 0ull, 0ull, 0ull};
       if (stamp) tsub[0] = gtimer();
       bool fast = false;
-      if (S.P != 0 && p.minimizer == 0) fast = solve6_warp(S.H, S.b, S.x, &s_red[1][0]);
+      if (S.P != 0 && p.minimizer == 0 && n_constr == 0) fast = solve6_warp(S.H, S.b, S.x, &s_red[1][0]);
       __syncwarp();
      if (lane == 0) {
       const double* a = s_tot;
@@ -707,6 +837,8 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
       } else {
         if (p.minimizer == 0) {
           if (fast) S.solve_info = 0;
+          else if (n_constr > 0)   // equality-constrained (KKT) system, PointToPlane.cpp:461-505
+            xicp_solve(S.H, S.b, S.X, S.x, &S.solve_info, *reinterpret_cast<KktScratch*>(s_dyn));
           else solve6_dev(S.H, S.b, S.x, &S.solve_info);  // rank-deficient / borderline systems: serial reference path
           if (stamp) tsub[1] = gtimer();
           p2plane_T_dev(S.x, real);
@@ -809,6 +941,10 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     const float denom = (float)((long long)p.k * (long long)p.N);
     o->weighted_point_used_ratio = S.wsum / denom;   // ErrorMinimizer.cpp:139-140
     o->point_used_ratio = (float)S.P / denom;
+    o->returned_prior = S.X.return_prior; o->xicp_borderline = S.X.borderline;
+    for (int i = 0; i < 3; ++i) { o->loc_xyz[i] = S.X.loc_xyz[i]; o->loc_rpy[i] = S.X.loc_rpy[i]; }
+    for (int i = 0; i < 9; ++i) { o->eig_t[i] = S.X.Ut[i]; o->eig_r[i] = S.X.Ur[i]; }
+    for (int i = 0; i < 12; ++i) o->xicp_sums[i] = S.X.sums[i];
   }
 }
 

@@ -43,7 +43,9 @@ __global__ void __launch_bounds__(kMeanThreads) read_sum_kernel(const float4* __
 
 // frames[0..15] = T_refIn_refMean (set at initReference); this kernel fills
 // frames[16..31] = T_refMean_readMean = T_refIn_refMean^-1 * T_init * T_readIn_readMean (ICP.cpp:983)
-// frames[32..47] = T_readIn_readMean (ICP.cpp:968-970), frames[48..50] = reading centroid
+// frames[32..47] = T_readIn_readMean (ICP.cpp:968-970), frames[48..50] = reading centroid,
+// frames[64..79] = T_refMean_dataIn = T_refIn_refMean^-1 * T_init (ICP.cpp:975), frames[80..95] = its inverse
+// (transformationToOptimizationFrame.inverse() of the X-ICP detection, ICP.cpp:2236)
 __global__ void frames_kernel(const double* __restrict__ partials, int nblocks, int N, const float* __restrict__ Tinit,
                               float* __restrict__ frames) {
   // one warp: lane l sums blocks l, l + 32, ... (fixed order), then a fixed shuffle tree
@@ -66,6 +68,9 @@ __global__ void frames_kernel(const double* __restrict__ partials, int nblocks, 
   mul4_dev(tmp, Tread, Tpre);
   for (int t = 0; t < 16; ++t) { frames[16 + t] = Tpre[t]; frames[32 + t] = Tread[t]; }
   for (int d = 0; d < 3; ++d) frames[48 + d] = mean[d];
+  float tinv[16];
+  if (!inv4_dev(tmp, tinv)) eye4(tinv);
+  for (int t = 0; t < 16; ++t) { frames[64 + t] = tmp[t]; frames[80 + t] = tinv[t]; }
 }
 
 // reading.features.topRows(3).colwise() -= mean (ICP.cpp:973), then transformations.apply(reading,
@@ -98,6 +103,8 @@ __global__ void flush_kernel(float4* __restrict__ buf, size_t n, float v) {
 
 }  // namespace
 
+constexpr int kFrameFloats = 96;
+
 struct b200_icp {
   int device = 0;
   b200_icp_params prm;
@@ -118,13 +125,13 @@ struct b200_icp {
   size_t cap_cand = 0;
   int fast_path = 1;  // env B200_ICP_FAST=0 forces the general iteration
   unsigned* d_hist = nullptr;
-  double *d_partials = nullptr, *d_meanpart = nullptr;
+  double *d_partials = nullptr, *d_partials2 = nullptr, *d_meanpart = nullptr;
   IcpDeviceResult* d_out = nullptr;
   IcpLogEntry* d_log = nullptr;
   float *d_frames = nullptr, *d_Tinit = nullptr;
   // pinned host mirrors
   IcpDeviceResult* h_out = nullptr;
-  float* h_frames = nullptr;  // 64 floats
+  float* h_frames = nullptr;  // kFrameFloats floats
   float* h_Tinit = nullptr;
   cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
   int upload_launches = 0;
@@ -141,13 +148,14 @@ namespace {
 int icp_alloc_fixed(b200_icp* h) {
   B200_CUDA(cudaMalloc(&h->d_hist, (size_t)2 * 3 * kHistBins * sizeof(unsigned)));
   B200_CUDA(cudaMalloc(&h->d_partials, icp_partials_capacity(h->device) * sizeof(double)));
+  B200_CUDA(cudaMalloc(&h->d_partials2, icp_partials_capacity(h->device) * sizeof(double)));
   B200_CUDA(cudaMalloc(&h->d_meanpart, (size_t)3 * 1024 * sizeof(double)));
   B200_CUDA(cudaMalloc(&h->d_out, sizeof(IcpDeviceResult)));
   B200_CUDA(cudaMalloc(&h->d_log, (size_t)kMaxLog * sizeof(IcpLogEntry)));
-  B200_CUDA(cudaMalloc(&h->d_frames, 64 * sizeof(float)));
+  B200_CUDA(cudaMalloc(&h->d_frames, kFrameFloats * sizeof(float)));
   B200_CUDA(cudaMalloc(&h->d_Tinit, 16 * sizeof(float)));
   B200_CUDA(cudaMallocHost(&h->h_out, sizeof(IcpDeviceResult)));
-  B200_CUDA(cudaMallocHost(&h->h_frames, 64 * sizeof(float)));
+  B200_CUDA(cudaMallocHost(&h->h_frames, kFrameFloats * sizeof(float)));
   B200_CUDA(cudaMallocHost(&h->h_Tinit, 16 * sizeof(float)));
   for (int i = 0; i < 5; ++i) B200_CUDA(cudaEventCreate(&h->ev[i]));
   B200_CUDA(cudaMemset(h->d_log, 0, (size_t)kMaxLog * sizeof(IcpLogEntry)));
@@ -203,6 +211,14 @@ int check_params(const b200_icp_params* p) {
     return B200_E_BAD_PARAM;
   }
   if (p->minimizer != 0 && p->minimizer != 1) { set_error("unknown error minimizer"); return B200_E_BAD_PARAM; }
+  if (p->degeneracy != B200_DEGENERACY_NONE && p->degeneracy != B200_DEGENERACY_OPTIMIZED_EQUALITY) {
+    set_error("degeneracyAwareness: only None and OptimizedEqualityConstraints are built");
+    return B200_E_UNSUPPORTED;
+  }
+  if (p->degeneracy == B200_DEGENERACY_OPTIMIZED_EQUALITY && p->knn != 1) {
+    set_error("degeneracyAwareness OptimizedEqualityConstraints: knn must be 1");
+    return B200_E_UNSUPPORTED;
+  }
   if (p->max_iterations <= 0 && !p->use_differential) {
     set_error("ICP chain needs at least one transformation checker");
     return B200_E_BAD_PARAM;
@@ -259,12 +275,18 @@ int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool tim
     p.dbg_warp = h->d_dbg_warp;
   }
   if (h->debug_stats) B200_CUDA(cudaMemsetAsync(h->d_log, 0, (size_t)kMaxLog * sizeof(IcpLogEntry), s));
+  p.xicp = h->prm.degeneracy == B200_DEGENERACY_OPTIMIZED_EQUALITY ? 1 : 0;
+  p.x_enough = h->prm.xicp_enough_information; p.x_insufficient = h->prm.xicp_insufficient_information;
+  // ICP.cpp:648-665: cos(convertAngleInDegreesToRadians(angle)) in float
+  p.x_cos_min = std::cos(h->prm.xicp_min_alignment_angle_deg * (float)M_PI / 180.f);
+  p.x_cos_strong = std::cos(h->prm.xicp_strong_alignment_angle_deg * (float)M_PI / 180.f);
+  p.partials2 = h->d_partials2;
   p.hist = h->d_hist; p.partials = h->d_partials; p.out = h->d_out; p.log = h->d_log; p.frames = h->d_frames;
   B200_CUDA(cudaEventRecord(h->ev[2], s));
   B200_TRY(launch_icp_kernel(p, h->device, s, &h->last_grid));
   B200_CUDA(cudaEventRecord(h->ev[3], s));
   B200_CUDA(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(IcpDeviceResult), cudaMemcpyDeviceToHost, s));
-  B200_CUDA(cudaMemcpyAsync(h->h_frames, h->d_frames, 64 * sizeof(float), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaMemcpyAsync(h->h_frames, h->d_frames, kFrameFloats * sizeof(float), cudaMemcpyDeviceToHost, s));
   B200_CUDA(cudaEventRecord(h->ev[4], s));
   B200_CUDA(cudaStreamSynchronize(s));
   if (res) {
@@ -279,6 +301,12 @@ int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool tim
     res->weighted_point_used_ratio = o.weighted_point_used_ratio;
     res->point_used_ratio = o.point_used_ratio;
     res->points_touched = o.points_touched;
+    res->returned_prior = o.returned_prior; res->xicp_borderline = o.xicp_borderline;
+    for (int i = 0; i < 3; ++i) { res->loc_xyz[i] = o.loc_xyz[i]; res->loc_rpy[i] = o.loc_rpy[i]; }
+    std::memcpy(res->eig_t, o.eig_t, sizeof(o.eig_t));
+    std::memcpy(res->eig_r, o.eig_r, sizeof(o.eig_r));
+    std::memcpy(res->xicp_sums, o.xicp_sums, sizeof(o.xicp_sums));
+    if (o.returned_prior) std::memcpy(res->T, h->h_Tinit, 16 * sizeof(float));   // ICP.cpp:1335-1341
     res->grid_ctas = h->last_grid;
     B200_CUDA(cudaEventElapsedTime(&res->device_ms, h->ev[2], h->ev[3]));
     float pre = 0.f;
@@ -326,6 +354,10 @@ void b200_icp_default_params(b200_icp_params* p) {
   p->max_iterations = 40;                                          // TransformationCheckersImpl.h:70
   p->use_differential = 1; p->min_diff_rot = 0.001f; p->min_diff_trans = 0.001f; p->smooth_length = 3;  // :90-92
   p->cell_size = 0.f;
+  // degeneracyAwareness absent => kNone (ICP.cpp:586-590); the thresholds below are param/icp.yaml's
+  p->degeneracy = B200_DEGENERACY_NONE;
+  p->xicp_enough_information = 250.f; p->xicp_insufficient_information = 180.f;
+  p->xicp_min_alignment_angle_deg = 80.f; p->xicp_strong_alignment_angle_deg = 45.f;
 }
 
 int b200_icp_create(b200_icp** out, int device, const b200_icp_params* prm) {
@@ -365,7 +397,7 @@ void b200_icp_destroy(b200_icp* h) {
     cudaFree(h->d_raw); cudaFree(h->d_raw_n); cudaFree(h->d_read); cudaFree(h->d_read_n); cudaFree(h->d_stage3);
     cudaFree(h->d_ids); cudaFree(h->d_spos); cudaFree(h->d_dists); cudaFree(h->d_w);
     cudaFree(h->d_cand_d); cudaFree(h->d_cand_q); cudaFree(h->d_cand_rec);
-    cudaFree(h->d_hist); cudaFree(h->d_partials); cudaFree(h->d_meanpart); cudaFree(h->d_out); cudaFree(h->d_log);
+    cudaFree(h->d_hist); cudaFree(h->d_partials); cudaFree(h->d_partials2); cudaFree(h->d_meanpart); cudaFree(h->d_out); cudaFree(h->d_log);
     cudaFree(h->d_frames); cudaFree(h->d_Tinit); cudaFree(h->d_flush); cudaFree(h->d_dbg_warp);
     cudaFreeHost(h->h_out); cudaFreeHost(h->h_frames); cudaFreeHost(h->h_Tinit);
     for (int i = 0; i < 5; ++i)
@@ -409,7 +441,7 @@ int b200_icp_init_reference(b200_icp* h, const float* ref4xM, const float* refn3
   std::memset(&opts, 0, sizeof(opts));
   opts.cell_size = h->prm.cell_size;
   B200_TRY(index_build(h->map, &opts));
-  float frames[64];
+  float frames[kFrameFloats];
   std::memset(frames, 0, sizeof(frames));
   eye4(frames);
   frames[12] = mf[0]; frames[13] = mf[1]; frames[14] = mf[2];

@@ -43,6 +43,13 @@ struct IcpDeviceResult {
   float weighted_point_used_ratio;
   float point_used_ratio;
   unsigned long long points_touched;
+  // X-ICP (IcpKernelParams::xicp): detection flags of the first iteration (1 = localizable), eigenvectors as they
+  // stand after the last iteration, full alignment sums (double), prior returned (ICP.cpp:1335-1341), and whether a
+  // decision fell inside the rounding band of the reference's sequential float sums
+  int returned_prior, xicp_borderline;
+  int loc_xyz[3], loc_rpy[3];
+  float eig_t[9], eig_r[9];
+  double xicp_sums[12];
 };
 
 struct IcpKernelParams {
@@ -68,7 +75,12 @@ struct IcpKernelParams {
   int fast_path;            // 0: always run the general 4-barrier iteration
   unsigned* dbg_warp;       // debug: per warp slot of iteration 0: {rows, candidates, passes, ns} (nullable)
   int debug_stats;          // collect IcpLogEntry::dbg_* (adds global atomics; profiling aid only)
-  const float* frames;      // 3 x 16 floats: T_refIn_refMean, T_refMean_readMean, T_readIn_readMean
+  const float* frames;      // 16-float blocks: T_refIn_refMean, T_refMean_readMean, T_readIn_readMean, (centroid),
+                            // T_refMean_dataIn (ICP.cpp:975), its inverse
+  // X-ICP, degeneracyAwareness = OptimizedEqualityConstraints (ICP.cpp:629-670); k = 1, point-to-plane only
+  int xicp;
+  float x_enough, x_insufficient, x_cos_min, x_cos_strong;
+  double* partials2;        // [gridDim.x][16]: alignment sums of the detection pass
 };
 
 // launches the persistent kernel for capacity K in {1, 4, 16} (K >= p.k); cooperative launch, grid chosen from

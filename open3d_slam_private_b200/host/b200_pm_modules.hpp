@@ -15,6 +15,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <limits>
+#include <map>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -274,6 +275,33 @@ struct B200ICP {
   ~B200ICP() { b200_icp_destroy(h_); }
   B200ICP(const B200ICP&) = delete;
   B200ICP& operator=(const B200ICP&) = delete;
+
+  // "degeneracyAwareness" node of the ICP YAML (ICP::loadAdditionalYAMLContent, ICP.cpp:575-760): method name and its
+  // string parameters, e.g. ("OptimizedEqualityConstraints", {{"enoughInformationThreshold", "250"}, ...}) as in
+  // open3d_slam_ros/param/icp.yaml. Returns false exactly where the reference's loader does (a parameter missing,
+  // ICP.cpp:636-669); methods that are not built throw InvalidParameter. Call before initReference.
+  bool setDegeneracyAwareness(const std::string& method, const std::map<std::string, std::string>& params) {
+    if (method == "None") { prm.degeneracy = B200_DEGENERACY_NONE; return true; }
+    if (method == "OptimizedEqualityConstraints") {
+      const char* keys[4] = {"enoughInformationThreshold", "insufficientInformationThreshold",
+                             "point2NormalMinimalAlignmentAngleThreshold", "point2NormalStrongAlignmentAngleThreshold"};
+      float v[4];
+      for (int i = 0; i < 4; ++i) {
+        const auto it = params.find(keys[i]);
+        if (it == params.end()) return false;
+        v[i] = std::strtof(it->second.c_str(), nullptr);
+      }
+      prm.degeneracy = B200_DEGENERACY_OPTIMIZED_EQUALITY;
+      prm.xicp_enough_information = v[0]; prm.xicp_insufficient_information = v[1];
+      prm.xicp_min_alignment_angle_deg = v[2]; prm.xicp_strong_alignment_angle_deg = v[3];
+      return true;
+    }
+    throw typename PM::InvalidParameter("degeneracyAwareness: " + method + " is not built (None, OptimizedEqualityConstraints)");
+  }
+  // LocalizabilityAnalysisResults::localizabilityXyz_/Rpy_ of the last compute (PointMatcher.h:638-639), 1 = localizable
+  void localizability(int xyz[3], int rpy[3]) const {
+    for (int i = 0; i < 3; ++i) { xyz[i] = last.loc_xyz[i]; rpy[i] = last.loc_rpy[i]; }
+  }
 
   bool initReference(const typename PM::DataPoints& referenceIn) {
     require_3d<PM>(referenceIn);

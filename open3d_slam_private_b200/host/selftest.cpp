@@ -115,6 +115,28 @@ int main() {
   PM::OutlierWeights wl;
   PM::Matches ml = icp.matches(&wl);
   EXPECT(ml.ids.cols() == 1500 && wl.cols() == 1500);
+  // ---- X-ICP (degeneracyAwareness: OptimizedEqualityConstraints, param/icp.yaml): a near-planar scene observes only
+  // the translation along its normal and the two tilts; the other three directions are held by equality constraints
+  {
+    b200pm::B200ICP<PM> xicp;
+    xicp.prm.maxDist = 0.5f; xicp.prm.trimmed_ratio = 0.9f;
+    EXPECT(!xicp.setDegeneracyAwareness("OptimizedEqualityConstraints", {{"enoughInformationThreshold", "250"}}));
+    EXPECT(xicp.setDegeneracyAwareness("OptimizedEqualityConstraints",
+                                       {{"enoughInformationThreshold", "250"},
+                                        {"insufficientInformationThreshold", "180"},
+                                        {"point2NormalMinimalAlignmentAngleThreshold", "80"},
+                                        {"point2NormalStrongAlignmentAngleThreshold", "45"}}));
+    PM::TransformationParameters Tx = xicp(read, ref);
+    int lx[3], lr[3];
+    xicp.localizability(lx, lr);
+    std::printf("X-ICP: xyz %d%d%d rpy %d%d%d tz %.5f tx %.2e ty %.2e\n", lx[0], lx[1], lx[2], lr[0], lr[1], lr[2], Tx(2, 3),
+                Tx(0, 3), Tx(1, 3));
+    EXPECT(lx[0] == 1 && lx[1] == 0 && lx[2] == 0 && lr[0] == 1 && lr[1] == 1 && lr[2] == 0);
+    EXPECT(std::fabs(Tx(2, 3) + 0.08f) < 0.01f && std::fabs(Tx(0, 3)) < 2e-3f && std::fabs(Tx(1, 3)) < 2e-3f);
+    bool threwX = false;
+    try { xicp.setDegeneracyAwareness("SolutionRemapping", {}); } catch (const PM::InvalidParameter&) { threwX = true; }
+    EXPECT(threwX);
+  }
   // ---- boundary B
   Cloud src, tgt;
   for (int i = 0; i < 1500; ++i) src.points_.push_back(V3{{read.features(0, i), read.features(1, i), read.features(2, i)}});

@@ -151,6 +151,194 @@ void meanOf(const float* feat, int N, int mode, float* mean3) {
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// X-ICP localizability, degeneracyAwareness = OptimizedEqualityConstraints (param/icp.yaml of open3d_slam_ros;
+// loadAdditionalYAMLContent ICP.cpp:629-670). State = LocalizabilityParametersForErrorMinimization
+// (PointMatcher.h:585-660), local to one computeWithTransformedReference call (ICP.cpp:921).
+// ---------------------------------------------------------------------------------------------------------------
+struct XicpState {
+  bool repeatEigen = true;      // debugging_.whetherToRepeatEigenAnalysis_ (PointMatcher.h:592)
+  bool returnPrior = false;     // debugging_.whetherToReturnPrior_ (:595)
+  float Ut[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};   // translationEigenvectors_ (:634), columns
+  float Ur[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};   // rotationEigenvectors_ (:635)
+  int locXyz[3] = {1, 1, 1};    // localizabilityXyz_ (:638), 1 = kLocalizable
+  int locRpy[3] = {1, 1, 1};
+  float cT[3] = {0, 0, 0}, cR[3] = {0, 0, 0};  // translation/rotationConstraintValues_ (:625-626)
+  double sums[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // diagnostics: full (no early exit) sums, see oracle.h
+};
+
+bool inv3(const float* A, float* Ainv) {  // Gauss-Jordan with partial pivoting (dynamic 3x3 .inverse() = PartialPivLU)
+  float M[3][6];
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) { M[i][j] = A[i + 3 * j]; M[i][3 + j] = (i == j) ? 1.f : 0.f; }
+  for (int c = 0; c < 3; ++c) {
+    int piv = c;
+    for (int r = c + 1; r < 3; ++r)
+      if (std::fabs(M[r][c]) > std::fabs(M[piv][c])) piv = r;
+    if (M[piv][c] == 0.f) return false;
+    if (piv != c)
+      for (int j = 0; j < 6; ++j) std::swap(M[piv][j], M[c][j]);
+    const float d = M[c][c];
+    for (int j = 0; j < 6; ++j) M[c][j] /= d;
+    for (int r = 0; r < 3; ++r)
+      if (r != c) {
+        const float f = M[r][c];
+        for (int j = 0; j < 6; ++j) M[r][j] -= f * M[c][j];
+      }
+  }
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) Ainv[i + 3 * j] = M[i][3 + j];
+  return true;
+}
+
+void mul3v(const float* R, float* v) {  // v <- R v (column-major 3x3)
+  float o[3];
+  for (int i = 0; i < 3; ++i) o[i] = R[i] * v[0] + R[i + 3] * v[1] + R[i + 6] * v[2];
+  v[0] = o[0]; v[1] = o[1]; v[2] = o[2];
+}
+
+// ICP::eigenAnalysis, ICP.cpp:1580-1591: U of the SVD of the translation (bottom-right) and rotation (top-left)
+// 3x3 blocks of the 6x6 Hessian, singular values descending.
+// Eigen's U is a full orthonormal basis even when the smallest singular value is exactly zero (an exactly planar
+// set of normals); the one-sided Jacobi of la_small.hpp leaves that column zero, so it is completed here.
+void completeU3(float* U, const float* S) {
+  if (S[2] == 0.f && S[1] > 0.f) {
+    U[6] = U[1] * U[5] - U[2] * U[4];
+    U[7] = U[2] * U[3] - U[0] * U[5];
+    U[8] = U[0] * U[4] - U[1] * U[3];
+  }
+}
+void xicpEigenAnalysis(const float* H, float* Ut, float* Ur) {
+  float B[9], S[3], V[9];
+  for (int j = 0; j < 3; ++j)
+    for (int i = 0; i < 3; ++i) B[i + 3 * j] = H[(3 + i) + 6 * (3 + j)];
+  orc::jacobiSVD<float, 3>(B, Ut, S, V);
+  completeU3(Ut, S);
+  for (int j = 0; j < 3; ++j)
+    for (int i = 0; i < 3; ++i) B[i + 3 * j] = H[i + 6 * j];
+  orc::jacobiSVD<float, 3>(B, Ur, S, V);
+  completeU3(Ur, S);
+}
+
+// ICP::detectLocalizability, ICP.cpp:2128-2155: sequential float sums with the early exit in the loop condition.
+// full2 (diagnostics): the two sums over ALL points, in double.
+bool xicpDetect(const float* align3xP, int P, const float* v, float cosMin, float cosStrong, float enough,
+                float insufficient, double* full2) {
+  bool ok = false;
+  float combined = 0.f, high = 0.f;
+  for (int i = 0; i < P && !ok; ++i) {
+    const float* a = align3xP + 3 * (size_t)i;
+    const float al = std::fabs(a[0] * v[0] + a[1] * v[1] + a[2] * v[2]);
+    if (al > cosMin) combined += al;
+    if (al > cosStrong) high += al;
+    ok = (combined >= enough) || (high >= insufficient);
+  }
+  if (full2) {
+    double c = 0, h = 0;
+    for (int i = 0; i < P; ++i) {
+      const float* a = align3xP + 3 * (size_t)i;
+      const float al = std::fabs(a[0] * v[0] + a[1] * v[1] + a[2] * v[2]);
+      if (al > cosMin) c += (double)al;
+      if (al > cosStrong) h += (double)al;
+    }
+    full2[0] = c; full2[1] = h;
+  }
+  return ok;
+}
+
+// ICP::detectLocalizabilityWithOptimizedMethod, ICP.cpp:2187-2444. readP (4 x P) / refnP (3 x P) are the matched
+// reading points (refMean frame) and matched reference normals of ErrorElements; T_opt = T_refMean_dataIn
+// (transformationToOptimizationFrame, ICP.cpp:1067); T_convert_from_base_to_lidar_mat is the identity (:1012-1024).
+bool xicpDetectOptimized(const orc_icp_params* prm, const float* H, const float* readP, const float* refnP, int P,
+                         const float* T_opt, bool first, XicpState& st) {
+  if (P == 0) return false;                                      // :2191
+  bool allZero = true;
+  for (int i = 0; i < 36; ++i) allZero = allZero && (H[i] == 0.f);
+  if (allZero) return false;                                     // :2197
+  if (st.repeatEigen) xicpEigenAnalysis(H, st.Ut, st.Ur);        // :2205-2210
+  bool zt = true, zr = true;
+  for (int i = 0; i < 9; ++i) { zt = zt && (st.Ut[i] == 0.f); zr = zr && (st.Ur[i] == 0.f); }
+  if (zt || zr) return false;                                    // :2212-2219
+  if (!first) return true;                                       // :2221-2226
+
+  // :2236-2240: matched points and matched normals back into the frame the reading came in
+  float Tinv[16];
+  inv4(T_opt, Tinv);
+  std::vector<float> pts(readP, readP + 4 * (size_t)P), nrm(refnP, refnP + 3 * (size_t)P);
+  orc_rigid_apply(Tinv, pts.data(), nrm.data(), P);
+  // :2248-2267: eigenvectors into the same frame
+  float R[9], Rinv[9];
+  for (int j = 0; j < 3; ++j)
+    for (int i = 0; i < 3; ++i) R[i + 3 * j] = T_opt[i + 4 * j];
+  if (!inv3(R, Rinv)) return false;
+  for (int c = 0; c < 3; ++c) { mul3v(Rinv, st.Ur + 3 * c); mul3v(Rinv, st.Ut + 3 * c); }
+  // :2270-2271 calculateCrossProductElements (:1669-1697): centre (sequential float sums, :1604-1617), cross(p - c, n)
+  float center[3] = {0.f, 0.f, 0.f};
+  for (int i = 0; i < P; ++i)
+    for (int f = 0; f < 3; ++f) center[f] += pts[4 * (size_t)i + f];
+  for (int f = 0; f < 3; ++f) center[f] /= (float)P;
+  std::vector<float> rotAlign(3 * (size_t)P);
+  for (int i = 0; i < P; ++i) {
+    const float ax = pts[4 * (size_t)i] - center[0], ay = pts[4 * (size_t)i + 1] - center[1],
+                az = pts[4 * (size_t)i + 2] - center[2];
+    const float* n = nrm.data() + 3 * (size_t)i;
+    float c[3] = {ay * n[2] - az * n[1], az * n[0] - ax * n[2], ax * n[1] - ay * n[0]};  // ErrorMinimizer.cpp:376-378
+    const float nn = std::sqrt(c[0] * c[0] + c[1] * c[1] + c[2] * c[2]);
+    if (!(nn < 1.0f)) { c[0] /= nn; c[1] /= nn; c[2] /= nn; }  // :2283-2291
+    rotAlign[3 * (size_t)i] = c[0]; rotAlign[3 * (size_t)i + 1] = c[1]; rotAlign[3 * (size_t)i + 2] = c[2];
+  }
+  // :2294-2385
+  for (int e = 0; e < 3; ++e) {
+    const bool okT = xicpDetect(nrm.data(), P, st.Ut + 3 * e, prm->xicp_cos_min, prm->xicp_cos_strong, prm->xicp_enough,
+                                prm->xicp_insufficient, st.sums + 2 * e);
+    st.locXyz[e] = okT ? 1 : 0;
+    st.cT[e] = okT ? 1.f : 0.f;
+    const bool okR = xicpDetect(rotAlign.data(), P, st.Ur + 3 * e, prm->xicp_cos_min, prm->xicp_cos_strong,
+                                prm->xicp_enough, prm->xicp_insufficient, st.sums + 6 + 2 * e);
+    st.locRpy[e] = okR ? 1 : 0;
+    st.cR[e] = okR ? 1.f : 0.f;
+  }
+  // :2389-2411 eigenvectors back to the optimisation (refMean) frame
+  for (int c = 0; c < 3; ++c) { mul3v(R, st.Ur + 3 * c); mul3v(R, st.Ut + 3 * c); }
+  // :2415-2429
+  st.repeatEigen = false;
+  for (int i = 0; i < 3; ++i)
+    if (st.locXyz[i] == 0 || st.locRpy[i] == 0) { st.repeatEigen = true; break; }
+  return true;
+}
+
+// solvePossiblyUnderdeterminedLinearSystemWithEqualityConstraints, PointToPlane.cpp:461-505, with
+// readLocalizabilityFlags (:757-778) and generateConstrainedOptimizationProblem (:570-626)
+int xicpSolve(const float* H, const float* b, const XicpState& st, float* x6, int* info, int* nConstraints) {
+  int idx[6], c = 0;
+  for (int i = 0; i < 3; ++i) if (st.locRpy[i] == 0) idx[c++] = i;
+  for (int i = 0; i < 3; ++i) if (st.locXyz[i] == 0) idx[c++] = i + 3;
+  if (nConstraints) *nConstraints = c;
+  if (c == 0) return orc_solve6(H, b, x6, info);
+  const int n = 6 + c;
+  std::vector<float> A((size_t)n * n, 0.f), rhs(n, 0.f), x(n, 0.f);
+  for (int j = 0; j < 6; ++j)
+    for (int i = 0; i < 6; ++i) A[i + n * j] = H[i + 6 * j];
+  for (int i = 0; i < 6; ++i) rhs[i] = b[i];
+  for (int cc = 0; cc < c; ++cc) {
+    const int index = idx[cc];
+    if (index < 3) {
+      for (int i = 0; i < 3; ++i) { A[i + n * (6 + cc)] = st.Ur[i + 3 * index]; A[(6 + cc) + n * i] = st.Ur[i + 3 * index]; }
+      rhs[6 + cc] = st.cR[index];
+    } else {
+      for (int i = 0; i < 3; ++i) {
+        A[(i + 3) + n * (6 + cc)] = st.Ut[i + 3 * (index - 3)];
+        A[(6 + cc) + n * (i + 3)] = st.Ut[i + 3 * (index - 3)];
+      }
+      rhs[6 + cc] = st.cT[index - 3];
+    }
+  }
+  const int r = orc_solve_n(A.data(), rhs.data(), n, x.data(), info);
+  for (int i = 0; i < 6; ++i) x6[i] = x[i];
+  return r;
+}
+
 }  // namespace
 
 extern "C" int orc_icp(const orc_icp_params* prm, const float* ref4xM, const float* refn3xM, int M,
@@ -241,6 +429,9 @@ extern "C" int orc_icp_compute(void* href, const orc_icp_params* prm, const floa
   mul4(tmp, T_readIn_readMean, T_refMean_readMean);       // ICP.cpp:983
   orc_rigid_apply(T_refMean_readMean, reading.data(), readingN.empty() ? nullptr : readingN.data(), N);  // :984
 
+  float T_refMean_dataIn[16];                              // :975
+  mul4(invRef, Tinit, T_refMean_dataIn);
+  XicpState xs;
   float T_iter[16];
   eye4(T_iter);
   bool iterate = true, maxReached = false;
@@ -285,7 +476,14 @@ extern "C" int orc_icp_compute(void* href, const orc_icp_params* prm, const floa
       if (!refn3xM) { status = ORC_E_BAD_PARAM; break; }   // InvalidField "normals", ICP.cpp:1519
       orc_p2plane_hb(readP.data(), refP.data(), refnP.data(), wP.data(), P, prm->accum, H, b);  // :1071
       int info;
-      orc_solve6(H, b, x, &info);                          // :1205 -> PointToPlane.cpp:299
+      if (prm->degeneracy == 1) {                          // :1112-1141
+        if (!xicpDetectOptimized(prm, H, readP.data(), refnP.data(), P, T_refMean_dataIn, iterationCount == 0, xs))
+          xs.returnPrior = true;
+        if (xs.returnPrior) break;                         // :1175-1179
+        xicpSolve(H, b, xs, x, &info, nullptr);            // :1205 -> PointToPlane.cpp:311-316
+      } else {
+        orc_solve6(H, b, x, &info);                        // :1205 -> PointToPlane.cpp:299
+      }
       orc_p2plane_T(x, real);
     } else {
       orc_p2point_T2(readP.data(), refP.data(), wP.data(), P, prm->accum, real);
@@ -310,6 +508,12 @@ extern "C" int orc_icp_compute(void* href, const orc_icp_params* prm, const floa
   mul4(T_refIn_refMean, T_iter, r1);
   mul4(r1, T_refMean_readMean, r2);
   mul4(r2, invRead, res->T);
+  if (xs.returnPrior) std::memcpy(res->T, Tinit, 16 * sizeof(float));  // :1335-1341
+  res->returned_prior = xs.returnPrior ? 1 : 0;
+  for (int i = 0; i < 3; ++i) { res->loc_xyz[i] = xs.locXyz[i]; res->loc_rpy[i] = xs.locRpy[i]; }
+  std::memcpy(res->eig_t, xs.Ut, sizeof(xs.Ut));
+  std::memcpy(res->eig_r, xs.Ur, sizeof(xs.Ur));
+  std::memcpy(res->xicp_sums, xs.sums, sizeof(xs.sums));
   res->iterations = iterationCount;
   res->max_iterations_reached = maxReached ? 1 : 0;
   res->n_matches_last = P;

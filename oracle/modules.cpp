@@ -173,16 +173,21 @@ int orc_p2plane_hb(const float* read, const float* ref, const float* n, const fl
   return ORC_OK;
 }
 
-// solvePossiblyUnderdeterminedLinearSystem, isConstrained = false — PointToPlane.cpp:199-256
-int orc_solve6(const float* A, const float* b, float* x, int* info) {
-  orc::FullPivQR<float, 6> qr;
+// solvePossiblyUnderdeterminedLinearSystem — PointToPlane.cpp:199-256. N = 6 for the plain system, 6 + c for the
+// equality-constrained (KKT) system of solvePossiblyUnderdeterminedLinearSystemWithEqualityConstraints (:461-505);
+// isConstrained only changes what the reference prints.
+extern "C++" {
+namespace {
+template <int N>
+int solveN(const float* A, const float* b, float* x, int* info) {
+  orc::FullPivQR<float, N> qr;
   qr.compute(A);
   auto svd_double = [&]() {
-    double Ad[36], bd[6], xd[6];
-    for (int i = 0; i < 36; ++i) Ad[i] = A[i];
-    for (int i = 0; i < 6; ++i) bd[i] = b[i];
-    orc::svdSolve<double, 6>(Ad, bd, xd);
-    for (int i = 0; i < 6; ++i) x[i] = (float)xd[i];
+    double Ad[N * N], bd[N], xd[N];
+    for (int i = 0; i < N * N; ++i) Ad[i] = A[i];
+    for (int i = 0; i < N; ++i) bd[i] = b[i];
+    orc::svdSolve<double, N>(Ad, bd, xd);
+    for (int i = 0; i < N; ++i) x[i] = (float)xd[i];
   };
   if (qr.isInvertible()) {   // :203 / :249-255
     svd_double();
@@ -193,24 +198,24 @@ int orc_solve6(const float* A, const float* b, float* x, int* info) {
   const int rank = qr.rank();
   if (info) *info = 1;
   if (rank == 0) {
-    for (int i = 0; i < 6; ++i) x[i] = 0.f;  // llt of a 0x0 system: x = 0 (then NaN guard downstream is moot)
+    for (int i = 0; i < N; ++i) x[i] = 0.f;  // llt of a 0x0 system: x = 0 (then NaN guard downstream is moot)
   } else {
-    float Q[36];
+    float Q[N * N];
     qr.matrixQ(Q);
     // AP = A * colsPermutation
-    float AP[36];
-    for (int j = 0; j < 6; ++j)
-      for (int i = 0; i < 6; ++i) AP[i + 6 * j] = A[i + 6 * qr.colPerm[j]];
+    float AP[N * N];
+    for (int j = 0; j < N; ++j)
+      for (int i = 0; i < N; ++i) AP[i + N * j] = A[i + N * qr.colPerm[j]];
     // R1 = (Q1^T * A * P).block(0,0,rank,6), Q1t = Q^T rows 0..rank-1
-    std::vector<float> R1(rank * 6), qtb(rank);
+    std::vector<float> R1(rank * N), qtb(rank);
     for (int r = 0; r < rank; ++r) {
-      for (int j = 0; j < 6; ++j) {
+      for (int j = 0; j < N; ++j) {
         float acc = 0.f;
-        for (int i = 0; i < 6; ++i) acc += Q[i + 6 * r] * AP[i + 6 * j];
+        for (int i = 0; i < N; ++i) acc += Q[i + N * r] * AP[i + N * j];
         R1[r + rank * j] = acc;
       }
       float acc = 0.f;
-      for (int i = 0; i < 6; ++i) acc += Q[i + 6 * r] * b[i];
+      for (int i = 0; i < N; ++i) acc += Q[i + N * r] * b[i];
       qtb[r] = acc;
     }
     // G = R1 * R1^T (rank x rank), Cholesky solve G z = Q1^T b  (llt().solve, :222)
@@ -218,7 +223,7 @@ int orc_solve6(const float* A, const float* b, float* x, int* info) {
     for (int a = 0; a < rank; ++a)
       for (int c = 0; c < rank; ++c) {
         float acc = 0.f;
-        for (int j = 0; j < 6; ++j) acc += R1[a + rank * j] * R1[c + rank * j];
+        for (int j = 0; j < N; ++j) acc += R1[a + rank * j] * R1[c + rank * j];
         G[a + rank * c] = acc;
       }
     std::vector<float> L(rank * rank, 0.f);
@@ -244,29 +249,46 @@ int orc_solve6(const float* A, const float* b, float* x, int* info) {
       z[i] = s / L[i + rank * i];
     }
     // y = R1.triangularView<Upper>()^T * z : only the upper-triangular part (j >= r) of R1 is used, :222
-    float y[6];
-    for (int j = 0; j < 6; ++j) {
+    float y[N];
+    for (int j = 0; j < N; ++j) {
       float acc = 0.f;
       for (int r = 0; r < rank && r <= j; ++r) acc += R1[r + rank * j] * z[r];
       y[j] = acc;
     }
     // x = colsPermutation * y : x[colPerm[j]] = y[j], :231
-    for (int j = 0; j < 6; ++j) x[qr.colPerm[j]] = y[j];
+    for (int j = 0; j < N; ++j) x[qr.colPerm[j]] = y[j];
   }
   // accuracy check b.isApprox(A x, 1e-5) — :233-234 (||b - ax||^2 <= prec^2 * min(||b||^2, ||ax||^2))
-  float ax[6];
-  for (int i = 0; i < 6; ++i) {
+  float ax[N];
+  for (int i = 0; i < N; ++i) {
     float acc = 0.f;
-    for (int j = 0; j < 6; ++j) acc += A[i + 6 * j] * x[j];
+    for (int j = 0; j < N; ++j) acc += A[i + N * j] * x[j];
     ax[i] = acc;
   }
   float e2 = 0.f, b2 = 0.f, a2 = 0.f;
-  for (int i = 0; i < 6; ++i) { e2 += (b[i] - ax[i]) * (b[i] - ax[i]); b2 += b[i] * b[i]; a2 += ax[i] * ax[i]; }
+  for (int i = 0; i < N; ++i) { e2 += (b[i] - ax[i]) * (b[i] - ax[i]); b2 += b[i] * b[i]; a2 += ax[i] * ax[i]; }
   if (!(e2 <= 1e-5f * 1e-5f * std::min(b2, a2))) {
     svd_double();  // :236-238
     if (info) *info = 2;
   }
   return ORC_OK;
+}
+}  // namespace
+}  // extern "C++"
+
+int orc_solve6(const float* A, const float* b, float* x, int* info) { return solveN<6>(A, b, x, info); }
+
+int orc_solve_n(const float* A, const float* b, int n, float* x, int* info) {
+  switch (n) {
+    case 6: return solveN<6>(A, b, x, info);
+    case 7: return solveN<7>(A, b, x, info);
+    case 8: return solveN<8>(A, b, x, info);
+    case 9: return solveN<9>(A, b, x, info);
+    case 10: return solveN<10>(A, b, x, info);
+    case 11: return solveN<11>(A, b, x, info);
+    case 12: return solveN<12>(A, b, x, info);
+    default: return ORC_E_BAD_PARAM;
+  }
 }
 
 // x -> T : PointToPlane.cpp:337-381 (6-DOF branch; force2D/force4DOF unsupported)

@@ -63,6 +63,8 @@ int orc_p2plane_hb(const float* read4xP, const float* ref4xP, const float* refn3
 /* ---- solvePossiblyUnderdeterminedLinearSystem (PointToPlane.cpp:113-265, unconstrained branch).
  * info: 0 = full-rank double-SVD path, 1 = rank-deficient minimal-norm path, 2 = SVD fallback */
 int orc_solve6(const float* A36, const float* b6, float* x6, int* info);
+/* the same routine for the (6 + c) x (6 + c) equality-constrained system (PointToPlane.cpp:461-505), 6 <= n <= 12 */
+int orc_solve_n(const float* Ann, const float* bn, int n, float* xn, int* info);
 /* x -> 4x4 (PointToPlane.cpp:337-381) */
 int orc_p2plane_T(const float* x6, float* T16);
 
@@ -105,6 +107,12 @@ typedef struct {
   int accum;            /* see orc_p2plane_hb */
   int mean_mode;        /* 0 = reference-literal sequential float mean, 1 = double sum rounded to float */
   int knn_threads;      /* kd-tree query threads (1 = like the single-threaded reference) */
+  /* degeneracyAwareness (ICP.cpp:575-760): 0 = None, 1 = OptimizedEqualityConstraints (X-ICP, :629-670) */
+  int degeneracy;
+  float xicp_enough;        /* enoughInformationThreshold */
+  float xicp_insufficient;  /* insufficientInformationThreshold */
+  float xicp_cos_min;       /* cos(point2NormalMinimalAlignmentAngleThreshold) */
+  float xicp_cos_strong;    /* cos(point2NormalStrongAlignmentAngleThreshold) */
 } orc_icp_params;
 
 typedef struct {
@@ -117,6 +125,14 @@ typedef struct {
   float T_refMean_readMean[16];
   float weighted_point_used_ratio;
   long points_touched;
+  /* X-ICP (degeneracy = 1): flags of the first iteration's detection (1 = localizable), eigenvectors as they stand
+   * after the last iteration (columns, refMean frame), whether the prior was returned (ICP.cpp:1335-1341), and as
+   * diagnostics the alignment sums over ALL matched pairs in double (the reference stops early):
+   * xicp_sums[2e], [2e+1] = combined/high for translation eigenvector e; [6+2e], [7+2e] for rotation eigenvector e */
+  int returned_prior;
+  int loc_xyz[3], loc_rpy[3];
+  float eig_t[9], eig_r[9];
+  double xicp_sums[12];
 } orc_icp_result;
 
 /* log_* (nullable): per-iteration dumps, capacity max_log iterations: H 36, b 6, x 6, T_iter 16 floats, P int */

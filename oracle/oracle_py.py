@@ -28,6 +28,8 @@ class IcpParams(C.Structure):
         ("use_differential", C.c_int), ("min_diff_rot", C.c_float), ("min_diff_trans", C.c_float),
         ("smooth_length", C.c_int), ("counter_first", C.c_int), ("accum", C.c_int), ("mean_mode", C.c_int),
         ("knn_threads", C.c_int),
+        ("degeneracy", C.c_int), ("xicp_enough", C.c_float), ("xicp_insufficient", C.c_float),
+        ("xicp_cos_min", C.c_float), ("xicp_cos_strong", C.c_float),
     ]
 
 
@@ -37,6 +39,8 @@ class IcpResult(C.Structure):
         ("T", C.c_float * 16), ("T_iter", C.c_float * 16), ("T_refIn_refMean", C.c_float * 16),
         ("T_refMean_readMean", C.c_float * 16), ("weighted_point_used_ratio", C.c_float),
         ("points_touched", C.c_long),
+        ("returned_prior", C.c_int), ("loc_xyz", C.c_int * 3), ("loc_rpy", C.c_int * 3),
+        ("eig_t", C.c_float * 9), ("eig_r", C.c_float * 9), ("xicp_sums", C.c_double * 12),
     ]
 
 
@@ -192,6 +196,19 @@ def solve6(H, b):
     return x, info.value
 
 
+def solve_n(A, b):
+    """orc_solve_n: the (6 + c) x (6 + c) equality-constrained system of PointToPlane.cpp:461-505."""
+    A = np.asarray(A, np.float32)
+    n = A.shape[0]
+    Ac = np.ascontiguousarray(A.T).ravel()
+    b = f32(b)
+    x = np.empty(n, np.float32)
+    info = C.c_int()
+    st = lib().orc_solve_n(_fp(Ac), _fp(b), n, _fp(x), C.byref(info))
+    assert st == 0
+    return x, info.value
+
+
 def p2plane_T(x):
     x = f32(x)
     T = np.empty(16, np.float32)
@@ -242,7 +259,9 @@ def default_params(**kw):
     p = IcpParams(knn=1, maxDist=np.inf, use_trimmed=1, trimmed_ratio=0.85, use_maxdist_filter=0, maxdist_filter=1.0,
                   use_surface_normal_filter=0, surface_normal_max_angle=1.57, minimizer=0, max_iterations=40,
                   use_differential=1, min_diff_rot=0.001, min_diff_trans=0.001, smooth_length=3, counter_first=1,
-                  accum=1, mean_mode=1, knn_threads=1)
+                  accum=1, mean_mode=1, knn_threads=1, degeneracy=0, xicp_enough=250.0, xicp_insufficient=180.0,
+                  xicp_cos_min=float(np.cos(np.float32(np.deg2rad(np.float32(80.0))))),
+                  xicp_cos_strong=float(np.cos(np.float32(np.deg2rad(np.float32(45.0))))))
     for k_, v in kw.items():
         assert hasattr(p, k_), k_
         setattr(p, k_, v)
@@ -279,6 +298,11 @@ def icp(params, ref4, refn, read4, readn=None, T_init=None, max_log=64, forced_T
                 n_matches_last=res.n_matches_last, T=m(res.T), T_iter=m(res.T_iter),
                 T_refIn_refMean=m(res.T_refIn_refMean), T_refMean_readMean=m(res.T_refMean_readMean),
                 weighted_point_used_ratio=res.weighted_point_used_ratio, points_touched=res.points_touched,
+                returned_prior=bool(res.returned_prior), loc_xyz=np.array(res.loc_xyz[:], np.int32),
+                loc_rpy=np.array(res.loc_rpy[:], np.int32),
+                eig_t=np.array(res.eig_t[:], np.float32).reshape(3, 3).T.copy(),
+                eig_r=np.array(res.eig_r[:], np.float32).reshape(3, 3).T.copy(),
+                xicp_sums=np.array(res.xicp_sums[:], np.float64),
                 H=logH[:it].reshape(it, 6, 6).transpose(0, 2, 1).copy(), b=logb[:it], x=logx[:it],
                 T_iters=logT[:it].reshape(it, 4, 4).transpose(0, 2, 1).copy(), P=logP[:it], ids=ids, dists=dists,
                 weights=w)
