@@ -57,6 +57,8 @@ def parse():
     ap.add_argument("--poses", type=int, default=8, help="distinct synthetic scans (cycled over the steps)")
     ap.add_argument("--cpu-sample", type=int, default=3, help="registrations timed for the CPU baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--degeneracy", default="none", choices=["none", "xicp"],
+                    help="xicp: degeneracyAwareness OptimizedEqualityConstraints with param/icp.yaml's thresholds")
     ap.add_argument("--no-flush", action="store_true", help="keep L2 warm between steps (reported in config)")
     return ap.parse_args()
 
@@ -64,6 +66,16 @@ def parse():
 def icp_kwargs():
     return dict(knn=1, maxDist=0.5, use_trimmed=1, trimmed_ratio=0.9, max_iterations=30, use_differential=1,
                 min_diff_rot=1e-3, min_diff_trans=8e-3, smooth_length=3, minimizer=0)
+
+
+def xicp_kwargs(args, oracle):
+    """degeneracyAwareness of open3d_slam_ros/param/icp.yaml (250 / 180 / 80 deg / 45 deg) when --degeneracy xicp"""
+    if getattr(args, "degeneracy", "none") != "xicp":
+        return {}
+    if oracle:
+        return dict(degeneracy=1, xicp_enough=250.0, xicp_insufficient=180.0)   # angles: oracle defaults (80 / 45 deg)
+    return dict(degeneracy=1, xicp_enough_information=250.0, xicp_insufficient_information=180.0,
+                xicp_min_alignment_angle_deg=80.0, xicp_strong_alignment_angle_deg=45.0)
 
 
 def workload(args):
@@ -136,14 +148,14 @@ def dist_env():
     return rank, world, local
 
 
-def cpu_baseline(ref4, refn, scans, n_sample, threads):
+def cpu_baseline(ref4, refn, scans, n_sample, threads, args=None):
     """The CPU oracle on the host cores: initReference (kd-tree build) timed apart from compute(), like the SLAM
     (Mapper.cpp:343 vs :373). Returns registrations/s over the bounded sample."""
     from oracle import oracle_py as O
     t0 = time.perf_counter()
     ses = O.IcpSession(ref4, refn)
     build_s = time.perf_counter() - t0
-    p = O.default_params(counter_first=0, knn_threads=threads, **icp_kwargs())
+    p = O.default_params(counter_first=0, knn_threads=threads, **icp_kwargs(), **xicp_kwargs(args, True))
     times, iters = [], []
     for i in range(n_sample):
         r4, Ti, _ = scans[i % len(scans)]
@@ -164,6 +176,7 @@ def config_dict(args, extra=None):
                      "(knn 1, maxDist 0.5, eps 0, TrimmedDist 0.90, Differential{1e-3,8e-3,3}+Counter{30})"
                      % (args.scan_points, args.map_points),
          "map_points": args.map_points, "scan_points": args.scan_points, "distinct_scans": args.poses,
+         "degeneracyAwareness": "OptimizedEqualityConstraints{250,180,80,45}" if getattr(args, "degeneracy", "none") == "xicp" else "None",
          "step": "one registration (one scan -> pose)",
          "multi_gpu": "independent registrations sharded round-robin over ranks, one map replica per GPU, no collective"}
     if extra:
@@ -183,7 +196,7 @@ def run_reference(args):
     t0 = time.perf_counter()
     ses = O.IcpSession(ref4, refn)
     build_s = time.perf_counter() - t0
-    p = O.default_params(counter_first=0, knn_threads=threads, **icp_kwargs())
+    p = O.default_params(counter_first=0, knn_threads=threads, **icp_kwargs(), **xicp_kwargs(args, True))
     for i in range(args.warmup):
         ses.compute(p, scans[i % len(scans)][0], None, scans[i % len(scans)][1])
     t0 = time.perf_counter()
@@ -230,7 +243,7 @@ def run_b200(args):
 
     ref4, refn, scans, gen_s = workload(args)
     N = scans[0][0].shape[0]
-    icp = B.ICP(B.default_icp_params(**icp_kwargs()), device=local)
+    icp = B.ICP(B.default_icp_params(**icp_kwargs(), **xicp_kwargs(args, False)), device=local)
     t0 = time.perf_counter()
     icp.init_reference(ref4, refn)
     init_ref_s = time.perf_counter() - t0
@@ -239,7 +252,10 @@ def run_b200(args):
         t, a = pinned_copy(r4)
         keep.append(t)
         host_scans.append((a, Ti, Tt))
-    mine = lambda i: host_scans[(rank + i * world) % len(host_scans)]
+    # registration i of this rank: every rank walks through ALL distinct scans (offset by its rank), so the ranks do
+    # the same work over the run; (rank + i * world) % poses would pin one scan (and its iteration count) to a rank
+    # whenever world divides the number of scans
+    mine = lambda i: host_scans[(rank + i) % len(host_scans)]
     flush = (lambda: None) if args.no_flush else icp.flush_l2
 
     clk = ClockSampler(local) if rank == 0 else None   # started early: nvidia-smi needs a moment to come up
@@ -319,8 +335,8 @@ def run_b200(args):
         "clocks": clocks,
     }
     if world == 1 and not args.no_cpu_baseline:
-        out["cpu_baseline"] = cpu_baseline(ref4, refn, scans, args.cpu_sample, os.cpu_count() or 1)
-        one = cpu_baseline(ref4, refn, scans, 1, 1)
+        out["cpu_baseline"] = cpu_baseline(ref4, refn, scans, args.cpu_sample, os.cpu_count() or 1, args)
+        one = cpu_baseline(ref4, refn, scans, 1, 1, args)
         out["cpu_baseline"]["single_thread_value"] = one["value"]
     print(json.dumps(out))
     if dist is not None:
