@@ -191,8 +191,8 @@ typedef struct {
    * eigenvectors (columns, column-major 3x3, optimisation frame) after the last iteration; whether the prior was
    * returned (ICP.cpp:1335-1341: T = T_refIn_readIn); the alignment sums over all matched pairs (double):
    * xicp_sums[2e], [2e+1] = combined/high contribution for translation eigenvector e, [6+2e], [7+2e] for rotation
-   * eigenvector e; xicp_borderline != 0 when a sum lay within 0.5 % of a threshold that decided a flag (the reference's
-   * sequential float sum could round to the other side). */
+   * eigenvector e; xicp_borderline = number of flags whose sums lay within the rounding band (0.5 - 1 %) of a threshold and were therefore
+   * decided by replaying the reference's sequential float recurrence (ICP.cpp:2128-2155) on the device. */
   int returned_prior, xicp_borderline;
   int loc_xyz[3], loc_rpy[3];
   float eig_t[9], eig_r[9];

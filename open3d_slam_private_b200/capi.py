@@ -341,7 +341,7 @@ class ICP:
                    points_touched=res.points_touched, device_ms=res.device_ms, h2d_ms=res.h2d_ms,
                    total_ms=res.total_ms, e2e_ms=res.e2e_ms, kernel_launches=res.kernel_launches,
                    grid_ctas=res.grid_ctas, returned_prior=bool(res.returned_prior),
-                   xicp_borderline=bool(res.xicp_borderline), loc_xyz=np.array(res.loc_xyz[:], np.int32),
+                   xicp_borderline=int(res.xicp_borderline), loc_xyz=np.array(res.loc_xyz[:], np.int32),
                    loc_rpy=np.array(res.loc_rpy[:], np.int32),
                    eig_t=np.array(res.eig_t[:], np.float32).reshape(3, 3).T.copy(),
                    eig_r=np.array(res.eig_r[:], np.float32).reshape(3, 3).T.copy(),

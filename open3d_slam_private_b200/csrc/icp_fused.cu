@@ -154,6 +154,31 @@ __device__ __forceinline__ double role_sum(const float* s_v, int tid) {
   return a;
 }
 
+// Query -> (warp slot, lane) map. A warp holds 32 >> c groups of G = 1 << c CONSECUTIVE scan points; group g of slot w
+// is chunk (w + 97 g) mod nslots of part g of the scan. Consecutive scan points are neighbours in space, so the lanes
+// of a group read the same cell rows and the same 128-byte lines of the cell-sorted points (one L1 wavefront instead
+// of G); the groups of a warp come from 32 / G distant parts of the scan, so equally expensive queries (no neighbour
+// within maxDist, far neighbours) are still spread over all warps. c = 0 is one query per part (no coherence).
+// With c > 0 the slots are scattered over the chunks with a multiplicative hash (A coprime to nslots): the 16 warps
+// of a CTA hold chunks from all over the scan, so no CTA is handed a whole expensive region (measured without the
+// hash: the slowest CTA of the first iteration took 3x the mean).
+__device__ __forceinline__ unsigned slot_stride(unsigned nslots) {
+  const unsigned cand[4] = {2654435761u % 1000003u, 7919u, 104729u, 1299709u};
+  for (int t = 0; t < 4; ++t) {
+    unsigned a = cand[t] % nslots, b = nslots;
+    if (a == 0u) continue;
+    const unsigned a0 = a;
+    while (b) { const unsigned r = a % b; a = b; b = r; }
+    if (a == 1u) return a0;
+  }
+  return 1u;
+}
+__device__ __forceinline__ int query_of(int slot, int lane, int nslots, int c, unsigned stride) {
+  const unsigned g = (unsigned)lane >> c, j = (unsigned)lane & ((1u << c) - 1u);
+  const unsigned s2 = c ? (unsigned)(((unsigned long long)(unsigned)slot * stride) % (unsigned)nslots) : (unsigned)slot;
+  return (int)(((g * (unsigned)nslots + (s2 + g * 97u) % (unsigned)nslots) << c) + j);
+}
+
 template <int K>
 __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __grid_constant__ IcpKernelParams p) {
   cg::grid_group grid = cg::this_grid();
@@ -188,6 +213,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
   }
   __syncthreads();
   const bool xicp = (K == 1) && p.xicp && p.minimizer == 0;
+  const unsigned qstride = slot_stride((unsigned)((p.N + 31) >> 5));
   unsigned long long visited_total = 0ull;
 
   const bool stamp = (blockIdx.x == 0 && tid == 0 && p.log != nullptr);
@@ -222,7 +248,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     unsigned cand_base = 0u;  // candidates this CTA has parked so far
     for (int round = 0; round < rounds; ++round) {
       const int slot = (gtid >> 5) + round * (nthreads >> 5);
-      const int i = slot < nslots ? lane * nslots + (int)(((unsigned)slot + (unsigned)lane * 97u) % (unsigned)nslots) : p.N;
+      const int i = slot < nslots ? query_of(slot, lane, nslots, p.coh_log2, qstride) : p.N;
       const bool in = i < p.N;
       const float4 q = in ? apply_T(S.Tc, __ldg(&p.reading[i])) : make_float4(0.f, 0.f, 0.f, 1.f);
       unsigned vis = 0;
@@ -555,7 +581,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     for (int t = tid; t < kWarps * kAccum; t += kIcpThreads) (&s_red[0][0])[t] = 0.0;
     __syncthreads();
     for (int slot = gtid >> 5; slot < nslots; slot += nthreads >> 5) {  // same map as phase 1 (no barrier needed in between)
-      const int i = lane * nslots + (int)(((unsigned)slot + (unsigned)lane * 97u) % (unsigned)nslots);
+      const int i = query_of(slot, lane, nslots, p.coh_log2, qstride);
       const bool in = i < p.N;
       float4 q = make_float4(0.f, 0.f, 0.f, 1.f);
       float3 nq = make_float3(0.f, 0.f, 0.f);
@@ -734,7 +760,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
         __syncthreads();
         const float cmin = p.x_cos_min, cstr = p.x_cos_strong;
         for (int slot = gtid >> 5; slot < nslots; slot += nthreads >> 5) {
-          const int i = lane * nslots + (int)(((unsigned)slot + (unsigned)lane * 97u) % (unsigned)nslots);
+          const int i = query_of(slot, lane, nslots, p.coh_log2, qstride);
           double acc[12];
 #pragma unroll
           for (int t = 0; t < 12; ++t) acc[t] = 0.0;
@@ -784,12 +810,89 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
         __syncthreads();
         if (tid == 0) {
           XicpState& X = S.X;
+          X.border_mask = 0;
           for (int e = 0; e < 3; ++e) {
-            X.loc_xyz[e] = xicp_decide(X.sums[2 * e], X.sums[2 * e + 1], p.x_enough, p.x_insufficient, &X.borderline);
-            X.cT[e] = X.loc_xyz[e] ? 1.f : 0.f;
-            X.loc_rpy[e] = xicp_decide(X.sums[6 + 2 * e], X.sums[7 + 2 * e], p.x_enough, p.x_insufficient, &X.borderline);
-            X.cR[e] = X.loc_rpy[e] ? 1.f : 0.f;
+            int bl = 0;
+            X.loc_xyz[e] = xicp_decide(X.sums[2 * e], X.sums[2 * e + 1], p.x_enough, p.x_insufficient, P0, &bl);
+            if (bl) X.border_mask |= 1 << e;
+            bl = 0;
+            X.loc_rpy[e] = xicp_decide(X.sums[6 + 2 * e], X.sums[7 + 2 * e], p.x_enough, p.x_insufficient, P0, &bl);
+            if (bl) X.border_mask |= 8 << e;
           }
+        }
+        __syncthreads();
+        if (S.X.border_mask != 0 && wid == 0) {
+          // A sum lies within the rounding band of a threshold: replay the reference's own recurrence for that
+          // direction (ICP.cpp:2128-2155: sequential float sums over the matched pairs in ErrorElements order, exit
+          // test in the loop condition). One warp per CTA, every CTA alike (no further barrier): the lanes evaluate
+          // 32 consecutive pairs, then fold them in index order. Rare (band = 0.5 % of a threshold) and slow (~1 ms
+          // per direction), exact by construction.
+          const int mask = S.X.border_mask;
+          float cen[3] = {S.X.center[0], S.X.center[1], S.X.center[2]};
+          for (int pass = (mask & 0x38) ? -1 : 0; pass < 6; ++pass) {
+            if (pass >= 0 && !((mask >> pass) & 1)) continue;
+            const float* v = pass < 0 ? nullptr : (pass < 3 ? S.X.UtB + 3 * pass : S.X.UrB + 3 * (pass - 3));
+            float combined = 0.f, high = 0.f, c3[3] = {0.f, 0.f, 0.f};
+            bool done = false;
+            for (int base = 0; base < p.N && !done; base += 32) {
+              const int i = base + lane;
+              bool kept = false;
+              float al = 0.f, px = 0.f, py = 0.f, pz = 0.f;
+              if (i < p.N) {
+                const float d = __ldcg(&p.dists[i]), w = __ldcg(&p.weights[i]);
+                const int sp = __ldcg(&p.spos[i]);
+                if (d != INFINITY && w != 0.f && sp >= 0) {
+                  kept = true;
+                  const float4 q = apply_T(S.Tc, __ldg(&p.reading[i]));
+                  const float4 pb = apply_T(S.TcInv, q);
+                  px = pb.x; py = pb.y; pz = pb.z;
+                  if (pass >= 0) {
+                    const float4 n4 = __ldg(&p.g.nrm[sp]);
+                    const float3 nb = apply_R(S.R9Inv, make_float3(n4.x, n4.y, n4.z));
+                    if (pass < 3) al = fabsf(nb.x * v[0] + nb.y * v[1] + nb.z * v[2]);
+                    else {
+                      const float ax = pb.x - cen[0], ay = pb.y - cen[1], az = pb.z - cen[2];
+                      float c0 = ay * nb.z - az * nb.y, c1 = az * nb.x - ax * nb.z, c2 = ax * nb.y - ay * nb.x;
+                      const float nn = sqrtf(c0 * c0 + c1 * c1 + c2 * c2);
+                      if (!(nn < 1.0f)) { c0 /= nn; c1 /= nn; c2 /= nn; }
+                      al = fabsf(c0 * v[0] + c1 * v[1] + c2 * v[2]);
+                    }
+                  }
+                }
+              }
+              unsigned km = __ballot_sync(0xffffffffu, kept);
+              while (km && !done) {
+                const int l = __ffs(km) - 1;
+                km &= km - 1u;
+                if (pass < 0) {   // calculatePointCloudCenter, ICP.cpp:1604-1611
+                  c3[0] += __shfl_sync(0xffffffffu, px, l);
+                  c3[1] += __shfl_sync(0xffffffffu, py, l);
+                  c3[2] += __shfl_sync(0xffffffffu, pz, l);
+                } else {
+                  const float a = __shfl_sync(0xffffffffu, al, l);
+                  if (a > p.x_cos_min) combined += a;
+                  if (a > p.x_cos_strong) high += a;
+                  done = (combined >= p.x_enough) || (high >= p.x_insufficient);
+                }
+              }
+            }
+            if (pass < 0) {
+              const float Pf = (float)P0;
+              cen[0] = c3[0] / Pf; cen[1] = c3[1] / Pf; cen[2] = c3[2] / Pf;
+            } else if (lane == 0) {
+              if (pass < 3) S.X.loc_xyz[pass] = done ? 1 : 0;
+              else S.X.loc_rpy[pass - 3] = done ? 1 : 0;
+              S.X.borderline += 1;
+            }
+          }
+        }
+        // the replay reads every CTA's matches: nobody may start the next iteration (which overwrites them) before
+        // all are done
+        if (S.X.border_mask != 0) grid.sync();
+        else __syncthreads();
+        if (tid == 0) {
+          XicpState& X = S.X;
+          for (int e = 0; e < 3; ++e) { X.cT[e] = X.loc_xyz[e] ? 1.f : 0.f; X.cR[e] = X.loc_rpy[e] ? 1.f : 0.f; }
           for (int c = 0; c < 3; ++c) {                                    // :2389-2411 back to the optimisation frame
             mul3v_dev(X.R, X.UrB + 3 * c, X.Ur + 3 * c);
             mul3v_dev(X.R, X.UtB + 3 * c, X.Ut + 3 * c);

@@ -124,6 +124,7 @@ struct b200_icp {
   float* d_cand_d = nullptr; int* d_cand_q = nullptr; float4* d_cand_rec = nullptr;
   size_t cap_cand = 0;
   int fast_path = 1;  // env B200_ICP_FAST=0 forces the general iteration
+  int coh_log2 = 0;   // env B200_ICP_COH=0..5: see query_of (icp_fused.cu)
   unsigned* d_hist = nullptr;
   double *d_partials = nullptr, *d_partials2 = nullptr, *d_meanpart = nullptr;
   IcpDeviceResult* d_out = nullptr;
@@ -262,6 +263,7 @@ int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool tim
   p.ids = h->d_ids; p.dists = h->d_dists; p.spos = h->d_spos; p.weights = h->d_w;
   p.cand_d = h->d_cand_d; p.cand_q = h->d_cand_q; p.cand_rec = h->d_cand_rec; p.cand_seg = 0;
   p.fast_path = (h->fast_path && h->prm.knn == 1) ? 1 : 0;
+  p.coh_log2 = h->coh_log2;
   p.debug_stats = h->debug_stats;
   p.dbg_warp = nullptr;
   if (h->debug_stats) {
@@ -378,6 +380,7 @@ int b200_icp_create(b200_icp** out, int device, const b200_icp_params* prm) {
   h->prm = *prm;
   { const char* e = getenv("B200_ICP_DEBUG"); h->debug_stats = (e && e[0] == '1') ? 1 : 0; }
   { const char* e = getenv("B200_ICP_FAST"); h->fast_path = (e && e[0] == '0') ? 0 : 1; }
+  { const char* e = getenv("B200_ICP_COH"); if (e && e[0] >= '0' && e[0] <= '5') h->coh_log2 = e[0] - '0'; }
   h->map.device = device;
   int st = B200_OK;
   if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess)

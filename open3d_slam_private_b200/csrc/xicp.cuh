@@ -11,22 +11,28 @@
 // detectLocalizability is a sequential float loop whose exit test sits in the loop condition. Every term is
 // non-negative, so both running sums are monotone and "some prefix reached a threshold" is the same statement as
 // "the full sum reached it". The device therefore forms the two full sums per direction in parallel (double) and
-// certifies the decision against the worst-case rounding of the reference's float recurrence (kXicpBand); only a sum
-// inside that band is flagged as borderline.
+// certifies the decision against the worst-case rounding of the reference's float recurrence (xicp_band); a direction
+// whose sums fall inside that band is decided by replaying the reference's own sequential recurrence (icp_fused.cu),
+// so the flags are the reference's by construction.
 #pragma once
 #include "small_la.cuh"
 #include "solve.cuh"
 
 namespace b200 {
 
-constexpr double kXicpBand = 5e-3;   // >= (P - 1) * 2^-24 for P <= 83 000 pairs at the threshold magnitude; see DESIGN.md
+// Relative half-width of the band around a threshold inside which the parallel double sums do not certify the
+// reference's decision: the float recurrence of n <= P non-negative terms that stops at the threshold is off by at most
+// n * 2^-24 relative (half an ulp per addition of a running sum <= threshold); 20 % on top for the terms' own rounding
+// (the centre of calculatePointCloudCenter is summed in double here, sequentially in float there), floor 0.5 %.
+__device__ __forceinline__ double xicp_band(int P) { return fmax(5e-3, 1.2 * (double)P * 5.9604644775390625e-8); }
 constexpr int kKktCap = 12;          // 6 unknowns + up to 6 equality constraints
 
 // state of LocalizabilityParametersForErrorMinimization (PointMatcher.h:585-660) for one registration
 struct XicpState {
   int repeat_eigen;     // debugging_.whetherToRepeatEigenAnalysis_ (:592), starts true
   int return_prior;     // debugging_.whetherToReturnPrior_ (:595)
-  int borderline;       // a decision fell inside the rounding band of the reference's float sums
+  int borderline;       // decisions that fell inside the rounding band and were replayed exactly
+  int border_mask;      // bit e: translation eigenvector e, bit 3 + e: rotation eigenvector e
   int loc_xyz[3], loc_rpy[3];   // 1 = kLocalizable (:638-639)
   float cT[3], cR[3];   // translation/rotationConstraintValues_ (:625-626)
   float Ut[9], Ur[9];   // translation/rotationEigenvectors_ (:634-635), columns, optimisation (refMean) frame
@@ -37,7 +43,7 @@ struct XicpState {
 };
 
 __device__ inline void xicp_state_init(XicpState& X) {
-  X.repeat_eigen = 1; X.return_prior = 0; X.borderline = 0;
+  X.repeat_eigen = 1; X.return_prior = 0; X.borderline = 0; X.border_mask = 0;
   for (int i = 0; i < 3; ++i) { X.loc_xyz[i] = 1; X.loc_rpy[i] = 1; X.cT[i] = 0.f; X.cR[i] = 0.f; X.center[i] = 0.f; }
   for (int i = 0; i < 9; ++i) { X.Ut[i] = 0.f; X.Ur[i] = 0.f; X.UtB[i] = 0.f; X.UrB[i] = 0.f; }
   for (int i = 0; i < 12; ++i) X.sums[i] = 0.0;
@@ -96,11 +102,12 @@ __device__ inline void xicp_eigen_analysis(const float* H, float* Ut, float* Ur)
 
 // outcome of ICP::detectLocalizability from the two full sums: 1 enough information, 0 not; *borderline set when the
 // sums are within the rounding band of a threshold the decision depends on
-__device__ inline int xicp_decide(double combined, double high, float enough, float insufficient, int* borderline) {
-  const double e = (double)enough, u = (double)insufficient;
+__device__ inline int xicp_decide(double combined, double high, float enough, float insufficient, int P,
+                                  int* borderline) {
+  const double e = (double)enough, u = (double)insufficient, band = xicp_band(P);
   const bool yes = (combined >= e) || (high >= u);
-  const bool sure_yes = (combined >= e * (1.0 + kXicpBand)) || (high >= u * (1.0 + kXicpBand));
-  const bool sure_no = (combined < e * (1.0 - kXicpBand)) && (high < u * (1.0 - kXicpBand));
+  const bool sure_yes = (combined >= e * (1.0 + band)) || (high >= u * (1.0 + band));
+  const bool sure_no = (combined < e * (1.0 - band)) && (high < u * (1.0 - band));
   if (!(sure_yes || sure_no)) *borderline = 1;
   return yes ? 1 : 0;
 }

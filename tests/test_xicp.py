@@ -172,12 +172,34 @@ def test_device_xicp_parity(kind, flags, fast, monkeypatch):
     icp.inputs = (p, ref4, refn, read4, None, None)
     assert g["loc_xyz"].tolist() == o["loc_xyz"].tolist() == flags[0]
     assert g["loc_rpy"].tolist() == o["loc_rpy"].tolist() == flags[1]
-    assert not g["returned_prior"] and not g["xicp_borderline"]
+    assert not g["returned_prior"] and g["xicp_borderline"] == 0
     # the alignment sums over all pairs: same float terms, summed in double on both sides
     assert np.abs(g["xicp_sums"] - o["xicp_sums"]).max() <= 1e-4 * max(1.0, np.abs(o["xicp_sums"]).max())
     assert _same_up_to_sign(g["eig_t"], o["eig_t"], 1e-4) and _same_up_to_sign(g["eig_r"], o["eig_r"], 1e-4)
     # a constrained direction is only as well conditioned as the constraint: 10x the plain pose tolerance there
     assert_icp_parity(o, g, icp, pose_tol_scale=1.0 if kind == "room" else 10.0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("which", [2, 4, 8, 10])        # combined sums of translation e = 1, 2 and rotation e = 1, 2
+@pytest.mark.parametrize("rel", [-3e-4, -1e-6, 0.0, 1e-6, 3e-4])
+def test_device_xicp_borderline_sums_are_replayed_exactly(which, rel):
+    """A threshold placed within a few ulps / 0.03 % of an alignment sum: the parallel double sums cannot certify what
+    the reference's sequential float recurrence (ICP.cpp:2128-2155) would decide, so the device replays it. The flags
+    must be the oracle's (which runs that recurrence literally) on either side of the threshold."""
+    from open3d_slam_private_b200 import capi as B
+    ref4, refn, read4 = make_pair("room", seed=9, M=30000, N=6000)
+    base = O.icp(params(), ref4, refn, read4)
+    thr = float(np.float32(base["xicp_sums"][which] * (1.0 + rel)))
+    p = params(xicp_enough=thr, xicp_insufficient=1e9)
+    o = O.icp(p, ref4, refn, read4)
+    icp = B.ICP(_to_b(B, p))
+    icp.init_reference(ref4, refn)
+    g = icp.compute(read4, None, None, raise_on_error=False)
+    assert g["xicp_borderline"] >= 1
+    assert g["loc_xyz"].tolist() == o["loc_xyz"].tolist() and g["loc_rpy"].tolist() == o["loc_rpy"].tolist()
+    assert g["status"] == o["status"] and g["iterations"] == o["iterations"]
+    assert np.abs(g["T"] - o["T"]).max() < 1e-4
 
 
 @pytest.mark.gpu
