@@ -284,6 +284,21 @@ int b200_o3d_begin(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N
 int b200_o3d_step_linearize(b200_o3d* h, double* d_sums32 /* DEVICE pointer */);
 int b200_o3d_step_update(b200_o3d* h, const double* d_sums32 /* DEVICE pointer, totals over all slabs */);
 int b200_o3d_poll(b200_o3d* h, int* done, int* updates); /* synchronises the stream */
+/* The same loop with the sums exchanged over NVLink / NVSwitch PEER MEMORY inside the solve kernel instead of an
+ * allreduce between kernels (one process per GPU, or several handles in one process). Every rank:
+ *   b200_o3d_peer_init    allocates its mailbox; returns its device pointer and/or its 64-byte CUDA IPC handle;
+ *   (exchange the pointers / handles: torch.distributed.all_gather_object, MPI, ...)
+ *   b200_o3d_peer_connect maps the peers' mailboxes: mailboxes_dev[world] (+ devices[world], same process) or
+ *                         ipc_handles (world x 64 bytes, other processes); entry `rank` is ignored;
+ *   b200_o3d_enqueue_peers per registration: enqueues every iteration (match+linearise, exchange+solve) on `stream`
+ *                         (NULL: the handle's own) without any host synchronisation; b200_o3d_finish fetches the result.
+ * All ranks must run the same registrations in the same order with the same max_iteration (the packets carry a
+ * sequence number); a peer that does not deliver within 5 s makes b200_o3d_finish return B200_E_CUDA. */
+int b200_o3d_peer_init(b200_o3d* h, int rank, int world, void** mailbox_dev /* nullable */, void* ipc_handle_64 /* nullable */);
+int b200_o3d_peer_connect(b200_o3d* h, void* const* mailboxes_dev /* nullable */, const int* devices /* nullable */,
+                          const void* ipc_handles_64 /* nullable */);
+int b200_o3d_enqueue_peers(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16,
+                           void* stream);
 int b200_o3d_finish(b200_o3d* h, b200_o3d_result* res);
 /* correspondence_set_: matched target index per source point (-2: owned by another slab) (-1: none) and squared distances; either may be NULL */
 int b200_o3d_get_correspondences(b200_o3d* h, int32_t* ids_N, float* dists_N);

@@ -476,6 +476,33 @@ class O3dICP:
         _check(load().b200_o3d_begin(self._h, _fp(src4), _fp(normals), self._n, Tc.ctypes.data_as(C.POINTER(C.c_double)),
                                      C.c_void_p(stream or 0)))
 
+    # ---- peer exchange over NVLink / NVSwitch peer memory (include/b200reg.h: b200_o3d_peer_*)
+    def peer_init(self, rank, world):
+        """-> (device pointer of this rank's mailbox, its 64-byte CUDA IPC handle)"""
+        ptr = C.c_void_p()
+        handle = C.create_string_buffer(64)
+        _check(load().b200_o3d_peer_init(self._h, int(rank), int(world), C.byref(ptr), handle))
+        return ptr.value, handle.raw
+
+    def peer_connect(self, pointers=None, devices=None, handles=None):
+        """pointers (+ devices): mailboxes of handles living in this process; handles: IPC handles of other processes"""
+        if pointers is not None:
+            arr = (C.c_void_p * len(pointers))(*[C.c_void_p(p_) for p_ in pointers])
+            dev = None if devices is None else (C.c_int * len(devices))(*[int(d) for d in devices])
+            _check(load().b200_o3d_peer_connect(self._h, arr, dev, None))
+        else:
+            _check(load().b200_o3d_peer_connect(self._h, None, None, b"".join(handles)))
+
+    def enqueue_peers(self, src4, normals=None, init=None, stream=None):
+        """every iteration of one registration enqueued without host synchronisation; finish() fetches the result"""
+        src4, normals = f32(src4), f32(normals)
+        Ti = np.eye(4) if init is None else np.asarray(init, np.float64)
+        Tc = np.ascontiguousarray(Ti.T).ravel()
+        self._n = src4.shape[0]
+        self._keep = (src4, normals, Tc)   # the uploads are asynchronous
+        _check(load().b200_o3d_enqueue_peers(self._h, _fp(src4), _fp(normals), self._n,
+                                             Tc.ctypes.data_as(C.POINTER(C.c_double)), C.c_void_p(stream or 0)))
+
     def step_linearize(self, sums_ptr):
         _check(load().b200_o3d_step_linearize(self._h, C.c_void_p(sums_ptr)))
 

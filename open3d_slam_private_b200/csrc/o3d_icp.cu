@@ -262,34 +262,10 @@ __global__ void __launch_bounds__(kThreads) o3d_reduce_kernel(const __grid_const
   }
 }
 
-// one CTA: reduce, test convergence, solve, update
-// sums == nullptr: reduce this device's partials and go on; otherwise `sums` already holds the totals over all slabs
-// (after the allreduce) and the partials are not read
-__global__ void __launch_bounds__(kThreads) o3d_solve_kernel(const __grid_constant__ O3dParams p, int nblocks,
-                                                             const double* __restrict__ sums) {
-  __shared__ double s_sum[kThreads / kVals][kVals];
-  __shared__ double s_tot[kVals];
+// thread 0 of the solving CTA: fitness / RMSE of this match, convergence test against the previous one, the update
+// (TransformationEstimation*::ComputeTransformation) and T <- U T. s_tot: the 32 sums over all CTAs (and all slabs).
+__device__ void o3d_solve_tail(const O3dParams& p, const double* s_tot) {
   O3dState* st = p.st;
-  if (st->done) return;
-  const int tid = threadIdx.x;
-  if (sums) {
-    if (tid < kVals) s_tot[tid] = sums[tid];
-    __syncthreads();
-  } else {  // fixed order: slice-major over CTAs, then slices in order
-    const int c = tid & (kVals - 1), slice = tid / kVals;
-    constexpr int kSlices = kThreads / kVals;
-    double s = 0.0;
-    for (int b = slice; b < nblocks; b += kSlices) s += p.partials[(size_t)b * kVals + c];
-    s_sum[slice][c] = s;
-    __syncthreads();
-    if (tid < kVals) {
-      double t = 0.0;
-      for (int sl = 0; sl < kSlices; ++sl) t += s_sum[sl][tid];
-      s_tot[tid] = t;
-    }
-    __syncthreads();
-  }
-  if (tid != 0) return;
   const double cnt = s_tot[27];
   const double fit = cnt / (double)p.N;
   const double err = cnt > 0.0 ? sqrt(s_tot[28] / cnt) : 0.0;
@@ -377,6 +353,127 @@ __global__ void __launch_bounds__(kThreads) o3d_solve_kernel(const __grid_consta
   if (stop) st->done = 1;
 }
 
+// one CTA: reduce, test convergence, solve, update
+// sums == nullptr: reduce this device's partials and go on; otherwise `sums` already holds the totals over all slabs
+// (after the allreduce) and the partials are not read
+__global__ void __launch_bounds__(kThreads) o3d_solve_kernel(const __grid_constant__ O3dParams p, int nblocks,
+                                                             const double* __restrict__ sums) {
+  __shared__ double s_sum[kThreads / kVals][kVals];
+  __shared__ double s_tot[kVals];
+  O3dState* st = p.st;
+  if (st->done) return;
+  const int tid = threadIdx.x;
+  if (sums) {
+    if (tid < kVals) s_tot[tid] = sums[tid];
+    __syncthreads();
+  } else {  // fixed order: slice-major over CTAs, then slices in order
+    const int c = tid & (kVals - 1), slice = tid / kVals;
+    constexpr int kSlices = kThreads / kVals;
+    double s = 0.0;
+    for (int b = slice; b < nblocks; b += kSlices) s += p.partials[(size_t)b * kVals + c];
+    s_sum[slice][c] = s;
+    __syncthreads();
+    if (tid < kVals) {
+      double t = 0.0;
+      for (int sl = 0; sl < kSlices; ++sl) t += s_sum[sl][tid];
+      s_tot[tid] = t;
+    }
+    __syncthreads();
+  }
+  if (tid != 0) return;
+  o3d_solve_tail(p, s_tot);
+}
+
+// ---- peer exchange of the sums over NVLink / NVSwitch peer memory (partitioned map, one slab per GPU) ---------------
+// Replaces "reduce kernel -> NCCL allreduce of 32 doubles -> solve kernel" by ONE kernel per iteration: reduce this
+// device's partials, store them straight into every peer's mailbox (plain 8-byte stores to peer memory mapped with
+// CUDA IPC or, inside one process, peer access), wait until every peer's contribution has arrived in the own mailbox,
+// add the contributions in rank order (bit-identical totals on every rank, so no broadcast) and solve. The transfer
+// is 64 packets of 8 bytes per peer in NCCL's "LL" style: {32 data bits, 32-bit sequence number} written with one
+// 8-byte store, so a packet is valid exactly when its sequence number is the expected one — no fence, no flag word,
+// no host round trip; the sequence number (steps since the mailbox was created) doubles as the parity that keeps a
+// rank that is one step ahead from overwriting what a slower rank still has to read.
+constexpr int kPeerMax = 16;
+constexpr int kPackets = 2 * kVals;   // a double travels as two packets
+struct PeerView {
+  unsigned long long* box[kPeerMax];  // box[r]: rank r's mailbox [2 parities][world][kPackets] as seen from this device
+  int rank, world;
+  unsigned seq_base;                  // sequence number of the step before this registration's first
+  long long timeout_cycles;
+};
+
+__device__ __forceinline__ void peer_store(unsigned long long* a, unsigned long long v) {
+  asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(a), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long peer_load(const unsigned long long* a) {
+  unsigned long long v;
+  asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(a) : "memory");
+  return v;
+}
+
+__global__ void __launch_bounds__(kThreads) o3d_exchange_solve_kernel(const __grid_constant__ O3dParams p, int nblocks,
+                                                                      const __grid_constant__ PeerView pv) {
+  __shared__ double s_sum[kThreads / kVals][kVals];
+  __shared__ double s_tot[kVals];
+  __shared__ unsigned s_half[kPeerMax][kPackets];
+  __shared__ int s_fail;
+  O3dState* st = p.st;
+  if (st->done) return;
+  const int tid = threadIdx.x;
+  if (tid == 0) s_fail = 0;
+  {  // this device's sums, fixed order: slice-major over CTAs, then slices in order
+    const int c = tid & (kVals - 1), slice = tid / kVals;
+    constexpr int kSlices = kThreads / kVals;
+    double s = 0.0;
+    for (int b = slice; b < nblocks; b += kSlices) s += p.partials[(size_t)b * kVals + c];
+    s_sum[slice][c] = s;
+    __syncthreads();
+    if (tid < kVals) {
+      double t = 0.0;
+      for (int sl = 0; sl < kSlices; ++sl) t += s_sum[sl][tid];
+      s_tot[tid] = t;
+    }
+    __syncthreads();
+  }
+  const unsigned seq = pv.seq_base + (unsigned)st->matches_done + 1u;
+  const size_t par = (size_t)(seq & 1u) * (size_t)pv.world;
+  // scatter: packet k of my sums into slot [parity][my rank] of every rank's mailbox (mine included)
+  for (int t = tid; t < pv.world * kPackets; t += kThreads) {
+    const int r = t / kPackets, k = t - r * kPackets;
+    const unsigned long long bits = (unsigned long long)__double_as_longlong(s_tot[k >> 1]);
+    const unsigned half = (k & 1) ? (unsigned)(bits >> 32) : (unsigned)bits;
+    peer_store(pv.box[r] + (par + (size_t)pv.rank) * kPackets + k, ((unsigned long long)seq << 32) | half);
+  }
+  // gather: wait for packet k of every rank in my own mailbox
+  const long long t0 = clock64();
+  for (int t = tid; t < pv.world * kPackets; t += kThreads) {
+    const int r = t / kPackets, k = t - r * kPackets;
+    const unsigned long long* a = pv.box[pv.rank] + (par + (size_t)r) * kPackets + k;
+    unsigned long long v = peer_load(a);
+    while ((unsigned)(v >> 32) != seq) {
+      if (clock64() - t0 > pv.timeout_cycles) { s_fail = 1; break; }
+      __nanosleep(20);
+      v = peer_load(a);
+    }
+    s_half[r][k] = (unsigned)v;
+  }
+  __syncthreads();
+  if (s_fail) {  // a peer never delivered (crashed / out of step): stop instead of hanging the device
+    if (tid == 0) { st->status = B200_E_CUDA; st->done = 1; }
+    return;
+  }
+  if (tid < kVals) {  // totals in rank order: the same additions on every rank
+    double t = 0.0;
+    for (int r = 0; r < pv.world; ++r)
+      t += __longlong_as_double((long long)(((unsigned long long)s_half[r][2 * tid + 1] << 32) | s_half[r][2 * tid]));
+    s_tot[tid] = t;
+  }
+  __syncthreads();
+  if (tid != 0) return;
+  o3d_solve_tail(p, s_tot);
+}
+
+
 // estimateNormalsOrCovariancesIfNeeded's post-processing (CloudRegistration.cpp:67-79): NormalizeNormals, then
 // OrientNormalsTowardsCameraLocation with the camera at the origin of the cloud's frame; in double like the host
 __global__ void __launch_bounds__(kThreads) o3d_orient_normals_kernel(const float4* __restrict__ pts,
@@ -423,6 +520,12 @@ struct b200_o3d {
   cudaStream_t run_stream = nullptr;
   bool running = false;
   int launches = 0;
+  // peer exchange (o3d_exchange_solve_kernel)
+  unsigned long long* d_mailbox = nullptr;
+  PeerView pv;
+  bool peers_ready = false;
+  unsigned peer_seq = 0;
+  void* opened[kPeerMax] = {};   // mailboxes mapped with cudaIpcOpenMemHandle
 };
 
 extern "C" {
@@ -475,6 +578,9 @@ void b200_o3d_destroy(b200_o3d* h) {
     cudaFree(h->d_src); cudaFree(h->d_src_n); cudaFree(h->d_stage3); cudaFree(h->d_ids); cudaFree(h->d_dists);
     cudaFree(h->d_partials); cudaFree(h->d_state); cudaFree(h->d_gid); cudaFree(h->d_nstage);
     cudaFreeHost(h->h_state);
+    for (int r = 0; r < kPeerMax; ++r)
+      if (h->opened[r]) cudaIpcCloseMemHandle(h->opened[r]);
+    cudaFree(h->d_mailbox);
     for (int i = 0; i < 3; ++i)
       if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     h->map.release();
@@ -626,6 +732,86 @@ int b200_o3d_step_update(b200_o3d* h, const double* d_sums32) {
   return B200_OK;
 }
 
+int b200_o3d_peer_init(b200_o3d* h, int rank, int world, void** mailbox_dev, void* ipc_handle_64) {
+  if (!h || world < 1 || world > kPeerMax || rank < 0 || rank >= world) {
+    set_error("b200_o3d_peer_init: need 0 <= rank < world <= 16");
+    return B200_E_BAD_PARAM;
+  }
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "the C ABI hands IPC handles around as 64 bytes");
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  h->peers_ready = false;
+  for (int r = 0; r < kPeerMax; ++r)
+    if (h->opened[r]) { cudaIpcCloseMemHandle(h->opened[r]); h->opened[r] = nullptr; }
+  cudaFree(h->d_mailbox);
+  h->d_mailbox = nullptr;
+  const size_t bytes = (size_t)2 * world * kPackets * sizeof(unsigned long long);
+  B200_CUDA(cudaMalloc(&h->d_mailbox, bytes));
+  B200_CUDA(cudaMemset(h->d_mailbox, 0, bytes));   // sequence number 0 is never sent
+  B200_CUDA(cudaDeviceSynchronize());
+  std::memset(&h->pv, 0, sizeof(h->pv));
+  h->pv.rank = rank; h->pv.world = world;
+  h->peer_seq = 0;
+  if (mailbox_dev) *mailbox_dev = h->d_mailbox;
+  if (ipc_handle_64) {
+    cudaIpcMemHandle_t ih;
+    B200_CUDA(cudaIpcGetMemHandle(&ih, h->d_mailbox));
+    std::memcpy(ipc_handle_64, &ih, 64);
+  }
+  return B200_OK;
+}
+
+int b200_o3d_peer_connect(b200_o3d* h, void* const* mailboxes_dev, const int* devices, const void* ipc_handles_64) {
+  if (!h || !h->d_mailbox || (!mailboxes_dev && !ipc_handles_64)) {
+    set_error("b200_o3d_peer_connect: call b200_o3d_peer_init first and pass pointers or IPC handles");
+    return B200_E_BAD_PARAM;
+  }
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  for (int r = 0; r < h->pv.world; ++r) {
+    if (r == h->pv.rank) { h->pv.box[r] = h->d_mailbox; continue; }
+    if (mailboxes_dev) {  // same process: the pointer is valid here once peer access is on
+      if (devices && devices[r] != h->device) {
+        const cudaError_t e = cudaDeviceEnablePeerAccess(devices[r], 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return cuda_fail(e, "cudaDeviceEnablePeerAccess", __FILE__, __LINE__);
+        cudaGetLastError();
+      }
+      h->pv.box[r] = (unsigned long long*)mailboxes_dev[r];
+    } else {
+      cudaIpcMemHandle_t ih;
+      std::memcpy(&ih, (const char*)ipc_handles_64 + (size_t)64 * r, 64);
+      void* ptr = nullptr;
+      B200_CUDA(cudaIpcOpenMemHandle(&ptr, ih, cudaIpcMemLazyEnablePeerAccess));
+      h->opened[r] = ptr;
+      h->pv.box[r] = (unsigned long long*)ptr;
+    }
+  }
+  int khz = 0;
+  cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, h->device);
+  h->pv.timeout_cycles = (long long)(khz > 0 ? khz : 1500000) * 1000LL * 5LL;   // 5 s of SM clock
+  h->peers_ready = true;
+  return B200_OK;
+}
+
+int b200_o3d_enqueue_peers(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16,
+                           void* stream) {
+  if (!h || !h->peers_ready) { set_error("b200_o3d_enqueue_peers: peers not connected"); return B200_E_NOT_INITIALIZED; }
+  if (h->own_axis < 0 && h->pv.world > 1) { set_error("b200_o3d_enqueue_peers: no partition set"); return B200_E_NOT_INITIALIZED; }
+  B200_TRY(b200_o3d_begin(h, src4xN, srcn3xN, N, init16, stream));
+  DeviceGuard dg(h->device);
+  h->pv.seq_base = h->peer_seq;
+  // max_iteration updates need max_iteration + 1 matches; launches after `done` return at once (on every rank at the
+  // same step: the totals are bit-identical), so nothing is sent or awaited any more
+  for (int it = 0; it <= h->prm.max_iteration; ++it) {
+    o3d_match_lin_kernel<<<h->blocks, kThreads, 0, h->run_stream>>>(h->p);
+    o3d_exchange_solve_kernel<<<1, kThreads, 0, h->run_stream>>>(h->p, h->blocks, h->pv);
+  }
+  h->peer_seq += (unsigned)(h->prm.max_iteration + 1);
+  h->launches += 2 * (h->prm.max_iteration + 1);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
 int b200_o3d_poll(b200_o3d* h, int* done, int* updates) {
   if (!h || !h->running) { set_error("b200_o3d_poll: no registration begun"); return B200_E_NOT_INITIALIZED; }
   DeviceGuard dg(h->device);
@@ -652,6 +838,10 @@ int b200_o3d_finish(b200_o3d* h, b200_o3d_result* res) {
   res->kernel_launches = h->launches;
   B200_CUDA(cudaEventElapsedTime(&res->device_ms, h->ev[1], h->ev[2]));
   B200_CUDA(cudaEventElapsedTime(&res->total_ms, h->ev[0], h->ev[2]));
+  if (h->h_state->status != 0) {
+    set_error("b200_o3d: a peer's sums did not arrive within 5 s (rank missing or out of step)");
+    return h->h_state->status;
+  }
   return B200_OK;
 }
 

@@ -71,9 +71,27 @@ class SlabICP:
         self.poll_every = max(1, int(poll_every))
         self.sums = torch.zeros(N_SUMS, dtype=torch.float64, device="cuda:%d" % device)
         self.collectives = 0
+        self.peers = False
+
+    def connect_peers(self, dist):
+        """Exchange the sums over NVLink / NVSwitch peer memory inside the solve kernel instead of an allreduce between
+        kernels: every rank allocates a mailbox, the CUDA IPC handles travel once through dist.all_gather_object, and
+        from then on a registration is enqueued whole (no collective, no host polling)."""
+        rank, world = dist.get_rank(), dist.get_world_size()
+        _, handle = self.h.peer_init(rank, world)
+        handles = [None] * world
+        dist.all_gather_object(handles, handle)
+        self.h.peer_connect(handles=handles)
+        dist.barrier()
+        self.peers = True
 
     def register(self, src4, src_normals=None, init=None):
         torch = self.torch
+        if self.peers:
+            self.h.enqueue_peers(src4, src_normals, init)
+            res = self.h.finish()
+            res["collectives"] = 0
+            return res
         with torch.cuda.device(self.device):
             # torch's default stream is the legacy NULL stream: name it explicitly (cudaStreamLegacy == 0x1), a NULL
             # argument would select the handle's own stream and lose the ordering with the allreduce
@@ -113,7 +131,8 @@ def merge_correspondences(ids_list):
 
 def register_partitioned(map4, map_normals, src4, src_normals=None, init=None, dist=None, device=None, **kw):
     """Driver for one process per GPU: every rank passes the same map (or at least its own slab's points in map
-    order), builds its slab and runs the loop with an NCCL allreduce. dist = torch.distributed (initialised) or None."""
+    order), builds its slab and runs the loop with an NCCL allreduce (exchange="nccl") or with the sums exchanged over
+    peer memory inside the solve kernel (exchange="peer"). dist = torch.distributed (initialised) or None."""
     import torch
     world = dist.get_world_size() if dist is not None else 1
     rank = dist.get_rank() if dist is not None else 0
@@ -126,8 +145,11 @@ def register_partitioned(map4, map_normals, src4, src_normals=None, init=None, d
     if world > 1:
         def ar(t):
             dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    exchange = kw.pop("exchange", "nccl")
     slab = SlabICP(np.ascontiguousarray(map4[gid]), None if map_normals is None else np.ascontiguousarray(map_normals[gid]),
                    gid, axis, float(edges[rank]), float(edges[rank + 1]), device=device, allreduce=ar, **kw)
+    if world > 1 and exchange == "peer":
+        slab.connect_peers(dist)
     res = slab.register(src4, src_normals, init)
     ids, _ = slab.correspondences()
     if world > 1:
