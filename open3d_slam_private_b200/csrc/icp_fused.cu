@@ -49,6 +49,7 @@ struct BlockState {
   float wsum;
   // TrimmedDist bracket predicted from the previous iteration's limit (single-barrier path)
   int have_bracket, try_fast, path;
+  int coh;   // log2 of the run of consecutive scan points per warp in this iteration (query_of)
   float lim_prev, delta, lo, hi, dens, step_prev;
   unsigned limit_bits;
   float H[36], b[6], x[6];
@@ -58,6 +59,8 @@ struct BlockState {
 };
 
 constexpr int kWarps = kIcpThreads / 32;
+static_assert(sizeof(Warp1Scratch) * kWarps <= (size_t)kFastVals * kIcpThreads * sizeof(float),
+              "the search scratch must fit into the staging tile it shares");
 
 __device__ __forceinline__ unsigned block_excl_scan(unsigned v, unsigned* s, unsigned& total) {
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -220,7 +223,15 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
   unsigned long long ts[6] = {0ull, 0ull, 0ull, 0ull, 0ull, 0ull};
   while (true) {
     if (stamp) ts[0] = gtimer();
-    if (tid == 0) rigid_prepare(S.T_iter, S.Tc, S.R9);
+    if (tid == 0) {
+      rigid_prepare(S.T_iter, S.Tc, S.R9);
+      // p.coh_log2 < 0: automatic. The previous TrimmedDist limit (a high quantile of the match distances) tells how far
+      // the queries still are from their neighbours, in cells; without it, from the third iteration on.
+      if (p.coh_log2 >= 0) S.coh = p.coh_log2;
+      else if (S.iteration == 0) S.coh = 0;
+      else if (p.use_trimmed) S.coh = (S.have_bracket && sqrtf(S.lim_prev) * p.g.inv_cell < 0.6f) ? 5 : 0;
+      else S.coh = S.iteration >= 2 ? 5 : 0;
+    }
     zero_hist(s_hist);  // includes __syncthreads
     const int par = S.iteration & 1;
     unsigned* gh = p.hist + (size_t)par * 3 * kHistBins;
@@ -240,6 +251,11 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     // is a warp collective.
     const int nslots = (p.N + 31) >> 5;
     const int rounds = (nslots + (nthreads >> 5) - 1) / (nthreads >> 5);  // grid-uniform trip count
+    // Coherent warps (32 consecutive scan points: their cell rows and candidates share 128-byte lines, 1 L1 wavefront
+    // instead of up to 32) once nearly every query is settled by its own 2x2x2 block, i.e. when all queries cost the
+    // same; scattered lanes while some queries still need the cooperative passes (a coherent warp full of expensive
+    // queries is a tail the whole grid waits for: measured 3x on the first iteration).
+    const int coh = S.coh;
     // single-barrier shape for this iteration? (needs the previous limit when TrimmedDist is in the chain)
     const bool fast = (K == 1) && p.fast_path && p.minimizer == 0 && (!p.use_trimmed || (S.have_bracket && S.try_fast)) &&
                       !(xicp && S.iteration == 0);
@@ -248,7 +264,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     unsigned cand_base = 0u;  // candidates this CTA has parked so far
     for (int round = 0; round < rounds; ++round) {
       const int slot = (gtid >> 5) + round * (nthreads >> 5);
-      const int i = slot < nslots ? query_of(slot, lane, nslots, p.coh_log2, qstride) : p.N;
+      const int i = slot < nslots ? query_of(slot, lane, nslots, coh, qstride) : p.N;
       const bool in = i < p.N;
       const float4 q = in ? apply_T(S.Tc, __ldg(&p.reading[i])) : make_float4(0.f, 0.f, 0.f, 1.f);
       unsigned vis = 0;
@@ -256,8 +272,9 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
         float bd; int bid, bsp;
         unsigned w_rows = 0, w_pass = 0;
         const unsigned long long w_t0 = p.debug_stats ? gtimer() : 0ull;
-        knn_query_warp1(p.g, in, q.x, q.y, q.z, p.md2, bd, bid, bsp, vis, p.debug_stats ? &w_rows : nullptr,
-                        p.debug_stats ? &w_pass : nullptr);
+        // the search's per-warp scratch shares the staging tile: the tile is written only after the barrier below
+        knn_query_warp1(p.g, in, q.x, q.y, q.z, p.md2, bd, bid, bsp, vis, reinterpret_cast<Warp1Scratch*>(s_dyn)[wid],
+                        p.debug_stats ? &w_rows : nullptr, p.debug_stats ? &w_pass : nullptr);
         if (p.debug_stats) {
           dbg_rows += w_rows;
           if (p.dbg_warp && S.iteration == 0) {
@@ -326,6 +343,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
             if (!valid) w = 0.f;   // ErrorElements keeps pairs with a valid dist and a non-zero weight
           }
           // park the candidates of this round in the CTA's segment, in thread order (deterministic)
+          if (!p.use_trimmed) __syncthreads();   // (the scan below has its own barriers) every warp has left the search
           if (p.use_trimmed) {
             unsigned tot;
             const unsigned pos = block_excl_scan(is_cand, s_scan, tot);
@@ -581,7 +599,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     for (int t = tid; t < kWarps * kAccum; t += kIcpThreads) (&s_red[0][0])[t] = 0.0;
     __syncthreads();
     for (int slot = gtid >> 5; slot < nslots; slot += nthreads >> 5) {  // same map as phase 1 (no barrier needed in between)
-      const int i = query_of(slot, lane, nslots, p.coh_log2, qstride);
+      const int i = query_of(slot, lane, nslots, coh, qstride);
       const bool in = i < p.N;
       float4 q = make_float4(0.f, 0.f, 0.f, 1.f);
       float3 nq = make_float3(0.f, 0.f, 0.f);
@@ -760,7 +778,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
         __syncthreads();
         const float cmin = p.x_cos_min, cstr = p.x_cos_strong;
         for (int slot = gtid >> 5; slot < nslots; slot += nthreads >> 5) {
-          const int i = query_of(slot, lane, nslots, p.coh_log2, qstride);
+          const int i = query_of(slot, lane, nslots, coh, qstride);
           double acc[12];
 #pragma unroll
           for (int t = 0; t < 12; ++t) acc[t] = 0.0;

@@ -124,7 +124,7 @@ struct b200_icp {
   float* d_cand_d = nullptr; int* d_cand_q = nullptr; float4* d_cand_rec = nullptr;
   size_t cap_cand = 0;
   int fast_path = 1;  // env B200_ICP_FAST=0 forces the general iteration
-  int coh_log2 = 0;   // env B200_ICP_COH=0..5: see query_of (icp_fused.cu)
+  int coh_log2 = -1;  // env B200_ICP_COH=0..5 pins the coherent run of query_of (icp_fused.cu); default: chosen per iteration
   unsigned* d_hist = nullptr;
   double *d_partials = nullptr, *d_partials2 = nullptr, *d_meanpart = nullptr;
   IcpDeviceResult* d_out = nullptr;

@@ -73,7 +73,8 @@ struct IcpKernelParams {
   float* cand_d; int* cand_q; float4* cand_rec;   // capacity gridDim * cand_seg (cand_rec: 2 float4 per candidate)
   int cand_seg;             // entries per CTA segment (set by the launcher)
   int fast_path;            // 0: always run the general 4-barrier iteration
-  int coh_log2;             // log2 of the run of consecutive scan points a warp keeps together (0..5), see query_of
+  int coh_log2;             // log2 of the run of consecutive scan points a warp keeps together (0..5), see query_of;
+                            // < 0: chosen per iteration by the kernel
   unsigned* dbg_warp;       // debug: per warp slot of iteration 0: {rows, candidates, passes, ns} (nullable)
   int debug_stats;          // collect IcpLogEntry::dbg_* (adds global atomics; profiling aid only)
   const float* frames;      // 16-float blocks: T_refIn_refMean, T_refMean_readMean, T_readIn_readMean, (centroid),

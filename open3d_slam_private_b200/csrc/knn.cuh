@@ -242,9 +242,9 @@ __device__ void knn_query(const GridView& g, float qx, float qy, float qz, float
 // that still needs cells owns nrows(lane) rows of its current box; the rows of all lanes are numbered consecutively
 // (warp prefix sum) and dealt 32 x kItems at a time. Phase A resolves kItems rows per lane to candidate ranges (all
 // cell-table loads of a round are in flight together); phase B scans them. A lane scanning a row for another lane's
-// query keeps a local best; a segmented warp minimum (items of one owner are contiguous) folds the 32 local
-// results, and every owner picks up the minimum of its segment. (d, id) ordering with ties -> smallest id keeps the
-// result independent of which lane scanned what. Cells already scanned by an earlier pass are scanned again
+// query keeps a local best and folds it into the owner's slot of the per-warp scratch with one shared-memory
+// atomicMin (Warp1Scratch). (d, id) ordering with ties -> smallest id keeps the result independent of which lane
+// scanned what. Cells already scanned by an earlier pass are scanned again
 // (harmless for k = 1: the same (d, id) never replaces itself), which keeps an item one contiguous range.
 __device__ __forceinline__ bool better1(float d, int id, float bd, int bid) {
   return d < bd || (d == bd && id < bid);
@@ -259,8 +259,26 @@ __device__ __forceinline__ float next_halfwidth(float h, float need) {
 
 constexpr int kItems = 4;
 
+// Per-warp shared-memory scratch of the cooperative passes: every lane publishes the geometry of its query once per
+// pass; the lanes that scan a row for it read what they need with three 16-byte loads (instead of 15 shuffles), and
+// fold their findings with ONE shared-memory atomicMin on the key (bits(d) << 32 | id) — d >= 0, so the unsigned order
+// of the key is the (d, id) order of the reference, ties -> smallest index — instead of a 20-shuffle segmented minimum.
+struct __align__(16) Warp1Scratch {
+  float4 geo[32];               // ux, uy, uz, slack
+  float4 pos[32];               // qx, qy, qz, radius still needed (cell units)
+  int4 box[32];                 // x0, x1, y0, z0 of the box
+  float2 misc[32];              // maxDist^2, bits(number of rows along y)
+  unsigned long long best[32];  // key of the best candidate so far
+  int bsp[32];                  // its position in the cell-sorted array
+  int incl[32];                 // inclusive prefix of the row counts
+};
+
+__device__ __forceinline__ unsigned long long key1(float d, int id) {
+  return ((unsigned long long)__float_as_uint(d) << 32) | (unsigned)id;
+}
+
 __device__ inline void knn_query_warp1(const GridView& g, bool active, float qx, float qy, float qz, float md2,
-                                       float& best_d, int& best_id, int& best_sp, unsigned& visited,
+                                       float& best_d, int& best_id, int& best_sp, unsigned& visited, Warp1Scratch& ws,
                                        unsigned* rows_out = nullptr, unsigned* passes_out = nullptr) {
   constexpr unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
@@ -318,9 +336,20 @@ __device__ inline void knn_query_warp1(const GridView& g, bool active, float qx,
     }
     const int excl = incl - nrows;
     const int total = __shfl_sync(FULL, incl, 31);
-    const int bny = B.ny();
+    __syncwarp();   // the previous pass (or call) is done with the scratch
+    ws.incl[lane] = incl;
+    if (need) {
+      ws.geo[lane] = make_float4(q.ux, q.uy, q.uz, q.slack);
+      ws.pos[lane] = make_float4(q.qx, q.qy, q.qz, rc);
+      ws.box[lane] = make_int4(B.x0, B.x1, B.y0, B.z0);
+      ws.misc[lane] = make_float2(q.md2, __int_as_float(B.ny()));
+      // an unmatched query carries id -1 = 0xffffffff in the key: above every real id at the same (infinite) distance
+      ws.best[lane] = key1(best_d, best_id);
+      ws.bsp[lane] = best_sp;
+    }
+    __syncwarp();
     for (int base = 0; base < total; base += 32 * kItems) {
-      // ---- phase A: item -> owner -> row -> candidate range
+      // ---- phase A: item -> owner -> row -> candidate range (all cell-table loads of the round in flight together)
       uint32_t ra[kItems], rb[kItems];
       int own[kItems];
 #pragma unroll
@@ -328,37 +357,32 @@ __device__ inline void knn_query_warp1(const GridView& g, bool active, float qx,
         const int t = base + s * 32 + lane;
         int o = 0;  // owner of item t: the first lane whose inclusive prefix exceeds t
 #pragma unroll
-        for (int step = 16; step > 0; step >>= 1) {
-          const int v = __shfl_sync(FULL, incl, (o + step - 1) & 31);
-          if (v <= t) o += step;
-        }
+        for (int step = 16; step > 0; step >>= 1)
+          if (ws.incl[(o + step - 1) & 31] <= t) o += step;
         const bool work = t < total;
         o &= 31;
-        const float oux = __shfl_sync(FULL, q.ux, o), ouy = __shfl_sync(FULL, q.uy, o), ouz = __shfl_sync(FULL, q.uz, o);
-        const float oslack = __shfl_sync(FULL, q.slack, o);
-        const float orc = __shfl_sync(FULL, rc, o);
-        const int obx0 = __shfl_sync(FULL, B.x0, o), obx1 = __shfl_sync(FULL, B.x1, o);
-        const int oby0 = __shfl_sync(FULL, B.y0, o), obz0 = __shfl_sync(FULL, B.z0, o);
-        const int ony = __shfl_sync(FULL, bny, o);
-        const int oexcl = __shfl_sync(FULL, excl, o);
         ra[s] = 0u; rb[s] = 0u;
         own[s] = work ? o : -1;
         if (work && rows_out) ++*rows_out;
         if (work) {
-          const int r = t - oexcl;
+          const float4 og = ws.geo[o];   // ux, uy, uz, slack
+          const int4 ob = ws.box[o];     // x0, x1, y0, z0
+          const float orc = ws.pos[o].w;
+          const int ony = __float_as_int(ws.misc[o].y);
+          const int r = t - (o ? ws.incl[o - 1] : 0);
           const int rz = (int)(((float)r + 0.5f) * __frcp_rn((float)ony));  // exact: r, ony < 2^20
-          const int iz = obz0 + rz, iy = oby0 + (r - rz * ony);
-          int xa = obx0, xb = obx1;
+          const int iz = ob.w + rz, iy = ob.z + (r - rz * ony);
+          int xa = ob.x, xb = ob.y;
           bool skip = false;
           if (orc != INFINITY) {  // clip the row to the ball of the radius still needed
-            const float dy = fmaxf(fmaxf((float)iy - ouy, ouy - (float)(iy + 1)) - oslack, 0.f);
-            const float dz = fmaxf(fmaxf((float)iz - ouz, ouz - (float)(iz + 1)) - oslack, 0.f);
+            const float dy = fmaxf(fmaxf((float)iy - og.y, og.y - (float)(iy + 1)) - og.w, 0.f);
+            const float dz = fmaxf(fmaxf((float)iz - og.z, og.z - (float)(iz + 1)) - og.w, 0.f);
             const float rem = orc * orc - dy * dy - dz * dz;
             if (rem < 0.f) skip = true;
             else {
-              const float xh = sqrtf(rem) * 1.00001f + oslack;
+              const float xh = sqrtf(rem) * 1.00001f + og.w;
               int lo, hi;
-              axis_range(oux, xh, g.nx, lo, hi);
+              axis_range(og.x, xh, g.nx, lo, hi);
               xa = max(xa, lo); xb = min(xb, hi);
               skip = xa > xb;
             }
@@ -369,40 +393,32 @@ __device__ inline void knn_query_warp1(const GridView& g, bool active, float qx,
           }
         }
       }
-      // ---- phase B: scan, fold, hand back
+      // ---- phase B: scan, fold into the owner's key
 #pragma unroll
       for (int s = 0; s < kItems; ++s) {
         if (base + s * 32 >= total) break;  // warp-uniform
         const int o = own[s] & 31;
-        QueryGeom oq;
-        oq.qx = __shfl_sync(FULL, q.qx, o); oq.qy = __shfl_sync(FULL, q.qy, o); oq.qz = __shfl_sync(FULL, q.qz, o);
-        oq.md2 = __shfl_sync(FULL, q.md2, o);
         float ld = INFINITY;
         int lid = -1, lsp = -1;
         if (own[s] >= 0 && rb[s] > ra[s]) {
+          const float4 op = ws.pos[o];
+          QueryGeom oq;
+          oq.qx = op.x; oq.qy = op.y; oq.qz = op.z; oq.md2 = ws.misc[o].x;
           auto visit = [&](float d, int id, int sp) { if (better1(d, id, ld, lid)) { ld = d; lid = id; lsp = sp; } };
           scan_range(g, oq, ra[s], rb[s], visited, visit);
         }
-        const int seg = own[s] >= 0 ? own[s] : -1 - lane;  // idle lanes form singleton segments
-#pragma unroll
-        for (int off = 1; off < 32; off <<= 1) {  // segmented minimum towards the first lane of every segment
-          const float d2 = __shfl_down_sync(FULL, ld, off);
-          const int id2 = __shfl_down_sync(FULL, lid, off);
-          const int sp2 = __shfl_down_sync(FULL, lsp, off);
-          const int sg2 = __shfl_down_sync(FULL, seg, off);
-          if (lane + off < 32 && sg2 == seg && better1(d2, id2, ld, lid)) { ld = d2; lid = id2; lsp = sp2; }
-        }
-        const int b0 = base + s * 32;
-        const int lo = max(excl, b0), hi = min(incl, b0 + 32);
-        const bool has = need && lo < hi;
-        const int src = has ? (lo - b0) : lane;
-        const float rd = __shfl_sync(FULL, ld, src);
-        const int rid = __shfl_sync(FULL, lid, src);
-        const int rsp = __shfl_sync(FULL, lsp, src);
-        if (has && better1(rd, rid, best_d, best_id)) { best_d = rd; best_id = rid; best_sp = rsp; }
+        const unsigned long long k = key1(ld, lid);
+        if (lid >= 0) atomicMin(&ws.best[o], k);
+        __syncwarp();
+        if (lid >= 0 && ws.best[o] == k) ws.bsp[o] = lsp;   // the one lane that holds the minimum (ids are unique)
       }
     }
+    __syncwarp();
     if (need) {
+      const unsigned long long k = ws.best[lane];
+      best_d = __uint_as_float((unsigned)(k >> 32));
+      best_id = (int)(unsigned)(k & 0xffffffffull);
+      best_sp = ws.bsp[lane];
       const float nd = need_radius(g, q, best_d);
       if (h >= nd || covers_grid(g, B)) need = false;
       else h = next_halfwidth(h, nd);

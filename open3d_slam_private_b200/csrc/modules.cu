@@ -28,6 +28,7 @@ __global__ void __launch_bounds__(kThreads) knn_kernel(const __grid_constant__ G
                                                        float* __restrict__ dists,
                                                        unsigned long long* __restrict__ visited) {
   unsigned long long vis_total = 0ull;
+  __shared__ Warp1Scratch s_ws[K == 1 ? kThreads / 32 : 1];
   // warp-uniform trip count: the k = 1 search is a warp collective
   const int lane = threadIdx.x & 31;
   for (int base = (blockIdx.x * blockDim.x + threadIdx.x) - lane; base < N; base += gridDim.x * blockDim.x) {
@@ -42,7 +43,7 @@ __global__ void __launch_bounds__(kThreads) knn_kernel(const __grid_constant__ G
     unsigned vis = 0;
     if (K == 1) {
       float bd; int bid, bsp;
-      knn_query_warp1(g, in, q.x, q.y, q.z, m2, bd, bid, bsp, vis);
+      knn_query_warp1(g, in, q.x, q.y, q.z, m2, bd, bid, bsp, vis, s_ws[K == 1 ? (threadIdx.x >> 5) : 0]);
       if (in) { ids[i] = bid; dists[i] = bd; }
     } else if (in) {
       KList<K> L;

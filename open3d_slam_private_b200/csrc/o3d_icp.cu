@@ -76,6 +76,7 @@ __device__ __forceinline__ double3 gicp_axis(float4 n) {
 
 __global__ void __launch_bounds__(kThreads) o3d_match_lin_kernel(const __grid_constant__ O3dParams p) {
   __shared__ double s_part[kThreads / 32][kVals];
+  __shared__ Warp1Scratch s_ws[kThreads / 32];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   if (p.st->done) return;
   double T[12];
@@ -104,7 +105,7 @@ __global__ void __launch_bounds__(kThreads) o3d_match_lin_kernel(const __grid_co
     }
     float bd; int bid, bsp;
     unsigned vis = 0;
-    knn_query_warp1(p.g, mine, q.x, q.y, q.z, p.md2, bd, bid, bsp, vis);
+    knn_query_warp1(p.g, mine, q.x, q.y, q.z, p.md2, bd, bid, bsp, vis, s_ws[wid]);
     if (!in) continue;
     if (!mine) { p.ids[i] = -2; p.dists[i] = __int_as_float(0x7f800000); continue; }   // another slab's query
     p.ids[i] = (bid >= 0 && p.gid) ? __ldg(&p.gid[bid]) : bid; p.dists[i] = bd;
