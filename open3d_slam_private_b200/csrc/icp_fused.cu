@@ -229,7 +229,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
       // the queries still are from their neighbours, in cells; without it, from the third iteration on.
       if (p.coh_log2 >= 0) S.coh = p.coh_log2;
       else if (S.iteration == 0) S.coh = 0;
-      else if (p.use_trimmed) S.coh = (S.have_bracket && sqrtf(S.lim_prev) * p.g.inv_cell < 0.6f) ? 5 : 0;
+      else if (p.use_trimmed) S.coh = (S.have_bracket && sqrtf(S.lim_prev) * p.g.inv_cell < 0.4f) ? 5 : 0;
       else S.coh = S.iteration >= 2 ? 5 : 0;
     }
     zero_hist(s_hist);  // includes __syncthreads

@@ -6,7 +6,7 @@ from open3d_slam_private_b200 import capi as B, synth
 import bench
 
 M = int(os.environ.get("MAP", 5_000_000)); N = int(os.environ.get("SCAN", 131072))
-d = synth.make_c2(M=M, N=N, n_poses=2)
+d = synth.make_c2(M=M, N=N, n_poses=int(os.environ.get("POSES", 2)))
 kw = bench.icp_kwargs(); kw["cell_size"] = float(os.environ.get("CELL", 0))
 icp = B.ICP(B.default_icp_params(**kw))
 icp.init_reference(synth.feat4(d["map_xyz"]), d["map_normals"])
