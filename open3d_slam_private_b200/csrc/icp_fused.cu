@@ -820,10 +820,19 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
           __stcg(&p.partials2[(size_t)blockIdx.x * 16 + tid], sv);
         }
         grid.sync();
-        if (tid < 12) {
+        {  // fixed order (slice-major over the CTAs, then the slices in order): the same sums in every CTA
+          const int c = tid & 15, slice = tid >> 4;
+          constexpr int kSl = kIcpThreads / 16;
           double sv = 0.0;
-          for (unsigned b = 0; b < gridDim.x; ++b) sv += __ldcg(&p.partials2[(size_t)b * 16 + tid]);
-          S.X.sums[tid] = sv;
+          for (unsigned b = slice; b < gridDim.x; b += kSl) sv += __ldcg(&p.partials2[(size_t)b * 16 + c]);
+          double* red2 = &s_red[0][0];   // kSl x 16 doubles
+          red2[slice * 16 + c] = sv;
+          __syncthreads();
+          if (tid < 12) {
+            double t = 0.0;
+            for (int sl = 0; sl < kSl; ++sl) t += red2[sl * 16 + tid];
+            S.X.sums[tid] = t;
+          }
         }
         __syncthreads();
         if (tid == 0) {

@@ -156,6 +156,13 @@ int orc_o3d_icp(int kind, const float* src4xN, int N, const float* tgt4xM, int M
                 int max_iteration, double rel_fitness, double rel_rmse, int knn_threads, double* T16, double* fitness,
                 double* rmse, int* iterations, int32_t* corr_ids);
 
+/* ---- scan pre-processing (see prep.cpp): open3d_slam croppers (croppers.cpp:25-164) and Open3D
+ * VoxelDownSample (recalled from upstream v0.15.1) ---- */
+int orc_crop(int kind, double radius_min, double radius_max, double min_z, double max_z, const double* center3,
+             int invert, const float* pts4xN, int N, int32_t* kept_idx);
+int orc_voxel_downsample(double voxel_size, const float* pts4xN, const float* nrm3xN, int N, double* out3xK,
+                         double* outn3xK, int32_t* first_idx);
+
 /* the same split as the reference's initReference / compute (one reference, many readings) */
 void* orc_icp_ref_create(const float* ref4xM, const float* refn3xM, int M, int mean_mode);
 void orc_icp_ref_free(void* h);

@@ -46,7 +46,7 @@ class IcpResult(C.Structure):
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("knn.cpp", "modules.cpp", "normals.cpp", "icp.cpp", "o3d.cpp", "oracle.h",
+    srcs = [os.path.join(_HERE, f) for f in ("knn.cpp", "modules.cpp", "normals.cpp", "icp.cpp", "o3d.cpp", "prep.cpp", "oracle.h",
                                              "la_small.hpp")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s"])
@@ -366,3 +366,29 @@ def o3d_icp(kind, src4, tgt4, tgt_normals=None, src_normals=None, max_dist=1.0, 
                            C.byref(it), _ip(ids))
     return dict(status=st, T=T.reshape(4, 4).T.copy(), fitness=fit.value, inlier_rmse=rmse.value,
                 iterations=it.value, ids=ids)
+
+
+def crop(kind, pts4, radius_min=0.0, radius_max=0.0, min_z=0.0, max_z=0.0, center=(0.0, 0.0, 0.0), invert=False):
+    """orc_crop -> indices of the kept points, input order (croppers.cpp:66-95)"""
+    pts4 = f32(pts4)
+    n = pts4.shape[0]
+    idx = np.empty(max(n, 1), np.int32)
+    c = (C.c_double * 3)(*[float(v) for v in center])
+    k = lib().orc_crop(int(kind), C.c_double(radius_min), C.c_double(radius_max), C.c_double(min_z), C.c_double(max_z), c,
+                       int(bool(invert)), _fp(pts4), n, _ip(idx))
+    return idx[:k].copy()
+
+
+def voxel_downsample(voxel_size, pts4, normals=None):
+    """orc_voxel_downsample -> (points Kx3 float64, normals Kx3 float64 or None, first index K int32)"""
+    pts4, normals = f32(pts4), f32(normals)
+    n = pts4.shape[0]
+    out = np.empty((max(n, 1), 3), np.float64)
+    outn = np.empty((max(n, 1), 3), np.float64) if normals is not None else None
+    first = np.empty(max(n, 1), np.int32)
+    dp = C.POINTER(C.c_double)
+    k = lib().orc_voxel_downsample(C.c_double(voxel_size), _fp(pts4), _fp(normals), n, out.ctypes.data_as(dp),
+                                   None if outn is None else outn.ctypes.data_as(dp), _ip(first))
+    if k < 0:
+        return k, None, None
+    return out[:k].copy(), (None if outn is None else outn[:k].copy()), first[:k].copy()
