@@ -303,6 +303,41 @@ int b200_o3d_finish(b200_o3d* h, b200_o3d_result* res);
 /* correspondence_set_: matched target index per source point (-2: owned by another slab) (-1: none) and squared distances; either may be NULL */
 int b200_o3d_get_correspondences(b200_o3d* h, int32_t* ids_N, float* dists_N);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Scan pre-processing — what open3d_slam runs on every scan before it registers it
+ * (ScanToMapRegistration.cpp:36-54, Odometry.cpp:22-26) and on the map before a patch is cut out (:90-104).
+ * Clouds are the float memory images used everywhere else in this header (4 x N features, 3 x N normals).
+ * ---------------------------------------------------------------------------------------------------------- */
+typedef struct b200_prep b200_prep;
+int b200_prep_create(b200_prep** out, int device);
+void b200_prep_destroy(b200_prep* h);
+
+/* croppingVolumeFactory's volumes (open3d_slam/src/croppers.cpp:25-47) */
+#define B200_CROP_NONE 0          /* CroppingVolume base class: everything is inside (:49-51) */
+#define B200_CROP_CYLINDER 1      /* CylinderCroppingVolume (:160-164): radius_max, min_z, max_z */
+#define B200_CROP_MIN_RADIUS 2    /* MinRadiusCroppingVolume (:147-151): radius_min */
+#define B200_CROP_MAX_RADIUS 3    /* MaxRadiusCroppingVolume (:129-133): radius_max */
+#define B200_CROP_MINMAX_RADIUS 4 /* MinMaxRadiusCroppingVolume (:113-118) */
+typedef struct {
+  int kind;
+  int invert;            /* CroppingVolume::setIsInvertVolume (:56-58) */
+  double radius_min, radius_max, min_z, max_z;
+  double center[3];      /* pose_.translation() (CroppingVolume::setPose, :59-61) */
+} b200_crop_params;
+/* CroppingVolume::crop(cloud) (croppers.cpp:66-95): the points inside the volume, in input order, with their normals
+ * (nrm3xN / outn3xN nullable) and — CroppingVolume::getIndicesWithinVolume (:62-71) — their indices (nullable).
+ * Outputs have capacity N; *n_out receives the number kept. */
+int b200_prep_crop(b200_prep* h, const b200_crop_params* prm, const float* pts4xN, const float* nrm3xN, int N,
+                   float* out4xN, float* outn3xN, int32_t* kept_idx, int* n_out);
+/* o3d_slam::voxelize (helpers.cpp:108-115) -> open3d PointCloud::VoxelDownSample(voxel_size) (Open3D v0.15.1, not in
+ * the reference tree): voxel index floor((p - (min_bound - voxel_size / 2)) / voxel_size), points and normals of a
+ * voxel averaged in double in input order. Output (capacity N, column-major 3 x K doubles like Open3D's points_) is
+ * ordered by the index of the first point of each voxel (Open3D's order is unspecified); first_idx nullable. */
+int b200_prep_voxel_downsample(b200_prep* h, double voxel_size, const float* pts4xN, const float* nrm3xN, int N,
+                               double* out3xK, double* outn3xK, int32_t* first_idx, int* n_out);
+/* device time of the last call's kernels (CUDA events, uploads and read-backs excluded) */
+int b200_prep_last_device_ms(const b200_prep* h, float* ms);
+
 #ifdef __cplusplus
 }
 #endif

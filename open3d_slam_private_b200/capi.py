@@ -537,3 +537,67 @@ class O3dICP:
             self.close()
         except Exception:
             pass
+
+
+# ---- scan pre-processing (include/b200reg.h: b200_prep_*) -----------------------------------------------------------
+CROP_NONE, CROP_CYLINDER, CROP_MIN_RADIUS, CROP_MAX_RADIUS, CROP_MINMAX_RADIUS = 0, 1, 2, 3, 4
+
+
+class CropParams(C.Structure):
+    _fields_ = [("kind", C.c_int), ("invert", C.c_int), ("radius_min", C.c_double), ("radius_max", C.c_double),
+                ("min_z", C.c_double), ("max_z", C.c_double), ("center", C.c_double * 3)]
+
+
+class Prep:
+    """open3d_slam's per-scan pre-processing on the device: croppers (croppers.cpp) and voxelize (helpers.cpp:108-115)."""
+
+    def __init__(self, device=0):
+        require_device()
+        self._h = C.c_void_p()
+        _check(load().b200_prep_create(C.byref(self._h), device))
+
+    def crop(self, kind, pts4, normals=None, radius_min=0.0, radius_max=0.0, min_z=0.0, max_z=0.0,
+             center=(0.0, 0.0, 0.0), invert=False):
+        """-> (points K x 4 float32, normals K x 3 or None, kept indices K int32)"""
+        pts4, normals = f32(pts4), f32(normals)
+        n = pts4.shape[0]
+        prm = CropParams(int(kind), int(bool(invert)), radius_min, radius_max, min_z, max_z, (C.c_double * 3)(*center))
+        out = np.empty((max(n, 1), 4), np.float32)
+        outn = np.empty((max(n, 1), 3), np.float32) if normals is not None else None
+        idx = np.empty(max(n, 1), np.int32)
+        k = C.c_int()
+        _check(load().b200_prep_crop(self._h, C.byref(prm), _fp(pts4), _fp(normals), n, _fp(out), _fp(outn), _ip(idx),
+                                     C.byref(k)))
+        k = k.value
+        return out[:k].copy(), (None if outn is None else outn[:k].copy()), idx[:k].copy()
+
+    def voxel_downsample(self, voxel_size, pts4, normals=None):
+        """-> (points K x 3 float64, normals K x 3 float64 or None, index of the first member K int32)"""
+        pts4, normals = f32(pts4), f32(normals)
+        n = pts4.shape[0]
+        out = np.empty((max(n, 1), 3), np.float64)
+        outn = np.empty((max(n, 1), 3), np.float64) if normals is not None else None
+        first = np.empty(max(n, 1), np.int32)
+        k = C.c_int()
+        dp = C.POINTER(C.c_double)
+        _check(load().b200_prep_voxel_downsample(self._h, C.c_double(voxel_size), _fp(pts4), _fp(normals), n,
+                                                 out.ctypes.data_as(dp), None if outn is None else outn.ctypes.data_as(dp),
+                                                 _ip(first), C.byref(k)))
+        k = k.value
+        return out[:k].copy(), (None if outn is None else outn[:k].copy()), first[:k].copy()
+
+    def last_device_ms(self):
+        ms = C.c_float()
+        _check(load().b200_prep_last_device_ms(self._h, C.byref(ms)))
+        return ms.value
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            load().b200_prep_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

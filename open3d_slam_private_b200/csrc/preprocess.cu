@@ -1,0 +1,409 @@
+// Scan pre-processing on the device: what open3d_slam runs on every scan before the registration
+// (ScanToMapRegistration.cpp:36-54, Odometry.cpp:22-26) and on the map before a patch is registered against
+// (ScanToMapRegistration.cpp:90-104):
+//   CroppingVolume::crop / getIndicesWithinVolume   open3d_slam/src/croppers.cpp:53-95, volumes :115-164
+//   o3d_slam::voxelize -> PointCloud::VoxelDownSample   helpers.cpp:108-115 (Open3D v0.15.1, recalled from upstream)
+// Both are HBM-bound streaming passes. Crop: predicate in double on the float coordinates, order-preserving
+// compaction (flag -> scan -> scatter). Voxel down-sample: voxel key per point, open-addressing hash table built with
+// 64-bit atomicCAS, voxels numbered by the index of their first point (deterministic; Open3D's own order is that of an
+// std::unordered_map), members gathered per voxel and sorted by index so that the double sums run in input order like
+// the reference's sequential accumulation => means bit-identical to the oracle's.
+#include "common.cuh"
+#include "grid_index.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+using namespace b200;
+
+namespace b200 {
+size_t scan_tiles_for(size_t n);
+int inclusive_scan_u32(uint32_t* d_data, size_t n, uint32_t* d_tile, cudaStream_t s);
+}  // namespace b200
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr unsigned long long kEmpty = 0xffffffffffffffffull;
+
+inline int blocks_for(size_t n) { return (int)std::max<size_t>(1, std::min<size_t>((n + kThreads - 1) / kThreads, 148 * 16)); }
+
+struct CropP {
+  int kind, invert;
+  double rmin, rmax, zmin, zmax, cx, cy, cz;
+};
+
+__global__ void crop_flag_kernel(const float4* __restrict__ p, int N, CropP c, uint32_t* __restrict__ flag) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+    const float4 v = __ldg(&p[i]);
+    const double px = (double)v.x, py = (double)v.y, pz = (double)v.z;
+    const double dx = px - c.cx, dy = py - c.cy, dz = pz - c.cz;
+    bool in = true;
+    if (c.kind == 1) in = pz >= c.zmin && pz <= c.zmax && sqrt(dx * dx + dy * dy) <= c.rmax;        // croppers.cpp:162-164
+    else if (c.kind == 2) in = sqrt(dx * dx + dy * dy + dz * dz) >= c.rmin;                          // :149-151
+    else if (c.kind == 3) in = sqrt(dx * dx + dy * dy + dz * dz) <= c.rmax;                          // :131-133
+    else if (c.kind == 4) { const double d = sqrt(dx * dx + dy * dy + dz * dz); in = d <= c.rmax && d >= c.rmin; }  // :115-118
+    if (c.invert) in = !in;                                                                           // :53-55
+    flag[i] = in ? 1u : 0u;
+  }
+}
+
+// scan = inclusive scan of the flags: point i is kept iff scan[i] != scan[i - 1]; its slot is scan[i] - 1
+__global__ void crop_scatter_kernel(const float4* __restrict__ p, const float* __restrict__ n3, int N,
+                                    const uint32_t* __restrict__ scan, float4* __restrict__ out,
+                                    float* __restrict__ outn3, int* __restrict__ idx) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+    const uint32_t s = scan[i], s0 = i ? scan[i - 1] : 0u;
+    if (s == s0) continue;
+    const uint32_t o = s - 1u;
+    out[o] = __ldg(&p[i]);
+    idx[o] = i;
+    if (n3) {
+      outn3[3 * (size_t)o] = n3[3 * (size_t)i];
+      outn3[3 * (size_t)o + 1] = n3[3 * (size_t)i + 1];
+      outn3[3 * (size_t)o + 2] = n3[3 * (size_t)i + 2];
+    }
+  }
+}
+
+__device__ __forceinline__ uint32_t f2ord(float f) {
+  const uint32_t b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+
+// min and max per axis: 6 ordered-uint atomics per block
+__global__ void minmax_kernel(const float4* __restrict__ p, int N, uint32_t* __restrict__ out6) {
+  float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+    const float4 v = __ldg(&p[i]);
+    mn[0] = fminf(mn[0], v.x); mn[1] = fminf(mn[1], v.y); mn[2] = fminf(mn[2], v.z);
+    mx[0] = fmaxf(mx[0], v.x); mx[1] = fmaxf(mx[1], v.y); mx[2] = fmaxf(mx[2], v.z);
+  }
+  __shared__ float s[6][kThreads / 32];
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    for (int o = 16; o > 0; o >>= 1) {
+      mn[d] = fminf(mn[d], __shfl_xor_sync(0xffffffffu, mn[d], o));
+      mx[d] = fmaxf(mx[d], __shfl_xor_sync(0xffffffffu, mx[d], o));
+    }
+    if ((threadIdx.x & 31) == 0) { s[d][threadIdx.x >> 5] = mn[d]; s[3 + d][threadIdx.x >> 5] = mx[d]; }
+  }
+  __syncthreads();
+  if (threadIdx.x < 6) {
+    float v = s[threadIdx.x][0];
+    for (int w = 1; w < kThreads / 32; ++w) v = threadIdx.x < 3 ? fminf(v, s[threadIdx.x][w]) : fmaxf(v, s[threadIdx.x][w]);
+    if (threadIdx.x < 3) atomicMin(&out6[threadIdx.x], f2ord(v));
+    else atomicMax(&out6[threadIdx.x], f2ord(v));
+  }
+}
+
+struct VoxP {
+  double mbx, mby, mbz, vs;
+  unsigned long long mask;   // table size - 1 (power of two)
+};
+
+__device__ __forceinline__ unsigned long long mix64(unsigned long long x) {
+  x ^= x >> 33; x *= 0xff51afd7ed558ccdull; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ull; x ^= x >> 33;
+  return x;
+}
+
+// voxel index = floor((p - voxel_min_bound) / voxel_size) per axis (double, like Open3D); key = 21 bits per axis.
+// Inserts the key (linear probing), remembers the slot of every point, counts the members and keeps the smallest
+// member index of every voxel.
+__global__ void voxel_insert_kernel(const float4* __restrict__ p, int N, VoxP v, unsigned long long* __restrict__ keys,
+                                    uint32_t* __restrict__ cnt, int* __restrict__ first, uint32_t* __restrict__ slot_of,
+                                    int* __restrict__ err) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+    const float4 q = __ldg(&p[i]);
+    const double fx = floor(((double)q.x - v.mbx) / v.vs), fy = floor(((double)q.y - v.mby) / v.vs),
+                 fz = floor(((double)q.z - v.mbz) / v.vs);
+    if (!(fx >= 0.0 && fx < 2097152.0 && fy >= 0.0 && fy < 2097152.0 && fz >= 0.0 && fz < 2097152.0)) {
+      *err = 1;   // NaN coordinate or more than 2^21 voxels along an axis
+      slot_of[i] = 0xffffffffu;
+      continue;
+    }
+    const unsigned long long key = (unsigned long long)fx | ((unsigned long long)fy << 21) | ((unsigned long long)fz << 42);
+    unsigned long long s = mix64(key) & v.mask;
+    while (true) {
+      const unsigned long long old = atomicCAS(&keys[s], kEmpty, key);
+      if (old == kEmpty || old == key) break;
+      s = (s + 1ull) & v.mask;
+    }
+    slot_of[i] = (uint32_t)s;
+    atomicAdd(&cnt[s], 1u);
+    atomicMin(&first[s], i);
+  }
+}
+
+// flag[first point of every voxel] = 1
+__global__ void voxel_mark_kernel(const unsigned long long* __restrict__ keys, const int* __restrict__ first,
+                                  size_t T, uint32_t* __restrict__ flag) {
+  for (size_t s = blockIdx.x * (size_t)blockDim.x + threadIdx.x; s < T; s += (size_t)gridDim.x * blockDim.x)
+    if (keys[s] != kEmpty) flag[first[s]] = 1u;
+}
+
+// voxel number = (inclusive scan of the flags)[first] - 1; counts moved into voxel order (cntK[v + 1], for the scan)
+__global__ void voxel_number_kernel(const unsigned long long* __restrict__ keys, const int* __restrict__ first,
+                                    const uint32_t* __restrict__ cnt, size_t T, const uint32_t* __restrict__ scan,
+                                    uint32_t* __restrict__ vox_of_slot, uint32_t* __restrict__ offs,
+                                    int* __restrict__ firstK) {
+  for (size_t s = blockIdx.x * (size_t)blockDim.x + threadIdx.x; s < T; s += (size_t)gridDim.x * blockDim.x)
+    if (keys[s] != kEmpty) {
+      const uint32_t v = scan[first[s]] - 1u;
+      vox_of_slot[s] = v;
+      offs[v + 1] = cnt[s];
+      firstK[v] = first[s];
+    }
+}
+
+// offs = inclusive scan => offs[v] = start of voxel v, offs[v + 1] = end
+__global__ void voxel_members_kernel(const uint32_t* __restrict__ slot_of, int N, const uint32_t* __restrict__ vox_of_slot,
+                                     const uint32_t* __restrict__ offs, uint32_t* __restrict__ cursor,
+                                     int* __restrict__ members) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+    const uint32_t s = slot_of[i];
+    if (s == 0xffffffffu) continue;
+    const uint32_t v = vox_of_slot[s];
+    members[offs[v] + atomicAdd(&cursor[v], 1u)] = i;
+  }
+}
+
+// one thread per voxel: members into ascending index order (insertion sort; voxels hold a handful of points), then the
+// sums in double in that order — the reference accumulates while it walks the cloud — and the average
+__global__ void voxel_mean_kernel(const float4* __restrict__ p, const float* __restrict__ n3, int K,
+                                  const uint32_t* __restrict__ offs, int* __restrict__ members,
+                                  double* __restrict__ out3, double* __restrict__ outn3) {
+  for (int v = blockIdx.x * blockDim.x + threadIdx.x; v < K; v += gridDim.x * blockDim.x) {
+    const uint32_t a = offs[v], b = offs[v + 1];
+    for (uint32_t i = a + 1; i < b; ++i) {
+      const int m = members[i];
+      uint32_t j = i;
+      while (j > a && members[j - 1] > m) { members[j] = members[j - 1]; --j; }
+      members[j] = m;
+    }
+    double sx = 0.0, sy = 0.0, sz = 0.0, nx = 0.0, ny = 0.0, nz = 0.0;
+    for (uint32_t i = a; i < b; ++i) {
+      const int m = members[i];
+      const float4 q = __ldg(&p[m]);
+      sx += (double)q.x; sy += (double)q.y; sz += (double)q.z;
+      if (n3) { nx += (double)n3[3 * (size_t)m]; ny += (double)n3[3 * (size_t)m + 1]; nz += (double)n3[3 * (size_t)m + 2]; }
+    }
+    const double c = (double)(b - a);
+    out3[3 * (size_t)v] = sx / c; out3[3 * (size_t)v + 1] = sy / c; out3[3 * (size_t)v + 2] = sz / c;
+    if (n3) { outn3[3 * (size_t)v] = nx / c; outn3[3 * (size_t)v + 1] = ny / c; outn3[3 * (size_t)v + 2] = nz / c; }
+  }
+}
+
+}  // namespace
+
+// =================================================================================================================
+// host side
+// =================================================================================================================
+struct b200_prep {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  struct Buf {
+    void* p = nullptr;
+    size_t cap = 0;
+  };
+  enum { PTS, N3, FLAG, TILE, OUT4, OUTN3, IDX, KEYS, CNT, FIRST, SLOT, VOX, OFFS, CUR, MEMB, OUT3D, OUTN3D, FIRSTK, SCR, NBUF };
+  Buf buf[NBUF];
+  float last_ms = 0.f;
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+};
+
+namespace {
+
+int ensure(b200_prep* h, int which, size_t bytes) {
+  b200_prep::Buf& b = h->buf[which];
+  if (bytes <= b.cap) return B200_OK;
+  cudaFree(b.p);
+  b.p = nullptr; b.cap = 0;
+  const size_t want = bytes + bytes / 4 + 256;
+  B200_CUDA(cudaMalloc(&b.p, want));
+  b.cap = want;
+  return B200_OK;
+}
+template <class T> T* ptr(b200_prep* h, int which) { return reinterpret_cast<T*>(h->buf[which].p); }
+
+int upload_cloud(b200_prep* h, const float* pts4xN, const float* nrm3xN, int N) {
+  B200_TRY(ensure(h, b200_prep::PTS, (size_t)N * sizeof(float4)));
+  B200_CUDA(cudaMemcpyAsync(h->buf[b200_prep::PTS].p, pts4xN, (size_t)N * sizeof(float4), cudaMemcpyHostToDevice, h->stream));
+  if (nrm3xN) {
+    B200_TRY(ensure(h, b200_prep::N3, (size_t)N * 3 * sizeof(float)));
+    B200_CUDA(cudaMemcpyAsync(h->buf[b200_prep::N3].p, nrm3xN, (size_t)N * 3 * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+  }
+  return B200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200_prep_create(b200_prep** out, int device) {
+  if (!out) { set_error("b200_prep_create: bad arguments"); return B200_E_BAD_PARAM; }
+  *out = nullptr;
+  DeviceGuard dg(device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  b200_prep* h = new (std::nothrow) b200_prep();
+  if (!h) { set_error("out of host memory"); return B200_E_CUDA; }
+  h->device = device;
+  cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaEventCreate(&h->ev[0]);
+  if (e == cudaSuccess) e = cudaEventCreate(&h->ev[1]);
+  if (e != cudaSuccess) { const int st = cuda_fail(e, "b200_prep_create", __FILE__, __LINE__); b200_prep_destroy(h); return st; }
+  *out = h;
+  return B200_OK;
+}
+
+void b200_prep_destroy(b200_prep* h) {
+  if (!h) return;
+  {
+    DeviceGuard dg(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    for (int i = 0; i < b200_prep::NBUF; ++i) cudaFree(h->buf[i].p);
+    for (int i = 0; i < 2; ++i)
+      if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    if (h->stream) cudaStreamDestroy(h->stream);
+  }
+  delete h;
+}
+
+int b200_prep_crop(b200_prep* h, const b200_crop_params* prm, const float* pts4xN, const float* nrm3xN, int N,
+                   float* out4xN, float* outn3xN, int32_t* kept_idx, int* n_out) {
+  if (!h || !prm || N < 0 || (N > 0 && !pts4xN) || !n_out || prm->kind < B200_CROP_NONE || prm->kind > B200_CROP_MINMAX_RADIUS) {
+    set_error("b200_prep_crop: bad arguments");
+    return B200_E_BAD_PARAM;
+  }
+  *n_out = 0;
+  if (N == 0) return B200_OK;
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  cudaStream_t s = h->stream;
+  B200_TRY(upload_cloud(h, pts4xN, nrm3xN, N));
+  B200_TRY(ensure(h, b200_prep::FLAG, ((size_t)N + 2) * sizeof(uint32_t)));
+  B200_TRY(ensure(h, b200_prep::TILE, std::max<size_t>(1, scan_tiles_for((size_t)N)) * sizeof(uint32_t)));
+  B200_TRY(ensure(h, b200_prep::OUT4, (size_t)N * sizeof(float4)));
+  B200_TRY(ensure(h, b200_prep::IDX, (size_t)N * sizeof(int)));
+  if (nrm3xN) B200_TRY(ensure(h, b200_prep::OUTN3, (size_t)N * 3 * sizeof(float)));
+  CropP c{prm->kind, prm->invert ? 1 : 0, prm->radius_min, prm->radius_max, prm->min_z, prm->max_z,
+          prm->center[0], prm->center[1], prm->center[2]};
+  B200_CUDA(cudaEventRecord(h->ev[0], s));
+  uint32_t* flag = ptr<uint32_t>(h, b200_prep::FLAG);
+  crop_flag_kernel<<<blocks_for(N), kThreads, 0, s>>>(ptr<float4>(h, b200_prep::PTS), N, c, flag);
+  B200_TRY(inclusive_scan_u32(flag, (size_t)N, ptr<uint32_t>(h, b200_prep::TILE), s));
+  crop_scatter_kernel<<<blocks_for(N), kThreads, 0, s>>>(ptr<float4>(h, b200_prep::PTS),
+                                                         nrm3xN ? ptr<float>(h, b200_prep::N3) : nullptr, N, flag,
+                                                         ptr<float4>(h, b200_prep::OUT4),
+                                                         nrm3xN ? ptr<float>(h, b200_prep::OUTN3) : nullptr,
+                                                         ptr<int>(h, b200_prep::IDX));
+  B200_CUDA(cudaGetLastError());
+  B200_CUDA(cudaEventRecord(h->ev[1], s));
+  uint32_t K = 0;
+  B200_CUDA(cudaMemcpyAsync(&K, flag + (N - 1), sizeof(K), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  if (K > 0) {
+    if (out4xN) B200_CUDA(cudaMemcpyAsync(out4xN, h->buf[b200_prep::OUT4].p, (size_t)K * sizeof(float4), cudaMemcpyDeviceToHost, s));
+    if (outn3xN && nrm3xN) B200_CUDA(cudaMemcpyAsync(outn3xN, h->buf[b200_prep::OUTN3].p, (size_t)K * 3 * sizeof(float), cudaMemcpyDeviceToHost, s));
+    if (kept_idx) B200_CUDA(cudaMemcpyAsync(kept_idx, h->buf[b200_prep::IDX].p, (size_t)K * sizeof(int), cudaMemcpyDeviceToHost, s));
+    B200_CUDA(cudaStreamSynchronize(s));
+  }
+  B200_CUDA(cudaEventElapsedTime(&h->last_ms, h->ev[0], h->ev[1]));
+  *n_out = (int)K;
+  return B200_OK;
+}
+
+int b200_prep_voxel_downsample(b200_prep* h, double voxel_size, const float* pts4xN, const float* nrm3xN, int N,
+                               double* out3xK, double* outn3xK, int32_t* first_idx, int* n_out) {
+  if (!h || N < 0 || (N > 0 && (!pts4xN || !out3xK)) || !n_out) { set_error("b200_prep_voxel_downsample: bad arguments"); return B200_E_BAD_PARAM; }
+  *n_out = 0;
+  if (!(voxel_size > 0.0)) { set_error("VoxelDownSample: voxel_size <= 0"); return B200_E_BAD_PARAM; }
+  if (N == 0) return B200_OK;
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  cudaStream_t s = h->stream;
+  B200_TRY(upload_cloud(h, pts4xN, nrm3xN, N));
+  size_t T = 1024;
+  while (T < 2 * (size_t)N) T <<= 1;
+  B200_TRY(ensure(h, b200_prep::SCR, 64));
+  B200_TRY(ensure(h, b200_prep::FLAG, ((size_t)N + 2) * sizeof(uint32_t)));
+  B200_TRY(ensure(h, b200_prep::TILE, std::max<size_t>(1, scan_tiles_for((size_t)N + 2)) * sizeof(uint32_t)));
+  B200_TRY(ensure(h, b200_prep::KEYS, T * sizeof(unsigned long long)));
+  B200_TRY(ensure(h, b200_prep::CNT, T * sizeof(uint32_t)));
+  B200_TRY(ensure(h, b200_prep::FIRST, T * sizeof(int)));
+  B200_TRY(ensure(h, b200_prep::VOX, T * sizeof(uint32_t)));
+  B200_TRY(ensure(h, b200_prep::SLOT, (size_t)N * sizeof(uint32_t)));
+  B200_TRY(ensure(h, b200_prep::OFFS, ((size_t)N + 2) * sizeof(uint32_t)));
+  B200_TRY(ensure(h, b200_prep::CUR, (size_t)N * sizeof(uint32_t)));
+  B200_TRY(ensure(h, b200_prep::MEMB, (size_t)N * sizeof(int)));
+  B200_TRY(ensure(h, b200_prep::FIRSTK, (size_t)N * sizeof(int)));
+  B200_TRY(ensure(h, b200_prep::OUT3D, (size_t)N * 3 * sizeof(double)));
+  if (nrm3xN) B200_TRY(ensure(h, b200_prep::OUTN3D, (size_t)N * 3 * sizeof(double)));
+  const float4* d_pts = ptr<float4>(h, b200_prep::PTS);
+  const float* d_n3 = nrm3xN ? ptr<float>(h, b200_prep::N3) : nullptr;
+  uint32_t* scr = ptr<uint32_t>(h, b200_prep::SCR);
+  B200_CUDA(cudaEventRecord(h->ev[0], s));
+  // ---- bounds: voxel_min_bound = min_bound - voxel_size / 2
+  uint32_t init[8] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u, 0u, 0u};
+  B200_CUDA(cudaMemcpyAsync(scr, init, sizeof(init), cudaMemcpyHostToDevice, s));
+  minmax_kernel<<<blocks_for(N), kThreads, 0, s>>>(d_pts, N, scr);
+  B200_CUDA(cudaGetLastError());
+  uint32_t mm[6];
+  B200_CUDA(cudaMemcpyAsync(mm, scr, sizeof(mm), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  double mn[3], mx[3], ext = 0.0;
+  for (int d = 0; d < 3; ++d) {
+    mn[d] = (double)ordered_uint_as_float(mm[d]); mx[d] = (double)ordered_uint_as_float(mm[3 + d]);
+    ext = std::max(ext, mx[d] - mn[d]);
+  }
+  if (!(ext == ext) || voxel_size * 2147483647.0 < ext) { set_error("VoxelDownSample: voxel_size is too small"); return B200_E_BAD_PARAM; }
+  VoxP v{mn[0] - voxel_size * 0.5, mn[1] - voxel_size * 0.5, mn[2] - voxel_size * 0.5, voxel_size, (unsigned long long)T - 1ull};
+  // ---- hash insert, voxel numbering by first member
+  B200_CUDA(cudaMemsetAsync(h->buf[b200_prep::KEYS].p, 0xff, T * sizeof(unsigned long long), s));
+  B200_CUDA(cudaMemsetAsync(h->buf[b200_prep::CNT].p, 0, T * sizeof(uint32_t), s));
+  B200_CUDA(cudaMemsetAsync(h->buf[b200_prep::FIRST].p, 0x7f, T * sizeof(int), s));   // 0x7f7f7f7f > any index
+  B200_CUDA(cudaMemsetAsync(h->buf[b200_prep::FLAG].p, 0, ((size_t)N + 2) * sizeof(uint32_t), s));
+  B200_CUDA(cudaMemsetAsync(h->buf[b200_prep::CUR].p, 0, (size_t)N * sizeof(uint32_t), s));
+  B200_CUDA(cudaMemsetAsync(scr + 8, 0, sizeof(int), s));
+  unsigned long long* keys = ptr<unsigned long long>(h, b200_prep::KEYS);
+  uint32_t* cnt = ptr<uint32_t>(h, b200_prep::CNT);
+  int* first = ptr<int>(h, b200_prep::FIRST);
+  uint32_t* flag = ptr<uint32_t>(h, b200_prep::FLAG);
+  uint32_t* offs = ptr<uint32_t>(h, b200_prep::OFFS);
+  voxel_insert_kernel<<<blocks_for(N), kThreads, 0, s>>>(d_pts, N, v, keys, cnt, first, ptr<uint32_t>(h, b200_prep::SLOT),
+                                                         reinterpret_cast<int*>(scr + 8));
+  voxel_mark_kernel<<<blocks_for(T), kThreads, 0, s>>>(keys, first, T, flag);
+  B200_TRY(inclusive_scan_u32(flag, (size_t)N, ptr<uint32_t>(h, b200_prep::TILE), s));
+  uint32_t K = 0;
+  int err = 0;
+  B200_CUDA(cudaMemcpyAsync(&K, flag + (N - 1), sizeof(K), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaMemcpyAsync(&err, scr + 8, sizeof(err), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  if (err) { set_error("VoxelDownSample: a coordinate is not finite or the cloud spans more than 2^21 voxels along an axis"); return B200_E_BAD_PARAM; }
+  B200_CUDA(cudaMemsetAsync(offs, 0, ((size_t)K + 1) * sizeof(uint32_t), s));
+  voxel_number_kernel<<<blocks_for(T), kThreads, 0, s>>>(keys, first, cnt, T, flag, ptr<uint32_t>(h, b200_prep::VOX), offs,
+                                                         ptr<int>(h, b200_prep::FIRSTK));
+  B200_TRY(inclusive_scan_u32(offs, (size_t)K + 1, ptr<uint32_t>(h, b200_prep::TILE), s));
+  voxel_members_kernel<<<blocks_for(N), kThreads, 0, s>>>(ptr<uint32_t>(h, b200_prep::SLOT), N, ptr<uint32_t>(h, b200_prep::VOX),
+                                                          offs, ptr<uint32_t>(h, b200_prep::CUR), ptr<int>(h, b200_prep::MEMB));
+  voxel_mean_kernel<<<blocks_for(K), kThreads, 0, s>>>(d_pts, d_n3, (int)K, offs, ptr<int>(h, b200_prep::MEMB),
+                                                       ptr<double>(h, b200_prep::OUT3D),
+                                                       nrm3xN ? ptr<double>(h, b200_prep::OUTN3D) : nullptr);
+  B200_CUDA(cudaGetLastError());
+  B200_CUDA(cudaEventRecord(h->ev[1], s));
+  B200_CUDA(cudaMemcpyAsync(out3xK, h->buf[b200_prep::OUT3D].p, (size_t)K * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  if (outn3xK && nrm3xN) B200_CUDA(cudaMemcpyAsync(outn3xK, h->buf[b200_prep::OUTN3D].p, (size_t)K * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  if (first_idx) B200_CUDA(cudaMemcpyAsync(first_idx, h->buf[b200_prep::FIRSTK].p, (size_t)K * sizeof(int), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  B200_CUDA(cudaEventElapsedTime(&h->last_ms, h->ev[0], h->ev[1]));
+  *n_out = (int)K;
+  return B200_OK;
+}
+
+int b200_prep_last_device_ms(const b200_prep* h, float* ms) {
+  if (!h || !ms) { set_error("b200_prep_last_device_ms: bad arguments"); return B200_E_BAD_PARAM; }
+  *ms = h->last_ms;
+  return B200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,107 @@
+"""Scan pre-processing: open3d_slam's croppers (open3d_slam/src/croppers.cpp, in the reference tree)
+and Open3D's VoxelDownSample behind o3d_slam::voxelize (helpers.cpp:108-115; Open3D v0.15.1 is not in the tree, the
+oracle restates it as recalled from upstream: parity pinned to the oracle only). Bars: kept indices BIT-EXACT and in
+input order; voxel means bit-identical doubles (same additions in the same order), voxel set identical."""
+import numpy as np
+import pytest
+
+from oracle import oracle_py as O
+
+
+def scan_like(n, seed=0):
+    rng = np.random.default_rng(seed)
+    az = rng.uniform(0, 2 * np.pi, n)
+    r = rng.gamma(2.0, 8.0, n)
+    z = rng.normal(-1.0, 1.5, n)
+    xyz = np.c_[r * np.cos(az), r * np.sin(az), z].astype(np.float32)
+    nrm = rng.normal(size=(n, 3))
+    nrm /= np.linalg.norm(nrm, axis=1, keepdims=True)
+    return O.feat4(xyz), nrm.astype(np.float32)
+
+
+# ------------------------------------------------------------------------------------------------ oracle (CPU)
+def test_oracle_croppers_against_numpy():
+    p4, _ = scan_like(20000)
+    c = np.array([1.0, -2.0, 0.5])
+    d = np.linalg.norm(p4[:, :3].astype(np.float64) - c, axis=1)
+    assert np.array_equal(O.crop(3, p4, radius_max=15.0, center=c), np.nonzero(d <= 15.0)[0])
+    assert np.array_equal(O.crop(2, p4, radius_min=3.0, center=c), np.nonzero(d >= 3.0)[0])
+    assert np.array_equal(O.crop(4, p4, radius_min=3.0, radius_max=15.0, center=c), np.nonzero((d <= 15.0) & (d >= 3.0))[0])
+    assert np.array_equal(O.crop(4, p4, radius_min=3.0, radius_max=15.0, center=c, invert=True),
+                          np.nonzero(~((d <= 15.0) & (d >= 3.0)))[0])
+    d2 = np.linalg.norm(p4[:, :2].astype(np.float64) - c[:2], axis=1)
+    z = p4[:, 2].astype(np.float64)
+    assert np.array_equal(O.crop(1, p4, radius_max=20.0, min_z=-2.0, max_z=1.0, center=c),
+                          np.nonzero((z >= -2.0) & (z <= 1.0) & (d2 <= 20.0))[0])
+    assert len(O.crop(0, p4)) == len(p4)
+
+
+def test_oracle_voxel_downsample_properties():
+    p4, nrm = scan_like(30000, seed=3)
+    vs = 0.5
+    pts, nn, first = O.voxel_downsample(vs, p4, nrm)
+    x = p4[:, :3].astype(np.float64)
+    mb = x.min(0) - vs / 2
+    key = np.floor((x - mb) / vs).astype(np.int64)
+    uniq, inv, counts = np.unique(key, axis=0, return_inverse=True, return_counts=True)
+    assert len(pts) == len(uniq)
+    assert (np.diff(first) > 0).all()                       # ordered by first member
+    # every output point is the mean of its voxel, lies inside it, and the count-weighted mean is the cloud's mean
+    kout = np.floor((pts - mb) / vs).astype(np.int64)
+    assert np.array_equal(kout, key[first])
+    cnt_out = counts[inv.ravel()[first]]
+    assert np.allclose((pts * cnt_out[:, None]).sum(0) / len(x), x.mean(0), atol=1e-9)
+    assert np.allclose((nn * cnt_out[:, None]).sum(0) / len(x), nrm.astype(np.float64).mean(0), atol=1e-9)
+    assert O.voxel_downsample(0.0, p4)[0] == -1
+    again, _, _ = O.voxel_downsample(vs * 4, O.feat4(pts.astype(np.float32)))
+    assert len(again) < len(pts)
+
+
+# ------------------------------------------------------------------------------------------------ device (GPU)
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind,kw", [(0, {}), (1, dict(radius_max=20.0, min_z=-2.0, max_z=1.0)), (2, dict(radius_min=3.0)),
+                                     (3, dict(radius_max=15.0)), (4, dict(radius_min=3.0, radius_max=15.0)),
+                                     (4, dict(radius_min=3.0, radius_max=15.0, invert=True)), (3, dict(radius_max=1e-3))])
+def test_device_crop_bit_exact(kind, kw):
+    from open3d_slam_private_b200 import capi as B
+    p4, nrm = scan_like(131072, seed=kind)
+    c = (1.0, -2.0, 0.5)
+    prep = B.Prep()
+    out, outn, idx = prep.crop(kind, p4, nrm, center=c, **kw)
+    want = O.crop(kind, p4, center=c, **kw)
+    assert np.array_equal(idx, want)
+    assert np.array_equal(out, p4[want]) and np.array_equal(outn, nrm[want])
+    prep.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,vs", [(131072, 0.1), (131072, 0.5), (200000, 2.0), (5000, 0.02), (1, 0.3)])
+def test_device_voxel_downsample_bit_exact(n, vs):
+    from open3d_slam_private_b200 import capi as B
+    p4, nrm = scan_like(n, seed=n % 97)
+    prep = B.Prep()
+    pts, nn, first = prep.voxel_downsample(vs, p4, nrm)
+    opts, onn, ofirst = O.voxel_downsample(vs, p4, nrm)
+    assert np.array_equal(first, ofirst)
+    assert np.array_equal(pts.view(np.uint64), opts.view(np.uint64))      # same doubles, bit for bit
+    assert np.array_equal(nn.view(np.uint64), onn.view(np.uint64))
+    pts2, nn2, _ = prep.voxel_downsample(vs, p4)                          # handle reuse, no normals
+    assert nn2 is None and np.array_equal(pts2, pts)
+    assert prep.last_device_ms() > 0
+    prep.close()
+
+
+@pytest.mark.gpu
+def test_device_preprocess_errors_and_empty():
+    from open3d_slam_private_b200 import capi as B
+    prep = B.Prep()
+    p4, _ = scan_like(100)
+    with pytest.raises(B.B200Error):
+        prep.voxel_downsample(0.0, p4)
+    bad = p4.copy()
+    bad[3, 0] = np.nan
+    with pytest.raises(B.B200Error):
+        prep.voxel_downsample(0.5, bad)
+    out, _, idx = prep.crop(3, p4, radius_max=0.0, center=(1e6, 0, 0))
+    assert len(out) == 0 and len(idx) == 0
+    prep.close()
