@@ -335,6 +335,9 @@ int b200_prep_crop(b200_prep* h, const b200_crop_params* prm, const float* pts4x
  * ordered by the index of the first point of each voxel (Open3D's order is unspecified); first_idx nullable. */
 int b200_prep_voxel_downsample(b200_prep* h, double voxel_size, const float* pts4xN, const float* nrm3xN, int N,
                                double* out3xK, double* outn3xK, int32_t* first_idx, int* n_out);
+/* how many voxels of the last b200_prep_voxel_downsample had to be summed in input order (their values span so many
+ * binades that a double sum could round; every other voxel's sum is exact in any order and is formed with atomics) */
+int b200_prep_last_ordered_voxels(const b200_prep* h, int* n);
 /* device time of the last call's kernels (CUDA events, uploads and read-backs excluded) */
 int b200_prep_last_device_ms(const b200_prep* h, float* ms);
 

@@ -586,6 +586,11 @@ class Prep:
         k = k.value
         return out[:k].copy(), (None if outn is None else outn[:k].copy()), first[:k].copy()
 
+    def last_ordered_voxels(self):
+        n = C.c_int()
+        _check(load().b200_prep_last_ordered_voxels(self._h, C.byref(n)))
+        return n.value
+
     def last_device_ms(self):
         ms = C.c_float()
         _check(load().b200_prep_last_device_ms(self._h, C.byref(ms)))

@@ -6,8 +6,10 @@
 // Both are HBM-bound streaming passes. Crop: predicate in double on the float coordinates, order-preserving
 // compaction (flag -> scan -> scatter). Voxel down-sample: voxel key per point, open-addressing hash table built with
 // 64-bit atomicCAS, voxels numbered by the index of their first point (deterministic; Open3D's own order is that of an
-// std::unordered_map), members gathered per voxel and sorted by index so that the double sums run in input order like
-// the reference's sequential accumulation => means bit-identical to the oracle's.
+// std::unordered_map). The reference sums a voxel's points in double while it walks the cloud; a double sum of floats is
+// exact in EVERY order when the values' binades and their count leave room in the 53-bit mantissa (sum_is_exact), so
+// those voxels — practically all — are summed with warp-folded atomics; the rest gather their members, sort them by
+// index and sum in input order. Either way the means are bit-identical to the oracle's.
 #include "common.cuh"
 #include "grid_index.cuh"
 #include <algorithm>
@@ -107,31 +109,95 @@ __device__ __forceinline__ unsigned long long mix64(unsigned long long x) {
   return x;
 }
 
+// biased exponent range of the non-zero values (denormals count as exponent 1: same quantum 2^-149)
+__device__ __forceinline__ void exp_range(float v, int& lo, int& hi) {
+  const unsigned b = __float_as_uint(v) & 0x7fffffffu;
+  if (b == 0u) return;
+  const int e = max((int)(b >> 23), 1);
+  lo = min(lo, e); hi = max(hi, e);
+}
+
+// A sum of n floats in double is EXACT in every order (all partial sums representable) when
+// (emax - emin) + 24 + ceil(log2 n) <= 53; then the order-free atomic sums below equal the reference's sequential sum
+// bit for bit. Voxels that fail the test (values spanning many binades) take the ordered path.
+__device__ __forceinline__ bool sum_is_exact(int emin, int emax, unsigned n) {
+  if (emax == 0) return true;   // all zeros
+  const int clog = n <= 1u ? 0 : 32 - __clz(n - 1u);
+  return (emax - emin) + 24 + clog <= 53;
+}
+
 // voxel index = floor((p - voxel_min_bound) / voxel_size) per axis (double, like Open3D); key = 21 bits per axis.
-// Inserts the key (linear probing), remembers the slot of every point, counts the members and keeps the smallest
-// member index of every voxel.
-__global__ void voxel_insert_kernel(const float4* __restrict__ p, int N, VoxP v, unsigned long long* __restrict__ keys,
-                                    uint32_t* __restrict__ cnt, int* __restrict__ first, uint32_t* __restrict__ slot_of,
-                                    int* __restrict__ err) {
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
-    const float4 q = __ldg(&p[i]);
-    const double fx = floor(((double)q.x - v.mbx) / v.vs), fy = floor(((double)q.y - v.mby) / v.vs),
-                 fz = floor(((double)q.z - v.mbz) / v.vs);
-    if (!(fx >= 0.0 && fx < 2097152.0 && fy >= 0.0 && fy < 2097152.0 && fz >= 0.0 && fz < 2097152.0)) {
-      *err = 1;   // NaN coordinate or more than 2^21 voxels along an axis
-      slot_of[i] = 0xffffffffu;
-      continue;
+// Inserts the key (linear probing) and remembers the slot of every point. The lanes of a warp that fell into the same
+// voxel (consecutive scan points usually do) are folded first, in lane = index order, and ONE lane per voxel and warp
+// issues the atomics: member count, smallest member index, sums of the points (and normals) in double, exponent range.
+__global__ void voxel_insert_kernel(const float4* __restrict__ p, const float* __restrict__ n3, int N, VoxP v,
+                                    unsigned long long* __restrict__ keys, uint32_t* __restrict__ cnt,
+                                    int* __restrict__ first, uint32_t* __restrict__ slot_of, double* __restrict__ sums,
+                                    int* __restrict__ exps, int* __restrict__ err) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  for (int base = (blockIdx.x * blockDim.x + threadIdx.x) - lane; base < N; base += gridDim.x * blockDim.x) {
+    const int i = base + lane;
+    uint32_t s = 0xffffffffu;
+    float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+    float nx = 0.f, ny = 0.f, nz = 0.f;
+    if (i < N) {
+      q = __ldg(&p[i]);
+      if (n3) { nx = n3[3 * (size_t)i]; ny = n3[3 * (size_t)i + 1]; nz = n3[3 * (size_t)i + 2]; }
+      const double fx = floor(((double)q.x - v.mbx) / v.vs), fy = floor(((double)q.y - v.mby) / v.vs),
+                   fz = floor(((double)q.z - v.mbz) / v.vs);
+      if (!(fx >= 0.0 && fx < 2097152.0 && fy >= 0.0 && fy < 2097152.0 && fz >= 0.0 && fz < 2097152.0)) {
+        *err = 1;   // NaN coordinate or more than 2^21 voxels along an axis
+      } else {
+        const unsigned long long key = (unsigned long long)fx | ((unsigned long long)fy << 21) | ((unsigned long long)fz << 42);
+        unsigned long long t = mix64(key) & v.mask;
+        while (true) {
+          const unsigned long long old = atomicCAS(&keys[t], kEmpty, key);
+          if (old == kEmpty || old == key) break;
+          t = (t + 1ull) & v.mask;
+        }
+        s = (uint32_t)t;
+      }
+      slot_of[i] = s;
     }
-    const unsigned long long key = (unsigned long long)fx | ((unsigned long long)fy << 21) | ((unsigned long long)fz << 42);
-    unsigned long long s = mix64(key) & v.mask;
-    while (true) {
-      const unsigned long long old = atomicCAS(&keys[s], kEmpty, key);
-      if (old == kEmpty || old == key) break;
-      s = (s + 1ull) & v.mask;
+    // fold the lanes of the same voxel, ascending lane order
+    double sx = 0.0, sy = 0.0, sz = 0.0, tx = 0.0, ty = 0.0, tz = 0.0;
+    int plo = 255, phi = 0, nlo = 255, nhi = 0, leader = -1;
+    unsigned members = 0;
+    for (int l = 0; l < 32; ++l) {
+      const uint32_t sl = __shfl_sync(FULL, s, l);
+      const float ax = __shfl_sync(FULL, q.x, l), ay = __shfl_sync(FULL, q.y, l), az = __shfl_sync(FULL, q.z, l);
+      float bx = 0.f, by = 0.f, bz = 0.f;
+      if (n3) { bx = __shfl_sync(FULL, nx, l); by = __shfl_sync(FULL, ny, l); bz = __shfl_sync(FULL, nz, l); }
+      if (sl == s && s != 0xffffffffu) {
+        if (leader < 0) leader = l;
+        ++members;
+        sx += (double)ax; sy += (double)ay; sz += (double)az;
+        exp_range(ax, plo, phi); exp_range(ay, plo, phi); exp_range(az, plo, phi);
+        if (n3) {
+          tx += (double)bx; ty += (double)by; tz += (double)bz;
+          exp_range(bx, nlo, nhi); exp_range(by, nlo, nhi); exp_range(bz, nlo, nhi);
+        }
+      }
     }
-    slot_of[i] = (uint32_t)s;
-    atomicAdd(&cnt[s], 1u);
-    atomicMin(&first[s], i);
+    if (leader == lane) {
+      atomicAdd(&cnt[s], members);
+      atomicMin(&first[s], i);
+      double* a = sums + 6 * (size_t)s;
+      atomicAdd(a, sx); atomicAdd(a + 1, sy); atomicAdd(a + 2, sz);
+      int* e = exps + 4 * (size_t)s;
+      if (phi) { atomicMin(e, plo); atomicMax(e + 1, phi); }
+      if (n3) {
+        atomicAdd(a + 3, tx); atomicAdd(a + 4, ty); atomicAdd(a + 5, tz);
+        if (nhi) { atomicMin(e + 2, nlo); atomicMax(e + 3, nhi); }
+      }
+    }
+  }
+}
+
+__global__ void exps_init_kernel(int* __restrict__ exps, size_t T) {
+  for (size_t s = blockIdx.x * (size_t)blockDim.x + threadIdx.x; s < T; s += (size_t)gridDim.x * blockDim.x) {
+    exps[4 * s] = 255; exps[4 * s + 1] = 0; exps[4 * s + 2] = 255; exps[4 * s + 3] = 0;
   }
 }
 
@@ -142,21 +208,27 @@ __global__ void voxel_mark_kernel(const unsigned long long* __restrict__ keys, c
     if (keys[s] != kEmpty) flag[first[s]] = 1u;
 }
 
-// voxel number = (inclusive scan of the flags)[first] - 1; counts moved into voxel order (cntK[v + 1], for the scan)
+// voxel number = (inclusive scan of the flags)[first] - 1. Voxels whose sums are not provably exact (sum_is_exact) keep
+// their member count in offs[v + 1] (for the scan that lays out the member lists of the ordered path); the others get 0.
 __global__ void voxel_number_kernel(const unsigned long long* __restrict__ keys, const int* __restrict__ first,
-                                    const uint32_t* __restrict__ cnt, size_t T, const uint32_t* __restrict__ scan,
-                                    uint32_t* __restrict__ vox_of_slot, uint32_t* __restrict__ offs,
-                                    int* __restrict__ firstK) {
+                                    const uint32_t* __restrict__ cnt, const int* __restrict__ exps, int with_normals,
+                                    size_t T, const uint32_t* __restrict__ scan, uint32_t* __restrict__ vox_of_slot,
+                                    uint32_t* __restrict__ slot_of_vox, uint32_t* __restrict__ offs,
+                                    int* __restrict__ firstK, int* __restrict__ n_ordered) {
   for (size_t s = blockIdx.x * (size_t)blockDim.x + threadIdx.x; s < T; s += (size_t)gridDim.x * blockDim.x)
     if (keys[s] != kEmpty) {
       const uint32_t v = scan[first[s]] - 1u;
       vox_of_slot[s] = v;
-      offs[v + 1] = cnt[s];
+      slot_of_vox[v] = (uint32_t)s;
       firstK[v] = first[s];
+      const int* e = exps + 4 * s;
+      const bool exact = sum_is_exact(e[0], e[1], cnt[s]) && (!with_normals || sum_is_exact(e[2], e[3], cnt[s]));
+      offs[v + 1] = exact ? 0u : cnt[s];
+      if (!exact) atomicAdd(n_ordered, 1);
     }
 }
 
-// offs = inclusive scan => offs[v] = start of voxel v, offs[v + 1] = end
+// offs = inclusive scan => offs[v] = start of voxel v's member list, offs[v + 1] = its end (empty for exact voxels)
 __global__ void voxel_members_kernel(const uint32_t* __restrict__ slot_of, int N, const uint32_t* __restrict__ vox_of_slot,
                                      const uint32_t* __restrict__ offs, uint32_t* __restrict__ cursor,
                                      int* __restrict__ members) {
@@ -164,31 +236,41 @@ __global__ void voxel_members_kernel(const uint32_t* __restrict__ slot_of, int N
     const uint32_t s = slot_of[i];
     if (s == 0xffffffffu) continue;
     const uint32_t v = vox_of_slot[s];
+    if (offs[v + 1] == offs[v]) continue;
     members[offs[v] + atomicAdd(&cursor[v], 1u)] = i;
   }
 }
 
-// one thread per voxel: members into ascending index order (insertion sort; voxels hold a handful of points), then the
-// sums in double in that order — the reference accumulates while it walks the cloud — and the average
+// one thread per voxel. Exact voxels: average of the order-free sums. Ordered path: members into ascending index order
+// (insertion sort), then the sums in double in that order — the reference accumulates while it walks the cloud.
 __global__ void voxel_mean_kernel(const float4* __restrict__ p, const float* __restrict__ n3, int K,
                                   const uint32_t* __restrict__ offs, int* __restrict__ members,
-                                  double* __restrict__ out3, double* __restrict__ outn3) {
+                                  const uint32_t* __restrict__ slot_of_vox, const uint32_t* __restrict__ cnt,
+                                  const double* __restrict__ sums, double* __restrict__ out3, double* __restrict__ outn3) {
   for (int v = blockIdx.x * blockDim.x + threadIdx.x; v < K; v += gridDim.x * blockDim.x) {
     const uint32_t a = offs[v], b = offs[v + 1];
-    for (uint32_t i = a + 1; i < b; ++i) {
-      const int m = members[i];
-      uint32_t j = i;
-      while (j > a && members[j - 1] > m) { members[j] = members[j - 1]; --j; }
-      members[j] = m;
+    const uint32_t s = slot_of_vox[v];
+    double sx, sy, sz, nx = 0.0, ny = 0.0, nz = 0.0;
+    if (a == b) {
+      const double* q = sums + 6 * (size_t)s;
+      sx = q[0]; sy = q[1]; sz = q[2];
+      if (n3) { nx = q[3]; ny = q[4]; nz = q[5]; }
+    } else {
+      for (uint32_t i = a + 1; i < b; ++i) {
+        const int m = members[i];
+        uint32_t j = i;
+        while (j > a && members[j - 1] > m) { members[j] = members[j - 1]; --j; }
+        members[j] = m;
+      }
+      sx = sy = sz = 0.0;
+      for (uint32_t i = a; i < b; ++i) {
+        const int m = members[i];
+        const float4 q = __ldg(&p[m]);
+        sx += (double)q.x; sy += (double)q.y; sz += (double)q.z;
+        if (n3) { nx += (double)n3[3 * (size_t)m]; ny += (double)n3[3 * (size_t)m + 1]; nz += (double)n3[3 * (size_t)m + 2]; }
+      }
     }
-    double sx = 0.0, sy = 0.0, sz = 0.0, nx = 0.0, ny = 0.0, nz = 0.0;
-    for (uint32_t i = a; i < b; ++i) {
-      const int m = members[i];
-      const float4 q = __ldg(&p[m]);
-      sx += (double)q.x; sy += (double)q.y; sz += (double)q.z;
-      if (n3) { nx += (double)n3[3 * (size_t)m]; ny += (double)n3[3 * (size_t)m + 1]; nz += (double)n3[3 * (size_t)m + 2]; }
-    }
-    const double c = (double)(b - a);
+    const double c = (double)cnt[s];
     out3[3 * (size_t)v] = sx / c; out3[3 * (size_t)v + 1] = sy / c; out3[3 * (size_t)v + 2] = sz / c;
     if (n3) { outn3[3 * (size_t)v] = nx / c; outn3[3 * (size_t)v + 1] = ny / c; outn3[3 * (size_t)v + 2] = nz / c; }
   }
@@ -206,7 +288,8 @@ struct b200_prep {
     void* p = nullptr;
     size_t cap = 0;
   };
-  enum { PTS, N3, FLAG, TILE, OUT4, OUTN3, IDX, KEYS, CNT, FIRST, SLOT, VOX, OFFS, CUR, MEMB, OUT3D, OUTN3D, FIRSTK, SCR, NBUF };
+  enum { PTS, N3, FLAG, TILE, OUT4, OUTN3, IDX, KEYS, CNT, FIRST, SLOT, VOX, OFFS, CUR, MEMB, OUT3D, OUTN3D, FIRSTK, SCR, SUMS, EXPS, SLOTV, NBUF };
+  int last_ordered = 0;   // voxels of the last down-sample that took the ordered path
   Buf buf[NBUF];
   float last_ms = 0.f;
   cudaEvent_t ev[2] = {nullptr, nullptr};
@@ -332,6 +415,9 @@ int b200_prep_voxel_downsample(b200_prep* h, double voxel_size, const float* pts
   B200_TRY(ensure(h, b200_prep::CNT, T * sizeof(uint32_t)));
   B200_TRY(ensure(h, b200_prep::FIRST, T * sizeof(int)));
   B200_TRY(ensure(h, b200_prep::VOX, T * sizeof(uint32_t)));
+  B200_TRY(ensure(h, b200_prep::SUMS, T * 6 * sizeof(double)));
+  B200_TRY(ensure(h, b200_prep::EXPS, T * 4 * sizeof(int)));
+  B200_TRY(ensure(h, b200_prep::SLOTV, (size_t)N * sizeof(uint32_t)));
   B200_TRY(ensure(h, b200_prep::SLOT, (size_t)N * sizeof(uint32_t)));
   B200_TRY(ensure(h, b200_prep::OFFS, ((size_t)N + 2) * sizeof(uint32_t)));
   B200_TRY(ensure(h, b200_prep::CUR, (size_t)N * sizeof(uint32_t)));
@@ -364,13 +450,16 @@ int b200_prep_voxel_downsample(b200_prep* h, double voxel_size, const float* pts
   B200_CUDA(cudaMemsetAsync(h->buf[b200_prep::FIRST].p, 0x7f, T * sizeof(int), s));   // 0x7f7f7f7f > any index
   B200_CUDA(cudaMemsetAsync(h->buf[b200_prep::FLAG].p, 0, ((size_t)N + 2) * sizeof(uint32_t), s));
   B200_CUDA(cudaMemsetAsync(h->buf[b200_prep::CUR].p, 0, (size_t)N * sizeof(uint32_t), s));
-  B200_CUDA(cudaMemsetAsync(scr + 8, 0, sizeof(int), s));
+  B200_CUDA(cudaMemsetAsync(scr + 8, 0, 2 * sizeof(int), s));
+  B200_CUDA(cudaMemsetAsync(h->buf[b200_prep::SUMS].p, 0, T * 6 * sizeof(double), s));
+  exps_init_kernel<<<blocks_for(T), kThreads, 0, s>>>(ptr<int>(h, b200_prep::EXPS), T);
   unsigned long long* keys = ptr<unsigned long long>(h, b200_prep::KEYS);
   uint32_t* cnt = ptr<uint32_t>(h, b200_prep::CNT);
   int* first = ptr<int>(h, b200_prep::FIRST);
   uint32_t* flag = ptr<uint32_t>(h, b200_prep::FLAG);
   uint32_t* offs = ptr<uint32_t>(h, b200_prep::OFFS);
-  voxel_insert_kernel<<<blocks_for(N), kThreads, 0, s>>>(d_pts, N, v, keys, cnt, first, ptr<uint32_t>(h, b200_prep::SLOT),
+  voxel_insert_kernel<<<blocks_for(N), kThreads, 0, s>>>(d_pts, d_n3, N, v, keys, cnt, first, ptr<uint32_t>(h, b200_prep::SLOT),
+                                                         ptr<double>(h, b200_prep::SUMS), ptr<int>(h, b200_prep::EXPS),
                                                          reinterpret_cast<int*>(scr + 8));
   voxel_mark_kernel<<<blocks_for(T), kThreads, 0, s>>>(keys, first, T, flag);
   B200_TRY(inclusive_scan_u32(flag, (size_t)N, ptr<uint32_t>(h, b200_prep::TILE), s));
@@ -381,12 +470,14 @@ int b200_prep_voxel_downsample(b200_prep* h, double voxel_size, const float* pts
   B200_CUDA(cudaStreamSynchronize(s));
   if (err) { set_error("VoxelDownSample: a coordinate is not finite or the cloud spans more than 2^21 voxels along an axis"); return B200_E_BAD_PARAM; }
   B200_CUDA(cudaMemsetAsync(offs, 0, ((size_t)K + 1) * sizeof(uint32_t), s));
-  voxel_number_kernel<<<blocks_for(T), kThreads, 0, s>>>(keys, first, cnt, T, flag, ptr<uint32_t>(h, b200_prep::VOX), offs,
-                                                         ptr<int>(h, b200_prep::FIRSTK));
+  voxel_number_kernel<<<blocks_for(T), kThreads, 0, s>>>(keys, first, cnt, ptr<int>(h, b200_prep::EXPS), nrm3xN ? 1 : 0, T, flag,
+                                                         ptr<uint32_t>(h, b200_prep::VOX), ptr<uint32_t>(h, b200_prep::SLOTV),
+                                                         offs, ptr<int>(h, b200_prep::FIRSTK), reinterpret_cast<int*>(scr + 9));
   B200_TRY(inclusive_scan_u32(offs, (size_t)K + 1, ptr<uint32_t>(h, b200_prep::TILE), s));
   voxel_members_kernel<<<blocks_for(N), kThreads, 0, s>>>(ptr<uint32_t>(h, b200_prep::SLOT), N, ptr<uint32_t>(h, b200_prep::VOX),
                                                           offs, ptr<uint32_t>(h, b200_prep::CUR), ptr<int>(h, b200_prep::MEMB));
   voxel_mean_kernel<<<blocks_for(K), kThreads, 0, s>>>(d_pts, d_n3, (int)K, offs, ptr<int>(h, b200_prep::MEMB),
+                                                       ptr<uint32_t>(h, b200_prep::SLOTV), cnt, ptr<double>(h, b200_prep::SUMS),
                                                        ptr<double>(h, b200_prep::OUT3D),
                                                        nrm3xN ? ptr<double>(h, b200_prep::OUTN3D) : nullptr);
   B200_CUDA(cudaGetLastError());
@@ -394,9 +485,16 @@ int b200_prep_voxel_downsample(b200_prep* h, double voxel_size, const float* pts
   B200_CUDA(cudaMemcpyAsync(out3xK, h->buf[b200_prep::OUT3D].p, (size_t)K * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
   if (outn3xK && nrm3xN) B200_CUDA(cudaMemcpyAsync(outn3xK, h->buf[b200_prep::OUTN3D].p, (size_t)K * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
   if (first_idx) B200_CUDA(cudaMemcpyAsync(first_idx, h->buf[b200_prep::FIRSTK].p, (size_t)K * sizeof(int), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaMemcpyAsync(&h->last_ordered, scr + 9, sizeof(int), cudaMemcpyDeviceToHost, s));
   B200_CUDA(cudaStreamSynchronize(s));
   B200_CUDA(cudaEventElapsedTime(&h->last_ms, h->ev[0], h->ev[1]));
   *n_out = (int)K;
+  return B200_OK;
+}
+
+int b200_prep_last_ordered_voxels(const b200_prep* h, int* n) {
+  if (!h || !n) { set_error("b200_prep_last_ordered_voxels: bad arguments"); return B200_E_BAD_PARAM; }
+  *n = h->last_ordered;
   return B200_OK;
 }
 

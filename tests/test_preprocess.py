@@ -92,6 +92,33 @@ def test_device_voxel_downsample_bit_exact(n, vs):
 
 
 @pytest.mark.gpu
+def test_device_voxel_downsample_ordered_path_and_heavy_voxels():
+    """(1) A voxel whose values span more binades than a double sum can hold exactly must be summed in input order:
+    the result is still the oracle's bit for bit and the handle reports that the ordered path ran. (2) A voxel holding
+    tens of thousands of points (coarse voxel around the sensor) stays on the exact order-free path and is fast."""
+    from open3d_slam_private_b200 import capi as B
+    rng = np.random.default_rng(5)
+    p4, nrm = scan_like(40000, seed=11)
+    tiny = rng.integers(0, 40000, 4000)
+    p4[tiny, 0] = (rng.uniform(1, 2, 4000) * 10.0 ** rng.integers(-30, -12, 4000)).astype(np.float32)   # 1e-30 .. 1e-12 m
+    nrm[tiny, 1] = (rng.uniform(1, 2, 4000) * 10.0 ** rng.integers(-35, -20, 4000)).astype(np.float32)
+    prep = B.Prep()
+    pts, nn, first = prep.voxel_downsample(1.0, p4, nrm)
+    opts, onn, ofirst = O.voxel_downsample(1.0, p4, nrm)
+    assert prep.last_ordered_voxels() > 0
+    assert np.array_equal(first, ofirst)
+    assert np.array_equal(pts.view(np.uint64), opts.view(np.uint64))
+    assert np.array_equal(nn.view(np.uint64), onn.view(np.uint64))
+    dense, _ = scan_like(131072, seed=2)
+    dense[:, :3] *= 0.02                                   # everything within a few voxels of the origin
+    pts, _, first = prep.voxel_downsample(0.5, dense)
+    opts, _, ofirst = O.voxel_downsample(0.5, dense)
+    assert prep.last_ordered_voxels() == 0 and prep.last_device_ms() < 5.0
+    assert np.array_equal(first, ofirst) and np.array_equal(pts.view(np.uint64), opts.view(np.uint64))
+    prep.close()
+
+
+@pytest.mark.gpu
 def test_device_preprocess_errors_and_empty():
     from open3d_slam_private_b200 import capi as B
     prep = B.Prep()
