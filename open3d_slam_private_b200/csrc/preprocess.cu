@@ -8,8 +8,8 @@
 // 64-bit atomicCAS, voxels numbered by the index of their first point (deterministic; Open3D's own order is that of an
 // std::unordered_map). The reference sums a voxel's points in double while it walks the cloud; a double sum of floats is
 // exact in EVERY order when the values' binades and their count leave room in the 53-bit mantissa (sum_is_exact), so
-// those voxels — practically all — are summed with warp-folded atomics; the rest gather their members, sort them by
-// index and sum in input order. Either way the means are bit-identical to the oracle's.
+// those voxels — practically all — are summed with warp-folded atomics; for the rest one CTA per voxel collects the
+// members in index order and one thread sums them in input order. Either way the means are bit-identical to the oracle's.
 #include "common.cuh"
 #include "grid_index.cuh"
 #include <algorithm>
@@ -27,6 +27,7 @@ namespace {
 
 constexpr int kThreads = 256;
 constexpr unsigned long long kEmpty = 0xffffffffffffffffull;
+constexpr uint32_t kSmallVoxel = 64;   // ordered voxels up to this size are sorted and summed by one thread
 
 inline int blocks_for(size_t n) { return (int)std::max<size_t>(1, std::min<size_t>((n + kThreads - 1) / kThreads, 148 * 16)); }
 
@@ -214,7 +215,8 @@ __global__ void voxel_number_kernel(const unsigned long long* __restrict__ keys,
                                     const uint32_t* __restrict__ cnt, const int* __restrict__ exps, int with_normals,
                                     size_t T, const uint32_t* __restrict__ scan, uint32_t* __restrict__ vox_of_slot,
                                     uint32_t* __restrict__ slot_of_vox, uint32_t* __restrict__ offs,
-                                    int* __restrict__ firstK, int* __restrict__ n_ordered) {
+                                    int* __restrict__ firstK, int* __restrict__ n_ordered,
+                                    uint32_t* __restrict__ ordered_list) {
   for (size_t s = blockIdx.x * (size_t)blockDim.x + threadIdx.x; s < T; s += (size_t)gridDim.x * blockDim.x)
     if (keys[s] != kEmpty) {
       const uint32_t v = scan[first[s]] - 1u;
@@ -224,25 +226,78 @@ __global__ void voxel_number_kernel(const unsigned long long* __restrict__ keys,
       const int* e = exps + 4 * s;
       const bool exact = sum_is_exact(e[0], e[1], cnt[s]) && (!with_normals || sum_is_exact(e[2], e[3], cnt[s]));
       offs[v + 1] = exact ? 0u : cnt[s];
-      if (!exact) atomicAdd(n_ordered, 1);
+      if (!exact) {
+        atomicAdd(n_ordered, 1);
+        if (cnt[s] > kSmallVoxel) ordered_list[atomicAdd(n_ordered + 1, 1)] = v;   // large: one CTA each
+      }
     }
 }
 
-// offs = inclusive scan => offs[v] = start of voxel v's member list, offs[v + 1] = its end (empty for exact voxels)
+// member lists of the SMALL ordered voxels (any order; voxel_mean_kernel sorts them)
 __global__ void voxel_members_kernel(const uint32_t* __restrict__ slot_of, int N, const uint32_t* __restrict__ vox_of_slot,
-                                     const uint32_t* __restrict__ offs, uint32_t* __restrict__ cursor,
-                                     int* __restrict__ members) {
+                                     const uint32_t* __restrict__ cnt, const uint32_t* __restrict__ offs,
+                                     uint32_t* __restrict__ cursor, int* __restrict__ members) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
     const uint32_t s = slot_of[i];
     if (s == 0xffffffffu) continue;
     const uint32_t v = vox_of_slot[s];
-    if (offs[v + 1] == offs[v]) continue;
+    if (offs[v + 1] == offs[v] || cnt[s] > kSmallVoxel) continue;
     members[offs[v] + atomicAdd(&cursor[v], 1u)] = i;
   }
 }
 
-// one thread per voxel. Exact voxels: average of the order-free sums. Ordered path: members into ascending index order
-// (insertion sort), then the sums in double in that order — the reference accumulates while it walks the cloud.
+// Ordered path for LARGE voxels, one CTA per voxel that failed sum_is_exact (offs = inclusive scan of their member counts => offs[v] is
+// the start of voxel v's member list). The warps walk disjoint, ascending chunks of the cloud, pick the points of this
+// voxel (count, then write: ballot prefix keeps the index order inside a warp, the chunk order keeps it across warps),
+// and thread 0 then runs the reference's recurrence s <- fl(s + x_i) over the list. The search is the expensive part and
+// is parallel; the additions are few and sequential by nature.
+__global__ void __launch_bounds__(kThreads) voxel_ordered_kernel(const float4* __restrict__ p, const float* __restrict__ n3,
+                                                                 int N, const uint32_t* __restrict__ ordered_list,
+                                                                 const uint32_t* __restrict__ slot_of_vox,
+                                                                 const uint32_t* __restrict__ slot_of,
+                                                                 const uint32_t* __restrict__ offs, int* __restrict__ members,
+                                                                 double* __restrict__ out3, double* __restrict__ outn3) {
+  constexpr unsigned FULL = 0xffffffffu;
+  constexpr int kW = kThreads / 32;
+  __shared__ uint32_t s_cnt[kW];
+  const uint32_t v = ordered_list[blockIdx.x];
+  const uint32_t s = slot_of_vox[v];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int chunk = (((N + kW - 1) / kW) + 31) & ~31;
+  const int lo = w * chunk, hi = min(N, lo + chunk);
+  uint32_t c = 0;
+  for (int base = lo; base < hi; base += 32) {
+    const int i = base + lane;
+    c += __popc(__ballot_sync(FULL, i < hi && slot_of[i] == s));
+  }
+  if (lane == 0) s_cnt[w] = c;
+  __syncthreads();
+  uint32_t o = offs[v];
+  for (int k = 0; k < w; ++k) o += s_cnt[k];
+  for (int base = lo; base < hi; base += 32) {
+    const int i = base + lane;
+    const bool m = i < hi && slot_of[i] == s;
+    const unsigned bal = __ballot_sync(FULL, m);
+    if (m) members[o + __popc(bal & ((1u << lane) - 1u))] = i;
+    o += __popc(bal);
+  }
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  const uint32_t a = offs[v], b = offs[v + 1];
+  double sx = 0.0, sy = 0.0, sz = 0.0, nx = 0.0, ny = 0.0, nz = 0.0;
+  for (uint32_t i = a; i < b; ++i) {
+    const int m = members[i];
+    const float4 q = __ldg(&p[m]);
+    sx += (double)q.x; sy += (double)q.y; sz += (double)q.z;
+    if (n3) { nx += (double)n3[3 * (size_t)m]; ny += (double)n3[3 * (size_t)m + 1]; nz += (double)n3[3 * (size_t)m + 2]; }
+  }
+  const double cn = (double)(b - a);
+  out3[3 * (size_t)v] = sx / cn; out3[3 * (size_t)v + 1] = sy / cn; out3[3 * (size_t)v + 2] = sz / cn;
+  if (n3) { outn3[3 * (size_t)v] = nx / cn; outn3[3 * (size_t)v + 1] = ny / cn; outn3[3 * (size_t)v + 2] = nz / cn; }
+}
+
+// one thread per voxel. Passed sum_is_exact: average of the order-free sums. Small ordered voxel: members into ascending
+// index order (insertion sort), sums in double in that order. Large ordered voxels: voxel_ordered_kernel.
 __global__ void voxel_mean_kernel(const float4* __restrict__ p, const float* __restrict__ n3, int K,
                                   const uint32_t* __restrict__ offs, int* __restrict__ members,
                                   const uint32_t* __restrict__ slot_of_vox, const uint32_t* __restrict__ cnt,
@@ -250,6 +305,7 @@ __global__ void voxel_mean_kernel(const float4* __restrict__ p, const float* __r
   for (int v = blockIdx.x * blockDim.x + threadIdx.x; v < K; v += gridDim.x * blockDim.x) {
     const uint32_t a = offs[v], b = offs[v + 1];
     const uint32_t s = slot_of_vox[v];
+    if (a != b && cnt[s] > kSmallVoxel) continue;
     double sx, sy, sz, nx = 0.0, ny = 0.0, nz = 0.0;
     if (a == b) {
       const double* q = sums + 6 * (size_t)s;
@@ -288,7 +344,7 @@ struct b200_prep {
     void* p = nullptr;
     size_t cap = 0;
   };
-  enum { PTS, N3, FLAG, TILE, OUT4, OUTN3, IDX, KEYS, CNT, FIRST, SLOT, VOX, OFFS, CUR, MEMB, OUT3D, OUTN3D, FIRSTK, SCR, SUMS, EXPS, SLOTV, NBUF };
+  enum { PTS, N3, FLAG, TILE, OUT4, OUTN3, IDX, KEYS, CNT, FIRST, SLOT, VOX, OFFS, CUR, MEMB, OUT3D, OUTN3D, FIRSTK, SCR, SUMS, EXPS, SLOTV, ORDL, NBUF };
   int last_ordered = 0;   // voxels of the last down-sample that took the ordered path
   Buf buf[NBUF];
   float last_ms = 0.f;
@@ -418,6 +474,7 @@ int b200_prep_voxel_downsample(b200_prep* h, double voxel_size, const float* pts
   B200_TRY(ensure(h, b200_prep::SUMS, T * 6 * sizeof(double)));
   B200_TRY(ensure(h, b200_prep::EXPS, T * 4 * sizeof(int)));
   B200_TRY(ensure(h, b200_prep::SLOTV, (size_t)N * sizeof(uint32_t)));
+  B200_TRY(ensure(h, b200_prep::ORDL, (size_t)N * sizeof(uint32_t)));
   B200_TRY(ensure(h, b200_prep::SLOT, (size_t)N * sizeof(uint32_t)));
   B200_TRY(ensure(h, b200_prep::OFFS, ((size_t)N + 2) * sizeof(uint32_t)));
   B200_TRY(ensure(h, b200_prep::CUR, (size_t)N * sizeof(uint32_t)));
@@ -449,8 +506,7 @@ int b200_prep_voxel_downsample(b200_prep* h, double voxel_size, const float* pts
   B200_CUDA(cudaMemsetAsync(h->buf[b200_prep::CNT].p, 0, T * sizeof(uint32_t), s));
   B200_CUDA(cudaMemsetAsync(h->buf[b200_prep::FIRST].p, 0x7f, T * sizeof(int), s));   // 0x7f7f7f7f > any index
   B200_CUDA(cudaMemsetAsync(h->buf[b200_prep::FLAG].p, 0, ((size_t)N + 2) * sizeof(uint32_t), s));
-  B200_CUDA(cudaMemsetAsync(h->buf[b200_prep::CUR].p, 0, (size_t)N * sizeof(uint32_t), s));
-  B200_CUDA(cudaMemsetAsync(scr + 8, 0, 2 * sizeof(int), s));
+  B200_CUDA(cudaMemsetAsync(scr + 8, 0, 3 * sizeof(int), s));
   B200_CUDA(cudaMemsetAsync(h->buf[b200_prep::SUMS].p, 0, T * 6 * sizeof(double), s));
   exps_init_kernel<<<blocks_for(T), kThreads, 0, s>>>(ptr<int>(h, b200_prep::EXPS), T);
   unsigned long long* keys = ptr<unsigned long long>(h, b200_prep::KEYS);
@@ -472,20 +528,32 @@ int b200_prep_voxel_downsample(b200_prep* h, double voxel_size, const float* pts
   B200_CUDA(cudaMemsetAsync(offs, 0, ((size_t)K + 1) * sizeof(uint32_t), s));
   voxel_number_kernel<<<blocks_for(T), kThreads, 0, s>>>(keys, first, cnt, ptr<int>(h, b200_prep::EXPS), nrm3xN ? 1 : 0, T, flag,
                                                          ptr<uint32_t>(h, b200_prep::VOX), ptr<uint32_t>(h, b200_prep::SLOTV),
-                                                         offs, ptr<int>(h, b200_prep::FIRSTK), reinterpret_cast<int*>(scr + 9));
+                                                         offs, ptr<int>(h, b200_prep::FIRSTK), reinterpret_cast<int*>(scr + 9),
+                                                         ptr<uint32_t>(h, b200_prep::ORDL));
   B200_TRY(inclusive_scan_u32(offs, (size_t)K + 1, ptr<uint32_t>(h, b200_prep::TILE), s));
-  voxel_members_kernel<<<blocks_for(N), kThreads, 0, s>>>(ptr<uint32_t>(h, b200_prep::SLOT), N, ptr<uint32_t>(h, b200_prep::VOX),
-                                                          offs, ptr<uint32_t>(h, b200_prep::CUR), ptr<int>(h, b200_prep::MEMB));
+  int n_ord[2] = {0, 0};   // voxels on the ordered path, and how many of them are large
+  B200_CUDA(cudaMemcpyAsync(n_ord, scr + 9, sizeof(n_ord), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  if (n_ord[0] > n_ord[1]) {
+    B200_CUDA(cudaMemsetAsync(h->buf[b200_prep::CUR].p, 0, (size_t)K * sizeof(uint32_t), s));
+    voxel_members_kernel<<<blocks_for(N), kThreads, 0, s>>>(ptr<uint32_t>(h, b200_prep::SLOT), N, ptr<uint32_t>(h, b200_prep::VOX),
+                                                            cnt, offs, ptr<uint32_t>(h, b200_prep::CUR), ptr<int>(h, b200_prep::MEMB));
+  }
   voxel_mean_kernel<<<blocks_for(K), kThreads, 0, s>>>(d_pts, d_n3, (int)K, offs, ptr<int>(h, b200_prep::MEMB),
                                                        ptr<uint32_t>(h, b200_prep::SLOTV), cnt, ptr<double>(h, b200_prep::SUMS),
                                                        ptr<double>(h, b200_prep::OUT3D),
                                                        nrm3xN ? ptr<double>(h, b200_prep::OUTN3D) : nullptr);
+  if (n_ord[1] > 0)
+    voxel_ordered_kernel<<<n_ord[1], kThreads, 0, s>>>(d_pts, d_n3, N, ptr<uint32_t>(h, b200_prep::ORDL),
+                                                       ptr<uint32_t>(h, b200_prep::SLOTV), ptr<uint32_t>(h, b200_prep::SLOT), offs,
+                                                       ptr<int>(h, b200_prep::MEMB), ptr<double>(h, b200_prep::OUT3D),
+                                                       nrm3xN ? ptr<double>(h, b200_prep::OUTN3D) : nullptr);
+  h->last_ordered = n_ord[0];
   B200_CUDA(cudaGetLastError());
   B200_CUDA(cudaEventRecord(h->ev[1], s));
   B200_CUDA(cudaMemcpyAsync(out3xK, h->buf[b200_prep::OUT3D].p, (size_t)K * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
   if (outn3xK && nrm3xN) B200_CUDA(cudaMemcpyAsync(outn3xK, h->buf[b200_prep::OUTN3D].p, (size_t)K * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
   if (first_idx) B200_CUDA(cudaMemcpyAsync(first_idx, h->buf[b200_prep::FIRSTK].p, (size_t)K * sizeof(int), cudaMemcpyDeviceToHost, s));
-  B200_CUDA(cudaMemcpyAsync(&h->last_ordered, scr + 9, sizeof(int), cudaMemcpyDeviceToHost, s));
   B200_CUDA(cudaStreamSynchronize(s));
   B200_CUDA(cudaEventElapsedTime(&h->last_ms, h->ev[0], h->ev[1]));
   *n_out = (int)K;
