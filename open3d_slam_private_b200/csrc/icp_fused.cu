@@ -262,6 +262,14 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     const float br_lo = p.use_trimmed ? S.lo : INFINITY, br_hi = p.use_trimmed ? S.hi : INFINITY;
     double role_acc = 0.0;    // thread (value v = tid / 16, segment = tid % 16) sums value v over 32 threads
     unsigned cand_base = 0u;  // candidates this CTA has parked so far
+    // General shape, one query per thread (rounds == 1), point-to-plane: the match, the transformed query and the matched
+    // point and normal stay in registers across the quantile barriers, so that the linearisation phase neither re-reads
+    // its inputs nor waits for the gather (the loads are issued here, before the barriers).
+    const bool carry = (K == 1) && rounds == 1 && !fast && p.minimizer == 0;
+    bool st_in = false;
+    int st_i = 0, st_sp = -1;
+    float st_d = INFINITY;
+    float4 st_q = make_float4(0.f, 0.f, 0.f, 1.f), st_r4 = make_float4(0.f, 0.f, 0.f, 0.f), st_n4 = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int round = 0; round < rounds; ++round) {
       const int slot = (gtid >> 5) + round * (nthreads >> 5);
       const int i = slot < nslots ? query_of(slot, lane, nslots, coh, qstride) : p.N;
@@ -290,6 +298,13 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
         if (in) {
           p.ids[i] = bid; p.dists[i] = bd; p.spos[i] = bsp;
           if (p.use_trimmed && bd != INFINITY) atomicAdd(&s_hist[(__float_as_uint(bd) >> 20) & 0x7ffu], 1u);
+        }
+        if (carry) {
+          st_in = in; st_i = i; st_sp = bsp; st_d = bd; st_q = q;
+          if (in && bsp >= 0) {
+            st_r4 = __ldg(&p.g.pts[bsp]);
+            if (p.g.nrm) st_n4 = __ldg(&p.g.nrm[bsp]);
+          }
         }
         if (fast) {
           // weight factors that do not depend on the quantile, pair linearisation, class w.r.t. the bracket
@@ -596,6 +611,68 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     if (stamp) ts[2] = gtimer();
 
     // ---------------- phase 3: weights + linearisation, reduced to one partial per CTA ----------------
+    if (carry) {
+      float F[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, dot = 0.f, w = 0.f;
+      bool kept = false;
+      if (st_in) {
+        const float d = st_d;
+        const float4 q = st_q, r4 = st_r4, n4 = st_n4;
+        // outlier filter chain = product of the filters' weights (OutlierFilter.cpp:84-99); empty chain: (dist != inf)
+        const bool any = p.use_trimmed || p.use_maxdist || p.use_sn;
+        w = any ? 1.f : (d == INFINITY ? 0.f : 1.f);
+        if (p.use_trimmed) w *= (d <= limit) ? 1.f : 0.f;
+        if (p.use_maxdist) w *= (d <= p.maxdist_lim2) ? 1.f : 0.f;
+        if (p.use_sn && p.reading_n && p.g.nrm) {
+          if (st_sp < 0) w = 0.f;
+          else {
+            const float4 rn = __ldg(&p.reading_n[st_i]);
+            const float3 rr = apply_R(S.R9, make_float3(rn.x, rn.y, rn.z));
+            float a3[3] = {rr.x, rr.y, rr.z}, qn[3], nv[3] = {n4.x, n4.y, n4.z}, no[3];
+            normalized3_dev(a3, qn);
+            normalized3_dev(nv, no);
+            float dotn = __fmul_rn(qn[0], no[0]);
+            dotn = __fadd_rn(dotn, __fmul_rn(qn[1], no[1]));
+            dotn = __fadd_rn(dotn, __fmul_rn(qn[2], no[2]));
+            w *= (dotn < p.sn_cos) ? 0.f : 1.f;
+          }
+        }
+        p.weights[st_i] = w;
+        kept = (d != INFINITY) && (w != 0.f);  // ErrorElements, ErrorMinimizer.cpp:103-107
+        // crossProduct (ErrorMinimizer.cpp:376-378) and calculateOptimizationHessian (ICP.cpp:1527-1565)
+        F[0] = __fsub_rn(__fmul_rn(q.y, n4.z), __fmul_rn(q.z, n4.y));
+        F[1] = __fsub_rn(__fmul_rn(q.z, n4.x), __fmul_rn(q.x, n4.z));
+        F[2] = __fsub_rn(__fmul_rn(q.x, n4.y), __fmul_rn(q.y, n4.x));
+        F[3] = n4.x; F[4] = n4.y; F[5] = n4.z;
+        dot = __fmul_rn(__fsub_rn(q.x, r4.x), n4.x);
+        dot = __fadd_rn(dot, __fmul_rn(__fsub_rn(q.y, r4.y), n4.y));
+        dot = __fadd_rn(dot, __fmul_rn(__fsub_rn(q.z, r4.z), n4.z));
+      }
+      float4 pb = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (xicp && S.iteration == 0 && kept) pb = apply_T(S.TcInv, st_q);   // calculatePointCloudCenter, ICP.cpp:1594-1618
+      {
+        float* col = s_dyn + tid;
+        int t = 0;
+#pragma unroll
+        for (int c = 0; c < 6; ++c)
+#pragma unroll
+          for (int a = 0; a <= c; ++a) { col[t * kIcpThreads] = kept ? __fmul_rn(__fmul_rn(w, F[a]), F[c]) : 0.f; ++t; }
+#pragma unroll
+        for (int a = 0; a < 6; ++a) col[(21 + a) * kIcpThreads] = kept ? __fmul_rn(__fmul_rn(w, F[a]), dot) : 0.f;
+        col[27 * kIcpThreads] = kept ? 1.f : 0.f;
+        col[28 * kIcpThreads] = kept ? w : 0.f;
+        col[29 * kIcpThreads] = pb.x; col[30 * kIcpThreads] = pb.y; col[31 * kIcpThreads] = pb.z;
+      }
+      __syncthreads();
+      const double role = role_sum(s_dyn, tid);
+      double* red = &s_red[0][0];   // kFastVals x 16 segment sums, index = value * 16 + segment = tid
+      red[tid] = role;
+      __syncthreads();
+      if (tid < kAccum) {
+        double t = 0.0;
+        for (int sg = 0; sg < 16; ++sg) t += red[tid * 16 + sg];
+        __stcg(&p.partials[(size_t)blockIdx.x * kAccum + tid], t);
+      }
+    } else {
     for (int t = tid; t < kWarps * kAccum; t += kIcpThreads) (&s_red[0][0])[t] = 0.0;
     __syncthreads();
     for (int slot = gtid >> 5; slot < nslots; slot += nthreads >> 5) {  // same map as phase 1 (no barrier needed in between)
@@ -717,6 +794,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
       for (int w2 = 0; w2 < kWarps; ++w2) s += s_red[w2][tid];
       __stcg(&p.partials[(size_t)blockIdx.x * kAccum + tid], s);
     }
+    }  // !carry
     if (stamp) ts[3] = gtimer();
     grid.sync();
     if (stamp) ts[4] = gtimer();
