@@ -59,6 +59,7 @@ struct BlockState {
 };
 
 constexpr int kWarps = kIcpThreads / 32;
+constexpr float kBracketCands = 300.f;   // candidates the TrimmedDist bracket of the single-barrier shape aims at
 static_assert(sizeof(Warp1Scratch) * kWarps <= (size_t)kFastVals * kIcpThreads * sizeof(float),
               "the search scratch must fit into the staging tile it shares");
 
@@ -1103,7 +1104,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
         const float rel = S.have_bracket ? fabsf(limit - S.lim_prev) / S.lim_prev : 1.f;
         if (S.path != 0 && n_cand_seen > 0) S.dens = (float)n_cand_seen / S.delta;   // candidates per unit of delta
         else if (S.dens == 0.f) S.dens = 0.5f * (float)p.N * (float)p.k;
-        const float dmax = fminf(1200.f / S.dens, 0.25f);
+        const float dmax = fminf(kBracketCands / S.dens, 0.25f);
         // predicted movement of the limit: what was just seen, scaled by how fast the pose updates are shrinking
         float step = 0.f;
         for (int t = 0; t < 6; ++t) step += S.x[t] * S.x[t];
