@@ -35,7 +35,7 @@ METRIC = "icp_registrations_per_s_128k_scan_vs_5M_map"
 
 
 # dram bytes per launch of icp_persistent_kernel<1> on the default workload, from the committed ncu capture
-NCU_TRAFFIC_BYTES_PER_LAUNCH = 8.11e6
+NCU_TRAFFIC_BYTES_PER_LAUNCH = 9.58e6
 
 
 
@@ -326,8 +326,8 @@ def run_b200(args):
         "roofline": {"kernel": "icp_persistent_kernel<1>", "bound": "hbm", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": NCU_TRAFFIC_BYTES_PER_LAUNCH,
                      "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum, ncu --set full, "
-                                       "profiles/r01_icp_kernel_final2_ncu_summary.txt (default workload only)",
-                     "limiter": "issue/latency (smsp issue active 34 %), not HBM: the touched map cells stay in L2",
+                                       "profiles/r01_icp_kernel_final3_ncu_summary.txt (default workload only)",
+                     "limiter": "issue/latency (smsp issue active 30 %), not HBM: the touched map cells stay in L2",
                      "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg_bytes / K, "avg_launch_ms": kern_ms / K,
                      "knn_candidate_GBps": touched * 16 / (kern_ms * 1e-3) / 1e9,
