@@ -44,7 +44,7 @@ struct BlockState {
   int nrot;
   Quat rot[kMaxHist];
   float tr[kMaxHist][3];
-  unsigned sel_bin, sel_rank, sel_total;
+  unsigned sel_bin, sel_rank, sel_total, sel_cnt, list_base;
   int P, solve_info;
   float wsum;
   // TrimmedDist bracket predicted from the previous iteration's limit (single-barrier path)
@@ -116,11 +116,41 @@ __device__ __forceinline__ void select_bin(const unsigned* __restrict__ ghist, u
   if (total > 0u && rank >= ex && rank < ex + sum) {
 #pragma unroll
     for (int j = 0; j < per; ++j) {
-      if (rank >= ex && rank < ex + c[j]) { S.sel_bin = threadIdx.x * per + j; S.sel_rank = rank - ex; }
+      if (rank >= ex && rank < ex + c[j]) { S.sel_bin = threadIdx.x * per + j; S.sel_rank = rank - ex; S.sel_cnt = c[j]; }
       ex += c[j];
     }
   }
   __syncthreads();
+}
+
+// rank-th smallest (0-based) key among vals[0..n), key = bits(val) - base_bits < 2^nbits: radix select in shared memory,
+// 9 bits per pass (bins: 512 counters, one per thread). Called by the whole CTA; every thread returns the key.
+__device__ __forceinline__ unsigned smem_radix_select(const float* vals, unsigned n, unsigned base_bits, int nbits,
+                                                      unsigned rank, unsigned* bins, unsigned* s_scan, BlockState& S) {
+  const int tid = threadIdx.x;
+  unsigned prefix = 0u, mask = 0u;
+  int shift = nbits > 9 ? nbits - 9 : 0;
+  while (true) {
+    bins[tid] = 0u;
+    __syncthreads();
+    for (unsigned c = tid; c < n; c += kIcpThreads) {
+      const unsigned key = __float_as_uint(vals[c]) - base_bits;
+      if ((key & mask) == prefix) atomicAdd(&bins[(key >> shift) & 511u], 1u);
+    }
+    __syncthreads();
+    const unsigned cnt = bins[tid];
+    unsigned tot2;
+    const unsigned ex = block_excl_scan(cnt, s_scan, tot2);
+    if (rank >= ex && rank < ex + cnt) { S.sel_bin = (unsigned)tid; S.sel_rank = rank - ex; }
+    __syncthreads();
+    prefix |= S.sel_bin << shift;
+    mask |= 511u << shift;
+    rank = S.sel_rank;
+    __syncthreads();
+    if (shift == 0) break;
+    shift = shift > 9 ? shift - 9 : 0;
+  }
+  return prefix;
 }
 
 __device__ __forceinline__ void flush_hist(unsigned* s_hist, unsigned* __restrict__ ghist) {
@@ -241,6 +271,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     if (p.use_trimmed) {
       unsigned* gz = p.hist + (size_t)(par ^ 1) * 3 * kHistBins;
       for (int b = gtid; b < 3 * kHistBins; b += nthreads) gz[b] = 0u;
+      if (gtid == 0) p.list_count[par ^ 1] = 0u;
     }
 
     // ---------------- phase 1: transform + match ----------------
@@ -498,32 +529,11 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
           // the r_in-th smallest candidate: radix select, 9 bits per pass, on key = bits(d) - bits(lo) (monotone for
           // positive floats; the bracket is narrow, so 2-3 passes)
           {
-            unsigned* bins = reinterpret_cast<unsigned*>(red);  // 512 counters, one per thread
             const unsigned base_bits = __float_as_uint(br_lo);
             const unsigned range = __float_as_uint(br_hi) - base_bits;
             const int nbits = 32 - __clz((int)(range | 1u));
-            unsigned prefix = 0u, mask = 0u, rank = r_in;
-            int shift = nbits > 9 ? nbits - 9 : 0;
-            while (true) {
-              bins[tid] = 0u;
-              __syncthreads();
-              for (unsigned c = tid; c < n_cand; c += kIcpThreads) {
-                const unsigned key = __float_as_uint(s_cd[c]) - base_bits;
-                if ((key & mask) == prefix) atomicAdd(&bins[(key >> shift) & 511u], 1u);
-              }
-              __syncthreads();
-              const unsigned cnt = bins[tid];
-              unsigned tot2;
-              const unsigned ex = block_excl_scan(cnt, s_scan, tot2);
-              if (rank >= ex && rank < ex + cnt) { S.sel_bin = (unsigned)tid; S.sel_rank = rank - ex; }
-              __syncthreads();
-              prefix |= S.sel_bin << shift;
-              mask |= 511u << shift;
-              rank = S.sel_rank;
-              if (shift == 0) break;
-              shift = shift > 9 ? shift - 9 : 0;
-            }
-            if (tid == 0) S.limit_bits = base_bits + prefix;
+            const unsigned key = smem_radix_select(s_cd, n_cand, base_bits, nbits, r_in, reinterpret_cast<unsigned*>(red), s_scan, S);
+            if (tid == 0) S.limit_bits = base_bits + key;
             __syncthreads();
           }
           limit = __uint_as_float(S.limit_bits);
@@ -584,7 +594,26 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
         __syncthreads();
         break;
       }
-      const unsigned bin0 = S.sel_bin, rank0 = S.sel_rank;
+      const unsigned bin0 = S.sel_bin, rank0 = S.sel_rank, cnt0 = S.sel_cnt;
+      if (carry && cnt0 <= (unsigned)kListCap) {
+        // Second and third level in one step: the few distances of the selected bin (every thread still holds its own
+        // in a register) are appended to a list, and after ONE more barrier every CTA picks element rank0 of the list by
+        // a radix select in shared memory — instead of two more histogram passes with a barrier each.
+        const unsigned mine = (st_in && st_d != INFINITY && ((__float_as_uint(st_d) >> 20) & 0x7ffu) == bin0) ? 1u : 0u;
+        unsigned tot;
+        const unsigned pos = block_excl_scan(mine, s_scan, tot);
+        if (tid == 0 && tot) S.list_base = atomicAdd(&p.list_count[par], tot);
+        __syncthreads();
+        float* list = p.cand_d + (size_t)par * kListCap;   // free in a general iteration (the parked candidates live here)
+        if (mine) __stcg(&list[S.list_base + pos], st_d);
+        grid.sync();
+        float* s_list = s_dyn;
+        for (unsigned c = tid; c < cnt0; c += kIcpThreads) s_list[c] = __ldcg(&list[c]);
+        __syncthreads();
+        const unsigned base_bits = bin0 << 20;
+        const unsigned key = smem_radix_select(s_list, cnt0, base_bits, 20, rank0, reinterpret_cast<unsigned*>(&s_red[0][0]), s_scan, S);
+        limit = __uint_as_float(base_bits + key);
+      } else {
       zero_hist(s_hist);
       for (int i = gtid; i < p.N; i += nthreads)
         for (int j = 0; j < k; ++j) {
@@ -608,6 +637,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
       grid.sync();
       select_bin(gh + 2 * kHistBins, rank1, false, 0.f, s_scan, S);
       limit = __uint_as_float((pre << 9) | S.sel_bin);
+      }
     }
     if (stamp) ts[2] = gtimer();
 

@@ -147,7 +147,7 @@ struct b200_icp {
 namespace {
 
 int icp_alloc_fixed(b200_icp* h) {
-  B200_CUDA(cudaMalloc(&h->d_hist, (size_t)2 * 3 * kHistBins * sizeof(unsigned)));
+  B200_CUDA(cudaMalloc(&h->d_hist, ((size_t)2 * 3 * kHistBins + 2) * sizeof(unsigned)));
   B200_CUDA(cudaMalloc(&h->d_partials, icp_partials_capacity(h->device) * sizeof(double)));
   B200_CUDA(cudaMalloc(&h->d_partials2, icp_partials_capacity(h->device) * sizeof(double)));
   B200_CUDA(cudaMalloc(&h->d_meanpart, (size_t)3 * 1024 * sizeof(double)));
@@ -245,7 +245,7 @@ int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool tim
   prepare_reading_kernel<<<pb, 256, 0, s>>>(h->d_raw, h->has_read_n ? h->d_raw_n : nullptr, N, h->d_frames, h->d_read,
                                             h->d_read_n);
   B200_CUDA(cudaGetLastError());
-  B200_CUDA(cudaMemsetAsync(h->d_hist, 0, (size_t)2 * 3 * kHistBins * sizeof(unsigned), s));
+  B200_CUDA(cudaMemsetAsync(h->d_hist, 0, ((size_t)2 * 3 * kHistBins + 2) * sizeof(unsigned), s));
   B200_CUDA(cudaMemsetAsync(h->d_out, 0, sizeof(IcpDeviceResult), s));
   IcpKernelParams p;
   std::memset(&p, 0, sizeof(p));
@@ -283,6 +283,7 @@ int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool tim
   p.x_cos_min = std::cos(h->prm.xicp_min_alignment_angle_deg * (float)M_PI / 180.f);
   p.x_cos_strong = std::cos(h->prm.xicp_strong_alignment_angle_deg * (float)M_PI / 180.f);
   p.partials2 = h->d_partials2;
+  p.list_count = h->d_hist + (size_t)2 * 3 * kHistBins;
   p.hist = h->d_hist; p.partials = h->d_partials; p.out = h->d_out; p.log = h->d_log; p.frames = h->d_frames;
   B200_CUDA(cudaEventRecord(h->ev[2], s));
   B200_TRY(launch_icp_kernel(p, h->device, s, &h->last_grid));

@@ -10,6 +10,7 @@ constexpr int kAccum = 32;             // doubles per CTA partial (29 used)
 constexpr int kMaxHist = 64;           // ring of past poses kept for DifferentialTransformationChecker
 constexpr int kMaxLog = 64;            // per-iteration trace capacity
 constexpr int kFastVals = 32;          // values reduced per pair on the single-barrier path (27 H/b + 5 counters)
+constexpr int kListCap = 16384;        // distances of the selected first-level bin resolved in shared memory (general shape)
 constexpr int kCandCap = 2048;         // bracket candidates the single-barrier path resolves in shared memory
 // 64 KiB staging tile + candidate distances and positions
 constexpr size_t kIcpDynSmem = (size_t)kFastVals * kIcpThreads * sizeof(float) + (size_t)kCandCap * 8;
@@ -66,6 +67,7 @@ struct IcpKernelParams {
   // work buffers (k x N)
   int* ids; float* dists; int* spos; float* weights;
   unsigned* hist;           // [2][3][kHistBins]
+  unsigned* list_count;     // [2]: entries of the per-parity list of the selected bin's distances (cand_d, kListCap each)
   double* partials;         // [gridDim.x][kAccum]
   IcpDeviceResult* out;
   IcpLogEntry* log;         // kMaxLog entries
