@@ -12,8 +12,10 @@
 // Every CTA redundantly reduces the CTA partials in a fixed order and solves, so all CTAs hold bit-identical
 // state and only grid-wide barriers (no broadcasts) separate the phases.
 //
-// Two iteration shapes. GENERAL: match | barrier | 3-pass radix select of the TrimmedDist quantile (2 more
-// barriers) | weights + H/b partials | barrier | reduce + solve: 4 grid barriers. SINGLE-BARRIER (k = 1,
+// Two iteration shapes. GENERAL: match | barrier | first histogram level of the TrimmedDist quantile, the selected
+// bin's distances to a list | barrier | radix select of the list in shared memory, weights + H/b partials from the
+// registers that still hold the match | barrier | reduce + solve: 3 grid barriers (k > 1, more than one query per
+// thread or a bin above kListCap: three histogram levels, 4 barriers). SINGLE-BARRIER (k = 1,
 // point-to-plane): the quantile moves little between iterations, so the limit is bracketed by
 // [lim_prev (1 - delta), lim_prev (1 + delta)]; during matching every pair is classified as certainly inside (d <= lo,
 // accumulated at once), certainly outside (d > hi) or a candidate (few hundred; d and the pair's linearisation are
