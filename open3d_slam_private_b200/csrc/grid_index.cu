@@ -35,7 +35,8 @@ __global__ void pack_normals_kernel(const float* __restrict__ n3, float4* __rest
     out[i] = make_float4(n3[3 * (size_t)i], n3[3 * (size_t)i + 1], n3[3 * (size_t)i + 2], 0.f);
 }
 
-// ---- bounding box over finite coordinates: 6 ordered-uint atomics per block ---------------------------------
+// ---- bounding box over finite coordinates: 6 ordered-uint atomics per BLOCK (one per warp made the six addresses the
+// bottleneck: 87 us for 5 M points, 20 times the time of reading them)
 __global__ void bbox_kernel(const float4* __restrict__ p, int N, unsigned long long* __restrict__ scratch) {
   float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
@@ -45,19 +46,23 @@ __global__ void bbox_kernel(const float4* __restrict__ p, int N, unsigned long l
     for (int d = 0; d < 3; ++d)
       if (isfinite(c[d])) { mn[d] = fminf(mn[d], c[d]); mx[d] = fmaxf(mx[d], c[d]); }
   }
+  __shared__ float sm[6][kThreads / 32];
 #pragma unroll
-  for (int d = 0; d < 3; ++d)
+  for (int d = 0; d < 3; ++d) {
     for (int o = 16; o > 0; o >>= 1) {
       mn[d] = fminf(mn[d], __shfl_xor_sync(0xffffffffu, mn[d], o));
       mx[d] = fmaxf(mx[d], __shfl_xor_sync(0xffffffffu, mx[d], o));
     }
-  if ((threadIdx.x & 31) == 0) {
+    if ((threadIdx.x & 31) == 0) { sm[d][threadIdx.x >> 5] = mn[d]; sm[3 + d][threadIdx.x >> 5] = mx[d]; }
+  }
+  __syncthreads();
+  if (threadIdx.x < 6) {
+    const int d = threadIdx.x;
+    float v = sm[d][0];
+    for (int w = 1; w < kThreads / 32; ++w) v = d < 3 ? fminf(v, sm[d][w]) : fmaxf(v, sm[d][w]);
     uint32_t* s = reinterpret_cast<uint32_t*>(scratch);
-#pragma unroll
-    for (int d = 0; d < 3; ++d) {
-      atomicMin(&s[d], float_as_ordered_uint(mn[d]));
-      atomicMax(&s[3 + d], float_as_ordered_uint(mx[d]));
-    }
+    if (d < 3) atomicMin(&s[d], float_as_ordered_uint(v));
+    else atomicMax(&s[d], float_as_ordered_uint(v));
   }
 }
 
