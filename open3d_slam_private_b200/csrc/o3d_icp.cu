@@ -395,6 +395,7 @@ __global__ void __launch_bounds__(kThreads) o3d_solve_kernel(const __grid_consta
 // no host round trip; the sequence number (steps since the mailbox was created) doubles as the parity that keeps a
 // rank that is one step ahead from overwriting what a slower rank still has to read.
 constexpr int kPeerMax = 16;
+constexpr int kPeerChunk = 8;         // iterations enqueued at a time when the peers are other processes
 constexpr int kPackets = 2 * kVals;   // a double travels as two packets
 struct PeerView {
   unsigned long long* box[kPeerMax];  // box[r]: rank r's mailbox [2 parities][world][kPackets] as seen from this device
@@ -525,6 +526,8 @@ struct b200_o3d {
   unsigned long long* d_mailbox = nullptr;
   PeerView pv;
   bool peers_ready = false;
+  bool peers_ipc = false;     // peers live in other processes: b200_o3d_finish may enqueue the iterations in chunks
+  int peer_pending = 0;       // iterations of the running registration not enqueued yet
   unsigned peer_seq = 0;
   void* opened[kPeerMax] = {};   // mailboxes mapped with cudaIpcOpenMemHandle
 };
@@ -677,6 +680,7 @@ int b200_o3d_begin(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N
   if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
   cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
   h->running = false;
+  h->peer_pending = 0;
   if ((size_t)N > h->cap_src) {
     cudaFree(h->d_src); cudaFree(h->d_src_n); cudaFree(h->d_stage3); cudaFree(h->d_ids); cudaFree(h->d_dists);
     h->d_src = h->d_src_n = nullptr; h->d_stage3 = nullptr; h->d_ids = nullptr; h->d_dists = nullptr;
@@ -778,7 +782,9 @@ int b200_o3d_peer_connect(b200_o3d* h, void* const* mailboxes_dev, const int* de
         cudaGetLastError();
       }
       h->pv.box[r] = (unsigned long long*)mailboxes_dev[r];
+      h->peers_ipc = false;
     } else {
+      h->peers_ipc = true;
       cudaIpcMemHandle_t ih;
       std::memcpy(&ih, (const char*)ipc_handles_64 + (size_t)64 * r, 64);
       void* ptr = nullptr;
@@ -802,13 +808,20 @@ int b200_o3d_enqueue_peers(b200_o3d* h, const float* src4xN, const float* srcn3x
   DeviceGuard dg(h->device);
   h->pv.seq_base = h->peer_seq;
   // max_iteration updates need max_iteration + 1 matches; launches after `done` return at once (on every rank at the
-  // same step: the totals are bit-identical), so nothing is sent or awaited any more
-  for (int it = 0; it <= h->prm.max_iteration; ++it) {
+  // same step: the totals are bit-identical), so nothing is sent or awaited any more. One process per rank: the first
+  // eight iterations now, b200_o3d_finish adds eight more whenever the state it reads back is not done (every rank
+  // reads the same `done`, so all of them do) — a registration of 4-6 updates never pays for 2 x 25 idle launches.
+  // Several handles in one process: everything now (finish of one handle must not wait for work another handle's
+  // finish would have to enqueue).
+  const int total = h->prm.max_iteration + 1;
+  const int now = h->peers_ipc ? std::min(kPeerChunk, total) : total;
+  h->peer_pending = total - now;
+  for (int it = 0; it < now; ++it) {
     o3d_match_lin_kernel<<<h->blocks, kThreads, 0, h->run_stream>>>(h->p);
     o3d_exchange_solve_kernel<<<1, kThreads, 0, h->run_stream>>>(h->p, h->blocks, h->pv);
   }
-  h->peer_seq += (unsigned)(h->prm.max_iteration + 1);
-  h->launches += 2 * (h->prm.max_iteration + 1);
+  h->peer_seq += (unsigned)total;
+  h->launches += 2 * now;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
 }
@@ -844,9 +857,21 @@ int b200_o3d_finish(b200_o3d* h, b200_o3d_result* res) {
   if (!h || !h->running || !res) { set_error("b200_o3d_finish: no registration begun"); return B200_E_NOT_INITIALIZED; }
   DeviceGuard dg(h->device);
   cudaStream_t s = h->run_stream;
-  B200_CUDA(cudaEventRecord(h->ev[2], s));
-  B200_CUDA(cudaMemcpyAsync(h->h_state, h->d_state, sizeof(O3dState), cudaMemcpyDeviceToHost, s));
-  B200_CUDA(cudaStreamSynchronize(s));
+  while (true) {
+    B200_CUDA(cudaEventRecord(h->ev[2], s));
+    B200_CUDA(cudaMemcpyAsync(h->h_state, h->d_state, sizeof(O3dState), cudaMemcpyDeviceToHost, s));
+    B200_CUDA(cudaStreamSynchronize(s));
+    if (h->h_state->done || h->peer_pending <= 0) break;
+    const int n = std::min(kPeerChunk, h->peer_pending);   // peer exchange across processes, not converged yet
+    for (int it = 0; it < n; ++it) {
+      o3d_match_lin_kernel<<<h->blocks, kThreads, 0, s>>>(h->p);
+      o3d_exchange_solve_kernel<<<1, kThreads, 0, s>>>(h->p, h->blocks, h->pv);
+    }
+    h->peer_pending -= n;
+    h->launches += 2 * n;
+    B200_CUDA(cudaGetLastError());
+  }
+  h->peer_pending = 0;
   return o3d_fill_result(h, res);
 }
 
