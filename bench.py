@@ -35,7 +35,7 @@ METRIC = "icp_registrations_per_s_128k_scan_vs_5M_map"
 
 
 # dram bytes per launch of icp_persistent_kernel<1> on the default workload, from the committed ncu capture
-NCU_TRAFFIC_BYTES_PER_LAUNCH = 9.58e6
+NCU_TRAFFIC_BYTES_PER_LAUNCH = 9.38e6
 
 
 
