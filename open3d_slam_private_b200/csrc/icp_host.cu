@@ -47,7 +47,7 @@ __global__ void __launch_bounds__(kMeanThreads) read_sum_kernel(const float4* __
 // frames[64..79] = T_refMean_dataIn = T_refIn_refMean^-1 * T_init (ICP.cpp:975), frames[80..95] = its inverse
 // (transformationToOptimizationFrame.inverse() of the X-ICP detection, ICP.cpp:2236)
 __global__ void frames_kernel(const double* __restrict__ partials, int nblocks, int N, const float* __restrict__ Tinit,
-                              float* __restrict__ frames) {
+                              float* __restrict__ frames, int want_data_in) {
   // one warp: lane l sums blocks l, l + 32, ... (fixed order), then a fixed shuffle tree
   const int lane = threadIdx.x & 31;
   if (blockIdx.x != 0 || threadIdx.x >= 32) return;
@@ -68,9 +68,11 @@ __global__ void frames_kernel(const double* __restrict__ partials, int nblocks, 
   mul4_dev(tmp, Tread, Tpre);
   for (int t = 0; t < 16; ++t) { frames[16 + t] = Tpre[t]; frames[32 + t] = Tread[t]; }
   for (int d = 0; d < 3; ++d) frames[48 + d] = mean[d];
-  float tinv[16];
-  if (!inv4_dev(tmp, tinv)) eye4(tinv);
-  for (int t = 0; t < 16; ++t) { frames[64 + t] = tmp[t]; frames[80 + t] = tinv[t]; }
+  if (want_data_in) {   // only the X-ICP detection needs T_refMean_dataIn and its inverse
+    float tinv[16];
+    if (!inv4_dev(tmp, tinv)) eye4(tinv);
+    for (int t = 0; t < 16; ++t) { frames[64 + t] = tmp[t]; frames[80 + t] = tinv[t]; }
+  }
 }
 
 // reading.features.topRows(3).colwise() -= mean (ICP.cpp:973), then transformations.apply(reading,
@@ -240,7 +242,8 @@ int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool tim
   B200_CUDA(cudaEventRecord(h->ev[1], s));
   const int mb = std::min(kMeanBlocks, std::max(1, (N + kMeanThreads - 1) / kMeanThreads));
   read_sum_kernel<<<mb, kMeanThreads, 0, s>>>(h->d_raw, N, h->d_meanpart);
-  frames_kernel<<<1, 32, 0, s>>>(h->d_meanpart, mb, N, h->d_Tinit, h->d_frames);
+  frames_kernel<<<1, 32, 0, s>>>(h->d_meanpart, mb, N, h->d_Tinit, h->d_frames,
+                                 h->prm.degeneracy == B200_DEGENERACY_OPTIMIZED_EQUALITY ? 1 : 0);
   const int pb = std::max(1, std::min(148 * 8, (N + 255) / 256));
   prepare_reading_kernel<<<pb, 256, 0, s>>>(h->d_raw, h->has_read_n ? h->d_raw_n : nullptr, N, h->d_frames, h->d_read,
                                             h->d_read_n);
