@@ -268,6 +268,13 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     zero_hist(s_hist);  // includes __syncthreads
     const int par = S.iteration & 1;
     unsigned* gh = p.hist + (size_t)par * 3 * kHistBins;
+    // Everything one CTA writes and ANOTHER CTA reads within an iteration is double-buffered by the iteration's parity:
+    // a single-barrier iteration has no closing barrier, so a fast CTA may already be writing iteration n + 1 while a
+    // slow one still reads iteration n; it cannot reach iteration n + 2 before every CTA has passed barrier n + 1.
+    double* const partials = p.partials + (size_t)par * gridDim.x * kAccum;
+    float* const cand_d = p.cand_d + (size_t)par * p.cand_cap;
+    int* const cand_q = p.cand_q + (size_t)par * p.cand_cap;
+    float4* const cand_rec = p.cand_rec + (size_t)par * 2 * p.cand_cap;
     // zero the other parity's histograms for the next iteration: their last readers finished before the barrier
     // that ended the previous iteration, their next writers start after this iteration's barrier
     if (p.use_trimmed) {
@@ -398,9 +405,9 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
             const unsigned pos = block_excl_scan(is_cand, s_scan, tot);
             if (is_cand) {
               const size_t ci = (size_t)blockIdx.x * p.cand_seg + cand_base + pos;
-              p.cand_d[ci] = bd; p.cand_q[ci] = i;
-              p.cand_rec[2 * ci] = make_float4(F[0], F[1], F[2], F[3]);
-              p.cand_rec[2 * ci + 1] = make_float4(F[4], F[5], dot, w_other);
+              cand_d[ci] = bd; cand_q[ci] = i;
+              cand_rec[2 * ci] = make_float4(F[0], F[1], F[2], F[3]);
+              cand_rec[2 * ci + 1] = make_float4(F[4], F[5], dot, w_other);
             }
             cand_base += tot;
           }
@@ -465,7 +472,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
       if (tid < kFastVals) {
         double t = 0.0;
         for (int sg = 0; sg < 16; ++sg) t += red[tid * 16 + sg];
-        __stcg(&p.partials[(size_t)blockIdx.x * kAccum + tid], t);
+        __stcg(&partials[(size_t)blockIdx.x * kAccum + tid], t);
       }
       if (stamp) ts[1] = gtimer();
       grid.sync();
@@ -474,7 +481,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
         const int c = tid & (kAccum - 1), slice = tid / kAccum;
         constexpr int kSlices = kIcpThreads / kAccum;
         double sacc = 0.0;
-        for (unsigned b = slice; b < gridDim.x; b += kSlices) sacc += __ldcg(&p.partials[(size_t)b * kAccum + c]);
+        for (unsigned b = slice; b < gridDim.x; b += kSlices) sacc += __ldcg(&partials[(size_t)b * kAccum + c]);
         red[slice * kAccum + c] = sacc;
         __syncthreads();
         if (tid < kAccum) {
@@ -511,7 +518,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
           // compact numbering of the parked candidates: offsets of the CTA segments by a block scan, then every thread
           // resolves its candidates' segment by bisection (all loads of a round are independent)
           unsigned* s_off = reinterpret_cast<unsigned*>(s_hist);   // the level-0 histogram is not needed any more
-          const unsigned nb = tid < (int)gridDim.x ? (unsigned)(__ldcg(&p.partials[(size_t)tid * kAccum + 29]) + 0.5) : 0u;
+          const unsigned nb = tid < (int)gridDim.x ? (unsigned)(__ldcg(&partials[(size_t)tid * kAccum + 29]) + 0.5) : 0u;
           unsigned tot;
           const unsigned off = block_excl_scan(nb, s_scan, tot);
           s_off[tid] = off;
@@ -524,7 +531,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
               if (s_off[mid] <= c) lo_b = mid; else hi_b = mid - 1;
             }
             const int ci = lo_b * p.cand_seg + (int)(c - s_off[lo_b]);
-            s_cd[c] = __ldcg(&p.cand_d[ci]);
+            s_cd[c] = __ldcg(&cand_d[ci]);
             s_ci[c] = ci;
           }
           __syncthreads();
@@ -546,10 +553,9 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
             float F[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, dot = 0.f, w = 0.f;
             if (c < n_cand) {
               const int ci = s_ci[c];
-              const float4 ra = __ldcg(&p.cand_rec[2 * (size_t)ci]), rb = __ldcg(&p.cand_rec[2 * (size_t)ci + 1]);
+              const float4 ra = __ldcg(&cand_rec[2 * (size_t)ci]), rb = __ldcg(&cand_rec[2 * (size_t)ci + 1]);
               F[0] = ra.x; F[1] = ra.y; F[2] = ra.z; F[3] = ra.w; F[4] = rb.x; F[5] = rb.y; dot = rb.z;
               w = (s_cd[c] <= limit) ? rb.w : 0.f;
-              if (blockIdx.x == 0) p.weights[__ldcg(&p.cand_q[ci])] = w;
             }
             float* col = s_dyn + tid;
             const bool kept = w != 0.f;
@@ -566,6 +572,12 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
             __syncthreads();
             acc2 += role_sum(s_dyn, tid);
             __syncthreads();
+          }
+          // the weights of the parked pairs are written by the CTA that owns the queries (the next iteration's weight
+          // of a query is written by the same CTA, so program order within the CTA is all that is needed)
+          for (unsigned c = tid; c < cand_base; c += kIcpThreads) {
+            const size_t ci = (size_t)blockIdx.x * p.cand_seg + c;
+            p.weights[cand_q[ci]] = (cand_d[ci] <= limit) ? cand_rec[2 * ci + 1].w : 0.f;
           }
           red[tid] = acc2;
           __syncthreads();
@@ -606,7 +618,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
         const unsigned pos = block_excl_scan(mine, s_scan, tot);
         if (tid == 0 && tot) S.list_base = atomicAdd(&p.list_count[par], tot);
         __syncthreads();
-        float* list = p.cand_d + (size_t)par * kListCap;   // free in a general iteration (the parked candidates live here)
+        float* list = cand_d;   // this parity's candidate segment is free in a general iteration
         if (mine) __stcg(&list[S.list_base + pos], st_d);
         grid.sync();
         float* s_list = s_dyn;
@@ -703,7 +715,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
       if (tid < kAccum) {
         double t = 0.0;
         for (int sg = 0; sg < 16; ++sg) t += red[tid * 16 + sg];
-        __stcg(&p.partials[(size_t)blockIdx.x * kAccum + tid], t);
+        __stcg(&partials[(size_t)blockIdx.x * kAccum + tid], t);
       }
     } else {
     for (int t = tid; t < kWarps * kAccum; t += kIcpThreads) (&s_red[0][0])[t] = 0.0;
@@ -825,7 +837,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     if (tid < kAccum) {
       double s = 0.0;
       for (int w2 = 0; w2 < kWarps; ++w2) s += s_red[w2][tid];
-      __stcg(&p.partials[(size_t)blockIdx.x * kAccum + tid], s);
+      __stcg(&partials[(size_t)blockIdx.x * kAccum + tid], s);
     }
     }  // !carry
     if (stamp) ts[3] = gtimer();
@@ -837,7 +849,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
       const int c = tid & (kAccum - 1), slice = tid / kAccum;
       constexpr int kSlices = kIcpThreads / kAccum;
       double s = 0.0;
-      for (unsigned b = slice; b < gridDim.x; b += kSlices) s += __ldcg(&p.partials[(size_t)b * kAccum + c]);
+      for (unsigned b = slice; b < gridDim.x; b += kSlices) s += __ldcg(&partials[(size_t)b * kAccum + c]);
       s_red[slice][c] = s;
       __syncthreads();
       if (tid < kAccum) {
@@ -1202,6 +1214,7 @@ int launch_k(const IcpKernelParams& p, int device, cudaStream_t s, int* grid_out
   grid = std::min(grid, need);
   IcpKernelParams pc = p;
   pc.cand_seg = icp_cand_segment(p.N, grid);
+  pc.cand_cap = icp_cand_capacity(p.N);   // per parity
   if (grid > kIcpThreads || (size_t)grid * (size_t)pc.cand_seg > icp_cand_capacity(p.N)) pc.fast_path = 0;
   void* args[] = {(void*)&pc};
   B200_CUDA(cudaLaunchCooperativeKernel((void*)icp_persistent_kernel<K>, dim3(grid), dim3(kIcpThreads), args,
@@ -1223,7 +1236,7 @@ size_t icp_cand_capacity(int N) { return (size_t)N + (size_t)kIcpThreads * 1024;
 size_t icp_partials_capacity(int device) {
   int sms = 148;
   if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) { cudaGetLastError(); sms = 148; }
-  return (size_t)sms * 8 * kAccum;  // up to 8 CTAs per SM
+  return (size_t)sms * 8 * kAccum * 2;  // up to 8 CTAs per SM, two parities
 }
 
 int launch_icp_kernel(const IcpKernelParams& p, int device, cudaStream_t s, int* grid_out) {

@@ -196,9 +196,10 @@ int icp_ensure_reading(b200_icp* h, int N, bool normals) {
     cudaFree(h->d_cand_d); cudaFree(h->d_cand_q); cudaFree(h->d_cand_rec);
     h->d_cand_d = nullptr; h->d_cand_q = nullptr; h->d_cand_rec = nullptr;
     h->cap_cand = 0;
-    B200_CUDA(cudaMalloc(&h->d_cand_d, cneed * sizeof(float)));
-    B200_CUDA(cudaMalloc(&h->d_cand_q, cneed * sizeof(int)));
-    B200_CUDA(cudaMalloc(&h->d_cand_rec, cneed * 2 * sizeof(float4)));
+    // two parities each (icp_fused.cu: double-buffered by iteration)
+    B200_CUDA(cudaMalloc(&h->d_cand_d, 2 * cneed * sizeof(float)));
+    B200_CUDA(cudaMalloc(&h->d_cand_q, 2 * cneed * sizeof(int)));
+    B200_CUDA(cudaMalloc(&h->d_cand_rec, 2 * cneed * 2 * sizeof(float4)));
     h->cap_cand = cneed;
   }
   (void)normals;
@@ -503,9 +504,12 @@ int b200_icp_get_log(b200_icp* h, int max_log, float* H, float* b, float* x, flo
   DeviceGuard dg(h->device);
   IcpLogEntry* tmp = new (std::nothrow) IcpLogEntry[kMaxLog];
   if (!tmp) { set_error("out of host memory"); return B200_E_CUDA; }
-  if (cudaMemcpy(tmp, h->d_log, (size_t)kMaxLog * sizeof(IcpLogEntry), cudaMemcpyDeviceToHost) != cudaSuccess) {
+  // on the handle's own stream: a blocking cudaMemcpy would go through the legacy default stream and serialise
+  // against other handles' work (handles are re-entrant across threads, b200reg.h)
+  if (cudaMemcpyAsync(tmp, h->d_log, (size_t)kMaxLog * sizeof(IcpLogEntry), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+      cudaStreamSynchronize(h->stream) != cudaSuccess) {
     delete[] tmp;
-    return cuda_fail(cudaGetLastError(), "cudaMemcpy(log)", __FILE__, __LINE__);
+    return cuda_fail(cudaGetLastError(), "cudaMemcpyAsync(log)", __FILE__, __LINE__);
   }
   const int cnt = std::min(std::min(max_log, kMaxLog), h->h_out ? h->h_out->iterations : 0);
   for (int i = 0; i < cnt; ++i) {
@@ -525,9 +529,12 @@ int b200_icp_get_phase_times(b200_icp* h, int max_log, float* us, int* n) {
   DeviceGuard dg(h->device);
   IcpLogEntry* tmp = new (std::nothrow) IcpLogEntry[kMaxLog];
   if (!tmp) { set_error("out of host memory"); return B200_E_CUDA; }
-  if (cudaMemcpy(tmp, h->d_log, (size_t)kMaxLog * sizeof(IcpLogEntry), cudaMemcpyDeviceToHost) != cudaSuccess) {
+  // on the handle's own stream: a blocking cudaMemcpy would go through the legacy default stream and serialise
+  // against other handles' work (handles are re-entrant across threads, b200reg.h)
+  if (cudaMemcpyAsync(tmp, h->d_log, (size_t)kMaxLog * sizeof(IcpLogEntry), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+      cudaStreamSynchronize(h->stream) != cudaSuccess) {
     delete[] tmp;
-    return cuda_fail(cudaGetLastError(), "cudaMemcpy(log)", __FILE__, __LINE__);
+    return cuda_fail(cudaGetLastError(), "cudaMemcpyAsync(log)", __FILE__, __LINE__);
   }
   const int cnt = std::min(std::min(max_log, kMaxLog), h->h_out ? h->h_out->iterations : 0);
   for (int i = 0; i < cnt; ++i) {
@@ -545,9 +552,12 @@ int b200_icp_get_debug_stats(b200_icp* h, int max_log, double* st, int* n) {
   DeviceGuard dg(h->device);
   IcpLogEntry* tmp = new (std::nothrow) IcpLogEntry[kMaxLog];
   if (!tmp) { set_error("out of host memory"); return B200_E_CUDA; }
-  if (cudaMemcpy(tmp, h->d_log, (size_t)kMaxLog * sizeof(IcpLogEntry), cudaMemcpyDeviceToHost) != cudaSuccess) {
+  // on the handle's own stream: a blocking cudaMemcpy would go through the legacy default stream and serialise
+  // against other handles' work (handles are re-entrant across threads, b200reg.h)
+  if (cudaMemcpyAsync(tmp, h->d_log, (size_t)kMaxLog * sizeof(IcpLogEntry), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+      cudaStreamSynchronize(h->stream) != cudaSuccess) {
     delete[] tmp;
-    return cuda_fail(cudaGetLastError(), "cudaMemcpy(log)", __FILE__, __LINE__);
+    return cuda_fail(cudaGetLastError(), "cudaMemcpyAsync(log)", __FILE__, __LINE__);
   }
   const int cnt = std::min(std::min(max_log, kMaxLog), h->h_out ? h->h_out->iterations : 0);
   for (int i = 0; i < cnt; ++i) {
@@ -572,7 +582,8 @@ int b200_icp_get_debug_warps(b200_icp* h, uint32_t* out, int max_slots, int* n) 
   const int slots = std::min(max_slots, (h->N + 31) / 32);
   *n = 0;
   if (!h->d_dbg_warp || slots <= 0) return B200_OK;
-  B200_CUDA(cudaMemcpy(out, h->d_dbg_warp, (size_t)slots * 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  B200_CUDA(cudaMemcpyAsync(out, h->d_dbg_warp, (size_t)slots * 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+  B200_CUDA(cudaStreamSynchronize(h->stream));
   *n = slots;
   return B200_OK;
 }

@@ -68,12 +68,13 @@ struct IcpKernelParams {
   int* ids; float* dists; int* spos; float* weights;
   unsigned* hist;           // [2][3][kHistBins]
   unsigned* list_count;     // [2]: entries of the per-parity list of the selected bin's distances (cand_d, kListCap each)
-  double* partials;         // [gridDim.x][kAccum]
+  double* partials;         // [2 parities][gridDim.x][kAccum]
   IcpDeviceResult* out;
   IcpLogEntry* log;         // kMaxLog entries
   // single-barrier iteration (see icp_fused.cu): per-CTA segments of TrimmedDist bracket candidates
-  float* cand_d; int* cand_q; float4* cand_rec;   // capacity gridDim * cand_seg (cand_rec: 2 float4 per candidate)
+  float* cand_d; int* cand_q; float4* cand_rec;   // [2 parities][cand_cap] (cand_rec: 2 float4 per candidate)
   int cand_seg;             // entries per CTA segment (set by the launcher)
+  size_t cand_cap;          // entries per parity, >= gridDim * cand_seg (set by the launcher)
   int fast_path;            // 0: always run the general 4-barrier iteration
   int coh_log2;             // log2 of the run of consecutive scan points a warp keeps together (0..5), see query_of;
                             // < 0: chosen per iteration by the kernel
