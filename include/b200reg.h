@@ -29,7 +29,9 @@ typedef enum {
   B200_E_NAN = 3,          /* ConvergenceError("abs rotation norm not a number"), TransformationCheckersImpl.cpp:147 */
   B200_E_CUDA = 4,         /* CUDA runtime failure or no device */
   B200_E_UNSUPPORTED = 5,  /* accepted by the reference, not by this core (e.g. knn > 64, force2D) */
-  B200_E_NOT_INITIALIZED = 6 /* std::runtime_error("You must setup a matcher before running ICP") analogue */
+  B200_E_NOT_INITIALIZED = 6, /* std::runtime_error("You must setup a matcher before running ICP") analogue */
+  B200_E_BOUND = 7         /* ConvergenceError("limit out of bounds: ..."), BoundTransformationChecker,
+                              TransformationCheckersImpl.cpp:214-221 */
 } b200_status;
 
 const char* b200_last_error(void);
@@ -135,7 +137,7 @@ int b200_rigid_apply(int device, const float* T16, float* feat4xN, float* normal
 /* ------------------------------------------------------------------------------------------------------------
  * ICP chain — replaces PointMatcher<float>::ICP::{initReference, compute, operator()} (ICP.cpp:793-1349) for the
  * chain {RigidTransformation, KDTreeMatcher, [TrimmedDist][MaxDist][SurfaceNormal]OutlierFilter,
- * PointToPlane|PointToPoint ErrorMinimizer, [Counter][Differential]TransformationChecker}, degeneracyAwareness
+ * PointToPlane|PointToPoint ErrorMinimizer, [Counter][Differential][Bound]TransformationChecker}, degeneracyAwareness
  * None. All iterations run in ONE persistent cooperative kernel; the host reads back one result struct.
  * ---------------------------------------------------------------------------------------------------------- */
 typedef struct b200_icp b200_icp;
@@ -167,6 +169,13 @@ typedef struct {
   float xicp_insufficient_information;  /* insufficientInformationThreshold */
   float xicp_min_alignment_angle_deg;   /* point2NormalMinimalAlignmentAngleThreshold (degrees) */
   float xicp_strong_alignment_angle_deg;/* point2NormalStrongAlignmentAngleThreshold (degrees) */
+  /* BoundTransformationChecker (TransformationCheckersImpl.cpp:165-222): init stores rotation and translation of the
+   * first T_iter (identity, ICP.cpp:997); check raises ConvergenceError -> B200_E_BOUND as soon as
+   * angularDistance(q(T_iter), q0) > maxRotationNorm or |t - t0| > maxTranslationNorm. Evaluated after the
+   * Differential checker and before the Counter's stop takes effect (a chain listing Counter first would report
+   * MaxNumIterationsReached instead when both trigger in the same iteration). */
+  int use_bound;
+  float max_rotation_norm, max_translation_norm;   /* defaults 1, 1 (TransformationCheckersImpl.h:117-123) */
 } b200_icp_params;
 
 typedef struct {

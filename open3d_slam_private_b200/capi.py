@@ -14,7 +14,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIBPATH = os.path.join(_HERE, "lib", "libb200reg.so")
 _lib = None
 
-B200_OK, B200_E_NO_MATCHES, B200_E_BAD_PARAM, B200_E_NAN, B200_E_CUDA, B200_E_UNSUPPORTED, B200_E_NOT_INITIALIZED = range(7)
+(B200_OK, B200_E_NO_MATCHES, B200_E_BAD_PARAM, B200_E_NAN, B200_E_CUDA, B200_E_UNSUPPORTED, B200_E_NOT_INITIALIZED,
+ B200_E_BOUND) = range(8)
 OUTLIER_NULL, OUTLIER_MAXDIST, OUTLIER_MINDIST, OUTLIER_MEDIANDIST, OUTLIER_TRIMMEDDIST = range(5)
 
 _f32p = C.POINTER(C.c_float)
@@ -51,6 +52,7 @@ class IcpParams(C.Structure):
         ("smooth_length", C.c_int), ("cell_size", C.c_float),
         ("degeneracy", C.c_int), ("xicp_enough_information", C.c_float), ("xicp_insufficient_information", C.c_float),
         ("xicp_min_alignment_angle_deg", C.c_float), ("xicp_strong_alignment_angle_deg", C.c_float),
+        ("use_bound", C.c_int), ("max_rotation_norm", C.c_float), ("max_translation_norm", C.c_float),
     ]
 
 
@@ -112,7 +114,7 @@ def _check(st):
     if st == B200_OK:
         return
     msg = load().b200_last_error().decode("utf-8", "replace")
-    if st in (B200_E_NO_MATCHES, B200_E_NAN):
+    if st in (B200_E_NO_MATCHES, B200_E_NAN, B200_E_BOUND):
         raise ConvergenceError(st, msg)
     raise B200Error(st, msg)
 

@@ -45,6 +45,7 @@ struct BlockState {
   float counter;
   int nrot;
   Quat rot[kMaxHist];
+  Quat rot0;
   float tr[kMaxHist][3];
   unsigned sel_bin, sel_rank, sel_total, sel_cnt, list_base;
   int P, solve_info;
@@ -235,6 +236,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     S.counter = 0.f;
     S.nrot = 1;
     S.rot[0] = quat_from_T(S.T_iter);   // transformationCheckers.init, ICP.cpp:997
+    S.rot0 = S.rot[0];                  // BoundTransformationChecker::init (initialTranslation = 0)
     S.tr[0][0] = S.tr[0][1] = S.tr[0][2] = 0.f;
     S.P = 0; S.wsum = 0.f; S.solve_info = 0;
     S.have_bracket = 0; S.try_fast = 0; S.path = 0; S.lim_prev = 0.f; S.delta = 0.25f; S.lo = 0.f; S.hi = 0.f; S.dens = 0.f; S.step_prev = 0.f;
@@ -1126,7 +1128,14 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
           }
           if (cv0 != cv0 || cv1 != cv1) { S.status = B200_E_NAN; S.iterate = 0; }
         }
-        if (counterHit) { S.iterate = 0; S.maxReached = 1; }
+        if (p.use_bound && S.status == B200_OK) {
+          // BoundTransformationChecker::check (TransformationCheckersImpl.cpp:198-222) against the pose stored by init
+          // (T_iter = identity, ICP.cpp:997): throws ConvergenceError when a bound is exceeded
+          const float cvr = angular_distance(quat_from_T(S.T_iter), S.rot0);
+          const float cvt = sqrtf(S.T_iter[12] * S.T_iter[12] + S.T_iter[13] * S.T_iter[13] + S.T_iter[14] * S.T_iter[14]);
+          if (cvr > p.bound_rot || cvt > p.bound_trans) { S.status = B200_E_BOUND; S.iterate = 0; }
+        }
+        if (counterHit && S.status == B200_OK) { S.iterate = 0; S.maxReached = 1; }
         if (stamp) tsub[3] = gtimer();
       }
       if (blockIdx.x == 0 && S.iteration < kMaxLog && p.log) {

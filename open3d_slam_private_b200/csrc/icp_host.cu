@@ -223,6 +223,10 @@ int check_params(const b200_icp_params* p) {
     set_error("degeneracyAwareness OptimizedEqualityConstraints: knn must be 1");
     return B200_E_UNSUPPORTED;
   }
+  if (p->use_bound && !(p->max_rotation_norm >= 0.f && p->max_translation_norm >= 0.f)) {
+    set_error("BoundTransformationChecker: maxRotationNorm / maxTranslationNorm must be >= 0");
+    return B200_E_BAD_PARAM;
+  }
   if (p->max_iterations <= 0 && !p->use_differential) {
     set_error("ICP chain needs at least one transformation checker");
     return B200_E_BAD_PARAM;
@@ -264,6 +268,7 @@ int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool tim
   p.minimizer = h->prm.minimizer;
   p.max_iterations = h->prm.max_iterations; p.use_differential = h->prm.use_differential;
   p.min_rot = h->prm.min_diff_rot; p.min_trans = h->prm.min_diff_trans; p.smooth = h->prm.smooth_length;
+  p.use_bound = h->prm.use_bound; p.bound_rot = h->prm.max_rotation_norm; p.bound_trans = h->prm.max_translation_norm;
   p.ids = h->d_ids; p.dists = h->d_dists; p.spos = h->d_spos; p.weights = h->d_w;
   p.cand_d = h->d_cand_d; p.cand_q = h->d_cand_q; p.cand_rec = h->d_cand_rec; p.cand_seg = 0;
   p.fast_path = (h->fast_path && h->prm.knn == 1) ? 1 : 0;
@@ -332,6 +337,7 @@ int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool tim
   const int st = h->h_out->status;
   if (st == B200_E_NO_MATCHES) set_error("ConvergenceError: no point to minimize / no matches");
   else if (st == B200_E_NAN) set_error("ConvergenceError: abs rotation norm not a number");
+  else if (st == B200_E_BOUND) set_error("ConvergenceError: limit out of bounds (BoundTransformationChecker)");
   return st;
 }
 
@@ -365,6 +371,7 @@ void b200_icp_default_params(b200_icp_params* p) {
   p->degeneracy = B200_DEGENERACY_NONE;
   p->xicp_enough_information = 250.f; p->xicp_insufficient_information = 180.f;
   p->xicp_min_alignment_angle_deg = 80.f; p->xicp_strong_alignment_angle_deg = 45.f;
+  p->use_bound = 0; p->max_rotation_norm = 1.f; p->max_translation_norm = 1.f;   // TransformationCheckersImpl.h:117-123
 }
 
 int b200_icp_create(b200_icp** out, int device, const b200_icp_params* prm) {

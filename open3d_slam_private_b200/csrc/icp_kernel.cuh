@@ -64,6 +64,7 @@ struct IcpKernelParams {
   int use_sn; float sn_cos;
   int minimizer;            // 0 point-to-plane, 1 point-to-point
   int max_iterations; int use_differential; float min_rot, min_trans; int smooth;
+  int use_bound; float bound_rot, bound_trans;   // BoundTransformationChecker (TransformationCheckersImpl.cpp:165-222)
   // work buffers (k x N)
   int* ids; float* dists; int* spos; float* weights;
   unsigned* hist;           // [2][3][kHistBins]

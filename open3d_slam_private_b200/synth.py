@@ -93,17 +93,18 @@ class Scene:
                 pw_z = origin[2] + tw * dirs[:, 2]
                 ok = (tw > 0) & (np.abs(pw_x) <= hx) & (pw_z >= 0) & (pw_z <= H)
                 t = np.where(ok & (tw < t), tw, t)
-            # boxes: slab test, chunked over rays
+            # boxes and cylinders: chunked over rays, the chunks spread over host threads (numpy releases the GIL; every
+            # ray sees the same arithmetic whatever the chunking, so the scan does not depend on the thread count)
             inv = 1.0 / dirs
-            for lo in range(0, n, 16384):
-                sl = slice(lo, min(n, lo + 16384))
+
+            def chunk(lo):
+                sl = slice(lo, min(n, lo + 8192))
                 t1 = (self.box_min[None, :, :] - origin[None, None, :]) * inv[sl, None, :]
                 t2 = (self.box_max[None, :, :] - origin[None, None, :]) * inv[sl, None, :]
                 tn = np.nanmax(np.minimum(t1, t2), axis=2)
                 tf = np.nanmin(np.maximum(t1, t2), axis=2)
                 hit = (tf >= np.maximum(tn, 0)) & (tn > 0)
                 tb = np.where(hit, tn, np.inf).min(axis=1)
-                t[sl] = np.minimum(t[sl], tb)
                 # cylinders
                 dxy = dirs[sl, :2]
                 a = np.sum(dxy * dxy, axis=1)[:, None]
@@ -115,7 +116,18 @@ class Scene:
                 z = origin[2] + tc * dirs[sl, 2][:, None]
                 hitc = (disc >= 0) & (tc > 0) & (z >= 0) & (z <= self.cyl_h[None, :])
                 tcm = np.where(hitc, tc, np.inf).min(axis=1)
-                t[sl] = np.minimum(t[sl], tcm)
+                return sl, np.minimum(tb, tcm)
+
+            import os
+            from concurrent.futures import ThreadPoolExecutor
+
+            def guarded(lo):   # numpy's error state is per thread
+                with np.errstate(divide="ignore", invalid="ignore"):
+                    return chunk(lo)
+
+            with ThreadPoolExecutor(max_workers=min(32, os.cpu_count() or 1)) as ex:
+                for sl, tb in ex.map(guarded, range(0, n, 8192)):
+                    t[sl] = np.minimum(t[sl], tb)
         t[t > max_range] = np.inf
         return t
 

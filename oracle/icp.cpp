@@ -100,11 +100,13 @@ struct Checkers {
   const orc_icp_params* p;
   float counter = 0.f;
   std::vector<Quat> rot;
+  Quat rot0;              // BoundTransformationChecker::initialRotation3D
   std::vector<float> tr;  // 3 per entry
   void init(const float* T) {
     counter = 0.f;
     rot.clear(); tr.clear();
     rot.push_back(quatFromT(T));
+    rot0 = rot[0];
     tr.push_back(T[12]); tr.push_back(T[13]); tr.push_back(T[14]);
   }
   // returns status; sets iterate / maxReached
@@ -131,6 +133,13 @@ struct Checkers {
         if (cv0 < p->min_diff_rot && cv1 < p->min_diff_trans) iterate = false;
       }
       if (cv0 != cv0 || cv1 != cv1) return ORC_E_NAN;  // ConvergenceError, TransformationCheckersImpl.cpp:147-150
+    }
+    if (p->use_bound) {
+      // BoundTransformationChecker::check, TransformationCheckersImpl.cpp:198-222; init saw T_iter = identity
+      // (ICP.cpp:997): initialRotation3D = Quaternion(I), initialTranslation = 0
+      const float cvr = angularDistance(quatFromT(T), rot0);
+      const float cvt = std::sqrt(T[12] * T[12] + T[13] * T[13] + T[14] * T[14]);
+      if (cvr > p->max_rotation_norm || cvt > p->max_translation_norm) return ORC_E_BOUND;  // ConvergenceError, :214-221
     }
     if (counterHit) { iterate = false; maxReached = true; }
     return ORC_OK;

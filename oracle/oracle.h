@@ -25,6 +25,7 @@ extern "C" {
 #define ORC_E_NO_MATCHES 1   /* PointMatcher::ConvergenceError */
 #define ORC_E_BAD_PARAM 2
 #define ORC_E_NAN 3
+#define ORC_E_BOUND 7   /* ConvergenceError("limit out of bounds"), TransformationCheckersImpl.cpp:214-221 */
 
 /* ---- kNN (stands in for libnabo NNS::knn as called at MatchersImpl.cpp:98) ---- */
 int orc_knn_brute(const float* ref4xM, int M, const float* query4xN, int N, int k, float maxDist,
@@ -113,6 +114,9 @@ typedef struct {
   float xicp_insufficient;  /* insufficientInformationThreshold */
   float xicp_cos_min;       /* cos(point2NormalMinimalAlignmentAngleThreshold) */
   float xicp_cos_strong;    /* cos(point2NormalStrongAlignmentAngleThreshold) */
+  /* BoundTransformationChecker (TransformationCheckersImpl.cpp:165-222), evaluated after Differential */
+  int use_bound;
+  float max_rotation_norm, max_translation_norm;
 } orc_icp_params;
 
 typedef struct {

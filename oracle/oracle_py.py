@@ -13,6 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
 ORC_OK, ORC_E_NO_MATCHES, ORC_E_BAD_PARAM, ORC_E_NAN = 0, 1, 2, 3
+ORC_E_BOUND = 7
 
 _f32p = C.POINTER(C.c_float)
 _i32p = C.POINTER(C.c_int32)
@@ -30,6 +31,7 @@ class IcpParams(C.Structure):
         ("knn_threads", C.c_int),
         ("degeneracy", C.c_int), ("xicp_enough", C.c_float), ("xicp_insufficient", C.c_float),
         ("xicp_cos_min", C.c_float), ("xicp_cos_strong", C.c_float),
+        ("use_bound", C.c_int), ("max_rotation_norm", C.c_float), ("max_translation_norm", C.c_float),
     ]
 
 
@@ -261,18 +263,17 @@ def default_params(**kw):
                   use_differential=1, min_diff_rot=0.001, min_diff_trans=0.001, smooth_length=3, counter_first=1,
                   accum=1, mean_mode=1, knn_threads=1, degeneracy=0, xicp_enough=250.0, xicp_insufficient=180.0,
                   xicp_cos_min=float(np.cos(np.float32(np.deg2rad(np.float32(80.0))))),
-                  xicp_cos_strong=float(np.cos(np.float32(np.deg2rad(np.float32(45.0))))))
+                  xicp_cos_strong=float(np.cos(np.float32(np.deg2rad(np.float32(45.0))))),
+                  use_bound=0, max_rotation_norm=1.0, max_translation_norm=1.0)
     for k_, v in kw.items():
         assert hasattr(p, k_), k_
         setattr(p, k_, v)
     return p
 
 
-def icp(params, ref4, refn, read4, readn=None, T_init=None, max_log=64, forced_T_iters=None):
-    """forced_T_iters (n,4,4): one-step mode, see orc_icp_forced — T_iters[i] of the result is the oracle's own
-    update computed from forced_T_iters[i-1]; ids/dists/weights are those of the last iteration."""
-    ref4, refn, read4, readn = f32(ref4), f32(refn), f32(read4), f32(readn)
-    M, N, k = ref4.shape[0], read4.shape[0], params.knn
+def _icp_run(call, params, N, T_init, max_log, forced_T_iters):
+    """shared driver of orc_icp_forced / orc_icp_compute: allocates the logs, unpacks the result"""
+    k = params.knn
     Ti = np.eye(4, dtype=np.float32) if T_init is None else np.asarray(T_init, np.float32)
     Tc = np.ascontiguousarray(Ti.T).ravel()
     res = IcpResult()
@@ -289,9 +290,8 @@ def icp(params, ref4, refn, read4, readn=None, T_init=None, max_log=64, forced_T
     else:
         fT = np.ascontiguousarray(np.asarray(forced_T_iters, np.float32).transpose(0, 2, 1)).reshape(-1)
         nf = len(forced_T_iters)
-    st = lib().orc_icp_forced(C.byref(params), _fp(ref4), _fp(refn), M, _fp(read4), _fp(readn), N, _fp(Tc),
-                              C.byref(res), max_log, _fp(logH), _fp(logb), _fp(logx), _fp(logT), _ip(logP), _ip(ids),
-                              _fp(dists), _fp(w), _fp(fT), nf)
+    st = call(_fp(Tc), C.byref(res), max_log, _fp(logH), _fp(logb), _fp(logx), _fp(logT), _ip(logP), _ip(ids),
+              _fp(dists), _fp(w), _fp(fT), nf)
     it = min(res.iterations, max_log)
     m = lambda a: np.array(a, np.float32).reshape(4, 4).T.copy()
     return dict(status=st, iterations=res.iterations, max_iterations_reached=bool(res.max_iterations_reached),
@@ -306,6 +306,15 @@ def icp(params, ref4, refn, read4, readn=None, T_init=None, max_log=64, forced_T
                 H=logH[:it].reshape(it, 6, 6).transpose(0, 2, 1).copy(), b=logb[:it], x=logx[:it],
                 T_iters=logT[:it].reshape(it, 4, 4).transpose(0, 2, 1).copy(), P=logP[:it], ids=ids, dists=dists,
                 weights=w)
+
+
+def icp(params, ref4, refn, read4, readn=None, T_init=None, max_log=64, forced_T_iters=None):
+    """forced_T_iters (n,4,4): one-step mode, see orc_icp_forced — T_iters[i] of the result is the oracle's own
+    update computed from forced_T_iters[i-1]; ids/dists/weights are those of the last iteration."""
+    ref4, refn, read4, readn = f32(ref4), f32(refn), f32(read4), f32(readn)
+    M, N = ref4.shape[0], read4.shape[0]
+    call = lambda *a: lib().orc_icp_forced(C.byref(params), _fp(ref4), _fp(refn), M, _fp(read4), _fp(readn), N, *a)
+    return _icp_run(call, params, N, T_init, max_log, forced_T_iters)
 
 
 class IcpSession:
@@ -327,6 +336,13 @@ class IcpSession:
         m = lambda a: np.array(a, np.float32).reshape(4, 4).T.copy()
         return dict(status=st, iterations=res.iterations, max_iterations_reached=bool(res.max_iterations_reached),
                     n_matches_last=res.n_matches_last, T=m(res.T), points_touched=res.points_touched)
+
+    def icp(self, params, read4, readn=None, T_init=None, max_log=64, forced_T_iters=None):
+        """like the module-level icp() (logs, last matches, one-step mode) on the kept reference"""
+        read4, readn = f32(read4), f32(readn)
+        N = read4.shape[0]
+        call = lambda *a: lib().orc_icp_compute(self.h, C.byref(params), _fp(read4), _fp(readn), N, *a)
+        return _icp_run(call, params, N, T_init, max_log, forced_T_iters)
 
     def close(self):
         if getattr(self, "h", None):

@@ -42,7 +42,7 @@ def test_version_and_default_params():
 def test_struct_sizes_match_header():
     # the ctypes mirrors must have the C layout of include/b200reg.h
     lib = B.load()
-    assert ctypes.sizeof(B.IcpParams) == lib.b200_struct_size(0) == 21 * 4
+    assert ctypes.sizeof(B.IcpParams) == lib.b200_struct_size(0) == 24 * 4
     assert ctypes.sizeof(B.IcpResult) == lib.b200_struct_size(1)
     assert ctypes.sizeof(B.IndexOpts) == lib.b200_struct_size(2) == 16
     assert ctypes.sizeof(B.SurfaceNormalParams) == lib.b200_struct_size(3)
