@@ -696,6 +696,9 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
       }
       float4 pb = make_float4(0.f, 0.f, 0.f, 0.f);
       if (xicp && S.iteration == 0 && kept) pb = apply_T(S.TcInv, st_q);   // calculatePointCloudCenter, ICP.cpp:1594-1618
+      // The staging tile doubles as the search's per-warp scratch: without TrimmedDist no barrier lies between the
+      // search and this point, and a warp that is done must not overwrite the scratch of one still searching.
+      if (!p.use_trimmed) __syncthreads();
       {
         float* col = s_dyn + tid;
         int t = 0;
