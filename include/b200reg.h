@@ -110,6 +110,25 @@ int b200_dists_quantile(int device, const float* dists, int64_t n, float quantil
 int b200_outlier_surface_normal(int device, const float* nread3xN, const float* nref3xM, int M,
                                 const int32_t* ids_kxN, int knn, int N, float maxAngle, float* weights);
 
+/* b200_outlier_trimmed_noalloc — NO COUNTERPART IN THE REFERENCE; added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it). The same
+ * result as b200_outlier_dist(B200_OUTLIER_TRIMMEDDIST, ratio, ...) with these differences:
+ *   - d_dists (n floats, squared distances, +inf = invalid) and d_weights (n floats) are DEVICE pointers owned by the
+ *     caller; d_status_limit (nullable) is a DEVICE uint32[2] that receives {b200_status decided on the device
+ *     (B200_OK or B200_E_NO_MATCHES), bits of the float limit = Matches::getDistsQuantile}; when the status is
+ *     B200_E_NO_MATCHES no weight is written;
+ *   - the work is only ENQUEUED on cuda_stream (cudaStream_t; NULL = the legacy default stream): no synchronisation,
+ *     no host read-back, and no cudaMalloc / cudaFree / allocating routine of any kind. The radix-select scratch
+ *     (24 640 bytes) is a file-scope __device__ array every GPU that loads the library holds until the process exits;
+ *   - n must not exceed B200_NOALLOC_MAX_N (larger inputs: B200_E_UNSUPPORTED); ratio outside [0, 1] is
+ *     B200_E_BAD_PARAM (checked on the host, before the emptiness the device detects);
+ *   - every call shares that one array per device (each call clears it first): calls whose GPU work overlaps — other
+ *     streams, other host threads on the same device — RACE; serialise them per device. The first call on a device
+ *     resolves the array's device address (cudaGetSymbolAddress); make that call once before a graph capture. */
+#define B200_NOALLOC_MAX_N (1 << 24)
+int b200_outlier_trimmed_noalloc(int device, const float* d_dists, int64_t n, float ratio, float* d_weights,
+                                 uint32_t* d_status_limit, void* cuda_stream);
+
 /* ------------------------------------------------------------------------------------------------------------
  * ErrorMinimizer — replaces ErrorMinimizer::ErrorElements (ErrorMinimizer.cpp:59-193),
  * ICP::calculateOptimizationHessian (ICP.cpp:1513-1566), PointToPlaneErrorMinimizer::compute_in_place with

@@ -239,6 +239,17 @@ def outlier_dist(kind, param, dists, device=0):
     return w
 
 
+NOALLOC_MAX_N = 1 << 24
+
+
+def outlier_trimmed_noalloc(d_dists_ptr, n, ratio, d_weights_ptr, d_status_limit_ptr=0, stream=0, device=0):
+    """b200_outlier_trimmed_noalloc: DEVICE pointers (integers), only enqueues on `stream` (0: legacy default stream);
+    allocates nothing. Returns nothing; the status / limit land in the caller's device uint32[2]."""
+    _check(load().b200_outlier_trimmed_noalloc(device, C.c_void_p(d_dists_ptr), C.c_int64(n), C.c_float(ratio),
+                                               C.c_void_p(d_weights_ptr), C.c_void_p(d_status_limit_ptr or None),
+                                               C.c_void_p(stream or None)))
+
+
 def outlier_surface_normal(nread, nref, ids, max_angle, device=0):
     require_device()
     nread, nref = f32(nread), f32(nref)
