@@ -1,14 +1,17 @@
 #!/usr/bin/env python
-"""Secondary benchmarks for the BASELINE configs that are not bench.py's headline (C2):
+"""The BASELINE configs beside bench.py's headline (C2), as functions bench.py calls and folds into its ONE JSON line
+under "modes" (and a small CLI of its own: python bench_modes.py --mode c4 --gpus 1, or torchrun ... --mode c5).
 
-  --mode c3   GICP, covariances from k = 20 normals, 128k scan vs 5M map, one B200            (registrations/s)
-  --mode c4   batch of independent submap-to-submap registrations sharded over the ranks, no collective (pairs/s)
-  --mode c5   city-scale map spatially partitioned over the ranks, one NCCL allreduce of 32 doubles per iteration
-              (registrations/s; --tile-points per rank, 25 M x 8 = 200 M at full size)
+  index_build   KDTreeMatcher::init replacement on the 5 M-point map (bbox -> histogram -> scan -> scatter)
+  normals       SurfaceNormalDataPointsFilter k = 20 on the map (once) and on a scan (per registration)
+  c3            GICP, covariances from k = 20 normals, 131 072-pt scan vs 5 M-pt map, one B200
+  c4            batch of independent submap-to-submap registrations sharded over the ranks, no collective
+  c5            city-scale map spatially partitioned over the ranks, sums exchanged over NVLink peer memory
 
-Launch like bench.py (python bench_modes.py --mode c4 --gpus 1, or torchrun ... bench_modes.py --mode c5 --gpus N).
-Timing: CUDA events on the stream the kernels run on, max over ranks; rank 0 prints ONE JSON line. Inputs larger
-than L2 where stated. Everything runs through the C ABI (ctypes); no CPU fallback.
+Every mode returns {"ms", "value", "unit", "roofline": {...}, "e2e": {...}, "cpu_baseline": {...} (rank 0, one GPU
+only), ...}. Timing: CUDA events on the stream the kernels run on (inside the library), max over ranks. Algorithmic
+bytes per unit are SURVEY.md §8(d)'s: 116 B/point index build, 376 B/point normals at k = 20, 92 B per GICP
+correspondence-iteration, 64 B per point-to-plane correspondence-iteration. Everything goes through the C ABI.
 """
 import argparse
 import json
@@ -17,151 +20,236 @@ import time
 
 import numpy as np
 
-from bench import ClockSampler, dist_env, pinned_copy
+ROOT = os.path.dirname(os.path.abspath(__file__))
+B_INDEX_BUILD, B_NORMALS_K20, B_GICP, B_P2PLANE = 116, 376, 92, 64
 
 
-def parse():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--mode", choices=["c3", "c4", "c5"], required=True)
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--map-points", type=int, default=5_000_000)
-    ap.add_argument("--scan-points", type=int, default=131072)
-    ap.add_argument("--poses", type=int, default=4)
-    ap.add_argument("--batch", type=int, default=256, help="c4: registrations in the batch")
-    ap.add_argument("--pair-points", type=int, default=200_000, help="c4: points per submap")
-    ap.add_argument("--tile-points", type=int, default=25_000_000, help="c5: map points per rank")
-    ap.add_argument("--max-dist", type=float, default=0.5)
-    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
-                    help="c5: sums over NVLink peer memory inside the solve kernel, or an NCCL allreduce between kernels")
-    return ap.parse_args()
+def hbm_peak():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"
+    except (OSError, KeyError, ValueError):
+        return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def setup():
-    import torch
-    from open3d_slam_private_b200 import capi as B
-    rank, world, local = dist_env()
-    B.require_device()
-    torch.cuda.set_device(local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    return torch, B, dist, rank, world, local
+def roofline(kernel, alg_bytes, ms, per_unit):
+    peak, src = hbm_peak()
+    a = alg_bytes / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
+    return {"kernel": kernel, "bound": "hbm", "achieved": a, "peak": peak, "unit": "GB/s", "frac": a / peak,
+            "traffic": None, "algorithmic_bytes_per_launch": alg_bytes, "algorithmic_bytes_per_unit": per_unit,
+            "avg_launch_ms": ms, "peak_source": src}
 
 
-def max_over_ranks(torch, dist, vals):
-    if dist is None:
-        return list(vals)
-    t = torch.tensor(list(vals), device="cuda", dtype=torch.float64)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return t.tolist()
+def stats(v):
+    v = np.asarray(v, np.float64)
+    return {"median": float(np.median(v)), "p95": float(np.percentile(v, 95)), "mean": float(v.mean()), "n": int(v.size)}
 
 
-def emit(rank, dist, out):
-    if rank == 0:
-        print(json.dumps(out))
-    if dist is not None:
-        dist.destroy_process_group()
+class Ctx:
+    """what bench.py hands to a mode: plumbing (torch, capi, process group) and the C2 clouds when already generated"""
+
+    def __init__(self, args, torch, B, dist, rank, world, local, c2=None):
+        self.args, self.torch, self.B, self.dist = args, torch, B, dist
+        self.rank, self.world, self.local, self._c2 = rank, world, local, c2
+
+    def c2(self):
+        if self._c2 is None:
+            from open3d_slam_private_b200 import synth
+            d = synth.make_c2(M=self.args.map_points, N=self.args.scan_points, n_poses=min(4, self.args.poses))
+            self._c2 = (synth.feat4(d["map_xyz"]), d["map_normals"],
+                        [(synth.feat4(s["xyz"]), s["T_init"], s["T_true"]) for s in d["scans"]])
+        return self._c2
+
+    def max_over_ranks(self, vals):
+        if self.dist is None:
+            return [float(v) for v in vals]
+        t = self.torch.tensor([float(v) for v in vals], device="cuda", dtype=self.torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return t.tolist()
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    @property
+    def with_cpu(self):
+        return self.rank == 0 and self.world == 1 and not getattr(self.args, "no_cpu_baseline", False)
 
 
-_NIDX = {}
+def pinned(torch, a):
+    t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    return t, t.numpy()
 
 
-def device_normals(B, xyz4, knn, device):
-    """estimateNormalsOrCovariancesIfNeeded on the device: k-NN normals, normalised, flipped towards the origin. The
-    index handle is kept between calls (its device buffers are reused), as the C++ shims do."""
-    idx = _NIDX.get(device)
-    if idx is None:
-        idx = _NIDX[device] = B.Index(xyz4, device=device)
-    else:
-        idx.update(xyz4)
-    n = idx.self_normals(knn=knn)["normals"]
-    flip = (n * (-xyz4[:, :3])).sum(1) < 0
+def oriented(n, pts4):
+    """NormalizeNormals + OrientNormalsTowardsCameraLocation(origin) (CloudRegistration.cpp:75-77) on the host"""
+    n = np.ascontiguousarray(n, np.float32)
+    flip = (n * (-pts4[:, :3])).sum(1) < 0
     n[flip] *= -1
-    return np.ascontiguousarray(n, np.float32)
+    return n
 
 
-# ------------------------------------------------------------------------------------------------------------ C3
-def run_c3(args):
-    torch, B, dist, rank, world, local = setup()
-    from open3d_slam_private_b200 import synth
-    d = synth.make_c2(M=args.map_points, N=args.scan_points, n_poses=args.poses)
-    tgt4 = synth.feat4(d["map_xyz"])
+# --------------------------------------------------------------------------------------------------- index build
+def mode_index_build(ctx):
+    B = ctx.B
+    ref4, _, _ = ctx.c2()
+    M = ref4.shape[0]
+    keep, host = pinned(ctx.torch, ref4)
     t0 = time.perf_counter()
-    tgtn = device_normals(B, tgt4, 20, local)          # GICP "covariances from k = 20 neighbours" (normals -> C)
-    normals_map_s = time.perf_counter() - t0
-    h = B.O3dICP(kind=B.O3D_GENERALIZED, max_correspondence_distance=args.max_dist, max_iteration=30, device=local)
-    h.set_target(tgt4, tgtn)
-    scans = []
-    for s in d["scans"]:
-        s4 = synth.feat4(s["xyz"])
-        scans.append((pinned_copy(s4), s["T_init"].astype(np.float64), s["T_true"]))
-    clk = ClockSampler(local) if rank == 0 else None
-    nrm_ms = reg_ms = 0.0
-    iters, perr = [], 0.0
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
-    t_mark0 = None
-    for i in range(args.warmup + args.steps):
-        if i == args.warmup:
-            torch.cuda.synchronize()
-            t_mark0 = time.time()
-        (keep, s4), Ti, Tt = scans[(rank + i * world) % len(scans)]
+    idx = B.Index(host, device=ctx.local)
+    first_wall = (time.perf_counter() - t0) * 1e3
+    dev, wall = [], []
+    for _ in range(5):
         t0 = time.perf_counter()
-        sn = device_normals(B, s4, 20, local)          # per-scan covariances: part of the registration's cost
+        idx.update(host)
+        wall.append((time.perf_counter() - t0) * 1e3)
+        dev.append(idx.info()["build_ms"])
+    info = idx.info()
+    idx.close()
+    ms = float(np.median(dev))
+    out = {"what": "KDTreeMatcher::init replacement: uniform-grid index over the %d-point map" % M,
+           "ms": ms, "value": M / (ms * 1e-3), "unit": "points/s", "device_ms": stats(dev),
+           "roofline": roofline("bbox/hist/scan/scatter (grid_index.cu)", float(M) * B_INDEX_BUILD, ms, B_INDEX_BUILD),
+           "e2e": {"ms": float(np.median(wall)), "first_call_ms_incl_allocation": first_wall,
+                   "h2d_bytes_per_step": M * 16, "d2h_bytes_per_step": 64,
+                   "what": "b200_index_update(host map): H2D + build + host decisions, host wall clock"},
+           "cell_size": info.get("cell_size"), "dims": info.get("dims")}
+    if ctx.with_cpu:
+        from oracle import oracle_py as O
+        t0 = time.perf_counter()
+        kd = O.KdTree(ref4)
+        s = time.perf_counter() - t0
+        del kd
+        out["cpu_baseline"] = {"value": M / s, "unit": "points/s", "cores": 1, "kind": "port", "ms": s * 1e3,
+                               "sample": "one kd-tree build over the same %d-point map (oracle, single thread like libnabo's)" % M}
+    return out
+
+
+# --------------------------------------------------------------------------------------------------- normals
+def mode_normals(ctx, knn=20):
+    B = ctx.B
+    ref4, _, scans = ctx.c2()
+    M, N = ref4.shape[0], scans[0][0].shape[0]
+    midx = B.Index(ref4, device=ctx.local)
+    map_dev, map_wall = [], []
+    for _ in range(2):
+        t0 = time.perf_counter()
+        midx.self_normals(knn=knn)
+        map_wall.append((time.perf_counter() - t0) * 1e3)
+        map_dev.append(midx.last_device_ms())
+    midx.close()
+    sidx = B.Index(scans[0][0], device=ctx.local)
+    scan_dev, scan_wall, upd = [], [], []
+    for i in range(8):
+        s4 = scans[i % len(scans)][0]
+        t0 = time.perf_counter()
+        sidx.update(s4)
         t1 = time.perf_counter()
+        sidx.self_normals(knn=knn)
+        t2 = time.perf_counter()
+        upd.append((t1 - t0) * 1e3)
+        scan_wall.append((t2 - t0) * 1e3)
+        scan_dev.append(sidx.last_device_ms())
+    sidx.close()
+    mm, sm = float(np.min(map_dev)), float(np.median(scan_dev))
+    out = {"what": "SurfaceNormalDataPointsFilter knn = %d (self k-NN + covariance + 3x3 eigen) on the device" % knn,
+           "ms": mm, "value": M / (mm * 1e-3), "unit": "points/s",
+           "map": {"points": M, "device_ms": mm, "wall_ms_incl_d2h_of_normals": float(np.min(map_wall)),
+                   "roofline": roofline("surface_normal_warp_kernel", float(M) * B_NORMALS_K20, mm, B_NORMALS_K20)},
+           "scan": {"points": N, "device_ms": stats(scan_dev), "index_update_wall_ms": float(np.median(upd)),
+                    "wall_ms_incl_h2d_index_d2h": float(np.median(scan_wall)),
+                    "roofline": roofline("surface_normal_warp_kernel", float(N) * B_NORMALS_K20, sm, B_NORMALS_K20)},
+           "roofline": roofline("surface_normal_warp_kernel", float(M) * B_NORMALS_K20, mm, B_NORMALS_K20),
+           "e2e": {"ms": float(np.min(map_wall)), "h2d_bytes_per_step": 0, "d2h_bytes_per_step": M * 12,
+                   "what": "b200_index_self_normals on the resident map index, normals copied back"}}
+    if ctx.with_cpu:
+        from oracle import oracle_py as O
+        s4 = scans[0][0]
+        t0 = time.perf_counter()
+        O.surface_normals(s4, knn)
+        s = time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": N / s, "unit": "points/s", "cores": 1, "kind": "port", "ms": s * 1e3,
+                               "sample": "the %d-point scan (kd-tree build + k = %d normals), oracle on one thread as the "
+                                         "reference filter runs; the 5 M map scales per point" % (N, knn)}
+    return out
+
+
+# --------------------------------------------------------------------------------------------------- C3: GICP
+def mode_c3(ctx, steps=16, warmup=3):
+    B, torch = ctx.B, ctx.torch
+    ref4, _, scans = ctx.c2()
+    M, N = ref4.shape[0], scans[0][0].shape[0]
+    md = ctx.args.max_dist
+    midx = B.Index(ref4, device=ctx.local)
+    tgtn = oriented(midx.self_normals(knn=20)["normals"], ref4)    # "covariances from k = 20 neighbours" (normal -> C)
+    map_normals_ms = midx.last_device_ms()
+    midx.close()
+    h = B.O3dICP(kind=B.O3D_GENERALIZED, max_correspondence_distance=md, max_iteration=30, device=ctx.local)
+    h.set_target(ref4, tgtn)
+    sidx = B.Index(scans[0][0], device=ctx.local)
+    host = [(pinned(torch, s4), Ti.astype(np.float64), Tt) for s4, Ti, Tt in scans]
+    reg, nrm, wall, iters, perr = [], [], [], [], 0.0
+    last = None
+    for i in range(warmup + steps):
+        (keep, s4), Ti, Tt = host[i % len(host)]
+        t0 = time.perf_counter()
+        sidx.update(s4)
+        sn = oriented(sidx.self_normals(knn=20)["normals"], s4)     # per-scan covariances: part of a registration's cost
+        nms = sidx.last_device_ms()
         r = h.register(s4, sn, init=Ti)
-        if i >= args.warmup:
-            nrm_ms += (t1 - t0) * 1e3
-            reg_ms += r["total_ms"]
-            iters.append(r["iterations"])
+        t1 = time.perf_counter()
+        if i >= warmup:
+            reg.append(r["total_ms"]); nrm.append(nms); wall.append((t1 - t0) * 1e3); iters.append(r["iterations"])
             perr = max(perr, float(np.abs(r["T"][:3, 3] - Tt[:3, 3]).max()))
-    clocks = clk.stop(t_mark0, time.time()) if clk else None
-    reg_ms, nrm_ms = max_over_ranks(torch, dist, [reg_ms, nrm_ms])
-    K = args.steps
-    emit(rank, dist, {
-        "metric": "GICP registrations/sec (128k scan vs 5M map, covariances from k=20 normals)",
-        "value": world * K / (reg_ms * 1e-3), "unit": "registrations/s", "n_gpus": world, "steps": K,
-        "warmup": args.warmup, "ms_per_step": reg_ms / K, "higher_is_better": True, "scaling": "weak",
-        "dtype": "f32 match / f64 linearisation", "data": "synthetic",
-        "config": {"workload": "C3", "map_points": args.map_points, "scan_points": args.scan_points,
-                   "iterations_per_step": iters, "max_abs_translation_error_vs_truth_m": perr,
-                   "scan_normals_k20_wall_ms_per_step_incl_h2d_d2h": nrm_ms / K,
-                   "map_normals_k20_wall_s_incl_h2d_d2h": normals_map_s,
-                   "timed": "H2D of scan + normals, 31 x (match+linearise, solve) launches; CUDA events"},
-        "clocks": clocks})
+            last = (s4, sn, Ti, r)
+    sidx.close()
+    ms = float(np.mean(reg))
+    # every update is preceded by a match+linearise pass, and one more evaluates the final pose
+    passes = float(np.mean(iters)) + 1.0
+    out = {"what": "C3: GICP (Open3D semantics), covariances from k = 20 normals, %d-pt scan vs %d-pt map, max corr. "
+                   "distance %.2f" % (N, M, md),
+           "ms": ms, "value": 1e3 / ms, "unit": "registrations/s", "registration_ms": stats(reg),
+           "scan_normals_k20_device_ms": stats(nrm), "map_normals_k20_device_ms_once": map_normals_ms,
+           "updates_per_registration": stats(iters), "max_abs_translation_error_vs_truth_m": perr,
+           "roofline": roofline("o3d_match_lin_kernel (GICP rows)", passes * N * B_GICP, ms, B_GICP),
+           "e2e": {"ms": float(np.mean(wall)), "value": 1e3 / float(np.mean(wall)), "unit": "registrations/s",
+                   "h2d_bytes_per_step": N * 16 * 2 + N * 12, "d2h_bytes_per_step": N * 12 + 200,
+                   "what": "host scan in: index update + k = 20 normals (copied back, oriented on the host, uploaded) + "
+                           "b200_o3d_register, host wall clock"}}
+    if ctx.with_cpu and last is not None:
+        from oracle import oracle_py as O
+        s4, sn, Ti, r = last
+        cores = os.cpu_count() or 1
+        t0 = time.perf_counter()
+        o = O.o3d_icp(2, s4, ref4, tgtn, sn, max_dist=md, init=Ti, max_iteration=30, threads=cores)
+        s = time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": 1.0 / s, "unit": "registrations/s", "cores": cores, "kind": "port", "ms": s * 1e3,
+                               "sample": "one GICP registration of the same scan incl. the kd-tree build over the map, "
+                                         "oracle (Open3D v0.15.1 restated), %d threads for the match" % cores}
+        out["parity"] = {"iterations_equal": bool(o["iterations"] == r["iterations"]),
+                         "max_abs_dT_vs_oracle": float(np.abs(o["T"] - r["T"]).max())}
     h.close()
+    return out
 
 
-# ------------------------------------------------------------------------------------------------------------ C4
-def run_c4(args):
-    torch, B, dist, rank, world, local = setup()
+# --------------------------------------------------------------------------------------------------- C4: submap pairs
+def mode_c4(ctx, warmup=3):
+    B, torch, args = ctx.B, ctx.torch, ctx.args
     from open3d_slam_private_b200 import batch, synth
     distinct = synth.make_c4(n_distinct=min(8, args.batch), N=args.pair_points)
-    hosts = []
-    for p in distinct:
-        hosts.append(dict(tgt=pinned_copy(synth.feat4(p["tgt_xyz"])), src=pinned_copy(synth.feat4(p["src_xyz"])),
-                          T_init=p["T_init"], T_true=p["T_true"]))
-    mine = batch.shard_round_robin(args.batch, rank, world)
-    h = B.O3dICP(kind=B.O3D_POINT_TO_PLANE, max_correspondence_distance=args.max_dist, max_iteration=30, device=local)
+    hosts = [dict(tgt=pinned(torch, synth.feat4(p["tgt_xyz"])), src=pinned(torch, synth.feat4(p["src_xyz"])),
+                  T_init=p["T_init"], T_true=p["T_true"]) for p in distinct]
+    mine = batch.shard_round_robin(args.batch, ctx.rank, ctx.world)
+    h = B.O3dICP(kind=B.O3D_POINT_TO_PLANE, max_correspondence_distance=args.max_dist, max_iteration=30, device=ctx.local)
 
     def one(idx):
         p = hosts[idx % len(hosts)]
-        tgt4, src4 = p["tgt"][1], p["src"][1]
-        h.set_target_estimate_normals(tgt4, knn=10, max_dist=2.0)   # loop-closure submaps arrive without normals
-        r = h.register(src4, init=p["T_init"])
-        return r, p
+        h.set_target_estimate_normals(p["tgt"][1], knn=10, max_dist=2.0)   # loop-closure submaps arrive without normals
+        return h.register(p["src"][1], init=p["T_init"]), p
 
-    for i in range(args.warmup):
+    for i in range(warmup):
         one(i)
-    if dist is not None:
-        dist.barrier()
-    torch.cuda.synchronize()
-    clk = ClockSampler(local) if rank == 0 else None
-    t_mark0 = time.time()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
+    ctx.barrier()
     t0 = time.perf_counter()
     reg_ms, iters, perr = 0.0, [], 0.0
     for idx in mine:
@@ -169,30 +257,49 @@ def run_c4(args):
         reg_ms += r["total_ms"]
         iters.append(r["iterations"])
         perr = max(perr, float(np.abs(r["T"][:3, 3] - p["T_true"][:3, 3]).max()))
-    ev1.record()
     torch.cuda.synchronize()
     wall_ms = (time.perf_counter() - t0) * 1e3
-    clocks = clk.stop(t_mark0, time.time()) if clk else None
-    wall_ms, reg_ms = max_over_ranks(torch, dist, [wall_ms, reg_ms])
-    emit(rank, dist, {
-        "metric": "submap-to-submap registrations/sec (batch sharded over GPUs, no collective)",
-        "value": args.batch / (wall_ms * 1e-3), "unit": "registrations/s", "n_gpus": world, "steps": args.batch,
-        "warmup": args.warmup, "ms_per_step": wall_ms / max(1, len(mine)), "higher_is_better": True, "scaling": "strong",
-        "dtype": "f32 match / f64 linearisation", "data": "synthetic",
-        "config": {"workload": "C4", "batch": args.batch, "points_per_submap": args.pair_points,
-                   "per_registration": "H2D both submaps, index build, k=10 normals of the target on its own index, point-to-plane ICP "
-                                       "(Open3D semantics), D2H result — wall clock per rank, max over ranks",
-                   "registration_only_ms_max_rank_total": reg_ms, "mean_iterations": float(np.mean(iters)),
-                   "max_abs_translation_error_vs_truth_m": perr},
-        "clocks": clocks})
+    wall_ms, reg_ms = ctx.max_over_ranks([wall_ms, reg_ms])
+    it_sum = float(np.sum(iters) + len(iters))
+    per = reg_ms / max(1, len(mine))
+    Np = args.pair_points
+    out = {"what": "C4: %d independent %d-vs-%d-point submap registrations (point-to-plane, Open3D semantics), round-robin "
+                   "over %d GPU(s), no collective" % (args.batch, Np, Np, ctx.world),
+           "ms": wall_ms / max(1, len(mine)), "value": args.batch / (wall_ms * 1e-3), "unit": "registrations/s",
+           "n_gpus": ctx.world, "scaling": "strong", "collective": "none",
+           "registration_only_ms": per, "mean_updates": float(np.mean(iters)),
+           "max_abs_translation_error_vs_truth_m": perr,
+           "roofline": roofline("o3d_match_lin_kernel (point-to-plane)", it_sum * Np * B_P2PLANE / max(1, len(mine)), per, B_P2PLANE),
+           "e2e": {"ms": wall_ms / max(1, len(mine)), "value": args.batch / (wall_ms * 1e-3), "unit": "registrations/s",
+                   "h2d_bytes_per_step": 2 * Np * 16, "d2h_bytes_per_step": 200,
+                   "what": "per pair: H2D both submaps, index build, k = 10 target normals on the device, registration, "
+                           "result back; host wall clock over the rank's share, max over ranks"}}
+    if ctx.with_cpu:
+        from oracle import oracle_py as O
+        p = distinct[0]
+        tgt4, src4 = synth.feat4(p["tgt_xyz"]), synth.feat4(p["src_xyz"])
+        cores = os.cpu_count() or 1
+        t0 = time.perf_counter()
+        st, on = O.surface_normals(tgt4, 10, 2.0)
+        n = on["normals"].astype(np.float64)
+        n /= np.maximum(np.linalg.norm(n, axis=1, keepdims=True), 1e-300)
+        n = oriented(n.astype(np.float32), tgt4)
+        o = O.o3d_icp(0, src4, tgt4, n, None, max_dist=args.max_dist, init=p["T_init"].astype(np.float64),
+                      max_iteration=30, threads=cores)
+        s = time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": 1.0 / s, "unit": "registrations/s", "cores": cores, "kind": "port", "ms": s * 1e3,
+                               "sample": "one pair: k = 10 normals of the target (one thread) + point-to-plane ICP (kd-tree "
+                                         "match on %d threads), oracle" % cores}
     h.close()
+    return out
 
 
-# ------------------------------------------------------------------------------------------------------------ C5
-def run_c5(args):
-    torch, B, dist, rank, world, local = setup()
+# --------------------------------------------------------------------------------------------------- C5: partitioned map
+def mode_c5(ctx, steps=16, warmup=3):
+    B, torch, args, dist = ctx.B, ctx.torch, ctx.args, ctx.dist
     from open3d_slam_private_b200 import partition as P
     from open3d_slam_private_b200 import synth
+    world, rank = ctx.world, ctx.rank
     street = synth.TiledStreet(world)
     halo = float(P.halo_width(args.max_dist, world * street.L))
     t0 = time.perf_counter()
@@ -205,56 +312,78 @@ def run_c5(args):
             dist.all_reduce(t, op=dist.ReduceOp.SUM)
     t0 = time.perf_counter()
     slab = P.SlabICP(synth.feat4(xyz), nrm, gid, 0, float(edges[rank]), float(edges[rank + 1]), kind=B.O3D_POINT_TO_PLANE,
-                     max_correspondence_distance=args.max_dist, max_iteration=30, device=local, allreduce=ar)
-    if dist is not None and args.exchange == "peer":
+                     max_correspondence_distance=args.max_dist, max_iteration=30, device=ctx.local, allreduce=ar)
+    peer = dist is not None and args.exchange == "peer"
+    if peer:
         slab.connect_peers(dist)
     build_s = time.perf_counter() - t0
-    scans = [(pinned_copy(synth.feat4(s["xyz"])), s["T_init"], s["T_true"])
-             for s in synth.make_c5_scans(street, args.poses, args.scan_points)]
-    clk = ClockSampler(local) if rank == 0 else None
-    reg_ms, iters, perr, owned, coll = 0.0, [], 0.0, [], 0
-    t_mark0 = None
-    for i in range(args.warmup + args.steps):
-        if i == args.warmup:
-            if dist is not None:
-                dist.barrier()
-            torch.cuda.synchronize()
-            t_mark0 = time.time()
+    N = args.scan_points
+    scans = [(pinned(torch, synth.feat4(s["xyz"])), s["T_init"], s["T_true"]) for s in synth.make_c5_scans(street, 4, N)]
+    reg, iters, perr, owned = [], [], 0.0, []
+    for i in range(warmup + steps):
+        if i == warmup:
+            ctx.barrier()
         (keep, s4), Ti, Tt = scans[i % len(scans)]
         r = slab.register(s4, init=Ti)
-        if i >= args.warmup:
-            reg_ms += r["total_ms"]
-            iters.append(r["iterations"])
-            coll += r["collectives"]
+        if i >= warmup:
+            reg.append(r["total_ms"]); iters.append(r["iterations"])
             perr = max(perr, float(np.abs(r["T"][:3, 3] - Tt[:3, 3]).max()))
-            owned.append(int((slab.correspondences()[0] != -2).sum()))
-    clocks = clk.stop(t_mark0, time.time()) if clk else None
-    (reg_ms,) = max_over_ranks(torch, dist, [reg_ms])
+            if len(owned) < len(scans):
+                owned.append(int((slab.correspondences()[0] != -2).sum()))
+    (tot,) = ctx.max_over_ranks([float(np.sum(reg))])
     own_all = [owned]
     if dist is not None:
         own_all = [None] * world
         dist.all_gather_object(own_all, owned)
-    K = args.steps
-    emit(rank, dist, {
-        "metric": "scan-to-map registrations/sec, map spatially partitioned over the GPUs (H/b summed over the ranks)",
-        "value": K / (reg_ms * 1e-3), "unit": "registrations/s", "n_gpus": world, "steps": K, "warmup": args.warmup,
-        "ms_per_step": reg_ms / K, "higher_is_better": True, "scaling": "weak (map grows with the ranks, one scan)",
-        "dtype": "f32 match / f64 linearisation", "data": "synthetic",
-        "config": {"workload": "C5", "map_points_total": world * args.tile_points, "map_points_per_rank": args.tile_points,
-                   "slab_points_rank0_incl_halo": int(gid.size), "scan_points": args.scan_points, "halo_m": halo,
-                   "iterations_per_step": iters, "collectives_per_step": coll / K,
-                   "owned_scan_points_per_rank_first_step": [o[0] if o else 0 for o in own_all],
-                   "max_abs_translation_error_vs_truth_m": perr, "slab_generation_s": gen_s,
-                   "slab_h2d_and_index_build_s": build_s,
-                   "exchange": args.exchange if dist is not None else "none",
-                   "timed": ("H2D of the scan, (match+linearise, exchange over peer memory + solve) per iteration, all "
-                             "iterations enqueued at once, no host polling; " if (dist is not None and args.exchange == "peer")
-                             else "H2D of the scan, (match+linearise, reduce, NCCL allreduce, solve) per iteration, polled "
-                                  "every 4 iterations; ") + "CUDA events on the launching stream, max over ranks"},
-        "clocks": clocks})
+    ms = tot / steps
+    passes = float(np.mean(iters)) + 1.0
+    out = {"what": "C5: %d-pt scan vs a %d-point map cut into %d x-slabs of %d points (+ halo %.2f m), one slab per GPU"
+                   % (N, world * args.tile_points, world, args.tile_points, halo),
+           "ms": ms, "value": 1e3 / ms, "unit": "registrations/s", "n_gpus": world, "scaling": "weak (the map grows with the ranks)",
+           "collective": ("32 doubles per iteration over NVLink peer memory inside o3d_exchange_solve_kernel (no NCCL)"
+                          if peer else ("NCCL allreduce(SUM) of 32 doubles per iteration" if dist is not None else "none")),
+           "updates_per_registration": stats(iters), "max_abs_translation_error_vs_truth_m": perr,
+           "owned_scan_points_per_rank": [o[0] if o else 0 for o in own_all],
+           "slab_generation_s": gen_s, "slab_h2d_and_index_build_s": build_s,
+           "roofline": roofline("o3d_match_lin_kernel (point-to-plane, owned points)", passes * N * B_P2PLANE, ms, B_P2PLANE),
+           "e2e": {"ms": ms, "value": 1e3 / ms, "unit": "registrations/s", "h2d_bytes_per_step": N * 16 + 128,
+                   "d2h_bytes_per_step": 200,
+                   "what": "H2D of the scan on every rank + all iterations + result; CUDA events on the launching stream, "
+                           "max over ranks"}}
     slab.close()
+    return out
+
+
+MODES = {"index_build": mode_index_build, "normals": mode_normals, "c3": mode_c3, "c4": mode_c4, "c5": mode_c5}
+
+
+def add_mode_args(ap):
+    ap.add_argument("--batch", type=int, default=256, help="c4: registrations in the batch")
+    ap.add_argument("--pair-points", type=int, default=200_000, help="c4: points per submap")
+    ap.add_argument("--tile-points", type=int, default=25_000_000, help="c5: map points per rank")
+    ap.add_argument("--max-dist", type=float, default=0.5, help="c3/c4/c5: max correspondence distance")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="c5: sums over NVLink peer memory inside the solve kernel, or an NCCL allreduce between kernels")
+
+
+def main():
+    import bench
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--mode", choices=sorted(MODES), required=True)
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--map-points", type=int, default=5_000_000)
+    ap.add_argument("--scan-points", type=int, default=131072)
+    ap.add_argument("--poses", type=int, default=4)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    add_mode_args(ap)
+    args = ap.parse_args()
+    ctx = bench.make_ctx(args)
+    out = MODES[args.mode](ctx)
+    if ctx.rank == 0:
+        print(json.dumps({"mode": args.mode, **out}))
+    if ctx.dist is not None:
+        ctx.dist.destroy_process_group()
 
 
 if __name__ == "__main__":
-    a = parse()
-    {"c3": run_c3, "c4": run_c4, "c5": run_c5}[a.mode](a)
+    main()

@@ -67,6 +67,9 @@ int b200_index_update(b200_index* idx, const float* ref4xM, const float* normals
  * of candidate points examined (Matcher::visitCounter). */
 int b200_index_knn(b200_index* idx, const float* query4xN, int N, int knn, float epsilon, float maxDist,
                    const float* maxDistPerPoint, int32_t* ids_kxN, float* dists_kxN, uint64_t* visit_count);
+/* measurement aid: CUDA-event time (ms) of the kernels of the last b200_index_knn / b200_index_self_normals call on
+ * this handle (host<->device copies excluded) */
+int b200_index_last_device_ms(const b200_index* idx, float* ms);
 /* build statistics: cell size, grid dims, occupied cells, build time (ms, device) */
 int b200_index_info(const b200_index* idx, float* cell_size, int32_t dims[3], int64_t* occupied_cells,
                     float* build_ms);

@@ -189,6 +189,11 @@ class Index:
                                               _fp(out["meanDists"])))
         return {k_: v for k_, v in out.items() if v is not None}
 
+    def last_device_ms(self):
+        ms = C.c_float()
+        _check(load().b200_index_last_device_ms(self.h, C.byref(ms)))
+        return ms.value
+
     def info(self):
         cell = C.c_float()
         dims = (C.c_int32 * 3)()

@@ -89,6 +89,9 @@ struct b200_index {
   // outputs of b200_index_self_normals (grown on demand, kept between calls)
   float* d_sn = nullptr;
   size_t cap_sn = 0;
+  // CUDA events around the kernels of the last b200_index_knn / b200_index_self_normals (b200_index_last_device_ms)
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+  float last_ms = 0.f;
 };
 
 extern "C" {
@@ -137,6 +140,8 @@ int b200_index_create(b200_index** out, int device, const float* ref4xM, const f
   if ((st = index_build(h->map, opts))) return fail(st);
   if (cudaMalloc(&h->d_visited, sizeof(unsigned long long)) != cudaSuccess)
     return fail(cuda_fail(cudaGetLastError(), "cudaMalloc", __FILE__, __LINE__));
+  for (int i = 0; i < 2; ++i)
+    if (cudaEventCreate(&h->ev[i]) != cudaSuccess) return fail(cuda_fail(cudaGetLastError(), "cudaEventCreate", __FILE__, __LINE__));
   *out = h;
   return B200_OK;
 }
@@ -162,6 +167,8 @@ void b200_index_destroy(b200_index* h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     cudaFree(h->d_q); cudaFree(h->d_ids); cudaFree(h->d_dists); cudaFree(h->d_mdpp); cudaFree(h->d_visited);
     cudaFree(h->d_sn);
+    for (int i = 0; i < 2; ++i)
+      if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     h->map.release();
     if (h->stream) cudaStreamDestroy(h->stream);
   }
@@ -199,14 +206,23 @@ int b200_index_knn(b200_index* h, const float* query4xN, int N, int knn, float e
   B200_TRY(h2d(h->d_q, query4xN, (size_t)N * sizeof(float4), s));
   if (maxDistPerPoint) B200_TRY(h2d(h->d_mdpp, maxDistPerPoint, (size_t)N * sizeof(float), s));
   B200_CUDA(cudaMemsetAsync(h->d_visited, 0, sizeof(unsigned long long), s));
+  B200_CUDA(cudaEventRecord(h->ev[0], s));
   B200_TRY(knn_device(h->map.view(), h->d_q, N, knn, maxDist, maxDistPerPoint ? h->d_mdpp : nullptr, h->d_ids,
                       h->d_dists, h->d_visited, s));
+  B200_CUDA(cudaEventRecord(h->ev[1], s));
   B200_TRY(d2h(ids, h->d_ids, (size_t)N * knn * sizeof(int32_t), s));
   B200_TRY(d2h(dists, h->d_dists, (size_t)N * knn * sizeof(float), s));
   unsigned long long vis = 0;
   B200_TRY(d2h(&vis, h->d_visited, sizeof(vis), s));
   B200_CUDA(cudaStreamSynchronize(s));
+  B200_CUDA(cudaEventElapsedTime(&h->last_ms, h->ev[0], h->ev[1]));
   if (visit_count) *visit_count = (uint64_t)vis;
+  return B200_OK;
+}
+
+int b200_index_last_device_ms(const b200_index* h, float* ms) {
+  if (!h || !ms) { set_error("b200_index_last_device_ms: bad arguments"); return B200_E_BAD_PARAM; }
+  *ms = h->last_ms;
   return B200_OK;
 }
 
@@ -261,12 +277,15 @@ int b200_index_self_normals(b200_index* h, const b200_surface_normal_params* prm
   float* dp[6];
   size_t off = 0;
   for (int i = 0; i < 6; ++i) { dp[i] = cnt[i] ? h->d_sn + off : nullptr; off += cnt[i]; }
+  B200_CUDA(cudaEventRecord(h->ev[0], s));
   B200_TRY(surface_normals_device(h->map.view(), h->map.d_ref, N, k, prm->maxDist, prm->sortEigen, dp[0], dp[1], dp[2],
                                   dp[3], dp[4], dp[5], s));
+  B200_CUDA(cudaEventRecord(h->ev[1], s));
   float* host[6] = {normals, densities, eigValues, eigVectors, matchedIds, meanDists};
   for (int i = 0; i < 6; ++i)
     if (host[i]) B200_TRY(d2h(host[i], dp[i], cnt[i] * sizeof(float), s));
   B200_CUDA(cudaStreamSynchronize(s));
+  B200_CUDA(cudaEventElapsedTime(&h->last_ms, h->ev[0], h->ev[1]));
   return B200_OK;
 }
 

@@ -179,8 +179,10 @@ def feat4(xyz):
     return out
 
 
-def make_c2(M=5_000_000, N=131072, n_poses=32, seed=SEED, scene_kw=None):
-    """BASELINE config C2: map (M points + normals), n_poses scans of N points with truth and initial guesses."""
+def make_c2(M=5_000_000, N=131072, n_poses=32, seed=SEED, scene_kw=None, only=None):
+    """BASELINE config C2: map (M points + normals), n_poses scans of N points with truth and initial guesses.
+    only: indices of the scans to ray-cast (the others are None) — several processes can share the work, every scan
+    is the same whoever makes it."""
     sc = Scene(seed=seed, **(scene_kw or {}))
     map_xyz, map_n = sc.sample_map(M)
     rng = np.random.default_rng(seed + 77)
@@ -188,6 +190,9 @@ def make_c2(M=5_000_000, N=131072, n_poses=32, seed=SEED, scene_kw=None):
     for i in range(n_poses):
         pose = (rng.uniform(-sc.length / 2 + 20, sc.length / 2 - 20), rng.uniform(-sc.width / 2 + 4, sc.width / 2 - 4),
                 rng.uniform(-np.pi, np.pi))
+        if only is not None and i not in only:
+            scans.append(None)
+            continue
         pts, T_true = sc.scan(pose, n_points=N, seed=i)
         T_init = T_true @ perturbation(i)
         scans.append(dict(xyz=pts, T_true=T_true, T_init=T_init.astype(np.float32)))
