@@ -55,7 +55,7 @@ struct BlockState {
   int coh;   // log2 of the run of consecutive scan points per warp in this iteration (query_of)
   float lim_prev, delta, lo, hi, dens, step_prev;
   unsigned limit_bits;
-  float H[36], b[6], x[6];
+  float H[36], b[6], x[6], x_spd[6];
   // X-ICP: pose that takes the matched points back to the frame the reading came in (ICP.cpp:2236)
   float TcInv[16], R9Inv[9];
   XicpState X;
@@ -1081,8 +1081,8 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
       __syncwarp();
       unsigned long long tsub[5] = {0ull, 0ull, 0ull, 0ull, 0ull};
       if (stamp) tsub[0] = gtimer();
-      bool fast = false;
-      if (S.P != 0 && p.minimizer == 0 && n_constr == 0) fast = solve6_warp(S.H, S.b, S.x, &s_red[1][0]);
+      int fast = 0;
+      if (S.P != 0 && p.minimizer == 0 && n_constr == 0) fast = solve6_warp(S.H, S.b, S.x, &s_red[1][0], S.x_spd);
       __syncwarp();
      if (lane == 0) {
       const double* a = s_tot;
@@ -1094,10 +1094,10 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
         S.iterate = 0;
       } else {
         if (p.minimizer == 0) {
-          if (fast) S.solve_info = 0;
+          if (fast == 1) S.solve_info = 0;
           else if (n_constr > 0)   // equality-constrained (KKT) system, PointToPlane.cpp:461-505
             xicp_solve(S.H, S.b, S.X, S.x, &S.solve_info, *reinterpret_cast<KktScratch*>(s_dyn));
-          else solve6_dev(S.H, S.b, S.x, &S.solve_info);  // rank-deficient / borderline systems: serial reference path
+          else solve6_dev(S.H, S.b, S.x, &S.solve_info, fast == 2 ? S.x_spd : nullptr);  // rank-deficient / borderline: serial reference path
           if (stamp) tsub[1] = gtimer();
           p2plane_T_dev(S.x, real);
         } else {

@@ -74,8 +74,21 @@ __device__ __forceinline__ float3 apply_R(const float* R9, float3 n) {
 
 // solvePossiblyUnderdeterminedLinearSystem(A, b, x, false) — PointToPlane.cpp:199-256.
 // info: 0 full rank, 1 rank-deficient minimal-norm, 2 double-SVD fallback.
-static __device__ __noinline__ void solve6_dev(const float* A, const float* b, float* x, int* info) {
-  const int rank = la::pivqr_rank<float, 6>(A);  // register-resident; the full factorisation only when needed
+// x_spd (nullable): A^-1 b from a double LDL^T of the symmetrised A whose pivots are well conditioned (solve6_warp
+// returned 2). It stands in for the reference's double-precision JacobiSVD fallback: for a symmetric positive definite
+// matrix with cond <= 1e9 both are backward-stable solves of the same system and agree to cond * eps_double <= 2e-7
+// relative, below the rounding of the cast to float that follows. (A scan far from the map's centroid makes the
+// rotation block of H dwarf the translation block, the reference's FLOAT full-pivot QR then calls the matrix rank
+// deficient, its minimal-norm solution fails the isApprox test and every iteration ends in that SVD: measured 110 us
+// per iteration as a serial double Jacobi SVD, on 5 of the 32 benchmark poses.)
+static __device__ __noinline__ void solve6_dev(const float* A, const float* b, float* x, int* info,
+                                               const float* x_spd = nullptr) {
+  // x_spd given: the warp replayed the float QR and found rank < 6, so go straight to the full factorisation (whose
+  // rank() is the same decision) instead of running the register-resident rank pass first
+  la::PivQR<float, 6> qr;
+  int rank;
+  if (x_spd) { qr.compute(A); rank = qr.rank(); }
+  else rank = la::pivqr_rank<float, 6>(A);
   double Ad[36], bd[6], xd[6];
   for (int i = 0; i < 36; ++i) Ad[i] = (double)A[i];
   for (int i = 0; i < 6; ++i) bd[i] = (double)b[i];
@@ -95,8 +108,7 @@ static __device__ __noinline__ void solve6_dev(const float* A, const float* b, f
     return;
   }
   *info = 1;
-  la::PivQR<float, 6> qr;
-  qr.compute(A);
+  if (!x_spd) qr.compute(A);
   if (rank == 0) {
     for (int i = 0; i < 6; ++i) x[i] = 0.f;
   } else {
@@ -156,8 +168,12 @@ static __device__ __noinline__ void solve6_dev(const float* A, const float* b, f
     e2 += (b[i] - ax) * (b[i] - ax); b2 += b[i] * b[i]; a2 += ax * ax;
   }
   if (!(e2 <= 1e-5f * 1e-5f * fminf(b2, a2))) {
-    la::svdSolve<double, 6>(Ad, bd, xd);
-    for (int i = 0; i < 6; ++i) x[i] = (float)xd[i];
+    if (x_spd) {
+      for (int i = 0; i < 6; ++i) x[i] = x_spd[i];
+    } else {
+      la::svdSolve<double, 6>(Ad, bd, xd);
+      for (int i = 0; i < 6; ++i) x[i] = (float)xd[i];
+    }
     *info = 2;
   }
 }
@@ -234,9 +250,12 @@ __device__ inline bool pivqr_full_rank6_warp(const float* A, float* Q) {
 // FullPivHouseholderQR (PointToPlane.cpp:202-203) finds full rank with an 8x margin. 1/d_k comes from a float seed
 // and three Newton steps in double (IEEE double division/sqrt are long dependent sequences here); against
 // cond(A) ~ 1e4..1e5 the ~1 ulp quotient error is ~1e-11 relative in x, invisible after the cast to float.
-// Returns false (x untouched) when the serial reference routine has to decide: certificate failed, asymmetric input.
+// Returns 1: x is final (full rank by the reference's criterion). 0: nothing decided, x untouched (asymmetric input or
+// a non-positive pivot): the serial reference routine decides. 2: the reference's float QR finds A rank deficient
+// (replayed exactly), but the double LDL^T went through with well-conditioned pivots (min d / max d > 1e-9): x_spd
+// receives A^-1 b for solve6_dev to use where the reference falls back to its double SVD; x untouched.
 // W: 98 doubles of shared memory. Must be called by all 32 lanes of one warp.
-__device__ inline bool solve6_warp(const float* A, const float* b, float* x, double* W) {
+__device__ inline int solve6_warp(const float* A, const float* b, float* x, double* W, float* x_spd = nullptr) {
   constexpr unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const int blk = (lane >> 3) & 1, j = lane & 7;   // block 0: A, block 1: A - s I
@@ -277,10 +296,18 @@ __device__ inline bool solve6_warp(const float* A, const float* b, float* x, dou
   }
   // block 0 must have factored; block 1 is only the certificate
   const bool good0 = __all_sync(FULL, good || blk == 1);
-  if (!good0) return false;
+  if (!good0) return 0;
+  bool full = true;
   if (!__all_sync(FULL, good)) {
     // certificate failed: replay the reference's rank decision exactly (work matrix after the two double blocks)
-    if (!pivqr_full_rank6_warp(A, reinterpret_cast<float*>(W + 80))) return false;
+    full = pivqr_full_rank6_warp(A, reinterpret_cast<float*>(W + 80));
+    if (!full) {
+      if (!x_spd) return 0;
+      double rmin = rinv[0], rmax = rinv[0];   // reciprocals of the pivots
+      for (int k = 1; k < 6; ++k) { rmin = fmin(rmin, rinv[k]); rmax = fmax(rmax, rinv[k]); }
+      if (!(rmin > 1e-9 * rmax)) return 0;
+      x = x_spd;
+    }
   }
   // substitutions on block 0: lane i owns component i
   double v = (lane < 6) ? (double)b[lane] : 0.0;
@@ -294,7 +321,8 @@ __device__ inline bool solve6_warp(const float* A, const float* b, float* x, dou
     if (lane < k) v -= W[k + 6 * lane] * xk;
   }
   if (lane < 6) x[lane] = (float)v;
-  return true;
+  __syncwarp();
+  return full ? 1 : 2;
 }
 
 // x -> 4x4 — PointToPlane.cpp:337-381 (6-DOF branch)

@@ -1,4 +1,4 @@
-// Self-test of the host-side C++ shims against pm_mirror.h. Without a CUDA device it checks that every module
+// Self-test of the host-side C++ shims against pm_mirror.h (a literal mirror of the reference's PointMatcher.h names). Without a CUDA device it checks that every module
 // fails loudly with the mapped exception (no CPU fallback); with a device it runs the modules on a small synthetic
 // cloud and checks them against a brute-force computation done right here.
 #include <array>
@@ -8,11 +8,12 @@
 #include <random>
 #include <utility>
 
+#include "pm_mirror.h"   // in the reference tree: #include "pointmatcher/PointMatcher.h"
 #include "b200_cloud_registration.hpp"
 #include "b200_pm_modules.hpp"
-#include "pm_mirror.h"
 
-using PM = pmmirror::PM;
+using PM = PointMatcher<float>;
+using PointMatcherSupport::Parametrizable;
 
 static int fails = 0;
 #define EXPECT(c) do { if (!(c)) { std::printf("FAIL %s:%d %s\n", __FILE__, __LINE__, #c); ++fails; } } while (0)
@@ -46,6 +47,82 @@ struct Cloud { std::vector<V3> points_, normals_; };
 struct M4 { double m[16]; double& operator()(int i, int j) { return m[i + 4 * j]; } const double& operator()(int i, int j) const { return m[i + 4 * j]; } };
 struct Result { M4 transformation_; std::vector<std::pair<int, int>> correspondence_set_; double fitness_ = 0, inlier_rmse_ = 0; };
 
+// The shims go through the reference's own plugin mechanism: ADD_TO_REGISTRAR lines (what INTEGRATION.md adds to
+// PointMatcher<T>::PointMatcher(), Registry.cpp:61-128), creation BY NAME with the parameter strings of
+// open3d_slam_ros/param/icp.yaml, the "was set but is not used" exception (Registrar.h:103-111) and the documented
+// bounds (Parametrizable.cpp:179-184). No device is needed for any of this.
+template <class T>
+struct Registered : PointMatcher<T> {
+  typedef PointMatcher<T> PM_;
+  typedef typename PM_::Matcher Matcher;
+  typedef typename PM_::DataPointsFilter DataPointsFilter;
+  typedef typename PM_::OutlierFilter OutlierFilter;
+  typedef typename PM_::ErrorMinimizer ErrorMinimizer;
+  using PM_::MatcherRegistrar; using PM_::DataPointsFilterRegistrar; using PM_::OutlierFilterRegistrar; using PM_::ErrorMinimizerRegistrar;
+  Registered() {
+    ADD_TO_REGISTRAR(Matcher, B200KDTreeMatcher, typename b200pm::B200KDTreeMatcher<PM_>)
+    ADD_TO_REGISTRAR(DataPointsFilter, B200SurfaceNormalDataPointsFilter, typename b200pm::B200SurfaceNormalDataPointsFilter<PM_>)
+    ADD_TO_REGISTRAR(OutlierFilter, B200MaxDistOutlierFilter, typename b200pm::B200MaxDistOutlierFilter<PM_>)
+    ADD_TO_REGISTRAR(OutlierFilter, B200MinDistOutlierFilter, typename b200pm::B200MinDistOutlierFilter<PM_>)
+    ADD_TO_REGISTRAR(OutlierFilter, B200MedianDistOutlierFilter, typename b200pm::B200MedianDistOutlierFilter<PM_>)
+    ADD_TO_REGISTRAR(OutlierFilter, B200TrimmedDistOutlierFilter, typename b200pm::B200TrimmedDistOutlierFilter<PM_>)
+    ADD_TO_REGISTRAR(OutlierFilter, B200SurfaceNormalOutlierFilter, typename b200pm::B200SurfaceNormalOutlierFilter<PM_>)
+    ADD_TO_REGISTRAR(ErrorMinimizer, B200PointToPlaneErrorMinimizer, typename b200pm::B200PointToPlaneErrorMinimizer<PM_>)
+    ADD_TO_REGISTRAR(ErrorMinimizer, B200PointToPointErrorMinimizer, typename b200pm::B200PointToPointErrorMinimizer<PM_>)
+  }
+};
+
+static const Registered<float>& registry() {
+  static Registered<float> r;
+  return r;
+}
+
+static int registrar_checks() {
+  int before = fails;
+  const Registered<float>& pm = registry();
+  // param/icp.yaml: matcher: KDTreeMatcher {knn: 1, maxDist: 0.5, epsilon: 0.01} with the B200 name
+  std::shared_ptr<PM::Matcher> m = pm.MatcherRegistrar.create("B200KDTreeMatcher", {{"knn", "1"}, {"maxDist", "0.5"}, {"epsilon", "0.01"}});
+  auto* km = dynamic_cast<b200pm::B200KDTreeMatcher<PM>*>(m.get());
+  EXPECT(km && km->knn == 1 && km->maxDist == 0.5f && km->epsilon == 0.01f && km->searchType == 1 && km->className == "B200KDTreeMatcher");
+  EXPECT(m->parametersUsed.count("knn") && m->parametersUsed.count("searchType") && m->parameters.at("maxDist") == "0.5");
+  // outlierFilters: TrimmedDistOutlierFilter {ratio: 0.90}, SurfaceNormalOutlierFilter {maxAngle: 1.57}
+  std::shared_ptr<PM::OutlierFilter> tf = pm.OutlierFilterRegistrar.create("B200TrimmedDistOutlierFilter", {{"ratio", "0.90"}});
+  EXPECT(dynamic_cast<b200pm::B200TrimmedDistOutlierFilter<PM>*>(tf.get()) && dynamic_cast<b200pm::B200DistOutlierFilter<PM>*>(tf.get())->param == 0.90f);
+  std::shared_ptr<PM::OutlierFilter> sf = pm.OutlierFilterRegistrar.create("B200SurfaceNormalOutlierFilter", {{"maxAngle", "1.57"}});
+  EXPECT(dynamic_cast<b200pm::B200SurfaceNormalOutlierFilter<PM>*>(sf.get())->maxAngle == 1.57f);
+  // errorMinimizer: PointToPlaneErrorMinimizer (no parameters); the Mapper's normal filter (Mapper.cpp:44-52)
+  std::shared_ptr<PM::ErrorMinimizer> em = pm.ErrorMinimizerRegistrar.create("B200PointToPlaneErrorMinimizer");
+  EXPECT(em && em->className == "B200PointToPlaneErrorMinimizer");
+  std::shared_ptr<PM::DataPointsFilter> nf = pm.DataPointsFilterRegistrar.create(
+      "B200SurfaceNormalDataPointsFilter", {{"knn", "10"}, {"epsilon", "0.03"}, {"keepNormals", "1"}, {"keepDensities", "1"}});
+  auto* nfp = dynamic_cast<b200pm::B200SurfaceNormalDataPointsFilter<PM>*>(nf.get());
+  EXPECT(nfp && nfp->knn == 10u && nfp->keepDensities && !nfp->keepEigenValues && nfp->epsilon == 0.03f);
+  EXPECT(pm.MatcherRegistrar.getDescription("B200KDTreeMatcher").find("B200") != std::string::npos);
+  EXPECT(pm.MatcherRegistrar.getDescriptor("B200KDTreeMatcher")->availableParameters().size() == 5);
+  // a parameter that no constructor reads: "was set but is not used" (Registrar.h:103-111)
+  bool threw = false;
+  try { pm.MatcherRegistrar.create("B200KDTreeMatcher", {{"knn", "1"}, {"bogusKey", "3"}}); }
+  catch (const Parametrizable::InvalidParameter& e) { threw = std::string(e.what()).find("was set but is not used") != std::string::npos; }
+  EXPECT(threw);
+  // documented bounds (Parametrizable.cpp:179-184): ratio above 1.0, knn below 3 for the normal filter
+  threw = false;
+  try { pm.OutlierFilterRegistrar.create("B200TrimmedDistOutlierFilter", {{"ratio", "1.5"}}); }
+  catch (const Parametrizable::InvalidParameter& e) { threw = std::string(e.what()).find("larger than maximum") != std::string::npos; }
+  EXPECT(threw);
+  threw = false;
+  try { pm.DataPointsFilterRegistrar.create("B200SurfaceNormalDataPointsFilter", {{"knn", "2"}}); }
+  catch (const Parametrizable::InvalidParameter& e) { threw = std::string(e.what()).find("smaller than minimum") != std::string::npos; }
+  EXPECT(threw);
+  threw = false;
+  try { pm.MatcherRegistrar.create("NoSuchMatcher"); } catch (const PointMatcherSupport::InvalidElement&) { threw = true; }
+  EXPECT(threw);
+  threw = false;   // accepted by the reference, refused loudly here
+  try { pm.ErrorMinimizerRegistrar.create("B200PointToPlaneErrorMinimizer", {{"force2D", "1"}}); }
+  catch (const Parametrizable::InvalidParameter&) { threw = true; }
+  EXPECT(threw);
+  return fails - before;
+}
+
 int main() {
   const int ndev = b200_device_count();
   std::printf("devices: %d\n", ndev);
@@ -59,13 +136,15 @@ int main() {
     try { b200pm::B200ICP<PM> icp; icp.initReference(ref); } catch (const std::runtime_error&) { threw = true; }
     EXPECT(threw);
     threw = false;
-    try { b200pm::B200KDTreeMatcher<PM> m({{"knn", "0"}}); } catch (const PM::InvalidParameter&) { threw = true; }
+    try { b200pm::B200KDTreeMatcher<PM> m(PM::Parameters{{"knn", "0"}}); } catch (const PM::InvalidParameter&) { threw = true; }   // below the documented minimum
     EXPECT(threw);
+    fails += registrar_checks();
     std::printf(fails ? "selftest FAILED\n" : "selftest ok (no device: loud failure verified)\n");
     return fails ? 1 : 0;
   }
+  registrar_checks();
   // ---- matcher vs brute force (bit-exact: same float arithmetic, ties -> smallest index)
-  b200pm::B200KDTreeMatcher<PM> matcher({{"knn", "3"}, {"maxDist", "0.5"}});
+  b200pm::B200KDTreeMatcher<PM> matcher(PM::Parameters{{"knn", "3"}, {"maxDist", "0.5"}});
   matcher.init(ref);
   PM::Matches m = matcher.findClosests(read);
   EXPECT(m.ids.rows() == 3 && m.ids.cols() == 1500 && matcher.visitCounter > 0);
@@ -91,17 +170,17 @@ int main() {
   }
   EXPECT(bad == 0);
   // ---- outlier filters
-  b200pm::B200TrimmedDistOutlierFilter<PM> trimmed({{"ratio", "0.8"}});
+  b200pm::B200TrimmedDistOutlierFilter<PM> trimmed(PM::Parameters{{"ratio", "0.8"}});
   PM::OutlierWeights w = trimmed.compute(read, ref, m);
   long kept = 0, valid = 0;
   for (int i = 0; i < 1500; ++i)
     for (int k = 0; k < 3; ++k) { kept += w(k, i) != 0.f; valid += std::isfinite(m.dists(k, i)); }
   EXPECT(kept > 0 && kept <= valid && kept >= (long)(0.78 * valid));
-  b200pm::B200MaxDistOutlierFilter<PM> maxd({{"maxDist", "0.2"}});
+  b200pm::B200MaxDistOutlierFilter<PM> maxd(PM::Parameters{{"maxDist", "0.2"}});
   PM::OutlierWeights w2 = maxd.compute(read, ref, m);
   for (int i = 0; i < 1500; i += 11) EXPECT((w2(0, i) != 0.f) == (m.dists(0, i) <= 0.04f));
   // ---- surface normals
-  b200pm::B200SurfaceNormalDataPointsFilter<PM> sn({{"knn", "10"}, {"keepDensities", "1"}});
+  b200pm::B200SurfaceNormalDataPointsFilter<PM> sn(PM::Parameters{{"knn", "10"}, {"keepDensities", "1"}});
   PM::DataPoints withN = sn.filter(read);
   EXPECT(withN.descriptorExists("normals") && withN.descriptorExists("densities") && withN.descriptors.rows() == 4);
   int upright = 0;
@@ -112,6 +191,40 @@ int main() {
   icp.prm.maxDist = 0.5f; icp.prm.trimmed_ratio = 0.9f;
   PM::TransformationParameters T = icp(read, ref);
   EXPECT(std::fabs(T(2, 3) + 0.08f) < 0.01f && icp.last.iterations > 1);
+  // the call Mapper.cpp:372-373 makes: compute(cloud, <unused>, init, false) on the reference set before
+  PM::TransformationParameters T2 = icp.compute(read, PM::DataPoints(), PM::TransformationParameters::Identity(4, 4), false);
+  int sameT = 0;
+  for (int i = 0; i < 16; ++i) sameT += T2.data()[i] == T.data()[i];
+  EXPECT(sameT == 16);
+  // ---- error minimiser with this fork's signature: A_ / b_ formed (here on the device), then solved by compute()
+  {
+    std::shared_ptr<PM::ErrorMinimizer> em = registry().ErrorMinimizerRegistrar.create("B200PointToPlaneErrorMinimizer");
+    auto* p2p = dynamic_cast<b200pm::B200PointToPlaneErrorMinimizer<PM>*>(em.get());
+    PM::ErrorMinimizer::ErrorElements ee;
+    PM::OutlierWeights wl0;
+    PM::Matches ml0 = icp.matches(&wl0);
+    int P = 0;
+    for (int i = 0; i < 1500; ++i) P += (wl0(0, i) != 0.f && ml0.ids(0, i) >= 0);
+    ee.reading.features.resize(4, P); ee.reference.features.resize(4, P); ee.weights.resize(1, P);
+    PM::Matrix nn(3, P);
+    for (int i = 0, c = 0; i < 1500; ++i) {
+      if (!(wl0(0, i) != 0.f && ml0.ids(0, i) >= 0)) continue;
+      const int j = ml0.ids(0, i);
+      for (int d = 0; d < 4; ++d) { ee.reading.features(d, c) = read.features(d, i); ee.reference.features(d, c) = ref.features(d, j); }
+      for (int d = 0; d < 3; ++d) nn(d, c) = ref.descriptors(d, j);
+      ee.weights(0, c) = 1.f;
+      ++c;
+    }
+    ee.reference.addDescriptor("normals", nn);
+    PM::LocalizabilityParametersForErrorMinimization lp;
+    p2p->accumulate(ee, lp);
+    PM::TransformationParameters Te = em->compute(ee, lp);
+    EXPECT(lp.A_(5, 5) > 0.f && std::fabs(Te(2, 3) + 0.08f) < 0.02f && p2p->solveInfo == 0);
+    lp.degeneracyAwarenessMethod = PM::DegeneracyAwarenessMethod::kOptimizedEqualityConstraints;
+    bool threwE = false;
+    try { em->compute(ee, lp); } catch (const Parametrizable::InvalidParameter&) { threwE = true; }
+    EXPECT(threwE);
+  }
   PM::OutlierWeights wl;
   PM::Matches ml = icp.matches(&wl);
   EXPECT(ml.ids.cols() == 1500 && wl.cols() == 1500);

@@ -257,3 +257,26 @@ def test_c5_slabs_equal_unpartitioned_10M(c5, n_slabs):
             assert (ref_ids != o["ids"]).mean() < 1e-3
     for h in hs + [whole]:
         h.close()
+
+
+def test_c2_far_pose_takes_the_svd_fallback_branch(c2):
+    """A scan 55 m from the map's centroid: the rotation block of H dwarfs the translation block, the reference's float
+    full-pivot QR calls H rank deficient in EVERY iteration, the minimal-norm solution fails isApprox and the double
+    SVD fallback solves (PointToPlane.cpp:199-246, info = 2). The device answers that branch from the double LDL^T it
+    already holds (solve.cuh): same iteration count, pose and one-step parity as every other pose."""
+    d = synth.make_c2(M=1000, N=131072, n_poses=17, only={16})
+    s = d["scans"][16]
+    r4, Ti = synth.feat4(s["xyz"]), s["T_init"]
+    p = c2_params()
+    o = c2["ses"].icp(p, r4, None, Ti)
+    infos = [O.solve6(o["H"][k], o["b"][k])[1] for k in range(o["iterations"])]
+    assert set(infos) == {2}, infos
+    icp = B.ICP(to_b(p))
+    icp.init_reference(c2["ref4"], c2["refn"])
+    g = icp.compute(r4, None, Ti, raise_on_error=False)
+    icp.inputs = (p, c2["ref4"], c2["refn"], r4, None, Ti)
+    icp.oracle_forced = lambda Ts: c2["ses"].icp(p, r4, None, Ti, forced_T_iters=Ts)
+    assert_icp_parity(o, g, icp)
+    st = icp.debug_stats()
+    assert st[1:g["iterations"], 5].max() < 80.0, st[:, 5]     # the solve no longer costs 110 us (serial Jacobi SVD)
+    icp.close()
