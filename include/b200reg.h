@@ -70,6 +70,9 @@ int b200_index_knn(b200_index* idx, const float* query4xN, int N, int knn, float
 /* measurement aid: CUDA-event time (ms) of the kernels of the last b200_index_knn / b200_index_self_normals call on
  * this handle (host<->device copies excluded) */
 int b200_index_last_device_ms(const b200_index* idx, float* ms);
+/* measurement aid: how many points of the last b200_index_self_normals call the cell-block tile kernel handed to the
+ * exact warp-cooperative kernel (k-th neighbour not provably inside the staged region, or a crowded region) */
+int b200_index_last_normals_fallback(b200_index* idx, int* n);
 /* build statistics: cell size, grid dims, occupied cells, build time (ms, device) */
 int b200_index_info(const b200_index* idx, float* cell_size, int32_t dims[3], int64_t* occupied_cells,
                     float* build_ms);
@@ -83,7 +86,7 @@ typedef struct {
   float maxDist;      /* default inf */
   float epsilon;      /* accepted, search is exact */
   int sortEigen;      /* 0/1 */
-  int smoothNormals;  /* 0/1 */
+  int smoothNormals;  /* 0/1 (SurfaceNormal.cpp:265-288: in place, in index order; knn <= 32) */
 } b200_surface_normal_params;
 
 int b200_surface_normals(int device, const float* feat4xN, int N, const b200_surface_normal_params* prm,

@@ -177,17 +177,22 @@ class Index:
         opts = IndexOpts(cell_size, target_per_cell, max_cells)
         _check(load().b200_index_update(self.h, _fp(self.ref4), _fp(self.normals), self.ref4.shape[0], C.byref(opts)))
 
-    def self_normals(self, knn=5, max_dist=np.inf, sort_eigen=0, keep=("normals",)):
+    def self_normals(self, knn=5, max_dist=np.inf, sort_eigen=0, keep=("normals",), smooth=0):
         """SurfaceNormalDataPointsFilter over the indexed cloud itself"""
         n = self.ref4.shape[0]
         shapes = dict(normals=(n, 3), densities=(n,), eigValues=(n, 3), eigVectors=(n, 9), matchedIds=(n, knn),
                       meanDists=(n,))
         out = {k_: (np.empty(shapes[k_], np.float32) if k_ in keep else None) for k_ in shapes}
-        prm = SurfaceNormalParams(knn, max_dist, 0.0, sort_eigen, 0)
+        prm = SurfaceNormalParams(knn, max_dist, 0.0, sort_eigen, smooth)
         _check(load().b200_index_self_normals(self.h, C.byref(prm), _fp(out["normals"]), _fp(out["densities"]),
                                               _fp(out["eigValues"]), _fp(out["eigVectors"]), _fp(out["matchedIds"]),
                                               _fp(out["meanDists"])))
         return {k_: v for k_, v in out.items() if v is not None}
+
+    def last_normals_fallback(self):
+        n = C.c_int()
+        _check(load().b200_index_last_normals_fallback(self.h, C.byref(n)))
+        return n.value
 
     def last_device_ms(self):
         ms = C.c_float()

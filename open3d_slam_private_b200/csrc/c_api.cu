@@ -4,6 +4,7 @@
 #include "common.cuh"
 #include "grid_index.cuh"
 #include "modules.cuh"
+#include "normals.cuh"
 #include "icp_kernel.cuh"
 #include "solve.cuh"
 #include <algorithm>
@@ -220,6 +221,12 @@ int b200_index_knn(b200_index* h, const float* query4xN, int N, int knn, float e
   return B200_OK;
 }
 
+int b200_index_last_normals_fallback(b200_index* h, int* n) {
+  if (!h || !n) { set_error("b200_index_last_normals_fallback: bad arguments"); return B200_E_BAD_PARAM; }
+  DeviceGuard dg(h->map.device);
+  return surface_normals_last_fallback(h->map, n, h->stream);
+}
+
 int b200_index_last_device_ms(const b200_index* h, float* ms) {
   if (!h || !ms) { set_error("b200_index_last_device_ms: bad arguments"); return B200_E_BAD_PARAM; }
   *ms = h->last_ms;
@@ -246,9 +253,8 @@ static int check_sn_params(const b200_surface_normal_params* prm) {
   if (!prm) { set_error("b200_surface_normals: bad arguments"); return B200_E_BAD_PARAM; }
   if (prm->knn < 3) { set_error("SurfaceNormalDataPointsFilter: knn must be >= 3"); return B200_E_BAD_PARAM; }
   if (prm->knn > 64) { set_error("SurfaceNormal knn > 64 is not supported"); return B200_E_UNSUPPORTED; }
-  if (prm->smoothNormals) {
-    // the reference smooths in place in index order (SurfaceNormal.cpp:265-288): inherently sequential
-    set_error("smoothNormals = 1 is not supported by the B200 filter");
+  if (prm->smoothNormals && prm->knn > 32) {   // the smoothing pass takes its neighbour ids from the k <= 32 kernels
+    set_error("smoothNormals = 1 with knn > 32 is not supported by the B200 filter");
     return B200_E_UNSUPPORTED;
   }
   return B200_OK;
@@ -264,6 +270,7 @@ int b200_index_self_normals(b200_index* h, const b200_surface_normal_params* prm
   if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
   cudaStream_t s = h->stream;
   // one grown-on-demand buffer, carved per requested output
+  if (prm->smoothNormals && !normals) { set_error("smoothNormals needs the normals output"); return B200_E_BAD_PARAM; }
   const size_t cnt[6] = {normals ? (size_t)3 * N : 0, densities ? (size_t)N : 0, eigValues ? (size_t)3 * N : 0,
                          eigVectors ? (size_t)9 * N : 0, matchedIds ? (size_t)k * N : 0, meanDists ? (size_t)N : 0};
   size_t total = 0;
@@ -278,8 +285,8 @@ int b200_index_self_normals(b200_index* h, const b200_surface_normal_params* prm
   size_t off = 0;
   for (int i = 0; i < 6; ++i) { dp[i] = cnt[i] ? h->d_sn + off : nullptr; off += cnt[i]; }
   B200_CUDA(cudaEventRecord(h->ev[0], s));
-  B200_TRY(surface_normals_device(h->map.view(), h->map.d_ref, N, k, prm->maxDist, prm->sortEigen, dp[0], dp[1], dp[2],
-                                  dp[3], dp[4], dp[5], s));
+  B200_TRY(surface_normals_index(h->map, h->map.d_ref, false, N, k, prm->maxDist, prm->sortEigen, prm->smoothNormals,
+                                 dp[0], dp[1], dp[2], dp[3], dp[4], dp[5], s));
   B200_CUDA(cudaEventRecord(h->ev[1], s));
   float* host[6] = {normals, densities, eigValues, eigVectors, matchedIds, meanDists};
   for (int i = 0; i < 6; ++i)

@@ -220,7 +220,9 @@ __global__ void subtract3_kernel(float4* __restrict__ p, int N, float mx, float 
 void MapIndex::release() {
   DeviceGuard dg(device);
   cudaFree(d_ref); cudaFree(d_nrm_orig); cudaFree(d_pts); cudaFree(d_nrm); cudaFree(d_A); cudaFree(d_tile);
-  cudaFree(d_scratch);
+  cudaFree(d_scratch); cudaFree(d_sn_list); cudaFree(d_sn_ids);
+  d_sn_list = d_sn_ids = nullptr;
+  cap_sn_list = cap_sn_ids = 0;
   d_ref = d_nrm_orig = d_pts = d_nrm = nullptr;
   d_A = d_tile = nullptr;
   d_scratch = nullptr;

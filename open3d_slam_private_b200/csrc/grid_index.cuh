@@ -19,6 +19,11 @@ struct MapIndex {
   uint32_t* d_tile = nullptr;     // scan scratch
   unsigned long long* d_scratch = nullptr;  // 8 x u64: bbox (6 ordered uints), occupied count
   size_t cap_cells = 0, cap_pts = 0, cap_tiles = 0;
+  // scratch of surface_normals_index (normals_tile.cu), grown on demand: fallback list (+ counter), neighbour ids and
+  // done flags of the smoothing pass
+  int* d_sn_list = nullptr;
+  int* d_sn_ids = nullptr;
+  size_t cap_sn_list = 0, cap_sn_ids = 0;
   // grid parameters
   float ox = 0, oy = 0, oz = 0, cell = 1.f, inv_cell = 1.f;
   int nx = 1, ny = 1, nz = 1;

@@ -1,6 +1,7 @@
 // Stand-alone module kernels (see modules.cuh). HBM-bound streaming / gather kernels; grids sized as multiples of
 // the SM count; per-thread partials reduced with warp shuffles and one fixed-order final pass (deterministic).
 #include "modules.cuh"
+#include "normals.cuh"
 #include "knn.cuh"
 #include "solve.cuh"
 #include <algorithm>
@@ -480,67 +481,6 @@ int rigid_apply_device(const float* T16, float4* feat, float* n3, int N, cudaStr
 // =================================================================================================================
 namespace {
 
-// eigen-analysis of one neighbourhood covariance and the descriptor outputs (one thread per point)
-__device__ __forceinline__ void sn_finish(int i, float4 q, const float* C, int realKnn, float maxSq, float mx, float my,
-                                          float mz, int sortEigen, float* __restrict__ normals,
-                                          float* __restrict__ dens, float* __restrict__ eigva,
-                                          float* __restrict__ eigve, float* __restrict__ meandist) {
-  la::PivQR<float, 3> qr;
-  qr.compute(C);
-  const bool degenerate = !(qr.rank() + 1 >= 3);   // :191
-  float va[3] = {0.f, 0.f, 0.f}, ve[9];
-#pragma unroll
-  for (int t = 0; t < 9; ++t) ve[t] = 0.f;
-  if (!degenerate) {
-    double Cd[9], wd[3], Vd[9];
-    for (int t = 0; t < 9; ++t) Cd[t] = (double)C[t];
-    la::symEigen3(Cd, wd, Vd);
-    float v0[3], e0[9];
-    for (int t = 0; t < 3; ++t) v0[t] = (float)wd[t];
-    for (int t = 0; t < 9; ++t) e0[t] = (float)Vd[t];
-    int idx[3] = {0, 1, 2};
-    if (sortEigen) {  // stable ascending (sortIndexes, :199-210)
-      if (v0[idx[1]] < v0[idx[0]]) { const int t = idx[0]; idx[0] = idx[1]; idx[1] = t; }
-      if (v0[idx[2]] < v0[idx[1]]) { const int t = idx[1]; idx[1] = idx[2]; idx[2] = t; }
-      if (v0[idx[1]] < v0[idx[0]]) { const int t = idx[0]; idx[0] = idx[1]; idx[1] = t; }
-    }
-    for (int c = 0; c < 3; ++c) {
-      va[c] = v0[idx[c]];
-      for (int r = 0; r < 3; ++r) ve[r + 3 * c] = e0[r + 3 * idx[c]];
-    }
-  }
-  if (normals) {
-    int col = 0;
-    if (!sortEigen) {  // computeNormal, utils.h:131-150
-      float best = FLT_MAX;
-      for (int j = 0; j < 3; ++j)
-        if (va[j] < best) { col = j; best = va[j]; }
-    }
-    for (int r = 0; r < 3; ++r) normals[3 * (size_t)i + r] = fminf(1.f, fmaxf(-1.f, ve[r + 3 * col]));
-  }
-  if (dens) {
-    float dv = 0.f;
-    if (!degenerate) {  // computeDensity, utils.h:105-129
-      const float volume = __fmul_rn(__fmul_rn((float)(4. / 3.), (float)M_PI), __fmul_rn(maxSq, sqrtf(maxSq)));
-      dv = volume > 0.f ? (float)realKnn / volume : 0.f;
-    }
-    dens[i] = dv;
-  }
-  if (eigva) for (int r = 0; r < 3; ++r) eigva[3 * (size_t)i + r] = va[r];
-  if (eigve)
-    for (int r = 0; r < 3; ++r)
-      for (int c = 0; c < 3; ++c) eigve[9 * (size_t)i + 3 * r + c] = ve[r + 3 * c];
-  if (meandist) {
-    float md;
-    if (degenerate) md = 18446744073709551615.0f;  // float(numeric_limits<size_t>::max()), :245
-    else {
-      const float dx = __fsub_rn(q.x, mx), dy = __fsub_rn(q.y, my), dz = __fsub_rn(q.z, mz);
-      md = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
-    }
-    meandist[i] = md;
-  }
-}
-
 template <int K>
 __global__ void __launch_bounds__(128) surface_normal_kernel(const __grid_constant__ GridView g,
                                                              const float4* __restrict__ feat, int N, int knn,
@@ -600,11 +540,16 @@ __global__ void __launch_bounds__(128) surface_normal_warp_kernel(const __grid_c
                                                                   float md2, int sortEigen, float* __restrict__ normals,
                                                                   float* __restrict__ dens, float* __restrict__ eigva,
                                                                   float* __restrict__ eigve, float* __restrict__ matched,
-                                                                  float* __restrict__ meandist) {
+                                                                  float* __restrict__ meandist,
+                                                                  const int* __restrict__ list,
+                                                                  const int* __restrict__ list_count,
+                                                                  int* __restrict__ ids_out, int out_by_id) {
   constexpr unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
   const int er = lane % 3, ec = (lane / 3) % 3;   // covariance entry of lanes 0..8 (column-major r + 3 c)
+  // list != null: only the points feat[list[0 .. *list_count)] (the ones the tile kernel could not settle)
+  if (list) N = *list_count;
   for (int base = warp * 32; base < N; base += nwarps * 32) {
     float Cm[9];
 #pragma unroll
@@ -613,8 +558,9 @@ __global__ void __launch_bounds__(128) surface_normal_warp_kernel(const __grid_c
     float m_maxSq = 0.f, m_mx = 0.f, m_my = 0.f, m_mz = 0.f;
     float4 m_q = make_float4(0.f, 0.f, 0.f, 1.f);
     const int cnt = min(32, N - base);
+    const int my_i = lane < cnt ? (list ? list[base + lane] : base + lane) : 0;
     for (int t = 0; t < cnt; ++t) {
-      const int i = base + t;
+      const int i = __shfl_sync(FULL, my_i, t);
       const float4 q = __ldg(&feat[i]);
       unsigned vis = 0;
       float d; int id, sp;
@@ -649,10 +595,13 @@ __global__ void __launch_bounds__(128) surface_normal_warp_kernel(const __grid_c
         if (lane == t) Cm[e] = v;
       }
       if (lane == t) { m_real = realKnn; m_maxSq = maxSq; m_mx = mx; m_my = my; m_mz = mz; m_q = q; }
-      if (matched && lane < knn) matched[(size_t)i * knn + lane] = (float)id;
+      // out_by_id: feat is the cell-sorted array (w = bits of the original index) and the outputs go to that index
+      const int io = out_by_id ? __float_as_int(q.w) : i;
+      if (matched && lane < knn) matched[(size_t)io * knn + lane] = (float)id;
+      if (ids_out && lane < knn) ids_out[(size_t)io * knn + lane] = id;   // -1 where there is no neighbour
     }
     if (lane < cnt)
-      sn_finish(base + lane, m_q, Cm, m_real, m_maxSq, m_mx, m_my, m_mz, sortEigen, normals, dens, eigva, eigve, meandist);
+      sn_finish(out_by_id ? __float_as_int(m_q.w) : my_i, m_q, Cm, m_real, m_maxSq, m_mx, m_my, m_mz, sortEigen, normals, dens, eigva, eigve, meandist);
   }
 }
 
@@ -676,7 +625,7 @@ int surface_normals_device(const GridView& g, const float4* feat, int N, int knn
     const long long chunks = ((long long)N + 31) / 32;   // one warp per 32 points, 4 warps per block
     const int blocks = (int)std::min<long long>((chunks + 3) / 4, 148LL * 32);
     surface_normal_warp_kernel<<<std::max(1, blocks), 128, 0, s>>>(g, feat, N, knn, md2, sortEigen, normals, dens, eigva,
-                                                                   eigve, matched, meandist);
+                                                                   eigve, matched, meandist, nullptr, nullptr, nullptr, 0);
     B200_CUDA(cudaGetLastError());
     return B200_OK;
   }
@@ -685,6 +634,20 @@ int surface_normals_device(const GridView& g, const float4* feat, int N, int knn
 #undef B200_SN
   set_error("SurfaceNormal knn > 64 is not supported by the B200 filter");
   return B200_E_UNSUPPORTED;
+}
+
+// the exact warp-cooperative path for a LIST of points (device-side count; see normals_tile.cu) or, with d_list ==
+// null, for all N points of feat; out_by_id: feat is the cell-sorted array and outputs are indexed by original index
+int surface_normals_list_device(const GridView& g, const float4* feat, const int* d_list, const int* d_count, int knn,
+                                float maxDist, int sortEigen, float* normals, float* dens, float* eigva, float* eigve,
+                                float* matched, float* meandist, int* ids_out, int out_by_id, int N, cudaStream_t s) {
+  const float md2 = std::isinf(maxDist) ? INFINITY : maxDist * maxDist;
+  int blocks = 148 * 8;
+  if (!d_list) blocks = (int)std::max<long long>(1, std::min<long long>((((long long)N + 31) / 32 + 3) / 4, 148LL * 32));
+  surface_normal_warp_kernel<<<blocks, 128, 0, s>>>(g, feat, N, knn, md2, sortEigen, normals, dens, eigva, eigve, matched,
+                                                    meandist, d_list, d_count, ids_out, out_by_id);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
 }
 
 }  // namespace b200

@@ -21,6 +21,7 @@
 #include "grid_index.cuh"
 #include "knn.cuh"
 #include "modules.cuh"
+#include "normals.cuh"
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -643,8 +644,8 @@ int b200_o3d_set_target_estimate_normals(b200_o3d* h, const float* tgt4xM, int M
   }
   // the target's own index answers the neighbour queries; queries in cell-sorted order, so the normals land where
   // the registration kernels read them (no second index, no host round trip)
-  B200_TRY(surface_normals_device(h->map.view(), h->map.d_pts, M, knn, maxDist, 0, h->d_nstage, nullptr, nullptr, nullptr,
-                                  nullptr, nullptr, s));
+  B200_TRY(surface_normals_index(h->map, h->map.d_pts, true, M, knn, maxDist, 0, 0, h->d_nstage, nullptr, nullptr, nullptr,
+                                 nullptr, nullptr, s));
   o3d_orient_normals_kernel<<<(M + kThreads - 1) / kThreads, kThreads, 0, s>>>(h->map.d_pts, h->d_nstage, M, h->map.d_nrm);
   B200_CUDA(cudaGetLastError());
   B200_CUDA(cudaStreamSynchronize(s));
