@@ -298,12 +298,25 @@ void b200_o3d_destroy(b200_o3d* h);
  * normals may be NULL for kind 1 */
 int b200_o3d_set_target(b200_o3d* h, const float* tgt4xM, const float* tgtn3xM, int M);
 /* target cloud WITHOUT normals: estimateNormalsOrCovariancesIfNeeded (CloudRegistration.cpp:67-79) runs on the device
- * against the target's own index -- knn neighbours within maxDist (IcpParameters::knn_, maxDistanceKnn_), normalised,
- * oriented towards the origin of the cloud's frame -- and the normals never leave the device */
+ * against the target's own index -- Open3D semantics as in b200_o3d_estimate_normals below (at most knn neighbours
+ * within maxDist, IcpParameters::knn_ / maxDistanceKnn_; 1 <= knn <= 32) -- and the normals never leave the device */
 int b200_o3d_set_target_estimate_normals(b200_o3d* h, const float* tgt4xM, int M, int knn, float maxDist);
+/* estimateNormalsOrCovariancesIfNeeded (CloudRegistration.cpp:27-46, 67-79) for a cloud that is not the target (the
+ * SOURCE of a generalized-ICP registration, or any cloud handed to the virtual): Open3D EstimateNormals with
+ * KDTreeSearchParamHybrid(radius, knn) — neighbourhood = at most knn nearest points within radius, the point itself
+ * included; covariance in double, normalised by the count; fewer than 3 neighbours -> (0, 0, 1) — then
+ * NormalizeNormals and OrientNormalsTowardsCameraLocation(origin). normals3xN: column-major doubles like Open3D's
+ * normals_. N = 0 returns B200_OK without touching anything (the reference does nothing for an empty cloud). */
+int b200_o3d_estimate_normals(b200_o3d* h, const float* pts4xN, int N, int knn, float radius, double* normals3xN);
 /* registerClouds(source, target, init); srcn3xN is required for kind 2 only */
 int b200_o3d_register(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16,
                       b200_o3d_result* res);
+/* registerClouds for a source WITHOUT normals (generalized ICP: estimateNormalsOrCovariancesIfNeeded would have run on
+ * it first, CloudRegistration.cpp:27-46): the source is indexed on the device, its normals are estimated there with
+ * the semantics of b200_o3d_estimate_normals and go straight into the registration — one H2D of the points, no host
+ * round trip of the normals. total_ms / device time of the result include the estimation. */
+int b200_o3d_register_estimate_normals(b200_o3d* h, const float* src4xN, int N, int knn, float radius,
+                                       const double* init16, b200_o3d_result* res);
 /* Spatially partitioned map: each device holds one slab of the map (padded by a halo of
  * max_correspondence_distance) as its target and answers only for the source points whose transformed coordinate along
  * `axis` lies in [lo, hi) -- exactly one owner per point, so the union of the slabs' correspondences is the

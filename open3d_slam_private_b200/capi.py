@@ -474,6 +474,15 @@ class O3dICP:
         tgt4 = f32(tgt4)
         _check(load().b200_o3d_set_target_estimate_normals(self._h, _fp(tgt4), tgt4.shape[0], int(knn), C.c_float(max_dist)))
 
+    def estimate_normals(self, pts4, knn=20, radius=1.0):
+        """estimateNormalsOrCovariancesIfNeeded for any cloud (Open3D EstimateNormals + normalise + orient): (N, 3) float64"""
+        pts4 = f32(pts4)
+        n = pts4.shape[0]
+        out = np.empty((n, 3), np.float64)
+        _check(load().b200_o3d_estimate_normals(self._h, _fp(pts4), n, int(knn), C.c_float(radius),
+                                                out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out
+
     def register(self, src4, normals=None, init=None):
         src4, normals = f32(src4), f32(normals)
         Ti = np.eye(4) if init is None else np.asarray(init, np.float64)
@@ -482,6 +491,19 @@ class O3dICP:
         self._n = src4.shape[0]
         _check(load().b200_o3d_register(self._h, _fp(src4), _fp(normals), self._n,
                                         Tc.ctypes.data_as(C.POINTER(C.c_double)), C.byref(r)))
+        return dict(T=np.array(r.T, np.float64).reshape(4, 4).T.copy(), fitness=r.fitness, inlier_rmse=r.inlier_rmse,
+                    iterations=r.iterations, n_correspondences=r.n_correspondences, device_ms=r.device_ms,
+                    total_ms=r.total_ms, kernel_launches=r.kernel_launches)
+
+    def register_estimate_normals(self, src4, knn=20, radius=1.0, init=None):
+        """registerClouds for a source without normals: estimated on the device (Open3D semantics), no host round trip"""
+        src4 = f32(src4)
+        Ti = np.eye(4) if init is None else np.asarray(init, np.float64)
+        Tc = np.ascontiguousarray(Ti.T).ravel()
+        r = O3dResult()
+        self._n = src4.shape[0]
+        _check(load().b200_o3d_register_estimate_normals(self._h, _fp(src4), self._n, int(knn), C.c_float(radius),
+                                                         Tc.ctypes.data_as(C.POINTER(C.c_double)), C.byref(r)))
         return dict(T=np.array(r.T, np.float64).reshape(4, 4).T.copy(), fitness=r.fitness, inlier_rmse=r.inlier_rmse,
                     iterations=r.iterations, n_correspondences=r.n_correspondences, device_ms=r.device_ms,
                     total_ms=r.total_ms, kernel_launches=r.kernel_launches)

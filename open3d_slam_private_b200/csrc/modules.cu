@@ -550,6 +550,7 @@ __global__ void __launch_bounds__(128) surface_normal_warp_kernel(const __grid_c
   const int er = lane % 3, ec = (lane / 3) % 3;   // covariance entry of lanes 0..8 (column-major r + 3 c)
   // list != null: only the points feat[list[0 .. *list_count)] (the ones the tile kernel could not settle)
   if (list) N = *list_count;
+  const bool want_stats = normals || dens || eigva || eigve || meandist;
   for (int base = warp * 32; base < N; base += nwarps * 32) {
     float Cm[9];
 #pragma unroll
@@ -565,6 +566,12 @@ __global__ void __launch_bounds__(128) surface_normal_warp_kernel(const __grid_c
       unsigned vis = 0;
       float d; int id, sp;
       knn_query_warpk(g, q.x, q.y, q.z, md2, knn, d, id, sp, vis);
+      if (!want_stats) {   // only the neighbour ids are wanted (normals_tile.cu: self_knn_ids_index)
+        const int io = out_by_id ? __float_as_int(q.w) : i;
+        if (matched && lane < knn) matched[(size_t)io * knn + lane] = (float)id;
+        if (ids_out && lane < knn) ids_out[(size_t)io * knn + lane] = id;
+        continue;
+      }
       const bool valid = lane < knn && d != INFINITY;
       const int realKnn = __popc(__ballot_sync(FULL, valid));   // a prefix of the lanes (the list is sorted)
       float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -600,7 +607,7 @@ __global__ void __launch_bounds__(128) surface_normal_warp_kernel(const __grid_c
       if (matched && lane < knn) matched[(size_t)io * knn + lane] = (float)id;
       if (ids_out && lane < knn) ids_out[(size_t)io * knn + lane] = id;   // -1 where there is no neighbour
     }
-    if (lane < cnt)
+    if (lane < cnt && want_stats)
       sn_finish(out_by_id ? __float_as_int(m_q.w) : my_i, m_q, Cm, m_real, m_maxSq, m_mx, m_my, m_mz, sortEigen, normals, dens, eigva, eigve, meandist);
   }
 }

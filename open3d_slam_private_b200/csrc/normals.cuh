@@ -17,6 +17,7 @@ int surface_normals_index(MapIndex& idx, const float4* feat, bool feat_sorted, i
                           float* matched, float* meandist, cudaStream_t s);
 
 int surface_normals_last_fallback(const MapIndex& idx, int* n, cudaStream_t s);
+int self_knn_ids_index(MapIndex& idx, int knn, float maxDist, bool out_sorted, int** ids_out, cudaStream_t s);
 
 // modules.cu
 int surface_normals_list_device(const GridView& g, const float4* feat, const int* d_list, const int* d_count, int knn,

@@ -370,6 +370,26 @@ int surface_normals_index(MapIndex& idx, const float4* feat, bool feat_sorted, i
   return B200_OK;
 }
 
+// k nearest neighbours of every indexed point among the indexed points (the point itself included), within maxDist:
+// ids (original indices, -1 = none) k per point, indexed by sorted position (out_sorted) or by original index.
+// *ids_out points into idx's scratch and stays valid until the next normals / ids call on idx.
+int self_knn_ids_index(MapIndex& idx, int knn, float maxDist, bool out_sorted, int** ids_out, cudaStream_t s) {
+  const int N = idx.M;
+  if (knn < 1 || knn > 32) { set_error("self_knn_ids_index: 1 <= knn <= 32"); return B200_E_UNSUPPORTED; }
+  const size_t need = (size_t)N * knn;
+  if (need > idx.cap_sn_ids) {
+    cudaFree(idx.d_sn_ids);
+    idx.d_sn_ids = nullptr; idx.cap_sn_ids = 0;
+    B200_CUDA(cudaMalloc(&idx.d_sn_ids, need * sizeof(int)));
+    idx.cap_sn_ids = need;
+  }
+  const GridView g = idx.view();
+  *ids_out = idx.d_sn_ids;
+  if (N == 0) return B200_OK;
+  return surface_normals_list_device(g, g.pts, nullptr, nullptr, knn, maxDist, 0, nullptr, nullptr, nullptr, nullptr,
+                                     nullptr, nullptr, idx.d_sn_ids, out_sorted ? 0 : 1, N, s);
+}
+
 // points the tile kernel handed to the exact path in the last call (diagnostics; synchronises the stream)
 int surface_normals_last_fallback(const MapIndex& idx, int* n, cudaStream_t s) {
   *n = 0;

@@ -477,19 +477,65 @@ __global__ void __launch_bounds__(kThreads) o3d_exchange_solve_kernel(const __gr
 }
 
 
-// estimateNormalsOrCovariancesIfNeeded's post-processing (CloudRegistration.cpp:67-79): NormalizeNormals, then
-// OrientNormalsTowardsCameraLocation with the camera at the origin of the cloud's frame; in double like the host
-__global__ void __launch_bounds__(kThreads) o3d_orient_normals_kernel(const float4* __restrict__ pts,
-                                                                      const float* __restrict__ n3, int M,
-                                                                      float4* __restrict__ out) {
+// Open3D v0.15.1 PointCloud::EstimateNormals(KDTreeSearchParamHybrid(radius, max_nn)) + NormalizeNormals +
+// OrientNormalsTowardsCameraLocation(origin), the sequence of estimateNormalsOrCovariancesIfNeeded
+// (CloudRegistration.cpp:27-46, 67-79). Open3D is not in the reference tree: restated from upstream —
+//   EstimatePerPointCovariances: neighbours = hybrid search (within radius, at most max_nn, the point itself
+//     included, nearest first); fewer than 3 -> covariance = Identity; else utility::ComputeCovariance: the nine
+//     cumulants (x, y, z, xx, xy, xz, yy, yz, zz) summed in DOUBLE in neighbour order, divided by the count,
+//     cov = E[p p^T] - E[p] E[p]^T;
+//   ComputeNormal: eigenvector of the smallest eigenvalue (Identity -> (0, 0, 1)); zero vector -> (0, 0, 1);
+//   NormalizeNormals; OrientNormalsTowardsCameraLocation(0): zero normal -> direction to the camera, else flipped when
+//     normal . (camera - point) < 0.
+// ids: k per point (original indices, nearest first, -1 = none) at row `j`; pts_by_id: the cloud in original order;
+// q: the points the rows belong to. Output: float4 at row j (registration kernels) and / or double 3 x N at out_d row.
+__global__ void __launch_bounds__(kThreads) o3d_estimate_normals_kernel(const int* __restrict__ ids, int knn,
+                                                                        const float4* __restrict__ pts_by_id,
+                                                                        const float4* __restrict__ q, int M,
+                                                                        float4* __restrict__ out4,
+                                                                        double* __restrict__ out_d, int out_by_id) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= M) return;
-  const float4 p = __ldg(&pts[j]);
-  double v[3] = {(double)n3[3 * (size_t)j], (double)n3[3 * (size_t)j + 1], (double)n3[3 * (size_t)j + 2]};
+  double cum[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  int n = 0;
+  for (int t = 0; t < knn; ++t) {
+    const int id = ids[(size_t)j * knn + t];
+    if (id < 0) continue;
+    const float4 p = __ldg(&pts_by_id[id]);
+    const double x = (double)p.x, y = (double)p.y, z = (double)p.z;
+    cum[0] += x; cum[1] += y; cum[2] += z;
+    cum[3] += x * x; cum[4] += x * y; cum[5] += x * z;
+    cum[6] += y * y; cum[7] += y * z; cum[8] += z * z;
+    ++n;
+  }
+  double v[3] = {0.0, 0.0, 1.0};
+  if (n >= 3) {
+    for (int t = 0; t < 9; ++t) cum[t] /= (double)n;
+    double C[9], w[3], V[9];
+    C[0] = cum[3] - cum[0] * cum[0];
+    C[4] = cum[6] - cum[1] * cum[1];
+    C[8] = cum[8] - cum[2] * cum[2];
+    C[1] = C[3] = cum[4] - cum[0] * cum[1];
+    C[2] = C[6] = cum[5] - cum[0] * cum[2];
+    C[5] = C[7] = cum[7] - cum[1] * cum[2];
+    la::symEigen3(C, w, V);
+    int c = 0;
+    if (w[1] < w[c]) c = 1;
+    if (w[2] < w[c]) c = 2;
+    v[0] = V[3 * c]; v[1] = V[3 * c + 1]; v[2] = V[3 * c + 2];
+    if (v[0] * v[0] + v[1] * v[1] + v[2] * v[2] == 0.0) { v[0] = 0.0; v[1] = 0.0; v[2] = 1.0; }
+  }
   const double nn = sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
   if (nn > 0.0) { v[0] /= nn; v[1] /= nn; v[2] /= nn; }
-  if (v[0] * (-(double)p.x) + v[1] * (-(double)p.y) + v[2] * (-(double)p.z) < 0.0) { v[0] = -v[0]; v[1] = -v[1]; v[2] = -v[2]; }
-  out[j] = make_float4((float)v[0], (float)v[1], (float)v[2], 0.f);
+  const float4 p = __ldg(&q[j]);
+  const double r[3] = {-(double)p.x, -(double)p.y, -(double)p.z};   // camera (origin) - point
+  if (v[0] * r[0] + v[1] * r[1] + v[2] * r[2] < 0.0) { v[0] = -v[0]; v[1] = -v[1]; v[2] = -v[2]; }
+  // out_by_id: q is the cell-sorted array (w = bits of the original index) and the outputs go to that index
+  const size_t o = out_by_id ? (size_t)__float_as_int(p.w) : (size_t)j;
+  if (out4) out4[o] = make_float4((float)v[0], (float)v[1], (float)v[2], 0.f);
+  if (out_d) {
+    out_d[3 * o] = v[0]; out_d[3 * o + 1] = v[1]; out_d[3 * o + 2] = v[2];
+  }
 }
 
 }  // namespace
@@ -499,6 +545,9 @@ struct b200_o3d {
   b200_o3d_params prm;
   cudaStream_t stream = nullptr;
   MapIndex map;
+  MapIndex nmap;               // scratch index of b200_o3d_estimate_normals
+  double* d_nd = nullptr;      // its double normals
+  size_t cap_nd = 0;
   bool target_ready = false;
   float4 *d_src = nullptr, *d_src_n = nullptr;
   float* d_stage3 = nullptr;
@@ -515,8 +564,6 @@ struct b200_o3d {
   int own_axis = -1;
   float own_lo = 0.f, own_hi = 0.f;
   int* d_gid = nullptr;
-  float* d_nstage = nullptr;   // 3 x M normals before orientation (set_target_estimate_normals)
-  size_t cap_nstage = 0;
   // stepwise run
   O3dParams p;
   int blocks = 0;
@@ -559,6 +606,7 @@ int b200_o3d_create(b200_o3d** out, int device, const b200_o3d_params* prm) {
   h->device = device;
   h->prm = *prm;
   h->map.device = device;
+  h->nmap.device = device;
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
   h->max_blocks = sms * 8;
@@ -566,6 +614,7 @@ int b200_o3d_create(b200_o3d** out, int device, const b200_o3d_params* prm) {
   cudaError_t e;
   if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail(e, "cudaStreamCreate");
   h->map.stream = h->stream;
+  h->nmap.stream = h->stream;
   if ((e = cudaMalloc(&h->d_partials, (size_t)h->max_blocks * kVals * sizeof(double))) != cudaSuccess) return fail(e, "cudaMalloc");
   if ((e = cudaMalloc(&h->d_state, sizeof(O3dState))) != cudaSuccess) return fail(e, "cudaMalloc");
   if ((e = cudaMallocHost(&h->h_state, sizeof(O3dState))) != cudaSuccess) return fail(e, "cudaMallocHost");
@@ -581,7 +630,7 @@ void b200_o3d_destroy(b200_o3d* h) {
     DeviceGuard dg(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     cudaFree(h->d_src); cudaFree(h->d_src_n); cudaFree(h->d_stage3); cudaFree(h->d_ids); cudaFree(h->d_dists);
-    cudaFree(h->d_partials); cudaFree(h->d_state); cudaFree(h->d_gid); cudaFree(h->d_nstage);
+    cudaFree(h->d_partials); cudaFree(h->d_state); cudaFree(h->d_gid);
     cudaFreeHost(h->h_state);
     for (int r = 0; r < kPeerMax; ++r)
       if (h->opened[r]) cudaIpcCloseMemHandle(h->opened[r]);
@@ -589,6 +638,8 @@ void b200_o3d_destroy(b200_o3d* h) {
     for (int i = 0; i < 3; ++i)
       if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     h->map.release();
+    h->nmap.release();
+    cudaFree(h->d_nd);
     if (h->stream) cudaStreamDestroy(h->stream);
   }
   delete h;
@@ -624,7 +675,7 @@ int b200_o3d_set_target(b200_o3d* h, const float* tgt4xM, const float* tgtn3xM, 
 
 int b200_o3d_set_target_estimate_normals(b200_o3d* h, const float* tgt4xM, int M, int knn, float maxDist) {
   if (!h || M <= 0 || !tgt4xM) { set_error("b200_o3d_set_target_estimate_normals: bad arguments"); return B200_E_BAD_PARAM; }
-  if (knn < 3 || knn > 64) { set_error("b200_o3d_set_target_estimate_normals: knn must be in 3..64"); return B200_E_BAD_PARAM; }
+  if (knn < 1 || knn > 32) { set_error("b200_o3d_set_target_estimate_normals: knn must be in 1..32"); return B200_E_BAD_PARAM; }
   DeviceGuard dg(h->device);
   if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
   h->target_ready = false;
@@ -636,23 +687,48 @@ int b200_o3d_set_target_estimate_normals(b200_o3d* h, const float* tgt4xM, int M
   std::memset(&opts, 0, sizeof(opts));
   opts.cell_size = h->prm.cell_size;
   B200_TRY(index_build(h->map, &opts));
-  if ((size_t)M > h->cap_nstage) {
-    cudaFree(h->d_nstage);
-    h->d_nstage = nullptr; h->cap_nstage = 0;
-    B200_CUDA(cudaMalloc(&h->d_nstage, (size_t)M * 3 * sizeof(float)));
-    h->cap_nstage = (size_t)M;
-  }
-  // the target's own index answers the neighbour queries; queries in cell-sorted order, so the normals land where
-  // the registration kernels read them (no second index, no host round trip)
-  B200_TRY(surface_normals_index(h->map, h->map.d_pts, true, M, knn, maxDist, 0, 0, h->d_nstage, nullptr, nullptr, nullptr,
-                                 nullptr, nullptr, s));
-  o3d_orient_normals_kernel<<<(M + kThreads - 1) / kThreads, kThreads, 0, s>>>(h->map.d_pts, h->d_nstage, M, h->map.d_nrm);
+  // the target's own index answers the neighbour queries; rows in cell-sorted order, so the normals land where the
+  // registration kernels read them (no second index, no host round trip)
+  int* ids = nullptr;
+  B200_TRY(self_knn_ids_index(h->map, knn, maxDist, true, &ids, s));
+  o3d_estimate_normals_kernel<<<(M + kThreads - 1) / kThreads, kThreads, 0, s>>>(ids, knn, h->map.d_ref, h->map.d_pts, M,
+                                                                                 h->map.d_nrm, nullptr, 0);
   B200_CUDA(cudaGetLastError());
   B200_CUDA(cudaStreamSynchronize(s));
   cudaFree(h->d_gid);
   h->d_gid = nullptr;
   h->own_axis = -1;
   h->target_ready = true;
+  return B200_OK;
+}
+
+int b200_o3d_estimate_normals(b200_o3d* h, const float* pts4xN, int N, int knn, float radius, double* normals3xN) {
+  if (!h || N < 0 || (N > 0 && (!pts4xN || !normals3xN))) { set_error("b200_o3d_estimate_normals: bad arguments"); return B200_E_BAD_PARAM; }
+  if (knn < 1 || knn > 32) { set_error("b200_o3d_estimate_normals: knn must be in 1..32"); return B200_E_BAD_PARAM; }
+  if (!(radius > 0.f)) { set_error("b200_o3d_estimate_normals: radius must be > 0"); return B200_E_BAD_PARAM; }
+  if (N == 0) return B200_OK;   // the reference returns without doing anything for an empty cloud
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  cudaStream_t s = h->stream;
+  // a scratch index of its own: the registration target stays untouched
+  B200_TRY(index_alloc_points(h->nmap, N, false));
+  B200_TRY(upload_features(h->nmap.d_ref, pts4xN, N, s));
+  b200_index_opts opts;
+  std::memset(&opts, 0, sizeof(opts));
+  B200_TRY(index_build(h->nmap, &opts));
+  int* ids = nullptr;
+  B200_TRY(self_knn_ids_index(h->nmap, knn, radius, true, &ids, s));
+  if ((size_t)N > h->cap_nd) {
+    cudaFree(h->d_nd);
+    h->d_nd = nullptr; h->cap_nd = 0;
+    B200_CUDA(cudaMalloc(&h->d_nd, (size_t)N * 3 * sizeof(double)));
+    h->cap_nd = (size_t)N;
+  }
+  o3d_estimate_normals_kernel<<<(N + kThreads - 1) / kThreads, kThreads, 0, s>>>(ids, knn, h->nmap.d_ref, h->nmap.d_pts, N,
+                                                                                 nullptr, h->d_nd, 1);
+  B200_CUDA(cudaGetLastError());
+  B200_CUDA(cudaMemcpyAsync(normals3xN, h->d_nd, (size_t)N * 3 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
   return B200_OK;
 }
 
@@ -673,10 +749,15 @@ int b200_o3d_set_partition(b200_o3d* h, int axis, float lo, float hi, const int3
   return B200_OK;
 }
 
-int b200_o3d_begin(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16, void* stream) {
+}  // extern "C"
+
+// est_knn > 0: the source normals are estimated on the device (Open3D semantics, o3d_estimate_normals_kernel) from a
+// scratch index over the uploaded source instead of being handed over
+static int o3d_begin_impl(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16,
+                          void* stream, int est_knn, float est_radius) {
   if (!h || N <= 0 || !src4xN) { set_error("b200_o3d_begin: bad arguments"); return B200_E_BAD_PARAM; }
   if (!h->target_ready) { set_error("b200_o3d: no target set"); return B200_E_NOT_INITIALIZED; }
-  if (h->prm.kind == 2 && !srcn3xN) { set_error("b200_o3d: generalized ICP needs source normals (covariances are derived from them)"); return B200_E_BAD_PARAM; }
+  if (h->prm.kind == 2 && !srcn3xN && est_knn <= 0) { set_error("b200_o3d: generalized ICP needs source normals (covariances are derived from them)"); return B200_E_BAD_PARAM; }
   DeviceGuard dg(h->device);
   if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
   cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
@@ -697,6 +778,23 @@ int b200_o3d_begin(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N
   B200_CUDA(cudaEventRecord(h->ev[0], s));
   B200_TRY(upload_features(h->d_src, src4xN, N, s));
   if (srcn3xN) B200_TRY(upload_normals(h->d_src_n, srcn3xN, N, h->d_stage3, s));
+  int est_launches = 0;
+  if (!srcn3xN && est_knn > 0) {
+    h->nmap.stream = s;
+    B200_TRY(index_alloc_points(h->nmap, N, false));
+    B200_CUDA(cudaMemcpyAsync(h->nmap.d_ref, h->d_src, (size_t)N * sizeof(float4), cudaMemcpyDeviceToDevice, s));
+    b200_index_opts opts;
+    std::memset(&opts, 0, sizeof(opts));
+    B200_TRY(index_build(h->nmap, &opts));
+    int* nids = nullptr;
+    B200_TRY(self_knn_ids_index(h->nmap, est_knn, est_radius, true, &nids, s));
+    o3d_estimate_normals_kernel<<<(N + kThreads - 1) / kThreads, kThreads, 0, s>>>(nids, est_knn, h->nmap.d_ref, h->nmap.d_pts,
+                                                                                   N, h->d_src_n, nullptr, 1);
+    B200_CUDA(cudaGetLastError());
+    h->nmap.stream = h->stream;
+    est_launches = 8;   // index build (bbox, 2 histograms, scan passes, scatter) + k-NN ids + normals
+  }
+  const bool have_n = srcn3xN || est_knn > 0;
   std::memset(h->h_state, 0, sizeof(O3dState));
   for (int i = 0; i < 16; ++i) h->h_state->T[i] = init16 ? init16[i] : ((i % 5 == 0) ? 1.0 : 0.0);
   B200_CUDA(cudaMemcpyAsync(h->d_state, h->h_state, sizeof(O3dState), cudaMemcpyHostToDevice, s));
@@ -704,7 +802,7 @@ int b200_o3d_begin(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N
   std::memset(&p, 0, sizeof(p));
   p.g = h->map.view();
   p.src = h->d_src;
-  p.src_n = srcn3xN ? h->d_src_n : nullptr;
+  p.src_n = have_n ? h->d_src_n : nullptr;
   p.N = N; p.kind = h->prm.kind;
   p.md2 = h->prm.max_correspondence_distance * h->prm.max_correspondence_distance;
   p.max_iteration = h->prm.max_iteration;
@@ -713,10 +811,16 @@ int b200_o3d_begin(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N
   p.own_axis = h->own_axis; p.own_lo = h->own_lo; p.own_hi = h->own_hi; p.gid = h->d_gid;
   h->blocks = std::max(1, std::min(h->max_blocks, (N + kThreads - 1) / kThreads));
   h->run_stream = s;
-  h->launches = srcn3xN ? 1 : 0;
+  h->launches = srcn3xN ? 1 : est_launches;
   B200_CUDA(cudaEventRecord(h->ev[1], s));
   h->running = true;
   return B200_OK;
+}
+
+extern "C" {
+
+int b200_o3d_begin(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16, void* stream) {
+  return o3d_begin_impl(h, src4xN, srcn3xN, N, init16, stream, 0, 0.f);
 }
 
 int b200_o3d_step_linearize(b200_o3d* h, double* d_sums32) {
@@ -876,11 +980,25 @@ int b200_o3d_finish(b200_o3d* h, b200_o3d_result* res) {
   return o3d_fill_result(h, res);
 }
 
+static int o3d_register_impl(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16,
+                             b200_o3d_result* res, int est_knn, float est_radius);
+
 int b200_o3d_register(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16,
                       b200_o3d_result* res) {
+  return o3d_register_impl(h, src4xN, srcn3xN, N, init16, res, 0, 0.f);
+}
+
+int b200_o3d_register_estimate_normals(b200_o3d* h, const float* src4xN, int N, int knn, float radius,
+                                       const double* init16, b200_o3d_result* res) {
+  if (knn < 1 || knn > 32 || !(radius > 0.f)) { set_error("b200_o3d_register_estimate_normals: 1 <= knn <= 32, radius > 0"); return B200_E_BAD_PARAM; }
+  return o3d_register_impl(h, src4xN, nullptr, N, init16, res, knn, radius);
+}
+
+static int o3d_register_impl(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16,
+                             b200_o3d_result* res, int est_knn, float est_radius) {
   if (!res) { set_error("b200_o3d_register: bad arguments"); return B200_E_BAD_PARAM; }
   if (h && h->own_axis >= 0) { set_error("b200_o3d_register: the target is one slab of a partitioned map; drive it with begin/step/finish"); return B200_E_BAD_PARAM; }
-  B200_TRY(b200_o3d_begin(h, src4xN, srcn3xN, N, init16, nullptr));
+  B200_TRY(o3d_begin_impl(h, src4xN, srcn3xN, N, init16, nullptr, est_knn, est_radius));
   DeviceGuard dg(h->device);
   // max_iteration updates need max_iteration + 1 matches. The iterations are enqueued kChunk at a time without any
   // host synchronisation inside a chunk; launches after `done` return at once, and the read-back of the state that

@@ -41,7 +41,7 @@ class RegistrationIcpB200 {
   int device_ = 0;
 
   RegistrationIcpB200() = default;
-  ~RegistrationIcpB200() { b200_o3d_destroy(h_); b200_index_destroy(nidx_); }
+  ~RegistrationIcpB200() { b200_o3d_destroy(h_); }
   RegistrationIcpB200(const RegistrationIcpB200&) = delete;
   RegistrationIcpB200& operator=(const RegistrationIcpB200&) = delete;
 
@@ -79,30 +79,22 @@ class RegistrationIcpB200 {
   }
   int lastIterations_ = 0;
 
-  // CloudRegistration::estimateNormalsOrCovariancesIfNeeded (CloudRegistration.cpp:27-46, 67-79): skip when the
-  // cloud has normals; else k-NN normals (hybrid radius = maxRadiusNormalEstimation_), normalised, flipped towards
-  // the origin (OrientNormalsTowardsCameraLocation with the default camera location).
+  // CloudRegistration::estimateNormalsOrCovariancesIfNeeded (CloudRegistration.cpp:27-46, 67-79): nothing when the
+  // cloud has normals or is empty; else Open3D's EstimateNormals(KDTreeSearchParamHybrid(maxRadiusNormalEstimation_,
+  // knnNormalEstimation_)) + NormalizeNormals + OrientNormalsTowardsCameraLocation on the device
+  // (b200_o3d_estimate_normals: double covariance normalised by the count, < 3 neighbours -> (0, 0, 1)).
   void estimateNormalsOrCovariancesIfNeeded(Cloud* cloud) {
-    if (!cloud || (cloud->normals_.size() == cloud->points_.size() && !cloud->points_.empty())) return;
+    if (!cloud || cloud->points_.empty()) return;
+    if (cloud->normals_.size() == cloud->points_.size()) return;   // HasNormals()
+    ensure();
     std::vector<float> f4;
     to_feat4(cloud->points_, f4);
     const int n = (int)cloud->points_.size();
-    std::vector<float> nrm(3 * (size_t)n);
-    b200_surface_normal_params prm;
-    prm.knn = knnNormalEstimation_; prm.maxDist = (float)maxRadiusNormalEstimation_; prm.epsilon = 0.f;
-    prm.sortEigen = 0; prm.smoothNormals = 0;
-    if (!nidx_) check(b200_index_create(&nidx_, device_, f4.data(), nullptr, n, nullptr));
-    else check(b200_index_update(nidx_, f4.data(), nullptr, n, nullptr));   // device buffers kept between scans
-    check(b200_index_self_normals(nidx_, &prm, nrm.data(), nullptr, nullptr, nullptr, nullptr, nullptr));
+    std::vector<double> nrm(3 * (size_t)n);
+    check(b200_o3d_estimate_normals(h_, f4.data(), n, knnNormalEstimation_, (float)maxRadiusNormalEstimation_, nrm.data()));
     cloud->normals_.resize(n);
-    for (int i = 0; i < n; ++i) {
-      double v[3] = {nrm[3 * i], nrm[3 * i + 1], nrm[3 * i + 2]};
-      const double nn = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
-      if (nn > 0) { v[0] /= nn; v[1] /= nn; v[2] /= nn; }
-      const auto& p = cloud->points_[i];
-      if (v[0] * (-p[0]) + v[1] * (-p[1]) + v[2] * (-p[2]) < 0) { v[0] = -v[0]; v[1] = -v[1]; v[2] = -v[2]; }
-      cloud->normals_[i][0] = v[0]; cloud->normals_[i][1] = v[1]; cloud->normals_[i][2] = v[2];
-    }
+    for (int i = 0; i < n; ++i)
+      for (int d = 0; d < 3; ++d) cloud->normals_[i][d] = nrm[3 * (size_t)i + d];
   }
 
  private:
@@ -132,7 +124,6 @@ class RegistrationIcpB200 {
     check(b200_o3d_create(&h_, device_, &p));
   }
   b200_o3d* h_ = nullptr;
-  b200_index* nidx_ = nullptr;
 };
 
 }  // namespace b200o3d

@@ -270,3 +270,65 @@ extern "C" int orc_o3d_icp(int kind, const float* src4xN, int N, const float* tg
   if (corr_ids) std::memcpy(corr_ids, ids.data(), sizeof(int32_t) * (size_t)N);
   return ORC_OK;
 }
+
+// ---- estimateNormalsOrCovariancesIfNeeded (CloudRegistration.cpp:27-46, 67-79) ---------------------------------------
+// Open3D v0.15.1 PointCloud::EstimateNormals(KDTreeSearchParamHybrid(radius, max_nn), fast = true),
+// NormalizeNormals, OrientNormalsTowardsCameraLocation(Zero) — RECALLED from upstream (geometry/EstimateNormals.cpp,
+// utility/Eigen.cpp ComputeCovariance, geometry/PointCloud.cpp): "parity unpinned" like the rest of this file.
+//   EstimatePerPointCovariances: indices = hybrid search around the point (itself included, nearest first, at most
+//     max_nn, within radius); size < 3 -> Identity; else cumulants (x y z xx xy xz yy yz zz) summed in double over
+//     the indices, divided by the count: cov = E[p p^T] - E[p] E[p]^T
+//   ComputeNormal: eigenvector of the smallest eigenvalue (FastEigen3x3; Identity -> (0,0,1)); zero -> (0,0,1)
+//   NormalizeNormals; orientation: zero normal -> direction to the camera ((0,0,1) when that is zero too), else
+//     flipped when normal . (camera - point) < 0
+// Stated deviations: the neighbour search runs on the float-converted points with the k-NN contract of knn.cpp
+// (Open3D searches the double points with FLANN); the eigenvector comes from a cyclic Jacobi iteration instead of
+// FastEigen3x3's closed form — both return the smallest eigenvector of the same matrix, they differ by rounding
+// and, for (near-)equal smallest eigenvalues, by the choice within the eigenspace (the tests exclude those points).
+extern "C" int orc_o3d_estimate_normals(const float* pts4xN, int N, int max_nn, float radius, int threads,
+                                        double* normals3xN, int32_t* n_neighbours) {
+  if (N < 0 || max_nn < 1 || !(radius > 0.f)) return ORC_E_BAD_PARAM;
+  if (N == 0) return ORC_OK;
+  std::vector<int32_t> ids((size_t)max_nn * N);
+  std::vector<float> dists((size_t)max_nn * N);
+  void* tree = orc_kdtree_build(pts4xN, N);
+  orc_kdtree_knn(tree, pts4xN, N, max_nn, radius, threads > 0 ? threads : 1, ids.data(), dists.data());
+  orc_kdtree_free(tree);
+  for (int i = 0; i < N; ++i) {
+    double cum[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    int n = 0;
+    for (int j = 0; j < max_nn; ++j) {
+      const int id = ids[(size_t)i * max_nn + j];
+      if (id < 0) continue;
+      const double x = pts4xN[4 * (size_t)id], y = pts4xN[4 * (size_t)id + 1], z = pts4xN[4 * (size_t)id + 2];
+      cum[0] += x; cum[1] += y; cum[2] += z;
+      cum[3] += x * x; cum[4] += x * y; cum[5] += x * z;
+      cum[6] += y * y; cum[7] += y * z; cum[8] += z * z;
+      ++n;
+    }
+    if (n_neighbours) n_neighbours[i] = n;
+    double v[3] = {0.0, 0.0, 1.0};
+    if (n >= 3) {
+      for (int t = 0; t < 9; ++t) cum[t] /= (double)n;
+      double C[9], w[3], V[9];
+      C[0] = cum[3] - cum[0] * cum[0];
+      C[4] = cum[6] - cum[1] * cum[1];
+      C[8] = cum[8] - cum[2] * cum[2];
+      C[1] = C[3] = cum[4] - cum[0] * cum[1];
+      C[2] = C[6] = cum[5] - cum[0] * cum[2];
+      C[5] = C[7] = cum[7] - cum[1] * cum[2];
+      orc::symEigen<double, 3>(C, w, V);
+      int c = 0;
+      if (w[1] < w[c]) c = 1;
+      if (w[2] < w[c]) c = 2;
+      v[0] = V[3 * c]; v[1] = V[3 * c + 1]; v[2] = V[3 * c + 2];
+      if (v[0] * v[0] + v[1] * v[1] + v[2] * v[2] == 0.0) { v[0] = 0.0; v[1] = 0.0; v[2] = 1.0; }
+    }
+    const double nn = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+    if (nn > 0.0) { v[0] /= nn; v[1] /= nn; v[2] /= nn; }
+    const double r[3] = {-(double)pts4xN[4 * (size_t)i], -(double)pts4xN[4 * (size_t)i + 1], -(double)pts4xN[4 * (size_t)i + 2]};
+    if (v[0] * r[0] + v[1] * r[1] + v[2] * r[2] < 0.0) { v[0] = -v[0]; v[1] = -v[1]; v[2] = -v[2]; }
+    normals3xN[3 * (size_t)i] = v[0]; normals3xN[3 * (size_t)i + 1] = v[1]; normals3xN[3 * (size_t)i + 2] = v[2];
+  }
+  return ORC_OK;
+}

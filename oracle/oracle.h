@@ -160,6 +160,12 @@ int orc_o3d_icp(int kind, const float* src4xN, int N, const float* tgt4xM, int M
                 int max_iteration, double rel_fitness, double rel_rmse, int knn_threads, double* T16, double* fitness,
                 double* rmse, int* iterations, int32_t* corr_ids);
 
+/* estimateNormalsOrCovariancesIfNeeded (CloudRegistration.cpp:27-46, 67-79): Open3D EstimateNormals with
+ * KDTreeSearchParamHybrid(radius, max_nn) + NormalizeNormals + OrientNormalsTowardsCameraLocation(origin), see o3d.cpp.
+ * normals3xN: doubles; n_neighbours (nullable): neighbourhood size per point */
+int orc_o3d_estimate_normals(const float* pts4xN, int N, int max_nn, float radius, int threads, double* normals3xN,
+                             int32_t* n_neighbours);
+
 /* ---- scan pre-processing (see prep.cpp): open3d_slam croppers (croppers.cpp:25-164) and Open3D
  * VoxelDownSample (recalled from upstream v0.15.1) ---- */
 int orc_crop(int kind, double radius_min, double radius_max, double min_z, double max_z, const double* center3,

@@ -384,6 +384,18 @@ def o3d_icp(kind, src4, tgt4, tgt_normals=None, src_normals=None, max_dist=1.0, 
                 iterations=it.value, ids=ids)
 
 
+def o3d_estimate_normals(pts4, knn=20, radius=1.0, threads=4):
+    """-> (normals (N,3) float64, neighbourhood sizes (N,) int32); see orc_o3d_estimate_normals"""
+    pts4 = f32(pts4)
+    n = pts4.shape[0]
+    out = np.empty((n, 3), np.float64)
+    cnt = np.empty(n, np.int32)
+    st = lib().orc_o3d_estimate_normals(_fp(pts4), n, int(knn), C.c_float(radius), int(threads),
+                                        out.ctypes.data_as(C.POINTER(C.c_double)), _ip(cnt))
+    assert st == ORC_OK, st
+    return out, cnt
+
+
 def crop(kind, pts4, radius_min=0.0, radius_max=0.0, min_z=0.0, max_z=0.0, center=(0.0, 0.0, 0.0), invert=False):
     """orc_crop -> indices of the kept points, input order (croppers.cpp:66-95)"""
     pts4 = f32(pts4)

@@ -193,11 +193,8 @@ def test_c4_submap_pair_parity():
     g = h.register(src4, init=init)
     ids, d = h.correspondences()
     h.close()
-    st, on = O.surface_normals(tgt4, 10, 2.0)
-    n = on["normals"].astype(np.float64)
-    n /= np.maximum(np.linalg.norm(n, axis=1, keepdims=True), 1e-300)
-    n = _oriented(n, tgt4)
-    o = O.o3d_icp(0, src4, tgt4, n, None, max_dist=0.5, init=init, max_iteration=30, threads=CPU)
+    n, _ = O.o3d_estimate_normals(tgt4, 10, 2.0, threads=CPU)    # Open3D EstimateNormals restated (oracle/o3d.cpp)
+    o = O.o3d_icp(0, src4, tgt4, n.astype(np.float32), None, max_dist=0.5, init=init, max_iteration=30, threads=CPU)
     assert g["iterations"] == o["iterations"]
     assert rot_angle(g["T"][:3, :3], o["T"][:3, :3]) < 1e-5
     assert np.abs(g["T"][:3, 3] - o["T"][:3, 3]).max() < 1e-5

@@ -165,3 +165,27 @@ def test_surface_normals_on_plane():
     assert st == 0
     assert (np.abs(out["normals"] @ n_true) > 1 - 1e-4).all()
     assert (out["ids"][:, 0] == np.arange(500)).all()  # self match first (ALLOW_SELF_MATCH)
+
+
+def test_o3d_estimate_normals_oracle_against_numpy(golden_dir):
+    """the oracle's Open3D EstimateNormals restatement (count-normalised double covariance of the hybrid neighbourhood,
+    smallest eigenvector, < 3 neighbours -> (0,0,1), oriented to the origin) against numpy on the same neighbourhoods"""
+    f = O.feat4(np.load(os.path.join(golden_dir, "car_cloud400.npz"))["xyz"])
+    f = np.concatenate([f, O.feat4(np.array([[50, 50, 50]], np.float32))])
+    n, cnt = O.o3d_estimate_normals(f, 10, 2.0)
+    ids, d = O.KdTree(f).knn(f, 10, 2.0, threads=4)
+    checked = 0
+    for i in range(0, f.shape[0] - 1, 41):
+        nb = f[ids[i][ids[i] >= 0]][:, :3].astype(np.float64)
+        assert cnt[i] == nb.shape[0] and ids[i, 0] == i          # the point itself is its first neighbour
+        if nb.shape[0] < 3:                                       # Identity covariance -> (0, 0, 1), then oriented
+            assert np.array_equal(np.abs(n[i]), [0.0, 0.0, 1.0])
+            continue
+        w, v = np.linalg.eigh(np.cov(nb.T, bias=True))
+        if (w[1] - w[0]) < 1e-6 * w[2]:
+            continue
+        e = v[:, 0] if v[:, 0] @ (-f[i, :3].astype(np.float64)) >= 0 else -v[:, 0]
+        assert np.abs(e - n[i]).max() < 1e-7
+        checked += 1
+    assert checked > 400
+    assert cnt[-1] == 1 and np.array_equal(n[-1], [0.0, 0.0, -1.0])
