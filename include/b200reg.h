@@ -388,6 +388,39 @@ int b200_prep_last_ordered_voxels(const b200_prep* h, int* n);
 /* device time of the last call's kernels (CUDA events, uploads and read-backs excluded) */
 int b200_prep_last_device_ms(const b200_prep* h, float* ms);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Map maintenance on the device — what open3d_slam does to the active submap between two
+ * registrations, with the map resident in HBM (stored as doubles like Open3D's points_ / normals_):
+ *   b200_map_insert_scan  = Submap::insertScan (open3d_slam/src/Submap.cpp:39-96): o3d_slam::transform of the scan by
+ *       mapToRangeSensor (helpers.cpp:283-318), mapCloud_ += scan, voxelizeWithinCroppingVolume (helpers.cpp:117-200):
+ *       points outside `crop` (the map-builder cropper, its centre set to the sensor position by the caller,
+ *       Submap.cpp:86) pass through in input order; the points inside are averaged per voxel floor(p / voxel_size)
+ *       (VoxelHashMap.hpp:48-51), normals averaged then normalised. New map = pass-through points, then the voxels
+ *       ordered by the index of their first member (the reference's order is that of an std::unordered_map).
+ *       voxel_size <= 0: the map is just the concatenation (helpers.cpp:121-124). An empty scan changes nothing.
+ *   b200_map_crop         = CroppingVolume::crop of the map (ScanToMapIcp::cropSubmap, ScanToMapRegistration.cpp:90-96)
+ *       as the float images of this header (open3dToPointmatcher's double -> float, open3d_conversions.cpp:57-118)
+ *   b200_map_crop_to_icp  = the same patch handed to ICP::initReference (Mapper.cpp:329-347) WITHOUT leaving the
+ *       device: cut straight into the registration handle's reference buffers, mean-centred and indexed there.
+ * Voxel membership, counts and the pass-through set are exact; voxel means are double atomics (unspecified order):
+ * equal to the reference's sequential sums to a few ulps.
+ * ---------------------------------------------------------------------------------------------------------- */
+typedef struct b200_map b200_map;
+int b200_map_create(b200_map** out, int device);
+void b200_map_destroy(b200_map* m);
+/* replace the map (mapCloud_ = cloud; e.g. the initial map, Submap.cpp:47-51); nrm3xM nullable; column-major doubles */
+int b200_map_set(b200_map* m, const double* pts3xM, const double* nrm3xM, int M);
+int b200_map_size(const b200_map* m, int* M, int* has_normals);
+int b200_map_download(b200_map* m, double* pts3xM, double* nrm3xM);
+/* scan: float images (4 x N features, 3 x N normals or NULL); T16: mapToRangeSensor, column-major double 4x4 */
+int b200_map_insert_scan(b200_map* m, const float* scan4xN, const float* scann3xN, int N, const double* T16,
+                         double voxel_size, const b200_crop_params* crop, int* n_outside, int* new_size);
+/* outputs have capacity b200_map_size points; any of them may be NULL; kept_idx = indices into the map */
+int b200_map_crop(b200_map* m, const b200_crop_params* crop, float* out4xK, float* outn3xK, int32_t* kept_idx, int* n_out);
+int b200_map_crop_to_icp(b200_map* m, const b200_crop_params* crop, b200_icp* icp, int* n_patch);
+/* device time of the kernels of the last insert_scan / crop_to_icp (uploads and read-backs excluded) */
+int b200_map_last_device_ms(const b200_map* m, float* ms);
+
 #ifdef __cplusplus
 }
 #endif

@@ -651,3 +651,79 @@ class Prep:
             self.close()
         except Exception:
             pass
+
+
+def crop_params(kind=0, radius_min=0.0, radius_max=0.0, min_z=0.0, max_z=0.0, center=(0.0, 0.0, 0.0), invert=False):
+    return CropParams(int(kind), int(bool(invert)), float(radius_min), float(radius_max), float(min_z), float(max_z),
+                      (C.c_double * 3)(*[float(v) for v in center]))
+
+
+class Map:
+    """Device-resident map (b200_map_*): Submap::insertScan, cropSubmap and the hand-over of the patch to an ICP
+    handle without the map crossing PCIe. Points / normals are (M, 3) float64 like Open3D's."""
+
+    def __init__(self, device=0):
+        require_device()
+        self._h = C.c_void_p()
+        _check(load().b200_map_create(C.byref(self._h), device))
+
+    @staticmethod
+    def _dp(a):
+        return None if a is None else a.ctypes.data_as(C.POINTER(C.c_double))
+
+    def set(self, pts3, normals3=None):
+        p = np.ascontiguousarray(pts3, np.float64)
+        n = None if normals3 is None else np.ascontiguousarray(normals3, np.float64)
+        _check(load().b200_map_set(self._h, self._dp(p), self._dp(n), p.shape[0]))
+
+    def size(self):
+        m, hn = C.c_int(), C.c_int()
+        _check(load().b200_map_size(self._h, C.byref(m), C.byref(hn)))
+        return m.value, bool(hn.value)
+
+    def download(self):
+        m, hn = self.size()
+        p = np.empty((m, 3), np.float64)
+        n = np.empty((m, 3), np.float64) if hn else None
+        _check(load().b200_map_download(self._h, self._dp(p), self._dp(n)))
+        return p, n
+
+    def insert_scan(self, scan4, scan_normals, T, voxel_size, crop):
+        """-> (points passed through, new map size)"""
+        scan4, scan_normals = f32(scan4), f32(scan_normals)
+        Tc = np.ascontiguousarray(np.asarray(T, np.float64).T).ravel()
+        no, ns = C.c_int(), C.c_int()
+        _check(load().b200_map_insert_scan(self._h, _fp(scan4), _fp(scan_normals), scan4.shape[0], self._dp(Tc),
+                                           C.c_double(voxel_size), C.byref(crop), C.byref(no), C.byref(ns)))
+        return no.value, ns.value
+
+    def crop(self, crop):
+        m, hn = self.size()
+        out = np.empty((max(m, 1), 4), np.float32)
+        outn = np.empty((max(m, 1), 3), np.float32) if hn else None
+        idx = np.empty(max(m, 1), np.int32)
+        k = C.c_int()
+        _check(load().b200_map_crop(self._h, C.byref(crop), _fp(out), _fp(outn), _ip(idx), C.byref(k)))
+        k = k.value
+        return out[:k].copy(), (None if outn is None else outn[:k].copy()), idx[:k].copy()
+
+    def crop_to_icp(self, crop, icp):
+        k = C.c_int()
+        _check(load().b200_map_crop_to_icp(self._h, C.byref(crop), icp.h, C.byref(k)))
+        return k.value
+
+    def last_device_ms(self):
+        ms = C.c_float()
+        _check(load().b200_map_last_device_ms(self._h, C.byref(ms)))
+        return ms.value
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            load().b200_map_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -14,6 +14,11 @@
 
 using namespace b200;
 
+namespace b200 {
+int icp_reference_from_device(b200_icp* h, int M, bool has_normals);
+float4* icp_reference_points(b200_icp* h, int M, bool with_normals, float4** normals_out, cudaStream_t* stream_out);
+}  // namespace b200
+
 namespace {
 
 constexpr int kMeanBlocks = 256;
@@ -446,7 +451,35 @@ int b200_icp_init_reference(b200_icp* h, const float* ref4xM, const float* refn3
     cudaFreeAsync(stage, s);
     if (st) return st;
   }
-  h->ref_has_normals = refn3xM != nullptr;
+  return icp_reference_from_device(h, M, refn3xM != nullptr);
+}
+
+}  // extern "C"
+
+namespace b200 {
+
+// buffers of the handle's index for a reference of M points that the caller fills ON THE DEVICE (map_maint.cu)
+float4* icp_reference_points(b200_icp* h, int M, bool with_normals, float4** normals_out, cudaStream_t* stream_out) {
+  DeviceGuard dg(h->device);
+  h->ref_ready = false;
+  if (index_alloc_points(h->map, M, with_normals) != B200_OK) return nullptr;
+  if (normals_out) *normals_out = with_normals ? h->map.d_nrm_orig : nullptr;
+  if (stream_out) *stream_out = h->stream;
+  return h->map.d_ref;
+}
+
+// the rest of ICP::initReference (ICP.cpp:847-898) on a reference resident in h->map.d_ref / d_nrm_orig:
+// mean-centre, build the index, store T_refIn_refMean
+int icp_reference_from_device(b200_icp* h, int M, bool has_normals) {
+  if (h->prm.minimizer == 0 && !has_normals) {  // InvalidField at getDescriptorViewByName("normals"), ICP.cpp:1519
+    set_error("PointToPlaneErrorMinimizer needs the 'normals' descriptor on the reference");
+    return B200_E_BAD_PARAM;
+  }
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  cudaStream_t s = h->stream;
+  h->ref_ready = false;
+  h->ref_has_normals = has_normals;
   // centroid in double, rounded to float; reference expressed in <refMean> (ICP.cpp:883-890)
   double mean[3];
   B200_TRY(device_mean3(h->map.d_ref, M, h->d_meanpart, mean, s));
@@ -466,6 +499,10 @@ int b200_icp_init_reference(b200_icp* h, const float* ref4xM, const float* refn3
   h->ref_ready = true;
   return B200_OK;
 }
+
+}  // namespace b200
+
+extern "C" {
 
 int b200_icp_compute(b200_icp* h, const float* read4xN, const float* readn3xN, int N, const float* Tinit16,
                      b200_icp_result* res) {

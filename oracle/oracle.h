@@ -173,6 +173,14 @@ int orc_crop(int kind, double radius_min, double radius_max, double min_z, doubl
 int orc_voxel_downsample(double voxel_size, const float* pts4xN, const float* nrm3xN, int N, double* out3xK,
                          double* outn3xK, int32_t* first_idx);
 
+/* map maintenance, Submap::insertScan (Submap.cpp:39-96) and the cropper on a double cloud; see prep.cpp */
+int orc_map_insert_scan(const double* map3xM, const double* mapn3xM, int M, const float* scan4xN, const float* scann3xN,
+                        int N, const double* T16, double voxel_size, int crop_kind, double radius_min, double radius_max,
+                        double min_z, double max_z, const double* center3, int invert, double* out3xK, double* outn3xK,
+                        int* n_outside);
+int orc_crop_d(int kind, double radius_min, double radius_max, double min_z, double max_z, const double* center3,
+               int invert, const double* pts3xN, int N, int32_t* kept_idx);
+
 /* the same split as the reference's initReference / compute (one reference, many readings) */
 void* orc_icp_ref_create(const float* ref4xM, const float* refn3xM, int M, int mean_mode);
 void orc_icp_ref_free(void* h);

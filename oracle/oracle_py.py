@@ -420,3 +420,38 @@ def voxel_downsample(voxel_size, pts4, normals=None):
     if k < 0:
         return k, None, None
     return out[:k].copy(), (None if outn is None else outn[:k].copy()), first[:k].copy()
+
+
+def map_insert_scan(map3, mapn3, scan4, scann3, T, voxel_size, kind=0, radius_min=0.0, radius_max=0.0, min_z=0.0,
+                    max_z=0.0, center=(0.0, 0.0, 0.0), invert=False):
+    """Submap::insertScan restated (orc_map_insert_scan) -> (points (K,3) f64, normals or None, n_outside)"""
+    dp = C.POINTER(C.c_double)
+    map3 = np.ascontiguousarray(map3, np.float64).reshape(-1, 3)
+    mapn3 = None if mapn3 is None else np.ascontiguousarray(mapn3, np.float64).reshape(-1, 3)
+    scan4, scann3 = f32(scan4), f32(scann3)
+    M, N = map3.shape[0], scan4.shape[0]
+    has_n = scann3 is not None
+    if has_n and mapn3 is None:
+        mapn3 = np.zeros((0, 3), np.float64)
+    out = np.empty((M + N, 3), np.float64)
+    outn = np.empty((M + N, 3), np.float64) if has_n else None
+    Tc = np.ascontiguousarray(np.asarray(T, np.float64).T).ravel()
+    c = (C.c_double * 3)(*[float(v) for v in center])
+    no = C.c_int()
+    lib().orc_map_insert_scan.restype = C.c_int
+    k = lib().orc_map_insert_scan(map3.ctypes.data_as(dp), None if mapn3 is None else mapn3.ctypes.data_as(dp), M,
+                                  _fp(scan4), _fp(scann3), N, Tc.ctypes.data_as(dp), C.c_double(voxel_size), int(kind),
+                                  C.c_double(radius_min), C.c_double(radius_max), C.c_double(min_z), C.c_double(max_z), c,
+                                  int(bool(invert)), out.ctypes.data_as(dp), None if outn is None else outn.ctypes.data_as(dp),
+                                  C.byref(no))
+    return out[:k].copy(), (None if outn is None else outn[:k].copy()), no.value
+
+
+def crop_d(kind, pts3, radius_min=0.0, radius_max=0.0, min_z=0.0, max_z=0.0, center=(0.0, 0.0, 0.0), invert=False):
+    pts3 = np.ascontiguousarray(pts3, np.float64)
+    n = pts3.shape[0]
+    idx = np.empty(max(n, 1), np.int32)
+    c = (C.c_double * 3)(*[float(v) for v in center])
+    k = lib().orc_crop_d(int(kind), C.c_double(radius_min), C.c_double(radius_max), C.c_double(min_z), C.c_double(max_z), c,
+                         int(bool(invert)), pts3.ctypes.data_as(C.POINTER(C.c_double)), n, _ip(idx))
+    return idx[:k].copy()
