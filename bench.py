@@ -59,7 +59,7 @@ def parse():
     ap.add_argument("--poses", type=int, default=32, help="distinct synthetic scans (cycled over the steps; SURVEY 8(d): 32)")
     ap.add_argument("--modes", default="auto",
                     help="comma list of bench_modes.py modes folded into the line under \"modes\" (index_build, normals, c3, "
-                         "c4, c5); auto: index_build,normals,c3,c4 on one GPU, c4,c5 on several; none: headline only")
+                         "c4, c5, map); auto: index_build,normals,c3,c4,map on one GPU, c4,c5 on several; none: headline only")
     import bench_modes
     bench_modes.add_mode_args(ap)
     ap.add_argument("--cpu-sample", type=int, default=3, help="registrations timed for the CPU baseline")
@@ -313,7 +313,7 @@ def mode_list(args, world):
     if args.modes == "none":
         return []
     if args.modes == "auto":
-        return ["index_build", "normals", "c3", "c4"] if world == 1 else ["c4", "c5"]
+        return ["index_build", "normals", "c3", "c4", "map"] if world == 1 else ["c4", "c5"]
     return [m for m in args.modes.split(",") if m]
 
 
