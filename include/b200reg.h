@@ -243,6 +243,13 @@ int b200_icp_init_reference(b200_icp* icp, const float* ref4xM, const float* ref
  * the call Mapper.cpp:372-373 makes. readn3xN may be NULL. Tinit16 NULL = identity (ICP::operator(), ICP.cpp:793). */
 int b200_icp_compute(b200_icp* icp, const float* read4xN, const float* readn3xN, int N, const float* Tinit16,
                      b200_icp_result* res);
+/* The same two calls taking Open3D clouds as they lie in memory (std::vector<Eigen::Vector3d>: 3 x N column-major
+ * DOUBLES; normals nullable): open3dToPointmatcher (open3d_utils/open3d_conversions/src/open3d_conversions.cpp:57-118),
+ * the per-point double -> float cast the Mapper runs on the host before every initReference / compute
+ * (Mapper.cpp:337-343 "This is time consuming"), happens on the device — the cloud crosses PCIe once, unconverted. */
+int b200_icp_init_reference_o3d(b200_icp* icp, const double* pts3xM, const double* nrm3xM, int M);
+int b200_icp_compute_o3d(b200_icp* icp, const double* pts3xN, const double* nrm3xN, int N, const float* Tinit16,
+                         b200_icp_result* res);
 /* Same registration with the reading already resident on the device (for kernel-only timing):
  * upload once, then run any number of times. */
 int b200_icp_upload_reading(b200_icp* icp, const float* read4xN, const float* readn3xN, int N);
@@ -317,6 +324,14 @@ int b200_o3d_register(b200_o3d* h, const float* src4xN, const float* srcn3xN, in
  * round trip of the normals. total_ms / device time of the result include the estimation. */
 int b200_o3d_register_estimate_normals(b200_o3d* h, const float* src4xN, int N, int knn, float radius,
                                        const double* init16, b200_o3d_result* res);
+/* Loop-closure constraint (first slice): open3d GetInformationMatrixFromPointClouds(source, target,
+ * max_correspondence_distance, T) as called at PlaceRecognition.cpp:148-149 (Open3D v0.15.1, not in the reference
+ * tree): correspondences = 1-NN of the transformed source in the handle's target within the distance; information =
+ * sum over them of G^T G with the rows G = [-[t]x | I] of the matched TARGET point t. info36: column-major 6x6 doubles.
+ * Also the fitness / inlier RMSE of that match (minRefinementFitness_ test, PlaceRecognition.cpp:118-128); nullable. */
+int b200_o3d_information_matrix(b200_o3d* h, const float* src4xN, int N, const double* T16,
+                                float max_correspondence_distance, double* info36, double* fitness, double* inlier_rmse,
+                                int* n_correspondences);
 /* Spatially partitioned map: each device holds one slab of the map (padded by a halo of
  * max_correspondence_distance) as its target and answers only for the source points whose transformed coordinate along
  * `axis` lies in [lo, hi) -- exactly one owner per point, so the union of the slabs' correspondences is the
@@ -376,6 +391,14 @@ typedef struct {
  * Outputs have capacity N; *n_out receives the number kept. */
 int b200_prep_crop(b200_prep* h, const b200_crop_params* prm, const float* pts4xN, const float* nrm3xN, int N,
                    float* out4xN, float* outn3xN, int32_t* kept_idx, int* n_out);
+/* o3d_slam::randomDownSample (helpers.cpp:100-106; ScanToMapRegistration.cpp:44,54, Odometry.cpp:26) -> open3d
+ * PointCloud::RandomDownSample(ratio): size_t(ratio * N) points drawn without replacement (Open3D shuffles with an
+ * mt19937 seeded from std::random_device, so the reference's own choice is not reproducible); ratio >= 1 leaves the
+ * cloud as it is (helpers.cpp:101-103), ratio <= 0 is Open3D's "sampling_ratio must lie in (0, 1]" error. Here the
+ * sample is the size_t(ratio * N) points with the smallest keys of a bijective 32-bit hash of (index, seed): uniform,
+ * reproducible for a given seed; output in input order. */
+int b200_prep_random_downsample(b200_prep* h, double ratio, uint32_t seed, const float* pts4xN, const float* nrm3xN, int N,
+                                float* out4xN, float* outn3xN, int32_t* kept_idx, int* n_out);
 /* o3d_slam::voxelize (helpers.cpp:108-115) -> open3d PointCloud::VoxelDownSample(voxel_size) (Open3D v0.15.1, not in
  * the reference tree): voxel index floor((p - (min_bound - voxel_size / 2)) / voxel_size), points and normals of a
  * voxel averaged in double in input order. Output (capacity N, column-major 3 x K doubles like Open3D's points_) is

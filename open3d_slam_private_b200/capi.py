@@ -381,6 +381,25 @@ class ICP:
         st = load().b200_icp_compute(self.h, _fp(read4), _fp(normals), self._n, _fp(Tc), C.byref(res))
         return self._result(res, st, raise_on_error)
 
+    def init_reference_o3d(self, pts3, normals3=None):
+        """Open3D double clouds (N, 3) float64 straight in: open3dToPointmatcher's cast happens on the device"""
+        dp = C.POINTER(C.c_double)
+        self._p3 = np.ascontiguousarray(pts3, np.float64)
+        self._n3 = None if normals3 is None else np.ascontiguousarray(normals3, np.float64)
+        _check(load().b200_icp_init_reference_o3d(self.h, self._p3.ctypes.data_as(dp),
+                                                  None if self._n3 is None else self._n3.ctypes.data_as(dp), self._p3.shape[0]))
+
+    def compute_o3d(self, pts3, normals3=None, T_init=None, raise_on_error=True):
+        dp = C.POINTER(C.c_double)
+        p = np.ascontiguousarray(pts3, np.float64)
+        n = None if normals3 is None else np.ascontiguousarray(normals3, np.float64)
+        self._n = p.shape[0]
+        Tc = None if T_init is None else _colmajor(T_init)
+        res = IcpResult()
+        st = load().b200_icp_compute_o3d(self.h, p.ctypes.data_as(dp), None if n is None else n.ctypes.data_as(dp), self._n,
+                                         _fp(Tc), C.byref(res))
+        return self._result(res, st, raise_on_error)
+
     def upload_reading(self, read4, normals=None):
         read4, normals = f32(read4), f32(normals)
         self._n = read4.shape[0]
@@ -494,6 +513,19 @@ class O3dICP:
         return dict(T=np.array(r.T, np.float64).reshape(4, 4).T.copy(), fitness=r.fitness, inlier_rmse=r.inlier_rmse,
                     iterations=r.iterations, n_correspondences=r.n_correspondences, device_ms=r.device_ms,
                     total_ms=r.total_ms, kernel_launches=r.kernel_launches)
+
+    def information_matrix(self, src4, T, max_correspondence_distance):
+        """GetInformationMatrixFromPointClouds against the handle's target -> (6x6 float64, fitness, rmse, n_corr)"""
+        src4 = f32(src4)
+        Tc = np.ascontiguousarray(np.asarray(T, np.float64).T).ravel()
+        info = np.empty(36, np.float64)
+        fit, rmse, n = C.c_double(), C.c_double(), C.c_int()
+        dp = C.POINTER(C.c_double)
+        _check(load().b200_o3d_information_matrix(self._h, _fp(src4), src4.shape[0], Tc.ctypes.data_as(dp),
+                                                  C.c_float(max_correspondence_distance), info.ctypes.data_as(dp),
+                                                  C.byref(fit), C.byref(rmse), C.byref(n)))
+        self._n = src4.shape[0]
+        return info.reshape(6, 6).T.copy(), fit.value, rmse.value, n.value
 
     def register_estimate_normals(self, src4, knn=20, radius=1.0, init=None):
         """registerClouds for a source without normals: estimated on the device (Open3D semantics), no host round trip"""
@@ -613,6 +645,19 @@ class Prep:
         k = C.c_int()
         _check(load().b200_prep_crop(self._h, C.byref(prm), _fp(pts4), _fp(normals), n, _fp(out), _fp(outn), _ip(idx),
                                      C.byref(k)))
+        k = k.value
+        return out[:k].copy(), (None if outn is None else outn[:k].copy()), idx[:k].copy()
+
+    def random_downsample(self, ratio, pts4, normals=None, seed=0):
+        """-> (points K x 4, normals K x 3 or None, kept indices K int32), K = int(ratio * N)"""
+        pts4, normals = f32(pts4), f32(normals)
+        n = pts4.shape[0]
+        out = np.empty((max(n, 1), 4), np.float32)
+        outn = np.empty((max(n, 1), 3), np.float32) if normals is not None else None
+        idx = np.empty(max(n, 1), np.int32)
+        k = C.c_int()
+        _check(load().b200_prep_random_downsample(self._h, C.c_double(ratio), C.c_uint32(seed), _fp(pts4), _fp(normals), n,
+                                                  _fp(out), _fp(outn), _ip(idx), C.byref(k)))
         k = k.value
         return out[:k].copy(), (None if outn is None else outn[:k].copy()), idx[:k].copy()
 

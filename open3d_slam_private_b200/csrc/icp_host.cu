@@ -103,6 +103,17 @@ __global__ void prepare_reading_kernel(const float4* __restrict__ raw, const flo
   }
 }
 
+// open3dToPointmatcher (open3d_utils/open3d_conversions/src/open3d_conversions.cpp:57-118): features(r, i) =
+// float(points_[i][r]), normals.col(i) = normals_[i].cast<float>() — done on the device, the cloud crosses PCIe once
+// as it lies in Open3D's std::vector<Eigen::Vector3d>
+__global__ void pack_o3d_kernel(const double* __restrict__ p3, const double* __restrict__ n3, int N,
+                                float4* __restrict__ out, float4* __restrict__ outn) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+    out[i] = make_float4((float)p3[3 * (size_t)i], (float)p3[3 * (size_t)i + 1], (float)p3[3 * (size_t)i + 2], 1.f);
+    if (n3) outn[i] = make_float4((float)n3[3 * (size_t)i], (float)n3[3 * (size_t)i + 1], (float)n3[3 * (size_t)i + 2], 0.f);
+  }
+}
+
 __global__ void flush_kernel(float4* __restrict__ buf, size_t n, float v) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     buf[i] = make_float4(v, v, v, v);
@@ -145,6 +156,8 @@ struct b200_icp {
   int upload_launches = 0;
   float4* d_flush = nullptr;
   size_t flush_elems = 0;
+  double* d_o3d = nullptr;   // staging of Open3D double clouds (3 + 3 doubles per point)
+  size_t cap_o3d = 0;
   int last_grid = 0;
   int debug_stats = 0;  // env B200_ICP_DEBUG=1
   unsigned* d_dbg_warp = nullptr;
@@ -418,7 +431,7 @@ void b200_icp_destroy(b200_icp* h) {
     cudaFree(h->d_ids); cudaFree(h->d_spos); cudaFree(h->d_dists); cudaFree(h->d_w);
     cudaFree(h->d_cand_d); cudaFree(h->d_cand_q); cudaFree(h->d_cand_rec);
     cudaFree(h->d_hist); cudaFree(h->d_partials); cudaFree(h->d_partials2); cudaFree(h->d_meanpart); cudaFree(h->d_out); cudaFree(h->d_log);
-    cudaFree(h->d_frames); cudaFree(h->d_Tinit); cudaFree(h->d_flush); cudaFree(h->d_dbg_warp);
+    cudaFree(h->d_frames); cudaFree(h->d_Tinit); cudaFree(h->d_flush); cudaFree(h->d_dbg_warp); cudaFree(h->d_o3d);
     cudaFreeHost(h->h_out); cudaFreeHost(h->h_frames); cudaFreeHost(h->h_Tinit);
     for (int i = 0; i < 5; ++i)
       if (h->ev[i]) cudaEventDestroy(h->ev[i]);
@@ -513,6 +526,49 @@ int b200_icp_compute(b200_icp* h, const float* read4xN, const float* readn3xN, i
   if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
   B200_TRY(icp_upload(h, read4xN, readn3xN, N));
   return icp_launch(h, Tinit16, res, true);
+}
+
+static int icp_stage_o3d(b200_icp* h, const double* p3, const double* n3, int N, float4* out, float4* outn) {
+  if ((size_t)N > h->cap_o3d) {
+    cudaFree(h->d_o3d);
+    h->d_o3d = nullptr; h->cap_o3d = 0;
+    B200_CUDA(cudaMalloc(&h->d_o3d, (size_t)N * 6 * sizeof(double)));
+    h->cap_o3d = (size_t)N;
+  }
+  cudaStream_t s = h->stream;
+  double* dn = n3 ? h->d_o3d + 3 * (size_t)N : nullptr;
+  B200_CUDA(cudaMemcpyAsync(h->d_o3d, p3, (size_t)N * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
+  if (n3) B200_CUDA(cudaMemcpyAsync(dn, n3, (size_t)N * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
+  pack_o3d_kernel<<<std::max(1, std::min(148 * 8, (N + 255) / 256)), 256, 0, s>>>(h->d_o3d, dn, N, out, outn);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+
+int b200_icp_compute_o3d(b200_icp* h, const double* pts3xN, const double* nrm3xN, int N, const float* Tinit16,
+                         b200_icp_result* res) {
+  if (!h || N < 0 || (N > 0 && !pts3xN)) { set_error("b200_icp_compute_o3d: bad arguments"); return B200_E_BAD_PARAM; }
+  if (!h->ref_ready) { set_error("You must setup a matcher before running ICP (no reference)"); return B200_E_NOT_INITIALIZED; }
+  if (N == 0) { set_error("The reading point cloud is empty."); return B200_E_BAD_PARAM; }
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  B200_TRY(icp_ensure_reading(h, N, nrm3xN != nullptr));
+  B200_CUDA(cudaEventRecord(h->ev[0], h->stream));
+  B200_TRY(icp_stage_o3d(h, pts3xN, nrm3xN, N, h->d_raw, h->d_raw_n));
+  h->upload_launches = 1;
+  h->N = N;
+  h->has_read_n = nrm3xN != nullptr;
+  return icp_launch(h, Tinit16, res, true);
+}
+
+int b200_icp_init_reference_o3d(b200_icp* h, const double* pts3xM, const double* nrm3xM, int M) {
+  if (!h || M < 0 || (M > 0 && !pts3xM)) { set_error("b200_icp_init_reference_o3d: bad arguments"); return B200_E_BAD_PARAM; }
+  h->ref_ready = false;
+  if (M == 0) { set_error("The reference point cloud is empty"); return B200_E_NOT_INITIALIZED; }
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  B200_TRY(index_alloc_points(h->map, M, nrm3xM != nullptr));
+  B200_TRY(icp_stage_o3d(h, pts3xM, nrm3xM, M, h->map.d_ref, h->map.d_nrm_orig));
+  return icp_reference_from_device(h, M, nrm3xM != nullptr);
 }
 
 int b200_icp_upload_reading(b200_icp* h, const float* read4xN, const float* readn3xN, int N) {

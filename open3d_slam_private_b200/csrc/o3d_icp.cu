@@ -112,12 +112,25 @@ __global__ void __launch_bounds__(kThreads) o3d_match_lin_kernel(const __grid_co
     p.ids[i] = (bid >= 0 && p.gid) ? __ldg(&p.gid[bid]) : bid; p.dists[i] = bd;
     if (bid < 0) continue;
     const float4 t4 = __ldg(&p.g.pts[bsp]);
-    const float4 n4 = p.kind == 1 ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldg(&p.g.nrm[bsp]);
+    const float4 n4 = (p.kind == 1 || p.kind == 3) ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldg(&p.g.nrm[bsp]);
     const double s[3] = {(double)q.x, (double)q.y, (double)q.z};
     const double d[3] = {s[0] - (double)t4.x, s[1] - (double)t4.y, s[2] - (double)t4.z};
     acc[27] += 1.0;
     acc[28] += (double)bd;
-    if (p.kind == 1) {
+    if (p.kind == 3) {
+      // GetInformationMatrixFromPointClouds (Open3D v0.15.1, as called at PlaceRecognition.cpp:148-149): G^T G over the
+      // correspondences with the three rows G = [-[t]x | I] of the matched TARGET point t
+      const double x = (double)t4.x, y = (double)t4.y, z = (double)t4.z;
+      const double G[3][6] = {{0.0, z, -y, 1.0, 0.0, 0.0}, {-z, 0.0, x, 0.0, 1.0, 0.0}, {y, -x, 0.0, 0.0, 0.0, 1.0}};
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        int t = 0;
+#pragma unroll
+        for (int c = 0; c < 6; ++c)
+#pragma unroll
+          for (int a = 0; a <= c; ++a) acc[t++] += G[r][a] * G[r][c];
+      }
+    } else if (p.kind == 1) {
       // Umeyama moments: sum s (0..2), sum t (3..5), sum t s^T (6..14, column-major)
       const double t[3] = {(double)t4.x, (double)t4.y, (double)t4.z};
 #pragma unroll
@@ -615,7 +628,7 @@ int b200_o3d_create(b200_o3d** out, int device, const b200_o3d_params* prm) {
   if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail(e, "cudaStreamCreate");
   h->map.stream = h->stream;
   h->nmap.stream = h->stream;
-  if ((e = cudaMalloc(&h->d_partials, (size_t)h->max_blocks * kVals * sizeof(double))) != cudaSuccess) return fail(e, "cudaMalloc");
+  if ((e = cudaMalloc(&h->d_partials, ((size_t)h->max_blocks + 1) * kVals * sizeof(double))) != cudaSuccess) return fail(e, "cudaMalloc");
   if ((e = cudaMalloc(&h->d_state, sizeof(O3dState))) != cudaSuccess) return fail(e, "cudaMalloc");
   if ((e = cudaMallocHost(&h->h_state, sizeof(O3dState))) != cudaSuccess) return fail(e, "cudaMallocHost");
   for (int i = 0; i < 3; ++i)
@@ -982,6 +995,39 @@ int b200_o3d_finish(b200_o3d* h, b200_o3d_result* res) {
 
 static int o3d_register_impl(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16,
                              b200_o3d_result* res, int est_knn, float est_radius);
+
+int b200_o3d_information_matrix(b200_o3d* h, const float* src4xN, int N, const double* T16,
+                                float max_correspondence_distance, double* info36, double* fitness, double* inlier_rmse,
+                                int* n_correspondences) {
+  if (!h || N <= 0 || !src4xN || !info36) { set_error("b200_o3d_information_matrix: bad arguments"); return B200_E_BAD_PARAM; }
+  if (!(max_correspondence_distance > 0.f)) { set_error("b200_o3d_information_matrix: max_correspondence_distance must be > 0"); return B200_E_BAD_PARAM; }
+  if (h->own_axis >= 0) { set_error("b200_o3d_information_matrix: not for a slab of a partitioned map"); return B200_E_BAD_PARAM; }
+  const int kind0 = h->prm.kind;
+  h->prm.kind = 1;   // the upload path of a registration that needs no normals
+  const int st = o3d_begin_impl(h, src4xN, nullptr, N, T16, nullptr, 0, 0.f);
+  h->prm.kind = kind0;
+  B200_TRY(st);
+  DeviceGuard dg(h->device);
+  h->running = false;
+  cudaStream_t s = h->run_stream;
+  O3dParams p = h->p;
+  p.kind = 3;
+  p.md2 = max_correspondence_distance * max_correspondence_distance;
+  o3d_match_lin_kernel<<<h->blocks, kThreads, 0, s>>>(p);
+  o3d_reduce_kernel<<<1, kThreads, 0, s>>>(p, h->blocks, h->d_partials + (size_t)h->max_blocks * kVals);
+  B200_CUDA(cudaGetLastError());
+  double sums[kVals];
+  B200_CUDA(cudaMemcpyAsync(sums, h->d_partials + (size_t)h->max_blocks * kVals, sizeof(sums), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  int t = 0;
+  for (int c = 0; c < 6; ++c)
+    for (int a = 0; a <= c; ++a) { info36[a + 6 * c] = sums[t]; info36[c + 6 * a] = sums[t]; ++t; }
+  const double cnt = sums[27];
+  if (fitness) *fitness = cnt / (double)N;
+  if (inlier_rmse) *inlier_rmse = cnt > 0.0 ? std::sqrt(sums[28] / cnt) : 0.0;
+  if (n_correspondences) *n_correspondences = (int)(cnt + 0.5);
+  return B200_OK;
+}
 
 int b200_o3d_register(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N, const double* init16,
                       b200_o3d_result* res) {

@@ -332,6 +332,57 @@ __global__ void voxel_mean_kernel(const float4* __restrict__ p, const float* __r
   }
 }
 
+// ---- RandomDownSample ------------------------------------------------------------------------------------------------
+// key(i) = fmix32(i ^ seed * 0x9E3779B9): fmix32 (murmur3's finaliser) is a bijection of the 32-bit integers, so the
+// keys of distinct points are distinct and "the K smallest keys" is a uniformly random K-subset without replacement.
+__device__ __forceinline__ uint32_t rds_key(uint32_t i, uint32_t seed) {
+  uint32_t x = i ^ (seed * 0x9E3779B9u);
+  x ^= x >> 16; x *= 0x85ebca6bu; x ^= x >> 13; x *= 0xc2b2ae35u; x ^= x >> 16;
+  return x;
+}
+// st: [0] wanted rank (K - 1, then the rank inside the selected bin), [1] selected high half, [2] K-th smallest key
+__global__ void rds_hist_kernel(int N, uint32_t seed, int pass, const uint32_t* __restrict__ st, uint32_t* __restrict__ hist) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+    const uint32_t k = rds_key((uint32_t)i, seed);
+    if (pass == 0) atomicAdd(&hist[k >> 16], 1u);
+    else if ((k >> 16) == st[1]) atomicAdd(&hist[65536u + (k & 0xffffu)], 1u);
+  }
+}
+__global__ void __launch_bounds__(1024) rds_pick_kernel(int pass, uint32_t* __restrict__ st, const uint32_t* __restrict__ hist) {
+  __shared__ uint32_t s_sum[1024];
+  const int tid = threadIdx.x;
+  const uint32_t* hh = hist + (pass ? 65536 : 0);
+  uint32_t c[64], sum = 0;
+  for (int j = 0; j < 64; ++j) { c[j] = hh[tid * 64 + j]; sum += c[j]; }
+  s_sum[tid] = sum;
+  __syncthreads();
+  for (int o = 1; o < 1024; o <<= 1) {   // inclusive scan (Hillis-Steele; 10 steps)
+    const uint32_t v = tid >= o ? s_sum[tid - o] : 0u;
+    __syncthreads();
+    s_sum[tid] += v;
+    __syncthreads();
+  }
+  const uint32_t rank = st[0];
+  uint32_t ex = s_sum[tid] - sum;
+  __syncthreads();
+  if (rank >= ex && rank < ex + sum) {
+    for (int j = 0; j < 64; ++j) {
+      if (rank < ex + c[j]) {
+        const uint32_t bin = (uint32_t)(tid * 64 + j);
+        if (pass == 0) { st[1] = bin; st[0] = rank - ex; }
+        else st[2] = (st[1] << 16) | bin;
+        break;
+      }
+      ex += c[j];
+    }
+  }
+}
+__global__ void rds_flag_kernel(int N, uint32_t seed, const uint32_t* __restrict__ st, uint32_t* __restrict__ flag) {
+  const uint32_t kth = st[2];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x)
+    flag[i] = rds_key((uint32_t)i, seed) <= kth ? 1u : 0u;
+}
+
 }  // namespace
 
 // =================================================================================================================
@@ -447,6 +498,65 @@ int b200_prep_crop(b200_prep* h, const b200_crop_params* prm, const float* pts4x
     if (kept_idx) B200_CUDA(cudaMemcpyAsync(kept_idx, h->buf[b200_prep::IDX].p, (size_t)K * sizeof(int), cudaMemcpyDeviceToHost, s));
     B200_CUDA(cudaStreamSynchronize(s));
   }
+  B200_CUDA(cudaEventElapsedTime(&h->last_ms, h->ev[0], h->ev[1]));
+  *n_out = (int)K;
+  return B200_OK;
+}
+
+// o3d_slam::randomDownSample (helpers.cpp:100-106) -> open3d PointCloud::RandomDownSample(ratio) (v0.15.1, not in the
+// reference tree: sample_size = size_t(ratio * n) indices drawn without replacement by shuffling with an mt19937 seeded
+// from std::random_device — the reference's own output is not reproducible). Here: the sample_size points with the
+// smallest keys of a bijective hash of (index, seed), in input order.
+int b200_prep_random_downsample(b200_prep* h, double ratio, uint32_t seed, const float* pts4xN, const float* nrm3xN, int N,
+                                float* out4xN, float* outn3xN, int32_t* kept_idx, int* n_out) {
+  if (!h || N < 0 || (N > 0 && !pts4xN) || !n_out) { set_error("b200_prep_random_downsample: bad arguments"); return B200_E_BAD_PARAM; }
+  if (!(ratio > 0.0)) { set_error("RandomDownSample: sampling_ratio must lie in (0, 1]"); return B200_E_BAD_PARAM; }
+  *n_out = 0;
+  if (N == 0) return B200_OK;
+  if (ratio >= 1.0) {   // "if (downSamplingRatio >= 1.0) return" (helpers.cpp:101-103): the cloud is left as it is
+    if (out4xN) std::memcpy(out4xN, pts4xN, (size_t)N * 4 * sizeof(float));
+    if (outn3xN && nrm3xN) std::memcpy(outn3xN, nrm3xN, (size_t)N * 3 * sizeof(float));
+    if (kept_idx) for (int i = 0; i < N; ++i) kept_idx[i] = i;
+    *n_out = N;
+    h->last_ms = 0.f;
+    return B200_OK;
+  }
+  const size_t K = (size_t)(ratio * (double)N);
+  if (K == 0) return B200_OK;
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  cudaStream_t s = h->stream;
+  B200_TRY(upload_cloud(h, pts4xN, nrm3xN, N));
+  B200_TRY(ensure(h, b200_prep::FLAG, ((size_t)N + 2) * sizeof(uint32_t)));
+  B200_TRY(ensure(h, b200_prep::TILE, std::max<size_t>(1, scan_tiles_for((size_t)N)) * sizeof(uint32_t)));
+  B200_TRY(ensure(h, b200_prep::OUT4, (size_t)N * sizeof(float4)));
+  B200_TRY(ensure(h, b200_prep::IDX, (size_t)N * sizeof(int)));
+  B200_TRY(ensure(h, b200_prep::SCR, (2 * 65536 + 4) * sizeof(uint32_t)));
+  if (nrm3xN) B200_TRY(ensure(h, b200_prep::OUTN3, (size_t)N * 3 * sizeof(float)));
+  uint32_t* hist = ptr<uint32_t>(h, b200_prep::SCR);
+  uint32_t* st = hist + 2 * 65536;
+  const uint32_t st0[4] = {(uint32_t)(K - 1), 0u, 0u, 0u};
+  B200_CUDA(cudaMemsetAsync(hist, 0, 2 * 65536 * sizeof(uint32_t), s));
+  B200_CUDA(cudaMemcpyAsync(st, st0, sizeof(st0), cudaMemcpyHostToDevice, s));
+  B200_CUDA(cudaEventRecord(h->ev[0], s));
+  uint32_t* flag = ptr<uint32_t>(h, b200_prep::FLAG);
+  for (int pass = 0; pass < 2; ++pass) {
+    rds_hist_kernel<<<blocks_for(N), kThreads, 0, s>>>(N, seed, pass, st, hist);
+    rds_pick_kernel<<<1, 1024, 0, s>>>(pass, st, hist);
+  }
+  rds_flag_kernel<<<blocks_for(N), kThreads, 0, s>>>(N, seed, st, flag);
+  B200_TRY(inclusive_scan_u32(flag, (size_t)N, ptr<uint32_t>(h, b200_prep::TILE), s));
+  crop_scatter_kernel<<<blocks_for(N), kThreads, 0, s>>>(ptr<float4>(h, b200_prep::PTS),
+                                                         nrm3xN ? ptr<float>(h, b200_prep::N3) : nullptr, N, flag,
+                                                         ptr<float4>(h, b200_prep::OUT4),
+                                                         nrm3xN ? ptr<float>(h, b200_prep::OUTN3) : nullptr,
+                                                         ptr<int>(h, b200_prep::IDX));
+  B200_CUDA(cudaGetLastError());
+  B200_CUDA(cudaEventRecord(h->ev[1], s));
+  if (out4xN) B200_CUDA(cudaMemcpyAsync(out4xN, h->buf[b200_prep::OUT4].p, K * sizeof(float4), cudaMemcpyDeviceToHost, s));
+  if (outn3xN && nrm3xN) B200_CUDA(cudaMemcpyAsync(outn3xN, h->buf[b200_prep::OUTN3].p, K * 3 * sizeof(float), cudaMemcpyDeviceToHost, s));
+  if (kept_idx) B200_CUDA(cudaMemcpyAsync(kept_idx, h->buf[b200_prep::IDX].p, K * sizeof(int), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
   B200_CUDA(cudaEventElapsedTime(&h->last_ms, h->ev[0], h->ev[1]));
   *n_out = (int)K;
   return B200_OK;

@@ -332,3 +332,44 @@ extern "C" int orc_o3d_estimate_normals(const float* pts4xN, int N, int max_nn, 
   }
   return ORC_OK;
 }
+
+// ---- GetInformationMatrixFromPointClouds (Open3D v0.15.1 pipelines/registration/Registration.cpp, recalled; called at
+// open3d_slam/src/PlaceRecognition.cpp:148-149) --------------------------------------------------------------------
+//   pcd = source transformed by T; correspondences = GetRegistrationResultAndCorrespondences(pcd, target, kdtree,
+//   max_correspondence_distance): 1-NN within the distance; GTG = sum over correspondences of G_r G_r^T for the three
+//   rows (0, z, -y, 1, 0, 0), (-z, 0, x, 0, 1, 0), (y, -x, 0, 0, 0, 1) of the matched TARGET point (x, y, z).
+// Same float-cloud convention as orc_o3d_icp: the transformed source is rounded to float for the match.
+extern "C" int orc_o3d_information_matrix(const float* src4xN, int N, const float* tgt4xM, int M, const double* T16,
+                                          float max_dist, int threads, double* info36, double* fitness, double* rmse,
+                                          int32_t* corr_ids) {
+  if (N <= 0 || M <= 0) return ORC_E_BAD_PARAM;
+  std::vector<float> q(4 * (size_t)N);
+  for (int i = 0; i < N; ++i) {
+    const double x = src4xN[4 * (size_t)i], y = src4xN[4 * (size_t)i + 1], z = src4xN[4 * (size_t)i + 2];
+    for (int r = 0; r < 3; ++r) q[4 * (size_t)i + r] = (float)(T16[r] * x + T16[r + 4] * y + T16[r + 8] * z + T16[r + 12]);
+    q[4 * (size_t)i + 3] = 1.f;
+  }
+  std::vector<int32_t> ids((size_t)N);
+  std::vector<float> d((size_t)N);
+  void* tree = orc_kdtree_build(tgt4xM, M);
+  orc_kdtree_knn(tree, q.data(), N, 1, max_dist, threads > 0 ? threads : 1, ids.data(), d.data());
+  orc_kdtree_free(tree);
+  double GTG[36];
+  for (double& v : GTG) v = 0.0;
+  double cnt = 0.0, s2 = 0.0;
+  for (int i = 0; i < N; ++i) {
+    if (corr_ids) corr_ids[i] = ids[i];
+    if (ids[i] < 0) continue;
+    const double x = tgt4xM[4 * (size_t)ids[i]], y = tgt4xM[4 * (size_t)ids[i] + 1], z = tgt4xM[4 * (size_t)ids[i] + 2];
+    const double G[3][6] = {{0.0, z, -y, 1.0, 0.0, 0.0}, {-z, 0.0, x, 0.0, 1.0, 0.0}, {y, -x, 0.0, 0.0, 0.0, 1.0}};
+    for (int r = 0; r < 3; ++r)
+      for (int c = 0; c < 6; ++c)
+        for (int a = 0; a < 6; ++a) GTG[a + 6 * c] += G[r][a] * G[r][c];
+    cnt += 1.0;
+    s2 += (double)d[i];
+  }
+  std::memcpy(info36, GTG, sizeof(GTG));
+  if (fitness) *fitness = cnt / (double)N;
+  if (rmse) *rmse = cnt > 0.0 ? std::sqrt(s2 / cnt) : 0.0;
+  return ORC_OK;
+}

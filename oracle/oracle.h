@@ -166,6 +166,10 @@ int orc_o3d_icp(int kind, const float* src4xN, int N, const float* tgt4xM, int M
 int orc_o3d_estimate_normals(const float* pts4xN, int N, int max_nn, float radius, int threads, double* normals3xN,
                              int32_t* n_neighbours);
 
+/* GetInformationMatrixFromPointClouds as called at PlaceRecognition.cpp:148-149 (see o3d.cpp); corr_ids nullable */
+int orc_o3d_information_matrix(const float* src4xN, int N, const float* tgt4xM, int M, const double* T16, float max_dist,
+                               int threads, double* info36, double* fitness, double* rmse, int32_t* corr_ids);
+
 /* ---- scan pre-processing (see prep.cpp): open3d_slam croppers (croppers.cpp:25-164) and Open3D
  * VoxelDownSample (recalled from upstream v0.15.1) ---- */
 int orc_crop(int kind, double radius_min, double radius_max, double min_z, double max_z, const double* center3,

@@ -396,6 +396,21 @@ def o3d_estimate_normals(pts4, knn=20, radius=1.0, threads=4):
     return out, cnt
 
 
+def o3d_information_matrix(src4, tgt4, T, max_dist, threads=4):
+    """-> (6x6 float64, fitness, rmse, matched target ids (N,) int32)"""
+    src4, tgt4 = f32(src4), f32(tgt4)
+    dp = C.POINTER(C.c_double)
+    Tc = np.ascontiguousarray(np.asarray(T, np.float64).T).ravel()
+    info = np.empty(36, np.float64)
+    fit, rmse = C.c_double(), C.c_double()
+    ids = np.empty(src4.shape[0], np.int32)
+    st = lib().orc_o3d_information_matrix(_fp(src4), src4.shape[0], _fp(tgt4), tgt4.shape[0], Tc.ctypes.data_as(dp),
+                                          C.c_float(max_dist), int(threads), info.ctypes.data_as(dp), C.byref(fit),
+                                          C.byref(rmse), _ip(ids))
+    assert st == ORC_OK, st
+    return info.reshape(6, 6).T.copy(), fit.value, rmse.value, ids
+
+
 def crop(kind, pts4, radius_min=0.0, radius_max=0.0, min_z=0.0, max_z=0.0, center=(0.0, 0.0, 0.0), invert=False):
     """orc_crop -> indices of the kept points, input order (croppers.cpp:66-95)"""
     pts4 = f32(pts4)
@@ -455,3 +470,19 @@ def crop_d(kind, pts3, radius_min=0.0, radius_max=0.0, min_z=0.0, max_z=0.0, cen
     k = lib().orc_crop_d(int(kind), C.c_double(radius_min), C.c_double(radius_max), C.c_double(min_z), C.c_double(max_z), c,
                          int(bool(invert)), pts3.ctypes.data_as(C.POINTER(C.c_double)), n, _ip(idx))
     return idx[:k].copy()
+
+
+def random_downsample_indices(n, ratio, seed=0):
+    """The selection rule of b200_prep_random_downsample restated in numpy (Open3D's own RandomDownSample draws from
+    std::random_device and cannot be reproduced): the int(ratio * n) indices with the smallest fmix32(i ^ seed * phi)."""
+    if ratio >= 1.0:
+        return np.arange(n, dtype=np.int32)
+    k = int(ratio * n)
+    x = np.arange(n, dtype=np.uint32) ^ np.uint32((int(seed) * 0x9E3779B9) & 0xFFFFFFFF)
+    x ^= x >> np.uint32(16)
+    x = (x.astype(np.uint64) * np.uint64(0x85ebca6b) & np.uint64(0xFFFFFFFF)).astype(np.uint32)
+    x ^= x >> np.uint32(13)
+    x = (x.astype(np.uint64) * np.uint64(0xc2b2ae35) & np.uint64(0xFFFFFFFF)).astype(np.uint32)
+    x ^= x >> np.uint32(16)
+    assert np.unique(x).size == n          # a bijection: no ties
+    return np.sort(np.argsort(x, kind="stable")[:k]).astype(np.int32)

@@ -211,3 +211,27 @@ def test_o3d_gicp_with_source_normals_estimated_on_device(cars):
                   max_iteration=30, threads=4)
     assert o["iterations"] == b["iterations"]
     assert rot_angle(o["T"][:3, :3], b["T"][:3, :3]) < 1e-5 and np.abs(o["T"][:3, 3] - b["T"][:3, 3]).max() < 1e-5
+
+
+def test_o3d_information_matrix(cars):
+    """GetInformationMatrixFromPointClouds (PlaceRecognition.cpp:148-149) and the fitness of the same match: the device
+    sums over bit-identical correspondences, so G^T G agrees to double rounding"""
+    tgt4, tgtn, src4, _ = cars
+    T = small_T(0.01, -0.02, 0.015, [0.3, -0.1, 0.05])
+    h = B.O3dICP(kind=0, max_correspondence_distance=1.0, max_iteration=30)
+    h.set_target(tgt4, tgtn)
+    for md in (0.3, 1.0):
+        info, fit, rmse, n = h.information_matrix(src4, T, md)
+        ids, _ = h.correspondences()
+        oi, ofit, ormse, oids = O.o3d_information_matrix(src4, tgt4, T, md)
+        assert (ids == oids).all() and n == int((oids >= 0).sum()) and fit == ofit
+        assert abs(rmse - ormse) <= 1e-12 * max(1.0, ormse)
+        assert np.abs(info - oi).max() <= 1e-12 * np.abs(oi).max()
+        assert np.array_equal(info, info.T) and info[3, 3] == n and info[4, 4] == n and info[5, 5] == n
+    r = h.register(src4)                      # the handle still registers afterwards
+    assert r["iterations"] > 0
+    far = src4.copy()
+    far[:, :3] += 1000.0
+    info, fit, rmse, n = h.information_matrix(far, np.eye(4), 0.5)
+    assert n == 0 and fit == 0.0 and not info.any()
+    h.close()

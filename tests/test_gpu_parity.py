@@ -528,3 +528,26 @@ def _uniform_cloud_normals(tile):
     oi, od = O.KdTree(f).knn(np.ascontiguousarray(f[pick]), 20, np.inf, threads=4)
     assert (out["matchedIds"][pick].astype(np.int64) == oi).all()
     assert (np.abs(out["normals"][pick, 2]) > 0.95).mean() > 0.99
+
+
+def test_icp_open3d_double_clouds(gold):
+    """b200_icp_init_reference_o3d / b200_icp_compute_o3d: Open3D's double clouds in, open3dToPointmatcher's
+    double -> float cast (open3d_conversions.cpp:57-118) on the device == the cast on the host, bit for bit"""
+    rng = np.random.default_rng(0)
+    ref_d = gold["c400"]["xyz"].astype(np.float64) + rng.uniform(-1e-9, 1e-9, gold["c400"]["xyz"].shape)   # true doubles
+    refn_d = gold["c400"]["normals"].astype(np.float64)
+    read_d = gold["c401"]["xyz"].astype(np.float64) + rng.uniform(-1e-9, 1e-9, gold["c401"]["xyz"].shape)
+    p = B.default_icp_params(maxDist=0.5, trimmed_ratio=0.9, max_iterations=30, min_diff_trans=0.008)
+    a = B.ICP(p)
+    a.init_reference_o3d(ref_d, refn_d)
+    ra = a.compute_o3d(read_d)
+    ia, da, wa = a.matches()
+    b = B.ICP(p)
+    b.init_reference(O.feat4(ref_d.astype(np.float32)), refn_d.astype(np.float32))
+    rb = b.compute(O.feat4(read_d.astype(np.float32)))
+    ib, db, wb = b.matches()
+    assert ra["iterations"] == rb["iterations"] and np.array_equal(ra["T"], rb["T"])
+    assert (ia == ib).all() and (bits(da) == bits(db)).all() and (wa == wb).all()
+    with pytest.raises(B.B200Error):
+        B.ICP(p).compute_o3d(read_d)          # no reference yet
+    a.close(); b.close()

@@ -135,3 +135,30 @@ def test_device_preprocess_errors_and_empty():
     out, _, idx = prep.crop(3, p4, radius_max=0.0, center=(1e6, 0, 0))
     assert len(out) == 0 and len(idx) == 0
     prep.close()
+
+
+@pytest.mark.gpu
+def test_random_downsample():
+    """o3d_slam::randomDownSample (helpers.cpp:100-106): exactly int(ratio * N) points, no repeats, input order, uniform;
+    ratio >= 1 leaves the cloud alone; the index set equals the numpy restatement of the selection rule"""
+    from open3d_slam_private_b200 import capi as B
+    rng = np.random.default_rng(8)
+    pts = O.feat4(rng.normal(size=(131072, 3)).astype(np.float32))
+    nrm = rng.normal(size=(131072, 3)).astype(np.float32)
+    p = B.Prep()
+    for ratio, seed in ((0.35, 0), (0.25, 7), (0.9, 123), (1e-4, 5)):
+        o4, on, idx = p.random_downsample(ratio, pts, nrm, seed=seed)
+        assert idx.size == int(ratio * pts.shape[0]) and (np.diff(idx) > 0).all()
+        assert np.array_equal(idx, O.random_downsample_indices(pts.shape[0], ratio, seed))
+        assert np.array_equal(o4, pts[idx]) and np.array_equal(on, nrm[idx])
+    _, _, a = p.random_downsample(0.35, pts, seed=1)
+    _, _, b = p.random_downsample(0.35, pts, seed=2)
+    assert not np.array_equal(a, b) and abs(np.intersect1d(a, b).size / a.size - 0.35) < 0.02   # independent draws
+    counts = np.bincount(a // 4096, minlength=32)            # uniform over the cloud: 32 blocks of 4096 points
+    assert np.abs(counts - 0.35 * 4096).max() < 6 * np.sqrt(4096 * 0.35 * 0.65)
+    o4, on, idx = p.random_downsample(1.0, pts, nrm)
+    assert np.array_equal(o4, pts) and np.array_equal(idx, np.arange(pts.shape[0]))
+    with pytest.raises(B.B200Error):
+        p.random_downsample(0.0, pts)
+    assert p.random_downsample(0.5, pts[:0])[2].size == 0
+    p.close()
