@@ -17,7 +17,7 @@ LIB = os.path.join(LIBDIR, "libb200reg.so")
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "-fmad=false",
-         "-Xcompiler", "-fPIC,-ffp-contract=off,-Wall", "-Xptxas", "-v"]
+         "-Xcompiler", "-fPIC,-ffp-contract=off,-Wall", "-Xptxas", "-v"] + os.environ.get("B200_NVCC_EXTRA", "").split()
 
 
 def _deps():

@@ -90,10 +90,11 @@ def load():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(_LIBPATH):
+    path = os.environ.get("B200REG_LIB") or _LIBPATH   # (experiments: a differently compiled build of the same sources)
+    if not os.path.exists(path):
         from . import build as _b
         _b.build()
-    lib = C.CDLL(_LIBPATH)
+    lib = C.CDLL(path)
     lib.b200_last_error.restype = C.c_char_p
     _lib = lib
     return lib

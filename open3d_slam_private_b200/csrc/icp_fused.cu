@@ -33,7 +33,7 @@
 namespace cg = cooperative_groups;
 
 namespace b200 {
-int icp_cand_segment(int N, int grid);
+int icp_cand_segment(int nslots, int grid);
 size_t icp_cand_capacity(int N);
 namespace {
 
@@ -210,7 +210,10 @@ __device__ __forceinline__ unsigned slot_stride(unsigned nslots) {
   }
   return 1u;
 }
-__device__ __forceinline__ int query_of(int slot, int lane, int nslots, int c, unsigned stride) {
+// A warp may hold fewer than 32 queries (qpw = 4, 8, 16: small scans spread over all SMs; the idle lanes help in the
+// cooperative parts of the search): lanes >= qpw get no query, and there are qpw >> c groups per slot.
+__device__ __forceinline__ int query_of(int slot, int lane, int nslots, int c, unsigned stride, int qpw) {
+  if (lane >= qpw) return 0x7fffffff;
   const unsigned g = (unsigned)lane >> c, j = (unsigned)lane & ((1u << c) - 1u);
   const unsigned s2 = c ? (unsigned)(((unsigned long long)(unsigned)slot * stride) % (unsigned)nslots) : (unsigned)slot;
   return (int)(((g * (unsigned)nslots + (s2 + g * 97u) % (unsigned)nslots) << c) + j);
@@ -251,7 +254,8 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
   }
   __syncthreads();
   const bool xicp = (K == 1) && p.xicp && p.minimizer == 0;
-  const unsigned qstride = slot_stride((unsigned)((p.N + 31) >> 5));
+  const int qpw = 1 << p.qpw_log2;   // queries per warp (launcher: 32 unless the scan is too small to fill the SMs)
+  const unsigned qstride = slot_stride((unsigned)((p.N + qpw - 1) >> p.qpw_log2));
   unsigned long long visited_total = 0ull;
 
   const bool stamp = (blockIdx.x == 0 && tid == 0 && p.log != nullptr);
@@ -266,6 +270,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
       else if (S.iteration == 0) S.coh = 0;
       else if (p.use_trimmed) S.coh = (S.have_bracket && sqrtf(S.lim_prev) * p.g.inv_cell < 0.4f) ? 5 : 0;
       else S.coh = S.iteration >= 2 ? 5 : 0;
+      if (S.coh > p.qpw_log2) S.coh = p.qpw_log2;
     }
     zero_hist(s_hist);  // includes __syncthreads
     const int par = S.iteration & 1;
@@ -292,7 +297,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     // coherent, so equally cheap or equally expensive) are spread over different warps; a warp holding 32 expensive
     // queries was the tail every other warp waited for at the grid barrier. Warp-uniform trip count: the k = 1 search
     // is a warp collective.
-    const int nslots = (p.N + 31) >> 5;
+    const int nslots = (p.N + qpw - 1) >> p.qpw_log2;
     const int rounds = (nslots + (nthreads >> 5) - 1) / (nthreads >> 5);  // grid-uniform trip count
     // Coherent warps (32 consecutive scan points: their cell rows and candidates share 128-byte lines, 1 L1 wavefront
     // instead of up to 32) once nearly every query is settled by its own 2x2x2 block, i.e. when all queries cost the
@@ -315,7 +320,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     float4 st_q = make_float4(0.f, 0.f, 0.f, 1.f), st_r4 = make_float4(0.f, 0.f, 0.f, 0.f), st_n4 = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int round = 0; round < rounds; ++round) {
       const int slot = (gtid >> 5) + round * (nthreads >> 5);
-      const int i = slot < nslots ? query_of(slot, lane, nslots, coh, qstride) : p.N;
+      const int i = slot < nslots ? query_of(slot, lane, nslots, coh, qstride, qpw) : p.N;
       const bool in = i < p.N;
       const float4 q = in ? apply_T(S.Tc, __ldg(&p.reading[i])) : make_float4(0.f, 0.f, 0.f, 1.f);
       unsigned vis = 0;
@@ -324,8 +329,11 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
         unsigned w_rows = 0, w_pass = 0;
         const unsigned long long w_t0 = p.debug_stats ? gtimer() : 0ull;
         // the search's per-warp scratch shares the staging tile: the tile is written only after the barrier below
+        // warm start from the previous iteration's match of the same query (its own thread wrote it or, after a change
+        // of the query map, another CTA did before the barrier that closed that iteration)
+        const int hint = (in && S.iteration > 0 && p.warm_start) ? __ldcg(&p.spos[i]) : -1;
         knn_query_warp1(p.g, in, q.x, q.y, q.z, p.md2, bd, bid, bsp, vis, reinterpret_cast<Warp1Scratch*>(s_dyn)[wid],
-                        p.debug_stats ? &w_rows : nullptr, p.debug_stats ? &w_pass : nullptr);
+                        p.debug_stats ? &w_rows : nullptr, p.debug_stats ? &w_pass : nullptr, qpw < 32, hint);
         if (p.debug_stats) {
           dbg_rows += w_rows;
           if (p.dbg_warp && S.iteration == 0) {
@@ -726,7 +734,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     for (int t = tid; t < kWarps * kAccum; t += kIcpThreads) (&s_red[0][0])[t] = 0.0;
     __syncthreads();
     for (int slot = gtid >> 5; slot < nslots; slot += nthreads >> 5) {  // same map as phase 1 (no barrier needed in between)
-      const int i = query_of(slot, lane, nslots, coh, qstride);
+      const int i = query_of(slot, lane, nslots, coh, qstride, qpw);
       const bool in = i < p.N;
       float4 q = make_float4(0.f, 0.f, 0.f, 1.f);
       float3 nq = make_float3(0.f, 0.f, 0.f);
@@ -906,7 +914,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
         __syncthreads();
         const float cmin = p.x_cos_min, cstr = p.x_cos_strong;
         for (int slot = gtid >> 5; slot < nslots; slot += nthreads >> 5) {
-          const int i = query_of(slot, lane, nslots, coh, qstride);
+          const int i = query_of(slot, lane, nslots, coh, qstride, qpw);
           double acc[12];
 #pragma unroll
           for (int t = 0; t < 12; ++t) acc[t] = 0.0;
@@ -1221,11 +1229,26 @@ int launch_k(const IcpKernelParams& p, int device, cudaStream_t s, int* grid_out
   B200_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
   if (per_sm < 1) { set_error("persistent ICP kernel does not fit on an SM"); return B200_E_CUDA; }
   int grid = per_sm * sms;
-  // do not launch more CTAs than there is work for (fewer CTAs = cheaper grid barriers)
-  const int need = std::max(1, (p.N + kIcpThreads - 1) / kIcpThreads);
-  grid = std::min(grid, need);
   IcpKernelParams pc = p;
-  pc.cand_seg = icp_cand_segment(p.N, grid);
+  // A small scan does not fill the machine with 32 queries per warp (25 k points = 49 CTAs on 148 SMs, and the
+  // matching phase lasts as long as the slowest warp): give a warp fewer queries, down to 4, while the warps still
+  // fit in one wave. k = 1 only (the k > 1 search is per thread).
+  pc.qpw_log2 = 5;
+  if (K == 1) {
+    const int warps_cap = grid * (kIcpThreads / 32);
+    while (pc.qpw_log2 > 2 && ((p.N + (1 << (pc.qpw_log2 - 1)) - 1) >> (pc.qpw_log2 - 1)) <= warps_cap) --pc.qpw_log2;
+    if (p.qpw_log2 >= 2 && p.qpw_log2 <= 5) pc.qpw_log2 = p.qpw_log2;   // pinned by the caller (B200_ICP_QPW)
+  }
+  // Warm start of the searches (knn.cuh): one more dependent load per query and iteration against fewer cells to
+  // visit. Measured: a loss on the dense, uniform map (C2 0.46 -> 0.50 ms: the matching phase is a chain of memory
+  // latencies there, not a volume of candidates), a gain on a raw scan as target (car_cloud 1.91 -> 1.67 ms:
+  // crowded cells). Small scans are registered against such targets, so: on iff the warps were thinned out.
+  if (pc.warm_start < 0) pc.warm_start = pc.qpw_log2 < 5 ? 1 : 0;
+  // do not launch more CTAs than there is work for (fewer CTAs = cheaper grid barriers)
+  const int nslots = (p.N + (1 << pc.qpw_log2) - 1) >> pc.qpw_log2;
+  const int need = std::max(1, (nslots + kIcpThreads / 32 - 1) / (kIcpThreads / 32));
+  grid = std::min(grid, need);
+  pc.cand_seg = icp_cand_segment(nslots, grid);
   pc.cand_cap = icp_cand_capacity(p.N);   // per parity
   if (grid > kIcpThreads || (size_t)grid * (size_t)pc.cand_seg > icp_cand_capacity(p.N)) pc.fast_path = 0;
   void* args[] = {(void*)&pc};
@@ -1238,8 +1261,8 @@ int launch_k(const IcpKernelParams& p, int device, cudaStream_t s, int* grid_out
 }  // namespace
 
 // candidates one CTA can park: every query it owns (rounds x threads)
-int icp_cand_segment(int N, int grid) {
-  const int nslots = (N + 31) / 32, warps = grid * (kIcpThreads / 32);
+int icp_cand_segment(int nslots, int grid) {
+  const int warps = grid * (kIcpThreads / 32);
   const int rounds = (nslots + warps - 1) / warps;
   return rounds * kIcpThreads;
 }

@@ -142,6 +142,8 @@ struct b200_icp {
   float* d_cand_d = nullptr; int* d_cand_q = nullptr; float4* d_cand_rec = nullptr;
   size_t cap_cand = 0;
   int fast_path = 1;  // env B200_ICP_FAST=0 forces the general iteration
+  int warm_start = -1;  // env B200_ICP_WARM=0/1 pins the warm start of the searches; default: on for small scans (launcher)
+  int qpw_log2 = -1;  // env B200_ICP_QPW=2..5 pins log2 of the queries per warp; default: chosen by the launcher from N
   int coh_log2 = -1;  // env B200_ICP_COH=0..5 pins the coherent run of query_of (icp_fused.cu); default: chosen per iteration
   unsigned* d_hist = nullptr;
   double *d_partials = nullptr, *d_partials2 = nullptr, *d_meanpart = nullptr;
@@ -291,10 +293,12 @@ int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool tim
   p.cand_d = h->d_cand_d; p.cand_q = h->d_cand_q; p.cand_rec = h->d_cand_rec; p.cand_seg = 0;
   p.fast_path = (h->fast_path && h->prm.knn == 1) ? 1 : 0;
   p.coh_log2 = h->coh_log2;
+  p.qpw_log2 = h->qpw_log2;
+  p.warm_start = h->warm_start;   // < 0: the launcher decides
   p.debug_stats = h->debug_stats;
   p.dbg_warp = nullptr;
   if (h->debug_stats) {
-    const size_t need = (size_t)((N + 31) / 32) * 4;
+    const size_t need = (size_t)((N + 3) / 4) * 4;   // one entry per warp slot, at most N / 4 slots
     if (need > h->cap_dbg_warp) {
       cudaFree(h->d_dbg_warp);
       h->d_dbg_warp = nullptr;
@@ -411,6 +415,8 @@ int b200_icp_create(b200_icp** out, int device, const b200_icp_params* prm) {
   { const char* e = getenv("B200_ICP_DEBUG"); h->debug_stats = (e && e[0] == '1') ? 1 : 0; }
   { const char* e = getenv("B200_ICP_FAST"); h->fast_path = (e && e[0] == '0') ? 0 : 1; }
   { const char* e = getenv("B200_ICP_COH"); if (e && e[0] >= '0' && e[0] <= '5') h->coh_log2 = e[0] - '0'; }
+  { const char* e = getenv("B200_ICP_WARM"); if (e && (e[0] == '0' || e[0] == '1')) h->warm_start = e[0] - '0'; }
+  { const char* e = getenv("B200_ICP_QPW"); if (e && e[0] >= '2' && e[0] <= '5') h->qpw_log2 = e[0] - '0'; }
   h->map.device = device;
   int st = B200_OK;
   if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess)

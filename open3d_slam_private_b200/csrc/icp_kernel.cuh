@@ -79,6 +79,8 @@ struct IcpKernelParams {
   int fast_path;            // 0: always run the general 4-barrier iteration
   int coh_log2;             // log2 of the run of consecutive scan points a warp keeps together (0..5), see query_of;
                             // < 0: chosen per iteration by the kernel
+  int qpw_log2;             // log2 of the queries a warp holds (2..5); < 0 on input: chosen by the launcher
+  int warm_start;           // seed every search after the first iteration with the query's previous match
   unsigned* dbg_warp;       // debug: per warp slot of iteration 0: {rows, candidates, passes, ns} (nullable)
   int debug_stats;          // collect IcpLogEntry::dbg_* (adds global atomics; profiling aid only)
   const float* frames;      // 16-float blocks: T_refIn_refMean, T_refMean_readMean, T_readIn_readMean, (centroid),

@@ -277,9 +277,43 @@ __device__ __forceinline__ unsigned long long key1(float d, int id) {
   return ((unsigned long long)__float_as_uint(d) << 32) | (unsigned)id;
 }
 
+// Rows longer than this are scanned by the whole warp (32 consecutive candidates per load, one 512-byte request)
+// instead of by the lane that owns them: on a non-uniform target (a raw LiDAR scan: cells near the sensor hold tens
+// of points, far ones a single point) one lane walking a crowded row kept the other 31 waiting.
+constexpr uint32_t kLongRow = 12u;
+
+// All 32 lanes scan candidates [a, b) for ONE query (warp-uniform arguments); every lane returns the warp's best
+// (d, id, sorted position), id = -1 when no candidate lies within maxDist.
+__device__ __forceinline__ void warp_scan_row1(const GridView& g, float qx, float qy, float qz, float md2, uint32_t a,
+                                               uint32_t b, float& d, int& id, int& sp) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const uint32_t lane = threadIdx.x & 31u;
+  float ld = INFINITY;
+  int lid = -1, lsp = -1;
+  for (uint32_t j0 = a; j0 < b; j0 += 64u) {   // two independent loads per lane in flight
+    const uint32_t j = j0 + lane, j2 = j + 32u;
+    const float4 p0 = __ldg(&g.pts[min(j, b - 1u)]), p1 = __ldg(&g.pts[min(j2, b - 1u)]);
+    const float d0 = dist2_rn(qx, qy, qz, p0.x, p0.y, p0.z), d1 = dist2_rn(qx, qy, qz, p1.x, p1.y, p1.z);
+    if (j < b && d0 <= md2 && better1(d0, __float_as_int(p0.w), ld, lid)) { ld = d0; lid = __float_as_int(p0.w); lsp = (int)j; }
+    if (j2 < b && d1 <= md2 && better1(d1, __float_as_int(p1.w), ld, lid)) { ld = d1; lid = __float_as_int(p1.w); lsp = (int)j2; }
+  }
+  const unsigned long long mine = key1(ld, lid);
+  unsigned long long k = mine;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long t = __shfl_xor_sync(FULL, k, o);
+    k = t < k ? t : k;
+  }
+  const unsigned who = __ballot_sync(FULL, mine == k);   // ids are unique: one lane unless nothing was found
+  d = __uint_as_float((unsigned)(k >> 32));
+  id = (int)(unsigned)(k & 0xffffffffull);
+  sp = __shfl_sync(FULL, lsp, __ffs(who) - 1);
+}
+
 __device__ inline void knn_query_warp1(const GridView& g, bool active, float qx, float qy, float qz, float md2,
                                        float& best_d, int& best_id, int& best_sp, unsigned& visited, Warp1Scratch& ws,
-                                       unsigned* rows_out = nullptr, unsigned* passes_out = nullptr) {
+                                       unsigned* rows_out = nullptr, unsigned* passes_out = nullptr,
+                                       bool coop_first = false, int hint_sp = -1) {
   constexpr unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   best_d = INFINITY; best_id = -1; best_sp = -1;
@@ -292,24 +326,87 @@ __device__ inline void knn_query_warp1(const GridView& g, bool active, float qx,
     need = false;
   }
   float h = need ? first_halfwidth(g, q) : 0.f;
+  // Warm start: hint_sp is the sorted position of a point the caller believes to be close (the previous iteration's
+  // match). Its distance bounds the neighbour's, so the first box shrinks from the 2x2x2 block to the cells the ball of
+  // that radius touches — still every point at that distance or closer, so the answer (ties included) is unchanged.
+  if (need && hint_sp >= 0) {
+    const float4 hp = __ldg(&g.pts[hint_sp]);
+    const float hd = dist2_rn(q.qx, q.qy, q.qz, hp.x, hp.y, hp.z);
+    if (hd <= q.md2) {
+      best_d = hd; best_id = __float_as_int(hp.w); best_sp = hint_sp;
+      h = fminf(h, need_radius(g, q, hd));
+    }
+  }
   // ---- pass 1, per lane: the 2x2x2 block around the query. Every lane has the same <= 4 rows of work, so there is
   // nothing to balance and no shuffle traffic; near convergence this pass settles every query. All cell-table
   // loads are issued before the first candidate is touched.
-  if (need && h <= 0.5f) {
-    const CellBox B = ball_box(g, q.ux, q.uy, q.uz, h + q.slack);
-    if (B.y1 - B.y0 <= 1 && B.z1 - B.z0 <= 1) {
-      uint32_t ra[4], rb[4];
+  {
+    CellBox B;
+    B.x0 = B.y0 = B.z0 = 1; B.x1 = B.y1 = B.z1 = 0;
+    // coop_first (warp-uniform): few lanes carry a query, so even the first box is dealt row by row to all 32 lanes
+    bool p1 = need && h <= 0.5f && !coop_first;
+    if (p1) {
+      B = ball_box(g, q.ux, q.uy, q.uz, h + q.slack);
+      p1 = B.y1 - B.y0 <= 1 && B.z1 - B.z0 <= 1;
+    }
+    uint32_t ra[4] = {0u, 0u, 0u, 0u}, rb[4] = {0u, 0u, 0u, 0u};
+    if (p1) {
 #pragma unroll
       for (int r = 0; r < 4; ++r) {
         const int iy = B.y0 + (r & 1), iz = B.z0 + (r >> 1);
-        ra[r] = 0u; rb[r] = 0u;
         if (iy <= B.y1 && iz <= B.z1 && B.x0 <= B.x1) {
           const uint32_t* row = g.G + ((size_t)g.nx * ((size_t)iy + (size_t)g.ny * (size_t)iz));
           ra[r] = __ldg(row + B.x0); rb[r] = __ldg(row + B.x1 + 1);
           if (rows_out) ++*rows_out;
         }
       }
+    }
+    // crowded rows: the whole warp scans them, one (lane, row) after the other
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const bool longr = p1 && rb[r] > ra[r] && rb[r] - ra[r] > kLongRow;
+      unsigned m = __ballot_sync(FULL, longr);
+      while (m) {
+        const int src = __ffs(m) - 1;
+        m &= m - 1u;
+        const uint32_t a = __shfl_sync(FULL, ra[r], src), b = __shfl_sync(FULL, rb[r], src);
+        const float sx = __shfl_sync(FULL, q.qx, src), sy = __shfl_sync(FULL, q.qy, src), sz = __shfl_sync(FULL, q.qz, src);
+        const float smd = __shfl_sync(FULL, q.md2, src);
+        float d; int id, sp;
+        warp_scan_row1(g, sx, sy, sz, smd, a, b, d, id, sp);
+        if (lane == src) {
+          visited += b - a;
+          if (id >= 0 && better1(d, id, best_d, best_id)) { best_d = d; best_id = id; best_sp = sp; }
+        }
+      }
+      if (longr) rb[r] = ra[r];   // done
+    }
+    if (p1) {
       auto visit = [&](float d, int id, int sp) { if (better1(d, id, best_d, best_id)) { best_d = d; best_id = id; best_sp = sp; } };
+#ifdef B200_KNN_HEAD
+      // the first kHead candidates of all four rows in flight together (one memory latency instead of one per row)
+      {
+        constexpr uint32_t kHead = B200_KNN_HEAD;
+        float4 c[4][kHead];
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+          for (uint32_t t = 0; t < kHead; ++t)
+            if (ra[r] + t < rb[r]) c[r][t] = __ldg(&g.pts[ra[r] + t]);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+#pragma unroll
+          for (uint32_t t = 0; t < kHead; ++t)
+            if (ra[r] + t < rb[r]) {
+              const float d = dist2_rn(q.qx, q.qy, q.qz, c[r][t].x, c[r][t].y, c[r][t].z);
+              if (d <= q.md2) visit(d, __float_as_int(c[r][t].w), (int)(ra[r] + t));
+            }
+          const uint32_t n = min(rb[r] - ra[r], kHead);
+          visited += n;
+          ra[r] += n;
+        }
+      }
+#endif
 #pragma unroll
       for (int r = 0; r < 4; ++r)
         if (rb[r] > ra[r]) scan_range(g, q, ra[r], rb[r], visited, visit);
@@ -400,7 +497,20 @@ __device__ inline void knn_query_warp1(const GridView& g, bool active, float qx,
         const int o = own[s] & 31;
         float ld = INFINITY;
         int lid = -1, lsp = -1;
-        if (own[s] >= 0 && rb[s] > ra[s]) {
+        const bool has = own[s] >= 0 && rb[s] > ra[s];
+        const bool longr = has && rb[s] - ra[s] > kLongRow;
+        unsigned lm = __ballot_sync(FULL, longr);
+        while (lm) {   // crowded rows: the whole warp scans them, one item after the other
+          const int src = __ffs(lm) - 1;
+          lm &= lm - 1u;
+          const uint32_t a = __shfl_sync(FULL, ra[s], src), b = __shfl_sync(FULL, rb[s], src);
+          const int so = __shfl_sync(FULL, o, src);
+          const float4 op = ws.pos[so];
+          float d; int id, sp;
+          warp_scan_row1(g, op.x, op.y, op.z, ws.misc[so].x, a, b, d, id, sp);
+          if (lane == src) { visited += b - a; ld = d; lid = id; lsp = sp; }
+        }
+        if (has && !longr) {
           const float4 op = ws.pos[o];
           QueryGeom oq;
           oq.qx = op.x; oq.qy = op.y; oq.qz = op.z; oq.md2 = ws.misc[o].x;
