@@ -280,7 +280,22 @@ __device__ __forceinline__ unsigned long long key1(float d, int id) {
 // Rows longer than this are scanned by the whole warp (32 consecutive candidates per load, one 512-byte request)
 // instead of by the lane that owns them: on a non-uniform target (a raw LiDAR scan: cells near the sensor hold tens
 // of points, far ones a single point) one lane walking a crowded row kept the other 31 waiting.
-constexpr uint32_t kLongRow = 12u;
+constexpr uint32_t kLongRow = 16u;
+
+// Which rows to share: the warp scans the shared rows one after the other (~1.5 load round trips each), while a lane
+// on its own needs len / 4 of them. Sharing the rows longer than theta pays while their number stays below theta / 6
+// (one crowded cell among sparse ones: yes; a coherent warp that meets a dense patch as a whole: no). `len` = this
+// lane's longest row (0: none). Returns the threshold (warp-uniform), 0xffffffff = share nothing.
+__device__ __forceinline__ uint32_t long_row_threshold(uint32_t len) {
+  uint32_t theta = kLongRow;
+  while (theta <= 512u) {
+    const int c = __popc(__ballot_sync(0xffffffffu, len > theta));
+    if (c == 0) return 0xffffffffu;
+    if ((uint32_t)c * 6u <= theta) return theta;
+    theta <<= 1;
+  }
+  return 0xffffffffu;
+}
 
 // All 32 lanes scan candidates [a, b) for ONE query (warp-uniform arguments); every lane returns the warp's best
 // (d, id, sorted position), id = -1 when no candidate lies within maxDist.
@@ -362,9 +377,14 @@ __device__ inline void knn_query_warp1(const GridView& g, bool active, float qx,
       }
     }
     // crowded rows: the whole warp scans them, one (lane, row) after the other
+    uint32_t mylen = 0u;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) mylen = max(mylen, rb[r] - ra[r]);
+    if (__any_sync(FULL, mylen > kLongRow)) {
+    const uint32_t theta = long_row_threshold(mylen);
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
-      const bool longr = p1 && rb[r] > ra[r] && rb[r] - ra[r] > kLongRow;
+      const bool longr = rb[r] - ra[r] > theta;
       unsigned m = __ballot_sync(FULL, longr);
       while (m) {
         const int src = __ffs(m) - 1;
@@ -381,32 +401,9 @@ __device__ inline void knn_query_warp1(const GridView& g, bool active, float qx,
       }
       if (longr) rb[r] = ra[r];   // done
     }
+    }
     if (p1) {
       auto visit = [&](float d, int id, int sp) { if (better1(d, id, best_d, best_id)) { best_d = d; best_id = id; best_sp = sp; } };
-#ifdef B200_KNN_HEAD
-      // the first kHead candidates of all four rows in flight together (one memory latency instead of one per row)
-      {
-        constexpr uint32_t kHead = B200_KNN_HEAD;
-        float4 c[4][kHead];
-#pragma unroll
-        for (int r = 0; r < 4; ++r)
-#pragma unroll
-          for (uint32_t t = 0; t < kHead; ++t)
-            if (ra[r] + t < rb[r]) c[r][t] = __ldg(&g.pts[ra[r] + t]);
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-#pragma unroll
-          for (uint32_t t = 0; t < kHead; ++t)
-            if (ra[r] + t < rb[r]) {
-              const float d = dist2_rn(q.qx, q.qy, q.qz, c[r][t].x, c[r][t].y, c[r][t].z);
-              if (d <= q.md2) visit(d, __float_as_int(c[r][t].w), (int)(ra[r] + t));
-            }
-          const uint32_t n = min(rb[r] - ra[r], kHead);
-          visited += n;
-          ra[r] += n;
-        }
-      }
-#endif
 #pragma unroll
       for (int r = 0; r < 4; ++r)
         if (rb[r] > ra[r]) scan_range(g, q, ra[r], rb[r], visited, visit);
@@ -491,6 +488,10 @@ __device__ inline void knn_query_warp1(const GridView& g, bool active, float qx,
         }
       }
       // ---- phase B: scan, fold into the owner's key
+      uint32_t mylen = 0u;
+#pragma unroll
+      for (int s = 0; s < kItems; ++s) mylen = max(mylen, rb[s] - ra[s]);
+      const uint32_t theta = __any_sync(FULL, mylen > kLongRow) ? long_row_threshold(mylen) : 0xffffffffu;
 #pragma unroll
       for (int s = 0; s < kItems; ++s) {
         if (base + s * 32 >= total) break;  // warp-uniform
@@ -498,8 +499,8 @@ __device__ inline void knn_query_warp1(const GridView& g, bool active, float qx,
         float ld = INFINITY;
         int lid = -1, lsp = -1;
         const bool has = own[s] >= 0 && rb[s] > ra[s];
-        const bool longr = has && rb[s] - ra[s] > kLongRow;
-        unsigned lm = __ballot_sync(FULL, longr);
+        const bool longr = has && rb[s] - ra[s] > theta;
+        unsigned lm = theta != 0xffffffffu ? __ballot_sync(FULL, longr) : 0u;
         while (lm) {   // crowded rows: the whole warp scans them, one item after the other
           const int src = __ffs(lm) - 1;
           lm &= lm - 1u;
