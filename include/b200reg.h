@@ -254,6 +254,29 @@ int b200_icp_compute_o3d(b200_icp* icp, const double* pts3xN, const double* nrm3
  * upload once, then run any number of times. */
 int b200_icp_upload_reading(b200_icp* icp, const float* read4xN, const float* readn3xN, int N);
 int b200_icp_run_resident(b200_icp* icp, const float* Tinit16, b200_icp_result* res);
+/* The same chain over a SPATIALLY PARTITIONED map (BASELINE config C5): one handle per rank holds one
+ * slab of the map padded by maxDist; the scan is replicated. Per iteration of ICP::computeWithTransformedReference
+ * (ICP.cpp:1027-1311):
+ *   b200_icp_slab_match    matcher->findClosests (:1051) for the queries the rank owns under the current pose; writes
+ *                          the exchange arrays on the device: d_match9xN = N float4 matched points | N float4 matched
+ *                          normals | N float squared distances, d_idN = N global indices; zeros for queries of other
+ *                          ranks. The caller sums both arrays over the ranks (one all-reduce each; nothing to do for
+ *                          a single slab);
+ *   b200_icp_slab_iterate  outlierFilters.compute incl. TrimmedDist's quantile over ALL pairs (:1055,
+ *                          OutlierFiltersImpl.cpp:140-147, Matches.cpp:60-87), ErrorElements, errorMinimizer->compute,
+ *                          T_iter update, transformationCheckers.check (:1292) on the summed arrays; *iterate = 0 when
+ *                          a checker stopped the loop (or it failed: see the result's status).
+ * Every rank computes the same pose from the same sums (no broadcast). Result, iteration count, matches and weights
+ * are bit-identical to b200_icp_compute on one device holding the whole map. knn = 1, degeneracyAwareness None.
+ * gid_M: global index of every slab point (null: identity); map_mean3: centroid of the WHOLE map (the reference frame
+ * of ICP.cpp:883-890 is the whole map's); [lo, hi): the rank's own interval along axis (0..2), map frame, +-inf at
+ * the ends. d_* are DEVICE pointers of the caller (e.g. torch tensors) on the handle's device. */
+int b200_icp_init_reference_slab(b200_icp* icp, const float* ref4xM, const float* refn3xM, int M, const int32_t* gid_M,
+                                 const double* map_mean3, int axis, float lo, float hi);
+int b200_icp_slab_begin(b200_icp* icp, const float* read4xN, const float* readn3xN, int N, const float* Tinit16);
+int b200_icp_slab_match(b200_icp* icp, float* d_match9xN, int32_t* d_idN);
+int b200_icp_slab_iterate(b200_icp* icp, const float* d_match9xN, const int32_t* d_idN, int* iterate);
+int b200_icp_slab_finish(b200_icp* icp, b200_icp_result* res);
 /* ICP::matches / ICP::outlierWeights of the last iteration (PointMatcher.h ICPChainBase members) */
 int b200_icp_get_matches(b200_icp* icp, int32_t* ids_kxN, float* dists_kxN, float* weights_kxN);
 /* per-iteration trace (first max_log iterations): H 36, b 6, x 6, T_iter 16 floats, P int. Returns count in *n. */

@@ -401,6 +401,34 @@ class ICP:
                                          _fp(Tc), C.byref(res))
         return self._result(res, st, raise_on_error)
 
+    # ---- partitioned map (b200_icp_slab_*): this handle holds one padded slab; d_* are device pointers (int)
+    def init_reference_slab(self, slab4, normals, gid, map_mean, axis, lo, hi):
+        self._ref4, self._refn = f32(slab4), f32(normals)
+        self._gid = None if gid is None else np.ascontiguousarray(gid, np.int32)
+        mean = np.ascontiguousarray(map_mean, np.float64)
+        _check(load().b200_icp_init_reference_slab(self.h, _fp(self._ref4), _fp(self._refn), self._ref4.shape[0],
+                                                   _ip(self._gid), mean.ctypes.data_as(C.POINTER(C.c_double)), int(axis),
+                                                   C.c_float(lo), C.c_float(hi)))
+
+    def slab_begin(self, read4, normals=None, T_init=None):
+        read4, normals = f32(read4), f32(normals)
+        self._n = read4.shape[0]
+        Tc = None if T_init is None else _colmajor(T_init)
+        _check(load().b200_icp_slab_begin(self.h, _fp(read4), _fp(normals), self._n, _fp(Tc)))
+
+    def slab_match(self, d_match, d_ids):
+        _check(load().b200_icp_slab_match(self.h, C.c_void_p(int(d_match)), C.c_void_p(int(d_ids))))
+
+    def slab_iterate(self, d_match, d_ids):
+        it = C.c_int()
+        _check(load().b200_icp_slab_iterate(self.h, C.c_void_p(int(d_match)), C.c_void_p(int(d_ids)), C.byref(it)))
+        return bool(it.value)
+
+    def slab_finish(self, raise_on_error=True):
+        res = IcpResult()
+        st = load().b200_icp_slab_finish(self.h, C.byref(res))
+        return self._result(res, st, raise_on_error)
+
     def upload_reading(self, read4, normals=None):
         read4, normals = f32(read4), f32(normals)
         self._n = read4.shape[0]

@@ -233,7 +233,11 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
   const int gtid = blockIdx.x * kIcpThreads + tid;
   const int k = p.k;
 
-  if (tid == 0) {
+  static_assert(sizeof(BlockState) <= (size_t)kIcpStateWords * sizeof(unsigned), "resumable state does not fit");
+  if (p.resume) {
+    for (int t = tid; t < (int)(sizeof(BlockState) / sizeof(unsigned)); t += kIcpThreads)
+      reinterpret_cast<unsigned*>(&S)[t] = __ldcg(&p.state[t]);
+  } else if (tid == 0) {
     eye4(S.T_iter);
     S.iterate = 1; S.status = B200_OK; S.iteration = 0; S.maxReached = 0;
     S.counter = 0.f;
@@ -260,6 +264,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
 
   const bool stamp = (blockIdx.x == 0 && tid == 0 && p.log != nullptr);
   unsigned long long ts[6] = {0ull, 0ull, 0ull, 0ull, 0ull, 0ull};
+  int launch_iters = 0;
   while (true) {
     if (stamp) ts[0] = gtimer();
     if (tid == 0) {
@@ -332,6 +337,13 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
         // warm start from the previous iteration's match of the same query (its own thread wrote it or, after a change
         // of the query map, another CTA did before the barrier that closed that iteration)
         const int hint = (in && S.iteration > 0 && p.warm_start) ? __ldcg(&p.spos[i]) : -1;
+        if (p.forced) {   // the match was found elsewhere (partitioned map); its point and normal sit at position i
+          bd = INFINITY; bid = -1; bsp = -1;
+          if (in) {
+            bd = __ldcg(&p.forced_dist[i]); bid = __ldcg(&p.forced_id[i]);
+            if (bid >= 0) bsp = i; else bd = INFINITY;
+          }
+        } else
         knn_query_warp1(p.g, in, q.x, q.y, q.z, p.md2, bd, bid, bsp, vis, reinterpret_cast<Warp1Scratch*>(s_dyn)[wid],
                         p.debug_stats ? &w_rows : nullptr, p.debug_stats ? &w_pass : nullptr, qpw < 32, hint);
         if (p.debug_stats) {
@@ -1187,6 +1199,12 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     }
     __syncthreads();
     if (!S.iterate) break;
+    if (p.max_launch_iters > 0 && ++launch_iters >= p.max_launch_iters) break;
+  }
+  if (p.state && blockIdx.x == 0) {   // every CTA holds the same state; CTA 0 saves it for the next launch
+    __syncthreads();
+    for (int t = tid; t < (int)(sizeof(BlockState) / sizeof(unsigned)); t += kIcpThreads)
+      __stcg(&p.state[t], reinterpret_cast<const unsigned*>(&S)[t]);
   }
 
   // points touched: one atomic per warp
@@ -1201,6 +1219,7 @@ __global__ void __launch_bounds__(kIcpThreads, 2) icp_persistent_kernel(const __
     o->status = S.status;
     o->iterations = S.iteration;
     o->max_iterations_reached = S.maxReached;
+    o->iterate = S.iterate;
     o->n_matches_last = S.P;
     for (int t = 0; t < 16; ++t) o->T_iter[t] = S.T_iter[t];
     // move the result back to the callers' frames, ICP.cpp:1345

@@ -5,6 +5,7 @@
 #include "common.cuh"
 #include "grid_index.cuh"
 #include "icp_kernel.cuh"
+#include "knn.cuh"
 #include "solve.cuh"
 #include <algorithm>
 #include <cmath>
@@ -15,7 +16,7 @@
 using namespace b200;
 
 namespace b200 {
-int icp_reference_from_device(b200_icp* h, int M, bool has_normals);
+int icp_reference_from_device(b200_icp* h, int M, bool has_normals, const double* mean_given = nullptr);
 float4* icp_reference_points(b200_icp* h, int M, bool with_normals, float4** normals_out, cudaStream_t* stream_out);
 }  // namespace b200
 
@@ -119,6 +120,54 @@ __global__ void flush_kernel(float4* __restrict__ buf, size_t n, float v) {
     buf[i] = make_float4(v, v, v, v);
 }
 
+// Partitioned map, first half of an iteration on one rank: every query the rank owns (its position under the current
+// pose lies in the rank's interval [lo, hi) along `axis`) is matched against the rank's padded slab; the distance, the
+// GLOBAL index, the matched point and its normal go to the exchange arrays, all other entries are zero — so that the
+// sum over the ranks (one all-reduce) is the complete set of matches, bit for bit what one device holding the whole map
+// would have found (a neighbour within maxDist of an owned query lies inside the padded slab; ties go to the smallest
+// global index because a slab keeps the map's order). state: the resumable block state of the persistent kernel
+// (its first 16 floats are T_iter), null before the first iteration (T_iter = identity).
+__global__ void __launch_bounds__(256) slab_match_kernel(GridView g, const int* __restrict__ gid,
+                                                         const float4* __restrict__ reading, int N, float md2,
+                                                         const unsigned* __restrict__ state, int axis, float lo, float hi,
+                                                         float4* __restrict__ m_pt, float4* __restrict__ m_nrm,
+                                                         float* __restrict__ m_dist, int* __restrict__ m_id) {
+  __shared__ float T[16], Tc[16], R9[9];
+  __shared__ Warp1Scratch s_ws[256 / 32];
+  if (threadIdx.x == 0) {
+    if (state) for (int t = 0; t < 16; ++t) T[t] = __uint_as_float(state[t]);
+    else eye4(T);
+    rigid_prepare(T, Tc, R9);   // transformations.apply incl. correctParameters, as the persistent kernel does
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int nthreads = gridDim.x * blockDim.x;
+  for (int base = blockIdx.x * blockDim.x + wid * 32; base < N; base += nthreads) {
+    const int i = base + lane;
+    const bool in = i < N;
+    const float4 q = in ? apply_T(Tc, __ldg(&reading[i])) : make_float4(0.f, 0.f, 0.f, 1.f);
+    const float c = axis == 0 ? q.x : (axis == 1 ? q.y : q.z);
+    const bool mine = in && c >= lo && c < hi;   // (a NaN coordinate belongs to nobody: no match, like the search)
+    float bd; int bid, bsp;
+    unsigned vis = 0;
+    knn_query_warp1(g, mine, q.x, q.y, q.z, md2, bd, bid, bsp, vis, s_ws[wid]);
+    if (!in) continue;
+    float4 pt = make_float4(0.f, 0.f, 0.f, 0.f), nr = pt;
+    float d = 0.f;
+    int id = 0;
+    if (mine) {
+      d = bd; id = -1;
+      if (bid >= 0) {
+        id = gid ? __ldg(&gid[bid]) : bid;
+        const float4 t = __ldg(&g.pts[bsp]);
+        pt = make_float4(t.x, t.y, t.z, 0.f);
+        if (g.nrm) { const float4 n = __ldg(&g.nrm[bsp]); nr = make_float4(n.x, n.y, n.z, 0.f); }
+      }
+    }
+    m_pt[i] = pt; m_nrm[i] = nr; m_dist[i] = d; m_id[i] = id;
+  }
+}
+
 }  // namespace
 
 constexpr int kFrameFloats = 96;
@@ -164,6 +213,16 @@ struct b200_icp {
   int debug_stats = 0;  // env B200_ICP_DEBUG=1
   unsigned* d_dbg_warp = nullptr;
   size_t cap_dbg_warp = 0;
+  // partitioned map (b200_icp_slab_*): this handle's index holds one padded slab of the map
+  bool slab = false;
+  int slab_axis = 0;
+  float slab_lo = 0.f, slab_hi = 0.f;      // owned interval along slab_axis, in the <refMean> frame
+  int* d_gid = nullptr;                    // global index of every slab point (original order of the slab)
+  size_t cap_gid = 0;
+  unsigned* d_state = nullptr;             // resumable block state of the persistent kernel (kIcpStateWords)
+  int slab_started = 0;                    // 0: no registration open, 1: begun, no iteration yet, 2: iterating
+  int slab_iterate = 0;
+  bool slab_has_gid = false;
 };
 
 namespace {
@@ -258,7 +317,28 @@ int check_params(const b200_icp_params* p) {
   return B200_OK;
 }
 
+int icp_fill_params(b200_icp* h, IcpKernelParams& p);
+int icp_prologue(b200_icp* h, const float* Tinit16);
+int icp_result(b200_icp* h, b200_icp_result* res, bool timed_upload);
+
 int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool timed_upload) {
+  if (h->slab) { set_error("this handle holds one slab of a partitioned map: use b200_icp_slab_*"); return B200_E_BAD_PARAM; }
+  cudaStream_t s = h->stream;
+  B200_TRY(icp_prologue(h, Tinit16));
+  IcpKernelParams p;
+  B200_TRY(icp_fill_params(h, p));
+  B200_CUDA(cudaEventRecord(h->ev[2], s));
+  B200_TRY(launch_icp_kernel(p, h->device, s, &h->last_grid));
+  B200_CUDA(cudaEventRecord(h->ev[3], s));
+  B200_CUDA(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(IcpDeviceResult), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaMemcpyAsync(h->h_frames, h->d_frames, kFrameFloats * sizeof(float), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaEventRecord(h->ev[4], s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  return icp_result(h, res, timed_upload);
+}
+
+// mean of the reading, frames, reading in the <refMean> frame; work buffers cleared (one registration = one prologue)
+int icp_prologue(b200_icp* h, const float* Tinit16) {
   cudaStream_t s = h->stream;
   const int N = h->N;
   if (Tinit16) std::memcpy(h->h_Tinit, Tinit16, 16 * sizeof(float));
@@ -275,7 +355,12 @@ int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool tim
   B200_CUDA(cudaGetLastError());
   B200_CUDA(cudaMemsetAsync(h->d_hist, 0, ((size_t)2 * 3 * kHistBins + 2) * sizeof(unsigned), s));
   B200_CUDA(cudaMemsetAsync(h->d_out, 0, sizeof(IcpDeviceResult), s));
-  IcpKernelParams p;
+  if (h->debug_stats) B200_CUDA(cudaMemsetAsync(h->d_log, 0, (size_t)kMaxLog * sizeof(IcpLogEntry), s));
+  return B200_OK;
+}
+
+int icp_fill_params(b200_icp* h, IcpKernelParams& p) {
+  const int N = h->N;
   std::memset(&p, 0, sizeof(p));
   p.g = h->map.view();
   p.reading = h->d_read;
@@ -307,7 +392,6 @@ int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool tim
     }
     p.dbg_warp = h->d_dbg_warp;
   }
-  if (h->debug_stats) B200_CUDA(cudaMemsetAsync(h->d_log, 0, (size_t)kMaxLog * sizeof(IcpLogEntry), s));
   p.xicp = h->prm.degeneracy == B200_DEGENERACY_OPTIMIZED_EQUALITY ? 1 : 0;
   p.x_enough = h->prm.xicp_enough_information; p.x_insufficient = h->prm.xicp_insufficient_information;
   // ICP.cpp:648-665: cos(convertAngleInDegreesToRadians(angle)) in float
@@ -316,13 +400,10 @@ int icp_launch(b200_icp* h, const float* Tinit16, b200_icp_result* res, bool tim
   p.partials2 = h->d_partials2;
   p.list_count = h->d_hist + (size_t)2 * 3 * kHistBins;
   p.hist = h->d_hist; p.partials = h->d_partials; p.out = h->d_out; p.log = h->d_log; p.frames = h->d_frames;
-  B200_CUDA(cudaEventRecord(h->ev[2], s));
-  B200_TRY(launch_icp_kernel(p, h->device, s, &h->last_grid));
-  B200_CUDA(cudaEventRecord(h->ev[3], s));
-  B200_CUDA(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(IcpDeviceResult), cudaMemcpyDeviceToHost, s));
-  B200_CUDA(cudaMemcpyAsync(h->h_frames, h->d_frames, kFrameFloats * sizeof(float), cudaMemcpyDeviceToHost, s));
-  B200_CUDA(cudaEventRecord(h->ev[4], s));
-  B200_CUDA(cudaStreamSynchronize(s));
+  return B200_OK;
+}
+
+int icp_result(b200_icp* h, b200_icp_result* res, bool timed_upload) {
   if (res) {
     std::memset(res, 0, sizeof(*res));
     const IcpDeviceResult& o = *h->h_out;
@@ -438,6 +519,7 @@ void b200_icp_destroy(b200_icp* h) {
     cudaFree(h->d_cand_d); cudaFree(h->d_cand_q); cudaFree(h->d_cand_rec);
     cudaFree(h->d_hist); cudaFree(h->d_partials); cudaFree(h->d_partials2); cudaFree(h->d_meanpart); cudaFree(h->d_out); cudaFree(h->d_log);
     cudaFree(h->d_frames); cudaFree(h->d_Tinit); cudaFree(h->d_flush); cudaFree(h->d_dbg_warp); cudaFree(h->d_o3d);
+    cudaFree(h->d_gid); cudaFree(h->d_state);
     cudaFreeHost(h->h_out); cudaFreeHost(h->h_frames); cudaFreeHost(h->h_Tinit);
     for (int i = 0; i < 5; ++i)
       if (h->ev[i]) cudaEventDestroy(h->ev[i]);
@@ -489,7 +571,7 @@ float4* icp_reference_points(b200_icp* h, int M, bool with_normals, float4** nor
 
 // the rest of ICP::initReference (ICP.cpp:847-898) on a reference resident in h->map.d_ref / d_nrm_orig:
 // mean-centre, build the index, store T_refIn_refMean
-int icp_reference_from_device(b200_icp* h, int M, bool has_normals) {
+int icp_reference_from_device(b200_icp* h, int M, bool has_normals, const double* mean_given) {
   if (h->prm.minimizer == 0 && !has_normals) {  // InvalidField at getDescriptorViewByName("normals"), ICP.cpp:1519
     set_error("PointToPlaneErrorMinimizer needs the 'normals' descriptor on the reference");
     return B200_E_BAD_PARAM;
@@ -498,10 +580,12 @@ int icp_reference_from_device(b200_icp* h, int M, bool has_normals) {
   if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
   cudaStream_t s = h->stream;
   h->ref_ready = false;
+  h->slab = false;
   h->ref_has_normals = has_normals;
   // centroid in double, rounded to float; reference expressed in <refMean> (ICP.cpp:883-890)
   double mean[3];
-  B200_TRY(device_mean3(h->map.d_ref, M, h->d_meanpart, mean, s));
+  if (mean_given) { mean[0] = mean_given[0]; mean[1] = mean_given[1]; mean[2] = mean_given[2]; }   // (a slab: the whole map's)
+  else B200_TRY(device_mean3(h->map.d_ref, M, h->d_meanpart, mean, s));
   const float mf[3] = {(float)mean[0], (float)mean[1], (float)mean[2]};
   B200_TRY(device_subtract3(h->map.d_ref, M, mf[0], mf[1], mf[2], s));
   b200_index_opts opts;
@@ -704,6 +788,136 @@ int b200_icp_flush_l2(b200_icp* h) {
   flush_kernel<<<148 * 8, 256, 0, h->stream>>>(h->d_flush, h->flush_elems, 1.0f);
   B200_CUDA(cudaGetLastError());
   return B200_OK;
+}
+
+// ---- partitioned map (BASELINE C5) with the libpointmatcher chain ----------------------------------------
+// One handle per rank holds one padded slab of the map. An iteration is: b200_icp_slab_match on every rank (searches
+// for the queries the rank owns, zeros elsewhere) -> the caller sums the exchange arrays over the ranks (ONE all-reduce
+// of 9 N floats and one of N int32; NCCL or a plain add when several slabs share a device) -> b200_icp_slab_iterate on
+// every rank: the persistent kernel, told to take the matches as given, runs the rest of the iteration (outlier chain
+// incl. TrimmedDist's global quantile, ErrorElements, H/b, solve, pose update, checkers) and stops; its block state
+// (pose, checker history, ...) stays on the device for the next launch. Every rank computes the same pose from the
+// same sums: no broadcast. The result equals the un-partitioned b200_icp_compute bit for bit (tests/test_gpu_slab_pm.py).
+
+int b200_icp_init_reference_slab(b200_icp* h, const float* ref4xM, const float* refn3xM, int M, const int32_t* gid_M,
+                                 const double* map_mean3, int axis, float lo, float hi) {
+  if (!h || M <= 0 || !ref4xM || !map_mean3 || axis < 0 || axis > 2 || !(lo < hi)) {
+    set_error("b200_icp_init_reference_slab: bad arguments");
+    return B200_E_BAD_PARAM;
+  }
+  if (h->prm.knn != 1 || h->prm.degeneracy != B200_DEGENERACY_NONE) {
+    set_error("partitioned map: knn = 1 and degeneracyAwareness None only");
+    return B200_E_UNSUPPORTED;
+  }
+  if (h->prm.minimizer == 0 && !refn3xM) {
+    set_error("PointToPlaneErrorMinimizer needs the 'normals' descriptor on the reference");
+    return B200_E_BAD_PARAM;
+  }
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  cudaStream_t s = h->stream;
+  h->ref_ready = false;
+  B200_TRY(index_alloc_points(h->map, M, refn3xM != nullptr));
+  B200_TRY(upload_features(h->map.d_ref, ref4xM, M, s));
+  if (refn3xM) {
+    float* stage = nullptr;
+    B200_CUDA(cudaMallocAsync(&stage, (size_t)M * 3 * sizeof(float), s));
+    const int st = upload_normals(h->map.d_nrm_orig, refn3xM, M, stage, s);
+    cudaFreeAsync(stage, s);
+    if (st) return st;
+  }
+  if ((size_t)M > h->cap_gid) {
+    cudaFree(h->d_gid);
+    h->d_gid = nullptr; h->cap_gid = 0;
+    B200_CUDA(cudaMalloc(&h->d_gid, (size_t)M * sizeof(int)));
+    h->cap_gid = (size_t)M;
+  }
+  if (gid_M) B200_CUDA(cudaMemcpyAsync(h->d_gid, gid_M, (size_t)M * sizeof(int), cudaMemcpyHostToDevice, s));
+  if (!h->d_state) B200_CUDA(cudaMalloc(&h->d_state, (size_t)kIcpStateWords * sizeof(unsigned)));
+  B200_TRY(icp_reference_from_device(h, M, refn3xM != nullptr, map_mean3));
+  // the interval in the frame the queries live in (<refMean>): the same float subtraction on every rank
+  const float mf = (float)map_mean3[axis];
+  h->slab = true;
+  h->slab_axis = axis;
+  h->slab_lo = std::isinf(lo) ? lo : lo - mf;
+  h->slab_hi = std::isinf(hi) ? hi : hi - mf;
+  h->slab_started = 0;
+  h->slab_has_gid = gid_M != nullptr;
+  return B200_OK;
+}
+
+int b200_icp_slab_begin(b200_icp* h, const float* read4xN, const float* readn3xN, int N, const float* Tinit16) {
+  if (!h || N <= 0 || !read4xN) { set_error("b200_icp_slab_begin: bad arguments"); return B200_E_BAD_PARAM; }
+  if (!h->ref_ready || !h->slab) { set_error("b200_icp_slab_begin: no slab reference (b200_icp_init_reference_slab)"); return B200_E_NOT_INITIALIZED; }
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  B200_TRY(icp_upload(h, read4xN, readn3xN, N));
+  B200_TRY(icp_prologue(h, Tinit16));
+  h->slab_started = 1;
+  h->slab_iterate = 1;
+  return B200_OK;
+}
+
+int b200_icp_slab_match(b200_icp* h, float* d_match9xN, int32_t* d_idN) {
+  if (!h || !d_match9xN || !d_idN) { set_error("b200_icp_slab_match: bad arguments"); return B200_E_BAD_PARAM; }
+  if (!h->slab || h->slab_started == 0) { set_error("b200_icp_slab_match: b200_icp_slab_begin first"); return B200_E_NOT_INITIALIZED; }
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  const int N = h->N;
+  float4* m_pt = reinterpret_cast<float4*>(d_match9xN);
+  float4* m_nrm = m_pt + N;
+  float* m_dist = d_match9xN + (size_t)8 * N;
+  const float md2 = std::isinf(h->prm.maxDist) ? INFINITY : h->prm.maxDist * h->prm.maxDist;
+  const int blocks = std::max(1, std::min(148 * 8, (N + 255) / 256));
+  slab_match_kernel<<<blocks, 256, 0, h->stream>>>(h->map.view(), h->slab_has_gid ? h->d_gid : nullptr, h->d_read, N, md2,
+                                                  h->slab_started == 2 ? h->d_state : nullptr, h->slab_axis, h->slab_lo,
+                                                  h->slab_hi, m_pt, m_nrm, m_dist, d_idN);
+  B200_CUDA(cudaGetLastError());
+  B200_CUDA(cudaStreamSynchronize(h->stream));   // the caller's exchange runs on its own stream
+  return B200_OK;
+}
+
+int b200_icp_slab_iterate(b200_icp* h, const float* d_match9xN, const int32_t* d_idN, int* iterate) {
+  if (!h || !d_match9xN || !d_idN || !iterate) { set_error("b200_icp_slab_iterate: bad arguments"); return B200_E_BAD_PARAM; }
+  if (!h->slab || h->slab_started == 0) { set_error("b200_icp_slab_iterate: b200_icp_slab_begin first"); return B200_E_NOT_INITIALIZED; }
+  if (!h->slab_iterate) { set_error("b200_icp_slab_iterate: the registration has ended"); return B200_E_BAD_PARAM; }
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  cudaStream_t s = h->stream;
+  const int N = h->N;
+  IcpKernelParams p;
+  B200_TRY(icp_fill_params(h, p));
+  p.forced = 1;
+  p.forced_dist = d_match9xN + (size_t)8 * N;
+  p.forced_id = d_idN;
+  p.g.pts = reinterpret_cast<const float4*>(d_match9xN);
+  p.g.nrm = h->ref_has_normals ? reinterpret_cast<const float4*>(d_match9xN) + N : nullptr;
+  p.max_launch_iters = 1;
+  p.resume = h->slab_started == 2 ? 1 : 0;
+  p.state = h->d_state;
+  B200_CUDA(cudaMemsetAsync(h->d_hist, 0, ((size_t)2 * 3 * kHistBins + 2) * sizeof(unsigned), s));
+  B200_TRY(launch_icp_kernel(p, h->device, s, &h->last_grid));
+  B200_CUDA(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(IcpDeviceResult), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  h->slab_started = 2;
+  h->slab_iterate = h->h_out->iterate;
+  *iterate = h->slab_iterate;
+  return B200_OK;
+}
+
+int b200_icp_slab_finish(b200_icp* h, b200_icp_result* res) {
+  if (!h || !res) { set_error("b200_icp_slab_finish: bad arguments"); return B200_E_BAD_PARAM; }
+  if (!h->slab || h->slab_started != 2) { set_error("b200_icp_slab_finish: no iteration has run"); return B200_E_NOT_INITIALIZED; }
+  DeviceGuard dg(h->device);
+  cudaStream_t s = h->stream;
+  B200_CUDA(cudaEventRecord(h->ev[2], s));
+  B200_CUDA(cudaEventRecord(h->ev[3], s));
+  B200_CUDA(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(IcpDeviceResult), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaMemcpyAsync(h->h_frames, h->d_frames, kFrameFloats * sizeof(float), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaEventRecord(h->ev[4], s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  h->slab_started = 0;
+  return icp_result(h, res, false);
 }
 
 }  // extern "C"

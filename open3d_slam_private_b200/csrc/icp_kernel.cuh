@@ -10,6 +10,7 @@ constexpr int kAccum = 32;             // doubles per CTA partial (29 used)
 constexpr int kMaxHist = 64;           // ring of past poses kept for DifferentialTransformationChecker
 constexpr int kMaxLog = 64;            // per-iteration trace capacity
 constexpr int kFastVals = 32;          // values reduced per pair on the single-barrier path (27 H/b + 5 counters)
+constexpr int kIcpStateWords = 4096;    // capacity (unsigned) of the resumable block state
 constexpr int kListCap = 16384;        // distances of the selected first-level bin resolved in shared memory (general shape)
 constexpr int kCandCap = 2048;         // bracket candidates the single-barrier path resolves in shared memory
 // 64 KiB staging tile + candidate distances and positions
@@ -44,6 +45,7 @@ struct IcpDeviceResult {
   float weighted_point_used_ratio;
   float point_used_ratio;
   unsigned long long points_touched;
+  int iterate;                 // 1: the launch stopped at its iteration budget, the registration goes on (resume)
   // X-ICP (IcpKernelParams::xicp): detection flags of the first iteration (1 = localizable), eigenvectors as they
   // stand after the last iteration, full alignment sums (double), prior returned (ICP.cpp:1335-1341), and whether a
   // decision fell inside the rounding band of the reference's sequential float sums
@@ -85,6 +87,19 @@ struct IcpKernelParams {
   int debug_stats;          // collect IcpLogEntry::dbg_* (adds global atomics; profiling aid only)
   const float* frames;      // 16-float blocks: T_refIn_refMean, T_refMean_readMean, T_readIn_readMean, (centroid),
                             // T_refMean_dataIn (ICP.cpp:975), its inverse
+  // Partitioned map: the matches of an iteration come from outside — every rank searches its own slab
+  // for the queries it owns (slab_match_kernel), the ranks sum their contributions, and this kernel runs the rest of
+  // the iteration on the complete set. forced = 1: no search; query i is matched to (forced_id[i], forced_dist[i]),
+  // and g.pts / g.nrm point at N-entry arrays holding the matched point and normal of query i (so every gather of
+  // "the match at sorted position sp" works unchanged with sp = i). k = 1 only.
+  int forced;
+  const float* forced_dist;
+  const int* forced_id;
+  // Launch budget and resumable state: at most max_launch_iters iterations per launch (0: no limit); with resume = 1
+  // the block state (pose, checker history, TrimmedDist bracket, ...) is restored from `state` instead of initialised,
+  // and it is saved there whenever `state` is given. kIcpStateWords unsigned.
+  int max_launch_iters, resume;
+  unsigned* state;
   // X-ICP, degeneracyAwareness = OptimizedEqualityConstraints (ICP.cpp:629-670); k = 1, point-to-plane only
   int xicp;
   float x_enough, x_insufficient, x_cos_min, x_cos_strong;

@@ -27,7 +27,7 @@ namespace b200 {
 int inclusive_scan_u32(uint32_t* d_data, size_t n, uint32_t* d_tile, cudaStream_t s);
 size_t scan_tiles_for(size_t n);
 // icp_host.cu: finishes ICP::initReference on a reference already resident in the handle's index buffers
-int icp_reference_from_device(b200_icp* h, int M, bool has_normals);
+int icp_reference_from_device(b200_icp* h, int M, bool has_normals, const double* mean_given = nullptr);
 float4* icp_reference_points(b200_icp* h, int M, bool with_normals, float4** normals_out, cudaStream_t* stream_out);
 }  // namespace b200
 

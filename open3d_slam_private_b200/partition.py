@@ -8,9 +8,12 @@ transformed coordinate), and every map point within the correspondence distance 
 slab, so the union of the ranks' correspondences is the single-device result (ids are global, ties go to the smallest
 global index because slabs keep the map order).
 
-The loop semantics are boundary B's (Open3D RegistrationICP: 1-NN within max_correspondence_distance, no global
-quantile); libpointmatcher's TrimmedDist would need two extra histogram allreduces per iteration and is not offered in
-this mode (stated deviation).
+Two loops run partitioned. SlabICP: boundary B's (Open3D RegistrationICP: 1-NN within max_correspondence_distance,
+no global quantile) with one 32-double exchange per iteration. SlabPmICP: the libpointmatcher chain of caller A
+(TrimmedDist's global quantile, float H/b, the reference's checkers): the ranks exchange the MATCHES of an iteration
+(every query is matched by the one rank that owns it; the sum over the ranks of the zero-filled arrays is the complete
+set), then every rank runs the rest of the iteration on all of them with the same persistent kernel that serves the
+un-partitioned registration — so the result is that registration's, bit for bit.
 """
 import numpy as np
 
@@ -157,6 +160,138 @@ def register_partitioned(map4, map_normals, src4, src_normals=None, init=None, d
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ids = t.cpu().numpy()
     res["ids"] = ids
+    res["slab_points"] = int(gid.size)
+    slab.close()
+    return res
+
+
+class SlabPmICP:
+    """One rank's share of the libpointmatcher chain over a partitioned map (b200_icp_slab_*, include/b200reg.h).
+
+    allreduce(tensor): sums a CUDA tensor over the ranks in place (torch.distributed.all_reduce with NCCL), None for a
+    single slab. The exchange arrays (9 N floats + N int32 per iteration) are torch tensors on the handle's device."""
+
+    def __init__(self, slab4, slab_normals, gid, map_mean, axis, lo, hi, params=None, device=0, allreduce=None):
+        import torch
+        self.torch = torch
+        self.device = device
+        self.icp = B.ICP(params, device=device)
+        self.icp.init_reference_slab(slab4, slab_normals, gid, map_mean, axis, lo, hi)
+        self.allreduce = allreduce
+        self.fbuf = self.ibuf = None
+        self.collectives = 0
+
+    def _buffers(self, n):
+        torch = self.torch
+        if self.fbuf is None or self.fbuf.numel() != 9 * n:
+            dev = "cuda:%d" % self.device
+            self.fbuf = torch.zeros(9 * n, dtype=torch.float32, device=dev)
+            self.ibuf = torch.zeros(n, dtype=torch.int32, device=dev)
+        return self.fbuf, self.ibuf
+
+    def begin(self, read4, normals=None, T_init=None):
+        self.icp.slab_begin(read4, normals, T_init)
+        self.collectives = 0
+        return self._buffers(int(np.asarray(read4).shape[0]))
+
+    def match(self):
+        self.icp.slab_match(self.fbuf.data_ptr(), self.ibuf.data_ptr())
+
+    def iterate(self, fbuf=None, ibuf=None):
+        fbuf = self.fbuf if fbuf is None else fbuf
+        ibuf = self.ibuf if ibuf is None else ibuf
+        return self.icp.slab_iterate(fbuf.data_ptr(), ibuf.data_ptr())
+
+    def register(self, read4, normals=None, T_init=None, raise_on_error=True):
+        """the whole loop of one rank: match -> all-reduce of the exchange arrays -> rest of the iteration"""
+        torch = self.torch
+        with torch.cuda.device(self.device):
+            self.begin(read4, normals, T_init)
+            go = True
+            while go:
+                self.match()
+                if self.allreduce is not None:
+                    self.allreduce(self.fbuf)
+                    self.allreduce(self.ibuf)
+                    torch.cuda.current_stream().synchronize()
+                    self.collectives += 2
+                go = self.iterate()
+            res = self.icp.slab_finish(raise_on_error)
+        res["collectives"] = self.collectives
+        return res
+
+    def matches(self):
+        return self.icp.matches()
+
+    def close(self):
+        self.icp.close()
+
+
+def map_mean(map4):
+    """centroid of the whole map in double (ICP.cpp:883-890 subtracts its float rounding from the reference)"""
+    return np.asarray(map4, np.float32)[:, :3].astype(np.float64).mean(0)
+
+
+def register_slabs_pm_one_device(map4, map_normals, read4, n_slabs, params=None, T_init=None, mean=None, device=0,
+                                 read_normals=None, plan=None):
+    """All slabs on ONE device, one after the other (tests, and the proof that the partition reproduces the
+    un-partitioned run): the exchange is a plain sum of the slabs' arrays."""
+    import torch
+    axis, edges = plan_slabs(map4, n_slabs) if plan is None else plan     # plan = (axis, edges): cuts chosen by the caller
+    md = float(params.maxDist) if params is not None else 1.0
+    mean = map_mean(map4) if mean is None else mean
+    slabs, owned = [], []
+    for g in range(n_slabs):
+        gid = slab_members(map4, axis, edges, g, md)
+        slabs.append(SlabPmICP(np.ascontiguousarray(map4[gid]), None if map_normals is None else np.ascontiguousarray(map_normals[gid]),
+                               gid, mean, axis, float(edges[g]), float(edges[g + 1]), params=params, device=device))
+    with torch.cuda.device(device):
+        for sl in slabs:
+            sl.begin(read4, read_normals, T_init)
+        go, iters = True, 0
+        while go:
+            for sl in slabs:
+                sl.match()
+            if iters == 0:
+                owned = [int((sl.ibuf != 0).sum().item()) for sl in slabs]   # (id 0 of slab 0 also reads as "not owned")
+            ftot = torch.stack([sl.fbuf for sl in slabs]).sum(0)
+            itot = torch.stack([sl.ibuf for sl in slabs]).sum(0, dtype=torch.int32)
+            torch.cuda.synchronize()
+            flags = [sl.iterate(ftot, itot) for sl in slabs]
+            assert len(set(flags)) == 1, "the slabs disagree on whether to go on"
+            go = flags[0]
+            iters += 1
+        results = [sl.icp.slab_finish(False) for sl in slabs]
+    out = results[0]
+    out["all_T"] = [r["T"] for r in results]
+    out["matches"] = slabs[0].matches()
+    out["slab_points"] = [int(sl.icp._ref4.shape[0]) for sl in slabs]
+    out["owned_first_iteration"] = owned
+    for sl in slabs:
+        sl.close()
+    return out
+
+
+def register_partitioned_pm(map4, map_normals, read4, params=None, T_init=None, dist=None, device=None, mean=None,
+                            read_normals=None):
+    """One process per GPU: every rank passes the same map (or at least its own slab's points in map order and the
+    whole map's centroid), builds its slab and runs the loop with two NCCL all-reduces per iteration."""
+    import torch
+    world = dist.get_world_size() if dist is not None else 1
+    rank = dist.get_rank() if dist is not None else 0
+    if device is None:
+        device = rank % max(1, torch.cuda.device_count())
+    axis, edges = plan_slabs(map4, world)
+    md = float(params.maxDist) if params is not None else 1.0
+    gid = slab_members(map4, axis, edges, rank, md)
+    ar = None
+    if world > 1:
+        def ar(t):
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    slab = SlabPmICP(np.ascontiguousarray(map4[gid]), None if map_normals is None else np.ascontiguousarray(map_normals[gid]),
+                     gid, map_mean(map4) if mean is None else mean, axis, float(edges[rank]), float(edges[rank + 1]),
+                     params=params, device=device, allreduce=ar)
+    res = slab.register(read4, read_normals, T_init, raise_on_error=False)
     res["slab_points"] = int(gid.size)
     slab.close()
     return res
