@@ -93,6 +93,41 @@ def test_ref_trans_default_identity_filter(gold):
     assert rel < 1e-3  # in practice the oracle lands on the stored transform
 
 
+def _reading_filter(name, f4):
+    """the reading-side DataPointsFilter of the config as a mask (semantics: the cited inPlaceFilter bodies)"""
+    x = f4[:, :3]
+    if name == "defaultRemoveNaNDataPointsFilter":       # RemoveNaN.cpp: drop columns holding a NaN
+        return f4[~np.isnan(x).any(1)]
+    if name == "defaultMaxDistDataPointsFilter":         # MaxDist.cpp:60-71, dim = -1: keep norm < |maxDist| (200)
+        return f4[np.linalg.norm(x, axis=1) < 200.0]
+    if name == "defaultPointToPlaneMinDistDataPointsFilter":   # MinDist.cpp, dim = -1: keep norm > |minDist| (1)
+        return f4[np.linalg.norm(x, axis=1) > 1.0]
+    if name == "defaultBoundingBoxDataPointsFilter":     # BoundingBox.cpp:82-107: xMin 0.2, rest default (-1 .. 1), removeInside
+        inside = (x[:, 0] > 0.2) & (x[:, 0] < 1) & (x[:, 1] > -1) & (x[:, 1] < 1) & (x[:, 2] > -1) & (x[:, 2] < 1)
+        return f4[~inside]
+    raise KeyError(name)
+
+
+@pytest.mark.parametrize("name", ["defaultRemoveNaNDataPointsFilter", "defaultMaxDistDataPointsFilter",
+                                  "defaultBoundingBoxDataPointsFilter", "defaultPointToPlaneMinDistDataPointsFilter"])
+def test_ref_trans_more_deterministic_configs(gold, name):
+    """utest.cpp:81-161 for four more icp_data/*.yaml configs whose reading filter is a plain mask; the rest of the
+    chain is the one of defaultIdentityDataPointsFilter.yaml. Criterion as in the reference: relative median error of
+    curT * data against refT * data below 5 % (data = the UNFILTERED reading, utest.cpp:147-159)."""
+    rf, rn = O.sampling_surface_normal(O.feat4(gold["cloud0"]), knn=10, ratio=0.666666, sampling_method=1)
+    p = O.default_params(trimmed_ratio=0.75, max_iterations=40, min_diff_rot=0.001, min_diff_trans=0.01, smooth_length=4)
+    data = O.feat4(gold["cloud1"])
+    reading = np.ascontiguousarray(_reading_filter(name, data))
+    assert 0 < reading.shape[0] <= data.shape[0]
+    r = O.icp(p, rf, rn, reading)
+    assert r["status"] == 0
+    refT = np.array(gold[name + ".ref_trans"])
+    D = data.T.astype(np.float64)
+    cur = r["T"].astype(np.float64) @ D
+    rel = np.median(np.abs(cur - refT @ D)) / np.median(np.abs(cur))
+    assert rel < 0.05, rel
+
+
 def test_kdtree_matches_brute_force(gold):
     ref4 = O.feat4(gold["c400"]["xyz"])
     q4 = O.feat4(gold["c401"]["xyz"][:1500])
