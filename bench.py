@@ -313,7 +313,7 @@ def mode_list(args, world):
     if args.modes == "none":
         return []
     if args.modes == "auto":
-        return ["index_build", "normals", "c3", "c4", "map"] if world == 1 else ["c4", "c5"]
+        return ["index_build", "normals", "c3", "c4", "map", "lc"] if world == 1 else ["c4", "c5"]
     return [m for m in args.modes.split(",") if m]
 
 

@@ -7,6 +7,7 @@ under "modes" (and a small CLI of its own: python bench_modes.py --mode c4 --gpu
   c3            GICP, covariances from k = 20 normals, 131 072-pt scan vs 5 M-pt map, one B200
   c4            batch of independent submap-to-submap registrations sharded over the ranks, no collective
   c5            city-scale map spatially partitioned over the ranks, sums exchanged over NVLink peer memory
+  lc            loop-closure front half: FPFH of both submaps of a C4 pair + RANSAC feature matching
 
 Every mode returns {"ms", "value", "unit", "roofline": {...}, "e2e": {...}, "cpu_baseline": {...} (rank 0, one GPU
 only), ...}. Timing: CUDA events on the stream the kernels run on (inside the library), max over ranks. Algorithmic
@@ -467,8 +468,77 @@ def mode_map(ctx, steps=12, warmup=2):
     return out
 
 
+# --------------------------------------------------------------------------------------------------- loop closure
+def mode_lc(ctx, steps=5):
+    """SURVEY 8(f) rank 4: Submap::computeFeatures (voxelise 0.5 m -> normals -> FPFH, Submap.cpp:255-275) on both
+    submaps of a C4 pair, then RegistrationRANSACBasedOnFeatureMatching (PlaceRecognition.cpp:81-85) with the
+    reference's defaults (Parameters.hpp:122-133)."""
+    B, args = ctx.B, ctx.args
+    from open3d_slam_private_b200 import synth
+    p = synth.make_c4(n_distinct=1, N=args.pair_points)[0]
+    prep, est, lc = B.Prep(device=ctx.local), B.O3dICP(kind=B.O3D_POINT_TO_POINT, device=ctx.local), B.LoopClosure(device=ctx.local)
+
+    def features(xyz):
+        t0 = time.perf_counter()
+        sp, _, _ = prep.voxel_downsample(0.5, synth.feat4(xyz))          # featureVoxelSize_
+        vox_ms = prep.last_device_ms()
+        sp4 = synth.feat4(sp.astype(np.float32))
+        nrm = est.estimate_normals(sp4, knn=10, radius=1.0)              # normalKnn_, normalEstimationRadius_
+        f, cnt = lc.compute_fpfh(sp4, nrm, 2.5, 100)                     # featureRadius_, featureKnn_
+        return sp4, nrm, f, cnt, vox_ms, lc.last_device_ms(), (time.perf_counter() - t0) * 1e3
+
+    fp_ms, wall_ms, rs_ms, rs_wall = [], [], [], []
+    for it in range(steps + 1):
+        s4, sn, sf, scnt, _, ms_s, w_s = features(p["src_xyz"])
+        t4, tn, tf, tcnt, _, ms_t, w_t = features(p["tgt_xyz"])
+        t0 = time.perf_counter()
+        r = lc.ransac(s4, t4, sf, tf, seed=1 + it)
+        w = (time.perf_counter() - t0) * 1e3
+        if it:   # the first pass allocates
+            fp_ms += [ms_s, ms_t]; wall_ms += [w_s, w_t]; rs_ms.append(r["device_ms"]); rs_wall.append(w)
+    n_sp = (len(s4) + len(t4)) / 2
+    dT = np.linalg.inv(p["T_true"]) @ r["T"]
+    ms = float(np.median(fp_ms))
+    per_pt = 16 + 24 + 4 * 100 + 33 * 8 * 2    # point, normal, neighbour ids, SPFH written + FPFH written
+    out = {"what": "loop-closure front half on a C4 pair (%d-point submaps -> %d / %d sparse points): FPFH (radius 2.5, "
+                   "knn 100) per submap, then RANSAC feature matching (1 M iterations max, confidence 0.99, mutual filter, "
+                   "distance + edge-length checkers)" % (args.pair_points, len(s4), len(t4)),
+           "ms": ms, "value": n_sp / (ms * 1e-3), "unit": "points/s (FPFH)", "fpfh_device_ms": stats(fp_ms),
+           "fpfh_mean_neighbours": float((scnt.mean() + tcnt.mean()) / 2),
+           "ransac_device_ms": stats(rs_ms), "ransac_iterations_run": int(r["iterations_run"]),
+           "ransac_validations": int(r["validations"]), "ransac_feature_correspondences": int(r["n_feature_correspondences"]),
+           "ransac_inlier_correspondences": int(len(r["correspondences"])), "ransac_fitness": float(r["fitness"]),
+           "ransac_kernel_launches": int(r["kernel_launches"]),
+           "ransac_translation_error_vs_truth_m": float(np.abs(dT[:3, 3]).max()),
+           "roofline": roofline("hybrid_knn + spfh + fpfh kernels (loop_closure.cu)", n_sp * per_pt, ms, per_pt),
+           "e2e": {"ms": float(np.median(wall_ms)), "ransac_ms": float(np.median(rs_wall)),
+                   "h2d_bytes_per_step": int(args.pair_points * 16), "d2h_bytes_per_step": int(n_sp * 33 * 8),
+                   "what": "per submap: H2D of the 200 k points, voxel down-sample, normals and FPFH on the device, features "
+                           "back (host wall clock); ransac_ms: b200_lc_ransac_feature_matching with host clouds and features"}}
+    out["roofline"]["limiter"] = ("L2 gathers and double-precision transcendentals (acos, atan2 per pair), not HBM: the "
+                                  "neighbour rows are re-read 100 times from L2")
+    if ctx.with_cpu:
+        from oracle import oracle_py as O
+        cores = os.cpu_count() or 1
+        t0 = time.perf_counter()
+        of, _ = O.o3d_fpfh(s4, sn, 2.5, 100, threads=cores)
+        s_f = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        o = O.o3d_ransac(s4, t4, sf, tf, seed=steps + 1, threads=cores)
+        s_r = time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": len(s4) / s_f, "unit": "points/s (FPFH)", "cores": cores, "kind": "port",
+                               "ms": s_f * 1e3, "ransac_ms": s_r * 1e3,
+                               "sample": "FPFH of the source submap and one RANSAC feature matching, oracle on %d threads "
+                                         "(Open3D's own loops are OpenMP-parallel)" % cores}
+        out["parity"] = {"fpfh_max_abs_diff_median": float(np.median(np.abs(of - sf).max(1))),
+                         "ransac_T_max_abs_diff": float(np.abs(o["T"] - r["T"]).max()),
+                         "ransac_iterations_equal": bool(o["iterations_run"] == r["iterations_run"])}
+    lc.close(); prep.close(); est.close()
+    return out
+
+
 MODES = {"index_build": mode_index_build, "normals": mode_normals, "c3": mode_c3, "c4": mode_c4, "c5": mode_c5,
-         "map": mode_map}
+         "map": mode_map, "lc": mode_lc}
 
 
 def add_mode_args(ap):

@@ -37,7 +37,8 @@ typedef enum {
 const char* b200_last_error(void);
 int b200_version(void);
 /* sizeof of the ABI structs as compiled (0 b200_icp_params, 1 b200_icp_result, 2 b200_index_opts,
- * 3 b200_surface_normal_params), so a binding can verify its mirror */
+ * 3 b200_surface_normal_params, 4 b200_o3d_params, 5 b200_o3d_result, 6 b200_ransac_params, 7 b200_ransac_result), so a
+ * binding can verify its mirror */
 int b200_struct_size(int which);
 /* number of visible CUDA devices (0 when none / driver missing) */
 int b200_device_count(void);
@@ -466,6 +467,65 @@ int b200_map_crop(b200_map* m, const b200_crop_params* crop, float* out4xK, floa
 int b200_map_crop_to_icp(b200_map* m, const b200_crop_params* crop, b200_icp* icp, int* n_patch);
 /* device time of the kernels of the last insert_scan / crop_to_icp (uploads and read-backs excluded) */
 int b200_map_last_device_ms(const b200_map* m, float* ms);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Loop-closure front half — what open3d_slam runs once per finished submap and once per
+ * loop-closure candidate before the ICP refinement (b200_o3d_register) and the information matrix
+ * (b200_o3d_information_matrix). Open3D v0.15.1 is not in the reference tree: semantics recalled from upstream
+ * (pipelines/registration/Feature.cpp, Registration.cpp, CorrespondenceChecker.cpp), parity unpinned.
+ * Clouds are the float memory images of this header (4 x N); features are 33 x N doubles, column-major like
+ * open3d::pipelines::registration::Feature::data_.
+ * ---------------------------------------------------------------------------------------------------------- */
+typedef struct b200_lc b200_lc;
+int b200_lc_create(b200_lc** out, int device);
+void b200_lc_destroy(b200_lc* h);
+/* Submap::computeFeatures (open3d_slam/src/Submap.cpp:255-275): registration::ComputeFPFHFeature(cloud,
+ * KDTreeSearchParamHybrid(radius, max_nn)) — featureRadius_ 2.5, featureKnn_ 100 (Parameters.hpp:124-125). The
+ * neighbourhood of a point = at most max_nn nearest points within radius, nearest first, the first one (the point
+ * itself) skipped; SPFH = 3 x 11-bin histograms of the pair features, 100 / (n - 1) per neighbour; FPFH = sum of the
+ * neighbours' SPFHs weighted by 1 / squared distance, each 11-bin group normalised to 100, plus the point's own SPFH.
+ * normals3xN: column-major doubles like Open3D's normals_ (b200_o3d_estimate_normals returns them that way).
+ * max_nn <= 2048; nn_count_N (nullable) receives the neighbourhood sizes. N = 0 returns B200_OK. */
+int b200_lc_compute_fpfh(b200_lc* h, const float* pts4xN, const double* normals3xN, int N, float radius, int max_nn,
+                         double* fpfh33xN, int32_t* nn_count_N);
+/* the feature-space search of RegistrationRANSACBasedOnFeatureMatching (KDTreeFlann(feature).SearchKNN(col, 1)):
+ * exact nearest column of b for every column of a, squared L2 in double summed in bin order, ties -> smallest
+ * index. d2_N nullable. */
+int b200_lc_feature_nn(b200_lc* h, const double* a33xN, int N, const double* b33xM, int M, int32_t* nn_N, double* d2_N);
+typedef struct {
+  int mutual_filter;                  /* PlaceRecognition.cpp:82 passes true */
+  double max_correspondence_distance; /* ransacMaxCorrespondenceDistance_ */
+  int ransac_n;                       /* ransacModelSize_; 3..8 here (< 3: Open3D returns an empty result) */
+  double edge_length_similarity;      /* CorrespondenceCheckerBasedOnEdgeLength(correspondenceCheckerEdgeLength_); <= 0: absent */
+  double distance_threshold;          /* CorrespondenceCheckerBasedOnDistance(correspondenceCheckerDistance_); <= 0: absent */
+  int max_iteration;                  /* RANSACConvergenceCriteria(ransacNumIter_, ransacProbability_) */
+  double confidence;
+  uint64_t seed;                      /* sample stream: see below */
+  int batch;                          /* hypotheses per launch (0: 65536); does not change the result */
+} b200_ransac_params;
+typedef struct {
+  double T[16];                       /* RegistrationResult::transformation_, column-major */
+  double fitness, inlier_rmse;        /* over the feature correspondences (EvaluateRANSACBasedOnCorrespondence) */
+  int n_correspondences;              /* correspondence_set_.size(): what PlaceRecognition.cpp:87 tests against
+                                         ransacMinCorrespondenceSetSize_ */
+  int n_feature_correspondences;      /* size of the set the hypotheses were drawn from */
+  int mutual_used;                    /* 0: the mutual set had fewer than 3 * ransac_n pairs, all pairs were used */
+  int64_t iterations_run, validations;
+  float device_ms;
+  int kernel_launches;
+} b200_ransac_result;
+void b200_lc_default_ransac_params(b200_ransac_params* prm);
+/* RegistrationRANSACBasedOnFeatureMatching as called at PlaceRecognition.cpp:81-85 (TransformationEstimationPointToPoint
+ * without scaling; both checkers). Open3D draws its samples from an mt19937 seeded by std::random_device inside an
+ * OpenMP loop and is not reproducible by design; here sample j of iteration i is a counter-based hash of (seed, i, j)
+ * and the iterations are consumed in index order with the semantics of the upstream loop run by one thread (one best
+ * result by (fitness, rmse), exit estimate log(1 - confidence) / log(1 - inlier_ratio^ransac_n)): reproducible for a
+ * given seed and independent of `batch`. corr2xK (nullable, capacity 2 x Ns): the inlier pairs (source, target). */
+int b200_lc_ransac_feature_matching(b200_lc* h, const float* src4xN, int Ns, const float* tgt4xM, int Nt,
+                                    const double* src_fpfh33xN, const double* tgt_fpfh33xM, const b200_ransac_params* prm,
+                                    b200_ransac_result* res, int32_t* corr2xK);
+/* device time of the last call's kernels (CUDA events; uploads and read-backs excluded) */
+int b200_lc_last_device_ms(const b200_lc* h, float* ms);
 
 #ifdef __cplusplus
 }

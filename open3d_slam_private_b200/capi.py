@@ -81,6 +81,19 @@ class O3dResult(C.Structure):
                 ("total_ms", C.c_float)]
 
 
+class RansacParams(C.Structure):
+    _fields_ = [("mutual_filter", C.c_int), ("max_correspondence_distance", C.c_double), ("ransac_n", C.c_int),
+                ("edge_length_similarity", C.c_double), ("distance_threshold", C.c_double), ("max_iteration", C.c_int),
+                ("confidence", C.c_double), ("seed", C.c_uint64), ("batch", C.c_int)]
+
+
+class RansacResult(C.Structure):
+    _fields_ = [("T", C.c_double * 16), ("fitness", C.c_double), ("inlier_rmse", C.c_double),
+                ("n_correspondences", C.c_int), ("n_feature_correspondences", C.c_int), ("mutual_used", C.c_int),
+                ("iterations_run", C.c_int64), ("validations", C.c_int64), ("device_ms", C.c_float),
+                ("kernel_launches", C.c_int)]
+
+
 def lib_path():
     return _LIBPATH
 
@@ -496,7 +509,7 @@ class ICP:
             pass
 
 
-O3D_POINT_TO_PLANE, O3D_GENERALIZED = 0, 2
+O3D_POINT_TO_PLANE, O3D_POINT_TO_POINT, O3D_GENERALIZED = 0, 1, 2
 
 
 class O3dICP:
@@ -652,6 +665,76 @@ CROP_NONE, CROP_CYLINDER, CROP_MIN_RADIUS, CROP_MAX_RADIUS, CROP_MINMAX_RADIUS =
 class CropParams(C.Structure):
     _fields_ = [("kind", C.c_int), ("invert", C.c_int), ("radius_min", C.c_double), ("radius_max", C.c_double),
                 ("min_z", C.c_double), ("max_z", C.c_double), ("center", C.c_double * 3)]
+
+
+class LoopClosure:
+    """Loop-closure front half on the device (b200_lc_*): ComputeFPFHFeature (Submap.cpp:272) and
+    RegistrationRANSACBasedOnFeatureMatching (PlaceRecognition.cpp:81-85)."""
+
+    def __init__(self, device=0):
+        require_device()
+        self._h = C.c_void_p()
+        _check(load().b200_lc_create(C.byref(self._h), device))
+
+    def compute_fpfh(self, pts4, normals, radius=2.5, max_nn=100):
+        """-> (features (N, 33) float64, neighbourhood sizes (N,) int32)"""
+        pts4 = f32(pts4)
+        nrm = np.ascontiguousarray(normals, np.float64)
+        n = pts4.shape[0]
+        out = np.empty((n, 33), np.float64)
+        cnt = np.empty(n, np.int32)
+        dp = C.POINTER(C.c_double)
+        _check(load().b200_lc_compute_fpfh(self._h, _fp(pts4), nrm.ctypes.data_as(dp), n, C.c_float(radius), int(max_nn),
+                                           out.ctypes.data_as(dp), _ip(cnt)))
+        return out, cnt
+
+    def feature_nn(self, a, b):
+        """exact nearest row of b (M, 33) for every row of a (N, 33) -> (ids int32, squared distances float64)"""
+        a, b = np.ascontiguousarray(a, np.float64), np.ascontiguousarray(b, np.float64)
+        ids = np.empty(a.shape[0], np.int32)
+        d2 = np.empty(a.shape[0], np.float64)
+        dp = C.POINTER(C.c_double)
+        _check(load().b200_lc_feature_nn(self._h, a.ctypes.data_as(dp), a.shape[0], b.ctypes.data_as(dp), b.shape[0],
+                                         _ip(ids), d2.ctypes.data_as(dp)))
+        return ids, d2
+
+    def ransac(self, src4, tgt4, sf, tf, **kw):
+        """-> dict (T 4x4, fitness, inlier_rmse, correspondences (K, 2), ...); keywords = b200_ransac_params fields"""
+        src4, tgt4 = f32(src4), f32(tgt4)
+        sf, tf = np.ascontiguousarray(sf, np.float64), np.ascontiguousarray(tf, np.float64)
+        prm = RansacParams()
+        load().b200_lc_default_ransac_params(C.byref(prm))
+        for k, v in kw.items():
+            if not hasattr(prm, k):
+                raise TypeError("unknown RANSAC parameter %r" % k)
+            setattr(prm, k, int(v) if k in ("mutual_filter", "ransac_n", "max_iteration", "seed", "batch") else float(v))
+        res = RansacResult()
+        corr = np.empty((max(src4.shape[0], 1), 2), np.int32)
+        dp = C.POINTER(C.c_double)
+        _check(load().b200_lc_ransac_feature_matching(self._h, _fp(src4), src4.shape[0], _fp(tgt4), tgt4.shape[0],
+                                                      sf.ctypes.data_as(dp), tf.ctypes.data_as(dp), C.byref(prm),
+                                                      C.byref(res), _ip(corr)))
+        return dict(T=np.array(res.T).reshape(4, 4).T.copy(), fitness=res.fitness, inlier_rmse=res.inlier_rmse,
+                    correspondences=corr[:res.n_correspondences].copy(),
+                    n_feature_correspondences=res.n_feature_correspondences, mutual_used=bool(res.mutual_used),
+                    iterations_run=res.iterations_run, validations=res.validations, device_ms=res.device_ms,
+                    kernel_launches=res.kernel_launches)
+
+    def last_device_ms(self):
+        ms = C.c_float()
+        _check(load().b200_lc_last_device_ms(self._h, C.byref(ms)))
+        return ms.value
+
+    def close(self):
+        if self._h:
+            load().b200_lc_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class Prep:

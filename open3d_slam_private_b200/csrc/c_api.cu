@@ -107,6 +107,8 @@ int b200_struct_size(int which) {
     case 3: return (int)sizeof(b200_surface_normal_params);
     case 4: return (int)sizeof(b200_o3d_params);
     case 5: return (int)sizeof(b200_o3d_result);
+    case 6: return (int)sizeof(b200_ransac_params);
+    case 7: return (int)sizeof(b200_ransac_result);
     default: return -1;
   }
 }

@@ -170,6 +170,34 @@ int orc_o3d_estimate_normals(const float* pts4xN, int N, int max_nn, float radiu
 int orc_o3d_information_matrix(const float* src4xN, int N, const float* tgt4xM, int M, const double* T16, float max_dist,
                                int threads, double* info36, double* fitness, double* rmse, int32_t* corr_ids);
 
+/* ---- loop-closure front half (see fpfh.cpp): Open3D v0.15.1 ComputeFPFHFeature as called at
+ * Submap.cpp:272 and RegistrationRANSACBasedOnFeatureMatching as called at PlaceRecognition.cpp:81-85 (recalled from
+ * upstream: parity unpinned). Features are 33 x N doubles, column-major like open3d Feature::data_. ---- */
+int orc_o3d_fpfh(const float* pts4xN, const double* nrm3xN, int N, float radius, int max_nn, int threads,
+                 double* fpfh33xN, int32_t* nn_count);
+int orc_o3d_feature_nn(const double* a33xN, int N, const double* b33xM, int M, int threads, int32_t* nn_N, double* d2_N);
+typedef struct {
+  int mutual_filter;
+  double max_correspondence_distance;
+  int ransac_n;                    /* 3..8 */
+  double edge_length_similarity;   /* CorrespondenceCheckerBasedOnEdgeLength, <= 0: absent */
+  double distance_threshold;       /* CorrespondenceCheckerBasedOnDistance, <= 0: absent */
+  int max_iteration;               /* RANSACConvergenceCriteria */
+  double confidence;
+  uint64_t seed;                   /* counter-based sample stream, see fpfh.cpp */
+} orc_ransac_params;
+typedef struct {
+  double T[16];                    /* column-major */
+  double fitness, inlier_rmse;
+  int n_correspondences;           /* correspondence_set_.size() */
+  int n_feature_correspondences;   /* size of the feature correspondence set the hypotheses were drawn from */
+  int mutual_used;
+  int64_t iterations_run, validations;
+} orc_ransac_result;
+int orc_o3d_ransac_feature_matching(const float* src4xN, int Ns, const float* tgt4xM, int Nt, const double* sf33xN,
+                                    const double* tf33xM, const orc_ransac_params* prm, int threads,
+                                    orc_ransac_result* res, int32_t* corr2xK);
+
 /* ---- scan pre-processing (see prep.cpp): open3d_slam croppers (croppers.cpp:25-164) and Open3D
  * VoxelDownSample (recalled from upstream v0.15.1) ---- */
 int orc_crop(int kind, double radius_min, double radius_max, double min_z, double max_z, const double* center3,

@@ -48,7 +48,7 @@ class IcpResult(C.Structure):
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("knn.cpp", "modules.cpp", "normals.cpp", "icp.cpp", "o3d.cpp", "prep.cpp", "oracle.h",
+    srcs = [os.path.join(_HERE, f) for f in ("knn.cpp", "modules.cpp", "normals.cpp", "icp.cpp", "o3d.cpp", "prep.cpp", "fpfh.cpp", "oracle.h",
                                              "la_small.hpp")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s"])
@@ -409,6 +409,63 @@ def o3d_information_matrix(src4, tgt4, T, max_dist, threads=4):
                                           C.byref(rmse), _ip(ids))
     assert st == ORC_OK, st
     return info.reshape(6, 6).T.copy(), fit.value, rmse.value, ids
+
+
+class RansacParams(C.Structure):
+    _fields_ = [("mutual_filter", C.c_int), ("max_correspondence_distance", C.c_double), ("ransac_n", C.c_int),
+                ("edge_length_similarity", C.c_double), ("distance_threshold", C.c_double), ("max_iteration", C.c_int),
+                ("confidence", C.c_double), ("seed", C.c_uint64)]
+
+
+class RansacResult(C.Structure):
+    _fields_ = [("T", C.c_double * 16), ("fitness", C.c_double), ("inlier_rmse", C.c_double),
+                ("n_correspondences", C.c_int), ("n_feature_correspondences", C.c_int), ("mutual_used", C.c_int),
+                ("iterations_run", C.c_int64), ("validations", C.c_int64)]
+
+
+def o3d_fpfh(pts4, normals, radius, max_nn, threads=4):
+    """orc_o3d_fpfh -> (features (N,33) float64, neighbourhood sizes (N,) int32)"""
+    pts4 = f32(pts4)
+    nrm = np.ascontiguousarray(normals, np.float64)
+    n = pts4.shape[0]
+    out = np.empty((n, 33), np.float64)
+    cnt = np.empty(n, np.int32)
+    dp = C.POINTER(C.c_double)
+    st = lib().orc_o3d_fpfh(_fp(pts4), nrm.ctypes.data_as(dp), n, C.c_float(radius), int(max_nn), int(threads),
+                            out.ctypes.data_as(dp), _ip(cnt))
+    assert st == ORC_OK, st
+    return out, cnt
+
+
+def o3d_feature_nn(a, b, threads=4):
+    """exact 1-NN of every row of a (N,33) in b (M,33) -> (ids int32, squared distances float64)"""
+    a, b = np.ascontiguousarray(a, np.float64), np.ascontiguousarray(b, np.float64)
+    ids = np.empty(a.shape[0], np.int32)
+    d2 = np.empty(a.shape[0], np.float64)
+    dp = C.POINTER(C.c_double)
+    st = lib().orc_o3d_feature_nn(a.ctypes.data_as(dp), a.shape[0], b.ctypes.data_as(dp), b.shape[0], int(threads),
+                                  _ip(ids), d2.ctypes.data_as(dp))
+    assert st == ORC_OK, st
+    return ids, d2
+
+
+def o3d_ransac(src4, tgt4, sf, tf, mutual_filter=True, max_correspondence_distance=0.75, ransac_n=3,
+               edge_length_similarity=0.5, distance_threshold=0.75, max_iteration=1000000, confidence=0.99, seed=1,
+               threads=4):
+    """orc_o3d_ransac_feature_matching -> dict (T 4x4, fitness, inlier_rmse, correspondences (K,2), ...)"""
+    src4, tgt4 = f32(src4), f32(tgt4)
+    sf, tf = np.ascontiguousarray(sf, np.float64), np.ascontiguousarray(tf, np.float64)
+    prm = RansacParams(int(bool(mutual_filter)), max_correspondence_distance, int(ransac_n), edge_length_similarity,
+                       distance_threshold, int(max_iteration), confidence, int(seed))
+    res = RansacResult()
+    corr = np.empty((max(src4.shape[0], 1), 2), np.int32)
+    dp = C.POINTER(C.c_double)
+    st = lib().orc_o3d_ransac_feature_matching(_fp(src4), src4.shape[0], _fp(tgt4), tgt4.shape[0], sf.ctypes.data_as(dp),
+                                               tf.ctypes.data_as(dp), C.byref(prm), int(threads), C.byref(res), _ip(corr))
+    assert st == ORC_OK, st
+    return dict(T=np.array(res.T).reshape(4, 4).T.copy(), fitness=res.fitness, inlier_rmse=res.inlier_rmse,
+                correspondences=corr[:res.n_correspondences].copy(), n_feature_correspondences=res.n_feature_correspondences,
+                mutual_used=bool(res.mutual_used), iterations_run=res.iterations_run, validations=res.validations)
 
 
 def crop(kind, pts4, radius_min=0.0, radius_max=0.0, min_z=0.0, max_z=0.0, center=(0.0, 0.0, 0.0), invert=False):
