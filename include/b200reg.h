@@ -524,6 +524,14 @@ void b200_lc_default_ransac_params(b200_ransac_params* prm);
 int b200_lc_ransac_feature_matching(b200_lc* h, const float* src4xN, int Ns, const float* tgt4xM, int Nt,
                                     const double* src_fpfh33xN, const double* tgt_fpfh33xM, const b200_ransac_params* prm,
                                     b200_ransac_result* res, int32_t* corr2xK);
+/* computeIndicesOfOverlappingPoints(source, target, sourceToTarget, voxelSize, minNumPointsPerVoxel, &idxsSource,
+ * &idxsTarget) (open3d_slam/src/helpers.cpp:320-345; called between RANSAC and the refinement, PlaceRecognition.cpp:
+ * 98-108, and by the odometry constraints, constraint_builders.cpp:54): both clouds into one VoxelMap (key =
+ * floor(p / voxelSize) per axis, VoxelHashMap.hpp:48-51; the source transformed by T16 first), kept = the points whose
+ * voxel holds at least min_points of BOTH clouds. Outputs (capacity Ns / Nt) in ascending index order (the reference's
+ * order is that of an std::unordered_map walk). */
+int b200_lc_overlap_indices(b200_lc* h, const float* src4xN, int Ns, const float* tgt4xM, int Nt, const double* T16,
+                            double voxel_size, int min_points, int32_t* src_idx, int* n_src, int32_t* tgt_idx, int* n_tgt);
 /* device time of the last call's kernels (CUDA events; uploads and read-backs excluded) */
 int b200_lc_last_device_ms(const b200_lc* h, float* ms);
 

@@ -720,6 +720,17 @@ class LoopClosure:
                     iterations_run=res.iterations_run, validations=res.validations, device_ms=res.device_ms,
                     kernel_launches=res.kernel_launches)
 
+    def overlap_indices(self, src4, tgt4, T, voxel_size, min_points=1):
+        """computeIndicesOfOverlappingPoints (helpers.cpp:320-345) -> (source indices, target indices) int32, ascending"""
+        src4, tgt4 = f32(src4), f32(tgt4)
+        Tc = np.ascontiguousarray(np.asarray(T, np.float64).T).ravel()
+        si, ti = np.empty(max(len(src4), 1), np.int32), np.empty(max(len(tgt4), 1), np.int32)
+        ns, nt = C.c_int(), C.c_int()
+        _check(load().b200_lc_overlap_indices(self._h, _fp(src4), len(src4), _fp(tgt4), len(tgt4),
+                                              Tc.ctypes.data_as(C.POINTER(C.c_double)), C.c_double(voxel_size), int(min_points),
+                                              _ip(si), C.byref(ns), _ip(ti), C.byref(nt)))
+        return si[:ns.value].copy(), ti[:nt.value].copy()
+
     def last_device_ms(self):
         ms = C.c_float()
         _check(load().b200_lc_last_device_ms(self._h, C.byref(ms)))

@@ -1297,7 +1297,9 @@ int launch_icp_kernel(const IcpKernelParams& p, int device, cudaStream_t s, int*
   if (p.k <= 1) return launch_k<1>(p, device, s, grid_out);
   if (p.k <= 4) return launch_k<4>(p, device, s, grid_out);
   if (p.k <= 16) return launch_k<16>(p, device, s, grid_out);
-  set_error("ICP chain supports knn <= 16 (use b200_index_knn for larger k)");
+  if (p.k <= 32) return launch_k<32>(p, device, s, grid_out);
+  if (p.k <= 64) return launch_k<64>(p, device, s, grid_out);   // the k-best list lives in local memory from here on
+  set_error("ICP chain supports knn <= 64 (the limit of the matcher, b200_index_knn)");
   return B200_E_UNSUPPORTED;
 }
 

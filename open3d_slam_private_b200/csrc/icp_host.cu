@@ -287,7 +287,7 @@ int icp_ensure_reading(b200_icp* h, int N, bool normals) {
 
 int check_params(const b200_icp_params* p) {
   if (p->knn < 1) { set_error("KDTreeMatcher: knn must be >= 1"); return B200_E_BAD_PARAM; }
-  if (p->knn > 16) { set_error("ICP chain supports knn <= 16"); return B200_E_UNSUPPORTED; }
+  if (p->knn > 64) { set_error("ICP chain supports knn <= 64 (the limit of the matcher)"); return B200_E_UNSUPPORTED; }
   if (!(p->maxDist >= 0.f)) { set_error("KDTreeMatcher: maxDist must be >= 0"); return B200_E_BAD_PARAM; }
   if (p->use_trimmed && !(p->trimmed_ratio > 0.f && p->trimmed_ratio <= 1.f)) {
     set_error("TrimmedDistOutlierFilter: ratio must lie in (0, 1]");

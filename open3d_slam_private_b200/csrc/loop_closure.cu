@@ -36,6 +36,8 @@
 #include "knn.cuh"
 
 namespace b200 {
+int inclusive_scan_u32(uint32_t* d_data, size_t n, uint32_t* d_tile, cudaStream_t s);   // preprocess.cu
+size_t scan_tiles_for(size_t n);
 namespace {
 
 constexpr int kHKThreads = 128;
@@ -658,6 +660,63 @@ __global__ void __launch_bounds__(1024) ransac_final_kernel(const RansacParamsDe
   if (tid == 0) *n_out = s_base;
 }
 
+
+// ---- computeIndicesOfOverlappingPoints (open3d_slam/src/helpers.cpp:320-345) ----------------------------------------
+// Both clouds go into one voxel table (key = floor(p / voxelSize) per axis, VoxelHashMap.hpp:48-51, 21 bits per axis;
+// the source transformed first, helpers.cpp:328-330) with one counter per cloud; a point is kept when its voxel holds
+// at least min_points of BOTH clouds.
+constexpr unsigned long long kVoxEmpty = ~0ull;
+__device__ __forceinline__ unsigned long long mix64(unsigned long long x) {
+  x ^= x >> 33; x *= 0xff51afd7ed558ccdull; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ull; x ^= x >> 33;
+  return x;
+}
+struct Mat4 { double m[16]; };
+__global__ void overlap_insert_kernel(const float4* __restrict__ src, int Ns, const float4* __restrict__ tgt, int Nt,
+                                      const Mat4 T, double inv, unsigned long long mask,
+                                      unsigned long long* __restrict__ keys, uint32_t* __restrict__ cnt2,
+                                      uint32_t* __restrict__ slot_of, int* __restrict__ bad) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < Ns + Nt; i += gridDim.x * blockDim.x) {
+    const bool is_src = i < Ns;
+    const float4 q = __ldg(is_src ? &src[i] : &tgt[i - Ns]);
+    double p[3] = {(double)q.x, (double)q.y, (double)q.z};
+    if (is_src) { double t[3]; xform3(T.m, p, t); p[0] = t[0]; p[1] = t[1]; p[2] = t[2]; }
+    const double fx = floor(p[0] * inv), fy = floor(p[1] * inv), fz = floor(p[2] * inv);
+    if (!(fabs(fx) < 1048575.0 && fabs(fy) < 1048575.0 && fabs(fz) < 1048575.0)) { *bad = 1; slot_of[i] = 0xffffffffu; continue; }
+    const unsigned long long key = ((unsigned long long)((long long)fx + 1048576ll) << 42) |
+                                   ((unsigned long long)((long long)fy + 1048576ll) << 21) |
+                                   (unsigned long long)((long long)fz + 1048576ll);
+    unsigned long long s = mix64(key) & mask;
+    while (true) {
+      const unsigned long long prev = atomicCAS(&keys[s], kVoxEmpty, key);
+      if (prev == kVoxEmpty || prev == key) break;
+      s = (s + 1ull) & mask;
+    }
+    slot_of[i] = (uint32_t)s;
+    atomicAdd(&cnt2[2 * s + (is_src ? 0 : 1)], 1u);
+  }
+}
+__global__ void overlap_flag_kernel(const uint32_t* __restrict__ slot_of, const uint32_t* __restrict__ cnt2, int n,
+                                    uint32_t min_points, uint32_t* __restrict__ flag) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t s = slot_of[i];
+    flag[i] = (s != 0xffffffffu && cnt2[2 * (size_t)s] >= min_points && cnt2[2 * (size_t)s + 1] >= min_points) ? 1u : 0u;
+  }
+}
+// scan = inclusive scan of the flags over [source | target]; kept indices of each cloud in index order
+__global__ void overlap_scatter_kernel(const uint32_t* __restrict__ scan, int Ns, int Nt, int* __restrict__ out_src,
+                                       int* __restrict__ out_tgt) {
+  const uint32_t ns_kept = Ns ? scan[Ns - 1] : 0u;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < Ns + Nt; i += gridDim.x * blockDim.x) {
+    const uint32_t a = scan[i], a0 = i ? scan[i - 1] : 0u;
+    if (a == a0) continue;
+    if (i < Ns) out_src[a0] = i;
+    else out_tgt[a0 - ns_kept] = i - Ns;
+  }
+}
+__global__ void fill_u64_lc_kernel(unsigned long long* __restrict__ p, size_t n, unsigned long long v) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
+}
+
 template <class T>
 int grow(T** p, size_t* cap, size_t n) {
   if (n <= *cap) return B200_OK;
@@ -695,6 +754,11 @@ struct b200_lc {
          cap_surv_T = 0, cap_corr = 0;
   RansacState* d_state = nullptr;
   RansacState* h_state = nullptr;   // pinned
+  // overlap scratch
+  unsigned long long* d_vkeys = nullptr;
+  uint32_t *d_vcnt = nullptr, *d_vslot = nullptr, *d_vflag = nullptr, *d_vtile = nullptr;
+  int *d_vsrc = nullptr, *d_vtgt = nullptr;
+  size_t cap_vkeys = 0, cap_vcnt = 0, cap_vslot = 0, cap_vflag = 0, cap_vtile = 0, cap_vsrc = 0, cap_vtgt = 0;
 };
 
 static int feature_nn(b200_lc* h, const double* d_a, int N, const double* d_b, int M, int* d_nn, double* d_d2) {
@@ -748,6 +812,8 @@ void b200_lc_destroy(b200_lc* h) {
     cudaFree(h->d_pt); cudaFree(h->d_err2); cudaFree(h->d_surv_T); cudaFree(h->d_part_j); cudaFree(h->d_ij); cudaFree(h->d_ji);
     cudaFree(h->d_cs); cudaFree(h->d_ct); cudaFree(h->d_good); cudaFree(h->d_slot); cudaFree(h->d_surv_h); cudaFree(h->d_corr);
     cudaFree(h->d_n); cudaFree(h->d_state);
+    cudaFree(h->d_vkeys); cudaFree(h->d_vcnt); cudaFree(h->d_vslot); cudaFree(h->d_vflag); cudaFree(h->d_vtile);
+    cudaFree(h->d_vsrc); cudaFree(h->d_vtgt);
     cudaFreeHost(h->h_state);
     for (int i = 0; i < 2; ++i)
       if (h->ev[i]) cudaEventDestroy(h->ev[i]);
@@ -963,6 +1029,64 @@ int b200_lc_ransac_feature_matching(b200_lc* h, const float* src4xN, int Ns, con
   res->validations = st.validations;
   res->device_ms = h->last_ms;
   res->kernel_launches = launches;
+  return B200_OK;
+}
+
+int b200_lc_overlap_indices(b200_lc* h, const float* src4xN, int Ns, const float* tgt4xM, int Nt, const double* T16,
+                            double voxel_size, int min_points, int32_t* src_idx, int* n_src, int32_t* tgt_idx, int* n_tgt) {
+  if (!h || Ns < 0 || Nt < 0 || (Ns > 0 && !src4xN) || (Nt > 0 && !tgt4xM) || !T16 || !n_src || !n_tgt ||
+      (Ns > 0 && !src_idx) || (Nt > 0 && !tgt_idx)) {
+    set_error("b200_lc_overlap_indices: bad arguments");
+    return B200_E_BAD_PARAM;
+  }
+  if (!(voxel_size > 0.0) || min_points < 1) { set_error("b200_lc_overlap_indices: voxel_size > 0 and min_points >= 1 (helpers.cpp:323)"); return B200_E_BAD_PARAM; }
+  *n_src = *n_tgt = 0;
+  const int n = Ns + Nt;
+  if (n == 0) return B200_OK;
+  DeviceGuard dg(h->device);
+  if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
+  cudaStream_t s = h->stream;
+  size_t slots = 1024;
+  while (slots < 2 * (size_t)n) slots <<= 1;
+  B200_TRY(grow(&h->d_src, &h->cap_src, (size_t)std::max(Ns, 1)));
+  B200_TRY(grow(&h->d_tgt, &h->cap_tgt, (size_t)std::max(Nt, 1)));
+  B200_TRY(grow(&h->d_vkeys, &h->cap_vkeys, slots));
+  B200_TRY(grow(&h->d_vcnt, &h->cap_vcnt, 2 * slots));
+  B200_TRY(grow(&h->d_vslot, &h->cap_vslot, (size_t)n));
+  B200_TRY(grow(&h->d_vflag, &h->cap_vflag, (size_t)n));
+  B200_TRY(grow(&h->d_vtile, &h->cap_vtile, scan_tiles_for((size_t)n) + 1));
+  B200_TRY(grow(&h->d_vsrc, &h->cap_vsrc, (size_t)std::max(Ns, 1)));
+  B200_TRY(grow(&h->d_vtgt, &h->cap_vtgt, (size_t)std::max(Nt, 1)));
+  if (Ns) B200_TRY(upload_features(h->d_src, src4xN, Ns, s));
+  if (Nt) B200_TRY(upload_features(h->d_tgt, tgt4xM, Nt, s));
+  B200_CUDA(cudaMemsetAsync(h->d_flag, 0, sizeof(int), s));
+  B200_CUDA(cudaEventRecord(h->ev[0], s));
+  fill_u64_lc_kernel<<<296, 256, 0, s>>>(h->d_vkeys, slots, kVoxEmpty);
+  B200_CUDA(cudaMemsetAsync(h->d_vcnt, 0, 2 * slots * sizeof(uint32_t), s));
+  Mat4 T;
+  std::memcpy(T.m, T16, sizeof(T.m));
+  const int blocks = std::min(148 * 8, (n + 255) / 256);
+  overlap_insert_kernel<<<blocks, 256, 0, s>>>(h->d_src, Ns, h->d_tgt, Nt, T, 1.0 / voxel_size, (unsigned long long)slots - 1ull,
+                                               h->d_vkeys, h->d_vcnt, h->d_vslot, h->d_flag);
+  overlap_flag_kernel<<<blocks, 256, 0, s>>>(h->d_vslot, h->d_vcnt, n, (uint32_t)min_points, h->d_vflag);
+  B200_CUDA(cudaGetLastError());
+  B200_TRY(inclusive_scan_u32(h->d_vflag, (size_t)n, h->d_vtile, s));
+  overlap_scatter_kernel<<<blocks, 256, 0, s>>>(h->d_vflag, Ns, Nt, h->d_vsrc, h->d_vtgt);
+  B200_CUDA(cudaGetLastError());
+  B200_CUDA(cudaEventRecord(h->ev[1], s));
+  uint32_t tot[2] = {0u, 0u};
+  int bad = 0;
+  if (Ns) B200_CUDA(cudaMemcpyAsync(&tot[0], h->d_vflag + (Ns - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaMemcpyAsync(&tot[1], h->d_vflag + (n - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaMemcpyAsync(&bad, h->d_flag, sizeof(int), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  cudaEventElapsedTime(&h->last_ms, h->ev[0], h->ev[1]);
+  if (bad) { set_error("b200_lc_overlap_indices: a voxel index lies beyond +-2^20"); return B200_E_BAD_PARAM; }
+  *n_src = (int)tot[0];
+  *n_tgt = (int)(tot[1] - tot[0]);
+  if (*n_src) B200_CUDA(cudaMemcpyAsync(src_idx, h->d_vsrc, (size_t)*n_src * sizeof(int), cudaMemcpyDeviceToHost, s));
+  if (*n_tgt) B200_CUDA(cudaMemcpyAsync(tgt_idx, h->d_vtgt, (size_t)*n_tgt * sizeof(int), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
   return B200_OK;
 }
 

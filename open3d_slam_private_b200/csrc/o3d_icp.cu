@@ -26,6 +26,7 @@
 #include <cmath>
 #include <cstring>
 #include <new>
+#include <cstdlib>
 
 using namespace b200;
 
@@ -61,6 +62,10 @@ struct O3dParams {
   int own_axis;          // -1: not partitioned
   float own_lo, own_hi;
   const int* gid;
+  // query -> lane map of the match kernel: 0 = 32 consecutive source points per warp, 1 = lane l of warp slot w takes
+  // point l * nslots + w (spatially coherent, equally expensive points spread over all warps), 2 = 1 until the
+  // previous match's RMSE is below 0.4 cells (every query settled by its own 2x2x2 block), then 0
+  int qmap;
 };
 
 __device__ __forceinline__ double3 gicp_axis(float4 n) {
@@ -75,29 +80,60 @@ __device__ __forceinline__ double3 gicp_axis(float4 n) {
   return make_double3(c, y / nn, z / nn);
 }
 
-__global__ void __launch_bounds__(kThreads) o3d_match_lin_kernel(const __grid_constant__ O3dParams p) {
-  __shared__ double s_part[kThreads / 32][kVals];
-  __shared__ Warp1Scratch s_ws[kThreads / 32];
+// The match kernel is a chain of dependent L2 gathers (the 1-NN search), so what it needs is resident warps. The 29
+// double sums of the linearisation used to live in registers (128 per thread: 16 warps per SM). Now a lane keeps ONE
+// sum: every lane stages the values of its correspondence in a per-warp shared-memory tile (two batches of at most 16
+// rows x 32 lanes, column index rotated by the row so that neither the writes nor the row reads conflict by more than
+// two ways), and lane r adds row r over the 32 lanes in lane order — same additions for every launch geometry, 64
+// registers, 32 warps per SM.
+constexpr int kStageRows = 16;
+struct StageTile { double v[kStageRows][32]; };
+
+// one batch: rows [T0, T1) of the values `emit` enumerates (emit calls put(t, value) with compile-time t after
+// unrolling); lane (T0 ? 16 : 0) + r accumulates row r
+template <int T0, int T1, class Emit>
+__device__ __forceinline__ void stage_batch(StageTile& tile, int lane, bool active, Emit&& emit, double& acc) {
+  static_assert(T1 - T0 <= kStageRows, "batch too tall");
+  emit([&](int t, double v) {
+    if (t >= T0 && t < T1) tile.v[t - T0][(lane + (t - T0)) & 31] = active ? v : 0.0;
+  });
+  __syncwarp();
+  const int r = lane - (T0 ? 16 : 0);
+  if (r >= 0 && r < T1 - T0) {
+    double a = acc;
+#pragma unroll 8
+    for (int c = 0; c < 32; ++c) a += tile.v[r][(c + r) & 31];
+    acc = a;
+  }
+  __syncwarp();
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(kThreads, 4) o3d_match_lin_kernel(const __grid_constant__ O3dParams p) {
+  // the search's per-warp scratch and the staging tile are never live at the same time (__syncwarp in between)
+  __shared__ __align__(16) unsigned char s_raw[kThreads / 32][sizeof(StageTile)];
+  static_assert(sizeof(Warp1Scratch) <= sizeof(StageTile), "the search scratch must fit into the staging tile");
+  __shared__ double s_T[12];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   if (p.st->done) return;
-  double T[12];
-#pragma unroll
-  for (int j = 0; j < 4; ++j)
-#pragma unroll
-    for (int i = 0; i < 3; ++i) T[i + 3 * j] = p.st->T[i + 4 * j];
-  double acc[kVals];
-#pragma unroll
-  for (int t = 0; t < kVals; ++t) acc[t] = 0.0;
+  if (tid < 12) s_T[tid] = p.st->T[(tid % 3) + 4 * (tid / 3)];
+  __syncthreads();
+  // lane l < 15 holds value l, lane 16 + u holds value 15 + u (u < 14): 29 sums per warp
+  double acc = 0.0;
   const int nthreads = gridDim.x * kThreads;
-  for (int base = blockIdx.x * kThreads + wid * 32; base < p.N; base += nthreads) {
-    const int i = base + lane;
+  const int nslots = (p.N + 31) >> 5;
+  const bool scatter = p.qmap == 1 || (p.qmap == 2 && (p.st->matches_done == 0 || !(p.st->rmse < 0.4 * (double)p.g.cell)));
+  StageTile& tile = *reinterpret_cast<StageTile*>(s_raw[wid]);
+  Warp1Scratch& scratch = *reinterpret_cast<Warp1Scratch*>(s_raw[wid]);
+  for (int slot = blockIdx.x * (kThreads / 32) + wid; slot < nslots; slot += nthreads >> 5) {
+    const int i = scatter ? lane * nslots + (slot + lane * 97) % nslots : slot * 32 + lane;
     const bool in = i < p.N;
     float4 q = make_float4(0.f, 0.f, 0.f, 1.f);
     if (in) {
       const float4 s = __ldg(&p.src[i]);
-      q.x = (float)(T[0] * s.x + T[3] * s.y + T[6] * s.z + T[9]);
-      q.y = (float)(T[1] * s.x + T[4] * s.y + T[7] * s.z + T[10]);
-      q.z = (float)(T[2] * s.x + T[5] * s.y + T[8] * s.z + T[11]);
+      q.x = (float)(s_T[0] * s.x + s_T[3] * s.y + s_T[6] * s.z + s_T[9]);
+      q.y = (float)(s_T[1] * s.x + s_T[4] * s.y + s_T[7] * s.z + s_T[10]);
+      q.z = (float)(s_T[2] * s.x + s_T[5] * s.y + s_T[8] * s.z + s_T[11]);
     }
     bool mine = in;
     if (p.own_axis >= 0) {
@@ -106,101 +142,132 @@ __global__ void __launch_bounds__(kThreads) o3d_match_lin_kernel(const __grid_co
     }
     float bd; int bid, bsp;
     unsigned vis = 0;
-    knn_query_warp1(p.g, mine, q.x, q.y, q.z, p.md2, bd, bid, bsp, vis, s_ws[wid]);
-    if (!in) continue;
-    if (!mine) { p.ids[i] = -2; p.dists[i] = __int_as_float(0x7f800000); continue; }   // another slab's query
-    p.ids[i] = (bid >= 0 && p.gid) ? __ldg(&p.gid[bid]) : bid; p.dists[i] = bd;
-    if (bid < 0) continue;
-    const float4 t4 = __ldg(&p.g.pts[bsp]);
-    const float4 n4 = (p.kind == 1 || p.kind == 3) ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldg(&p.g.nrm[bsp]);
+    knn_query_warp1(p.g, mine, q.x, q.y, q.z, p.md2, bd, bid, bsp, vis, scratch);
+    __syncwarp();
+    if (in) {
+      if (!mine) { p.ids[i] = -2; p.dists[i] = __int_as_float(0x7f800000); }   // another slab's query
+      else { p.ids[i] = (bid >= 0 && p.gid) ? __ldg(&p.gid[bid]) : bid; p.dists[i] = bd; }
+    }
+    const bool hit = in && mine && bid >= 0;
+    if (!__any_sync(0xffffffffu, hit)) continue;
+    float4 t4 = make_float4(0.f, 0.f, 0.f, 0.f), n4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (hit) {
+      t4 = __ldg(&p.g.pts[bsp]);
+      if (KIND == 0 || KIND == 2) n4 = __ldg(&p.g.nrm[bsp]);
+    }
     const double s[3] = {(double)q.x, (double)q.y, (double)q.z};
     const double d[3] = {s[0] - (double)t4.x, s[1] - (double)t4.y, s[2] - (double)t4.z};
-    acc[27] += 1.0;
-    acc[28] += (double)bd;
-    if (p.kind == 3) {
+    // values 27 (count) and 28 (sum d^2) ride in the second batch of the first (or only) row
+    if (KIND == 3) {
       // GetInformationMatrixFromPointClouds (Open3D v0.15.1, as called at PlaceRecognition.cpp:148-149): G^T G over the
       // correspondences with the three rows G = [-[t]x | I] of the matched TARGET point t
       const double x = (double)t4.x, y = (double)t4.y, z = (double)t4.z;
-      const double G[3][6] = {{0.0, z, -y, 1.0, 0.0, 0.0}, {-z, 0.0, x, 0.0, 1.0, 0.0}, {y, -x, 0.0, 0.0, 0.0, 1.0}};
 #pragma unroll
       for (int r = 0; r < 3; ++r) {
+        const double G[6] = {r == 0 ? 0.0 : (r == 1 ? -z : y), r == 0 ? z : (r == 1 ? 0.0 : -x), r == 0 ? -y : (r == 1 ? x : 0.0),
+                             r == 0 ? 1.0 : 0.0, r == 1 ? 1.0 : 0.0, r == 2 ? 1.0 : 0.0};
+        auto emit = [&](auto&& put) {
+          int t = 0;
+#pragma unroll
+          for (int c = 0; c < 6; ++c)
+#pragma unroll
+            for (int a = 0; a <= c; ++a) put(t++, G[a] * G[c]);
+          if (r == 0) { put(27, 1.0); put(28, (double)bd); }
+        };
+        stage_batch<0, 15>(tile, lane, hit, emit, acc);
+        stage_batch<15, 29>(tile, lane, hit, emit, acc);
+      }
+    } else if (KIND == 1) {
+      // Umeyama moments: sum s (0..2), sum t (3..5), sum t s^T (6..14, column-major)
+      const double t[3] = {(double)t4.x, (double)t4.y, (double)t4.z};
+      auto emit = [&](auto&& put) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { put(a, s[a]); put(3 + a, t[a]); }
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+#pragma unroll
+          for (int r = 0; r < 3; ++r) put(6 + r + 3 * c, t[r] * s[c]);
+        put(27, 1.0); put(28, (double)bd);
+      };
+      stage_batch<0, 15>(tile, lane, hit, emit, acc);
+      stage_batch<15, 29>(tile, lane, hit, emit, acc);
+    } else if (KIND == 0) {
+      const double n[3] = {(double)n4.x, (double)n4.y, (double)n4.z};
+      const double r = d[0] * n[0] + d[1] * n[1] + d[2] * n[2];
+      const double J[6] = {s[1] * n[2] - s[2] * n[1], s[2] * n[0] - s[0] * n[2], s[0] * n[1] - s[1] * n[0], n[0], n[1], n[2]};
+      auto emit = [&](auto&& put) {
         int t = 0;
 #pragma unroll
         for (int c = 0; c < 6; ++c)
 #pragma unroll
-          for (int a = 0; a <= c; ++a) acc[t++] += G[r][a] * G[r][c];
-      }
-    } else if (p.kind == 1) {
-      // Umeyama moments: sum s (0..2), sum t (3..5), sum t s^T (6..14, column-major)
-      const double t[3] = {(double)t4.x, (double)t4.y, (double)t4.z};
+          for (int a = 0; a <= c; ++a) put(t++, J[a] * J[c]);
 #pragma unroll
-      for (int a = 0; a < 3; ++a) { acc[a] += s[a]; acc[3 + a] += t[a]; }
-#pragma unroll
-      for (int c = 0; c < 3; ++c)
-#pragma unroll
-        for (int r = 0; r < 3; ++r) acc[6 + r + 3 * c] += t[r] * s[c];
-    } else if (p.kind == 0) {
-      const double n[3] = {(double)n4.x, (double)n4.y, (double)n4.z};
-      const double r = d[0] * n[0] + d[1] * n[1] + d[2] * n[2];
-      const double J[6] = {s[1] * n[2] - s[2] * n[1], s[2] * n[0] - s[0] * n[2], s[0] * n[1] - s[1] * n[0], n[0], n[1], n[2]};
-      int t = 0;
-#pragma unroll
-      for (int c = 0; c < 6; ++c)
-#pragma unroll
-        for (int a = 0; a <= c; ++a) acc[t++] += J[a] * J[c];
-#pragma unroll
-      for (int a = 0; a < 6; ++a) acc[21 + a] += J[a] * r;
+        for (int a = 0; a < 6; ++a) put(21 + a, J[a] * r);
+        put(27, 1.0); put(28, (double)bd);
+      };
+      stage_batch<0, 15>(tile, lane, hit, emit, acc);
+      stage_batch<15, 29>(tile, lane, hit, emit, acc);
     } else {
       // M = C_t + R C_s R^T = 2 I - (1 - eps) (a a^T + b b^T), a = target axis, b = rotated source axis
       const double3 a = gicp_axis(n4);
-      const double3 b0 = gicp_axis(__ldg(&p.src_n[i]));
-      const double3 b = make_double3(T[0] * b0.x + T[3] * b0.y + T[6] * b0.z, T[1] * b0.x + T[4] * b0.y + T[7] * b0.z,
-                                     T[2] * b0.x + T[5] * b0.y + T[8] * b0.z);
+      const double3 b0 = gicp_axis(hit ? __ldg(&p.src_n[i]) : make_float4(1.f, 0.f, 0.f, 0.f));
+      const double3 b = make_double3(s_T[0] * b0.x + s_T[3] * b0.y + s_T[6] * b0.z, s_T[1] * b0.x + s_T[4] * b0.y + s_T[7] * b0.z,
+                                     s_T[2] * b0.x + s_T[5] * b0.y + s_T[8] * b0.z);
       const double k1 = 1.0 - p.eps;
       const double ab = a.x * b.x + a.y * b.y + a.z * b.z;
       // eigenpairs in span{a, b}: u+ ~ a + b (lambda 2 - k1 (1 + ab)), u- ~ a - b (lambda 2 - k1 (1 - ab)); rest: 2
-      double up[3] = {a.x + b.x, a.y + b.y, a.z + b.z}, um[3] = {a.x - b.x, a.y - b.y, a.z - b.z};
+      const double up[3] = {a.x + b.x, a.y + b.y, a.z + b.z}, um[3] = {a.x - b.x, a.y - b.y, a.z - b.z};
       const double np2 = up[0] * up[0] + up[1] * up[1] + up[2] * up[2], nm2 = um[0] * um[0] + um[1] * um[1] + um[2] * um[2];
       const double w0 = 0.70710678118654752440;  // 2^-1/2
       const double wp = np2 > 1e-24 ? 1.0 / sqrt(2.0 - k1 * (1.0 + ab)) - w0 : 0.0;
       const double wm = nm2 > 1e-24 ? 1.0 / sqrt(2.0 - k1 * (1.0 - ab)) - w0 : 0.0;
       const double ip = np2 > 1e-24 ? wp / np2 : 0.0, im = nm2 > 1e-24 ? wm / nm2 : 0.0;
-      double W[9];  // symmetric: W = w0 I + wp u+ u+^T + wm u- u-^T
-#pragma unroll
-      for (int c = 0; c < 3; ++c)
-#pragma unroll
-        for (int r = 0; r < 3; ++r) W[r + 3 * c] = (r == c ? w0 : 0.0) + ip * up[r] * up[c] + im * um[r] * um[c];
-      // J = W [ -[s]x  I ], r = W d; three rows
+      // J = W [ -[s]x  I ], r = W d, W = w0 I + wp u+ u+^T + wm u- u-^T (symmetric); three rows, staged one at a time
 #pragma unroll
       for (int row = 0; row < 3; ++row) {
-        const double wr[3] = {W[row], W[row + 3], W[row + 6]};
+        const double wr[3] = {(row == 0 ? w0 : 0.0) + ip * up[row] * up[0] + im * um[row] * um[0],
+                              (row == 1 ? w0 : 0.0) + ip * up[row] * up[1] + im * um[row] * um[1],
+                              (row == 2 ? w0 : 0.0) + ip * up[row] * up[2] + im * um[row] * um[2]};
         // -[s]x has columns (0, -s2, s1), (s2, 0, -s0), (-s1, s0, 0)
         const double J[6] = {wr[2] * s[1] - wr[1] * s[2], wr[0] * s[2] - wr[2] * s[0], wr[1] * s[0] - wr[0] * s[1],
                              wr[0], wr[1], wr[2]};
         const double r = wr[0] * d[0] + wr[1] * d[1] + wr[2] * d[2];
-        int t = 0;
+        auto emit = [&](auto&& put) {
+          int t = 0;
 #pragma unroll
-        for (int c = 0; c < 6; ++c)
+          for (int c = 0; c < 6; ++c)
 #pragma unroll
-          for (int a2 = 0; a2 <= c; ++a2) acc[t++] += J[a2] * J[c];
+            for (int a2 = 0; a2 <= c; ++a2) put(t++, J[a2] * J[c]);
 #pragma unroll
-        for (int a2 = 0; a2 < 6; ++a2) acc[21 + a2] += J[a2] * r;
+          for (int a2 = 0; a2 < 6; ++a2) put(21 + a2, J[a2] * r);
+          if (row == 0) { put(27, 1.0); put(28, (double)bd); }
+        };
+        stage_batch<0, 15>(tile, lane, hit, emit, acc);
+        stage_batch<15, 29>(tile, lane, hit, emit, acc);
       }
     }
   }
-  // CTA partial: warp shuffle tree, then warps in order (deterministic)
-#pragma unroll
-  for (int t = 0; t < 29; ++t) {
-    double v = acc[t];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane == 0) s_part[wid][t] = v;
-  }
+  // CTA partial: the warps' sums in warp order (deterministic); value t sits on lane t (t < 15) or lane t + 1
+  __syncthreads();
+  double* part = reinterpret_cast<double*>(&s_raw[0][0]);   // reused: [warp][32]
+  part[wid * 32 + lane] = acc;
   __syncthreads();
   if (tid < kVals) {
     double v = 0.0;
-    for (int w = 0; w < kThreads / 32 && tid < 29; ++w) v += s_part[w][tid];
+    if (tid < 29) {
+      const int src_lane = tid < 15 ? tid : tid + 1;
+      for (int w = 0; w < kThreads / 32; ++w) v += part[w * 32 + src_lane];
+    }
     p.partials[(size_t)blockIdx.x * kVals + tid] = v;
+  }
+}
+
+static void launch_match_lin(const O3dParams& p, int blocks, cudaStream_t s) {
+  switch (p.kind) {
+    case 0: o3d_match_lin_kernel<0><<<blocks, kThreads, 0, s>>>(p); break;
+    case 1: o3d_match_lin_kernel<1><<<blocks, kThreads, 0, s>>>(p); break;
+    case 2: o3d_match_lin_kernel<2><<<blocks, kThreads, 0, s>>>(p); break;
+    default: o3d_match_lin_kernel<3><<<blocks, kThreads, 0, s>>>(p); break;
   }
 }
 
@@ -280,7 +347,10 @@ __global__ void __launch_bounds__(kThreads) o3d_reduce_kernel(const __grid_const
 // thread 0 of the solving CTA: fitness / RMSE of this match, convergence test against the previous one, the update
 // (TransformationEstimation*::ComputeTransformation) and T <- U T. s_tot: the 32 sums over all CTAs (and all slabs).
 __device__ void o3d_solve_tail(const O3dParams& p, const double* s_tot) {
-  O3dState* st = p.st;
+  // the state is worked on in registers / local memory and written back once: every st-> access used to be a
+  // dependent round trip to L2 in this single-thread tail
+  O3dState loc = *p.st;
+  O3dState* st = &loc;
   const double cnt = s_tot[27];
   const double fit = cnt / (double)p.N;
   const double err = cnt > 0.0 ? sqrt(s_tot[28] / cnt) : 0.0;
@@ -366,6 +436,7 @@ __device__ void o3d_solve_tail(const O3dParams& p, const double* s_tot) {
     }
   }
   if (stop) st->done = 1;
+  *p.st = loc;
 }
 
 // one CTA: reduce, test convergence, solve, update
@@ -574,6 +645,7 @@ struct b200_o3d {
   O3dState* h_state = nullptr;  // pinned
   cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
   // partition (one slab of a larger map)
+  int qmap = 2;                // O3dParams::qmap (B200_O3D_QMAP overrides)
   int own_axis = -1;
   float own_lo = 0.f, own_hi = 0.f;
   int* d_gid = nullptr;
@@ -618,6 +690,7 @@ int b200_o3d_create(b200_o3d** out, int device, const b200_o3d_params* prm) {
   if (!h) { set_error("out of host memory"); return B200_E_CUDA; }
   h->device = device;
   h->prm = *prm;
+  if (const char* e = std::getenv("B200_O3D_QMAP")) h->qmap = std::atoi(e);
   h->map.device = device;
   h->nmap.device = device;
   int sms = 148;
@@ -822,7 +895,9 @@ static int o3d_begin_impl(b200_o3d* h, const float* src4xN, const float* srcn3xN
   p.rel_fitness = h->prm.relative_fitness; p.rel_rmse = h->prm.relative_rmse; p.eps = h->prm.gicp_epsilon;
   p.ids = h->d_ids; p.dists = h->d_dists; p.partials = h->d_partials; p.st = h->d_state;
   p.own_axis = h->own_axis; p.own_lo = h->own_lo; p.own_hi = h->own_hi; p.gid = h->d_gid;
-  h->blocks = std::max(1, std::min(h->max_blocks, (N + kThreads - 1) / kThreads));
+  p.qmap = h->qmap;
+  // four resident CTAs per SM (64 registers, 25 KB of shared memory each): one wave, every warp walks its slots
+  h->blocks = std::max(1, std::min(h->max_blocks / 2, (N + kThreads - 1) / kThreads));
   h->run_stream = s;
   h->launches = srcn3xN ? 1 : est_launches;
   B200_CUDA(cudaEventRecord(h->ev[1], s));
@@ -839,7 +914,7 @@ int b200_o3d_begin(b200_o3d* h, const float* src4xN, const float* srcn3xN, int N
 int b200_o3d_step_linearize(b200_o3d* h, double* d_sums32) {
   if (!h || !h->running || !d_sums32) { set_error("b200_o3d_step_linearize: no registration begun"); return B200_E_NOT_INITIALIZED; }
   DeviceGuard dg(h->device);
-  o3d_match_lin_kernel<<<h->blocks, kThreads, 0, h->run_stream>>>(h->p);
+  launch_match_lin(h->p, h->blocks, h->run_stream);
   o3d_reduce_kernel<<<1, kThreads, 0, h->run_stream>>>(h->p, h->blocks, d_sums32);
   h->launches += 2;
   B200_CUDA(cudaGetLastError());
@@ -935,7 +1010,7 @@ int b200_o3d_enqueue_peers(b200_o3d* h, const float* src4xN, const float* srcn3x
   const int now = h->peers_ipc ? std::min(kPeerChunk, total) : total;
   h->peer_pending = total - now;
   for (int it = 0; it < now; ++it) {
-    o3d_match_lin_kernel<<<h->blocks, kThreads, 0, h->run_stream>>>(h->p);
+    launch_match_lin(h->p, h->blocks, h->run_stream);
     o3d_exchange_solve_kernel<<<1, kThreads, 0, h->run_stream>>>(h->p, h->blocks, h->pv);
   }
   h->peer_seq += (unsigned)total;
@@ -982,7 +1057,7 @@ int b200_o3d_finish(b200_o3d* h, b200_o3d_result* res) {
     if (h->h_state->done || h->peer_pending <= 0) break;
     const int n = std::min(kPeerChunk, h->peer_pending);   // peer exchange across processes, not converged yet
     for (int it = 0; it < n; ++it) {
-      o3d_match_lin_kernel<<<h->blocks, kThreads, 0, s>>>(h->p);
+      launch_match_lin(h->p, h->blocks, s);
       o3d_exchange_solve_kernel<<<1, kThreads, 0, s>>>(h->p, h->blocks, h->pv);
     }
     h->peer_pending -= n;
@@ -1013,7 +1088,7 @@ int b200_o3d_information_matrix(b200_o3d* h, const float* src4xN, int N, const d
   O3dParams p = h->p;
   p.kind = 3;
   p.md2 = max_correspondence_distance * max_correspondence_distance;
-  o3d_match_lin_kernel<<<h->blocks, kThreads, 0, s>>>(p);
+  launch_match_lin(p, h->blocks, s);
   o3d_reduce_kernel<<<1, kThreads, 0, s>>>(p, h->blocks, h->d_partials + (size_t)h->max_blocks * kVals);
   B200_CUDA(cudaGetLastError());
   double sums[kVals];
@@ -1055,7 +1130,7 @@ static int o3d_register_impl(b200_o3d* h, const float* src4xN, const float* srcn
   for (int it = 0; it <= h->prm.max_iteration;) {
     const int n = std::min(kChunk, h->prm.max_iteration + 1 - it);
     for (int j = 0; j < n; ++j) {
-      o3d_match_lin_kernel<<<h->blocks, kThreads, 0, s>>>(h->p);
+      launch_match_lin(h->p, h->blocks, s);
       o3d_solve_kernel<<<1, kThreads, 0, s>>>(h->p, h->blocks, nullptr);
     }
     it += n;

@@ -25,7 +25,9 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <map>
 #include <thread>
+#include <tuple>
 #include <vector>
 #include "oracle.h"
 
@@ -363,5 +365,41 @@ extern "C" int orc_o3d_ransac_feature_matching(const float* src4xN, int Ns, cons
       }
     }
   res->n_correspondences = k;
+  return ORC_OK;
+}
+
+// computeIndicesOfOverlappingPoints (open3d_slam/src/helpers.cpp:320-345, IN the reference tree): VoxelMap with the
+// layers "target" and "source" (the source transformed by sourceToTarget first), key = getVoxelIdx(p, inverse voxel
+// size) = floor(p * (1 / voxelSize)) per axis (VoxelHashMap.hpp:43-51); the indices of every voxel that holds at least
+// minNumPointsPerVoxel points of both layers. The reference appends them in std::unordered_map order; here ascending.
+extern "C" int orc_overlap_indices(const float* src4xN, int Ns, const float* tgt4xM, int Nt, const double* T16,
+                                   double voxel_size, int min_points, int32_t* src_idx, int* n_src, int32_t* tgt_idx,
+                                   int* n_tgt) {
+  if (!(voxel_size > 0.0) || min_points < 1) return ORC_E_BAD_PARAM;
+  const double inv = 1.0 / voxel_size;
+  typedef std::tuple<int, int, int> Key;
+  std::map<Key, std::pair<int, int>> vox;
+  std::vector<Key> ks((size_t)Ns), kt((size_t)Nt);
+  for (int i = 0; i < Ns; ++i) {
+    double q[3];
+    xform(T16, src4xN + 4 * (size_t)i, q);
+    ks[i] = Key((int)std::floor(q[0] * inv), (int)std::floor(q[1] * inv), (int)std::floor(q[2] * inv));
+    ++vox[ks[i]].first;
+  }
+  for (int i = 0; i < Nt; ++i) {
+    const float* p = tgt4xM + 4 * (size_t)i;
+    kt[i] = Key((int)std::floor((double)p[0] * inv), (int)std::floor((double)p[1] * inv), (int)std::floor((double)p[2] * inv));
+    ++vox[kt[i]].second;
+  }
+  int a = 0, b = 0;
+  for (int i = 0; i < Ns; ++i) {
+    const auto& c = vox[ks[i]];
+    if (c.first >= min_points && c.second >= min_points) src_idx[a++] = i;
+  }
+  for (int i = 0; i < Nt; ++i) {
+    const auto& c = vox[kt[i]];
+    if (c.first >= min_points && c.second >= min_points) tgt_idx[b++] = i;
+  }
+  *n_src = a; *n_tgt = b;
   return ORC_OK;
 }

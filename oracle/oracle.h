@@ -198,6 +198,10 @@ int orc_o3d_ransac_feature_matching(const float* src4xN, int Ns, const float* tg
                                     const double* tf33xM, const orc_ransac_params* prm, int threads,
                                     orc_ransac_result* res, int32_t* corr2xK);
 
+/* computeIndicesOfOverlappingPoints (open3d_slam/src/helpers.cpp:320-345); outputs ascending, capacity Ns / Nt */
+int orc_overlap_indices(const float* src4xN, int Ns, const float* tgt4xM, int Nt, const double* T16, double voxel_size,
+                        int min_points, int32_t* src_idx, int* n_src, int32_t* tgt_idx, int* n_tgt);
+
 /* ---- scan pre-processing (see prep.cpp): open3d_slam croppers (croppers.cpp:25-164) and Open3D
  * VoxelDownSample (recalled from upstream v0.15.1) ---- */
 int orc_crop(int kind, double radius_min, double radius_max, double min_z, double max_z, const double* center3,

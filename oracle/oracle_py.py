@@ -468,6 +468,18 @@ def o3d_ransac(src4, tgt4, sf, tf, mutual_filter=True, max_correspondence_distan
                 mutual_used=bool(res.mutual_used), iterations_run=res.iterations_run, validations=res.validations)
 
 
+def overlap_indices(src4, tgt4, T, voxel_size, min_points=1):
+    """orc_overlap_indices -> (source indices, target indices) int32, ascending"""
+    src4, tgt4 = f32(src4), f32(tgt4)
+    Tc = np.ascontiguousarray(np.asarray(T, np.float64).T).ravel()
+    si, ti = np.empty(max(len(src4), 1), np.int32), np.empty(max(len(tgt4), 1), np.int32)
+    ns, nt = C.c_int(), C.c_int()
+    st = lib().orc_overlap_indices(_fp(src4), len(src4), _fp(tgt4), len(tgt4), Tc.ctypes.data_as(C.POINTER(C.c_double)),
+                                   C.c_double(voxel_size), int(min_points), _ip(si), C.byref(ns), _ip(ti), C.byref(nt))
+    assert st == ORC_OK, st
+    return si[:ns.value].copy(), ti[:nt.value].copy()
+
+
 def crop(kind, pts4, radius_min=0.0, radius_max=0.0, min_z=0.0, max_z=0.0, center=(0.0, 0.0, 0.0), invert=False):
     """orc_crop -> indices of the kept points, input order (croppers.cpp:66-95)"""
     pts4 = f32(pts4)

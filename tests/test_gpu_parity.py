@@ -302,6 +302,8 @@ def test_icp_validT3d_and_parity(gold):
     dict(use_trimmed=0, use_maxdist_filter=1, maxdist_filter=0.3),
     dict(use_trimmed=0),                                                                      # empty filter chain
     dict(knn=3, trimmed_ratio=0.7),
+    dict(knn=20, trimmed_ratio=0.8, max_iterations=6),                                        # k-best list of 32
+    dict(knn=40, trimmed_ratio=0.8, maxDist=2.0, max_iterations=4),                           # k-best list of 64
     dict(minimizer=1, trimmed_ratio=0.8),                                                     # point-to-point
     dict(use_differential=0, max_iterations=7),
     dict(trimmed_ratio=1.0, maxDist=0.2),

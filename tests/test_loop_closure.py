@@ -179,6 +179,21 @@ def test_oracle_ransac_recovers_the_submap_transform():
     assert (r2["T"] == r["T"]).all() and r2["iterations_run"] == r["iterations_run"]
 
 
+def test_oracle_overlap_indices_known_answer():
+    # voxel 1.0: source points (after a +10 shift in x) and target points share voxel (10, 0, 0) only
+    src = O.feat4(np.array([[0.2, 0.3, 0.4], [0.7, 0.1, 0.9], [5.5, 0.5, 0.5], [-0.5, 0.5, 0.5]], np.float32))
+    tgt = O.feat4(np.array([[10.9, 0.9, 0.1], [3.5, 0.5, 0.5], [10.1, 0.2, 0.3], [9.5, 0.5, 0.5]], np.float32))
+    T = np.eye(4); T[0, 3] = 10.0
+    si, ti = O.overlap_indices(src, tgt, T, 1.0, 1)
+    assert si.tolist() == [0, 1, 3] and ti.tolist() == [0, 2, 3]      # (-0.5 + 10) and 9.5 share voxel 9
+    si, ti = O.overlap_indices(src, tgt, T, 1.0, 2)
+    assert si.tolist() == [0, 1] and ti.tolist() == [0, 2]
+    # negative coordinates floor downwards (VoxelHashMap.hpp:48-51)
+    si, ti = O.overlap_indices(O.feat4(np.array([[-0.1, 0, 0]], np.float32)), O.feat4(np.array([[0.1, 0, 0]], np.float32)),
+                               np.eye(4), 1.0, 1)
+    assert len(si) == 0 and len(ti) == 0
+
+
 def test_ransac_struct_sizes_match_header():
     lib = B.load()
     assert ctypes.sizeof(B.RansacParams) == lib.b200_struct_size(6)
@@ -316,3 +331,20 @@ def test_ransac_exact_correspondences_known_answer():
     o = O.o3d_ransac(O.feat4(src), O.feat4(tgt[perm]), feat, feat[perm], **kw)
     assert_ransac_equal(r, o)
     assert r["fitness"] == 1.0 and np.abs(r["T"] - T).max() < 1e-4
+
+
+@pytest.mark.gpu
+def test_overlap_indices_bit_exact():
+    # PlaceRecognition.cpp:98-108: the dense submaps, the RANSAC pose, voxel = 3 x the map voxel size
+    p = synth.make_c4(n_distinct=1, N=60_000)[0]
+    src4, tgt4 = synth.feat4(p["src_xyz"]), synth.feat4(p["tgt_xyz"])
+    lc = B.LoopClosure()
+    for vox, mn, T in ((0.3, 1, p["T_true"]), (0.75, 3, p["T_init"]), (2.0, 40, np.eye(4))):
+        si, ti = lc.overlap_indices(src4, tgt4, T, vox, mn)
+        osi, oti = O.overlap_indices(src4, tgt4, T, vox, mn)
+        assert len(si) == len(osi) and (si == osi).all() and len(ti) == len(oti) and (ti == oti).all()
+    assert 0 < len(si) < len(src4)
+    si, ti = lc.overlap_indices(src4[:0], tgt4, np.eye(4), 0.5, 1)
+    assert len(si) == 0 and len(ti) == 0
+    with pytest.raises(B.B200Error):
+        lc.overlap_indices(src4, tgt4, np.eye(4), 0.0, 1)
