@@ -172,7 +172,9 @@ __global__ void __launch_bounds__(kThreads, 4) o3d_match_lin_kernel(const __grid
           for (int c = 0; c < 6; ++c)
 #pragma unroll
             for (int a = 0; a <= c; ++a) put(t++, G[a] * G[c]);
-          if (r == 0) { put(27, 1.0); put(28, (double)bd); }
+#pragma unroll
+          for (int u = 21; u < 27; ++u) put(u, 0.0);
+          put(27, r == 0 ? 1.0 : 0.0); put(28, r == 0 ? (double)bd : 0.0);   // every row of the tile is rewritten
         };
         stage_batch<0, 15>(tile, lane, hit, emit, acc);
         stage_batch<15, 29>(tile, lane, hit, emit, acc);
@@ -187,6 +189,8 @@ __global__ void __launch_bounds__(kThreads, 4) o3d_match_lin_kernel(const __grid
         for (int c = 0; c < 3; ++c)
 #pragma unroll
           for (int r = 0; r < 3; ++r) put(6 + r + 3 * c, t[r] * s[c]);
+#pragma unroll
+        for (int u = 15; u < 27; ++u) put(u, 0.0);
         put(27, 1.0); put(28, (double)bd);
       };
       stage_batch<0, 15>(tile, lane, hit, emit, acc);
@@ -240,7 +244,7 @@ __global__ void __launch_bounds__(kThreads, 4) o3d_match_lin_kernel(const __grid
             for (int a2 = 0; a2 <= c; ++a2) put(t++, J[a2] * J[c]);
 #pragma unroll
           for (int a2 = 0; a2 < 6; ++a2) put(21 + a2, J[a2] * r);
-          if (row == 0) { put(27, 1.0); put(28, (double)bd); }
+          put(27, row == 0 ? 1.0 : 0.0); put(28, row == 0 ? (double)bd : 0.0);
         };
         stage_batch<0, 15>(tile, lane, hit, emit, acc);
         stage_batch<15, 29>(tile, lane, hit, emit, acc);
@@ -662,6 +666,7 @@ struct b200_o3d {
   bool peers_ipc = false;     // peers live in other processes: b200_o3d_finish may enqueue the iterations in chunks
   int peer_pending = 0;       // iterations of the running registration not enqueued yet
   unsigned peer_seq = 0;
+  bool peer_run = false;      // the running registration exchanges over the mailboxes
   void* opened[kPeerMax] = {};   // mailboxes mapped with cudaIpcOpenMemHandle
 };
 
@@ -988,7 +993,9 @@ int b200_o3d_peer_connect(b200_o3d* h, void* const* mailboxes_dev, const int* de
   }
   int khz = 0;
   cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, h->device);
-  h->pv.timeout_cycles = (long long)(khz > 0 ? khz : 1500000) * 1000LL * 5LL;   // 5 s of SM clock
+  long long timeout_ms = 5000;   // 5 s of SM clock; B200_O3D_PEER_TIMEOUT_MS overrides (tests of the failure path)
+  if (const char* e = std::getenv("B200_O3D_PEER_TIMEOUT_MS")) timeout_ms = std::max(1LL, std::atoll(e));
+  h->pv.timeout_cycles = (long long)(khz > 0 ? khz : 1500000) * timeout_ms;
   h->peers_ready = true;
   return B200_OK;
 }
@@ -1013,7 +1020,7 @@ int b200_o3d_enqueue_peers(b200_o3d* h, const float* src4xN, const float* srcn3x
     launch_match_lin(h->p, h->blocks, h->run_stream);
     o3d_exchange_solve_kernel<<<1, kThreads, 0, h->run_stream>>>(h->p, h->blocks, h->pv);
   }
-  h->peer_seq += (unsigned)total;
+  h->peer_run = true;   // b200_o3d_finish advances peer_seq by the steps actually taken
   h->launches += 2 * now;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
@@ -1040,7 +1047,7 @@ static int o3d_fill_result(b200_o3d* h, b200_o3d_result* res) {
   B200_CUDA(cudaEventElapsedTime(&res->device_ms, h->ev[1], h->ev[2]));
   B200_CUDA(cudaEventElapsedTime(&res->total_ms, h->ev[0], h->ev[2]));
   if (h->h_state->status != 0) {
-    set_error("b200_o3d: a peer's sums did not arrive within 5 s (rank missing or out of step)");
+    set_error("b200_o3d: a peer's sums did not arrive within the time limit (5 s by default; rank missing or out of step): re-run b200_o3d_peer_init / peer_connect on all ranks");
     return h->h_state->status;
   }
   return B200_OK;
@@ -1065,6 +1072,13 @@ int b200_o3d_finish(b200_o3d* h, b200_o3d_result* res) {
     B200_CUDA(cudaGetLastError());
   }
   h->peer_pending = 0;
+  if (h->peer_run) {
+    // Sequence numbers stay consecutive across registrations (every rank takes the same number of steps: the totals
+    // are bit-identical), so the two parity slots of the mailbox are enough at the boundary as well: a rank that has
+    // started the next registration is one step ahead of a peer still reading the last step, never two.
+    h->peer_seq = h->pv.seq_base + (unsigned)h->h_state->matches_done;
+    h->peer_run = false;
+  }
   return o3d_fill_result(h, res);
 }
 

@@ -7,6 +7,7 @@ GPU part: two slabs driven step by step on one device with the sums added in bet
 reproduce the un-partitioned device registration; with >= 2 GPUs the same through NCCL.
 """
 import os
+import time
 import socket
 
 import numpy as np
@@ -209,6 +210,40 @@ def test_slabs_exchanging_over_mailboxes_equal_unpartitioned(n_slabs):
         assert (ids == ref_ids).all()
     for h in hs:
         h.close()
+
+
+@pytest.mark.gpu
+def test_peer_exchange_times_out_instead_of_hanging(monkeypatch):
+    """A peer that never delivers (crashed rank, rank out of step): the exchange kernel gives up after the time limit
+    (5 s of SM clock by default, 0.2 s here), the remaining enqueued iterations return at once, b200_o3d_finish reports
+    the failure, and the device stays usable."""
+    from open3d_slam_private_b200 import capi as B
+    monkeypatch.setenv("B200_O3D_PEER_TIMEOUT_MS", "200")
+    tgt4, tgtn, src4 = _clouds()
+    kw = dict(kind=0, max_correspondence_distance=MD, max_iteration=30)
+    axis, edges = P.plan_slabs(tgt4, 2)
+    hs, ptrs = [], []
+    for g in range(2):
+        gid = P.slab_members(tgt4, axis, edges, g, MD)
+        h = B.O3dICP(**kw)
+        h.set_target(np.ascontiguousarray(tgt4[gid]), np.ascontiguousarray(tgtn[gid]))
+        h.set_partition(axis, float(edges[g]), float(edges[g + 1]), gid)
+        ptrs.append(h.peer_init(g, 2)[0])
+        hs.append(h)
+    for h in hs:
+        h.peer_connect(pointers=ptrs, devices=[0, 0])
+    t0 = time.perf_counter()
+    hs[0].enqueue_peers(src4)              # slab 1 never takes part
+    with pytest.raises(B.B200Error) as e:
+        hs[0].finish()
+    assert "did not arrive" in str(e.value)
+    assert time.perf_counter() - t0 < 3.0
+    for h in hs:
+        h.close()
+    whole = B.O3dICP(**kw)                 # the device is fine
+    whole.set_target(tgt4, tgtn)
+    assert whole.register(src4)["iterations"] > 0
+    whole.close()
 
 
 def _nccl_worker(rank, world, port, q, exchange="nccl"):
