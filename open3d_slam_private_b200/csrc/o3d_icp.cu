@@ -329,27 +329,46 @@ __device__ void kabsch3(const double* S, double* R) {
     for (int r = 0; r < 3; ++r) R[r + 3 * c] = u1[r] * v1[c] + u2[r] * v2[c] + sgn * u3[r] * v3[c];
 }
 
-// one CTA: this device's partials -> out[kVals] (zeros once the registration is done, so a late allreduce is harmless)
-__global__ void __launch_bounds__(kThreads) o3d_reduce_kernel(const __grid_constant__ O3dParams p, int nblocks,
-                                                              double* __restrict__ out) {
-  __shared__ double s_sum[kThreads / kVals][kVals];
+// This device's sums from the CTA partials, fixed order (slice-major over CTAs, eight loads in flight per thread, then
+// the slices in order): the reduction is a chain of L2 latencies, so it is spread over kRedThreads = 1024 threads
+// (32 slices x 32 values: 19 partials per thread at 592 CTAs instead of 74 with 256 threads).
+constexpr int kRedThreads = 1024;
+constexpr int kRedSlices = kRedThreads / kVals;
+__device__ __forceinline__ void reduce_partials_cta(const double* __restrict__ partials, int nblocks, bool live,
+                                                    double (*s_sum)[kVals], double* s_tot) {
   const int tid = threadIdx.x;
   const int c = tid & (kVals - 1), slice = tid / kVals;
-  constexpr int kSlices = kThreads / kVals;
   double s = 0.0;
-  if (!p.st->done)
-    for (int b = slice; b < nblocks; b += kSlices) s += p.partials[(size_t)b * kVals + c];
+  if (live) {
+    int b = slice;
+    for (; b + 7 * kRedSlices < nblocks; b += 8 * kRedSlices) {
+      double v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = __ldcg(&partials[(size_t)(b + u * kRedSlices) * kVals + c]);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) s += v[u];
+    }
+    for (; b < nblocks; b += kRedSlices) s += __ldcg(&partials[(size_t)b * kVals + c]);
+  }
   s_sum[slice][c] = s;
   __syncthreads();
   if (tid < kVals) {
     double t = 0.0;
-    for (int sl = 0; sl < kSlices; ++sl) t += s_sum[sl][tid];
-    out[tid] = t;
+    for (int sl = 0; sl < kRedSlices; ++sl) t += s_sum[sl][tid];
+    s_tot[tid] = t;
   }
+  __syncthreads();
 }
 
-// thread 0 of the solving CTA: fitness / RMSE of this match, convergence test against the previous one, the update
-// (TransformationEstimation*::ComputeTransformation) and T <- U T. s_tot: the 32 sums over all CTAs (and all slabs).
+// one CTA: this device's partials -> out[kVals] (zeros once the registration is done, so a late allreduce is harmless)
+__global__ void __launch_bounds__(kRedThreads) o3d_reduce_kernel(const __grid_constant__ O3dParams p, int nblocks,
+                                                                 double* __restrict__ out) {
+  __shared__ double s_sum[kRedSlices][kVals];
+  __shared__ double s_tot[kVals];
+  reduce_partials_cta(p.partials, nblocks, !p.st->done, s_sum, s_tot);
+  if (threadIdx.x < kVals) out[threadIdx.x] = s_tot[threadIdx.x];
+}
+
 __device__ void o3d_solve_tail(const O3dParams& p, const double* s_tot) {
   // the state is worked on in registers / local memory and written back once: every st-> access used to be a
   // dependent round trip to L2 in this single-thread tail
@@ -446,9 +465,9 @@ __device__ void o3d_solve_tail(const O3dParams& p, const double* s_tot) {
 // one CTA: reduce, test convergence, solve, update
 // sums == nullptr: reduce this device's partials and go on; otherwise `sums` already holds the totals over all slabs
 // (after the allreduce) and the partials are not read
-__global__ void __launch_bounds__(kThreads) o3d_solve_kernel(const __grid_constant__ O3dParams p, int nblocks,
-                                                             const double* __restrict__ sums) {
-  __shared__ double s_sum[kThreads / kVals][kVals];
+__global__ void __launch_bounds__(kRedThreads) o3d_solve_kernel(const __grid_constant__ O3dParams p, int nblocks,
+                                                                const double* __restrict__ sums) {
+  __shared__ double s_sum[kRedSlices][kVals];
   __shared__ double s_tot[kVals];
   O3dState* st = p.st;
   if (st->done) return;
@@ -456,19 +475,8 @@ __global__ void __launch_bounds__(kThreads) o3d_solve_kernel(const __grid_consta
   if (sums) {
     if (tid < kVals) s_tot[tid] = sums[tid];
     __syncthreads();
-  } else {  // fixed order: slice-major over CTAs, then slices in order
-    const int c = tid & (kVals - 1), slice = tid / kVals;
-    constexpr int kSlices = kThreads / kVals;
-    double s = 0.0;
-    for (int b = slice; b < nblocks; b += kSlices) s += p.partials[(size_t)b * kVals + c];
-    s_sum[slice][c] = s;
-    __syncthreads();
-    if (tid < kVals) {
-      double t = 0.0;
-      for (int sl = 0; sl < kSlices; ++sl) t += s_sum[sl][tid];
-      s_tot[tid] = t;
-    }
-    __syncthreads();
+  } else {
+    reduce_partials_cta(p.partials, nblocks, true, s_sum, s_tot);
   }
   if (tid != 0) return;
   o3d_solve_tail(p, s_tot);
@@ -502,9 +510,9 @@ __device__ __forceinline__ unsigned long long peer_load(const unsigned long long
   return v;
 }
 
-__global__ void __launch_bounds__(kThreads) o3d_exchange_solve_kernel(const __grid_constant__ O3dParams p, int nblocks,
-                                                                      const __grid_constant__ PeerView pv) {
-  __shared__ double s_sum[kThreads / kVals][kVals];
+__global__ void __launch_bounds__(kRedThreads) o3d_exchange_solve_kernel(const __grid_constant__ O3dParams p, int nblocks,
+                                                                         const __grid_constant__ PeerView pv) {
+  __shared__ double s_sum[kRedSlices][kVals];
   __shared__ double s_tot[kVals];
   __shared__ unsigned s_half[kPeerMax][kPackets];
   __shared__ int s_fail;
@@ -512,24 +520,11 @@ __global__ void __launch_bounds__(kThreads) o3d_exchange_solve_kernel(const __gr
   if (st->done) return;
   const int tid = threadIdx.x;
   if (tid == 0) s_fail = 0;
-  {  // this device's sums, fixed order: slice-major over CTAs, then slices in order
-    const int c = tid & (kVals - 1), slice = tid / kVals;
-    constexpr int kSlices = kThreads / kVals;
-    double s = 0.0;
-    for (int b = slice; b < nblocks; b += kSlices) s += p.partials[(size_t)b * kVals + c];
-    s_sum[slice][c] = s;
-    __syncthreads();
-    if (tid < kVals) {
-      double t = 0.0;
-      for (int sl = 0; sl < kSlices; ++sl) t += s_sum[sl][tid];
-      s_tot[tid] = t;
-    }
-    __syncthreads();
-  }
+  reduce_partials_cta(p.partials, nblocks, true, s_sum, s_tot);   // ends with a barrier: s_fail is visible too
   const unsigned seq = pv.seq_base + (unsigned)st->matches_done + 1u;
   const size_t par = (size_t)(seq & 1u) * (size_t)pv.world;
   // scatter: packet k of my sums into slot [parity][my rank] of every rank's mailbox (mine included)
-  for (int t = tid; t < pv.world * kPackets; t += kThreads) {
+  for (int t = tid; t < pv.world * kPackets; t += kRedThreads) {
     const int r = t / kPackets, k = t - r * kPackets;
     const unsigned long long bits = (unsigned long long)__double_as_longlong(s_tot[k >> 1]);
     const unsigned half = (k & 1) ? (unsigned)(bits >> 32) : (unsigned)bits;
@@ -537,7 +532,7 @@ __global__ void __launch_bounds__(kThreads) o3d_exchange_solve_kernel(const __gr
   }
   // gather: wait for packet k of every rank in my own mailbox
   const long long t0 = clock64();
-  for (int t = tid; t < pv.world * kPackets; t += kThreads) {
+  for (int t = tid; t < pv.world * kPackets; t += kRedThreads) {
     const int r = t / kPackets, k = t - r * kPackets;
     const unsigned long long* a = pv.box[pv.rank] + (par + (size_t)r) * kPackets + k;
     unsigned long long v = peer_load(a);
@@ -920,7 +915,7 @@ int b200_o3d_step_linearize(b200_o3d* h, double* d_sums32) {
   if (!h || !h->running || !d_sums32) { set_error("b200_o3d_step_linearize: no registration begun"); return B200_E_NOT_INITIALIZED; }
   DeviceGuard dg(h->device);
   launch_match_lin(h->p, h->blocks, h->run_stream);
-  o3d_reduce_kernel<<<1, kThreads, 0, h->run_stream>>>(h->p, h->blocks, d_sums32);
+  o3d_reduce_kernel<<<1, kRedThreads, 0, h->run_stream>>>(h->p, h->blocks, d_sums32);
   h->launches += 2;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
@@ -929,7 +924,7 @@ int b200_o3d_step_linearize(b200_o3d* h, double* d_sums32) {
 int b200_o3d_step_update(b200_o3d* h, const double* d_sums32) {
   if (!h || !h->running || !d_sums32) { set_error("b200_o3d_step_update: no registration begun"); return B200_E_NOT_INITIALIZED; }
   DeviceGuard dg(h->device);
-  o3d_solve_kernel<<<1, kThreads, 0, h->run_stream>>>(h->p, h->blocks, d_sums32);
+  o3d_solve_kernel<<<1, kRedThreads, 0, h->run_stream>>>(h->p, h->blocks, d_sums32);
   h->launches += 1;
   B200_CUDA(cudaGetLastError());
   return B200_OK;
@@ -1018,7 +1013,7 @@ int b200_o3d_enqueue_peers(b200_o3d* h, const float* src4xN, const float* srcn3x
   h->peer_pending = total - now;
   for (int it = 0; it < now; ++it) {
     launch_match_lin(h->p, h->blocks, h->run_stream);
-    o3d_exchange_solve_kernel<<<1, kThreads, 0, h->run_stream>>>(h->p, h->blocks, h->pv);
+    o3d_exchange_solve_kernel<<<1, kRedThreads, 0, h->run_stream>>>(h->p, h->blocks, h->pv);
   }
   h->peer_run = true;   // b200_o3d_finish advances peer_seq by the steps actually taken
   h->launches += 2 * now;
@@ -1065,7 +1060,7 @@ int b200_o3d_finish(b200_o3d* h, b200_o3d_result* res) {
     const int n = std::min(kPeerChunk, h->peer_pending);   // peer exchange across processes, not converged yet
     for (int it = 0; it < n; ++it) {
       launch_match_lin(h->p, h->blocks, s);
-      o3d_exchange_solve_kernel<<<1, kThreads, 0, s>>>(h->p, h->blocks, h->pv);
+      o3d_exchange_solve_kernel<<<1, kRedThreads, 0, s>>>(h->p, h->blocks, h->pv);
     }
     h->peer_pending -= n;
     h->launches += 2 * n;
@@ -1103,7 +1098,7 @@ int b200_o3d_information_matrix(b200_o3d* h, const float* src4xN, int N, const d
   p.kind = 3;
   p.md2 = max_correspondence_distance * max_correspondence_distance;
   launch_match_lin(p, h->blocks, s);
-  o3d_reduce_kernel<<<1, kThreads, 0, s>>>(p, h->blocks, h->d_partials + (size_t)h->max_blocks * kVals);
+  o3d_reduce_kernel<<<1, kRedThreads, 0, s>>>(p, h->blocks, h->d_partials + (size_t)h->max_blocks * kVals);
   B200_CUDA(cudaGetLastError());
   double sums[kVals];
   B200_CUDA(cudaMemcpyAsync(sums, h->d_partials + (size_t)h->max_blocks * kVals, sizeof(sums), cudaMemcpyDeviceToHost, s));
@@ -1145,7 +1140,7 @@ static int o3d_register_impl(b200_o3d* h, const float* src4xN, const float* srcn
     const int n = std::min(kChunk, h->prm.max_iteration + 1 - it);
     for (int j = 0; j < n; ++j) {
       launch_match_lin(h->p, h->blocks, s);
-      o3d_solve_kernel<<<1, kThreads, 0, s>>>(h->p, h->blocks, nullptr);
+      o3d_solve_kernel<<<1, kRedThreads, 0, s>>>(h->p, h->blocks, nullptr);
     }
     it += n;
     h->launches += 2 * n;
