@@ -30,6 +30,7 @@
 //                         CTA then walks the batch in iteration order exactly like the sequential loop would (best
 //                         result, exit estimate), so the answer does not depend on the batch size.
 #include <cstring>
+#include <cstdlib>
 #include <new>
 #include <algorithm>
 #include "grid_index.cuh"
@@ -239,10 +240,46 @@ __global__ void __launch_bounds__(36 * kFpfhPts) fpfh_kernel(const float4* __res
 // ---- feature-space 1-NN -------------------------------------------------------------------------------------------
 constexpr int kNNThreads = 128;
 constexpr int kNNTile = 32;
+constexpr int kNNTileBytes = kNNTile * 33 * (int)sizeof(double);   // 8448 = 528 x 16
+
+// 1-D TMA (cp.async.bulk) + mbarrier helpers: a tile of 32 feature columns is ONE contiguous, 16-byte aligned run of
+// 8448 bytes in global memory — exactly what the bulk-copy engine moves without occupying a single load slot.
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra LAB_DONE;\n"
+      "bra LAB_WAIT;\n"
+      "LAB_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+
+// TMA = true: two shared-memory stages filled by cp.async.bulk (one elected thread, completion on an mbarrier), the
+// copy of tile t + 1 in flight while tile t is scanned, one __syncthreads per tile (stage release). TMA = false: every
+// thread loads its share of the tile with ordinary loads, two __syncthreads per tile. Same arithmetic, same results.
+// b must be readable up to the next multiple of 16 bytes behind column M - 1 (the callers allocate the slack).
+template <bool TMA>
 __global__ void __launch_bounds__(kNNThreads) feature_nn_kernel(const double* __restrict__ a, int N,
                                                                 const double* __restrict__ b, int M, int chunk,
                                                                 double* __restrict__ part_d, int* __restrict__ part_j) {
-  __shared__ double s_b[kNNTile * 33];
+  __shared__ __align__(128) double s_b[TMA ? 2 : 1][kNNTile * 33];
+  __shared__ __align__(8) unsigned long long s_bar[2];
   const int i = blockIdx.x * kNNThreads + threadIdx.x;
   const int j0 = blockIdx.y * chunk, j1 = min(M, j0 + chunk);
   double f[33];
@@ -250,16 +287,48 @@ __global__ void __launch_bounds__(kNNThreads) feature_nn_kernel(const double* __
   for (int t = 0; t < 33; ++t) f[t] = i < N ? a[(size_t)33 * i + t] : 0.0;
   double best = INFINITY;
   int bj = -1;
-  for (int j = j0; j < j1; j += kNNTile) {
+  const int ntiles = (j1 - j0 + kNNTile - 1) / kNNTile;
+  auto tile_bytes = [&](int t) {
+    const int nt = min(kNNTile, j1 - (j0 + t * kNNTile));
+    return (unsigned)((nt * 33 * (int)sizeof(double) + 15) & ~15);
+  };
+  if (TMA) {
+    if (threadIdx.x == 0) {
+      mbar_init(&s_bar[0], 1);
+      mbar_init(&s_bar[1], 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0)
+      for (int t = 0; t < 2 && t < ntiles; ++t) {
+        mbar_expect_tx(&s_bar[t], tile_bytes(t));
+        bulk_g2s(s_b[t], b + (size_t)33 * (j0 + t * kNNTile), tile_bytes(t), &s_bar[t]);
+      }
+  }
+  for (int t = 0; t < ntiles; ++t) {
+    const int j = j0 + t * kNNTile;
     const int nt = min(kNNTile, j1 - j);
-    __syncthreads();
-    for (int t = threadIdx.x; t < nt * 33; t += kNNThreads) s_b[t] = b[(size_t)33 * j + t];
-    __syncthreads();
+    const int st = TMA ? (t & 1) : 0;
+    if (TMA) {
+      mbar_wait(&s_bar[st], (unsigned)((t >> 1) & 1));
+    } else {
+      __syncthreads();
+      for (int u = threadIdx.x; u < nt * 33; u += kNNThreads) s_b[0][u] = b[(size_t)33 * j + u];
+      __syncthreads();
+    }
+    const double* tb = s_b[st];
     for (int jj = 0; jj < nt; ++jj) {
       double d = 0.0;
 #pragma unroll
-      for (int t = 0; t < 33; ++t) { const double e = f[t] - s_b[jj * 33 + t]; d += e * e; }
+      for (int u = 0; u < 33; ++u) { const double e = f[u] - tb[jj * 33 + u]; d += e * e; }
       if (d < best) { best = d; bj = j + jj; }
+    }
+    if (TMA) {
+      __syncthreads();   // every thread is done with this stage: refill it with tile t + 2
+      if (threadIdx.x == 0 && t + 2 < ntiles) {
+        mbar_expect_tx(&s_bar[st], tile_bytes(t + 2));
+        bulk_g2s(s_b[st], b + (size_t)33 * (j0 + (t + 2) * kNNTile), tile_bytes(t + 2), &s_bar[st]);
+      }
     }
   }
   if (i < N) {
@@ -770,7 +839,9 @@ static int feature_nn(b200_lc* h, const double* d_a, int N, const double* d_b, i
   chunks = (M + chunk - 1) / chunk;
   B200_TRY(grow(&h->d_part_d, &h->cap_part_d, (size_t)chunks * N));
   B200_TRY(grow(&h->d_part_j, &h->cap_part_j, (size_t)chunks * N));
-  feature_nn_kernel<<<dim3(blocks_x, chunks), kNNThreads, 0, s>>>(d_a, N, d_b, M, chunk, h->d_part_d, h->d_part_j);
+  static const bool use_tma = [] { const char* e = std::getenv("B200_LC_TMA"); return !e || std::atoi(e) != 0; }();
+  if (use_tma) feature_nn_kernel<true><<<dim3(blocks_x, chunks), kNNThreads, 0, s>>>(d_a, N, d_b, M, chunk, h->d_part_d, h->d_part_j);
+  else feature_nn_kernel<false><<<dim3(blocks_x, chunks), kNNThreads, 0, s>>>(d_a, N, d_b, M, chunk, h->d_part_d, h->d_part_j);
   B200_CUDA(cudaGetLastError());
   feature_nn_reduce_kernel<<<(N + 255) / 256, 256, 0, s>>>(h->d_part_d, h->d_part_j, N, chunks, d_nn, d_d2);
   B200_CUDA(cudaGetLastError());
@@ -871,8 +942,8 @@ int b200_lc_feature_nn(b200_lc* h, const double* a33xN, int N, const double* b33
   DeviceGuard dg(h->device);
   if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
   cudaStream_t s = h->stream;
-  B200_TRY(grow(&h->d_sf, &h->cap_sf, (size_t)33 * N));
-  B200_TRY(grow(&h->d_tf, &h->cap_tf, (size_t)33 * M));
+  B200_TRY(grow(&h->d_sf, &h->cap_sf, (size_t)33 * N + 2));   // + 16 bytes: the bulk copies round a tile up to 16
+  B200_TRY(grow(&h->d_tf, &h->cap_tf, (size_t)33 * M + 2));
   B200_TRY(grow(&h->d_ij, &h->cap_ij, (size_t)N));
   B200_TRY(grow(&h->d_err2, &h->cap_err2, (size_t)N));
   B200_CUDA(cudaMemcpyAsync(h->d_sf, a33xN, (size_t)33 * N * sizeof(double), cudaMemcpyHostToDevice, s));
@@ -922,8 +993,8 @@ int b200_lc_ransac_feature_matching(b200_lc* h, const float* src4xN, int Ns, con
   cudaStream_t s = h->stream;
   B200_TRY(grow(&h->d_src, &h->cap_src, (size_t)Ns));
   B200_TRY(grow(&h->d_tgt, &h->cap_tgt, (size_t)Nt));
-  B200_TRY(grow(&h->d_sf, &h->cap_sf, (size_t)33 * Ns));
-  B200_TRY(grow(&h->d_tf, &h->cap_tf, (size_t)33 * Nt));
+  B200_TRY(grow(&h->d_sf, &h->cap_sf, (size_t)33 * Ns + 2));
+  B200_TRY(grow(&h->d_tf, &h->cap_tf, (size_t)33 * Nt + 2));
   B200_TRY(grow(&h->d_ij, &h->cap_ij, (size_t)Ns));
   B200_TRY(grow(&h->d_ji, &h->cap_ji, (size_t)Nt));
   B200_TRY(grow(&h->d_cs, &h->cap_cs, (size_t)Ns));
