@@ -377,18 +377,31 @@ int index_build(MapIndex& idx, const b200_index_opts* opts) {
       // occupancy (2-D scaling law), at most 4 histogram passes
       cell = ext > 0.f ? ext * std::sqrt(target / (float)idx.M) : 1.f;
       cell = std::max(cell, min_cell);
+      bool capped = false;   // the cell is the finest one the table cap allows: nothing finer to try
       for (int pass = 0; pass < 4; ++pass) {
         while (!dims_for(e, cell, max_cells, idx)) cell *= 1.26f;
         cell = idx.cell;
         B200_TRY(histogram_pass(idx, occ));
+        if (capped) break;
         const float per = (float)idx.M / (float)std::max<int64_t>(1, occ);
         if (per > target / 1.5f && per < target * 1.5f) break;
         float next = cell * std::sqrt(target / per);
         next = std::max(next, min_cell);
         if (std::fabs(next - cell) < 0.05f * cell || pass == 3) break;
-        // would the finer table still fit? if not, keep the current one
+        // Would the finer table still fit? If not, go straight to the finest one that does and stop there (a raw scan:
+        // a few dense square metres around the sensor inside a bounding box of hectares — keeping the coarse cell left
+        // 28 points per occupied cell and 614 candidates per k = 20 query where the finest feasible table has ~150).
         MapIndex probe = idx;
-        if (next < cell && !dims_for(e, next, max_cells, probe)) break;
+        if (next < cell && !dims_for(e, next, max_cells, probe)) {
+          float lo = next, hi = cell;   // lo does not fit, hi does
+          for (int it = 0; it < 16; ++it) {
+            const float mid = std::sqrt(lo * hi);
+            if (dims_for(e, mid, max_cells, probe)) hi = mid; else lo = mid;
+          }
+          if (!(hi < 0.95f * cell)) break;
+          next = hi;
+          capped = true;
+        }
         cell = next;
       }
     }

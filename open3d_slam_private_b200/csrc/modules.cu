@@ -535,7 +535,10 @@ __global__ void __launch_bounds__(128) surface_normal_kernel(const __grid_consta
 // the lanes), mean and covariance accumulated in LIST ORDER with the same float operations as the per-thread kernel
 // (lanes 0..8 own one covariance entry each); the 9 entries move to the lane that owns the point. Phase 2: every lane
 // finishes its own point (rank test, eigen-decomposition, outputs).
-__global__ void __launch_bounds__(128) surface_normal_warp_kernel(const __grid_constant__ GridView g,
+#ifndef B200_SN_MINBLOCKS
+#define B200_SN_MINBLOCKS 8   // 64 registers: 32 resident warps per SM (measured on the 5 M-point map, k = 20: 17.7 -> 14.6 ms)
+#endif
+__global__ void __launch_bounds__(128, B200_SN_MINBLOCKS) surface_normal_warp_kernel(const __grid_constant__ GridView g,
                                                                   const float4* __restrict__ feat, int N, int knn,
                                                                   float md2, int sortEigen, float* __restrict__ normals,
                                                                   float* __restrict__ dens, float* __restrict__ eigva,
