@@ -460,8 +460,8 @@ int b200_p2plane_solve(int device, const float* H36, const float* b6, float* x6,
   CallCtx c(device);
   B200_TRY(c.open());
   Tmp io;
-  B200_TRY(io.alloc(65 * 4, c.s));
-  float buf[65] = {0};
+  B200_TRY(io.alloc(66 * 4, c.s));
+  float buf[66] = {0};   // 36 H, 6 b | 6 x, 16 T, solve info, the warp path's verdict
   std::memcpy(buf, H36, 36 * 4);
   std::memcpy(buf + 36, b6, 6 * 4);
   B200_TRY(h2d(io.p, buf, sizeof(buf), c.s));

@@ -142,8 +142,12 @@ __global__ void __launch_bounds__(256) slab_match_kernel(GridView g, const int* 
   __syncthreads();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int nthreads = gridDim.x * blockDim.x;
-  for (int base = blockIdx.x * blockDim.x + wid * 32; base < N; base += nthreads) {
-    const int i = base + lane;
+  // lane l of warp slot w takes query l * nslots + w: scan neighbours (equally expensive searches) are spread over all
+  // warps — on the dense C5 slabs 32 consecutive points per warp cost twice as much per pass (o3d_match_lin_kernel,
+  // B200_O3D_QMAP sweep); every output is written by query index, so the map does not change a bit of the result
+  const int nslots = (N + 31) >> 5;
+  for (int slot = blockIdx.x * (blockDim.x >> 5) + wid; slot < nslots; slot += nthreads >> 5) {
+    const int i = lane * nslots + (slot + lane * 97) % nslots;
     const bool in = i < N;
     const float4 q = in ? apply_T(Tc, __ldg(&reading[i])) : make_float4(0.f, 0.f, 0.f, 1.f);
     const float c = axis == 0 ? q.x : (axis == 1 ? q.y : q.z);

@@ -361,16 +361,28 @@ __global__ void hessian_final_kernel(const double* __restrict__ partials, int nb
   }
 }
 
-__global__ void solve_kernel(float* __restrict__ io) {
-  float H[36], b[6], x[6], T[16];
-  for (int i = 0; i < 36; ++i) H[i] = io[i];
-  for (int i = 0; i < 6; ++i) b[i] = io[36 + i];
-  int info = 0;
-  solve6_dev(H, b, x, &info);
-  p2plane_T_dev(x, T);
-  for (int i = 0; i < 6; ++i) io[42 + i] = x[i];
-  for (int i = 0; i < 16; ++i) io[48 + i] = T[i];
-  io[64] = __int_as_float(info);
+// One warp, the same sequence the registration kernel runs (icp_fused.cu): the warp solve with its rank certificate
+// first, the serial reference-literal path only when that decides nothing (0) or replays a rank-deficient QR (2).
+// io[65] receives the warp path's return value (tests: certificate vs replay across the rank threshold).
+__global__ void __launch_bounds__(32) solve_kernel(float* __restrict__ io) {
+  __shared__ float H[36], b[6], x[6], x_spd[6];
+  __shared__ double W[98];
+  const int lane = threadIdx.x;
+  for (int i = lane; i < 36; i += 32) H[i] = io[i];
+  if (lane < 6) { b[lane] = io[36 + lane]; x[lane] = 0.f; x_spd[lane] = 0.f; }
+  __syncwarp();
+  const int fast = solve6_warp(H, b, x, W, x_spd);
+  __syncwarp();
+  if (lane == 0) {
+    int info = 0;
+    if (fast != 1) solve6_dev(H, b, x, &info, fast == 2 ? x_spd : nullptr);
+    float T[16];
+    p2plane_T_dev(x, T);
+    for (int i = 0; i < 6; ++i) io[42 + i] = x[i];
+    for (int i = 0; i < 16; ++i) io[48 + i] = T[i];
+    io[64] = __int_as_float(info);
+    io[65] = __int_as_float(fast);
+  }
 }
 
 __global__ void __launch_bounds__(kRedThreads) moments_kernel(const float4* __restrict__ read,
@@ -455,7 +467,7 @@ int p2plane_hessian_device(const float4* read, const float4* ref, const float* n
 }
 
 int p2plane_solve_device(float* io, cudaStream_t s) {
-  solve_kernel<<<1, 1, 0, s>>>(io);
+  solve_kernel<<<1, 32, 0, s>>>(io);
   B200_CUDA(cudaGetLastError());
   return B200_OK;
 }

@@ -244,10 +244,14 @@ __device__ inline bool pivqr_full_rank6_warp(const float* A, float* Q) {
 // unrolled register version (and the serial reference path) took 7-9 us per iteration, this one well under 2 us.
 //
 // Lanes 0..5 factor A = L D L^T in double (column j on lane j); lanes 8..13 run the SAME instructions on A - s I,
-// s = 8 * (6 eps_f) * trace(A), which is the rank certificate: every diagonal entry of any QR factor satisfies
-// |R_kk| >= sigma_min(A), and the reference's rank threshold is 6 eps_f * max|R_kk| <= 6 eps_f * trace(A) for a
-// symmetric positive semidefinite A; if A - s I is still positive definite then lambda_min(A) > s and
-// FullPivHouseholderQR (PointToPlane.cpp:202-203) finds full rank with an 8x margin. 1/d_k comes from a float seed
+// s = 2.8 * (6 eps_f) * cmax with cmax = the largest column norm of A, which is the rank certificate: every diagonal
+// entry of any QR factor satisfies |R_kk| >= sigma_min(A), and the reference's rank threshold is 6 eps_f * max|R_kk|
+// <= 6 eps_f * cmax (Householder reflections preserve column norms); if A - s I is still positive definite then
+// lambda_min(A) > s and FullPivHouseholderQR (PointToPlane.cpp:202-203) finds full rank. The factor 2.8 = 1 (the
+// threshold itself) + 1.8 of allowance for the ~eps_f |A| rounding of a FLOAT QR: an empirical margin, not a proven
+// bound — which is why a failed certificate does not decide anything: the QR rank decision is then replayed exactly
+// (pivqr_full_rank6_warp), and tests sweep lambda_min across 1x..4x the threshold against the oracle's rank decision
+// (tests/test_gpu_parity.py::test_solve_rank_threshold_band). 1/d_k comes from a float seed
 // and three Newton steps in double (IEEE double division/sqrt are long dependent sequences here); against
 // cond(A) ~ 1e4..1e5 the ~1 ulp quotient error is ~1e-11 relative in x, invisible after the cast to float.
 // Returns 1: x is final (full rank by the reference's criterion). 0: nothing decided, x untouched (asymmetric input or

@@ -212,6 +212,35 @@ def test_hessian_solve_and_p2point(matched):
     assert np.abs(Tpg - O.p2point_T(o["reading"], o["reference"], o["weights"], accum=0)).max() < 5e-5
 
 
+def test_solve_rank_threshold_band():
+    """The warp solve's rank certificate (lambda_min(A) > 2.8 x 6 eps_f x the largest column norm) and, where it does
+    not decide, the exact replay of the reference's float FullPivHouseholderQR rank test must reach the oracle's branch
+    (PointToPlane.cpp:199-256) for matrices whose smallest eigenvalue sits anywhere around that threshold."""
+    rng = np.random.default_rng(17)
+    eps = np.finfo(np.float32).eps
+    seen = set()
+    for trial in range(40):
+        Q, _ = np.linalg.qr(rng.normal(size=(6, 6)))
+        lam = np.array([1.0, 0.8, 0.6, 0.5, 0.3, 0.0]) * rng.uniform(0.5, 50.0)
+        cmax = lam[0]
+        for t in (0.05, 0.3, 0.6, 0.9, 1.0, 1.1, 1.5, 2.0, 2.8, 3.2, 4.0, 8.0, 100.0):
+            lam[5] = t * 6 * eps * cmax
+            H = ((Q * lam) @ Q.T).astype(np.float32)
+            H = ((H + H.T) * np.float32(0.5)).astype(np.float32)
+            b = (H.astype(np.float64) @ rng.normal(size=6)).astype(np.float32)
+            x, info = O.solve6(H, b)
+            xg, _, infog = B.p2plane_solve(H, b)
+            assert info == infog, (trial, t, info, infog)
+            seen.add(info)
+            if info == 0 and t >= 8.0:      # well-conditioned enough for the solutions to be comparable entry by entry
+                assert np.allclose(xg, x, rtol=2e-3, atol=1e-5), (trial, t)
+            else:                            # near-singular: compare through the residual the reference's isApprox uses
+                r0 = np.linalg.norm(H.astype(np.float64) @ x - b)
+                r1 = np.linalg.norm(H.astype(np.float64) @ xg - b)
+                assert r1 <= r0 * 1.5 + 1e-4 * max(np.linalg.norm(b), 1e-6), (trial, t, r0, r1)
+    assert 0 in seen and len(seen) >= 2      # both sides of the rank decision were exercised
+
+
 def test_rigid_apply_bit_exact(gold):
     rng = np.random.default_rng(9)
     f = O.feat4(gold["cloud0"])
