@@ -276,6 +276,11 @@ int b200_icp_init_reference_slab(b200_icp* icp, const float* ref4xM, const float
                                  const double* map_mean3, int axis, float lo, float hi);
 int b200_icp_slab_begin(b200_icp* icp, const float* read4xN, const float* readn3xN, int N, const float* Tinit16);
 int b200_icp_slab_match(b200_icp* icp, float* d_match9xN, int32_t* d_idN);
+/* the same, only enqueued on the handle's stream, and that stream (a cudaStream_t): a caller that runs its exchange on
+ * this stream (NCCL through torch: make it the current stream) needs no host synchronisation between the match, the
+ * all-reduces and b200_icp_slab_iterate, which is enqueued on it as well */
+int b200_icp_slab_match_async(b200_icp* icp, float* d_match9xN, int32_t* d_idN);
+void* b200_icp_slab_stream(b200_icp* icp);
 int b200_icp_slab_iterate(b200_icp* icp, const float* d_match9xN, const int32_t* d_idN, int* iterate);
 int b200_icp_slab_finish(b200_icp* icp, b200_icp_result* res);
 /* ICP::matches / ICP::outlierWeights of the last iteration (PointMatcher.h ICPChainBase members) */

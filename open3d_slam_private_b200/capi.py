@@ -432,6 +432,14 @@ class ICP:
     def slab_match(self, d_match, d_ids):
         _check(load().b200_icp_slab_match(self.h, C.c_void_p(int(d_match)), C.c_void_p(int(d_ids))))
 
+    def slab_match_async(self, d_match, d_ids):
+        _check(load().b200_icp_slab_match_async(self.h, C.c_void_p(int(d_match)), C.c_void_p(int(d_ids))))
+
+    def slab_stream(self):
+        f = load().b200_icp_slab_stream
+        f.restype = C.c_void_p
+        return f(self.h) or 0
+
     def slab_iterate(self, d_match, d_ids):
         it = C.c_int()
         _check(load().b200_icp_slab_iterate(self.h, C.c_void_p(int(d_match)), C.c_void_p(int(d_ids)), C.byref(it)))

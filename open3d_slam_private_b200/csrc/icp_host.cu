@@ -862,7 +862,12 @@ int b200_icp_slab_begin(b200_icp* h, const float* read4xN, const float* readn3xN
   return B200_OK;
 }
 
-int b200_icp_slab_match(b200_icp* h, float* d_match9xN, int32_t* d_idN) {
+static int slab_match_impl(b200_icp* h, float* d_match9xN, int32_t* d_idN, bool sync);
+int b200_icp_slab_match(b200_icp* h, float* d_match9xN, int32_t* d_idN) { return slab_match_impl(h, d_match9xN, d_idN, true); }
+int b200_icp_slab_match_async(b200_icp* h, float* d_match9xN, int32_t* d_idN) { return slab_match_impl(h, d_match9xN, d_idN, false); }
+void* b200_icp_slab_stream(b200_icp* h) { return h ? (void*)h->stream : nullptr; }
+
+static int slab_match_impl(b200_icp* h, float* d_match9xN, int32_t* d_idN, bool sync) {
   if (!h || !d_match9xN || !d_idN) { set_error("b200_icp_slab_match: bad arguments"); return B200_E_BAD_PARAM; }
   if (!h->slab || h->slab_started == 0) { set_error("b200_icp_slab_match: b200_icp_slab_begin first"); return B200_E_NOT_INITIALIZED; }
   DeviceGuard dg(h->device);
@@ -877,7 +882,7 @@ int b200_icp_slab_match(b200_icp* h, float* d_match9xN, int32_t* d_idN) {
                                                   h->slab_started == 2 ? h->d_state : nullptr, h->slab_axis, h->slab_lo,
                                                   h->slab_hi, m_pt, m_nrm, m_dist, d_idN);
   B200_CUDA(cudaGetLastError());
-  B200_CUDA(cudaStreamSynchronize(h->stream));   // the caller's exchange runs on its own stream
+  if (sync) B200_CUDA(cudaStreamSynchronize(h->stream));   // the caller's exchange runs on its own stream
   return B200_OK;
 }
 

@@ -179,6 +179,7 @@ class SlabPmICP:
         self.icp.init_reference_slab(slab4, slab_normals, gid, map_mean, axis, lo, hi)
         self.allreduce = allreduce
         self.fbuf = self.ibuf = None
+        self._ext = None
         self.collectives = 0
 
     def _buffers(self, n):
@@ -187,6 +188,7 @@ class SlabPmICP:
             dev = "cuda:%d" % self.device
             self.fbuf = torch.zeros(9 * n, dtype=torch.float32, device=dev)
             self.ibuf = torch.zeros(n, dtype=torch.int32, device=dev)
+            torch.cuda.synchronize(self.device)   # the fills ran on torch's stream, the kernels use the handle's
         return self.fbuf, self.ibuf
 
     def begin(self, read4, normals=None, T_init=None):
@@ -207,15 +209,20 @@ class SlabPmICP:
         torch = self.torch
         with torch.cuda.device(self.device):
             self.begin(read4, normals, T_init)
-            go = True
-            while go:
-                self.match()
-                if self.allreduce is not None:
-                    self.allreduce(self.fbuf)
-                    self.allreduce(self.ibuf)
-                    torch.cuda.current_stream().synchronize()
-                    self.collectives += 2
-                go = self.iterate()
+            # the exchange runs on the handle's own stream (made torch's current stream, so NCCL orders itself against
+            # it): match kernel -> all-reduces -> rest of the iteration with one host synchronisation per iteration (the
+            # read-back of `iterate`) instead of three
+            if self._ext is None:
+                self._ext = torch.cuda.ExternalStream(self.icp.slab_stream(), device=self.device)
+            with torch.cuda.stream(self._ext):
+                go = True
+                while go:
+                    self.icp.slab_match_async(self.fbuf.data_ptr(), self.ibuf.data_ptr())
+                    if self.allreduce is not None:
+                        self.allreduce(self.fbuf)
+                        self.allreduce(self.ibuf)
+                        self.collectives += 2
+                    go = self.iterate()
             res = self.icp.slab_finish(raise_on_error)
         res["collectives"] = self.collectives
         return res
