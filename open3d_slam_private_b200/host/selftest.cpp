@@ -10,6 +10,7 @@
 
 #include "pm_mirror.h"   // in the reference tree: #include "pointmatcher/PointMatcher.h"
 #include "b200_cloud_registration.hpp"
+#include "b200_place_recognition.hpp"
 #include "b200_pm_modules.hpp"
 
 using PM = PointMatcher<float>;
@@ -45,6 +46,9 @@ static PM::DataPoints plane_cloud(int n, unsigned seed, float dz, bool normals) 
 struct V3 { double v[3]; double& operator[](int i) { return v[i]; } const double& operator[](int i) const { return v[i]; } };
 struct Cloud { std::vector<V3> points_, normals_; };
 struct M4 { double m[16]; double& operator()(int i, int j) { return m[i + 4 * j]; } const double& operator()(int i, int j) const { return m[i + 4 * j]; } };
+// open3d::pipelines::registration::Feature as far as the shim touches it: data_(row, col), Resize(dim, n)
+struct FeatureData { std::vector<double> v; int rows = 0; double& operator()(int r, int c) { return v[r + (size_t)rows * c]; } const double& operator()(int r, int c) const { return v[r + (size_t)rows * c]; } };
+struct Feature { FeatureData data_; void Resize(int dim, int n) { data_.rows = dim; data_.v.assign((size_t)dim * n, 0.0); } };
 struct Result { M4 transformation_; std::vector<std::pair<int, int>> correspondence_set_; double fitness_ = 0, inlier_rmse_ = 0; };
 
 // The shims go through the reference's own plugin mechanism: ADD_TO_REGISTRAR lines (what INTEGRATION.md adds to
@@ -281,6 +285,42 @@ int main() {
     Result r2 = rk.registerClouds(srcN, tgt, I);
     std::printf("boundary B kind %d: tz %.5f fitness %.4f iterations %d\n", (int)k, r2.transformation_(2, 3), r2.fitness_, rk.lastIterations_);
     EXPECT(std::fabs(r2.transformation_(2, 3) + 0.08) < 0.02 && r2.fitness_ > 0.9);
+  }
+  // ---- loop-closure front half: FPFH of the target and of a moved copy of it, RANSAC brings the copy back
+  {
+    Cloud a = bare, b;              // `bare` got its normals from estimateNormalsOrCovariancesIfNeeded above
+    const double yaw = 0.2, c = std::cos(yaw), sn = std::sin(yaw), t[3] = {0.7, -0.4, 0.1};
+    for (size_t i = 0; i < a.points_.size(); ++i) {   // b = T^-1 a, so that T maps b (source) onto a (target)
+      const V3& p = a.points_[i];
+      const V3& n = a.normals_[i];
+      const double q[3] = {p[0] - t[0], p[1] - t[1], p[2] - t[2]};
+      b.points_.push_back(V3{{c * q[0] + sn * q[1], -sn * q[0] + c * q[1], q[2]}});
+      b.normals_.push_back(V3{{c * n[0] + sn * n[1], -sn * n[0] + c * n[1], n[2]}});
+    }
+    b200o3d::PlaceRecognitionB200 pr;
+    pr.featureRadius_ = 1.5; pr.featureKnn_ = 50;
+    pr.ransacMaxCorrespondenceDistance_ = 0.05; pr.correspondenceCheckerDistance_ = 0.05; pr.correspondenceCheckerEdgeLength_ = 0.9;
+    Feature fa, fb;
+    pr.computeFpfhFeature(a, &fa);
+    pr.computeFpfhFeature(b, &fb);
+    double colsum = 0.0;
+    for (int r = 0; r < 33; ++r) colsum += fa.data_(r, 0);
+    Result lc = pr.ransacFeatureMatching<Cloud, Feature, Result>(b, a, fb, fa);
+    std::printf("loop closure: fpfh column sum %.1f, ransac fitness %.3f corr %zu iterations %lld t (%.3f %.3f %.3f)\n", colsum,
+                lc.fitness_, lc.correspondence_set_.size(), (long long)pr.lastIterations_, lc.transformation_(0, 3),
+                lc.transformation_(1, 3), lc.transformation_(2, 3));
+    EXPECT(std::fabs(colsum - 600.0) < 1e-6 || colsum == 0.0);
+    EXPECT(lc.fitness_ > 0.5 && lc.correspondence_set_.size() >= 25);
+    EXPECT(std::fabs(lc.transformation_(0, 3) - t[0]) < 0.02 && std::fabs(lc.transformation_(1, 3) - t[1]) < 0.02 &&
+           std::fabs(lc.transformation_(2, 3) - t[2]) < 0.02);
+    std::vector<size_t> is, it;
+    pr.overlappingIndices(b, a, lc.transformation_, 0.3, 1, &is, &it);
+    EXPECT(is.size() > b.points_.size() * 9 / 10 && it.size() > a.points_.size() * 9 / 10);
+    bool threwF = false;
+    Cloud noN;
+    noN.points_ = a.points_;
+    try { pr.computeFpfhFeature(noN, &fa); } catch (const std::runtime_error&) { threwF = true; }
+    EXPECT(threwF);
   }
   std::printf(fails ? "selftest FAILED\n" : "selftest ok (device path)\n");
   return fails ? 1 : 0;
