@@ -197,6 +197,9 @@ __global__ void __launch_bounds__(kSpfhWarps * 32) spfh_kernel(const float4* __r
 }
 
 constexpr int kFpfhPts = 7;
+// Fallback for neighbourhoods too large for the shared-memory tile of fpfh_cta_kernel: 36 threads per point, every
+// thread walks the neighbours itself (dependent loads and one division per step: latency-bound, 0.73 ms for a
+// 6 000-point submap at knn 100 where the tile kernel takes a tenth of that).
 __global__ void __launch_bounds__(36 * kFpfhPts) fpfh_kernel(const float4* __restrict__ pts, const int* __restrict__ ids,
                                                             const int* __restrict__ cnt, int N, int k,
                                                             const double* __restrict__ spfh, double* __restrict__ out) {
@@ -234,6 +237,65 @@ __global__ void __launch_bounds__(36 * kFpfhPts) fpfh_kernel(const float4* __res
       v += spfh[(size_t)33 * i + x];
     }
     out[(size_t)33 * i + x] = v;
+  }
+}
+
+// One CTA per point. Phase A: the (neighbour, bin) quotients spfh[bin, id_k] / d_k are independent of one another, so
+// all 128 threads compute them with their loads in flight together and park them in a shared-memory tile [k][33]
+// (a skipped neighbour, d = 0, parks zeros: adding +0.0 to these non-negative sums changes nothing). Phase B: 33 threads
+// run the reference's neighbour-order recurrence of one bin each from the tile, 3 threads the group sums' (k, bin)
+// recurrence — the same additions in the same order as the fallback above and as the reference, with no load or
+// division left on the dependent chain.
+constexpr int kFpfhCtaThreads = 128;
+__global__ void __launch_bounds__(kFpfhCtaThreads) fpfh_cta_kernel(const float4* __restrict__ pts, const int* __restrict__ ids,
+                                                                  const int* __restrict__ cnt, int N, int k,
+                                                                  const double* __restrict__ spfh, double* __restrict__ out) {
+  extern __shared__ __align__(16) double s_val[];   // k x 33 quotients, then k distances, then k ids
+  __shared__ double s_sum[3];
+  const int i = blockIdx.x, tid = threadIdx.x;
+  const int n = cnt[i];
+  if (n <= 1) {
+    if (tid < 33) out[(size_t)33 * i + tid] = 0.0;
+    return;
+  }
+  double* s_dist = s_val + (size_t)33 * k;
+  int* s_id = reinterpret_cast<int*>(s_dist + k);
+  const float4 q = __ldg(&pts[i]);
+  const double qx = (double)q.x, qy = (double)q.y, qz = (double)q.z;
+  for (int t = 1 + tid; t < n; t += kFpfhCtaThreads) {
+    const int id = ids[(size_t)i * k + t];
+    const float4 p = __ldg(&pts[id]);
+    const double dx = (double)p.x - qx, dy = (double)p.y - qy, dz = (double)p.z - qz;
+    s_dist[t] = dx * dx + dy * dy + dz * dz;
+    s_id[t] = id;
+  }
+  __syncthreads();
+  const int pairs = (n - 1) * 33;
+  for (int p = tid; p < pairs; p += kFpfhCtaThreads) {
+    const int t = 1 + p / 33, j = p - (t - 1) * 33;
+    const double d = s_dist[t];
+    s_val[(size_t)33 * t + j] = d == 0.0 ? 0.0 : spfh[(size_t)33 * s_id[t] + j] / d;
+  }
+  __syncthreads();
+  double acc = 0.0;
+  if (tid < 33) {
+    for (int t = 1; t < n; ++t) acc += s_val[(size_t)33 * t + tid];
+  } else if (tid < 36) {
+    const int g0 = 11 * (tid - 33);
+    for (int t = 1; t < n; ++t) {
+      const double* v = s_val + (size_t)33 * t + g0;
+#pragma unroll
+      for (int j = 0; j < 11; ++j) acc += v[j];
+    }
+    s_sum[tid - 33] = acc;
+  }
+  __syncthreads();
+  if (tid < 33) {
+    double s = s_sum[tid / 11];
+    if (s != 0.0) s = 100.0 / s;
+    double v = acc * s;
+    v += spfh[(size_t)33 * i + tid];
+    out[(size_t)33 * i + tid] = v;
   }
 }
 
@@ -921,7 +983,13 @@ int b200_lc_compute_fpfh(b200_lc* h, const float* pts4xN, const double* normals3
   B200_CUDA(cudaGetLastError());
   spfh_kernel<<<(N + kSpfhWarps - 1) / kSpfhWarps, kSpfhWarps * 32, 0, s>>>(h->idx.d_ref, h->d_nrm, h->d_ids, h->d_cnt, N, max_nn, h->d_spfh);
   B200_CUDA(cudaGetLastError());
-  fpfh_kernel<<<(N + kFpfhPts - 1) / kFpfhPts, dim3(36, kFpfhPts), 0, s>>>(h->idx.d_ref, h->d_ids, h->d_cnt, N, max_nn, h->d_spfh, h->d_fpfh);
+  const size_t tile = (size_t)max_nn * (33 * sizeof(double) + sizeof(double) + sizeof(int));
+  if (tile <= 200 * 1024) {
+    if (tile > 48 * 1024) B200_CUDA(cudaFuncSetAttribute(fpfh_cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile));
+    fpfh_cta_kernel<<<N, kFpfhCtaThreads, tile, s>>>(h->idx.d_ref, h->d_ids, h->d_cnt, N, max_nn, h->d_spfh, h->d_fpfh);
+  } else {
+    fpfh_kernel<<<(N + kFpfhPts - 1) / kFpfhPts, dim3(36, kFpfhPts), 0, s>>>(h->idx.d_ref, h->d_ids, h->d_cnt, N, max_nn, h->d_spfh, h->d_fpfh);
+  }
   B200_CUDA(cudaGetLastError());
   B200_CUDA(cudaEventRecord(h->ev[1], s));
   int flag = 0;

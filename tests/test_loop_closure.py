@@ -205,7 +205,8 @@ def test_ransac_struct_sizes_match_header():
 def test_fpfh_small_cloud_vs_oracle():
     pts, nrm = small_cloud()
     lc = B.LoopClosure()
-    for radius, max_nn in ((0.8, 100), (1.5, 12), (0.3, 5), (100.0, 300)):
+    # max_nn 800: the neighbourhood tile no longer fits into shared memory, the per-thread fallback kernel runs
+    for radius, max_nn in ((0.8, 100), (1.5, 12), (0.3, 5), (100.0, 300), (100.0, 800)):
         f, cnt = lc.compute_fpfh(O.feat4(pts), nrm, radius, max_nn)
         g, gcnt = O.o3d_fpfh(O.feat4(pts), nrm, radius, max_nn)
         assert (cnt == gcnt).all()
