@@ -5,7 +5,8 @@
 Inputs (data files, not sources), all under /root/reference/libpointmatcher/examples/data/:
   cloud.00000.vtk / cloud.00001.vtk      ASCII VTK, xyz           (utest.cpp:83-84, BASELINE config C1)
   car_cloud400.csv / car_cloud401.csv    CSV x,y,z,nx,ny,nz       (utest.cpp:347-348)
-  icp_data/default{Identity,RemoveNaN,MaxDist,BoundingBox,PointToPlaneMinDist}DataPointsFilter.ref_trans
+  icp_data/default{Identity,RemoveNaN,MaxDist,BoundingBox,PointToPlaneMinDist,DistanceLimit,MaxQuantileOnAxis,
+           FixStepSampling,ObservationDirection,OrientNormals,SimpleSensorNoise}DataPointsFilter.ref_trans
                                                                   (utest.cpp:81-161 golden transforms)
 Reference goldens hard-coded in the reference's tests are restated in tests/golden/reference_goldens.json:
   validT3d (utest.cpp:355-359), icpSingular expected T (utest.cpp:195-197), icpIdentity (utest.cpp:203-220).
@@ -79,7 +80,10 @@ def main():
         # more deterministic configs of the same test (reading-side data-point filters that are plain masks)
         **{n + ".ref_trans": np.loadtxt(os.path.join(REF, "icp_data", n + ".ref_trans")).tolist()
            for n in ("defaultRemoveNaNDataPointsFilter", "defaultMaxDistDataPointsFilter",
-                     "defaultBoundingBoxDataPointsFilter", "defaultPointToPlaneMinDistDataPointsFilter")},
+                     "defaultBoundingBoxDataPointsFilter", "defaultPointToPlaneMinDistDataPointsFilter",
+                     "defaultDistanceLimitDataPointsFilter", "defaultMaxQuantileOnAxisDataPointsFilter",
+                     "defaultFixStepSamplingDataPointsFilter", "defaultObservationDirectionDataPointsFilter",
+                     "defaultOrientNormalsDataPointsFilter", "defaultSimpleSensorNoiseDataPointsFilter")},
         "ref_trans_criterion": "median|curT*data - refT*data| / median|curT*data| < 0.05 (utest.cpp:147-159)",
         "icpSingular_expected": [[1, 0, 0, 0], [0, 1, 0, 0], [0, 0, 1, 1], [0, 0, 0, 1]],
         "icpIdentity_epsilon": 1e-4,

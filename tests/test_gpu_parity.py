@@ -344,6 +344,26 @@ def test_icp_chain_variants(gold, kw):
     assert_icp_parity(o, g, icp)
 
 
+def test_device_pipeline_reaches_the_reference_goldens(gold):
+    """The reference's own end-to-end goldens (icp_data/*.ref_trans, criterion of utest.cpp:147-159) with NOTHING from
+    the oracle on the path: SurfaceNormalDataPointsFilter (knn 10) on the device for the reference cloud, then the
+    registration on the device — the three configs whose reading filters only add descriptors."""
+    ref4, data = O.feat4(gold["cloud0"]), O.feat4(gold["cloud1"])
+    nrm = B.surface_normals(ref4, knn=10)["normals"]
+    icp = B.ICP(B.default_icp_params(trimmed_ratio=0.75, max_iterations=40, min_diff_rot=0.001, min_diff_trans=0.01,
+                                     smooth_length=4))
+    icp.init_reference(ref4, nrm)
+    r = icp.compute(data)
+    assert r["status"] == 0
+    D = data.T.astype(np.float64)
+    cur = r["T"].astype(np.float64) @ D
+    for name in ("defaultObservationDirectionDataPointsFilter", "defaultOrientNormalsDataPointsFilter",
+                 "defaultSimpleSensorNoiseDataPointsFilter"):
+        refT = np.array(gold[name + ".ref_trans"])
+        rel = np.median(np.abs(cur - refT @ D)) / np.median(np.abs(cur))
+        assert rel < 0.05, (name, rel)
+
+
 def test_icp_surface_normal_filter(gold):
     ref4, refn = O.feat4(gold["c400"]["xyz"]), gold["c400"]["normals"]
     read4 = O.feat4(gold["c401"]["xyz"])

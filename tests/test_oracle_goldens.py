@@ -105,13 +105,23 @@ def _reading_filter(name, f4):
     if name == "defaultBoundingBoxDataPointsFilter":     # BoundingBox.cpp:82-107: xMin 0.2, rest default (-1 .. 1), removeInside
         inside = (x[:, 0] > 0.2) & (x[:, 0] < 1) & (x[:, 1] > -1) & (x[:, 1] < 1) & (x[:, 2] > -1) & (x[:, 2] < 1)
         return f4[~inside]
+    if name == "defaultDistanceLimitDataPointsFilter":   # DistanceLimit.cpp:75-93, dim = -1, removeInside 0: keep norm < |dist| (200)
+        return f4[np.linalg.norm(x, axis=1) < 200.0]
+    if name == "defaultMaxQuantileOnAxisDataPointsFilter":   # MaxQuantileOnAxis.cpp:62-92, dim 0, ratio 0.72
+        n = f4.shape[0]
+        limit = np.sort(x[:, 0])[int(n * 0.72)]              # nth_element at size * ratio, values[nbPointsOut]
+        return f4[x[:, 0] < limit]
+    if name == "defaultFixStepSamplingDataPointsFilter":     # FixStepSampling.cpp:72-86, step 10: columns phase, phase + 10, ...
+        return f4[3::10]                                     # phase = rand() % 10: glibc's first unseeded rand() is 1804289383
     raise KeyError(name)
 
 
 @pytest.mark.parametrize("name", ["defaultRemoveNaNDataPointsFilter", "defaultMaxDistDataPointsFilter",
-                                  "defaultBoundingBoxDataPointsFilter", "defaultPointToPlaneMinDistDataPointsFilter"])
+                                  "defaultBoundingBoxDataPointsFilter", "defaultPointToPlaneMinDistDataPointsFilter",
+                                  "defaultDistanceLimitDataPointsFilter", "defaultMaxQuantileOnAxisDataPointsFilter",
+                                  "defaultFixStepSamplingDataPointsFilter"])
 def test_ref_trans_more_deterministic_configs(gold, name):
-    """utest.cpp:81-161 for four more icp_data/*.yaml configs whose reading filter is a plain mask; the rest of the
+    """utest.cpp:81-161 for seven more icp_data/*.yaml configs whose reading filter is a plain mask; the rest of the
     chain is the one of defaultIdentityDataPointsFilter.yaml. Criterion as in the reference: relative median error of
     curT * data against refT * data below 5 % (data = the UNFILTERED reading, utest.cpp:147-159)."""
     rf, rn = O.sampling_surface_normal(O.feat4(gold["cloud0"]), knn=10, ratio=0.666666, sampling_method=1)
@@ -120,6 +130,28 @@ def test_ref_trans_more_deterministic_configs(gold, name):
     reading = np.ascontiguousarray(_reading_filter(name, data))
     assert 0 < reading.shape[0] <= data.shape[0]
     r = O.icp(p, rf, rn, reading)
+    assert r["status"] == 0
+    refT = np.array(gold[name + ".ref_trans"])
+    D = data.T.astype(np.float64)
+    cur = r["T"].astype(np.float64) @ D
+    rel = np.median(np.abs(cur - refT @ D)) / np.median(np.abs(cur))
+    assert rel < 0.05, rel
+
+
+@pytest.mark.parametrize("name", ["defaultObservationDirectionDataPointsFilter", "defaultOrientNormalsDataPointsFilter",
+                                  "defaultSimpleSensorNoiseDataPointsFilter"])
+def test_ref_trans_surface_normal_reference_configs(gold, name):
+    """utest.cpp:81-161 for three icp_data/*.yaml configs whose REFERENCE filter is the plain
+    SurfaceNormalDataPointsFilter (knn 10: every point kept) and whose reading filters only add descriptors
+    (SurfaceNormal, ObservationDirection, OrientNormals, SimpleSensorNoise leave the reading's points untouched and
+    point-to-plane uses the reference's normals only): pins the oracle's surface normals + ICP against the reference's
+    golden transforms."""
+    ref = O.feat4(gold["cloud0"])
+    st, sn = O.surface_normals(ref, 10)
+    assert st == 0
+    p = O.default_params(trimmed_ratio=0.75, max_iterations=40, min_diff_rot=0.001, min_diff_trans=0.01, smooth_length=4)
+    data = O.feat4(gold["cloud1"])
+    r = O.icp(p, ref, sn["normals"], data)
     assert r["status"] == 0
     refT = np.array(gold[name + ".ref_trans"])
     D = data.T.astype(np.float64)
