@@ -384,7 +384,11 @@ int b200_o3d_poll(b200_o3d* h, int* done, int* updates); /* synchronises the str
  *   b200_o3d_enqueue_peers per registration: enqueues every iteration (match+linearise, exchange+solve) on `stream`
  *                         (NULL: the handle's own) without any host synchronisation; b200_o3d_finish fetches the result.
  * All ranks must run the same registrations in the same order with the same max_iteration (the packets carry a
- * sequence number); a peer that does not deliver within 5 s makes b200_o3d_finish return B200_E_CUDA. */
+ * sequence number, consecutive across registrations); a peer that does not deliver within 5 s (B200_O3D_PEER_TIMEOUT_MS)
+ * makes b200_o3d_finish return B200_E_CUDA, after which the ranks are out of step: b200_o3d_peer_init +
+ * b200_o3d_peer_connect must be re-run on ALL ranks, collectively. The same holds for calling b200_o3d_peer_init again
+ * for any other reason: it frees this rank's mailbox, which the peers still have mapped — every rank must re-connect
+ * before the next registration. */
 int b200_o3d_peer_init(b200_o3d* h, int rank, int world, void** mailbox_dev /* nullable */, void* ipc_handle_64 /* nullable */);
 int b200_o3d_peer_connect(b200_o3d* h, void* const* mailboxes_dev /* nullable */, const int* devices /* nullable */,
                           const void* ipc_handles_64 /* nullable */);
