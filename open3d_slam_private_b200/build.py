@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 OBJDIR = os.path.join(HERE, "build")
-SOURCES = ["grid_index.cu", "modules.cu", "icp_fused.cu", "icp_host.cu", "o3d_icp.cu", "preprocess.cu", "no_alloc.cu", "normals_tile.cu", "map_maint.cu", "loop_closure.cu", "c_api.cu"]
+SOURCES = ["grid_index.cu", "modules.cu", "icp_fused.cu", "icp_fused_big.cu", "icp_host.cu", "o3d_icp.cu", "preprocess.cu", "no_alloc.cu", "normals_tile.cu", "map_maint.cu", "loop_closure.cu", "c_api.cu"]
 LIB = os.path.join(LIBDIR, "libb200reg.so")
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")

@@ -1279,6 +1279,21 @@ int launch_k(const IcpKernelParams& p, int device, cudaStream_t s, int* grid_out
 
 }  // namespace
 
+// The kernel is instantiated for five list sizes; the two large ones (k-best lists of 32 and 64) are compiled as a
+// translation unit of their own (icp_fused_big.cu includes this file with B200_ICP_FUSED_PART = 1) so that the two
+// halves build in parallel.
+#ifndef B200_ICP_FUSED_PART
+#define B200_ICP_FUSED_PART 0
+#endif
+
+#if B200_ICP_FUSED_PART == 1
+int launch_icp_kernel_big(const IcpKernelParams& p, int device, cudaStream_t s, int* grid_out) {
+  if (p.k <= 32) return launch_k<32>(p, device, s, grid_out);
+  return launch_k<64>(p, device, s, grid_out);   // the k-best list lives in local memory from here on
+}
+#else
+int launch_icp_kernel_big(const IcpKernelParams& p, int device, cudaStream_t s, int* grid_out);
+
 // candidates one CTA can park: every query it owns (rounds x threads)
 int icp_cand_segment(int nslots, int grid) {
   const int warps = grid * (kIcpThreads / 32);
@@ -1297,10 +1312,10 @@ int launch_icp_kernel(const IcpKernelParams& p, int device, cudaStream_t s, int*
   if (p.k <= 1) return launch_k<1>(p, device, s, grid_out);
   if (p.k <= 4) return launch_k<4>(p, device, s, grid_out);
   if (p.k <= 16) return launch_k<16>(p, device, s, grid_out);
-  if (p.k <= 32) return launch_k<32>(p, device, s, grid_out);
-  if (p.k <= 64) return launch_k<64>(p, device, s, grid_out);   // the k-best list lives in local memory from here on
+  if (p.k <= 64) return launch_icp_kernel_big(p, device, s, grid_out);
   set_error("ICP chain supports knn <= 64 (the limit of the matcher, b200_index_knn)");
   return B200_E_UNSUPPORTED;
 }
+#endif
 
 }  // namespace b200
