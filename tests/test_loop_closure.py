@@ -349,3 +349,74 @@ def test_overlap_indices_bit_exact():
     assert len(si) == 0 and len(ti) == 0
     with pytest.raises(B.B200Error):
         lc.overlap_indices(src4, tgt4, np.eye(4), 0.0, 1)
+
+
+def _splitmix(x):
+    m = (1 << 64) - 1
+    x &= m
+    x ^= x >> 30; x = (x * 0xbf58476d1ce4e5b9) & m
+    x ^= x >> 27; x = (x * 0x94d049bb133111eb) & m
+    x ^= x >> 31
+    return x
+
+
+def np_ransac(src, tgt, cs, ct, rn, max2, edge, dist_thr, max_iteration, confidence, seed):
+    """RegistrationRANSACBasedOnCorrespondence restated with numpy + python integers (independent of oracle/fpfh.cpp):
+    the documented sample stream, both checkers, Umeyama by numpy's SVD, the (fitness, rmse) order and the exit estimate"""
+    nc = len(cs)
+    S, D = src[cs].astype(np.float64), tgt[ct].astype(np.float64)
+    best_good, best_rmse, best_T = 0, 0.0, np.eye(4)
+    exit_itr, itr, validations = max_iteration, 0, 0
+    while itr < max_iteration and itr < exit_itr:
+        idx = [(((_splitmix(seed + (itr * rn + j) * 0x9e3779b97f4a7c15) >> 32) * nc) >> 32) for j in range(rn)]
+        itr += 1
+        s, d = S[idx], D[idx]
+        ok = True
+        if edge > 0:
+            for a in range(rn):
+                for b in range(a + 1, rn):
+                    ds, dt = np.linalg.norm(s[a] - s[b]), np.linalg.norm(d[a] - d[b])
+                    if ds < dt * edge or dt < ds * edge:
+                        ok = False
+        if not ok:
+            continue
+        ms, md = s.mean(0), d.mean(0)
+        U, _, Vt = np.linalg.svd((d - md).T @ (s - ms) / rn)
+        R = U @ np.diag([1.0, 1.0, np.sign(np.linalg.det(U) * np.linalg.det(Vt)) or 1.0]) @ Vt
+        T = np.eye(4); T[:3, :3] = R; T[:3, 3] = md - R @ ms
+        if dist_thr > 0 and (np.linalg.norm(s @ R.T + T[:3, 3] - d, axis=1) > dist_thr).any():
+            continue
+        validations += 1
+        e = ((S @ R.T + T[:3, 3] - D) ** 2).sum(1)
+        inl = e < max2
+        good = int(inl.sum())
+        rmse = float(np.sqrt(e[inl].sum() / good)) if good else 0.0
+        if good > best_good or (good == best_good and good > 0 and rmse < best_rmse):
+            best_good, best_rmse, best_T = good, rmse, T
+            pw = (good / nc) ** rn
+            if confidence < 1.0 and pw > 0:
+                k = 0.0 if pw >= 1.0 else np.log(1.0 - confidence) / np.log(1.0 - pw)
+                if 0 <= k < exit_itr:
+                    exit_itr = int(np.ceil(k))
+    return dict(T=best_T, good=best_good, rmse=best_rmse, iterations_run=itr, validations=validations)
+
+
+@pytest.mark.parametrize("seed,rn", [(5, 3), (6, 4), (7, 3)])
+def test_oracle_ransac_equals_numpy_restatement(seed, rn):
+    rng = np.random.default_rng(seed)
+    n = 500
+    src = rng.uniform(-10, 10, (n, 3)).astype(np.float32)
+    T = yaw_T(-0.4, [0.5, -1.0, 0.3])
+    tgt = (src.astype(np.float64) @ T[:3, :3].T + T[:3, 3] + 0.01 * rng.standard_normal((n, 3))).astype(np.float32)
+    feat = rng.uniform(0, 100, (n, 33))
+    tfeat = feat.copy()
+    wrong = rng.choice(n, 200, replace=False)                 # 40 % of the feature matches point at the wrong target
+    tfeat[wrong] = rng.uniform(0, 100, (200, 33))
+    kw = dict(mutual_filter=False, max_correspondence_distance=0.08, ransac_n=rn, edge_length_similarity=0.9,
+              distance_threshold=0.1, max_iteration=400, confidence=0.9999, seed=seed)
+    o = O.o3d_ransac(O.feat4(src), O.feat4(tgt), feat, tfeat, **kw)
+    ij, _ = O.o3d_feature_nn(feat, tfeat)
+    g = np_ransac(src, tgt, np.arange(n), ij, rn, 0.08 ** 2, 0.9, 0.1, 400, 0.9999, seed)
+    assert o["iterations_run"] == g["iterations_run"] and o["validations"] == g["validations"]
+    assert len(o["correspondences"]) == g["good"] and g["good"] > 100
+    assert np.abs(o["T"] - g["T"]).max() < 1e-9 and abs(o["inlier_rmse"] - g["rmse"]) < 1e-12
