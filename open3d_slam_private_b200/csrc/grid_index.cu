@@ -246,13 +246,18 @@ int upload_normals(float4* d_dst, const float* h_nrm3xN, int N, float* d_stage, 
 
 int index_alloc_points(MapIndex& idx, int M, bool with_normals) {
   if ((size_t)M > idx.cap_pts) {
+    // A handle that is re-initialised with clouds of varying size (the map patch cut around the robot at every
+    // reference update, a scan indexed per registration) grows with a quarter of headroom, so that a patch a few
+    // points larger than the largest so far does not cost four cudaFree + four cudaMalloc (milliseconds, and a device
+    // synchronisation) on the per-scan path; the first allocation is exact (a 5 M-point map is loaded once).
+    const size_t want = idx.cap_pts ? (size_t)M + (size_t)M / 4 : (size_t)M;
     cudaFree(idx.d_ref); cudaFree(idx.d_pts); cudaFree(idx.d_nrm_orig); cudaFree(idx.d_nrm);
     idx.d_ref = idx.d_pts = idx.d_nrm_orig = idx.d_nrm = nullptr;
     idx.cap_pts = 0;
-    const size_t bytes = std::max<size_t>(1, (size_t)M) * sizeof(float4);
+    const size_t bytes = std::max<size_t>(1, want) * sizeof(float4);
     B200_CUDA(cudaMalloc(&idx.d_ref, bytes));
     B200_CUDA(cudaMalloc(&idx.d_pts, bytes));
-    idx.cap_pts = (size_t)M;
+    idx.cap_pts = want;
   }
   if (with_normals && !idx.d_nrm_orig) {
     const size_t bytes = std::max<size_t>(1, idx.cap_pts) * sizeof(float4);
@@ -307,13 +312,14 @@ bool dims_for(const Extents& e, float cell, uint64_t max_cells, MapIndex& idx) {
 int ensure_table(MapIndex& idx) {
   const size_t need = idx.ncells() + 2;
   if (need > idx.cap_cells) {
+    const size_t want = idx.cap_cells ? need + need / 4 : need;   // same headroom rule as the point buffers
     cudaFree(idx.d_A); cudaFree(idx.d_tile);
     idx.d_A = idx.d_tile = nullptr;
     idx.cap_cells = 0;
-    B200_CUDA(cudaMalloc(&idx.d_A, need * sizeof(uint32_t)));
-    const size_t tiles = (need + kScanTile - 1) / kScanTile;
+    B200_CUDA(cudaMalloc(&idx.d_A, want * sizeof(uint32_t)));
+    const size_t tiles = (want + kScanTile - 1) / kScanTile;
     B200_CUDA(cudaMalloc(&idx.d_tile, std::max<size_t>(1, tiles) * sizeof(uint32_t)));
-    idx.cap_cells = need;
+    idx.cap_cells = want;
     idx.cap_tiles = tiles;
   }
   return B200_OK;
