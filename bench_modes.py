@@ -483,9 +483,9 @@ def mode_lc(ctx, steps=5):
         sp, _, _ = prep.voxel_downsample(0.5, synth.feat4(xyz))          # featureVoxelSize_
         vox_ms = prep.last_device_ms()
         sp4 = synth.feat4(sp.astype(np.float32))
-        nrm = est.estimate_normals(sp4, knn=10, radius=1.0)              # normalKnn_, normalEstimationRadius_
-        f, cnt = lc.compute_fpfh(sp4, nrm, 2.5, 100)                     # featureRadius_, featureKnn_
-        return sp4, nrm, f, cnt, vox_ms, lc.last_device_ms(), (time.perf_counter() - t0) * 1e3
+        # normalKnn_ / normalEstimationRadius_ and featureRadius_ / featureKnn_ on one index, normals stay on the device
+        nrm, f = lc.compute_features(sp4, normal_radius=1.0, normal_knn=10, fpfh_radius=2.5, fpfh_max_nn=100)
+        return sp4, nrm, f, None, vox_ms, lc.last_device_ms(), (time.perf_counter() - t0) * 1e3
 
     fp_ms, wall_ms, rs_ms, rs_wall = [], [], [], []
     for it in range(steps + 1):
@@ -500,11 +500,10 @@ def mode_lc(ctx, steps=5):
     dT = np.linalg.inv(p["T_true"]) @ r["T"]
     ms = float(np.median(fp_ms))
     per_pt = 16 + 24 + 4 * 100 + 33 * 8 * 2    # point, normal, neighbour ids, SPFH written + FPFH written
-    out = {"what": "loop-closure front half on a C4 pair (%d-point submaps -> %d / %d sparse points): FPFH (radius 2.5, "
-                   "knn 100) per submap, then RANSAC feature matching (1 M iterations max, confidence 0.99, mutual filter, "
+    out = {"what": "loop-closure front half on a C4 pair (%d-point submaps -> %d / %d sparse points): normals (radius 1, knn 10) + FPFH (radius 2.5, "
+                   "knn 100) per submap in one call, then RANSAC feature matching (1 M iterations max, confidence 0.99, mutual filter, "
                    "distance + edge-length checkers)" % (args.pair_points, len(s4), len(t4)),
-           "ms": ms, "value": n_sp / (ms * 1e-3), "unit": "points/s (FPFH)", "fpfh_device_ms": stats(fp_ms),
-           "fpfh_mean_neighbours": float((scnt.mean() + tcnt.mean()) / 2),
+           "ms": ms, "value": n_sp / (ms * 1e-3), "unit": "points/s (normals + FPFH)", "fpfh_device_ms": stats(fp_ms),
            "ransac_device_ms": stats(rs_ms), "ransac_iterations_run": int(r["iterations_run"]),
            "ransac_validations": int(r["validations"]), "ransac_feature_correspondences": int(r["n_feature_correspondences"]),
            "ransac_inlier_correspondences": int(len(r["correspondences"])), "ransac_fitness": float(r["fitness"]),
@@ -521,14 +520,15 @@ def mode_lc(ctx, steps=5):
         from oracle import oracle_py as O
         cores = os.cpu_count() or 1
         t0 = time.perf_counter()
-        of, _ = O.o3d_fpfh(s4, sn, 2.5, 100, threads=cores)
+        on, _ = O.o3d_estimate_normals(s4, 10, 1.0, threads=cores)
+        of, _ = O.o3d_fpfh(s4, on, 2.5, 100, threads=cores)
         s_f = time.perf_counter() - t0
         t0 = time.perf_counter()
         o = O.o3d_ransac(s4, t4, sf, tf, seed=steps + 1, threads=cores)
         s_r = time.perf_counter() - t0
-        out["cpu_baseline"] = {"value": len(s4) / s_f, "unit": "points/s (FPFH)", "cores": cores, "kind": "port",
+        out["cpu_baseline"] = {"value": len(s4) / s_f, "unit": "points/s (normals + FPFH)", "cores": cores, "kind": "port",
                                "ms": s_f * 1e3, "ransac_ms": s_r * 1e3,
-                               "sample": "FPFH of the source submap and one RANSAC feature matching, oracle on %d threads "
+                               "sample": "normals + FPFH of the source submap and one RANSAC feature matching, oracle on %d threads "
                                          "(Open3D's own loops are OpenMP-parallel)" % cores}
         out["parity"] = {"fpfh_max_abs_diff_median": float(np.median(np.abs(of - sf).max(1))),
                          "ransac_T_max_abs_diff": float(np.abs(o["T"] - r["T"]).max()),

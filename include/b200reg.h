@@ -497,6 +497,13 @@ void b200_lc_destroy(b200_lc* h);
  * max_nn <= 2048; nn_count_N (nullable) receives the neighbourhood sizes. N = 0 returns B200_OK. */
 int b200_lc_compute_fpfh(b200_lc* h, const float* pts4xN, const double* normals3xN, int N, float radius, int max_nn,
                          double* fpfh33xN, int32_t* nn_count_N);
+/* The whole feature step of Submap::computeFeatures after the voxel down-sample (Submap.cpp:269-272) in one call and on
+ * one index: EstimateNormals(KDTreeSearchParamHybrid(normalEstimationRadius_, normalKnn_)) + NormalizeNormals +
+ * OrientNormalsTowardsCameraLocation(origin) (the semantics of b200_o3d_estimate_normals; normal_knn <= 32), then
+ * ComputeFPFHFeature as above on those normals, which never leave the device (normals3xN nullable: returned when the
+ * caller wants sparseMapCloud_.normals_ filled). Equal to b200_o3d_estimate_normals followed by b200_lc_compute_fpfh. */
+int b200_lc_compute_features(b200_lc* h, const float* pts4xN, int N, float normal_radius, int normal_knn, float fpfh_radius,
+                             int fpfh_max_nn, double* normals3xN, double* fpfh33xN);
 /* the feature-space search of RegistrationRANSACBasedOnFeatureMatching (KDTreeFlann(feature).SearchKNN(col, 1)):
  * exact nearest column of b for every column of a, squared L2 in double summed in bin order, ties -> smallest
  * index. d2_N nullable. */

@@ -696,6 +696,17 @@ class LoopClosure:
                                            out.ctypes.data_as(dp), _ip(cnt)))
         return out, cnt
 
+    def compute_features(self, pts4, normal_radius=1.0, normal_knn=10, fpfh_radius=2.5, fpfh_max_nn=100):
+        """normals (Open3D semantics) + FPFH on one index -> (normals (N, 3) float64, features (N, 33) float64)"""
+        pts4 = f32(pts4)
+        n = pts4.shape[0]
+        nrm, out = np.empty((n, 3), np.float64), np.empty((n, 33), np.float64)
+        dp = C.POINTER(C.c_double)
+        _check(load().b200_lc_compute_features(self._h, _fp(pts4), n, C.c_float(normal_radius), int(normal_knn),
+                                               C.c_float(fpfh_radius), int(fpfh_max_nn), nrm.ctypes.data_as(dp),
+                                               out.ctypes.data_as(dp)))
+        return nrm, out
+
     def feature_nn(self, a, b):
         """exact nearest row of b (M, 33) for every row of a (N, 33) -> (ids int32, squared distances float64)"""
         a, b = np.ascontiguousarray(a, np.float64), np.ascontiguousarray(b, np.float64)

@@ -35,10 +35,13 @@
 #include <algorithm>
 #include "grid_index.cuh"
 #include "knn.cuh"
+#include "normals.cuh"
 
 namespace b200 {
 int inclusive_scan_u32(uint32_t* d_data, size_t n, uint32_t* d_tile, cudaStream_t s);   // preprocess.cu
 size_t scan_tiles_for(size_t n);
+int o3d_normals_from_ids_device(const int* ids, int knn, const float4* pts_by_id, const float4* q, int M, double* out_d,
+                                int out_by_id, cudaStream_t s);   // o3d_icp.cu
 namespace {
 
 constexpr int kHKThreads = 128;
@@ -956,12 +959,10 @@ void b200_lc_destroy(b200_lc* h) {
   delete h;
 }
 
-int b200_lc_compute_fpfh(b200_lc* h, const float* pts4xN, const double* normals3xN, int N, float radius, int max_nn,
-                         double* fpfh33xN, int32_t* nn_count_N) {
-  if (!h || N < 0 || (N > 0 && (!pts4xN || !normals3xN || !fpfh33xN))) { set_error("b200_lc_compute_fpfh: bad arguments"); return B200_E_BAD_PARAM; }
-  if (max_nn < 1 || max_nn > kHKCap) { set_error("b200_lc_compute_fpfh: max_nn must be in 1..2048"); return B200_E_BAD_PARAM; }
-  if (!(radius > 0.f) || std::isinf(radius)) { set_error("b200_lc_compute_fpfh: radius must be positive and finite"); return B200_E_BAD_PARAM; }
-  if (N == 0) return B200_OK;
+// normals3xN == nullptr: the normals are estimated on the device first (est_knn, est_radius; Open3D semantics) on the
+// same index and optionally returned through normals_out3xN
+static int lc_fpfh_impl(b200_lc* h, const float* pts4xN, const double* normals3xN, int N, float radius, int max_nn,
+                        double* fpfh33xN, int32_t* nn_count_N, int est_knn, float est_radius, double* normals_out3xN) {
   DeviceGuard dg(h->device);
   if (!dg.ok) return cuda_fail(cudaErrorInvalidDevice, "cudaSetDevice", __FILE__, __LINE__);
   cudaStream_t s = h->stream;
@@ -972,12 +973,17 @@ int b200_lc_compute_fpfh(b200_lc* h, const float* pts4xN, const double* normals3
   B200_TRY(grow(&h->d_fpfh, &h->cap_fpfh, (size_t)33 * N));
   B200_TRY(grow(&h->d_ids, &h->cap_ids, (size_t)max_nn * N));
   B200_TRY(grow(&h->d_cnt, &h->cap_cnt, (size_t)N));
-  B200_CUDA(cudaMemcpyAsync(h->d_nrm, normals3xN, (size_t)3 * N * sizeof(double), cudaMemcpyHostToDevice, s));
+  if (normals3xN) B200_CUDA(cudaMemcpyAsync(h->d_nrm, normals3xN, (size_t)3 * N * sizeof(double), cudaMemcpyHostToDevice, s));
   B200_CUDA(cudaMemsetAsync(h->d_flag, 0, sizeof(int), s));
   B200_CUDA(cudaEventRecord(h->ev[0], s));
   b200_index_opts opts;
   std::memset(&opts, 0, sizeof(opts));
   B200_TRY(index_build(h->idx, &opts));
+  if (!normals3xN) {
+    int* nids = nullptr;
+    B200_TRY(self_knn_ids_index(h->idx, est_knn, est_radius, true, &nids, s));
+    B200_TRY(o3d_normals_from_ids_device(nids, est_knn, h->idx.d_ref, h->idx.d_pts, N, h->d_nrm, 1, s));
+  }
   const GridView g = h->idx.view();
   hybrid_knn_kernel<<<N, kHKThreads, 0, s>>>(g, h->idx.d_ref, N, max_nn, radius * radius, h->d_ids, h->d_cnt, h->d_flag);
   B200_CUDA(cudaGetLastError());
@@ -996,6 +1002,7 @@ int b200_lc_compute_fpfh(b200_lc* h, const float* pts4xN, const double* normals3
   B200_CUDA(cudaMemcpyAsync(&flag, h->d_flag, sizeof(int), cudaMemcpyDeviceToHost, s));
   B200_CUDA(cudaMemcpyAsync(fpfh33xN, h->d_fpfh, (size_t)33 * N * sizeof(double), cudaMemcpyDeviceToHost, s));
   if (nn_count_N) B200_CUDA(cudaMemcpyAsync(nn_count_N, h->d_cnt, (size_t)N * sizeof(int), cudaMemcpyDeviceToHost, s));
+  if (normals_out3xN) B200_CUDA(cudaMemcpyAsync(normals_out3xN, h->d_nrm, (size_t)3 * N * sizeof(double), cudaMemcpyDeviceToHost, s));
   B200_CUDA(cudaStreamSynchronize(s));
   cudaEventElapsedTime(&h->last_ms, h->ev[0], h->ev[1]);
   if (flag) {
@@ -1003,6 +1010,25 @@ int b200_lc_compute_fpfh(b200_lc* h, const float* pts4xN, const double* normals3
     return B200_E_UNSUPPORTED;
   }
   return B200_OK;
+}
+
+int b200_lc_compute_fpfh(b200_lc* h, const float* pts4xN, const double* normals3xN, int N, float radius, int max_nn,
+                         double* fpfh33xN, int32_t* nn_count_N) {
+  if (!h || N < 0 || (N > 0 && (!pts4xN || !normals3xN || !fpfh33xN))) { set_error("b200_lc_compute_fpfh: bad arguments"); return B200_E_BAD_PARAM; }
+  if (max_nn < 1 || max_nn > kHKCap) { set_error("b200_lc_compute_fpfh: max_nn must be in 1..2048"); return B200_E_BAD_PARAM; }
+  if (!(radius > 0.f) || std::isinf(radius)) { set_error("b200_lc_compute_fpfh: radius must be positive and finite"); return B200_E_BAD_PARAM; }
+  if (N == 0) return B200_OK;
+  return lc_fpfh_impl(h, pts4xN, normals3xN, N, radius, max_nn, fpfh33xN, nn_count_N, 0, 0.f, nullptr);
+}
+
+int b200_lc_compute_features(b200_lc* h, const float* pts4xN, int N, float normal_radius, int normal_knn, float fpfh_radius,
+                             int fpfh_max_nn, double* normals3xN, double* fpfh33xN) {
+  if (!h || N < 0 || (N > 0 && (!pts4xN || !fpfh33xN))) { set_error("b200_lc_compute_features: bad arguments"); return B200_E_BAD_PARAM; }
+  if (normal_knn < 1 || normal_knn > 32 || !(normal_radius > 0.f)) { set_error("b200_lc_compute_features: normal_knn in 1..32, normal_radius > 0"); return B200_E_BAD_PARAM; }
+  if (fpfh_max_nn < 1 || fpfh_max_nn > kHKCap) { set_error("b200_lc_compute_features: fpfh_max_nn must be in 1..2048"); return B200_E_BAD_PARAM; }
+  if (!(fpfh_radius > 0.f) || std::isinf(fpfh_radius)) { set_error("b200_lc_compute_features: fpfh_radius must be positive and finite"); return B200_E_BAD_PARAM; }
+  if (N == 0) return B200_OK;
+  return lc_fpfh_impl(h, pts4xN, nullptr, N, fpfh_radius, fpfh_max_nn, fpfh33xN, nullptr, normal_knn, normal_radius, normals3xN);
 }
 
 int b200_lc_feature_nn(b200_lc* h, const double* a33xN, int N, const double* b33xM, int M, int32_t* nn_N, double* d2_N) {

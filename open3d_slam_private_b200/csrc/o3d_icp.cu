@@ -623,6 +623,17 @@ __global__ void __launch_bounds__(kThreads) o3d_estimate_normals_kernel(const in
 
 }  // namespace
 
+namespace b200 {
+// for loop_closure.cu: Open3D normals (o3d_estimate_normals_kernel) from neighbour lists that are already on the device
+int o3d_normals_from_ids_device(const int* ids, int knn, const float4* pts_by_id, const float4* q, int M, double* out_d,
+                                int out_by_id, cudaStream_t s) {
+  o3d_estimate_normals_kernel<<<(M + kThreads - 1) / kThreads, kThreads, 0, s>>>(ids, knn, pts_by_id, q, M, nullptr, out_d,
+                                                                                 out_by_id);
+  B200_CUDA(cudaGetLastError());
+  return B200_OK;
+}
+}  // namespace b200
+
 struct b200_o3d {
   int device = 0;
   b200_o3d_params prm;

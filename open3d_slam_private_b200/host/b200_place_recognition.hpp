@@ -60,6 +60,29 @@ class PlaceRecognitionB200 {
       for (int r = 0; r < 33; ++r) feature->data_(r, i) = out[33 * (size_t)i + r];
   }
 
+  // Submap::computeFeatures after the voxel down-sample (Submap.cpp:269-272) in one call: EstimateNormals(Hybrid(
+  // normalEstimationRadius_, normalKnn_)) + NormalizeNormals + OrientNormalsTowardsCameraLocation(0) + ComputeFPFHFeature
+  // on one device index; fills cloud->normals_ like the reference's sequence does
+  double normalEstimationRadius_ = 1.0;   // Parameters.hpp:122
+  int normalKnn_ = 10;                    // Parameters.hpp:126
+  template <class Cloud, class Feature>
+  void estimateNormalsAndComputeFpfh(Cloud* cloud, Feature* feature) {
+    ensure();
+    const int n = (int)cloud->points_.size();
+    feature->Resize(33, n);
+    cloud->normals_.resize(n);
+    if (n == 0) return;
+    std::vector<float> f4;
+    to_feat4(cloud->points_, f4);
+    std::vector<double> nrm(3 * (size_t)n), out(33 * (size_t)n);
+    check(b200_lc_compute_features(h_, f4.data(), n, (float)normalEstimationRadius_, normalKnn_, (float)featureRadius_, featureKnn_,
+                                   nrm.data(), out.data()));
+    for (int i = 0; i < n; ++i) {
+      for (int d = 0; d < 3; ++d) cloud->normals_[i][d] = nrm[3 * (size_t)i + d];
+      for (int r = 0; r < 33; ++r) feature->data_(r, i) = out[33 * (size_t)i + r];
+    }
+  }
+
   template <class Cloud, class Feature, class Result>
   Result ransacFeatureMatching(const Cloud& source, const Cloud& target, const Feature& sourceFeature,
                                const Feature& targetFeature) {

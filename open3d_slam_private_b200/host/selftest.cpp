@@ -303,6 +303,18 @@ int main() {
     Feature fa, fb;
     pr.computeFpfhFeature(a, &fa);
     pr.computeFpfhFeature(b, &fb);
+    {   // the one-call variant on a cloud without normals gives the same features as normals-then-FPFH on `a`
+      Cloud a2;
+      a2.points_ = a.points_;
+      Feature fa2;
+      pr.normalEstimationRadius_ = reg.maxRadiusNormalEstimation_; pr.normalKnn_ = reg.knnNormalEstimation_;
+      pr.estimateNormalsAndComputeFpfh(&a2, &fa2);
+      bool same = a2.normals_.size() == a.normals_.size();
+      for (size_t i = 0; same && i < a.normals_.size(); ++i)
+        for (int d = 0; d < 3; ++d) same = same && a2.normals_[i][d] == a.normals_[i][d];
+      for (size_t i = 0; same && i < fa.data_.v.size(); ++i) same = same && fa2.data_.v[i] == fa.data_.v[i];
+      EXPECT(same);
+    }
     double colsum = 0.0;
     for (int r = 0; r < 33; ++r) colsum += fa.data_(r, 0);
     Result lc = pr.ransacFeatureMatching<Cloud, Feature, Result>(b, a, fb, fa);

@@ -420,3 +420,20 @@ def test_oracle_ransac_equals_numpy_restatement(seed, rn):
     assert o["iterations_run"] == g["iterations_run"] and o["validations"] == g["validations"]
     assert len(o["correspondences"]) == g["good"] and g["good"] > 100
     assert np.abs(o["T"] - g["T"]).max() < 1e-9 and abs(o["inlier_rmse"] - g["rmse"]) < 1e-12
+
+
+@pytest.mark.gpu
+def test_compute_features_equals_normals_then_fpfh():
+    """Submap::computeFeatures' normals + FPFH in one call on one index = b200_o3d_estimate_normals followed by
+    b200_lc_compute_fpfh, bit for bit (the normals never leave the device in between)"""
+    p = submap_pair()
+    lc = B.LoopClosure()
+    est = B.O3dICP(kind=0)
+    for pts in (p["t4"], p["s4"][:3000]):
+        nrm = est.estimate_normals(pts, knn=10, radius=1.0)
+        f, _ = lc.compute_fpfh(pts, nrm, 2.5, 100)
+        n2, f2 = lc.compute_features(pts, normal_radius=1.0, normal_knn=10, fpfh_radius=2.5, fpfh_max_nn=100)
+        assert np.array_equal(n2, nrm) and np.array_equal(f2, f)
+    est.close()
+    with pytest.raises(B.B200Error):
+        lc.compute_features(p["t4"], normal_knn=64)
