@@ -35,9 +35,10 @@ METRIC = "icp_registrations_per_s_128k_scan_vs_5M_map"
 
 
 # dram bytes per launch of icp_persistent_kernel<1> on the default workload, from the committed ncu capture
-NCU_TRAFFIC_BYTES_PER_LAUNCH = 9.38e6
+# (round-2 capture, two launches: 7.83 + 0.44 MB and 9.81 + 0.38 MB; their mean)
+NCU_TRAFFIC_BYTES_PER_LAUNCH = 9.23e6
 NCU_TRAFFIC_SOURCE = ("dram__bytes_read.sum + dram__bytes_write.sum, ncu --set full, "
-                      "profiles/r01_icp_kernel_final3_ncu_summary.txt (default workload only)")
+                      "profiles/r02_icp_kernel_ncu_summary.txt (default workload only)")
 
 
 
