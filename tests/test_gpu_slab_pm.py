@@ -91,3 +91,39 @@ def test_slab_handle_error_paths():
     with pytest.raises(B.B200Error):
         B.ICP(B.default_icp_params(knn=3)).init_reference_slab(map4, mapn, None, mean, 0, -np.inf, np.inf)
     icp.close()
+
+
+def test_stream_ordered_driver_on_one_slab():
+    """partition.SlabPmICP.register — the multi-rank driver: match enqueued on the handle's own stream
+    (b200_icp_slab_match_async), the exchange ordered on that stream (b200_icp_slab_stream as torch's current stream), one
+    host synchronisation per iteration — with a single slab and an in-place "all-reduce" that adds nothing: the result is
+    the whole-map run bit for bit, twice in a row on the same handle."""
+    import os
+    import torch
+    from open3d_slam_private_b200 import capi as B, partition as P
+    g = os.path.join(os.path.dirname(__file__), "golden")
+    c400, c401 = np.load(os.path.join(g, "car_cloud400.npz")), np.load(os.path.join(g, "car_cloud401.npz"))
+    map4, mapn, read4 = O.feat4(c400["xyz"]), c400["normals"], O.feat4(c401["xyz"])
+    prm = B.default_icp_params(maxDist=0.5, trimmed_ratio=0.9, max_iterations=30, min_diff_trans=0.008)
+    whole = B.ICP(prm)
+    whole.init_reference(map4, mapn)
+    r0 = whole.compute(read4, None, None)
+    m0 = whole.matches()
+    whole.close()
+    mean = r0["T_refIn_refMean"][:3, 3].astype(np.float64)
+    calls = []
+
+    def fake_allreduce(t):            # runs on the current stream = the handle's: ordering, not arithmetic, is under test
+        calls.append(int(torch.cuda.current_stream().cuda_stream))
+        t.add_(0)
+
+    pm = P.SlabPmICP(map4, mapn, np.arange(map4.shape[0], dtype=np.int32), mean, 0, -np.inf, np.inf, params=prm,
+                     allreduce=fake_allreduce)
+    for rep in range(2):
+        r1 = pm.register(read4)
+        assert r1["status"] == 0 and r1["iterations"] == r0["iterations"]
+        assert (bits(r1["T"]) == bits(r0["T"])).all()
+        ids, d, w = pm.matches()
+        assert np.array_equal(ids, m0[0]) and (bits(d) == bits(m0[1])).all() and (bits(w) == bits(m0[2])).all()
+    assert calls and all(c == pm.icp.slab_stream() for c in calls)
+    pm.close()
