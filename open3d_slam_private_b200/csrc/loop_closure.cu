@@ -84,17 +84,32 @@ __global__ void __launch_bounds__(kHKThreads) hybrid_knn_kernel(const GridView g
       }
     }
     __syncthreads();
-    if (pass == 0 && tid == 0) {
-      unsigned cum = 0;
-      int b = 0;
-      for (; b < kHKBins; ++b) {
-        cum += hist[b];
-        if (cum >= (unsigned)k) break;
+    if (pass == 0 && warp == 0) {
+      // first bin at which the running count reaches k: a lane sums its 32 bins (rotated start: no bank conflicts), the
+      // warp scans the 32 sums, the lane the count crosses in walks its own bins (one thread walking all 1024 left
+      // the other 127 at the barrier for most of the CTA's life: ncu, profiles/r02_lc_kernels_ncu_summary.txt)
+      static_assert(kHKBins == 32 * 32, "one lane per 32 bins");
+      unsigned own = 0;
+      for (int j = 0; j < 32; ++j) own += hist[lane * 32 + ((j + lane) & 31)];
+      unsigned inc = own;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const unsigned v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
       }
-      if (b < kHKBins) {              // at least k in the ball: everything up to the k-th one's bin
+      const unsigned crossed = __ballot_sync(0xffffffffu, inc >= (unsigned)k);
+      if (crossed == 0u) {            // fewer than k in the ball: all of them
+        if (lane == 31 && inc > (unsigned)kHKCap) s_bad = 1;
+      } else if (lane == __ffs(crossed) - 1) {   // at least k: everything up to the k-th one's bin
+        unsigned cum = inc - own;
+        int b = lane * 32;
+        for (;; ++b) {
+          cum += hist[b];
+          if (cum >= (unsigned)k) break;
+        }
         s_thr = b;
         if (cum > (unsigned)kHKCap) s_bad = 1;
-      } else if (cum > (unsigned)kHKCap) s_bad = 1;
+      }
     }
     __syncthreads();
     if (s_bad) {   // more equal-distance candidates than the sort buffer holds: reported, not guessed
