@@ -119,6 +119,20 @@ __global__ void __launch_bounds__(kHKThreads) hybrid_knn_kernel(const GridView g
     }
   }
   const int n = s_n;
+  if (n <= 2 * kHKThreads) {
+    // short lists (the usual case: ~100 in the ball): a key's place is the number of smaller keys (keys are distinct:
+    // the index is part of them) — broadcast reads, no barrier; same order as the sort below
+    const int m = min(n, k);
+    for (int t = tid; t < n; t += kHKThreads) {
+      const unsigned long long mine = keys[t];
+      int rank = 0;
+      for (int j = 0; j < n; ++j) rank += keys[j] < mine ? 1 : 0;
+      if (rank < k) ids[(size_t)i * k + rank] = (int)(unsigned)(mine & 0xffffffffull);
+    }
+    for (int t = m + tid; t < k; t += kHKThreads) ids[(size_t)i * k + t] = -1;
+    if (tid == 0) cnt[i] = m;
+    return;
+  }
   int P = 1;
   while (P < n) P <<= 1;
   for (int t = n + tid; t < P; t += kHKThreads) keys[t] = ~0ull;
